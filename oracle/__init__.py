@@ -1,0 +1,264 @@
+"""CPU oracles for the succinct column-segment codec -- TEST INFRASTRUCTURE ONLY.
+
+Only tests/, ``__graft_entry__.smoke()`` and bench.py's ``cpu_baseline`` / ``--impl reference`` legs may
+import this package.  The product path (duckdb_adaptive_compression_b200) never does.
+
+Two interchangeable back ends behind one ctypes wrapper (`Oracle`):
+
+* ``kind="port"``      -> oracle/liboracle.so, the SDSL-free C restatement (succinct_oracle.c, "L1").
+* ``kind="reference"`` -> oracle/_ref/libadacom_ref.so, ref_harness.cpp linked with the reference's own
+  vendored SDSL compiled from /root/reference ("L0").  Present whenever `make -C oracle ref` ran in a
+  container that has /root/reference; the built .so travels to the GPU box.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from dataclasses import dataclass
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+L1_PATH = os.path.join(HERE, "liboracle.so")
+L0_PATH = os.path.join(HERE, "_ref", "libadacom_ref.so")
+
+PADDED = 1
+LITERAL = 2
+
+CMP_EQ, CMP_NE, CMP_LT, CMP_GT, CMP_LE, CMP_GE = range(6)
+
+VECTOR_SIZE = 2048       # STANDARD_VECTOR_SIZE (vector_size.hpp:17)
+BLOCK_SIZE = 262144 - 8  # Storage::BLOCK_SIZE (constants.hpp:101-106)
+
+_FIELDS = dict(count=0, width=1, bit_size=2, min_factor=3, max_factor=4, compacted=5, repacked=6, function=7,
+               words=8, num_elements=9)
+
+
+def build(force: bool = False) -> None:
+    """Compile the L1 port and, when /root/reference is present, the L0 reference harness."""
+    if force or not os.path.exists(L1_PATH) or (
+            os.path.getmtime(L1_PATH) < os.path.getmtime(os.path.join(HERE, "succinct_oracle.c"))):
+        subprocess.check_call(["make", "-C", HERE, "l1"], stdout=subprocess.DEVNULL)
+    subprocess.check_call(["make", "-C", HERE, "ref"], stdout=subprocess.DEVNULL)
+
+
+def have_reference() -> bool:
+    return os.path.exists(L0_PATH)
+
+
+class _BenchResult(C.Structure):
+    _fields_ = [("analyze_s", C.c_double), ("encode_s", C.c_double), ("scan_s", C.c_double), ("sum_s", C.c_double),
+                ("values", C.c_uint64), ("sum_lo", C.c_uint64), ("sum_hi", C.c_uint64), ("sum_count", C.c_uint64),
+                ("packed_bytes", C.c_uint64)]
+
+
+class _Sum128(C.Structure):
+    _fields_ = [("lo", C.c_uint64), ("hi", C.c_uint64), ("count", C.c_uint64)]
+
+
+@dataclass
+class SegmentMeta:
+    count: int
+    width: int
+    bit_size: int
+    min_factor: int
+    max_factor: int
+    compacted: bool
+    repacked: bool
+    function: int
+    words: int
+    data_size: int
+
+
+def _ptr(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Oracle:
+    """ctypes front end shared by the L1 port (prefix orc_) and the L0 reference harness (prefix ref_)."""
+
+    def __init__(self, kind: str = "port"):
+        if kind == "port":
+            if not os.path.exists(L1_PATH):
+                build()
+            self.lib = C.CDLL(L1_PATH)
+            self.p = "orc_"
+        elif kind == "reference":
+            if not os.path.exists(L0_PATH):
+                raise FileNotFoundError(f"{L0_PATH} missing: run `make -C oracle ref` where /root/reference exists")
+            self.lib = C.CDLL(L0_PATH)
+            self.p = "ref_"
+        else:
+            raise ValueError(kind)
+        self.kind = kind
+        f = self._f
+        f("segment_new_succinct", C.c_void_p, [C.c_uint8, C.c_int, C.c_uint64])
+        f("segment_new_uncompressed", C.c_void_p, [C.c_uint8, C.c_int, C.c_uint64])
+        f("segment_delete", None, [C.c_void_p])
+        f("segment_append", C.c_uint64, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64])
+        f("segment_append_uncompressed", C.c_uint64, [C.c_void_p, C.c_void_p, C.c_uint64])
+        f("bit_compress_from_succinct", None, [C.c_void_p, C.c_int])
+        f("bit_compress_from_uncompressed", None, [C.c_void_p, C.c_int])
+        f("scan_partial", None, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint64, C.c_int])
+        f("uncompress_succinct", None, [C.c_void_p, C.c_int])
+        f("segment_data_size", C.c_uint64, [C.c_void_p])
+        f("segment_get", C.c_uint64, [C.c_void_p, C.c_int])
+        f("segment_words", C.c_void_p, [C.c_void_p])
+        f("segment_block", C.c_void_p, [C.c_void_p])
+        f("segment_serialize", C.c_uint64, [C.c_void_p, C.c_void_p, C.c_uint64])
+        f("bits_hi", C.c_uint32, [C.c_uint64])
+        f("bench_column", C.c_int, [C.c_void_p, C.c_uint64, C.c_uint8, C.c_int, C.c_uint64, C.c_int, C.c_int,
+                                    C.POINTER(_BenchResult)])
+        if kind == "port":
+            f("segment_sum", None, [C.c_void_p, C.c_int, C.POINTER(_Sum128)])
+            f("segment_filter", None, [C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.POINTER(_Sum128), C.c_void_p])
+            f("fetch_row", None, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_int])
+
+    def _f(self, name, restype, argtypes):
+        fn = getattr(self.lib, self.p + name)
+        fn.restype = restype
+        fn.argtypes = argtypes
+        setattr(self, "_" + name, fn)
+
+    # ---- segment life cycle ----
+    def new_succinct(self, dtype, segment_size=BLOCK_SIZE) -> "OracleSegment":
+        dt = np.dtype(dtype)
+        h = self._segment_new_succinct(dt.itemsize, int(dt.kind == "i"), segment_size)
+        return OracleSegment(self, h, dt, segment_size)
+
+    def new_uncompressed(self, dtype, segment_size=BLOCK_SIZE) -> "OracleSegment":
+        dt = np.dtype(dtype)
+        h = self._segment_new_uncompressed(dt.itemsize, int(dt.kind == "i"), segment_size)
+        return OracleSegment(self, h, dt, segment_size)
+
+    def bits_hi(self, x: int) -> int:
+        return int(self._bits_hi(x & 0xFFFFFFFFFFFFFFFF))
+
+    def encode(self, values: np.ndarray, flags: int = 0, validity: np.ndarray | None = None,
+               segment_size: int | None = None) -> "OracleSegment":
+        """append (2048 values per call, like ColumnData::AppendData) + BitCompressFromSuccinct."""
+        values = np.ascontiguousarray(values)
+        if segment_size is None:
+            segment_size = BLOCK_SIZE
+        seg = self.new_succinct(values.dtype, segment_size)
+        for off in range(0, len(values), VECTOR_SIZE):
+            m = min(VECTOR_SIZE, len(values) - off)
+            seg.append(values, off, m, validity=validity)
+        seg.bit_compress(flags)
+        return seg
+
+    def encode_adaptive(self, values: np.ndarray, flags: int = 0, segment_size: int | None = None) -> "OracleSegment":
+        values = np.ascontiguousarray(values)
+        if segment_size is None:
+            segment_size = BLOCK_SIZE
+        seg = self.new_uncompressed(values.dtype, segment_size)
+        seg.append_uncompressed(values)
+        seg.bit_compress_from_uncompressed(flags)
+        return seg
+
+    def bench_column(self, values: np.ndarray, seg_capacity: int, threads: int, copy_per_call: bool = False) -> dict:
+        values = np.ascontiguousarray(values)
+        res = _BenchResult()
+        rc = self._bench_column(_ptr(values), len(values), values.dtype.itemsize, int(values.dtype.kind == "i"),
+                                seg_capacity, threads, int(copy_per_call), C.byref(res))
+        if rc != 0:
+            raise RuntimeError("bench_column failed")
+        return dict(analyze_s=res.analyze_s, encode_s=res.encode_s, scan_s=res.scan_s, sum_s=res.sum_s,
+                    values=res.values, sum=(res.sum_hi << 64) | res.sum_lo, packed_bytes=res.packed_bytes)
+
+
+class OracleSegment:
+    def __init__(self, oracle: Oracle, handle, dtype: np.dtype, segment_size: int):
+        self.o, self.h, self.dtype, self.segment_size = oracle, handle, dtype, segment_size
+
+    def __del__(self):
+        try:
+            if self.h:
+                self.o._segment_delete(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def get(self, field: str) -> int:
+        return int(self.o._segment_get(self.h, _FIELDS[field]))
+
+    def meta(self) -> SegmentMeta:
+        g = self.get
+        return SegmentMeta(g("count"), g("width"), g("bit_size"), g("min_factor"), g("max_factor"),
+                           bool(g("compacted")), bool(g("repacked")), g("function"), g("words"), self.data_size())
+
+    def append(self, values: np.ndarray, offset: int, count: int, sel: np.ndarray | None = None,
+               validity: np.ndarray | None = None) -> int:
+        assert values.dtype == self.dtype and values.flags.c_contiguous
+        selp = _ptr(np.ascontiguousarray(sel, dtype=np.uint32)) if sel is not None else None
+        valp = _ptr(validity) if validity is not None else None
+        if validity is not None:
+            assert validity.dtype == np.uint64 and validity.flags.c_contiguous
+        return int(self.o._segment_append(self.h, _ptr(values), selp, valp, offset, count))
+
+    def append_uncompressed(self, values: np.ndarray) -> int:
+        assert values.dtype == self.dtype and values.flags.c_contiguous
+        return int(self.o._segment_append_uncompressed(self.h, _ptr(values), len(values)))
+
+    def bit_compress(self, flags: int = 0) -> None:
+        self.o._bit_compress_from_succinct(self.h, flags)
+
+    def bit_compress_from_uncompressed(self, flags: int = 0) -> None:
+        self.o._bit_compress_from_uncompressed(self.h, flags)
+
+    def scan_partial(self, start: int, scan_count: int, flags: int = 0, result: np.ndarray | None = None,
+                     result_offset: int = 0) -> np.ndarray:
+        if result is None:
+            result = np.zeros(result_offset + scan_count, dtype=self.dtype)
+        self.o._scan_partial(self.h, start, scan_count, _ptr(result), result_offset, flags)
+        return result
+
+    def decode_all(self, flags: int = 0) -> np.ndarray:
+        n = self.get("count")
+        out = np.zeros(n, dtype=self.dtype)
+        for off in range(0, n, VECTOR_SIZE):
+            m = min(VECTOR_SIZE, n - off)
+            self.o._scan_partial(self.h, off, m, _ptr(out), off, flags)
+        return out
+
+    def uncompress(self, flags: int = 0) -> np.ndarray:
+        n = self.get("bit_size") // max(self.get("width"), 1)
+        self.o._uncompress_succinct(self.h, flags)
+        raw = (C.c_uint8 * self.segment_size).from_address(self.o._segment_block(self.h))
+        return np.frombuffer(bytes(raw), dtype=self.dtype, count=n)
+
+    def data_size(self) -> int:
+        return int(self.o._segment_data_size(self.h))
+
+    def words(self) -> np.ndarray:
+        n = self.get("words")
+        if n == 0:
+            return np.zeros(0, dtype=np.uint64)
+        buf = (C.c_uint64 * n).from_address(self.o._segment_words(self.h))
+        return np.frombuffer(bytes(buf), dtype=np.uint64)
+
+    def serialize(self) -> bytes:
+        cap = self.data_size() + 16
+        buf = (C.c_uint8 * cap)()
+        n = self.o._segment_serialize(self.h, buf, cap)
+        return bytes(buf[:n])
+
+    # ---- port-only helpers ----
+    def sum(self, flags: int = 0) -> tuple[int, int]:
+        r = _Sum128()
+        self.o._segment_sum(self.h, flags, C.byref(r))
+        return ((r.hi << 64) | r.lo), int(r.count)
+
+    def filter(self, op: int, constant: int, flags: int = 0, want_bitmap: bool = False):
+        r = _Sum128()
+        n = self.get("count")
+        bm = np.zeros((n + 63) // 64, dtype=np.uint64) if want_bitmap else None
+        self.o._segment_filter(self.h, flags, op, constant & 0xFFFFFFFFFFFFFFFF, C.byref(r),
+                               _ptr(bm) if bm is not None else None)
+        return ((r.hi << 64) | r.lo), int(r.count), bm
+
+    def fetch_row(self, row_id: int, flags: int = 0):
+        out = np.zeros(1, dtype=self.dtype)
+        self.o._fetch_row(self.h, row_id, _ptr(out), 0, flags)
+        return out[0]
