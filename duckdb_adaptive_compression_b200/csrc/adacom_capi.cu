@@ -1,0 +1,1193 @@
+// adacom_capi.cu -- host implementation of the C ABI declared in include/adacom_gpu.h.
+//
+// Owns the HBM layout of a column (raw arena, packed extents, descriptor table), builds the work-unit
+// tables and enqueues the kernels of kernels_{encode,decode,misc}.cu on the context's compute stream.
+// There is no CPU compute path in this file: every entry point either launches kernels or fails.
+#include "../../include/adacom_gpu.h"
+#include "adacom_kernels.cuh"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+using namespace adacom;
+
+static_assert(sizeof(adacom_segment_meta) == 64, "adacom_segment_meta must stay 64 bytes");
+static_assert(sizeof(adacom_agg) == sizeof(Agg), "adacom_agg layout");
+
+namespace {
+std::string g_process_error;
+constexpr uint8_t kSegUncompressedFn = 8;  // function swapped to UNCOMPRESSED by Uncompact (GetDataSize rule)
+constexpr size_t kArenaPad = 256;          // slack behind every arena for the 16-byte rounded bulk copies
+}  // namespace
+
+struct adacom_ctx {
+	int device = 0;
+	int sm_count = 148;
+	cudaStream_t stream = nullptr;
+	std::string err;
+	uint64_t launches = 0;
+	std::mutex mu;
+	void *flush_buf = nullptr;
+	size_t flush_bytes = 0;
+	Agg *d_agg = nullptr;
+	unsigned long long *d_totals = nullptr;
+	Agg *h_agg = nullptr;                 // pinned
+	unsigned long long *h_totals = nullptr;  // pinned
+};
+
+struct Extent {
+	uint64_t *base = nullptr;
+	uint64_t words = 0;
+	uint64_t live = 0;  // repacked segments still pointing into this extent
+};
+
+struct JobTable {
+	uint64_t begin = 0, end = 0;
+	uint64_t epoch = ~0ull;
+	Job *d_jobs = nullptr;
+	uint32_t n = 0;
+	size_t capacity = 0;
+};
+
+struct adacom_column {
+	adacom_ctx *ctx = nullptr;
+	adacom_ptype ptype = ADACOM_INT64;
+	TypeInfo t {8, true};
+	uint64_t n_values = 0;
+	uint64_t n_segs = 0;
+	uint8_t *raw = nullptr;
+	SegDesc *d_desc = nullptr;
+	std::vector<SegDesc> h_desc;
+	bool mirror_dirty = false;
+	std::vector<Extent> extents;
+	JobTable tiles, chunks;
+	uint64_t epoch = 0;
+};
+
+namespace {
+
+adacom_status fail(adacom_ctx *ctx, adacom_status st, const std::string &msg) {
+	if (ctx) {
+		ctx->err = msg;
+	} else {
+		g_process_error = msg;
+	}
+	return st;
+}
+
+#define CK(ctx, call)                                                                                        \
+	do {                                                                                                     \
+		cudaError_t e__ = (call);                                                                            \
+		if (e__ != cudaSuccess) {                                                                            \
+			return fail((ctx), e__ == cudaErrorMemoryAllocation ? ADACOM_ERR_NOMEM : ADACOM_ERR_CUDA,       \
+			            std::string(#call) + ": " + cudaGetErrorString(e__));                               \
+		}                                                                                                    \
+	} while (0)
+
+#define LAUNCH(ctx, call)  \
+	do {                   \
+		CK((ctx), (call)); \
+		(ctx)->launches++; \
+	} while (0)
+
+bool type_info(adacom_ptype p, TypeInfo &t) {
+	switch (p) {
+	case ADACOM_UINT8: t = {1, false}; return true;
+	case ADACOM_INT8: t = {1, true}; return true;
+	case ADACOM_UINT16: t = {2, false}; return true;
+	case ADACOM_INT16: t = {2, true}; return true;
+	case ADACOM_UINT32: t = {4, false}; return true;
+	case ADACOM_INT32: t = {4, true}; return true;
+	case ADACOM_UINT64: t = {8, false}; return true;
+	case ADACOM_INT64: t = {8, true}; return true;
+	default: return false;
+	}
+}
+
+adacom_status sync_mirror(adacom_column *col) {
+	adacom_ctx *ctx = col->ctx;
+	if (col->mirror_dirty) {
+		CK(ctx, cudaMemcpyAsync(col->h_desc.data(), col->d_desc, col->n_segs * sizeof(SegDesc), cudaMemcpyDeviceToHost,
+		                        ctx->stream));
+		CK(ctx, cudaStreamSynchronize(ctx->stream));
+		col->mirror_dirty = false;
+	}
+	return ADACOM_OK;
+}
+
+adacom_status upload_jobs(adacom_column *col, JobTable &tab, const std::vector<Job> &jobs) {
+	adacom_ctx *ctx = col->ctx;
+	if (jobs.size() > tab.capacity) {
+		if (tab.d_jobs) {
+			CK(ctx, cudaFreeAsync(tab.d_jobs, ctx->stream));
+			tab.d_jobs = nullptr;
+		}
+		tab.capacity = jobs.size() + jobs.size() / 8 + 64;
+		CK(ctx, cudaMallocAsync((void **)&tab.d_jobs, tab.capacity * sizeof(Job), ctx->stream));
+	}
+	if (!jobs.empty()) {
+		// pageable source: the copy is staged before the call returns, so `jobs` may go out of scope
+		CK(ctx, cudaMemcpyAsync(tab.d_jobs, jobs.data(), jobs.size() * sizeof(Job), cudaMemcpyHostToDevice, ctx->stream));
+	}
+	tab.n = (uint32_t)jobs.size();
+	return ADACOM_OK;
+}
+
+// 2048-value tiles of [b, e): depends on the segment counts only
+adacom_status get_tiles(adacom_column *col, uint64_t b, uint64_t e) {
+	JobTable &tab = col->tiles;
+	if (tab.begin == b && tab.end == e && tab.epoch == 0) {
+		return ADACOM_OK;
+	}
+	std::vector<Job> jobs;
+	for (uint64_t g = b; g < e; g++) {
+		uint32_t n = (col->h_desc[g].count + kVectorSize - 1) / kVectorSize;
+		for (uint32_t k = 0; k < n; k++) {
+			jobs.push_back({(uint32_t)g, k});
+		}
+	}
+	adacom_status st = upload_jobs(col, tab, jobs);
+	if (st == ADACOM_OK) {
+		tab.begin = b;
+		tab.end = e;
+		tab.epoch = 0;
+	}
+	return st;
+}
+
+// <=16 KiB scan chunks of [b, e): depends on the current widths -> needs the mirror
+adacom_status get_chunks(adacom_column *col, uint64_t b, uint64_t e) {
+	JobTable &tab = col->chunks;
+	if (tab.begin == b && tab.end == e && tab.epoch == col->epoch) {
+		return ADACOM_OK;
+	}
+	adacom_status st = sync_mirror(col);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	std::vector<Job> jobs;
+	for (uint64_t g = b; g < e; g++) {
+		const SegDesc &d = col->h_desc[g];
+		uint32_t gran = scan_chunk_values(d.width);
+		uint32_t n = (d.count + gran - 1) / gran;
+		for (uint32_t k = 0; k < n; k++) {
+			jobs.push_back({(uint32_t)g, k});
+		}
+	}
+	st = upload_jobs(col, tab, jobs);
+	if (st == ADACOM_OK) {
+		tab.begin = b;
+		tab.end = e;
+		tab.epoch = col->epoch;
+	}
+	return st;
+}
+
+bool range_ok(const adacom_column *col, uint64_t b, uint64_t e) {
+	return col && b <= e && e <= col->n_segs;
+}
+
+uint64_t seg_bits(const SegDesc &d, int type_size) {
+	return (d.state & kSegRepacked) ? (uint64_t)d.count * d.width : (uint64_t)d.capacity * 8u * (uint64_t)type_size;
+}
+
+void fill_meta(const adacom_column *col, uint64_t g, adacom_segment_meta *m) {
+	const SegDesc &d = col->h_desc[g];
+	memset(m, 0, sizeof(*m));
+	m->row_start = d.row_start;
+	m->count = d.count;
+	m->word_offset = d.word_offset;
+	m->words = (d.state & kSegRepacked) ? ((uint64_t)d.count * d.width + 63) >> 6 : 0;
+	m->min_factor = d.min_factor;
+	m->max_factor = d.max_factor;
+	if (d.state & kSegUncompressedFn) {
+		m->size_in_bytes = (uint64_t)d.capacity * col->t.size;  // ColumnSegment::segment_size
+	} else {
+		m->size_in_bytes = 9 + 8 * ((seg_bits(d, col->t.size) + 63) >> 6);  // sdsl::size_in_bytes
+	}
+	m->width = d.width;
+	m->state = d.state;
+	m->type_size = (uint8_t)col->t.size;
+	m->is_signed = col->t.is_signed;
+	m->capacity = d.capacity;
+}
+
+adacom_status ensure_raw(adacom_column *col) {
+	if (!col->raw) {
+		CK(col->ctx, cudaMalloc((void **)&col->raw, col->n_values * col->t.size + kArenaPad));
+	}
+	return ADACOM_OK;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------------
+// context
+// ---------------------------------------------------------------------------------------------------
+
+extern "C" int adacom_abi_version(void) {
+	return ADACOM_ABI_VERSION;
+}
+
+extern "C" const char *adacom_last_error(const adacom_ctx *ctx) {
+	return ctx ? ctx->err.c_str() : g_process_error.c_str();
+}
+
+extern "C" adacom_status adacom_ctx_create(int device, adacom_ctx **out) {
+	if (!out) {
+		return fail(nullptr, ADACOM_ERR_INVALID, "adacom_ctx_create: out is NULL");
+	}
+	*out = nullptr;
+	int n = 0;
+	cudaError_t e = cudaGetDeviceCount(&n);
+	if (e != cudaSuccess || n == 0) {
+		return fail(nullptr, ADACOM_ERR_NO_DEVICE,
+		            std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0") +
+		                " (this codec has no CPU fallback)");
+	}
+	if (device < 0 || device >= n) {
+		return fail(nullptr, ADACOM_ERR_INVALID, "adacom_ctx_create: device ordinal out of range");
+	}
+	cudaDeviceProp prop;
+	CK(nullptr, cudaGetDeviceProperties(&prop, device));
+	if (prop.major != 10) {
+		return fail(nullptr, ADACOM_ERR_NO_DEVICE,
+		            std::string("device '") + prop.name + "' is sm_" + std::to_string(prop.major * 10 + prop.minor) +
+		                "; the kernels are built for sm_100a only");
+	}
+	CK(nullptr, cudaSetDevice(device));
+	adacom_ctx *ctx = new (std::nothrow) adacom_ctx();
+	if (!ctx) {
+		return fail(nullptr, ADACOM_ERR_NOMEM, "out of host memory");
+	}
+	ctx->device = device;
+	ctx->sm_count = prop.multiProcessorCount;
+	CK(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+	CK(nullptr, cudaMalloc((void **)&ctx->d_agg, sizeof(Agg)));
+	CK(nullptr, cudaMalloc((void **)&ctx->d_totals, 4 * sizeof(unsigned long long)));
+	CK(nullptr, cudaHostAlloc((void **)&ctx->h_agg, sizeof(Agg), cudaHostAllocDefault));
+	CK(nullptr, cudaHostAlloc((void **)&ctx->h_totals, 4 * sizeof(unsigned long long), cudaHostAllocDefault));
+	// keep freed extents cached in the stream-ordered pool instead of returning them to the driver
+	cudaMemPool_t pool;
+	if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+		uint64_t threshold = ~0ull;
+		cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold);
+	}
+	*out = ctx;
+	return ADACOM_OK;
+}
+
+extern "C" void adacom_ctx_destroy(adacom_ctx *ctx) {
+	if (!ctx) {
+		return;
+	}
+	cudaSetDevice(ctx->device);
+	cudaStreamSynchronize(ctx->stream);
+	cudaFree(ctx->flush_buf);
+	cudaFree(ctx->d_agg);
+	cudaFree(ctx->d_totals);
+	cudaFreeHost(ctx->h_agg);
+	cudaFreeHost(ctx->h_totals);
+	cudaStreamDestroy(ctx->stream);
+	delete ctx;
+}
+
+extern "C" adacom_status adacom_ctx_synchronize(adacom_ctx *ctx) {
+	if (!ctx) {
+		return ADACOM_ERR_INVALID;
+	}
+	CK(ctx, cudaStreamSynchronize(ctx->stream));
+	return ADACOM_OK;
+}
+
+extern "C" void *adacom_ctx_stream(adacom_ctx *ctx) {
+	return ctx ? (void *)ctx->stream : nullptr;
+}
+
+extern "C" uint64_t adacom_ctx_launch_count(const adacom_ctx *ctx) {
+	return ctx ? ctx->launches : 0;
+}
+
+extern "C" adacom_status adacom_event_create(adacom_ctx *ctx, void **event_out) {
+	if (!ctx || !event_out) {
+		return ADACOM_ERR_INVALID;
+	}
+	cudaEvent_t ev;
+	CK(ctx, cudaEventCreate(&ev));
+	*event_out = (void *)ev;
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_event_record(adacom_ctx *ctx, void *event) {
+	if (!ctx || !event) {
+		return ADACOM_ERR_INVALID;
+	}
+	CK(ctx, cudaEventRecord((cudaEvent_t)event, ctx->stream));
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_event_elapsed_ms(adacom_ctx *ctx, void *start, void *stop, float *ms_out) {
+	if (!ctx || !start || !stop || !ms_out) {
+		return ADACOM_ERR_INVALID;
+	}
+	CK(ctx, cudaEventSynchronize((cudaEvent_t)stop));
+	CK(ctx, cudaEventElapsedTime(ms_out, (cudaEvent_t)start, (cudaEvent_t)stop));
+	return ADACOM_OK;
+}
+
+extern "C" void adacom_event_destroy(adacom_ctx *ctx, void *event) {
+	(void)ctx;
+	if (event) {
+		cudaEventDestroy((cudaEvent_t)event);
+	}
+}
+
+extern "C" adacom_status adacom_host_alloc(adacom_ctx *ctx, size_t bytes, void **out) {
+	if (!ctx || !out) {
+		return ADACOM_ERR_INVALID;
+	}
+	cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault);
+	if (e != cudaSuccess) {
+		*out = nullptr;
+		return fail(ctx, ADACOM_ERR_NOMEM, std::string("cudaHostAlloc: ") + cudaGetErrorString(e));
+	}
+	return ADACOM_OK;
+}
+
+extern "C" void adacom_host_free(adacom_ctx *ctx, void *ptr) {
+	(void)ctx;
+	if (ptr) {
+		cudaFreeHost(ptr);
+	}
+}
+
+extern "C" adacom_status adacom_flush_l2(adacom_ctx *ctx) {
+	if (!ctx) {
+		return ADACOM_ERR_INVALID;
+	}
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	if (!ctx->flush_buf) {
+		ctx->flush_bytes = (size_t)256 << 20;  // 2x the 126 MB L2
+		CK(ctx, cudaMalloc(&ctx->flush_buf, ctx->flush_bytes));
+	}
+	CK(ctx, cudaMemsetAsync(ctx->flush_buf, 0, ctx->flush_bytes, ctx->stream));
+	return ADACOM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// column life cycle
+// ---------------------------------------------------------------------------------------------------
+
+static adacom_status column_alloc(adacom_ctx *ctx, adacom_ptype type, uint64_t n_segments, adacom_column **out) {
+	TypeInfo t;
+	if (!type_info(type, t)) {
+		return fail(ctx, ADACOM_ERR_UNSUPPORTED, "physical type not supported by the succinct codec");
+	}
+	if (n_segments >= (1ull << 32)) {
+		return fail(ctx, ADACOM_ERR_INVALID, "too many segments");
+	}
+	adacom_column *col = new (std::nothrow) adacom_column();
+	if (!col) {
+		return fail(ctx, ADACOM_ERR_NOMEM, "out of host memory");
+	}
+	col->ctx = ctx;
+	col->ptype = type;
+	col->t = t;
+	col->n_segs = n_segments;
+	col->h_desc.assign(n_segments, SegDesc());
+	*out = col;
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_column_create(adacom_ctx *ctx, adacom_ptype type, uint64_t n_segments,
+                                              const uint64_t *seg_counts, uint32_t seg_capacity, adacom_column **out) {
+	if (!ctx || !out || (n_segments && !seg_counts)) {
+		return fail(ctx, ADACOM_ERR_INVALID, "adacom_column_create: NULL argument");
+	}
+	*out = nullptr;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	CK(ctx, cudaSetDevice(ctx->device));
+	adacom_column *col = nullptr;
+	adacom_status st = column_alloc(ctx, type, n_segments, &col);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	const uint32_t cap = seg_capacity ? seg_capacity : kBlockSize / (uint32_t)col->t.size;
+	uint64_t row = 0;
+	for (uint64_t g = 0; g < n_segments; g++) {
+		if (seg_counts[g] > cap) {
+			delete col;
+			return fail(ctx, ADACOM_ERR_INVALID, "segment count exceeds its capacity");
+		}
+		SegDesc &d = col->h_desc[g];
+		memset(&d, 0, sizeof(d));
+		d.row_start = row;
+		d.min_factor = ~0ull;  // column_segment.cpp:96
+		d.max_factor = 0;
+		d.count = (uint32_t)seg_counts[g];
+		d.capacity = cap;
+		d.width = (uint8_t)(8 * col->t.size);  // succinct_vec.width(type_size * 8), column_segment.cpp:102
+		row += seg_counts[g];
+	}
+	col->n_values = row;
+	cudaError_t e = cudaMalloc((void **)&col->raw, row * col->t.size + kArenaPad);
+	if (e == cudaSuccess) {
+		e = cudaMalloc((void **)&col->d_desc, std::max<uint64_t>(n_segments, 1) * sizeof(SegDesc));
+	}
+	if (e == cudaSuccess && n_segments) {
+		e = cudaMemcpyAsync(col->d_desc, col->h_desc.data(), n_segments * sizeof(SegDesc), cudaMemcpyHostToDevice,
+		                    ctx->stream);
+	}
+	if (e != cudaSuccess) {
+		cudaFree(col->raw);
+		cudaFree(col->d_desc);
+		delete col;
+		return fail(ctx, e == cudaErrorMemoryAllocation ? ADACOM_ERR_NOMEM : ADACOM_ERR_CUDA,
+		            std::string("adacom_column_create: ") + cudaGetErrorString(e));
+	}
+	*out = col;
+	return ADACOM_OK;
+}
+
+extern "C" void adacom_column_destroy(adacom_column *col) {
+	if (!col) {
+		return;
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	cudaSetDevice(ctx->device);
+	cudaStreamSynchronize(ctx->stream);
+	for (auto &x : col->extents) {
+		if (x.base) {
+			cudaFreeAsync(x.base, ctx->stream);
+		}
+	}
+	if (col->tiles.d_jobs) {
+		cudaFreeAsync(col->tiles.d_jobs, ctx->stream);
+	}
+	if (col->chunks.d_jobs) {
+		cudaFreeAsync(col->chunks.d_jobs, ctx->stream);
+	}
+	cudaStreamSynchronize(ctx->stream);
+	cudaFree(col->raw);
+	cudaFree(col->d_desc);
+	delete col;
+}
+
+extern "C" uint64_t adacom_column_num_values(const adacom_column *col) {
+	return col ? col->n_values : 0;
+}
+
+extern "C" uint64_t adacom_column_num_segments(const adacom_column *col) {
+	return col ? col->n_segs : 0;
+}
+
+extern "C" void *adacom_column_raw_device_ptr(adacom_column *col) {
+	return col ? (void *)col->raw : nullptr;
+}
+
+extern "C" void *adacom_column_packed_device_ptr(adacom_column *col) {
+	if (!col || col->extents.empty()) {
+		return nullptr;
+	}
+	return (void *)col->extents.back().base;
+}
+
+extern "C" adacom_status adacom_column_upload_raw(adacom_column *col, const void *host_values, uint64_t first_value,
+                                                  uint64_t n) {
+	if (!col || (!host_values && n) || first_value + n > col->n_values) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_column_upload_raw: bad range");
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	adacom_status st = ensure_raw(col);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	CK(ctx, cudaMemcpyAsync(col->raw + first_value * col->t.size, host_values, n * col->t.size, cudaMemcpyHostToDevice,
+	                        ctx->stream));
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_column_release_raw(adacom_column *col) {
+	if (!col) {
+		return ADACOM_ERR_INVALID;
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	adacom_status st = sync_mirror(col);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	for (const SegDesc &d : col->h_desc) {
+		if (d.count && !(d.state & kSegRepacked)) {
+			return fail(ctx, ADACOM_ERR_STATE, "adacom_column_release_raw: a segment still lives in the raw arena");
+		}
+	}
+	CK(ctx, cudaStreamSynchronize(ctx->stream));
+	CK(ctx, cudaFree(col->raw));
+	col->raw = nullptr;
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_column_from_packed(adacom_ctx *ctx, adacom_ptype type, uint64_t n_segments,
+                                                   const adacom_segment_meta *metas, const uint64_t *host_words,
+                                                   uint64_t total_words, adacom_column **out) {
+	if (!ctx || !out || (n_segments && !metas) || (total_words && !host_words)) {
+		return fail(ctx, ADACOM_ERR_INVALID, "adacom_column_from_packed: NULL argument");
+	}
+	*out = nullptr;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	CK(ctx, cudaSetDevice(ctx->device));
+	adacom_column *col = nullptr;
+	adacom_status st = column_alloc(ctx, type, n_segments, &col);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	Extent ext;
+	ext.words = total_words;
+	cudaError_t e = cudaMallocAsync((void **)&ext.base, total_words * 8 + kArenaPad, ctx->stream);
+	if (e == cudaSuccess) {
+		e = cudaMalloc((void **)&col->d_desc, std::max<uint64_t>(n_segments, 1) * sizeof(SegDesc));
+	}
+	if (e != cudaSuccess) {
+		delete col;
+		return fail(ctx, ADACOM_ERR_NOMEM, std::string("adacom_column_from_packed: ") + cudaGetErrorString(e));
+	}
+	uint64_t row = 0;
+	for (uint64_t g = 0; g < n_segments; g++) {
+		const adacom_segment_meta &m = metas[g];
+		SegDesc &d = col->h_desc[g];
+		memset(&d, 0, sizeof(d));
+		bool repacked = m.state & ADACOM_SEG_REPACKED;
+		if (m.count && !repacked) {
+			cudaFreeAsync(ext.base, ctx->stream);
+			cudaFree(col->d_desc);
+			delete col;
+			return fail(ctx, ADACOM_ERR_INVALID, "adacom_column_from_packed: segment is not repacked (no packed image)");
+		}
+		if (repacked && (m.word_offset % kSegAlignWords != 0 ||
+		                 m.word_offset + (((uint64_t)m.count * m.width + 63) >> 6) > total_words)) {
+			cudaFreeAsync(ext.base, ctx->stream);
+			cudaFree(col->d_desc);
+			delete col;
+			return fail(ctx, ADACOM_ERR_INVALID, "adacom_column_from_packed: bad word_offset");
+		}
+		d.row_start = row;
+		d.word_offset = m.word_offset;
+		d.packed_ptr = repacked ? (uint64_t)(ext.base + m.word_offset) : 0;
+		d.min_factor = m.min_factor;
+		d.max_factor = m.max_factor;
+		d.count = (uint32_t)m.count;
+		d.capacity = m.capacity;
+		d.extent = 0;
+		d.width = m.width;
+		d.state = m.state;
+		ext.live += repacked ? 1 : 0;
+		row += m.count;
+	}
+	col->n_values = row;
+	col->extents.push_back(ext);
+	if (total_words) {
+		CK(ctx, cudaMemcpyAsync(ext.base, host_words, total_words * 8, cudaMemcpyHostToDevice, ctx->stream));
+	}
+	if (n_segments) {
+		CK(ctx, cudaMemcpyAsync(col->d_desc, col->h_desc.data(), n_segments * sizeof(SegDesc), cudaMemcpyHostToDevice,
+		                        ctx->stream));
+	}
+	*out = col;
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_column_fill_splitmix(adacom_column *col, uint64_t seed, uint64_t first_index,
+                                                     uint64_t mask) {
+	if (!col) {
+		return ADACOM_ERR_INVALID;
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	adacom_status st = ensure_raw(col);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	LAUNCH(ctx, launch_fill_splitmix(col->t, col->raw, col->n_values, seed, first_index, mask, ctx->stream));
+	return ADACOM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// analyze / encode
+// ---------------------------------------------------------------------------------------------------
+
+extern "C" adacom_status adacom_analyze(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags,
+                                        const uint64_t *validity, int validity_on_device) {
+	if (!range_ok(col, seg_begin, seg_end)) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_analyze: bad segment range");
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	if (!col->raw) {
+		return fail(ctx, ADACOM_ERR_STATE, "adacom_analyze: the raw arena was released");
+	}
+	uint64_t *d_validity = nullptr;
+	bool temp = false;
+	if (validity) {
+		if (validity_on_device) {
+			d_validity = const_cast<uint64_t *>(validity);
+		} else {
+			size_t bytes = ((col->n_values + 63) / 64) * 8;
+			CK(ctx, cudaMallocAsync((void **)&d_validity, bytes ? bytes : 8, ctx->stream));
+			CK(ctx, cudaMemcpyAsync(d_validity, validity, bytes, cudaMemcpyHostToDevice, ctx->stream));
+			temp = true;
+		}
+	}
+	LAUNCH(ctx, launch_analyze(col->t, col->d_desc, (uint32_t)seg_begin, (uint32_t)(seg_end - seg_begin), col->raw,
+	                           d_validity, (flags & ADACOM_ZERO_EXT_MINMAX) ? 1 : 0, ctx->stream));
+	if (temp) {
+		CK(ctx, cudaFreeAsync(d_validity, ctx->stream));
+	}
+	col->mirror_dirty = true;
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_encode(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags) {
+	if (!range_ok(col, seg_begin, seg_end)) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_encode: bad segment range");
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	if (!col->raw) {
+		return fail(ctx, ADACOM_ERR_STATE, "adacom_encode: the raw arena was released");
+	}
+	const uint32_t n = (uint32_t)(seg_end - seg_begin);
+	if (n == 0) {
+		return ADACOM_OK;
+	}
+	const uint32_t extent_id = (uint32_t)col->extents.size();
+	// 1. widths, repack decisions and payload offsets, all on the device
+	LAUNCH(ctx, launch_layout(col->t, col->d_desc, (uint32_t)seg_begin, n, flags, extent_id, ctx->d_totals, ctx->stream));
+	CK(ctx, cudaMemcpyAsync(ctx->h_totals, ctx->d_totals, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+	CK(ctx, cudaStreamSynchronize(ctx->stream));  // the only host round trip: 8 bytes, sizes the new extent
+	Extent ext;
+	ext.words = ctx->h_totals[0];
+	if (ext.words) {
+		// 2. a fresh extent: scans keep reading the old payloads until the descriptors are re-bound
+		CK(ctx, cudaMallocAsync((void **)&ext.base, ext.words * 8 + kArenaPad, ctx->stream));
+		LAUNCH(ctx, launch_bind_extent(col->d_desc, (uint32_t)seg_begin, n, ext.base, extent_id, ctx->stream));
+		adacom_status st = get_tiles(col, seg_begin, seg_end);
+		if (st != ADACOM_OK) {
+			return st;
+		}
+		// 3. pack
+		LAUNCH(ctx, launch_encode(col->t, col->d_desc, col->tiles.d_jobs, col->tiles.n, col->raw, extent_id, ctx->sm_count,
+		                          ctx->stream));
+	}
+	col->extents.push_back(ext);
+	col->mirror_dirty = true;
+	col->epoch++;
+	return ADACOM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// metadata / accounting
+// ---------------------------------------------------------------------------------------------------
+
+extern "C" adacom_status adacom_column_get_meta(adacom_column *col, uint64_t seg_begin, uint64_t seg_end,
+                                                adacom_segment_meta *out) {
+	if (!range_ok(col, seg_begin, seg_end) || (!out && seg_end > seg_begin)) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_column_get_meta: bad arguments");
+	}
+	std::lock_guard<std::mutex> lock(col->ctx->mu);
+	adacom_status st = sync_mirror(col);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	for (uint64_t g = seg_begin; g < seg_end; g++) {
+		fill_meta(col, g, out + (g - seg_begin));
+	}
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_column_data_size(adacom_column *col, uint64_t seg_begin, uint64_t seg_end,
+                                                 uint64_t *out) {
+	if (!range_ok(col, seg_begin, seg_end) || !out) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_column_data_size: bad arguments");
+	}
+	std::lock_guard<std::mutex> lock(col->ctx->mu);
+	adacom_status st = sync_mirror(col);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	uint64_t total = 0;
+	adacom_segment_meta m;
+	for (uint64_t g = seg_begin; g < seg_end; g++) {
+		fill_meta(col, g, &m);
+		total += m.size_in_bytes;
+	}
+	*out = total;
+	return ADACOM_OK;
+}
+
+extern "C" uint64_t adacom_column_packed_words(const adacom_column *col) {
+	if (!col || col->extents.empty()) {
+		return 0;
+	}
+	return col->extents.back().words;
+}
+
+extern "C" adacom_status adacom_column_download_packed(adacom_column *col, uint64_t first_word, uint64_t n_words,
+                                                       uint64_t *host_out) {
+	if (!col || col->extents.empty() || (!host_out && n_words) || first_word + n_words > col->extents.back().words) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_column_download_packed: bad range");
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	if (n_words) {
+		CK(ctx, cudaMemcpyAsync(host_out, col->extents.back().base + first_word, n_words * 8, cudaMemcpyDeviceToHost,
+		                        ctx->stream));
+	}
+	CK(ctx, cudaStreamSynchronize(ctx->stream));
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_segment_serialize(adacom_column *col, uint64_t seg, uint8_t *host_out,
+                                                  uint64_t capacity, uint64_t *bytes_out) {
+	if (!col || seg >= col->n_segs || !bytes_out) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_segment_serialize: bad arguments");
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	adacom_status st = sync_mirror(col);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	const SegDesc &d = col->h_desc[seg];
+	const uint64_t bits = seg_bits(d, col->t.size);
+	const uint64_t data_bytes = 8 * ((bits + 63) >> 6);
+	*bytes_out = 9 + data_bytes;
+	if (!host_out || capacity < 9 + data_bytes) {
+		return ADACOM_OK;  // size query
+	}
+	memcpy(host_out, &bits, 8);  // int_vector<0>::write_header: m_size, then the width byte
+	host_out[8] = d.width;
+	memset(host_out + 9, 0, data_bytes);
+	if (d.state & kSegRepacked) {
+		CK(ctx, cudaMemcpyAsync(host_out + 9, (const void *)d.packed_ptr, data_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+	} else if (col->raw && d.count) {
+		// slot-width vector: the first `count` slots are the raw values, the rest was never written
+		CK(ctx, cudaMemcpyAsync(host_out + 9, col->raw + d.row_start * col->t.size, (size_t)d.count * col->t.size,
+		                        cudaMemcpyDeviceToHost, ctx->stream));
+	}
+	CK(ctx, cudaStreamSynchronize(ctx->stream));
+	return ADACOM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// decode / scan
+// ---------------------------------------------------------------------------------------------------
+
+static uint64_t range_rows(const adacom_column *col, uint64_t b, uint64_t e) {
+	if (b == e) {
+		return 0;
+	}
+	const SegDesc &last = col->h_desc[e - 1];
+	return last.row_start + last.count - col->h_desc[b].row_start;
+}
+
+extern "C" adacom_status adacom_decode(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags, void *out,
+                                       int out_on_device) {
+	if (!range_ok(col, seg_begin, seg_end) || !out) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_decode: bad arguments");
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	const uint64_t rows = range_rows(col, seg_begin, seg_end);
+	if (rows == 0) {
+		return ADACOM_OK;
+	}
+	adacom_status st = get_tiles(col, seg_begin, seg_end);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	void *d_out = out;
+	if (!out_on_device) {
+		CK(ctx, cudaMallocAsync(&d_out, rows * col->t.size, ctx->stream));
+	}
+	DecodeArgs a;
+	a.desc = col->d_desc;
+	a.jobs = col->tiles.d_jobs;
+	a.n_jobs = col->tiles.n;
+	a.tile_granularity = kVectorSize;
+	a.raw = col->raw;
+	a.literal = (flags & ADACOM_LITERAL) ? 1 : 0;
+	a.out = d_out;
+	a.out_row0 = col->h_desc[seg_begin].row_start;
+	LAUNCH(ctx, launch_decode(col->t, kModeFlat, a, ctx->sm_count, ctx->stream));
+	if (!out_on_device) {
+		CK(ctx, cudaMemcpyAsync(out, d_out, rows * col->t.size, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(ctx, cudaFreeAsync(d_out, ctx->stream));
+		CK(ctx, cudaStreamSynchronize(ctx->stream));
+	}
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_scan_partial(adacom_column *col, uint64_t seg, uint64_t start, uint64_t scan_count,
+                                             int flags, void *result, uint64_t result_offset, int result_on_device) {
+	if (!col || seg >= col->n_segs || (!result && scan_count)) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_scan_partial: bad arguments");
+	}
+	adacom_ctx *ctx = col->ctx;
+	if (start + scan_count > col->h_desc[seg].count) {
+		return fail(ctx, ADACOM_ERR_INVALID, "adacom_scan_partial: scan runs past the end of the segment");
+	}
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	if (scan_count == 0) {
+		return ADACOM_OK;
+	}
+	const int literal = (flags & ADACOM_LITERAL) ? 1 : 0;
+	if (result_on_device) {
+		LAUNCH(ctx, launch_scan_range(col->t, col->d_desc, (uint32_t)seg, col->raw, start, scan_count, literal, result,
+		                              result_offset, ctx->stream));
+		return ADACOM_OK;
+	}
+	void *d_out = nullptr;
+	CK(ctx, cudaMallocAsync(&d_out, scan_count * col->t.size, ctx->stream));
+	LAUNCH(ctx, launch_scan_range(col->t, col->d_desc, (uint32_t)seg, col->raw, start, scan_count, literal, d_out, 0,
+	                              ctx->stream));
+	CK(ctx, cudaMemcpyAsync((uint8_t *)result + result_offset * col->t.size, d_out, scan_count * col->t.size,
+	                        cudaMemcpyDeviceToHost, ctx->stream));
+	CK(ctx, cudaFreeAsync(d_out, ctx->stream));
+	CK(ctx, cudaStreamSynchronize(ctx->stream));
+	return ADACOM_OK;
+}
+
+// free every packed extent that no repacked segment references any more
+static adacom_status gc_extents(adacom_column *col) {
+	adacom_ctx *ctx = col->ctx;
+	for (auto &x : col->extents) {
+		x.live = 0;
+	}
+	for (const SegDesc &d : col->h_desc) {
+		if ((d.state & kSegRepacked) && d.extent < col->extents.size()) {
+			col->extents[d.extent].live++;
+		}
+	}
+	for (auto &x : col->extents) {
+		if (x.base && x.live == 0) {
+			CK(ctx, cudaFreeAsync(x.base, ctx->stream));
+			x.base = nullptr;
+			x.words = 0;
+		}
+	}
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_uncompact(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags) {
+	if (!range_ok(col, seg_begin, seg_end)) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_uncompact: bad segment range");
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	adacom_status st = sync_mirror(col);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	st = ensure_raw(col);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	// Uncompact() is a no-op for segments that are not compacted (column_segment.cpp:327-330)
+	std::vector<Job> jobs;
+	for (uint64_t g = seg_begin; g < seg_end; g++) {
+		const SegDesc &d = col->h_desc[g];
+		if (!(d.state & kSegCompacted)) {
+			continue;
+		}
+		bool touch = (d.state & kSegRepacked) || ((flags & ADACOM_LITERAL) && d.min_factor != ~0ull);
+		if (!touch) {
+			continue;  // payload already sits in the raw arena at slot width
+		}
+		uint32_t n = (d.count + kVectorSize - 1) / kVectorSize;
+		for (uint32_t k = 0; k < n; k++) {
+			jobs.push_back({(uint32_t)g, k});
+		}
+	}
+	if (!jobs.empty()) {
+		JobTable tmp;
+		st = upload_jobs(col, tmp, jobs);
+		if (st != ADACOM_OK) {
+			return st;
+		}
+		DecodeArgs a;
+		a.desc = col->d_desc;
+		a.jobs = tmp.d_jobs;
+		a.n_jobs = tmp.n;
+		a.tile_granularity = kVectorSize;
+		a.raw = col->raw;
+		a.literal = (flags & ADACOM_LITERAL) ? 1 : 0;
+		a.out = col->raw;
+		a.out_row0 = 0;
+		LAUNCH(ctx, launch_decode(col->t, kModeFlat, a, ctx->sm_count, ctx->stream));
+		CK(ctx, cudaFreeAsync(tmp.d_jobs, ctx->stream));
+	}
+	for (uint64_t g = seg_begin; g < seg_end; g++) {
+		SegDesc &d = col->h_desc[g];
+		if (!(d.state & kSegCompacted)) {
+			continue;
+		}
+		d.state = (uint8_t)((d.state & kSegAnalyzed) | kSegUncompressedFn);
+		d.width = (uint8_t)(8 * col->t.size);
+		d.packed_ptr = 0;
+		d.word_offset = 0;
+	}
+	if (seg_end > seg_begin) {
+		CK(ctx, cudaMemcpyAsync(col->d_desc + seg_begin, col->h_desc.data() + seg_begin,
+		                        (seg_end - seg_begin) * sizeof(SegDesc), cudaMemcpyHostToDevice, ctx->stream));
+	}
+	col->epoch++;
+	return gc_extents(col);
+}
+
+static adacom_status run_agg(adacom_column *col, uint64_t b, uint64_t e, int flags, DecodeMode mode, uint32_t op_mask,
+                             uint64_t constant, uint32_t *bitmap32, Agg *device_out) {
+	adacom_ctx *ctx = col->ctx;
+	adacom_status st = get_chunks(col, b, e);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	CK(ctx, cudaMemsetAsync(device_out, 0, sizeof(Agg), ctx->stream));
+	DecodeArgs a;
+	a.desc = col->d_desc;
+	a.jobs = col->chunks.d_jobs;
+	a.n_jobs = col->chunks.n;
+	a.tile_granularity = 0;
+	a.raw = col->raw;
+	a.literal = (flags & ADACOM_LITERAL) ? 1 : 0;
+	a.agg = device_out;
+	a.op_mask = op_mask;
+	a.constant = constant;
+	a.bitmap32 = bitmap32;
+	a.out_row0 = b < e ? col->h_desc[b].row_start : 0;
+	LAUNCH(ctx, launch_decode(col->t, mode, a, ctx->sm_count, ctx->stream));
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_scan_sum_async(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags,
+                                               adacom_agg *device_out) {
+	if (!range_ok(col, seg_begin, seg_end) || !device_out) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_scan_sum_async: bad arguments");
+	}
+	std::lock_guard<std::mutex> lock(col->ctx->mu);
+	return run_agg(col, seg_begin, seg_end, flags, kModeSum, 0, 0, nullptr, (Agg *)device_out);
+}
+
+extern "C" adacom_status adacom_scan_sum(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags,
+                                         adacom_agg *out) {
+	if (!range_ok(col, seg_begin, seg_end) || !out) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_scan_sum: bad arguments");
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	adacom_status st = run_agg(col, seg_begin, seg_end, flags, kModeSum, 0, 0, nullptr, ctx->d_agg);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	CK(ctx, cudaMemcpyAsync(ctx->h_agg, ctx->d_agg, sizeof(Agg), cudaMemcpyDeviceToHost, ctx->stream));
+	CK(ctx, cudaStreamSynchronize(ctx->stream));
+	memcpy(out, ctx->h_agg, sizeof(Agg));
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_scan_filter(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags,
+                                            adacom_cmp op, int64_t constant, adacom_agg *out, uint64_t *device_bitmap) {
+	if (!range_ok(col, seg_begin, seg_end) || !out || (int)op < 0 || (int)op > 5) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_scan_filter: bad arguments");
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	if (device_bitmap) {
+		uint64_t rows = range_rows(col, seg_begin, seg_end);
+		CK(ctx, cudaMemsetAsync(device_bitmap, 0, ((rows + 63) / 64) * 8, ctx->stream));
+	}
+	adacom_status st = run_agg(col, seg_begin, seg_end, flags, kModeFilter, cmp_mask_for_op((int)op), (uint64_t)constant,
+	                           (uint32_t *)device_bitmap, ctx->d_agg);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	CK(ctx, cudaMemcpyAsync(ctx->h_agg, ctx->d_agg, sizeof(Agg), cudaMemcpyDeviceToHost, ctx->stream));
+	CK(ctx, cudaStreamSynchronize(ctx->stream));
+	memcpy(out, ctx->h_agg, sizeof(Agg));
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_point_filter_batch(adacom_column *col, uint64_t n_queries, const uint32_t *seg_idx,
+                                                   const int64_t *constants, int flags, uint64_t *out_count,
+                                                   uint64_t *out_first_row) {
+	if (!col || (n_queries && (!seg_idx || !constants || !out_count || !out_first_row)) || n_queries >= (1ull << 32)) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_point_filter_batch: bad arguments");
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	if (n_queries == 0) {
+		return ADACOM_OK;
+	}
+	adacom_status st = sync_mirror(col);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	std::vector<Job> jobs;
+	std::vector<uint32_t> job_query;
+	for (uint64_t q = 0; q < n_queries; q++) {
+		if (seg_idx[q] >= col->n_segs) {
+			return fail(ctx, ADACOM_ERR_INVALID, "adacom_point_filter_batch: segment index out of range");
+		}
+		const SegDesc &d = col->h_desc[seg_idx[q]];
+		uint32_t gran = scan_chunk_values(d.width);
+		uint32_t n = (d.count + gran - 1) / gran;
+		for (uint32_t k = 0; k < n; k++) {
+			jobs.push_back({seg_idx[q], k});
+			job_query.push_back((uint32_t)q);
+		}
+	}
+	JobTable tmp;
+	st = upload_jobs(col, tmp, jobs);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	uint32_t *d_job_query = nullptr;
+	int64_t *d_const = nullptr;
+	unsigned long long *d_count = nullptr, *d_first = nullptr;
+	CK(ctx, cudaMallocAsync((void **)&d_job_query, std::max<size_t>(job_query.size(), 1) * 4, ctx->stream));
+	CK(ctx, cudaMallocAsync((void **)&d_const, n_queries * 8, ctx->stream));
+	CK(ctx, cudaMallocAsync((void **)&d_count, n_queries * 8, ctx->stream));
+	CK(ctx, cudaMallocAsync((void **)&d_first, n_queries * 8, ctx->stream));
+	if (!job_query.empty()) {
+		CK(ctx, cudaMemcpyAsync(d_job_query, job_query.data(), job_query.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+	}
+	CK(ctx, cudaMemcpyAsync(d_const, constants, n_queries * 8, cudaMemcpyHostToDevice, ctx->stream));
+	CK(ctx, cudaMemsetAsync(d_count, 0, n_queries * 8, ctx->stream));
+	CK(ctx, cudaMemsetAsync(d_first, 0xff, n_queries * 8, ctx->stream));
+	DecodeArgs a;
+	a.desc = col->d_desc;
+	a.jobs = tmp.d_jobs;
+	a.n_jobs = tmp.n;
+	a.tile_granularity = 0;
+	a.raw = col->raw;
+	a.literal = (flags & ADACOM_LITERAL) ? 1 : 0;
+	a.job_query = d_job_query;
+	a.q_const = d_const;
+	a.q_count = d_count;
+	a.q_first = d_first;
+	LAUNCH(ctx, launch_decode(col->t, kModePoint, a, ctx->sm_count, ctx->stream));
+	CK(ctx, cudaMemcpyAsync(out_count, d_count, n_queries * 8, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(ctx, cudaMemcpyAsync(out_first_row, d_first, n_queries * 8, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(ctx, cudaFreeAsync(d_job_query, ctx->stream));
+	CK(ctx, cudaFreeAsync(d_const, ctx->stream));
+	CK(ctx, cudaFreeAsync(d_count, ctx->stream));
+	CK(ctx, cudaFreeAsync(d_first, ctx->stream));
+	if (tmp.d_jobs) {
+		CK(ctx, cudaFreeAsync(tmp.d_jobs, ctx->stream));
+	}
+	CK(ctx, cudaStreamSynchronize(ctx->stream));
+	return ADACOM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// fetch_row
+// ---------------------------------------------------------------------------------------------------
+
+extern "C" adacom_status adacom_fetch_rows(adacom_column *col, uint64_t n, const uint32_t *seg_idx,
+                                           const uint32_t *row_in_seg, int flags, void *out, int on_device) {
+	if (!col || (n && (!seg_idx || !row_in_seg || !out))) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_fetch_rows: bad arguments");
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	if (n == 0) {
+		return ADACOM_OK;
+	}
+	const int literal = (flags & ADACOM_LITERAL) ? 1 : 0;
+	if (on_device) {
+		LAUNCH(ctx, launch_fetch_rows(col->t, col->d_desc, col->raw, n, seg_idx, row_in_seg, literal, out, ctx->stream));
+		return ADACOM_OK;
+	}
+	for (uint64_t q = 0; q < n; q++) {
+		if (seg_idx[q] >= col->n_segs || row_in_seg[q] >= col->h_desc[seg_idx[q]].count) {
+			return fail(ctx, ADACOM_ERR_INVALID, "adacom_fetch_rows: (segment, row) out of range");
+		}
+	}
+	uint32_t *d_seg = nullptr, *d_row = nullptr;
+	void *d_out = nullptr;
+	CK(ctx, cudaMallocAsync((void **)&d_seg, n * 4, ctx->stream));
+	CK(ctx, cudaMallocAsync((void **)&d_row, n * 4, ctx->stream));
+	CK(ctx, cudaMallocAsync(&d_out, n * col->t.size, ctx->stream));
+	CK(ctx, cudaMemcpyAsync(d_seg, seg_idx, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+	CK(ctx, cudaMemcpyAsync(d_row, row_in_seg, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+	LAUNCH(ctx, launch_fetch_rows(col->t, col->d_desc, col->raw, n, d_seg, d_row, literal, d_out, ctx->stream));
+	CK(ctx, cudaMemcpyAsync(out, d_out, n * col->t.size, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(ctx, cudaFreeAsync(d_seg, ctx->stream));
+	CK(ctx, cudaFreeAsync(d_row, ctx->stream));
+	CK(ctx, cudaFreeAsync(d_out, ctx->stream));
+	CK(ctx, cudaStreamSynchronize(ctx->stream));
+	return ADACOM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// host-buffer convenience path
+// ---------------------------------------------------------------------------------------------------
+
+extern "C" adacom_status adacom_compress_host(adacom_ctx *ctx, adacom_ptype type, const void *host_values,
+                                              uint64_t n_segments, const uint64_t *seg_counts, uint32_t seg_capacity,
+                                              int flags, adacom_segment_meta *metas_out, uint64_t *host_words_out,
+                                              uint64_t host_words_capacity, uint64_t *total_words_out,
+                                              adacom_column **col_out) {
+	if (!ctx || !col_out || (!host_values && n_segments)) {
+		return fail(ctx, ADACOM_ERR_INVALID, "adacom_compress_host: NULL argument");
+	}
+	adacom_column *col = nullptr;
+	adacom_status st = adacom_column_create(ctx, type, n_segments, seg_counts, seg_capacity, &col);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	auto bail = [&](adacom_status s) {
+		adacom_column_destroy(col);
+		return s;
+	};
+	st = adacom_column_upload_raw(col, host_values, 0, col->n_values);
+	if (st != ADACOM_OK) {
+		return bail(st);
+	}
+	st = adacom_analyze(col, 0, n_segments, flags, nullptr, 0);
+	if (st != ADACOM_OK) {
+		return bail(st);
+	}
+	st = adacom_encode(col, 0, n_segments, flags);
+	if (st != ADACOM_OK) {
+		return bail(st);
+	}
+	const uint64_t words = adacom_column_packed_words(col);
+	if (total_words_out) {
+		*total_words_out = words;
+	}
+	if (host_words_out) {
+		if (host_words_capacity < words) {
+			return bail(fail(ctx, ADACOM_ERR_INVALID, "adacom_compress_host: host_words_capacity too small"));
+		}
+		st = adacom_column_download_packed(col, 0, words, host_words_out);
+		if (st != ADACOM_OK) {
+			return bail(st);
+		}
+	}
+	if (metas_out) {
+		st = adacom_column_get_meta(col, 0, n_segments, metas_out);
+		if (st != ADACOM_OK) {
+			return bail(st);
+		}
+	}
+	*col_out = col;
+	return ADACOM_OK;
+}

@@ -1,0 +1,70 @@
+// adacom_kernels.cuh -- host-callable launchers of the codec kernels.  Each launcher enqueues exactly
+// ONE kernel on `stream` and returns the cudaError_t of the launch.
+#pragma once
+
+#include "adacom_device.cuh"
+
+namespace adacom {
+
+enum DecodeMode : int { kModeFlat = 0, kModeSum = 1, kModeFilter = 2, kModePoint = 3 };
+
+struct TypeInfo {
+	int size;        // 1, 2, 4, 8
+	bool is_signed;
+};
+
+struct DecodeArgs {
+	const SegDesc *desc = nullptr;
+	const Job *jobs = nullptr;       // (segment, k) work units
+	uint32_t n_jobs = 0;
+	uint32_t tile_granularity = 0;   // kVectorSize -> 2048-value tiles; 0 -> scan chunks (scan_chunk_values(w))
+	const uint8_t *raw = nullptr;    // raw arena (source for segments that are not repacked)
+	int literal = 0;                 // ADACOM_LITERAL: add min even when the segment was not repacked (Q1)
+	// kModeFlat
+	void *out = nullptr;
+	uint64_t out_row0 = 0;           // out[(row_start + i) - out_row0]
+	// kModeSum / kModeFilter
+	Agg *agg = nullptr;
+	uint32_t op_mask = 0;
+	uint64_t constant = 0;
+	uint32_t *bitmap32 = nullptr;    // optional, bit (row - out_row0)
+	// kModePoint
+	const uint32_t *job_query = nullptr;
+	const int64_t *q_const = nullptr;
+	unsigned long long *q_count = nullptr;
+	unsigned long long *q_first = nullptr;
+};
+
+// TMA-staged unpack of packed tiles (+ fused SUM / filter).  grid = persistent CTAs.
+cudaError_t launch_decode(TypeInfo t, DecodeMode mode, const DecodeArgs &args, int sm_count, cudaStream_t stream);
+
+// scan_vector / scan_partial of one segment, arbitrary start (generic unaligned path, no staging)
+cudaError_t launch_scan_range(TypeInfo t, const SegDesc *desc, uint32_t seg, const uint8_t *raw, uint64_t start,
+                              uint64_t scan_count, int literal, void *result, uint64_t result_offset,
+                              cudaStream_t stream);
+
+// batched fetch_row gather
+cudaError_t launch_fetch_rows(TypeInfo t, const SegDesc *desc, const uint8_t *raw, uint64_t n, const uint32_t *seg_idx,
+                              const uint32_t *row_in_seg, int literal, void *out, cudaStream_t stream);
+
+// analyze: per-segment unsigned min/max (+ optional validity / NullValue fill); one CTA per segment
+cudaError_t launch_analyze(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, uint8_t *raw,
+                           const uint64_t *validity, int zero_ext, cudaStream_t stream);
+
+// layout: widths, repack decision, 128-byte aligned word offsets (exclusive scan), totals[0] = words
+cudaError_t launch_layout(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int flags, uint32_t extent,
+                          unsigned long long *totals, cudaStream_t stream);
+
+// bind packed_ptr = base + word_offset for the repacked segments of the range
+cudaError_t launch_bind_extent(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, uint64_t *base, uint32_t extent,
+                               cudaStream_t stream);
+
+// encode: TMA-staged raw tiles -> FOR subtract + bit-pack into the packed extent
+cudaError_t launch_encode(TypeInfo t, const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw,
+                          uint32_t extent, int sm_count, cudaStream_t stream);
+
+// synthetic generator: raw[i] = T(splitmix64(seed + first_index + i) & mask)
+cudaError_t launch_fill_splitmix(TypeInfo t, void *raw, uint64_t n, uint64_t seed, uint64_t first_index, uint64_t mask,
+                                 cudaStream_t stream);
+
+}  // namespace adacom

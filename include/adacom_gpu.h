@@ -1,0 +1,238 @@
+/*
+ * adacom_gpu.h -- C ABI of the B200-native succinct column-segment codec (libadacom_gpu.so).
+ *
+ * This is the drop-in boundary for AdaCom's succinct hot path.  Plain pointers and sizes only; every
+ * entry point returns an adacom_status and never throws.  The C++ shim in
+ * duckdb_adaptive_compression_b200/host/ wraps these calls behind the reference's own
+ * CompressionFunction / ColumnSegment / ColumnSegmentCatalog surface; INTEGRATION.md shows the
+ * binding a maintainer of the reference would add.
+ *
+ * Reference interfaces replaced (paths relative to the reference repository root):
+ *   plugin vtable ............ src/include/duckdb/function/compression_function.hpp:65-177
+ *   SuccinctFun::GetFunction . src/storage/compression/succinct.cpp:335-366
+ *   append + min/max ......... src/storage/compression/succinct.cpp:271-322          -> adacom_analyze
+ *   BitCompressFromSuccinct .. src/storage/table/column_segment.cpp:348-383          -> adacom_encode
+ *   BitCompressFromUncompr. .. src/storage/table/column_segment.cpp:385-456          -> adacom_encode(ADACOM_ZERO_EXT_MINMAX)
+ *   SuccinctScan/ScanPartial . src/storage/compression/succinct.cpp:123-144,232-240  -> adacom_scan_partial, adacom_decode
+ *   filter after scan ........ src/storage/table/column_segment.cpp:575-658          -> adacom_scan_filter (fused)
+ *   UncompressSuccinct ....... src/storage/table/column_segment.cpp:458-506          -> adacom_uncompact
+ *   SuccinctFetchRow ......... src/storage/compression/succinct.cpp:244-260          -> adacom_fetch_rows
+ *   GetDataSize .............. src/storage/table/column_segment.cpp:204-214          -> adacom_column_data_size
+ *
+ * Object model.  An adacom_ctx owns one GPU (device ordinal, streams, scratch).  An adacom_column is a
+ * batch of column segments of one physical type resident in that GPU's HBM: a raw arena (the slot-width
+ * int_vector payloads == flat T values, segments back to back), a packed arena (FOR + fixed-width
+ * SDSL-layout words, every segment starting on a 128-byte boundary) and a descriptor table.  All batched
+ * calls take a [seg_begin, seg_end) range and run as ONE kernel launch over that range.
+ *
+ * There is no CPU fallback: every compute entry point fails with ADACOM_ERR_CUDA / ADACOM_ERR_NO_DEVICE
+ * when no sm_100 device is usable.
+ */
+#ifndef ADACOM_GPU_H
+#define ADACOM_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ADACOM_ABI_VERSION 1
+
+typedef enum {
+	ADACOM_OK = 0,
+	ADACOM_ERR_INVALID = 1,     /* bad argument (the shim raises duckdb::InternalException) */
+	ADACOM_ERR_CUDA = 2,        /* a CUDA call failed; adacom_last_error() has the text */
+	ADACOM_ERR_NOMEM = 3,       /* device or pinned-host allocation failed (reference: std::bad_alloc) */
+	ADACOM_ERR_UNSUPPORTED = 4, /* physical type not supported by SuccinctFun::TypeIsSupported */
+	ADACOM_ERR_STATE = 5,       /* call not valid in the column's current state */
+	ADACOM_ERR_NO_DEVICE = 6    /* no CUDA device / not an sm_100 part */
+} adacom_status;
+
+/* duckdb::PhysicalType values of the supported types (src/include/duckdb/common/types.hpp) */
+typedef enum {
+	ADACOM_UINT8 = 2,
+	ADACOM_INT8 = 3,
+	ADACOM_UINT16 = 4,
+	ADACOM_INT16 = 5,
+	ADACOM_UINT32 = 6,
+	ADACOM_INT32 = 7,
+	ADACOM_UINT64 = 8,
+	ADACOM_INT64 = 9
+} adacom_ptype;
+
+/* comparison operators of TemplatedFilterSelection (column_segment.cpp:593-655) */
+typedef enum {
+	ADACOM_CMP_EQ = 0,
+	ADACOM_CMP_NE = 1,
+	ADACOM_CMP_LT = 2,
+	ADACOM_CMP_GT = 3,
+	ADACOM_CMP_LE = 4,
+	ADACOM_CMP_GE = 5
+} adacom_cmp;
+
+/* flags (mirror DBConfig's succinct switches, src/include/duckdb/main/config.hpp:189-197) */
+enum {
+	ADACOM_PADDED = 1,          /* succinct_padded_to_next_byte_enabled: w = (w + 7) & ~7 */
+	ADACOM_LITERAL = 2,         /* reproduce reference quirks Q1/Q2 literally */
+	ADACOM_ZERO_EXT_MINMAX = 4  /* adaptive encoder: min/max over zero-extended raw bytes (Q2b) */
+};
+
+/* per-segment state bits */
+enum {
+	ADACOM_SEG_COMPACTED = 1, /* ColumnSegment::compacted */
+	ADACOM_SEG_REPACKED = 2,  /* the width really shrank: payload lives in the packed arena */
+	ADACOM_SEG_ANALYZED = 4   /* min_factor / max_factor are valid */
+};
+
+/* Host view of one segment == the codec-relevant ColumnSegment members
+ * (src/include/duckdb/storage/table/column_segment.hpp:60,190-214). 64 bytes. */
+typedef struct {
+	uint64_t row_start;     /* index of the segment's first value inside the column (SegmentBase::start) */
+	uint64_t count;         /* SegmentBase::count */
+	uint64_t word_offset;   /* first 64-bit word of the payload in the packed arena (multiple of 16) */
+	uint64_t words;         /* payload words = ceil(count * width / 64) when repacked, else 0 */
+	uint64_t min_factor;    /* UINT64_MAX = unset */
+	uint64_t max_factor;
+	uint64_t size_in_bytes; /* sdsl::size_in_bytes(succinct_vec) == ColumnSegment::GetDataSize() */
+	uint8_t width;          /* succinct_vec.width() */
+	uint8_t state;          /* ADACOM_SEG_* */
+	uint8_t type_size;      /* 1, 2, 4, 8 */
+	uint8_t is_signed;
+	uint32_t capacity;      /* slots of the segment: segment_size / type_size */
+} adacom_segment_meta;
+
+/* 128-bit two's-complement aggregate (DuckDB SUM over integers -> HUGEINT) */
+typedef struct {
+	uint64_t sum_lo;
+	uint64_t sum_hi;
+	uint64_t count;
+	uint64_t reserved;
+} adacom_agg;
+
+typedef struct adacom_ctx adacom_ctx;
+typedef struct adacom_column adacom_column;
+
+/* ---- context -------------------------------------------------------------------------------------- */
+int adacom_abi_version(void);
+adacom_status adacom_ctx_create(int device, adacom_ctx **out);
+void adacom_ctx_destroy(adacom_ctx *ctx);
+/* text of the last error raised on this context (or on the process when ctx == NULL) */
+const char *adacom_last_error(const adacom_ctx *ctx);
+adacom_status adacom_ctx_synchronize(adacom_ctx *ctx);
+/* the compute stream (cudaStream_t) every kernel of this context is launched on */
+void *adacom_ctx_stream(adacom_ctx *ctx);
+/* number of kernels this context has launched so far (bench.py's gpu_launches) */
+uint64_t adacom_ctx_launch_count(const adacom_ctx *ctx);
+/* CUDA events on the compute stream, for timing the kernels where they are launched */
+adacom_status adacom_event_create(adacom_ctx *ctx, void **event_out);
+adacom_status adacom_event_record(adacom_ctx *ctx, void *event);
+adacom_status adacom_event_elapsed_ms(adacom_ctx *ctx, void *start, void *stop, float *ms_out); /* syncs on stop */
+void adacom_event_destroy(adacom_ctx *ctx, void *event);
+/* pinned host memory for staging (cudaHostAlloc) */
+adacom_status adacom_host_alloc(adacom_ctx *ctx, size_t bytes, void **out);
+void adacom_host_free(adacom_ctx *ctx, void *ptr);
+/* write `bytes` of zeros to a scratch buffer > L2 (benchmark hygiene: flush the 126 MB L2) */
+adacom_status adacom_flush_l2(adacom_ctx *ctx);
+
+/* ---- column life cycle ---------------------------------------------------------------------------- */
+/* A column of n_segments segments; segment g holds seg_counts[g] values and has seg_capacity slots
+ * (Storage::BLOCK_SIZE / sizeof(T) = 262136/S by default when seg_capacity == 0).  Allocates the raw
+ * arena (sum(seg_counts) * S bytes) and the descriptor table.  Fresh segments are SUCCINCT at slot width
+ * 8*S, not compacted (column_segment.cpp:101-105). */
+adacom_status adacom_column_create(adacom_ctx *ctx, adacom_ptype type, uint64_t n_segments,
+                                   const uint64_t *seg_counts, uint32_t seg_capacity, adacom_column **out);
+void adacom_column_destroy(adacom_column *col);
+uint64_t adacom_column_num_values(const adacom_column *col);
+uint64_t adacom_column_num_segments(const adacom_column *col);
+/* device pointer of the raw arena (T values, segments back to back; NULL once released) */
+void *adacom_column_raw_device_ptr(adacom_column *col);
+/* device pointer of the packed arena (uint64 words; NULL before the first encode) */
+void *adacom_column_packed_device_ptr(adacom_column *col);
+/* copy host T values [first_value, first_value + n) into the raw arena (async on the compute stream) */
+adacom_status adacom_column_upload_raw(adacom_column *col, const void *host_values, uint64_t first_value, uint64_t n);
+/* free the raw arena once every segment is repacked (ERR_STATE otherwise) */
+adacom_status adacom_column_release_raw(adacom_column *col);
+/* Build a column directly from packed images (the H2D staging format): metas[] as produced by
+ * adacom_column_get_meta, host_words = the packed arena (metas[g].word_offset indexes into it). */
+adacom_status adacom_column_from_packed(adacom_ctx *ctx, adacom_ptype type, uint64_t n_segments,
+                                        const adacom_segment_meta *metas, const uint64_t *host_words,
+                                        uint64_t total_words, adacom_column **out);
+/* synthetic-data generator for benchmarks: raw[i] = T(splitmix64(seed + first_index + i) & mask) */
+adacom_status adacom_column_fill_splitmix(adacom_column *col, uint64_t seed, uint64_t first_index, uint64_t mask);
+
+/* ---- analyze (SuccinctAppendLoop's min/max; optional validity mask + NullValue<T> fill) ------------- */
+/* validity: DuckDB validity words for the WHOLE column (bit i = row i valid), device or host pointer per
+ * validity_on_device; NULL = all valid.  NULL rows are excluded from min/max and their slot is
+ * overwritten with NullValue<T>() exactly like succinct.cpp:288-292. */
+adacom_status adacom_analyze(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags,
+                             const uint64_t *validity, int validity_on_device);
+
+/* ---- encode (BitCompressFromSuccinct / BitCompressFromUncompressed) -------------------------------- */
+/* width = hi(max - min) + 1 (padded to bytes with ADACOM_PADDED); segments whose width shrinks are packed
+ * into the packed arena, all segments of the range become `compacted`.  Re-encoding a range replaces the
+ * packed arena (epoch swap: scans never observe a half-written payload). */
+adacom_status adacom_encode(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags);
+
+/* ---- metadata / accounting --------------------------------------------------------------------------- */
+adacom_status adacom_column_get_meta(adacom_column *col, uint64_t seg_begin, uint64_t seg_end,
+                                     adacom_segment_meta *out);
+/* sum of ColumnSegment::GetDataSize() over the range (9 + 8*ceil(bits/64) per succinct segment) */
+adacom_status adacom_column_data_size(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, uint64_t *out);
+/* total payload words of the packed arena (including the 128-byte alignment gaps) */
+uint64_t adacom_column_packed_words(const adacom_column *col);
+/* copy the packed arena / one segment's payload words to the host */
+adacom_status adacom_column_download_packed(adacom_column *col, uint64_t first_word, uint64_t n_words,
+                                            uint64_t *host_out);
+/* sdsl::int_vector<0>::serialize image of one segment: 8-byte bit count, 1-byte width, data words */
+adacom_status adacom_segment_serialize(adacom_column *col, uint64_t seg, uint8_t *host_out, uint64_t capacity,
+                                       uint64_t *bytes_out);
+
+/* ---- decode / scan ------------------------------------------------------------------------------------ */
+/* Batched decode of [seg_begin, seg_end) into a flat T array: out[row - row_start(seg_begin)].
+ * out is a device pointer when out_on_device, else a host pointer (pinned or pageable). */
+adacom_status adacom_decode(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags, void *out,
+                            int out_on_device);
+/* scan_vector / scan_partial of ONE segment: result[result_offset + i] = value(start + i), i < scan_count
+ * (SuccinctScanPartial, succinct.cpp:123-144).  scan_count may exceed 2048. */
+adacom_status adacom_scan_partial(adacom_column *col, uint64_t seg, uint64_t start, uint64_t scan_count,
+                                  int flags, void *result, uint64_t result_offset, int result_on_device);
+/* UncompressSuccinct over a range: decode back into the raw arena, segments become not compacted */
+adacom_status adacom_uncompact(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags);
+
+/* fused decode + SUM (+COUNT) over a range; result on the host after an internal sync */
+adacom_status adacom_scan_sum(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags, adacom_agg *out);
+/* same, asynchronous: the aggregate is left in device memory (32 bytes, adacom_agg layout) */
+adacom_status adacom_scan_sum_async(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags,
+                                    adacom_agg *device_out);
+/* fused decode + (value <op> constant) + COUNT/SUM of the matching rows; optional selection bitmap
+ * (1 bit per row of the range, bit r - row_start(seg_begin); device pointer, zeroed by the call). */
+adacom_status adacom_scan_filter(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags, adacom_cmp op,
+                                 int64_t constant, adacom_agg *out, uint64_t *device_bitmap);
+/* batch of point filters (the Zipf look-up benchmarks): query q scans segment seg_idx[q] for
+ * value == constants[q]; out_count[q] = matches, out_first_row[q] = first matching row in the segment
+ * (UINT64_MAX when none).  All four arrays are host pointers. */
+adacom_status adacom_point_filter_batch(adacom_column *col, uint64_t n_queries, const uint32_t *seg_idx,
+                                        const int64_t *constants, int flags, uint64_t *out_count,
+                                        uint64_t *out_first_row);
+
+/* ---- fetch_row ------------------------------------------------------------------------------------------ */
+/* batched random access: out[q] = T(vec(seg_idx[q])[row_in_seg[q]] + min).  Host pointers unless
+ * on_device (then all three are device pointers). */
+adacom_status adacom_fetch_rows(adacom_column *col, uint64_t n, const uint32_t *seg_idx, const uint32_t *row_in_seg,
+                                int flags, void *out, int on_device);
+
+/* ---- host-buffer convenience paths (what bench.py's e2e leg times) ------------------------------------ */
+/* host T values -> analyze + encode on the GPU -> metas (+ packed words when host_words_out != NULL,
+ * capacity in words; *total_words_out receives the arena size). The column stays resident in *col_out. */
+adacom_status adacom_compress_host(adacom_ctx *ctx, adacom_ptype type, const void *host_values, uint64_t n_segments,
+                                   const uint64_t *seg_counts, uint32_t seg_capacity, int flags,
+                                   adacom_segment_meta *metas_out, uint64_t *host_words_out,
+                                   uint64_t host_words_capacity, uint64_t *total_words_out,
+                                   adacom_column **col_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ADACOM_GPU_H */
