@@ -21,7 +21,6 @@ static_assert(sizeof(adacom_agg) == sizeof(Agg), "adacom_agg layout");
 
 namespace {
 std::string g_process_error;
-constexpr uint8_t kSegUncompressedFn = 8;  // function swapped to UNCOMPRESSED by Uncompact (GetDataSize rule)
 constexpr size_t kArenaPad = 256;          // slack behind every arena for the 16-byte rounded bulk copies
 }  // namespace
 
@@ -109,6 +108,27 @@ bool type_info(adacom_ptype p, TypeInfo &t) {
 	}
 }
 
+// free every packed extent that no repacked segment references any more (needs a fresh mirror)
+adacom_status gc_extents(adacom_column *col) {
+	adacom_ctx *ctx = col->ctx;
+	for (auto &x : col->extents) {
+		x.live = 0;
+	}
+	for (const SegDesc &d : col->h_desc) {
+		if ((d.state & kSegRepacked) && d.extent < col->extents.size()) {
+			col->extents[d.extent].live++;
+		}
+	}
+	for (auto &x : col->extents) {
+		if (x.base && x.live == 0) {
+			CK(ctx, cudaFreeAsync(x.base, ctx->stream));
+			x.base = nullptr;
+			x.words = 0;
+		}
+	}
+	return ADACOM_OK;
+}
+
 adacom_status sync_mirror(adacom_column *col) {
 	adacom_ctx *ctx = col->ctx;
 	if (col->mirror_dirty) {
@@ -116,6 +136,7 @@ adacom_status sync_mirror(adacom_column *col) {
 		                        ctx->stream));
 		CK(ctx, cudaStreamSynchronize(ctx->stream));
 		col->mirror_dirty = false;
+		return gc_extents(col);
 	}
 	return ADACOM_OK;
 }
@@ -865,91 +886,42 @@ extern "C" adacom_status adacom_scan_partial(adacom_column *col, uint64_t seg, u
 	return ADACOM_OK;
 }
 
-// free every packed extent that no repacked segment references any more
-static adacom_status gc_extents(adacom_column *col) {
-	adacom_ctx *ctx = col->ctx;
-	for (auto &x : col->extents) {
-		x.live = 0;
-	}
-	for (const SegDesc &d : col->h_desc) {
-		if ((d.state & kSegRepacked) && d.extent < col->extents.size()) {
-			col->extents[d.extent].live++;
-		}
-	}
-	for (auto &x : col->extents) {
-		if (x.base && x.live == 0) {
-			CK(ctx, cudaFreeAsync(x.base, ctx->stream));
-			x.base = nullptr;
-			x.words = 0;
-		}
-	}
-	return ADACOM_OK;
-}
-
 extern "C" adacom_status adacom_uncompact(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags) {
 	if (!range_ok(col, seg_begin, seg_end)) {
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_uncompact: bad segment range");
 	}
 	adacom_ctx *ctx = col->ctx;
 	std::lock_guard<std::mutex> lock(ctx->mu);
-	adacom_status st = sync_mirror(col);
+	if (seg_begin == seg_end) {
+		return ADACOM_OK;
+	}
+	adacom_status st = ensure_raw(col);
 	if (st != ADACOM_OK) {
 		return st;
 	}
-	st = ensure_raw(col);
+	st = get_tiles(col, seg_begin, seg_end);
 	if (st != ADACOM_OK) {
 		return st;
 	}
-	// Uncompact() is a no-op for segments that are not compacted (column_segment.cpp:327-330)
-	std::vector<Job> jobs;
-	for (uint64_t g = seg_begin; g < seg_end; g++) {
-		const SegDesc &d = col->h_desc[g];
-		if (!(d.state & kSegCompacted)) {
-			continue;
-		}
-		bool touch = (d.state & kSegRepacked) || ((flags & ADACOM_LITERAL) && d.min_factor != ~0ull);
-		if (!touch) {
-			continue;  // payload already sits in the raw arena at slot width
-		}
-		uint32_t n = (d.count + kVectorSize - 1) / kVectorSize;
-		for (uint32_t k = 0; k < n; k++) {
-			jobs.push_back({(uint32_t)g, k});
-		}
-	}
-	if (!jobs.empty()) {
-		JobTable tmp;
-		st = upload_jobs(col, tmp, jobs);
-		if (st != ADACOM_OK) {
-			return st;
-		}
-		DecodeArgs a;
-		a.desc = col->d_desc;
-		a.jobs = tmp.d_jobs;
-		a.n_jobs = tmp.n;
-		a.tile_granularity = kVectorSize;
-		a.raw = col->raw;
-		a.literal = (flags & ADACOM_LITERAL) ? 1 : 0;
-		a.out = col->raw;
-		a.out_row0 = 0;
-		LAUNCH(ctx, launch_decode(col->t, kModeFlat, a, ctx->sm_count, ctx->stream));
-		CK(ctx, cudaFreeAsync(tmp.d_jobs, ctx->stream));
-	}
-	for (uint64_t g = seg_begin; g < seg_end; g++) {
-		SegDesc &d = col->h_desc[g];
-		if (!(d.state & kSegCompacted)) {
-			continue;
-		}
-		d.state = (uint8_t)((d.state & kSegAnalyzed) | kSegUncompressedFn);
-		d.width = (uint8_t)(8 * col->t.size);
-		d.packed_ptr = 0;
-		d.word_offset = 0;
-	}
-	if (seg_end > seg_begin) {
-		CK(ctx, cudaMemcpyAsync(col->d_desc + seg_begin, col->h_desc.data() + seg_begin,
-		                        (seg_end - seg_begin) * sizeof(SegDesc), cudaMemcpyHostToDevice, ctx->stream));
-	}
+	// fully asynchronous: decode the compacted segments of the range back into the raw arena (the kernel
+	// skips the others), then flip their descriptors on the device.  Dead extents are reclaimed the next time
+	// the host mirror is refreshed.
+	DecodeArgs a;
+	a.desc = col->d_desc;
+	a.jobs = col->tiles.d_jobs;
+	a.n_jobs = col->tiles.n;
+	a.tile_granularity = kVectorSize;
+	a.raw = col->raw;
+	a.literal = (flags & ADACOM_LITERAL) ? 1 : 0;
+	a.uncompact = 1;
+	a.out = col->raw;
+	a.out_row0 = 0;
+	LAUNCH(ctx, launch_decode(col->t, kModeFlat, a, ctx->sm_count, ctx->stream));
+	LAUNCH(ctx, launch_reset_uncompacted(col->d_desc, (uint32_t)seg_begin, (uint32_t)(seg_end - seg_begin), col->t.size,
+	                                     ctx->stream));
+	col->mirror_dirty = true;
 	col->epoch++;
-	return gc_extents(col);
+	return ADACOM_OK;
 }
 
 static adacom_status run_agg(adacom_column *col, uint64_t b, uint64_t e, int flags, DecodeMode mode, uint32_t op_mask,

@@ -14,7 +14,7 @@ constexpr uint32_t kVectorSize = 2048;   // STANDARD_VECTOR_SIZE (vector_size.hp
 constexpr uint32_t kBlockSize = 262136;  // Storage::BLOCK_SIZE (constants.hpp:101-106)
 constexpr uint32_t kSegAlignWords = 16;  // every packed segment starts on a 128-byte boundary
 
-enum : uint8_t { kSegCompacted = 1, kSegRepacked = 2, kSegAnalyzed = 4 };
+enum : uint8_t { kSegCompacted = 1, kSegRepacked = 2, kSegAnalyzed = 4, kSegUncompressedFn = 8 };
 enum : int { kFlagPadded = 1, kFlagLiteral = 2, kFlagZeroExt = 4 };
 
 // Device-resident segment descriptor (64 bytes, one per ColumnSegment).

@@ -20,6 +20,7 @@ struct DecodeArgs {
 	uint32_t tile_granularity = 0;   // kVectorSize -> 2048-value tiles; 0 -> scan chunks (scan_chunk_values(w))
 	const uint8_t *raw = nullptr;    // raw arena (source for segments that are not repacked)
 	int literal = 0;                 // ADACOM_LITERAL: add min even when the segment was not repacked (Q1)
+	int uncompact = 0;               // UncompressSuccinct mode: skip segments that are not compacted
 	// kModeFlat
 	void *out = nullptr;
 	uint64_t out_row0 = 0;           // out[(row_start + i) - out_row0]
@@ -58,6 +59,10 @@ cudaError_t launch_layout(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32_
 // bind packed_ptr = base + word_offset for the repacked segments of the range
 cudaError_t launch_bind_extent(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, uint64_t *base, uint32_t extent,
                                cudaStream_t stream);
+
+// after an uncompact decode: segments of the range that were compacted go back to slot width / UNCOMPRESSED
+cudaError_t launch_reset_uncompacted(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int type_size,
+                                     cudaStream_t stream);
 
 // encode: TMA-staged raw tiles -> FOR subtract + bit-pack into the packed extent
 cudaError_t launch_encode(TypeInfo t, const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw,

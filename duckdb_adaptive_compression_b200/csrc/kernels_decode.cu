@@ -52,6 +52,14 @@ __device__ __forceinline__ void issue_unit(const DecodeArgs &a, uint32_t job_idx
 	uint32_t gran = a.tile_granularity ? a.tile_granularity : scan_chunk_values(w);
 	uint32_t first = j.k * gran;
 	uint32_t cnt = min(gran, count - first);
+	if (a.uncompact) {
+		// Uncompact() is a no-op for segments that are not compacted (column_segment.cpp:327-330); a compacted
+		// segment that kept its slot width already sits in the raw arena (unless literal mode adds min, Q1)
+		bool touch = (state & kSegCompacted) && (repacked || (a.literal && min_factor != ~0ull));
+		if (!touch) {
+			cnt = 0;
+		}
+	}
 	uint64_t src = repacked ? packed_ptr + (((uint64_t)first * w) >> 3)
 	                        : (uint64_t)a.raw + (row_start + first) * (uint64_t)S;
 	uint64_t src16 = src & ~15ull;
@@ -66,8 +74,10 @@ __device__ __forceinline__ void issue_unit(const DecodeArgs &a, uint32_t job_idx
 	info->seg = j.seg;
 	info->first_value = first;
 	info->job = job_idx;
-	mbar_arrive_expect_tx(bar, bytes);
-	tma_load_1d(buf, (const void *)src16, bytes, bar);
+	mbar_arrive_expect_tx(bar, cnt ? bytes : 0u);
+	if (cnt) {
+		tma_load_1d(buf, (const void *)src16, bytes, bar);
+	}
 }
 
 template <int S, bool SIGNED, int MODE>

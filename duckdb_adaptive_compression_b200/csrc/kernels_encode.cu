@@ -242,6 +242,21 @@ __global__ void bind_extent_kernel(SegDesc *desc, uint32_t seg_begin, uint32_t n
 	}
 }
 
+// ColumnSegment::UncompressSuccinct's bookkeeping (column_segment.cpp:494-503): function -> UNCOMPRESSED,
+// compacted = false; the payload was already decoded into the raw arena by the decode kernel.
+__global__ void reset_uncompacted_kernel(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int type_size) {
+	uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+	if (g < n_segs) {
+		SegDesc *d = desc + seg_begin + g;
+		if (d->state & kSegCompacted) {
+			d->state = (uint8_t)((d->state & kSegAnalyzed) | kSegUncompressedFn);
+			d->width = (uint8_t)(8 * type_size);
+			d->packed_ptr = 0;
+			d->word_offset = 0;
+		}
+	}
+}
+
 // ---------------------------------------------------------------------------------------------------
 // encode
 // ---------------------------------------------------------------------------------------------------
@@ -464,6 +479,15 @@ cudaError_t launch_bind_extent(SegDesc *desc, uint32_t seg_begin, uint32_t n_seg
 		return cudaSuccess;
 	}
 	bind_extent_kernel<<<(n_segs + 255) / 256, 256, 0, stream>>>(desc, seg_begin, n_segs, base, extent);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_reset_uncompacted(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int type_size,
+                                     cudaStream_t stream) {
+	if (n_segs == 0) {
+		return cudaSuccess;
+	}
+	reset_uncompacted_kernel<<<(n_segs + 255) / 256, 256, 0, stream>>>(desc, seg_begin, n_segs, type_size);
 	return cudaGetLastError();
 }
 

@@ -48,7 +48,7 @@ def have_reference() -> bool:
 
 
 class _BenchResult(C.Structure):
-    _fields_ = [("analyze_s", C.c_double), ("encode_s", C.c_double), ("scan_s", C.c_double), ("sum_s", C.c_double),
+    _fields_ = [("analyze_s", C.c_double), ("encode_s", C.c_double), ("scan_s", C.c_double), ("sum_s", C.c_double), ("uncompact_s", C.c_double),
                 ("values", C.c_uint64), ("sum_lo", C.c_uint64), ("sum_hi", C.c_uint64), ("sum_count", C.c_uint64),
                 ("packed_bytes", C.c_uint64)]
 
@@ -164,7 +164,7 @@ class Oracle:
                                 seg_capacity, threads, int(copy_per_call), C.byref(res))
         if rc != 0:
             raise RuntimeError("bench_column failed")
-        return dict(analyze_s=res.analyze_s, encode_s=res.encode_s, scan_s=res.scan_s, sum_s=res.sum_s,
+        return dict(analyze_s=res.analyze_s, encode_s=res.encode_s, scan_s=res.scan_s, sum_s=res.sum_s, uncompact_s=res.uncompact_s,
                     values=res.values, sum=(res.sum_hi << 64) | res.sum_lo, packed_bytes=res.packed_bytes)
 
 

@@ -294,7 +294,7 @@ uint64_t ref_segment_serialize(void *h, uint8_t *out, uint64_t out_capacity) {
 
 // Timed CPU baseline on the reference's SDSL: one segment per task, segments dealt round-robin.
 struct ref_bench_result {
-	double analyze_s, encode_s, scan_s, sum_s;
+	double analyze_s, encode_s, scan_s, sum_s, uncompact_s;
 	uint64_t values;
 	uint64_t sum_lo, sum_hi, sum_count;
 	uint64_t packed_bytes;
@@ -311,10 +311,10 @@ int ref_bench_column(const void *values, uint64_t n, uint8_t type_size, int is_s
 		s = ref_segment_new_succinct(type_size, is_signed, seg_capacity * type_size);
 	}
 	const uint8_t *base = (const uint8_t *)values;
-	double phase_s[4] = {0, 0, 0, 0};
+	double phase_s[5] = {0, 0, 0, 0, 0};
 	std::vector<unsigned __int128> sums(threads, 0);
 	std::vector<uint64_t> packed(threads, 0);
-	for (int phase = 0; phase < 4; phase++) {
+	for (int phase = 0; phase < 5; phase++) {
 		std::vector<std::thread> pool;
 		std::vector<double> secs(threads, 0.0);
 		for (int tid = 0; tid < threads; tid++) {
@@ -333,6 +333,8 @@ int ref_bench_column(const void *values, uint64_t n, uint8_t type_size, int is_s
 					} else if (phase == 1) {
 						ref_bit_compress_from_succinct(&seg, 0);
 						packed[tid] += seg.succinct_vec.capacity() >> 3;
+					} else if (phase == 4) {
+						ref_uncompress_succinct(&seg, 0);
 					} else {
 						for (uint64_t off = 0; off < seg.count; off += 2048) {
 							uint64_t m = std::min<uint64_t>(seg.count - off, 2048);
@@ -374,6 +376,7 @@ int ref_bench_column(const void *values, uint64_t n, uint8_t type_size, int is_s
 	out->encode_s = phase_s[1];
 	out->scan_s = phase_s[2];
 	out->sum_s = phase_s[3];
+	out->uncompact_s = phase_s[4];
 	out->values = n;
 	out->sum_lo = (uint64_t)total;
 	out->sum_hi = (uint64_t)(total >> 64);

@@ -531,7 +531,7 @@ typedef struct {
 	int is_signed, threads, tid, copy_per_call, phase;
 	orc_segment *segs;
 	pthread_barrier_t *barrier;
-	double t[4];
+	double t[5];
 	orc_sum128 sum;
 	uint64_t packed_bytes;
 	uint8_t *sink; /* per-thread 2048-value result vector */
@@ -606,6 +606,13 @@ static void *bench_worker(void *arg) {
 		}
 	}
 	t->t[3] = now_s() - t0;
+	/* phase 4: UncompressSuccinct back to a flat block */
+	pthread_barrier_wait(t->barrier);
+	t0 = now_s();
+	for (uint64_t g = (uint64_t)t->tid; g < t->n_segments; g += (uint64_t)t->threads) {
+		orc_uncompress_succinct(&t->segs[g], 0);
+	}
+	t->t[4] = now_s() - t0;
 	return NULL;
 }
 
@@ -647,6 +654,7 @@ int orc_bench_column(const void *values, uint64_t n, uint8_t type_size, int is_s
 		if (t->t[1] > out->encode_s) out->encode_s = t->t[1];
 		if (t->t[2] > out->scan_s) out->scan_s = t->t[2];
 		if (t->t[3] > out->sum_s) out->sum_s = t->t[3];
+		if (t->t[4] > out->uncompact_s) out->uncompact_s = t->t[4];
 		uint64_t old = out->sum.lo;
 		out->sum.lo += t->sum.lo;
 		out->sum.hi += t->sum.hi + (out->sum.lo < old);

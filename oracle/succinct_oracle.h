@@ -121,14 +121,15 @@ void orc_segment_filter(const orc_segment *s, int flags, int op, uint64_t consta
 
 /* ---- timed CPU baseline: one task per segment, T pthreads, segments dealt round-robin ---- */
 typedef struct {
-	double analyze_s, encode_s, scan_s, sum_s; /* wall seconds, max over threads */
+	double analyze_s, encode_s, scan_s, sum_s, uncompact_s; /* wall seconds, max over threads */
 	uint64_t values;
 	orc_sum128 sum;
 	uint64_t packed_bytes;
 } orc_bench_result;
 
 /* values: n T-values; segments of seg_capacity values each (last one short).  Runs append(analyze),
- * BitCompressFromSuccinct, a full SuccinctScanPartial scan in 2048-value vectors, and scan+sum.
+ * BitCompressFromSuccinct, a full SuccinctScanPartial scan in 2048-value vectors, scan+sum and
+ * UncompressSuccinct.
  * copy_per_call != 0 reproduces quirk Q4 (deep copy of the packed segment per scan call). */
 int orc_bench_column(const void *values, uint64_t n, uint8_t type_size, int is_signed, uint64_t seg_capacity,
                      int threads, int copy_per_call, orc_bench_result *out);
