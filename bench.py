@@ -222,6 +222,7 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
     import duckdb_adaptive_compression_b200 as adacom
+    from duckdb_adaptive_compression_b200 import sharding
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -267,9 +268,7 @@ def run_ours(args):
         if world > 1:
             # the only cross-GPU exchange of the path: 64 x {sum_lo, sum_hi, count} per rank over NCCL
             ctx.synchronize()
-            gathered = torch.empty(world * aggs.numel(), dtype=torch.int64, device=dev)
-            dist.all_gather_into_tensor(gathered, aggs)
-            return gathered
+            return sharding.all_gather_aggregates(aggs)
         return None
 
     def barrier():

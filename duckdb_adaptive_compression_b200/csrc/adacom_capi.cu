@@ -41,8 +41,10 @@ struct adacom_ctx {
 
 struct Extent {
 	uint64_t *base = nullptr;
-	uint64_t words = 0;
-	uint64_t live = 0;  // repacked segments still pointing into this extent
+	uint64_t words = 0;      // payload words in use (incl. alignment gaps)
+	uint64_t capacity = 0;   // allocated words
+	uint64_t live = 0;       // repacked segments still pointing into this extent (valid after gc_extents)
+	uint64_t seg_begin = 0, seg_end = 0;  // the encode call that created it covered [seg_begin, seg_end)
 };
 
 struct JobTable {
@@ -64,6 +66,7 @@ struct adacom_column {
 	std::vector<SegDesc> h_desc;
 	bool mirror_dirty = false;
 	std::vector<Extent> extents;
+	std::vector<Extent> spares;  // dead extents kept for the next encode (no allocator call on the hot path)
 	JobTable tiles, chunks;
 	uint64_t epoch = 0;
 };
@@ -108,6 +111,31 @@ bool type_info(adacom_ptype p, TypeInfo &t) {
 	}
 }
 
+// A dead extent becomes a spare for the next encode; at most two spares are kept per column.
+adacom_status retire_extent(adacom_column *col, Extent &x) {
+	adacom_ctx *ctx = col->ctx;
+	if (x.base) {
+		Extent spare;
+		spare.base = x.base;
+		spare.capacity = x.capacity;
+		col->spares.push_back(spare);
+		if (col->spares.size() > 2) {
+			size_t smallest = 0;
+			for (size_t i = 1; i < col->spares.size(); i++) {
+				if (col->spares[i].capacity < col->spares[smallest].capacity) {
+					smallest = i;
+				}
+			}
+			CK(ctx, cudaFreeAsync(col->spares[smallest].base, ctx->stream));
+			col->spares.erase(col->spares.begin() + smallest);
+		}
+	}
+	x.base = nullptr;
+	x.words = 0;
+	x.capacity = 0;
+	return ADACOM_OK;
+}
+
 // free every packed extent that no repacked segment references any more (needs a fresh mirror)
 adacom_status gc_extents(adacom_column *col) {
 	adacom_ctx *ctx = col->ctx;
@@ -121,9 +149,10 @@ adacom_status gc_extents(adacom_column *col) {
 	}
 	for (auto &x : col->extents) {
 		if (x.base && x.live == 0) {
-			CK(ctx, cudaFreeAsync(x.base, ctx->stream));
-			x.base = nullptr;
-			x.words = 0;
+			adacom_status st = retire_extent(col, x);
+			if (st != ADACOM_OK) {
+				return st;
+			}
 		}
 	}
 	return ADACOM_OK;
@@ -488,6 +517,11 @@ extern "C" void adacom_column_destroy(adacom_column *col) {
 			cudaFreeAsync(x.base, ctx->stream);
 		}
 	}
+	for (auto &x : col->spares) {
+		if (x.base) {
+			cudaFreeAsync(x.base, ctx->stream);
+		}
+	}
 	if (col->tiles.d_jobs) {
 		cudaFreeAsync(col->tiles.d_jobs, ctx->stream);
 	}
@@ -572,6 +606,8 @@ extern "C" adacom_status adacom_column_from_packed(adacom_ctx *ctx, adacom_ptype
 	}
 	Extent ext;
 	ext.words = total_words;
+	ext.capacity = total_words;
+	ext.seg_end = n_segments;
 	cudaError_t e = cudaMallocAsync((void **)&ext.base, total_words * 8 + kArenaPad, ctx->stream);
 	if (e == cudaSuccess) {
 		e = cudaMalloc((void **)&col->d_desc, std::max<uint64_t>(n_segments, 1) * sizeof(SegDesc));
@@ -695,9 +731,26 @@ extern "C" adacom_status adacom_encode(adacom_column *col, uint64_t seg_begin, u
 	CK(ctx, cudaStreamSynchronize(ctx->stream));  // the only host round trip: 8 bytes, sizes the new extent
 	Extent ext;
 	ext.words = ctx->h_totals[0];
+	ext.seg_begin = seg_begin;
+	ext.seg_end = seg_end;
 	if (ext.words) {
-		// 2. a fresh extent: scans keep reading the old payloads until the descriptors are re-bound
-		CK(ctx, cudaMallocAsync((void **)&ext.base, ext.words * 8 + kArenaPad, ctx->stream));
+		// 2. a fresh extent: scans keep reading the old payloads until the descriptors are re-bound.
+		//    Prefer a retired extent of this column (smallest that fits) over an allocator call.
+		int pick = -1;
+		for (size_t i = 0; i < col->spares.size(); i++) {
+			if (col->spares[i].capacity >= ext.words &&
+			    (pick < 0 || col->spares[i].capacity < col->spares[(size_t)pick].capacity)) {
+				pick = (int)i;
+			}
+		}
+		if (pick >= 0) {
+			ext.base = col->spares[(size_t)pick].base;
+			ext.capacity = col->spares[(size_t)pick].capacity;
+			col->spares.erase(col->spares.begin() + pick);
+		} else {
+			ext.capacity = ext.words + ext.words / 32 + 64;
+			CK(ctx, cudaMallocAsync((void **)&ext.base, ext.capacity * 8 + kArenaPad, ctx->stream));
+		}
 		LAUNCH(ctx, launch_bind_extent(col->d_desc, (uint32_t)seg_begin, n, ext.base, extent_id, ctx->stream));
 		adacom_status st = get_tiles(col, seg_begin, seg_end);
 		if (st != ADACOM_OK) {
@@ -919,6 +972,16 @@ extern "C" adacom_status adacom_uncompact(adacom_column *col, uint64_t seg_begin
 	LAUNCH(ctx, launch_decode(col->t, kModeFlat, a, ctx->sm_count, ctx->stream));
 	LAUNCH(ctx, launch_reset_uncompacted(col->d_desc, (uint32_t)seg_begin, (uint32_t)(seg_end - seg_begin), col->t.size,
 	                                     ctx->stream));
+	// extents created by encode calls whose range lies inside [seg_begin, seg_end) are dead now (stream order
+	// makes the reuse safe); partially covered ones are reclaimed when the mirror is refreshed
+	for (auto &x : col->extents) {
+		if (x.base && x.seg_begin >= seg_begin && x.seg_end <= seg_end) {
+			st = retire_extent(col, x);
+			if (st != ADACOM_OK) {
+				return st;
+			}
+		}
+	}
 	col->mirror_dirty = true;
 	col->epoch++;
 	return ADACOM_OK;
