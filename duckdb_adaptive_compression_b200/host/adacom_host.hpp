@@ -1,0 +1,355 @@
+// adacom_host.hpp -- C++ host side above the C ABI: the reference's own plugin / segment / policy surface
+// for the succinct path, re-hosted on the GPU codec.
+//
+// Everything here mirrors a reference interface by name, argument meaning and error behaviour so that the
+// storage layer's call sites read the same (paths relative to the reference repository root):
+//
+//   CompressionFunction + typedefs .. src/include/duckdb/function/compression_function.hpp:29-177
+//   SuccinctFun ..................... src/include/duckdb/function/compression/compression.hpp:56-59,
+//                                     src/storage/compression/succinct.cpp:335-382
+//   ColumnSegment ................... src/include/duckdb/storage/table/column_segment.hpp:60,129-214,
+//                                     src/storage/table/column_segment.cpp:45-110,133-346
+//   ColumnSegmentCatalog ............ src/include/duckdb/catalog/catalog_entry/column_segment_catalog.hpp:14-54,
+//                                     src/catalog/catalog_entry/column_segment_catalog.cpp:13-135
+//   DBConfig succinct flags ......... src/include/duckdb/main/config.hpp:189-197
+//   BufferManager data-size counter . src/include/duckdb/storage/buffer_manager.hpp:71-82
+//
+// The stand-ins for Vector / UnifiedVectorFormat / ColumnScanState carry only what the succinct path reads.
+// All arithmetic happens in libadacom_gpu.so; this layer owns no codec loop (and no CPU fallback).
+#pragma once
+
+#include "../../include/adacom_gpu.h"
+
+#include <atomic>
+#include <condition_variable>
+#include <cstdint>
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <thread>
+#include <unordered_map>
+#include <vector>
+
+namespace adacom_host {
+
+using idx_t = uint64_t;
+using row_t = int64_t;
+using data_ptr_t = uint8_t *;
+using block_id_t = int64_t;
+using std::unique_ptr;
+
+constexpr idx_t STANDARD_VECTOR_SIZE = 2048;   // src/include/duckdb/common/vector_size.hpp:17
+constexpr idx_t BLOCK_SIZE = 262144 - 8;       // Storage::BLOCK_SIZE, src/include/duckdb/common/constants.hpp:101-106
+
+struct InternalException : public std::runtime_error {
+	explicit InternalException(const std::string &msg) : std::runtime_error(msg) {
+	}
+};
+
+// src/include/duckdb/common/types.hpp (values of the integer physical types)
+enum class PhysicalType : uint8_t {
+	BOOL = 1, UINT8 = 2, INT8 = 3, UINT16 = 4, INT16 = 5, UINT32 = 6, INT32 = 7, UINT64 = 8, INT64 = 9,
+	FLOAT = 11, DOUBLE = 12, VARCHAR = 200, INT128 = 204
+};
+idx_t GetTypeIdSize(PhysicalType type);
+bool TypeIsInteger(PhysicalType type);  // src/common/types.cpp:318-320 (INT128 included, quirk Q6)
+
+// src/include/duckdb/common/enums/compression_type.hpp:16-29
+enum class CompressionType : uint8_t { COMPRESSION_AUTO = 0, COMPRESSION_UNCOMPRESSED = 1, COMPRESSION_SUCCINCT = 10 };
+
+enum class VectorType : uint8_t { FLAT_VECTOR = 0 };
+
+// ---- minimal Vector / UnifiedVectorFormat ---------------------------------------------------------------
+struct Vector {
+	explicit Vector(PhysicalType type) : type(type), buffer(STANDARD_VECTOR_SIZE * GetTypeIdSize(type)) {
+	}
+	Vector(PhysicalType type, idx_t capacity) : type(type), buffer(capacity * GetTypeIdSize(type)) {
+	}
+	void SetVectorType(VectorType t) {
+		vector_type = t;
+	}
+	PhysicalType type;
+	VectorType vector_type = VectorType::FLAT_VECTOR;
+	std::vector<uint8_t> buffer;
+};
+struct FlatVector {
+	static data_ptr_t GetData(Vector &v) {
+		return v.buffer.data();
+	}
+};
+struct SelectionVector {
+	const uint32_t *sel = nullptr;  // nullptr = identity
+	idx_t get_index(idx_t i) const {
+		return sel ? sel[i] : i;
+	}
+};
+struct ValidityMask {
+	const uint64_t *mask = nullptr;  // nullptr = all valid
+	bool AllValid() const {
+		return mask == nullptr;
+	}
+	bool RowIsValid(idx_t row) const {
+		return !mask || ((mask[row >> 6] >> (row & 63)) & 1);
+	}
+};
+struct UnifiedVectorFormat {
+	const SelectionVector *sel = nullptr;
+	data_ptr_t data = nullptr;
+	ValidityMask validity;
+};
+
+// ---- state objects of the plugin ABI (compression_function.hpp:29-51) -----------------------------------
+struct AnalyzeState { virtual ~AnalyzeState() = default; };
+struct CompressionState { virtual ~CompressionState() = default; };
+struct CompressedSegmentState { virtual ~CompressedSegmentState() = default; };
+struct SegmentScanState { virtual ~SegmentScanState() = default; };
+struct CompressionAppendState { virtual ~CompressionAppendState() = default; };
+
+class ColumnSegment;
+class ColumnData;
+class ColumnDataCheckpointer;
+struct SegmentStatistics {
+	bool has_value = false;
+	int64_t min = 0, max = 0;      // signed view
+	uint64_t umin = 0, umax = 0;   // unsigned view
+};
+struct ColumnScanState {  // src/include/duckdb/storage/table/scan_state.hpp:43-74
+	ColumnSegment *current = nullptr;
+	idx_t row_index = 0;
+	idx_t internal_index = 0;
+	unique_ptr<SegmentScanState> scan_state;
+};
+struct ColumnFetchState {};
+struct ColumnAppendState {
+	unique_ptr<CompressionAppendState> append_state;
+};
+
+// ---- plugin vtable: same slots, same signatures (compression_function.hpp:65-177) -----------------------
+typedef unique_ptr<AnalyzeState> (*compression_init_analyze_t)(ColumnData &col_data, PhysicalType type);
+typedef bool (*compression_analyze_t)(AnalyzeState &state, Vector &input, idx_t count);
+typedef idx_t (*compression_final_analyze_t)(AnalyzeState &state);
+typedef unique_ptr<CompressionState> (*compression_init_compression_t)(ColumnDataCheckpointer &checkpointer,
+                                                                       unique_ptr<AnalyzeState> state);
+typedef void (*compression_compress_data_t)(CompressionState &state, Vector &scan_vector, idx_t count);
+typedef void (*compression_compress_finalize_t)(CompressionState &state);
+typedef unique_ptr<SegmentScanState> (*compression_init_segment_scan_t)(ColumnSegment &segment);
+typedef void (*compression_scan_vector_t)(ColumnSegment &segment, ColumnScanState &state, idx_t scan_count,
+                                          Vector &result);
+typedef void (*compression_scan_partial_t)(ColumnSegment &segment, ColumnScanState &state, idx_t scan_count,
+                                           Vector &result, idx_t result_offset);
+typedef void (*compression_fetch_row_t)(ColumnSegment &segment, ColumnFetchState &state, row_t row_id, Vector &result,
+                                        idx_t result_idx);
+typedef void (*compression_skip_t)(ColumnSegment &segment, ColumnScanState &state, idx_t skip_count);
+typedef unique_ptr<CompressedSegmentState> (*compression_init_segment_t)(ColumnSegment &segment, block_id_t block_id);
+typedef unique_ptr<CompressionAppendState> (*compression_init_append_t)(ColumnSegment &segment);
+typedef idx_t (*compression_append_t)(CompressionAppendState &append_state, ColumnSegment &segment,
+                                      SegmentStatistics &stats, UnifiedVectorFormat &data, idx_t offset, idx_t count);
+typedef idx_t (*compression_finalize_append_t)(ColumnSegment &segment, SegmentStatistics &stats);
+typedef void (*compression_revert_append_t)(ColumnSegment &segment, idx_t start_row);
+
+class CompressionFunction {
+public:
+	CompressionType type;
+	PhysicalType data_type;
+	compression_init_analyze_t init_analyze;
+	compression_analyze_t analyze;
+	compression_final_analyze_t final_analyze;
+	compression_init_compression_t init_compression;
+	compression_compress_data_t compress;
+	compression_compress_finalize_t compress_finalize;
+	compression_init_segment_scan_t init_scan;
+	compression_scan_vector_t scan_vector;
+	compression_scan_partial_t scan_partial;
+	compression_fetch_row_t fetch_row;
+	compression_skip_t skip;
+	compression_init_segment_t init_segment;
+	compression_init_append_t init_append;
+	compression_append_t append;
+	compression_finalize_append_t finalize_append;
+	compression_revert_append_t revert_append;
+};
+
+// Drop-in for SuccinctFun (src/storage/compression/succinct.cpp:335-382): same two static entry points.
+struct SuccinctGpuFun {
+	static CompressionFunction GetFunction(PhysicalType data_type);  // throws InternalException if unsupported
+	static bool TypeIsSupported(PhysicalType type);
+};
+
+// ---- database-level singletons the segment code reaches for ---------------------------------------------
+struct DBConfig {  // src/include/duckdb/main/config.hpp:189-197 (same names, same defaults)
+	bool succinct_enabled = true;
+	bool succinct_extract_prefix_enabled = true;
+	bool succinct_padded_to_next_byte_enabled = false;
+	bool adaptive_succinct_compression_enabled = false;
+	int gpu_device = 0;                      // B200 ordinal this database instance is pinned to
+	double compression_rate = 0.90;          // column_segment_catalog.cpp:65
+	double background_interval_s = 10.0;     // column_segment_catalog.cpp:70
+	CompressionFunction *GetCompressionFunction(CompressionType type, PhysicalType data_type);  // registry, locked
+
+private:
+	std::mutex lock;
+	std::unordered_map<uint32_t, std::unique_ptr<CompressionFunction>> functions;
+};
+
+class BufferManager {  // the two counters the succinct code adjusts (buffer_manager.hpp:71-82)
+public:
+	void AddToDataSize(int64_t delta) {
+		data_size += delta;
+	}
+	idx_t GetDataSize() const {
+		return (idx_t)data_size.load();
+	}
+
+private:
+	std::atomic<int64_t> data_size {0};
+};
+
+// Anything the access-frequency policy can compact: ColumnSegment implements it, CPU tests use a fake.
+class CompactableSegment {
+public:
+	virtual ~CompactableSegment() = default;
+	virtual void Compact() = 0;
+	virtual void Uncompact() = 0;
+	virtual idx_t GetDataSize() const = 0;
+	virtual bool IsDataSegment() const = 0;
+};
+
+struct AccessStatistics {
+	idx_t num_reads;
+};
+
+// Same public surface as the reference's ColumnSegmentCatalog; the statistics map is guarded by a mutex and
+// Compact/Uncompact run under it (the reference's races, quirk Q5, are not reproduced).
+class ColumnSegmentCatalog {
+public:
+	explicit ColumnSegmentCatalog(double compression_rate = 0.90, double interval_s = 10.0);
+	~ColumnSegmentCatalog();
+	void AddColumnSegment(CompactableSegment *segment);
+	void AddReadAccess(CompactableSegment *segment);
+	void RemoveColumnSegment(CompactableSegment *segment);
+	void EnableBackgroundThreadCompaction();
+	bool BackgroundCompactionEnabled() const {
+		return background_compaction_enabled;
+	}
+	void CompactAllSegments();
+	size_t GetTotalDataSize();
+	//! One iteration of CompressLowestKSegments' loop body (column_segment_catalog.cpp:71-112): sort by
+	//! reads, Compact() the coldest `compression_rate` share, Uncompact() the rest, zero the counters.
+	//! Returns {compacted, uncompacted}.
+	std::pair<size_t, size_t> RunCompactionEpoch();
+	idx_t NumReads(CompactableSegment *segment);
+	void StopBackgroundThread();
+
+private:
+	void CompressLowestKSegments();
+	std::mutex lock;
+	std::unordered_map<CompactableSegment *, AccessStatistics> statistics;
+	idx_t event_counter = 0;
+	bool background_compaction_enabled = false;
+	double compression_rate;
+	double interval_s;
+	std::thread worker;
+	std::condition_variable cv;
+	bool stop = false;
+};
+
+class DatabaseInstance {
+public:
+	explicit DatabaseInstance(const DBConfig *cfg = nullptr);
+	~DatabaseInstance();
+	DBConfig config;
+	BufferManager buffer_manager;
+	ColumnSegmentCatalog column_segment_catalog;
+	adacom_ctx *gpu = nullptr;  // created lazily by Gpu(); throws InternalException when no B200 is usable
+	adacom_ctx *Gpu();
+	[[noreturn]] void Throw(const char *what);
+};
+
+// ---- ColumnSegment ----------------------------------------------------------------------------------------
+enum class ColumnSegmentType : uint8_t { TRANSIENT, PERSISTENT };
+
+class ColumnSegment : public CompactableSegment {
+public:
+	//! ColumnSegment::CreateTransientSegment (column_segment.cpp:45-82): SUCCINCT for integer types when
+	//! succinct_enabled && !adaptive, else UNCOMPRESSED (adaptive mode compacts in the background).
+	static unique_ptr<ColumnSegment> CreateTransientSegment(DatabaseInstance &db, PhysicalType type, idx_t start,
+	                                                        idx_t segment_size = BLOCK_SIZE);
+	~ColumnSegment() override;
+
+	void InitializeScan(ColumnScanState &state);
+	void Scan(ColumnScanState &state, idx_t scan_count, Vector &result, idx_t result_offset, bool entire_vector);
+	void FetchRow(ColumnFetchState &state, row_t row_id, Vector &result, idx_t result_idx);
+	void Skip(ColumnScanState &state);
+	void InitializeAppend(ColumnAppendState &state);
+	idx_t Append(ColumnAppendState &state, UnifiedVectorFormat &data, idx_t offset, idx_t count);
+	idx_t FinalizeAppend(ColumnAppendState &state);
+
+	void Compact() override;
+	void Uncompact() override;
+	idx_t GetDataSize() const override;
+	idx_t SuccinctSize() const;
+	bool IsDataSegment() const override {
+		return is_data_segment;
+	}
+	idx_t SegmentSize() const {
+		return segment_size;
+	}
+	idx_t GetRelativeIndex(idx_t row_index) const {
+		return row_index - start;
+	}
+	uint64_t GetMinFactor();
+	uint64_t GetMax();
+	uint8_t Width();
+	bool IsBitCompressed() const {
+		return compacted;
+	}
+
+	DatabaseInstance &db;
+	PhysicalType type;
+	idx_t type_size;
+	ColumnSegmentType segment_type = ColumnSegmentType::TRANSIENT;
+	idx_t start;
+	idx_t count = 0;
+	idx_t num_elements = 0;
+	CompressionFunction *function;
+	SegmentStatistics stats;
+	idx_t segment_size;
+	bool compacted = false;
+	bool succinct_possible = false;
+	bool background_compaction_enabled = false;
+	bool is_data_segment = false;
+	bool force_reinitializing_scan_state = false;
+	std::mutex bit_compression_lock;
+
+	// device side: one single-segment column of the C ABI; values are staged here until the first Compact()
+	adacom_column *gpu_column = nullptr;
+	std::vector<uint8_t> staging;         // slot-width host image of the appended values (== the raw arena)
+	std::vector<uint64_t> staging_validity;
+	bool staging_has_nulls = false;
+	idx_t uploaded = 0;                   // values already copied to the device
+	uint64_t epoch = 0;                   // bumped by Compact/Uncompact: scan states re-initialise
+
+private:
+	ColumnSegment(DatabaseInstance &db, PhysicalType type, idx_t start, idx_t segment_size, CompressionFunction *function,
+	              bool succinct_possible, bool background, bool is_data_segment);
+	void Scan(ColumnScanState &state, idx_t scan_count, Vector &result);
+	void ScanPartial(ColumnScanState &state, idx_t scan_count, Vector &result, idx_t result_offset);
+	void EnsureDeviceColumn();
+	void Upload();
+	adacom_segment_meta Meta() const;
+	friend struct SuccinctGpuFun;
+};
+
+adacom_ptype ToAdacomType(PhysicalType type);
+
+// Hooks for the checkpoint-style slots: ColumnData / ColumnDataCheckpointer are opaque to the plugin ABI, so
+// the driver (DuckDB's ColumnDataCheckpointer::WriteToDisk, or a test) binds the database instance and reads
+// the flushed segments through these.
+void BindAnalyzeDatabase(DatabaseInstance *db);
+ColumnDataCheckpointer *NewCheckpointer(DatabaseInstance &db, PhysicalType type, idx_t row_start);
+void DeleteCheckpointer(ColumnDataCheckpointer *cp);
+std::vector<unique_ptr<ColumnSegment>> &CheckpointerSegments(ColumnDataCheckpointer &cp);
+
+}  // namespace adacom_host

@@ -1,0 +1,278 @@
+// host_test.cpp -- drives the C++ shim the way DuckDB drives the reference (needs a B200):
+//   ColumnData::AppendData      -> ColumnSegment::Append in 2048-value vectors, new segment when full
+//   ColumnData::ScanVector      -> ColumnSegment::Scan with row-group aligned vectors (start = 2048k + c),
+//                                  vectors straddling two segments arrive as two scan_partial calls
+//   ColumnData::FetchRow        -> ColumnSegment::FetchRow
+//   ColumnSegmentCatalog        -> CompactAllSegments / RunCompactionEpoch / GetTotalDataSize
+//   ColumnDataCheckpointer      -> init_analyze/analyze/final_analyze, init_compression/compress/compress_finalize
+#include "../adacom_host.hpp"
+
+#include <cstdio>
+#include <cstdlib>
+#include <random>
+
+using namespace adacom_host;
+
+#define CHECK(cond)                                                           \
+	do {                                                                      \
+		if (!(cond)) {                                                        \
+			fprintf(stderr, "FAILED %s:%d: %s\n", __FILE__, __LINE__, #cond); \
+			exit(1);                                                          \
+		}                                                                     \
+	} while (0)
+
+template <class T>
+struct Column {  // the slice of ColumnData the succinct path needs
+	DatabaseInstance &db;
+	PhysicalType type;
+	std::vector<unique_ptr<ColumnSegment>> segments;
+	ColumnAppendState append_state;
+	idx_t rows = 0;
+	Column(DatabaseInstance &db, PhysicalType type) : db(db), type(type) {
+	}
+	void AppendTransientSegment(idx_t start_row) {
+		segments.push_back(ColumnSegment::CreateTransientSegment(db, type, start_row));
+		segments.back()->InitializeAppend(append_state);
+	}
+	void AppendData(const T *values, const uint64_t *validity, idx_t count) {  // column_data.cpp:249-270
+		UnifiedVectorFormat vdata;
+		vdata.data = (data_ptr_t)values;
+		vdata.validity.mask = validity;
+		idx_t offset = 0;
+		while (count > 0) {
+			if (segments.empty()) {
+				AppendTransientSegment(rows);
+			}
+			idx_t copied = segments.back()->Append(append_state, vdata, offset, count);
+			rows += copied;
+			if (copied == count) {
+				break;
+			}
+			AppendTransientSegment(rows);
+			offset += copied;
+			count -= copied;
+		}
+	}
+	ColumnSegment *GetSegment(idx_t row) {
+		for (auto &s : segments) {
+			if (row >= s->start && row < s->start + s->count) {
+				return s.get();
+			}
+		}
+		return nullptr;
+	}
+	// ColumnData::ScanVector (column_data.cpp:92-139): one <=2048 vector starting at `row`
+	idx_t ScanVector(ColumnScanState &state, idx_t row, Vector &result) {
+		idx_t remaining = std::min<idx_t>(STANDARD_VECTOR_SIZE, rows - row);
+		idx_t scanned = 0;
+		while (remaining > 0) {
+			ColumnSegment *seg = GetSegment(row + scanned);
+			if (state.current != seg) {
+				state.current = seg;
+				seg->InitializeScan(state);
+			}
+			state.row_index = row + scanned;
+			idx_t in_seg = std::min<idx_t>(remaining, seg->start + seg->count - state.row_index);
+			bool entire = scanned == 0 && in_seg == remaining;
+			seg->Scan(state, in_seg, result, scanned, entire);
+			scanned += in_seg;
+			remaining -= in_seg;
+		}
+		return scanned;
+	}
+};
+
+template <class T>
+void RunColumn(DatabaseInstance &db, PhysicalType type, idx_t n, uint64_t span, int64_t base, bool nulls) {
+	std::mt19937_64 rng(42 + n + span);
+	std::vector<T> values(n);
+	for (auto &v : values) {
+		v = (T)(base + (int64_t)(rng() % span));
+	}
+	std::vector<uint64_t> validity((n + 63) / 64, ~0ull);
+	if (nulls) {
+		for (idx_t i = 0; i < n; i += 7) {
+			validity[i >> 6] &= ~(1ull << (i & 63));
+		}
+	}
+	Column<T> col(db, type);
+	for (idx_t off = 0; off < n; off += STANDARD_VECTOR_SIZE) {
+		idx_t m = std::min<idx_t>(STANDARD_VECTOR_SIZE, n - off);
+		// each call sees vector-local validity bits, like UnifiedVectorFormat
+		std::vector<uint64_t> local((m + 63) / 64, ~0ull);
+		for (idx_t i = 0; i < m; i++) {
+			if (!((validity[(off + i) >> 6] >> ((off + i) & 63)) & 1)) {
+				local[i >> 6] &= ~(1ull << (i & 63));
+			}
+		}
+		col.AppendData(values.data() + off, nulls ? local.data() : nullptr, m);
+	}
+	CHECK(col.rows == n);
+	idx_t cap = BLOCK_SIZE / sizeof(T);
+	CHECK(col.segments.size() == (n + cap - 1) / cap);
+	// full segments were compacted by Append (column_segment.cpp:266-268); the last one compacts lazily on scan
+	for (size_t g = 0; g + 1 < col.segments.size(); g++) {
+		CHECK(col.segments[g]->IsBitCompressed());
+	}
+	// full scan in row-aligned vectors, as TableScan would
+	ColumnScanState state;
+	Vector result(type);
+	for (idx_t row = 0; row < n; row += STANDARD_VECTOR_SIZE) {
+		idx_t got = col.ScanVector(state, row, result);
+		auto out = (T *)FlatVector::GetData(result);
+		for (idx_t i = 0; i < got; i++) {
+			bool valid = (validity[(row + i) >> 6] >> ((row + i) & 63)) & 1;
+			if (valid) {
+				CHECK(out[i] == values[row + i]);
+			}
+		}
+	}
+	CHECK(col.segments.back()->IsBitCompressed());
+	// sizes: sum of 9 + 8*ceil(n*w/64)
+	idx_t total = 0;
+	for (auto &s : col.segments) {
+		idx_t w = s->Width();
+		idx_t expect = w < 8 * sizeof(T) ? 9 + 8 * ((s->count * w + 63) / 64) : 9 + 8 * ((s->SegmentSize() * 8 + 63) / 64);
+		CHECK(s->GetDataSize() == expect);
+		total += expect;
+	}
+	CHECK(db.column_segment_catalog.GetTotalDataSize() >= total);
+	// fetch_row (intended semantics)
+	ColumnFetchState fstate;
+	Vector one(type);
+	for (int q = 0; q < 200; q++) {
+		idx_t row = rng() % n;
+		if (!((validity[row >> 6] >> (row & 63)) & 1)) {
+			continue;
+		}
+		col.GetSegment(row)->FetchRow(fstate, (row_t)row, one, 3);
+		CHECK(((T *)FlatVector::GetData(one))[3] == values[row]);
+	}
+	// Uncompact + re-scan + append after uncompact
+	col.segments[0]->Uncompact();
+	CHECK(!col.segments[0]->IsBitCompressed());
+	CHECK(col.segments[0]->GetDataSize() == col.segments[0]->SegmentSize());
+	ColumnScanState state2;
+	idx_t got = col.ScanVector(state2, 0, result);
+	for (idx_t i = 0; i < got; i++) {
+		if ((validity[i >> 6] >> (i & 63)) & 1) {
+			CHECK(((T *)FlatVector::GetData(result))[i] == values[i]);
+		}
+	}
+	CHECK(col.segments[0]->IsBitCompressed());  // lazily compacted again by the scan (non-adaptive mode)
+}
+
+int main() {
+	DatabaseInstance db;
+	idx_t base_size = db.buffer_manager.GetDataSize();
+	CHECK(base_size == 0);
+	RunColumn<int64_t>(db, PhysicalType::INT64, 100000, 1ull << 40, -5000000000000ll, false);
+	RunColumn<uint32_t>(db, PhysicalType::UINT32, 200000, 1ull << 16, 1000000, false);
+	RunColumn<int32_t>(db, PhysicalType::INT32, 150000, 1ull << 12, -100000, true);
+	RunColumn<int16_t>(db, PhysicalType::INT16, 300000, 1ull << 9, 100, false);
+	RunColumn<uint8_t>(db, PhysicalType::UINT8, 300000, 1ull << 5, 3, false);
+
+	// unsupported types raise InternalException exactly like SuccinctFun::GetFunction
+	bool threw = false;
+	try {
+		SuccinctGpuFun::GetFunction(PhysicalType::DOUBLE);
+	} catch (const InternalException &) {
+		threw = true;
+	}
+	CHECK(threw);
+	CHECK(!SuccinctGpuFun::TypeIsSupported(PhysicalType::INT128));
+	CHECK(SuccinctGpuFun::TypeIsSupported(PhysicalType::UINT16));
+
+	// adaptive mode: segments start UNCOMPRESSED, the policy compacts the cold 90 % and leaves the hot ones flat
+	{
+		DBConfig cfg;
+		cfg.adaptive_succinct_compression_enabled = true;
+		DatabaseInstance adb(&cfg);
+		Column<uint32_t> col(adb, PhysicalType::UINT32);
+		idx_t n = 65534 * 10;
+		std::vector<uint32_t> values(n);
+		for (idx_t i = 0; i < n; i++) {
+			values[i] = (uint32_t)i;
+		}
+		for (idx_t off = 0; off < n; off += STANDARD_VECTOR_SIZE) {
+			col.AppendData(values.data() + off, nullptr, std::min<idx_t>(STANDARD_VECTOR_SIZE, n - off));
+		}
+		CHECK(col.segments.size() == 10);
+		size_t before = adb.column_segment_catalog.GetTotalDataSize();
+		CHECK(before == 10 * BLOCK_SIZE);
+		ColumnScanState state;
+		Vector result(PhysicalType::UINT32);
+		for (int rep = 0; rep < 5; rep++) {  // segment 9 is hot
+			col.ScanVector(state, 65534 * 9 + 2, result);
+		}
+		for (auto &s : col.segments) {
+			CHECK(!s->IsBitCompressed());  // background mode: no lazy compaction on scan
+		}
+		auto res = adb.column_segment_catalog.RunCompactionEpoch();
+		CHECK(res.first == 9 && res.second == 1);  // 9/10 = 0.9f < 0.90 (reference float arithmetic)
+		CHECK(!col.segments[9]->IsBitCompressed());
+		size_t after = adb.column_segment_catalog.GetTotalDataSize();
+		CHECK(after == 9 * (9 + 8 * ((65534 * 16 + 63) / 64)) + 1 * BLOCK_SIZE);
+		// values survive (the build stores the frame of reference; reference quirk Q2 loses it)
+		for (idx_t row = 0; row < n; row += 50000) {
+			col.ScanVector(state, row, result);
+			CHECK(((uint32_t *)FlatVector::GetData(result))[0] == values[row]);
+		}
+	}
+
+	// checkpoint-style slots with real meaning: exact size from analyze, segments from compress
+	{
+		DatabaseInstance cdb;
+		BindAnalyzeDatabase(&cdb);
+		CompressionFunction fn = SuccinctGpuFun::GetFunction(PhysicalType::UINT32);
+		idx_t n = 200000;
+		std::vector<uint32_t> values(n);
+		for (idx_t i = 0; i < n; i++) {
+			values[i] = (uint32_t)i;
+		}
+		ColumnData *no_column_data = nullptr;
+		auto astate = fn.init_analyze(*no_column_data, PhysicalType::UINT32);
+		Vector v(PhysicalType::UINT32);
+		for (idx_t off = 0; off < n; off += STANDARD_VECTOR_SIZE) {
+			idx_t m = std::min<idx_t>(STANDARD_VECTOR_SIZE, n - off);
+			memcpy(v.buffer.data(), values.data() + off, m * 4);
+			CHECK(fn.analyze(*astate, v, m));
+		}
+		idx_t score = fn.final_analyze(*astate);
+		// 65534 x3 at 16/17/18 bits + 3398: 9 + 8*ceil(n*w/64) each
+		idx_t expect = 0;
+		idx_t counts[4] = {65534, 65534, 65534, 3398};
+		idx_t first = 0;
+		for (idx_t c : counts) {
+			uint64_t range = c - 1;
+			idx_t w = 1;
+			while ((range >> w) != 0) {
+				w++;
+			}
+			expect += 9 + 8 * ((c * w + 63) / 64);
+			first += c;
+		}
+		CHECK(score == expect);
+		ColumnDataCheckpointer *cp = NewCheckpointer(cdb, PhysicalType::UINT32, 0);
+		auto cstate = fn.init_compression(*cp, std::move(astate));
+		for (idx_t off = 0; off < n; off += STANDARD_VECTOR_SIZE) {
+			idx_t m = std::min<idx_t>(STANDARD_VECTOR_SIZE, n - off);
+			memcpy(v.buffer.data(), values.data() + off, m * 4);
+			fn.compress(*cstate, v, m);
+		}
+		fn.compress_finalize(*cstate);
+		auto &segs = CheckpointerSegments(*cp);
+		CHECK(segs.size() == 4);
+		idx_t bytes = 0;
+		for (auto &s : segs) {
+			CHECK(s->IsBitCompressed());
+			bytes += s->GetDataSize();
+		}
+		CHECK(bytes == expect);
+		cstate.reset();
+		DeleteCheckpointer(cp);
+		BindAnalyzeDatabase(nullptr);
+	}
+	printf("HOST_TESTS_OK\n");
+	return 0;
+}

@@ -1,0 +1,43 @@
+"""The C++ host shim above the C ABI (duckdb_adaptive_compression_b200/host): the reference's
+CompressionFunction / ColumnSegment / ColumnSegmentCatalog surface re-hosted on the GPU codec."""
+import os
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HOST = os.path.join(ROOT, "duckdb_adaptive_compression_b200", "host")
+
+
+def _build():
+    subprocess.check_call(["make", "-C", HOST], stdout=subprocess.DEVNULL)
+
+
+def test_policy_decision_rule_cpu():
+    """90/10 split with the reference's float arithmetic, counter reset, accounting, thread start/stop."""
+    _build()
+    out = subprocess.check_output([os.path.join(HOST, "build", "policy_test")], text=True, timeout=60)
+    assert "POLICY_TESTS_OK" in out
+
+
+def test_shim_exports_reference_surface():
+    _build()
+    out = subprocess.check_output(["nm", "-DC", "--defined-only", os.path.join(HOST, "libadacom_host.so")], text=True)
+    for sym in ["adacom_host::SuccinctGpuFun::GetFunction", "adacom_host::SuccinctGpuFun::TypeIsSupported",
+                "adacom_host::ColumnSegment::CreateTransientSegment", "adacom_host::ColumnSegment::Compact",
+                "adacom_host::ColumnSegment::Uncompact", "adacom_host::ColumnSegment::GetDataSize",
+                "adacom_host::ColumnSegment::Scan", "adacom_host::ColumnSegment::FetchRow",
+                "adacom_host::ColumnSegment::Append", "adacom_host::ColumnSegmentCatalog::AddReadAccess",
+                "adacom_host::ColumnSegmentCatalog::CompactAllSegments",
+                "adacom_host::ColumnSegmentCatalog::GetTotalDataSize",
+                "adacom_host::ColumnSegmentCatalog::EnableBackgroundThreadCompaction"]:
+        assert sym in out, sym
+
+
+@pytest.mark.gpu
+def test_shim_driven_like_duckdb_gpu():
+    exe = os.path.join(HOST, "build", "host_test")
+    if not os.path.exists(exe):
+        _build()
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "HOST_TESTS_OK" in r.stdout, r.stdout + r.stderr
