@@ -67,7 +67,7 @@ struct adacom_column {
 	bool mirror_dirty = false;
 	std::vector<Extent> extents;
 	std::vector<Extent> spares;  // dead extents kept for the next encode (no allocator call on the hot path)
-	JobTable tiles, chunks;
+	JobTable tiles, chunks, chunks_fast, chunks_slow;
 	uint64_t epoch = 0;
 };
 
@@ -210,7 +210,35 @@ adacom_status get_tiles(adacom_column *col, uint64_t b, uint64_t e) {
 	return st;
 }
 
-// <=16 KiB scan chunks of [b, e): depends on the current widths -> needs the mirror
+uint64_t extend_low_host(uint64_t x, int type_size, bool is_signed) {
+	if (type_size == 8) {
+		return x;
+	}
+	const unsigned shift = 64u - 8u * (unsigned)type_size;
+	return is_signed ? (uint64_t)(((int64_t)(x << shift)) >> shift) : ((x << shift) >> shift);
+}
+
+// sum(decoded) == sum(fields) + count * extend(min) holds when [min, min + 2^w - 1] does not wrap 2^64 and
+// stays inside one sign / truncation zone of T (true for every segment the reference can represent)
+bool linear_zone(const SegDesc &d, int type_size, bool is_signed) {
+	if (!(d.state & kSegRepacked) || d.width >= 64) {
+		return false;
+	}
+	const uint64_t lo = d.min_factor == ~0ull ? 0 : d.min_factor;
+	const uint64_t range = (1ull << d.width) - 1;
+	const uint64_t hi = lo + range;
+	if (hi < lo) {
+		return false;
+	}
+	const uint64_t e_lo = extend_low_host(lo, type_size, is_signed), e_hi = extend_low_host(hi, type_size, is_signed);
+	if (e_hi - e_lo != range) {
+		return false;
+	}
+	return is_signed ? (int64_t)e_lo <= (int64_t)e_hi : e_lo <= e_hi;
+}
+
+// <=16 KiB scan chunks of [b, e): depends on the current widths -> needs the mirror.  Three tables: every
+// chunk (filter / generic), and the SUM split into the width-specialised fast path and the generic rest.
 adacom_status get_chunks(adacom_column *col, uint64_t b, uint64_t e) {
 	JobTable &tab = col->chunks;
 	if (tab.begin == b && tab.end == e && tab.epoch == col->epoch) {
@@ -220,16 +248,24 @@ adacom_status get_chunks(adacom_column *col, uint64_t b, uint64_t e) {
 	if (st != ADACOM_OK) {
 		return st;
 	}
-	std::vector<Job> jobs;
+	std::vector<Job> jobs, fast, slow;
 	for (uint64_t g = b; g < e; g++) {
 		const SegDesc &d = col->h_desc[g];
 		uint32_t gran = scan_chunk_values(d.width);
 		uint32_t n = (d.count + gran - 1) / gran;
+		std::vector<Job> &split = linear_zone(d, col->t.size, col->t.is_signed) ? fast : slow;
 		for (uint32_t k = 0; k < n; k++) {
 			jobs.push_back({(uint32_t)g, k});
+			split.push_back({(uint32_t)g, k});
 		}
 	}
 	st = upload_jobs(col, tab, jobs);
+	if (st == ADACOM_OK) {
+		st = upload_jobs(col, col->chunks_fast, fast);
+	}
+	if (st == ADACOM_OK) {
+		st = upload_jobs(col, col->chunks_slow, slow);
+	}
 	if (st == ADACOM_OK) {
 		tab.begin = b;
 		tab.end = e;
@@ -525,8 +561,10 @@ extern "C" void adacom_column_destroy(adacom_column *col) {
 	if (col->tiles.d_jobs) {
 		cudaFreeAsync(col->tiles.d_jobs, ctx->stream);
 	}
-	if (col->chunks.d_jobs) {
-		cudaFreeAsync(col->chunks.d_jobs, ctx->stream);
+	for (JobTable *t : {&col->chunks, &col->chunks_fast, &col->chunks_slow}) {
+		if (t->d_jobs) {
+			cudaFreeAsync(t->d_jobs, ctx->stream);
+		}
 	}
 	cudaStreamSynchronize(ctx->stream);
 	cudaFree(col->raw);
@@ -995,10 +1033,24 @@ static adacom_status run_agg(adacom_column *col, uint64_t b, uint64_t e, int fla
 		return st;
 	}
 	CK(ctx, cudaMemsetAsync(device_out, 0, sizeof(Agg), ctx->stream));
+	const bool split_sum = mode == kModeSum;
+	if (split_sum && col->chunks_fast.n) {
+		ScanSumArgs f;
+		f.desc = col->d_desc;
+		f.jobs = col->chunks_fast.d_jobs;
+		f.n_jobs = col->chunks_fast.n;
+		f.type_size = col->t.size;
+		f.is_signed = col->t.is_signed ? 1 : 0;
+		f.agg = device_out;
+		LAUNCH(ctx, launch_scan_sum_fields(f, ctx->sm_count, ctx->stream));
+	}
+	if (split_sum && col->chunks_slow.n == 0) {
+		return ADACOM_OK;
+	}
 	DecodeArgs a;
 	a.desc = col->d_desc;
-	a.jobs = col->chunks.d_jobs;
-	a.n_jobs = col->chunks.n;
+	a.jobs = split_sum ? col->chunks_slow.d_jobs : col->chunks.d_jobs;
+	a.n_jobs = split_sum ? col->chunks_slow.n : col->chunks.n;
 	a.tile_granularity = 0;
 	a.raw = col->raw;
 	a.literal = (flags & ADACOM_LITERAL) ? 1 : 0;

@@ -39,6 +39,17 @@ struct DecodeArgs {
 // TMA-staged unpack of packed tiles (+ fused SUM / filter).  grid = persistent CTAs.
 cudaError_t launch_decode(TypeInfo t, DecodeMode mode, const DecodeArgs &args, int sm_count, cudaStream_t stream);
 
+// width-specialised fused scan+SUM over re-packed segments whose decoded interval is sign/truncation linear
+struct ScanSumArgs {
+	const SegDesc *desc = nullptr;
+	const Job *jobs = nullptr;  // scan chunks (scan_chunk_values(w) values each) of re-packed segments only
+	uint32_t n_jobs = 0;
+	int type_size = 8;
+	int is_signed = 1;
+	Agg *agg = nullptr;
+};
+cudaError_t launch_scan_sum_fields(const ScanSumArgs &args, int sm_count, cudaStream_t stream);
+
 // scan_vector / scan_partial of one segment, arbitrary start (generic unaligned path, no staging)
 cudaError_t launch_scan_range(TypeInfo t, const SegDesc *desc, uint32_t seg, const uint8_t *raw, uint64_t start,
                               uint64_t scan_count, int literal, void *result, uint64_t result_offset,

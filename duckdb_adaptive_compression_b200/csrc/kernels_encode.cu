@@ -261,7 +261,9 @@ __global__ void reset_uncompacted_kernel(SegDesc *desc, uint32_t seg_begin, uint
 // encode
 // ---------------------------------------------------------------------------------------------------
 
-constexpr int kEncodeThreads = 256;
+constexpr int kEncodeConsumerWarps = 8;
+constexpr int kEncodeConsumers = kEncodeConsumerWarps * 32;
+constexpr int kEncodeThreads = kEncodeConsumers + 32;  // + one producer warp feeding the TMA ring
 constexpr int kEncodeStages = 3;
 template <int S> struct EncodeStage { static constexpr uint32_t kBytes = kVectorSize * S + 32; };
 
@@ -272,12 +274,20 @@ struct EncodeInfo {
 	uint32_t cnt;        // values in the tile (0: segment not repacked, nothing to do)
 	uint32_t w;
 	uint32_t gap;        // last tile of a segment: zero words up to the next 128-byte boundary
+	uint32_t magic;      // ceil(2^24 / w): n / w == (n * magic) >> 24 for n < 2^17, w <= 64
+	uint32_t pad;
+};
+
+struct EncodeResolved {
+	EncodeInfo info;
+	uint64_t src16;
+	uint32_t bytes;
 };
 
 template <int S>
-__device__ __forceinline__ void issue_encode_tile(const SegDesc *desc, const Job *tiles, uint32_t tile_idx,
-                                                  const uint8_t *raw, uint32_t extent, uint8_t *buf, EncodeInfo *info,
-                                                  uint64_t *bar) {
+__device__ __forceinline__ EncodeResolved resolve_encode_tile(const SegDesc *desc, const Job *tiles, uint32_t tile_idx,
+                                                              const uint8_t *raw, uint32_t extent) {
+	EncodeResolved r;
 	Job j = tiles[tile_idx];
 	const SegDesc *d = desc + j.seg;
 	uint32_t count = d->count;
@@ -286,25 +296,24 @@ __device__ __forceinline__ void issue_encode_tile(const SegDesc *desc, const Job
 	bool repacked = (d->state & kSegRepacked) && d->extent == extent && d->packed_ptr != 0;
 	uint32_t cnt = repacked ? min(kVectorSize, count - first) : 0u;
 	uint64_t src = (uint64_t)raw + (d->row_start + first) * (uint64_t)S;
-	uint64_t src16 = src & ~15ull;
-	uint32_t byte_base = (uint32_t)(src - src16);
-	uint32_t bytes = (byte_base + cnt * S + 15u) & ~15u;
+	r.src16 = src & ~15ull;
+	uint32_t byte_base = (uint32_t)(src - r.src16);
+	r.bytes = cnt ? ((byte_base + cnt * S + 15u) & ~15u) : 0u;
 	uint64_t mn = d->min_factor;
-	info->sub = mn == ~0ull ? 0ull : mn;
-	info->out = (uint64_t *)d->packed_ptr + (uint64_t)j.k * (kVectorSize / 64) * w;
-	info->byte_base = byte_base;
-	info->cnt = cnt;
-	info->w = w;
+	r.info.sub = mn == ~0ull ? 0ull : mn;
+	r.info.out = (uint64_t *)d->packed_ptr + (uint64_t)j.k * (kVectorSize / 64) * w;
+	r.info.byte_base = byte_base;
+	r.info.cnt = cnt;
+	r.info.w = w;
 	uint32_t gap = 0;
 	if (cnt && first + cnt == count) {
 		uint64_t total = ((uint64_t)count * w + 63) >> 6;
 		gap = (uint32_t)(((total + kSegAlignWords - 1) & ~(uint64_t)(kSegAlignWords - 1)) - total);
 	}
-	info->gap = gap;
-	mbar_arrive_expect_tx(bar, cnt ? bytes : 0u);
-	if (cnt) {
-		tma_load_1d(buf, (const void *)src16, bytes, bar);
-	}
+	r.info.gap = gap;
+	r.info.magic = ((1u << 24) + w - 1u) / w;
+	r.info.pad = 0;
+	return r;
 }
 
 template <int S>
@@ -314,39 +323,68 @@ __device__ __forceinline__ uint64_t load_slot(const uint8_t *base, uint32_t i) {
 	return (uint64_t)((const T *)base)[i];
 }
 
+__device__ __forceinline__ uint32_t div_magic(uint32_t n, uint32_t magic) {
+	return (uint32_t)(((uint64_t)n * magic) >> 24);
+}
+
 template <int S>
 __global__ void __launch_bounds__(kEncodeThreads) encode_kernel(const SegDesc *desc, const Job *tiles, uint32_t n_tiles,
                                                                 const uint8_t *raw, uint32_t extent) {
 	extern __shared__ __align__(128) uint8_t stage_mem[];
-	__shared__ __align__(8) uint64_t bars[kEncodeStages];
+	__shared__ __align__(8) uint64_t full_bar[kEncodeStages];
+	__shared__ __align__(8) uint64_t empty_bar[kEncodeStages];
 	__shared__ EncodeInfo infos[kEncodeStages];
 	constexpr uint32_t kStage = EncodeStage<S>::kBytes;
 	const uint32_t tid = threadIdx.x;
 	const uint32_t lane = tid & 31u;
+	const uint32_t warp = tid >> 5;
 
 	if (tid == 0) {
 		for (int s = 0; s < kEncodeStages; s++) {
-			mbar_init(&bars[s], 1);
+			mbar_init(&full_bar[s], 1);
+			mbar_init(&empty_bar[s], 1);
 		}
 		mbar_fence_init();
 	}
 	__syncthreads();
-	if (tid == 0) {
-		for (int s = 0; s < kEncodeStages; s++) {
-			uint32_t t = blockIdx.x + (uint32_t)s * gridDim.x;
-			if (t < n_tiles) {
-				issue_encode_tile<S>(desc, tiles, t, raw, extent, stage_mem + s * kStage, &infos[s], &bars[s]);
+
+	if (warp == kEncodeConsumerWarps) {
+		// ---------------- producer warp: lane s feeds stage s ----------------
+		for (uint32_t it0 = 0;; it0 += kEncodeStages) {
+			if (blockIdx.x + it0 * gridDim.x >= n_tiles) {
+				break;
+			}
+			const uint32_t my_it = it0 + lane;
+			const uint32_t t = blockIdx.x + my_it * gridDim.x;
+			const bool have = lane < kEncodeStages && t < n_tiles;
+			EncodeResolved r;
+			if (have) {
+				r = resolve_encode_tile<S>(desc, tiles, t, raw, extent);
+			}
+#pragma unroll
+			for (int s = 0; s < kEncodeStages; s++) {
+				if ((int)lane == s && have) {
+					mbar_wait(&empty_bar[s], ((my_it / kEncodeStages) & 1u) ^ 1u);
+					infos[s] = r.info;
+					mbar_arrive_expect_tx(&full_bar[s], r.bytes);
+					if (r.bytes) {
+						tma_load_1d(stage_mem + s * kStage, (const void *)r.src16, r.bytes, &full_bar[s]);
+					}
+				}
+				__syncwarp();
 			}
 		}
+		return;
 	}
 
+	// ---------------- consumer warps ----------------
 	for (uint32_t it = 0;; it++) {
 		uint32_t t = blockIdx.x + it * gridDim.x;
 		if (t >= n_tiles) {
 			break;
 		}
 		const uint32_t s = it % kEncodeStages;
-		mbar_wait(&bars[s], (it / kEncodeStages) & 1u);
+		mbar_wait(&full_bar[s], (it / kEncodeStages) & 1u);
 		const EncodeInfo in = infos[s];
 		const uint8_t *vals = stage_mem + s * kStage + in.byte_base;
 		const uint32_t w = in.w;
@@ -359,14 +397,14 @@ __global__ void __launch_bounds__(kEncodeThreads) encode_kernel(const SegDesc *d
 				const uint32_t mask = (uint32_t)lo_set64(w);
 				const uint32_t sub = (uint32_t)in.sub;
 				uint32_t *out32 = (uint32_t *)in.out;
-				for (uint32_t j = tid; j < n_units; j += kEncodeThreads) {
+				for (uint32_t j = tid; j < n_units; j += kEncodeConsumers) {
 					const uint32_t bit0 = j * 32u;
-					uint32_t i0 = bit0 / w;
-					uint32_t i1 = min(cnt - 1u, (bit0 + 31u) / w);
+					const uint32_t i0 = div_magic(bit0, in.magic);
+					const uint32_t i1 = min(cnt - 1u, div_magic(bit0 + 31u, in.magic));
 					uint32_t acc = 0;
 					if (i0 < cnt) {
 						const uint32_t c = i1 - i0 + 1u;
-						uint32_t r = lane % c;  // rotate the start so the lanes of a warp hit different banks
+						uint32_t r = (lane * c) >> 5;  // rotate the start so the lanes of a warp hit different banks
 						for (uint32_t n = 0; n < c; n++) {
 							const uint32_t i = i0 + r;
 							const uint32_t f = ((uint32_t)load_slot<S>(vals, i) - sub) & mask;
@@ -380,10 +418,10 @@ __global__ void __launch_bounds__(kEncodeThreads) encode_kernel(const SegDesc *d
 			} else {
 				const uint32_t n_words = (cnt * w + 63u) >> 6;
 				const uint64_t mask = lo_set64(w);
-				for (uint32_t j = tid; j < n_words; j += kEncodeThreads) {
+				for (uint32_t j = tid; j < n_words; j += kEncodeConsumers) {
 					const uint32_t bit0 = j * 64u;
-					uint32_t i0 = bit0 / w;
-					uint32_t i1 = min(cnt - 1u, (bit0 + 63u) / w);
+					const uint32_t i0 = div_magic(bit0, in.magic);
+					const uint32_t i1 = min(cnt - 1u, div_magic(bit0 + 63u, in.magic));
 					uint64_t acc = 0;
 					for (uint32_t i = i0; i <= i1; i++) {  // at most 3 values touch one word when w > 32
 						const uint64_t f = (load_slot<S>(vals, i) - in.sub) & mask;
@@ -397,13 +435,10 @@ __global__ void __launch_bounds__(kEncodeThreads) encode_kernel(const SegDesc *d
 				in.out[((cnt * w + 63u) >> 6) + tid] = 0ull;
 			}
 		}
-
-		__syncthreads();
+		// consumers in lockstep (named barrier 1), then one of them frees the stage for the producer
+		asm volatile("bar.sync 1, %0;" ::"n"(kEncodeConsumers) : "memory");
 		if (tid == 0) {
-			uint32_t next = t + (uint32_t)kEncodeStages * gridDim.x;
-			if (next < n_tiles) {
-				issue_encode_tile<S>(desc, tiles, next, raw, extent, stage_mem + s * kStage, &infos[s], &bars[s]);
-			}
+			mbar_arrive(&empty_bar[s]);
 		}
 	}
 }

@@ -1,0 +1,387 @@
+// kernels_scan.cu -- width-specialised fused scan+SUM over packed words (the "decode+scan" headline path).
+//
+// The reference decodes a vector with one scalar bits::read_int per value (succinct.cpp:123-144) and DuckDB's
+// SUM then walks the materialised vector.  On a B200 the per-value formulation is ISSUE-bound below ~20 bits
+// (at w bits per value the HBM roofline asks each SM for 184/w values per cycle, the generic extract + 96-bit
+// accumulate costs ~12 instructions per value).  This kernel never materialises values:
+//
+//   * sum(decoded) = sum(fields) + count * extend(min_factor) whenever the decoded interval
+//     [min, min + 2^w - 1] stays inside one sign/truncation zone of T (always true for data the reference can
+//     represent; the host checks it per segment and routes the rest to the generic decode_kernel);
+//   * the field stream has period P = w / gcd(w, 64) words holding V = 64 / gcd(w, 64) values; a lane owns
+//     whole periods, so every shift and mask is a compile-time constant (template on w, 63 instantiations):
+//     2 instructions per extraction for w <= 32, IADD3 folds two fields per add; w = 1, 2, 4, 8, 16 use
+//     popc / SWAR + dp4a / dp2a;
+//   * lanes take consecutive periods: the lane stride in shared memory is P words with P odd, which makes the
+//     64-bit shared loads conflict-free;
+//   * packed chunks (<= 16 KiB, 16-byte aligned by construction) are staged by the TMA engine
+//     (cp.async.bulk + mbarrier) into a 4-deep ring by one elected thread, as in decode_kernel.
+//
+// Algorithmic HBM bytes: P_chunk read per chunk; the output is one atomic triple per CTA.
+#include "adacom_kernels.cuh"
+
+namespace adacom {
+
+namespace {
+
+constexpr int kConsumerWarps = 8;
+constexpr int kConsumers = kConsumerWarps * 32;
+constexpr int kThreads = kConsumers + 32;  // + one producer warp feeding the TMA ring
+constexpr int kStages = 4;
+constexpr uint32_t kStageBytes = 16384 + 32;
+
+struct ChunkInfo {
+	uint64_t ext_min;  // extend_low<S,SIGNED>(min_factor) as a 64-bit pattern (0 when nothing is added)
+	uint32_t cnt;
+	uint32_t w;
+	uint32_t min_is_negative;  // ext_min is to be read as a negative int64 (signed T)
+	uint32_t pad;
+};
+
+__host__ __device__ constexpr int gcd64(int w) {
+	int g = 1;
+	while (g < 64 && (w % (g * 2)) == 0) {
+		g *= 2;
+	}
+	return g;
+}
+
+__device__ __forceinline__ uint32_t dp4a_ones(uint32_t x, uint32_t acc) {
+	uint32_t r;
+	asm("dp4a.u32.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(x), "r"(0x01010101u), "r"(acc));
+	return r;
+}
+
+__device__ __forceinline__ uint32_t dp2a_ones(uint32_t x, uint32_t acc) {
+	uint32_t r;
+	asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(x), "r"(0x00000101u), "r"(acc));
+	return r;
+}
+
+// Periods in a full chunk of width w.
+__host__ __device__ constexpr int periods_per_chunk(int w) {
+	return 2 * gcd64(w) * (1024 / w);
+}
+
+// A period is split into Q sub-periods (power of two) so that a full chunk offers at least one piece of work
+// per consumer thread; all lanes of a warp take the SAME sub-period index, so the code stays convergent and
+// every shift is still a compile-time constant.
+__host__ __device__ constexpr int subperiods(int w) {
+	int q = 1;
+	while (periods_per_chunk(w) * q < kConsumers && q < 64 / gcd64(w)) {
+		q *= 2;
+	}
+	return q;
+}
+
+// Sum of the fields [q*V/Q, (q+1)*V/Q) of the period that starts at word p.
+template <int W, int Q, int q>
+__device__ __forceinline__ void sum_subperiod(const uint64_t *p, Acc96 &acc) {
+	constexpr int G = gcd64(W);
+	constexpr int V = 64 / G;
+	constexpr int VQ = V / Q;
+	constexpr int J0 = q * VQ;
+	constexpr int K0 = (J0 * W) >> 6;                    // first 64-bit word touched
+	constexpr int K1 = ((J0 + VQ) * W - 1) >> 6;         // last 64-bit word touched
+	constexpr int NW = K1 - K0 + 1;
+	constexpr int BASE = K0 * 64;
+	uint32_t r[2 * NW + 2];
+#pragma unroll
+	for (int k = 0; k < NW; k++) {
+		uint64_t x = p[K0 + k];
+		r[2 * k] = (uint32_t)x;
+		r[2 * k + 1] = (uint32_t)(x >> 32);
+	}
+	r[2 * NW] = 0;
+	r[2 * NW + 1] = 0;
+	if (W == 1) {
+		acc.add<false>((uint64_t)(__popc(r[0]) + __popc(r[1])));
+	} else if (W == 2) {
+		uint32_t s = 0;
+#pragma unroll
+		for (int k = 0; k < 2; k++) {
+			uint32_t t = (r[k] & 0x33333333u) + ((r[k] >> 2) & 0x33333333u);
+			t = (t & 0x0F0F0F0Fu) + ((t >> 4) & 0x0F0F0F0Fu);
+			s = dp4a_ones(t, s);
+		}
+		acc.add<false>((uint64_t)s);
+	} else if (W == 4) {
+		uint32_t s = 0;
+#pragma unroll
+		for (int k = 0; k < 2; k++) {
+			uint32_t t = (r[k] & 0x0F0F0F0Fu) + ((r[k] >> 4) & 0x0F0F0F0Fu);
+			s = dp4a_ones(t, s);
+		}
+		acc.add<false>((uint64_t)s);
+	} else if (W == 8) {
+		acc.add<false>((uint64_t)dp4a_ones(r[1], dp4a_ones(r[0], 0u)));
+	} else if (W == 16) {
+		acc.add<false>((uint64_t)dp2a_ones(r[1], dp2a_ones(r[0], 0u)));
+	} else if (W <= 32) {
+		constexpr uint32_t mask = W == 32 ? 0xFFFFFFFFu : ((1u << (W & 31)) - 1u);
+		uint64_t s64 = 0;
+		uint32_t s32 = 0;  // VQ * (2^W - 1) < 2^32 when W <= 26
+#pragma unroll
+		for (int j = 0; j < VQ; j++) {
+			const int pos = (J0 + j) * W - BASE, i = pos >> 5, off = pos & 31;
+			uint32_t f;
+			if (off + W <= 32) {
+				f = (off + W == 32) ? (r[i] >> off) : ((r[i] >> off) & mask);
+			} else {
+				f = __funnelshift_r(r[i], r[i + 1], off) & mask;
+			}
+			if (W <= 26) {
+				s32 += f;
+			} else {
+				s64 += f;
+			}
+		}
+		acc.add<false>(W <= 26 ? (uint64_t)s32 : s64);
+	} else {
+		constexpr uint32_t mask_hi = (1u << ((W - 32) & 31)) - 1u;
+#pragma unroll
+		for (int j = 0; j < VQ; j++) {
+			const int pos = (J0 + j) * W - BASE, i = pos >> 5, off = pos & 31;
+			uint32_t lo, hi;
+			if (off == 0) {
+				lo = r[i];
+				hi = r[i + 1] & mask_hi;
+			} else {
+				lo = __funnelshift_r(r[i], r[i + 1], off);
+				hi = __funnelshift_r(r[i + 1], r[i + 2], off) & mask_hi;
+			}
+			acc.add<false>(((uint64_t)hi << 32) | lo);
+		}
+	}
+}
+
+template <int W, int Q, int q>
+struct SubSwitch {
+	static __device__ __forceinline__ void run(uint32_t sub, const uint64_t *p, Acc96 &acc) {
+		if (sub == (uint32_t)q) {
+			sum_subperiod<W, Q, q>(p, acc);
+		} else {
+			SubSwitch<W, Q, q + 1>::run(sub, p, acc);
+		}
+	}
+};
+template <int W, int Q>
+struct SubSwitch<W, Q, Q> {
+	static __device__ __forceinline__ void run(uint32_t, const uint64_t *, Acc96 &) {
+	}
+};
+
+template <int W>
+__device__ __forceinline__ void sum_chunk_fields(const uint64_t *words, uint32_t cnt, uint32_t tid, Acc96 &acc) {
+	constexpr int G = gcd64(W);
+	constexpr int P = W / G;
+	constexpr int V = 64 / G;
+	constexpr int Q = subperiods(W);
+	const uint32_t n_units = cnt / V;
+	const uint32_t n_rows = ((n_units + 31u) >> 5) * Q;  // a row = 32 periods x one sub-period index
+	const uint32_t lane = tid & 31u;
+	for (uint32_t row = tid >> 5; row < n_rows; row += kConsumerWarps) {
+		const uint32_t sub = row % Q;               // warp-uniform
+		const uint32_t u = (row / Q) * 32u + lane;
+		if (u < n_units) {
+			SubSwitch<W, Q, 0>::run(sub, words + (size_t)u * P, acc);
+		}
+	}
+	// values behind the last whole period (only the last chunk of a segment has any)
+	const uint32_t done = n_units * V;
+	const uint32_t i = done + tid;
+	if (i < cnt) {
+		const uint32_t bit = i * W;
+		uint64_t f = W <= 32 ? (uint64_t)(read_bits32((const uint32_t *)words, bit) & (uint32_t)lo_set64(W))
+		                     : (read_bits64(words, bit) & lo_set64(W));
+		acc.add<false>(f);
+	}
+}
+
+// A full chunk of width w holds 2 * gcd(w,64) * floor(1024/w) periods.  The period-per-lane path needs at
+// least one period per consumer thread to keep all warps busy; the other widths (odd w >= 9, ...) have a
+// large per-value instruction budget (0.7 * w) and use the fully parallel lane-per-value extraction.
+__host__ __device__ constexpr bool period_path(int w) {
+	return w >= 1 && w <= 63;  // measured: the unrolled period path beats lane-per-value at every width
+}
+
+// lane-per-value: adjacent lanes read adjacent fields (conflict-free), runtime shifts
+__device__ __forceinline__ void sum_chunk_generic(const uint64_t *words, uint32_t w, uint32_t cnt, uint32_t tid,
+                                                  Acc96 &acc) {
+	if (w <= 32u) {
+		const uint32_t *words32 = (const uint32_t *)words;
+		const uint32_t mask = (uint32_t)lo_set64(w);
+		uint64_t s = 0;
+#pragma unroll 4
+		for (uint32_t i = tid; i < cnt; i += kConsumers) {
+			s += read_bits32(words32, i * w) & mask;
+		}
+		acc.add<false>(s);
+	} else {
+		const uint64_t mask = lo_set64(w);
+#pragma unroll 4
+		for (uint32_t i = tid; i < cnt; i += kConsumers) {
+			acc.add<false>(read_bits64(words, i * w) & mask);
+		}
+	}
+}
+
+template <int W0>
+struct WidthSwitch {
+	static __device__ __forceinline__ void run(uint32_t w, const uint64_t *words, uint32_t cnt, uint32_t tid, Acc96 &acc) {
+		if (period_path(W0) && w == W0) {
+			sum_chunk_fields<W0>(words, cnt, tid, acc);
+		} else {
+			WidthSwitch<W0 + 1>::run(w, words, cnt, tid, acc);
+		}
+	}
+};
+template <>
+struct WidthSwitch<64> {
+	static __device__ __forceinline__ void run(uint32_t w, const uint64_t *words, uint32_t cnt, uint32_t tid, Acc96 &acc) {
+		sum_chunk_generic(words, w, cnt, tid, acc);
+	}
+};
+
+struct ResolvedChunk {
+	ChunkInfo info;
+	uint64_t src;
+	uint32_t bytes;
+};
+
+__device__ __forceinline__ ResolvedChunk resolve_chunk(const ScanSumArgs &a, uint32_t job_idx) {
+	ResolvedChunk r;
+	Job j = a.jobs[job_idx];
+	const SegDesc *dp = a.desc + j.seg;
+	const uint32_t w = dp->width;
+	const uint32_t count = dp->count;
+	const uint64_t mn = dp->min_factor;
+	const uint32_t gran = scan_chunk_values(w);
+	const uint32_t first = j.k * gran;
+	const uint32_t cnt = min(gran, count - first);
+	r.src = dp->packed_ptr + (((uint64_t)first * w) >> 3);  // 16-byte aligned by construction
+	r.bytes = (((cnt * w + 7u) >> 3) + 15u) & ~15u;
+	uint64_t ext = 0;
+	uint32_t neg = 0;
+	if (mn != ~0ull) {  // this kernel only sees re-packed segments: min is always added (succinct.cpp:138-140)
+		const uint32_t shift = 64u - 8u * (uint32_t)a.type_size;
+		if (a.is_signed) {
+			ext = (uint64_t)(((int64_t)(mn << shift)) >> shift);
+			neg = (int64_t)ext < 0;
+		} else {
+			ext = (mn << shift) >> shift;
+		}
+	}
+	r.info.ext_min = ext;
+	r.info.cnt = cnt;
+	r.info.w = w;
+	r.info.min_is_negative = neg;
+	r.info.pad = 0;
+	return r;
+}
+
+__global__ void __launch_bounds__(kThreads, 3) scan_sum_fields_kernel(const ScanSumArgs a) {
+	extern __shared__ __align__(128) uint8_t stage_mem[];
+	__shared__ __align__(8) uint64_t full_bar[kStages];
+	__shared__ __align__(8) uint64_t empty_bar[kStages];
+	__shared__ ChunkInfo infos[kStages];
+	__shared__ uint64_t red[96];
+	const uint32_t tid = threadIdx.x;
+	const uint32_t lane = tid & 31u;
+	const uint32_t warp = tid >> 5;
+
+	if (tid == 0) {
+		for (int s = 0; s < kStages; s++) {
+			mbar_init(&full_bar[s], 1);
+			mbar_init(&empty_bar[s], kConsumerWarps);
+		}
+		mbar_fence_init();
+	}
+	__syncthreads();
+
+	Acc96 acc;              // sum of the fields (unsigned)
+	uint64_t corr_lo = 0;   // thread 0: sum over chunks of cnt * ext_min (128-bit two's complement)
+	uint64_t corr_hi = 0;
+	uint64_t n_values = 0;
+
+	if (warp == kConsumerWarps) {
+		for (uint32_t it0 = 0;; it0 += kStages) {
+			if (blockIdx.x + it0 * gridDim.x >= a.n_jobs) {
+				break;
+			}
+			const uint32_t my_it = it0 + lane;
+			const uint32_t job = blockIdx.x + my_it * gridDim.x;
+			const bool have = lane < kStages && job < a.n_jobs;
+			ResolvedChunk r;
+			if (have) {
+				r = resolve_chunk(a, job);
+			}
+#pragma unroll
+			for (int s = 0; s < kStages; s++) {
+				if ((int)lane == s && have) {
+					mbar_wait(&empty_bar[s], ((my_it / kStages) & 1u) ^ 1u);
+					infos[s] = r.info;
+					mbar_arrive_expect_tx(&full_bar[s], r.bytes);
+					tma_load_1d(stage_mem + s * kStageBytes, (const void *)r.src, r.bytes, &full_bar[s]);
+				}
+				__syncwarp();
+			}
+		}
+	} else {
+		for (uint32_t it = 0;; it++) {
+			uint32_t job = blockIdx.x + it * gridDim.x;
+			if (job >= a.n_jobs) {
+				break;
+			}
+			const uint32_t s = it % kStages;
+			mbar_wait(&full_bar[s], (it / kStages) & 1u);
+			const ChunkInfo in = infos[s];
+			const uint64_t *words = (const uint64_t *)(stage_mem + s * kStageBytes);
+			WidthSwitch<1>::run(in.w, words, in.cnt, tid, acc);
+			if (tid == 0) {
+				const uint64_t c = in.cnt;
+				uint64_t lo = in.ext_min * c;
+				uint64_t hi = __umul64hi(in.ext_min, c);
+				if (in.min_is_negative) {
+					hi -= c;  // signed x unsigned high part
+				}
+				add128(corr_lo, corr_hi, lo, hi);
+				n_values += c;
+			}
+			__syncwarp();
+			if (lane == 0) {
+				mbar_arrive(&empty_bar[s]);
+			}
+		}
+	}
+	uint64_t lo = acc.lo64(), hi = (uint64_t)acc.a2;
+	add128(lo, hi, corr_lo, corr_hi);
+	block_reduce_agg(lo, hi, n_values, red, a.agg);
+}
+
+}  // namespace
+
+cudaError_t launch_scan_sum_fields(const ScanSumArgs &args, int sm_count, cudaStream_t stream) {
+	static bool configured[64] = {};
+	const size_t smem = (size_t)kStages * kStageBytes;
+	int dev = 0;
+	cudaGetDevice(&dev);
+	if (!configured[dev & 63]) {
+		cudaError_t e = cudaFuncSetAttribute(scan_sum_fields_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		if (e != cudaSuccess) {
+			return e;
+		}
+		configured[dev & 63] = true;
+	}
+	if (args.n_jobs == 0) {
+		return cudaSuccess;
+	}
+	uint32_t grid = (uint32_t)sm_count * 3u;
+	if (grid > args.n_jobs) {
+		grid = args.n_jobs;
+	}
+	scan_sum_fields_kernel<<<grid, kThreads, smem, stream>>>(args);
+	return cudaGetLastError();
+}
+
+}  // namespace adacom

@@ -43,7 +43,9 @@ def main():
         t_en = min(ts)
         P = col.packed_words * 8
         t_de = timeit(lambda: col.decode(device_out=out.data_ptr()))
-        t_su = timeit(lambda: col.scan_sum())
+        agg = torch.zeros(4, dtype=torch.int64, device='cuda')
+        col.scan_sum()
+        t_su = timeit(lambda: col.scan_sum_async(agg.data_ptr()))
         GB = 1e-9
         raw = n * S
         print(json.dumps(dict(b=b, w=m.width, raw_GB=raw*GB, P_GB=P*GB,
