@@ -67,7 +67,10 @@ struct adacom_column {
 	bool mirror_dirty = false;
 	std::vector<Extent> extents;
 	std::vector<Extent> spares;  // dead extents kept for the next encode (no allocator call on the hot path)
-	JobTable tiles, chunks, chunks_fast, chunks_slow;
+	JobTable tiles;
+	Job *d_chunks = nullptr;          // device-built chunk table of the whole column (<= one chunk per 2048-value tile)
+	uint32_t *d_chunk_first = nullptr;  // n_segs + 1
+	uint64_t chunk_epoch = ~0ull;
 	uint64_t epoch = 0;
 };
 
@@ -210,68 +213,24 @@ adacom_status get_tiles(adacom_column *col, uint64_t b, uint64_t e) {
 	return st;
 }
 
-uint64_t extend_low_host(uint64_t x, int type_size, bool is_signed) {
-	if (type_size == 8) {
-		return x;
-	}
-	const unsigned shift = 64u - 8u * (unsigned)type_size;
-	return is_signed ? (uint64_t)(((int64_t)(x << shift)) >> shift) : ((x << shift) >> shift);
-}
-
-// sum(decoded) == sum(fields) + count * extend(min) holds when [min, min + 2^w - 1] does not wrap 2^64 and
-// stays inside one sign / truncation zone of T (true for every segment the reference can represent)
-bool linear_zone(const SegDesc &d, int type_size, bool is_signed) {
-	if (!(d.state & kSegRepacked) || d.width >= 64) {
-		return false;
-	}
-	const uint64_t lo = d.min_factor == ~0ull ? 0 : d.min_factor;
-	const uint64_t range = (1ull << d.width) - 1;
-	const uint64_t hi = lo + range;
-	if (hi < lo) {
-		return false;
-	}
-	const uint64_t e_lo = extend_low_host(lo, type_size, is_signed), e_hi = extend_low_host(hi, type_size, is_signed);
-	if (e_hi - e_lo != range) {
-		return false;
-	}
-	return is_signed ? (int64_t)e_lo <= (int64_t)e_hi : e_lo <= e_hi;
-}
-
-// <=16 KiB scan chunks of [b, e): depends on the current widths -> needs the mirror.  Three tables: every
-// chunk (filter / generic), and the SUM split into the width-specialised fast path and the generic rest.
-adacom_status get_chunks(adacom_column *col, uint64_t b, uint64_t e) {
-	JobTable &tab = col->chunks;
-	if (tab.begin == b && tab.end == e && tab.epoch == col->epoch) {
+// (re)build the column's chunk table on the device when the widths changed; fully asynchronous
+adacom_status ensure_chunks(adacom_column *col) {
+	adacom_ctx *ctx = col->ctx;
+	if (col->chunk_epoch == col->epoch) {
 		return ADACOM_OK;
 	}
-	adacom_status st = sync_mirror(col);
-	if (st != ADACOM_OK) {
-		return st;
-	}
-	std::vector<Job> jobs, fast, slow;
-	for (uint64_t g = b; g < e; g++) {
-		const SegDesc &d = col->h_desc[g];
-		uint32_t gran = scan_chunk_values(d.width);
-		uint32_t n = (d.count + gran - 1) / gran;
-		std::vector<Job> &split = linear_zone(d, col->t.size, col->t.is_signed) ? fast : slow;
-		for (uint32_t k = 0; k < n; k++) {
-			jobs.push_back({(uint32_t)g, k});
-			split.push_back({(uint32_t)g, k});
+	if (!col->d_chunks) {
+		uint64_t tiles = 0;
+		for (const SegDesc &d : col->h_desc) {
+			tiles += (d.count + kVectorSize - 1) / kVectorSize;
 		}
+		CK(ctx, cudaMalloc((void **)&col->d_chunks, (tiles + 1) * sizeof(Job)));
+		CK(ctx, cudaMalloc((void **)&col->d_chunk_first, (col->n_segs + 1) * sizeof(uint32_t)));
 	}
-	st = upload_jobs(col, tab, jobs);
-	if (st == ADACOM_OK) {
-		st = upload_jobs(col, col->chunks_fast, fast);
-	}
-	if (st == ADACOM_OK) {
-		st = upload_jobs(col, col->chunks_slow, slow);
-	}
-	if (st == ADACOM_OK) {
-		tab.begin = b;
-		tab.end = e;
-		tab.epoch = col->epoch;
-	}
-	return st;
+	LAUNCH(ctx, launch_build_chunks(col->d_desc, (uint32_t)col->n_segs, col->t.size, col->t.is_signed ? 1 : 0,
+	                                col->d_chunks, col->d_chunk_first, ctx->stream));
+	col->chunk_epoch = col->epoch;
+	return ADACOM_OK;
 }
 
 bool range_ok(const adacom_column *col, uint64_t b, uint64_t e) {
@@ -561,14 +520,12 @@ extern "C" void adacom_column_destroy(adacom_column *col) {
 	if (col->tiles.d_jobs) {
 		cudaFreeAsync(col->tiles.d_jobs, ctx->stream);
 	}
-	for (JobTable *t : {&col->chunks, &col->chunks_fast, &col->chunks_slow}) {
-		if (t->d_jobs) {
-			cudaFreeAsync(t->d_jobs, ctx->stream);
-		}
-	}
+
 	cudaStreamSynchronize(ctx->stream);
 	cudaFree(col->raw);
 	cudaFree(col->d_desc);
+	cudaFree(col->d_chunks);
+	cudaFree(col->d_chunk_first);
 	delete col;
 }
 
@@ -1028,29 +985,35 @@ extern "C" adacom_status adacom_uncompact(adacom_column *col, uint64_t seg_begin
 static adacom_status run_agg(adacom_column *col, uint64_t b, uint64_t e, int flags, DecodeMode mode, uint32_t op_mask,
                              uint64_t constant, uint32_t *bitmap32, Agg *device_out) {
 	adacom_ctx *ctx = col->ctx;
-	adacom_status st = get_chunks(col, b, e);
+	adacom_status st = ensure_chunks(col);
 	if (st != ADACOM_OK) {
 		return st;
 	}
 	CK(ctx, cudaMemsetAsync(device_out, 0, sizeof(Agg), ctx->stream));
-	const bool split_sum = mode == kModeSum;
-	if (split_sum && col->chunks_fast.n) {
+	if (b == e) {
+		return ADACOM_OK;
+	}
+	if (mode == kModeSum) {
 		ScanSumArgs f;
 		f.desc = col->d_desc;
-		f.jobs = col->chunks_fast.d_jobs;
-		f.n_jobs = col->chunks_fast.n;
+		f.jobs = col->d_chunks;
+		f.chunk_first = col->d_chunk_first;
+		f.seg_b = (uint32_t)b;
+		f.seg_e = (uint32_t)e;
+		f.raw = col->raw;
+		f.literal = (flags & ADACOM_LITERAL) ? 1 : 0;
 		f.type_size = col->t.size;
 		f.is_signed = col->t.is_signed ? 1 : 0;
 		f.agg = device_out;
 		LAUNCH(ctx, launch_scan_sum_fields(f, ctx->sm_count, ctx->stream));
-	}
-	if (split_sum && col->chunks_slow.n == 0) {
 		return ADACOM_OK;
 	}
 	DecodeArgs a;
 	a.desc = col->d_desc;
-	a.jobs = split_sum ? col->chunks_slow.d_jobs : col->chunks.d_jobs;
-	a.n_jobs = split_sum ? col->chunks_slow.n : col->chunks.n;
+	a.jobs = col->d_chunks;
+	a.chunk_first = col->d_chunk_first;
+	a.seg_b = (uint32_t)b;
+	a.seg_e = (uint32_t)e;
 	a.tile_granularity = 0;
 	a.raw = col->raw;
 	a.literal = (flags & ADACOM_LITERAL) ? 1 : 0;
@@ -1058,7 +1021,7 @@ static adacom_status run_agg(adacom_column *col, uint64_t b, uint64_t e, int fla
 	a.op_mask = op_mask;
 	a.constant = constant;
 	a.bitmap32 = bitmap32;
-	a.out_row0 = b < e ? col->h_desc[b].row_start : 0;
+	a.out_row0 = col->h_desc[b].row_start;
 	LAUNCH(ctx, launch_decode(col->t, mode, a, ctx->sm_count, ctx->stream));
 	return ADACOM_OK;
 }

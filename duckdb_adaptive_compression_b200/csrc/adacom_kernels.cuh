@@ -17,6 +17,10 @@ struct DecodeArgs {
 	const SegDesc *desc = nullptr;
 	const Job *jobs = nullptr;       // (segment, k) work units
 	uint32_t n_jobs = 0;
+	// device-built chunk table: when chunk_first != nullptr the kernel takes the jobs
+	// [chunk_first[seg_b], chunk_first[seg_e]) of `jobs` (n_jobs is ignored)
+	const uint32_t *chunk_first = nullptr;
+	uint32_t seg_b = 0, seg_e = 0;
 	uint32_t tile_granularity = 0;   // kVectorSize -> 2048-value tiles; 0 -> scan chunks (scan_chunk_values(w))
 	const uint8_t *raw = nullptr;    // raw arena (source for segments that are not repacked)
 	int literal = 0;                 // ADACOM_LITERAL: add min even when the segment was not repacked (Q1)
@@ -42,12 +46,21 @@ cudaError_t launch_decode(TypeInfo t, DecodeMode mode, const DecodeArgs &args, i
 // width-specialised fused scan+SUM over re-packed segments whose decoded interval is sign/truncation linear
 struct ScanSumArgs {
 	const SegDesc *desc = nullptr;
-	const Job *jobs = nullptr;  // scan chunks (scan_chunk_values(w) values each) of re-packed segments only
-	uint32_t n_jobs = 0;
+	const Job *jobs = nullptr;            // the column's device-built chunk table (Job.k bit 31 = fast path)
+	const uint32_t *chunk_first = nullptr;  // first chunk of every segment (+ total at [n_segs])
+	uint32_t seg_b = 0, seg_e = 0;        // segment range to scan
+	const uint8_t *raw = nullptr;         // raw arena (source of segments that are not re-packed)
+	int literal = 0;
 	int type_size = 8;
 	int is_signed = 1;
 	Agg *agg = nullptr;
 };
+
+constexpr uint32_t kJobFastBit = 0x80000000u;
+
+// chunk table of the whole column, built on the device from the current descriptors (no host round trip)
+cudaError_t launch_build_chunks(const SegDesc *desc, uint32_t n_segs, int type_size, int is_signed, Job *jobs_out,
+                                uint32_t *chunk_first, cudaStream_t stream);
 cudaError_t launch_scan_sum_fields(const ScanSumArgs &args, int sm_count, cudaStream_t stream);
 
 // scan_vector / scan_partial of one segment, arbitrary start (generic unaligned path, no staging)

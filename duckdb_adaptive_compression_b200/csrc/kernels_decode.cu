@@ -52,6 +52,7 @@ template <int S>
 __device__ __forceinline__ Resolved resolve_unit(const DecodeArgs &a, uint32_t job_idx) {
 	Resolved r;
 	Job j = a.jobs[job_idx];
+	j.k &= ~kJobFastBit;
 	const SegDesc *dp = a.desc + j.seg;
 	uint64_t row_start = dp->row_start;
 	uint64_t packed_ptr = dp->packed_ptr;
@@ -89,7 +90,7 @@ __device__ __forceinline__ Resolved resolve_unit(const DecodeArgs &a, uint32_t j
 }
 
 template <int S, bool SIGNED, int MODE>
-__global__ void __launch_bounds__(kThreads) decode_kernel(const DecodeArgs a) {
+__global__ void __launch_bounds__(kThreads) decode_kernel(DecodeArgs a) {
 	extern __shared__ __align__(128) uint8_t stage_mem[];
 	__shared__ __align__(8) uint64_t full_bar[kStages];
 	__shared__ __align__(8) uint64_t empty_bar[kStages];
@@ -100,6 +101,11 @@ __global__ void __launch_bounds__(kThreads) decode_kernel(const DecodeArgs a) {
 	const uint32_t tid = threadIdx.x;
 	const uint32_t lane = tid & 31u;
 	const uint32_t warp = tid >> 5;
+	if (a.chunk_first != nullptr) {  // job range read from the device-built chunk table
+		const uint32_t j0 = a.chunk_first[a.seg_b];
+		a.n_jobs = a.chunk_first[a.seg_e] - j0;
+		a.jobs += j0;
+	}
 
 	if (tid == 0) {
 		for (int s = 0; s < kStages; s++) {
@@ -236,11 +242,11 @@ cudaError_t launch_one(const DecodeArgs &args, int sm_count, cudaStream_t stream
 		}
 		configured[dev & 63] = true;
 	}
-	if (args.n_jobs == 0) {
+	if (args.n_jobs == 0 && args.chunk_first == nullptr) {
 		return cudaSuccess;
 	}
 	uint32_t grid = (uint32_t)sm_count * 3u;  // 3 CTAs x 64.1 KiB of stages per SM
-	if (grid > args.n_jobs) {
+	if (args.chunk_first == nullptr && grid > args.n_jobs) {
 		grid = args.n_jobs;
 	}
 	kernel<<<grid, kThreads, smem, stream>>>(args);

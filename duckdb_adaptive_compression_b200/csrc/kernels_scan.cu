@@ -31,10 +31,12 @@ constexpr int kStages = 4;
 constexpr uint32_t kStageBytes = 16384 + 32;
 
 struct ChunkInfo {
-	uint64_t ext_min;  // extend_low<S,SIGNED>(min_factor) as a 64-bit pattern (0 when nothing is added)
+	uint64_t ext_min;  // fast: extend_low<S,SIGNED>(min_factor) as a 64-bit pattern; slow: the value to add (or 0)
 	uint32_t cnt;
 	uint32_t w;
-	uint32_t min_is_negative;  // ext_min is to be read as a negative int64 (signed T)
+	uint32_t min_is_negative;  // fast: ext_min is to be read as a negative int64 (signed T)
+	uint32_t bit_base;         // slow: bit position of the first field inside the staged bytes (0..127)
+	uint32_t fast;
 	uint32_t pad;
 };
 
@@ -245,37 +247,50 @@ struct WidthSwitch<64> {
 
 struct ResolvedChunk {
 	ChunkInfo info;
-	uint64_t src;
+	uint64_t src16;
 	uint32_t bytes;
 };
 
-__device__ __forceinline__ ResolvedChunk resolve_chunk(const ScanSumArgs &a, uint32_t job_idx) {
+__device__ __forceinline__ uint64_t extend_runtime(uint64_t x, int type_size, int is_signed) {
+	const uint32_t shift = 64u - 8u * (uint32_t)type_size;
+	return is_signed ? (uint64_t)(((int64_t)(x << shift)) >> shift) : ((x << shift) >> shift);
+}
+
+__device__ __forceinline__ ResolvedChunk resolve_chunk(const ScanSumArgs &a, const Job *jobs, uint32_t job_idx) {
 	ResolvedChunk r;
-	Job j = a.jobs[job_idx];
+	Job j = jobs[job_idx];
+	const uint32_t fast = j.k & kJobFastBit;
+	j.k &= ~kJobFastBit;
 	const SegDesc *dp = a.desc + j.seg;
 	const uint32_t w = dp->width;
 	const uint32_t count = dp->count;
 	const uint64_t mn = dp->min_factor;
+	const bool repacked = dp->state & kSegRepacked;
 	const uint32_t gran = scan_chunk_values(w);
 	const uint32_t first = j.k * gran;
 	const uint32_t cnt = min(gran, count - first);
-	r.src = dp->packed_ptr + (((uint64_t)first * w) >> 3);  // 16-byte aligned by construction
-	r.bytes = (((cnt * w + 7u) >> 3) + 15u) & ~15u;
+	const uint64_t src = repacked ? dp->packed_ptr + (((uint64_t)first * w) >> 3)
+	                              : (uint64_t)a.raw + (dp->row_start + first) * (uint64_t)a.type_size;
+	r.src16 = src & ~15ull;
+	const uint32_t byte_base = (uint32_t)(src - r.src16);
+	r.bytes = (byte_base + ((cnt * w + 7u) >> 3) + 15u) & ~15u;
+	const bool add = (mn != ~0ull) && (repacked || a.literal);  // succinct.cpp:138-140 (+ Q1 in literal mode)
 	uint64_t ext = 0;
 	uint32_t neg = 0;
-	if (mn != ~0ull) {  // this kernel only sees re-packed segments: min is always added (succinct.cpp:138-140)
-		const uint32_t shift = 64u - 8u * (uint32_t)a.type_size;
-		if (a.is_signed) {
-			ext = (uint64_t)(((int64_t)(mn << shift)) >> shift);
-			neg = (int64_t)ext < 0;
-		} else {
-			ext = (mn << shift) >> shift;
+	if (fast) {
+		if (add) {
+			ext = extend_runtime(mn, a.type_size, a.is_signed);
+			neg = a.is_signed && (int64_t)ext < 0;
 		}
+	} else {
+		ext = add ? mn : 0ull;
 	}
 	r.info.ext_min = ext;
 	r.info.cnt = cnt;
 	r.info.w = w;
 	r.info.min_is_negative = neg;
+	r.info.bit_base = byte_base * 8u;
+	r.info.fast = fast;
 	r.info.pad = 0;
 	return r;
 }
@@ -289,6 +304,9 @@ __global__ void __launch_bounds__(kThreads, 3) scan_sum_fields_kernel(const Scan
 	const uint32_t tid = threadIdx.x;
 	const uint32_t lane = tid & 31u;
 	const uint32_t warp = tid >> 5;
+	const uint32_t j0 = a.chunk_first[a.seg_b];
+	const uint32_t n_jobs = a.chunk_first[a.seg_e] - j0;
+	const Job *jobs = a.jobs + j0;
 
 	if (tid == 0) {
 		for (int s = 0; s < kStages; s++) {
@@ -299,22 +317,23 @@ __global__ void __launch_bounds__(kThreads, 3) scan_sum_fields_kernel(const Scan
 	}
 	__syncthreads();
 
-	Acc96 acc;              // sum of the fields (unsigned)
-	uint64_t corr_lo = 0;   // thread 0: sum over chunks of cnt * ext_min (128-bit two's complement)
+	Acc96 acc;              // sum of the fields (unsigned) / of unsigned slow-path values
+	Acc96 sacc;             // slow path, signed T: sign-extended values
+	uint64_t corr_lo = 0;   // thread 0: sum over fast chunks of cnt * ext_min (128-bit two's complement)
 	uint64_t corr_hi = 0;
 	uint64_t n_values = 0;
 
 	if (warp == kConsumerWarps) {
 		for (uint32_t it0 = 0;; it0 += kStages) {
-			if (blockIdx.x + it0 * gridDim.x >= a.n_jobs) {
+			if (blockIdx.x + it0 * gridDim.x >= n_jobs) {
 				break;
 			}
 			const uint32_t my_it = it0 + lane;
 			const uint32_t job = blockIdx.x + my_it * gridDim.x;
-			const bool have = lane < kStages && job < a.n_jobs;
+			const bool have = lane < kStages && job < n_jobs;
 			ResolvedChunk r;
 			if (have) {
-				r = resolve_chunk(a, job);
+				r = resolve_chunk(a, jobs, job);
 			}
 #pragma unroll
 			for (int s = 0; s < kStages; s++) {
@@ -322,7 +341,7 @@ __global__ void __launch_bounds__(kThreads, 3) scan_sum_fields_kernel(const Scan
 					mbar_wait(&empty_bar[s], ((my_it / kStages) & 1u) ^ 1u);
 					infos[s] = r.info;
 					mbar_arrive_expect_tx(&full_bar[s], r.bytes);
-					tma_load_1d(stage_mem + s * kStageBytes, (const void *)r.src, r.bytes, &full_bar[s]);
+					tma_load_1d(stage_mem + s * kStageBytes, (const void *)r.src16, r.bytes, &full_bar[s]);
 				}
 				__syncwarp();
 			}
@@ -330,23 +349,43 @@ __global__ void __launch_bounds__(kThreads, 3) scan_sum_fields_kernel(const Scan
 	} else {
 		for (uint32_t it = 0;; it++) {
 			uint32_t job = blockIdx.x + it * gridDim.x;
-			if (job >= a.n_jobs) {
+			if (job >= n_jobs) {
 				break;
 			}
 			const uint32_t s = it % kStages;
 			mbar_wait(&full_bar[s], (it / kStages) & 1u);
 			const ChunkInfo in = infos[s];
 			const uint64_t *words = (const uint64_t *)(stage_mem + s * kStageBytes);
-			WidthSwitch<1>::run(in.w, words, in.cnt, tid, acc);
-			if (tid == 0) {
-				const uint64_t c = in.cnt;
-				uint64_t lo = in.ext_min * c;
-				uint64_t hi = __umul64hi(in.ext_min, c);
-				if (in.min_is_negative) {
-					hi -= c;  // signed x unsigned high part
+			if (in.fast) {
+				WidthSwitch<1>::run(in.w, words, in.cnt, tid, acc);
+				if (tid == 0) {
+					const uint64_t c = in.cnt;
+					uint64_t lo = in.ext_min * c;
+					uint64_t hi = __umul64hi(in.ext_min, c);
+					if (in.min_is_negative) {
+						hi -= c;  // signed x unsigned high part
+					}
+					add128(corr_lo, corr_hi, lo, hi);
 				}
-				add128(corr_lo, corr_hi, lo, hi);
-				n_values += c;
+			} else {
+				// generic path: raw (not re-packed) segments, or a decoded interval that crosses a sign /
+				// truncation boundary of T -- one value per lane per step, extended like DuckDB sees it
+				const uint32_t w = in.w;
+				const uint64_t mask = lo_set64(w);
+				for (uint32_t i = tid; i < in.cnt; i += kConsumers) {
+					const uint32_t bit = in.bit_base + i * w;
+					uint64_t f = w <= 32u ? (uint64_t)(read_bits32((const uint32_t *)words, bit) & (uint32_t)mask)
+					                      : (read_bits64(words, bit) & mask);
+					uint64_t v = extend_runtime(f + in.ext_min, a.type_size, a.is_signed);
+					if (a.is_signed) {
+						sacc.add<true>(v);
+					} else {
+						acc.add<false>(v);
+					}
+				}
+			}
+			if (tid == 0) {
+				n_values += in.cnt;
 			}
 			__syncwarp();
 			if (lane == 0) {
@@ -355,11 +394,98 @@ __global__ void __launch_bounds__(kThreads, 3) scan_sum_fields_kernel(const Scan
 		}
 	}
 	uint64_t lo = acc.lo64(), hi = (uint64_t)acc.a2;
+	add128(lo, hi, sacc.lo64(), sacc.hi64());
 	add128(lo, hi, corr_lo, corr_hi);
 	block_reduce_agg(lo, hi, n_values, red, a.agg);
 }
 
+// ---------------------------------------------------------------------------------------------------
+// chunk table builder (single CTA): per segment ceil(count / scan_chunk_values(width)) chunks, exclusive
+// scan -> chunk_first[], then the (segment, k | fast) pairs.  Runs after every encode / uncompact epoch.
+// ---------------------------------------------------------------------------------------------------
+
+constexpr int kBuildThreads = 1024;
+
+__device__ __forceinline__ bool linear_zone_dev(const SegDesc &d, int type_size, int is_signed) {
+	if (!(d.state & kSegRepacked) || d.width >= 64) {
+		return false;
+	}
+	const uint64_t lo = d.min_factor == ~0ull ? 0 : d.min_factor;
+	const uint64_t range = (1ull << d.width) - 1;
+	const uint64_t hi = lo + range;
+	if (hi < lo) {
+		return false;
+	}
+	const uint64_t e_lo = extend_runtime(lo, type_size, is_signed), e_hi = extend_runtime(hi, type_size, is_signed);
+	if (e_hi - e_lo != range) {
+		return false;
+	}
+	return is_signed ? (int64_t)e_lo <= (int64_t)e_hi : e_lo <= e_hi;
+}
+
+__global__ void __launch_bounds__(kBuildThreads) build_chunks_kernel(const SegDesc *desc, uint32_t n_segs, int type_size,
+                                                                    int is_signed, Job *jobs_out,
+                                                                    uint32_t *chunk_first) {
+	__shared__ uint32_t warp_tot[kBuildThreads / 32];
+	const uint32_t tid = threadIdx.x;
+	const uint32_t lane = tid & 31u, warp = tid >> 5;
+	const uint32_t per = (n_segs + kBuildThreads - 1) / kBuildThreads;
+	const uint32_t lo = min(n_segs, tid * per), hi = min(n_segs, lo + per);
+	uint32_t mine = 0;
+	for (uint32_t g = lo; g < hi; g++) {
+		const uint32_t gran = scan_chunk_values(desc[g].width);
+		mine += (desc[g].count + gran - 1) / gran;
+	}
+	// block-wide exclusive scan: warp shuffle scan + scan of the 32 warp totals
+	uint32_t incl = mine;
+#pragma unroll
+	for (int d = 1; d < 32; d <<= 1) {
+		uint32_t v = __shfl_up_sync(0xffffffffu, incl, d);
+		if ((int)lane >= d) {
+			incl += v;
+		}
+	}
+	if (lane == 31) {
+		warp_tot[warp] = incl;
+	}
+	__syncthreads();
+	if (warp == 0) {
+		uint32_t t = warp_tot[lane];
+		uint32_t ti = t;
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) {
+			uint32_t v = __shfl_up_sync(0xffffffffu, ti, d);
+			if ((int)lane >= d) {
+				ti += v;
+			}
+		}
+		warp_tot[lane] = ti - t;  // exclusive
+		if (lane == 31) {
+			chunk_first[n_segs] = ti;
+		}
+	}
+	__syncthreads();
+	uint32_t next = warp_tot[warp] + incl - mine;
+	for (uint32_t g = lo; g < hi; g++) {
+		const SegDesc d = desc[g];
+		const uint32_t gran = scan_chunk_values(d.width);
+		const uint32_t n = (d.count + gran - 1) / gran;
+		const uint32_t fast = linear_zone_dev(d, type_size, is_signed) ? kJobFastBit : 0u;
+		chunk_first[g] = next;
+		for (uint32_t k = 0; k < n; k++) {
+			jobs_out[next + k] = Job {g, k | fast};
+		}
+		next += n;
+	}
+}
+
 }  // namespace
+
+cudaError_t launch_build_chunks(const SegDesc *desc, uint32_t n_segs, int type_size, int is_signed, Job *jobs_out,
+                                uint32_t *chunk_first, cudaStream_t stream) {
+	build_chunks_kernel<<<1, kBuildThreads, 0, stream>>>(desc, n_segs, type_size, is_signed, jobs_out, chunk_first);
+	return cudaGetLastError();
+}
 
 cudaError_t launch_scan_sum_fields(const ScanSumArgs &args, int sm_count, cudaStream_t stream) {
 	static bool configured[64] = {};
@@ -373,13 +499,10 @@ cudaError_t launch_scan_sum_fields(const ScanSumArgs &args, int sm_count, cudaSt
 		}
 		configured[dev & 63] = true;
 	}
-	if (args.n_jobs == 0) {
+	if (args.seg_b >= args.seg_e) {
 		return cudaSuccess;
 	}
-	uint32_t grid = (uint32_t)sm_count * 3u;
-	if (grid > args.n_jobs) {
-		grid = args.n_jobs;
-	}
+	const uint32_t grid = (uint32_t)sm_count * 3u;  // persistent; CTAs beyond the chunk count exit at once
 	scan_sum_fields_kernel<<<grid, kThreads, smem, stream>>>(args);
 	return cudaGetLastError();
 }
