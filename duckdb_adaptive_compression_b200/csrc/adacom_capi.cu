@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
+#include <atomic>
 #include <mutex>
 #include <new>
 #include <string>
@@ -34,7 +35,8 @@ struct adacom_ctx {
 	void *flush_buf = nullptr;
 	size_t flush_bytes = 0;
 	Agg *d_agg = nullptr;
-	unsigned long long *d_totals = nullptr;
+	unsigned long long *d_totals = nullptr;  // device alias of h_totals (host-mapped)
+	unsigned long long ticket = 0;           // sequence number of the last layout launch
 	Agg *h_agg = nullptr;                 // pinned
 	unsigned long long *h_totals = nullptr;  // pinned
 };
@@ -45,14 +47,6 @@ struct Extent {
 	uint64_t capacity = 0;   // allocated words
 	uint64_t live = 0;       // repacked segments still pointing into this extent (valid after gc_extents)
 	uint64_t seg_begin = 0, seg_end = 0;  // the encode call that created it covered [seg_begin, seg_end)
-};
-
-struct JobTable {
-	uint64_t begin = 0, end = 0;
-	uint64_t epoch = ~0ull;
-	Job *d_jobs = nullptr;
-	uint32_t n = 0;
-	size_t capacity = 0;
 };
 
 struct adacom_column {
@@ -67,10 +61,10 @@ struct adacom_column {
 	bool mirror_dirty = false;
 	std::vector<Extent> extents;
 	std::vector<Extent> spares;  // dead extents kept for the next encode (no allocator call on the hot path)
-	JobTable tiles;
-	Job *d_chunks = nullptr;          // device-built chunk table of the whole column (<= one chunk per 2048-value tile)
-	uint32_t *d_chunk_first = nullptr;  // n_segs + 1
-	uint64_t chunk_epoch = ~0ull;
+	// 2048-value tiles of every segment, (segment, k) pairs in segment order: depends on the segment counts only,
+	// so it is built once; the tiles of the segments [b, e) are d_tiles[tile_first[b] .. tile_first[e])
+	Job *d_tiles = nullptr;
+	std::vector<uint32_t> tile_first;
 	uint64_t epoch = 0;
 };
 
@@ -173,63 +167,23 @@ adacom_status sync_mirror(adacom_column *col) {
 	return ADACOM_OK;
 }
 
-adacom_status upload_jobs(adacom_column *col, JobTable &tab, const std::vector<Job> &jobs) {
+adacom_status build_tiles(adacom_column *col) {
 	adacom_ctx *ctx = col->ctx;
-	if (jobs.size() > tab.capacity) {
-		if (tab.d_jobs) {
-			CK(ctx, cudaFreeAsync(tab.d_jobs, ctx->stream));
-			tab.d_jobs = nullptr;
-		}
-		tab.capacity = jobs.size() + jobs.size() / 8 + 64;
-		CK(ctx, cudaMallocAsync((void **)&tab.d_jobs, tab.capacity * sizeof(Job), ctx->stream));
-	}
-	if (!jobs.empty()) {
-		// pageable source: the copy is staged before the call returns, so `jobs` may go out of scope
-		CK(ctx, cudaMemcpyAsync(tab.d_jobs, jobs.data(), jobs.size() * sizeof(Job), cudaMemcpyHostToDevice, ctx->stream));
-	}
-	tab.n = (uint32_t)jobs.size();
-	return ADACOM_OK;
-}
-
-// 2048-value tiles of [b, e): depends on the segment counts only
-adacom_status get_tiles(adacom_column *col, uint64_t b, uint64_t e) {
-	JobTable &tab = col->tiles;
-	if (tab.begin == b && tab.end == e && tab.epoch == 0) {
-		return ADACOM_OK;
-	}
 	std::vector<Job> jobs;
-	for (uint64_t g = b; g < e; g++) {
-		uint32_t n = (col->h_desc[g].count + kVectorSize - 1) / kVectorSize;
+	col->tile_first.assign(col->n_segs + 1, 0);
+	for (uint64_t g = 0; g < col->n_segs; g++) {
+		col->tile_first[g] = (uint32_t)jobs.size();
+		const uint32_t n = (col->h_desc[g].count + kVectorSize - 1) / kVectorSize;
 		for (uint32_t k = 0; k < n; k++) {
 			jobs.push_back({(uint32_t)g, k});
 		}
 	}
-	adacom_status st = upload_jobs(col, tab, jobs);
-	if (st == ADACOM_OK) {
-		tab.begin = b;
-		tab.end = e;
-		tab.epoch = 0;
+	col->tile_first[col->n_segs] = (uint32_t)jobs.size();
+	CK(ctx, cudaMalloc((void **)&col->d_tiles, (jobs.size() + 1) * sizeof(Job)));
+	if (!jobs.empty()) {
+		// pageable source: staged before the call returns
+		CK(ctx, cudaMemcpyAsync(col->d_tiles, jobs.data(), jobs.size() * sizeof(Job), cudaMemcpyHostToDevice, ctx->stream));
 	}
-	return st;
-}
-
-// (re)build the column's chunk table on the device when the widths changed; fully asynchronous
-adacom_status ensure_chunks(adacom_column *col) {
-	adacom_ctx *ctx = col->ctx;
-	if (col->chunk_epoch == col->epoch) {
-		return ADACOM_OK;
-	}
-	if (!col->d_chunks) {
-		uint64_t tiles = 0;
-		for (const SegDesc &d : col->h_desc) {
-			tiles += (d.count + kVectorSize - 1) / kVectorSize;
-		}
-		CK(ctx, cudaMalloc((void **)&col->d_chunks, (tiles + 1) * sizeof(Job)));
-		CK(ctx, cudaMalloc((void **)&col->d_chunk_first, (col->n_segs + 1) * sizeof(uint32_t)));
-	}
-	LAUNCH(ctx, launch_build_chunks(col->d_desc, (uint32_t)col->n_segs, col->t.size, col->t.is_signed ? 1 : 0,
-	                                col->d_chunks, col->d_chunk_first, ctx->stream));
-	col->chunk_epoch = col->epoch;
 	return ADACOM_OK;
 }
 
@@ -314,9 +268,12 @@ extern "C" adacom_status adacom_ctx_create(int device, adacom_ctx **out) {
 	ctx->sm_count = prop.multiProcessorCount;
 	CK(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
 	CK(nullptr, cudaMalloc((void **)&ctx->d_agg, sizeof(Agg)));
-	CK(nullptr, cudaMalloc((void **)&ctx->d_totals, 4 * sizeof(unsigned long long)));
 	CK(nullptr, cudaHostAlloc((void **)&ctx->h_agg, sizeof(Agg), cudaHostAllocDefault));
-	CK(nullptr, cudaHostAlloc((void **)&ctx->h_totals, 4 * sizeof(unsigned long long), cudaHostAllocDefault));
+	// {payload words, ticket} written by layout_kernel straight into host memory; the encode path spins on the
+	// ticket (a few microseconds) instead of a copy + stream synchronisation
+	CK(nullptr, cudaHostAlloc((void **)&ctx->h_totals, 4 * sizeof(unsigned long long), cudaHostAllocMapped));
+	memset(ctx->h_totals, 0, 4 * sizeof(unsigned long long));
+	CK(nullptr, cudaHostGetDevicePointer((void **)&ctx->d_totals, ctx->h_totals, 0));
 	// keep freed extents cached in the stream-ordered pool instead of returning them to the driver
 	cudaMemPool_t pool;
 	if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
@@ -335,7 +292,6 @@ extern "C" void adacom_ctx_destroy(adacom_ctx *ctx) {
 	cudaStreamSynchronize(ctx->stream);
 	cudaFree(ctx->flush_buf);
 	cudaFree(ctx->d_agg);
-	cudaFree(ctx->d_totals);
 	cudaFreeHost(ctx->h_agg);
 	cudaFreeHost(ctx->h_totals);
 	cudaStreamDestroy(ctx->stream);
@@ -463,6 +419,10 @@ extern "C" adacom_status adacom_column_create(adacom_ctx *ctx, adacom_ptype type
 		return st;
 	}
 	const uint32_t cap = seg_capacity ? seg_capacity : kBlockSize / (uint32_t)col->t.size;
+	if ((uint64_t)cap * col->t.size > kBlockSize) {
+		delete col;
+		return fail(ctx, ADACOM_ERR_INVALID, "segment capacity exceeds one block (Storage::BLOCK_SIZE)");
+	}
 	uint64_t row = 0;
 	for (uint64_t g = 0; g < n_segments; g++) {
 		if (seg_counts[g] > cap) {
@@ -495,6 +455,13 @@ extern "C" adacom_status adacom_column_create(adacom_ctx *ctx, adacom_ptype type
 		return fail(ctx, e == cudaErrorMemoryAllocation ? ADACOM_ERR_NOMEM : ADACOM_ERR_CUDA,
 		            std::string("adacom_column_create: ") + cudaGetErrorString(e));
 	}
+	st = build_tiles(col);
+	if (st != ADACOM_OK) {
+		cudaFree(col->raw);
+		cudaFree(col->d_desc);
+		delete col;
+		return st;
+	}
 	*out = col;
 	return ADACOM_OK;
 }
@@ -517,15 +484,11 @@ extern "C" void adacom_column_destroy(adacom_column *col) {
 			cudaFreeAsync(x.base, ctx->stream);
 		}
 	}
-	if (col->tiles.d_jobs) {
-		cudaFreeAsync(col->tiles.d_jobs, ctx->stream);
-	}
 
 	cudaStreamSynchronize(ctx->stream);
 	cudaFree(col->raw);
 	cudaFree(col->d_desc);
-	cudaFree(col->d_chunks);
-	cudaFree(col->d_chunk_first);
+	cudaFree(col->d_tiles);
 	delete col;
 }
 
@@ -630,6 +593,12 @@ extern "C" adacom_status adacom_column_from_packed(adacom_ctx *ctx, adacom_ptype
 			delete col;
 			return fail(ctx, ADACOM_ERR_INVALID, "adacom_column_from_packed: bad word_offset");
 		}
+		if (m.count * (uint64_t)col->t.size > kBlockSize || (uint64_t)m.capacity * col->t.size > kBlockSize) {
+			cudaFreeAsync(ext.base, ctx->stream);
+			cudaFree(col->d_desc);
+			delete col;
+			return fail(ctx, ADACOM_ERR_INVALID, "adacom_column_from_packed: segment exceeds one block");
+		}
 		d.row_start = row;
 		d.word_offset = m.word_offset;
 		d.packed_ptr = repacked ? (uint64_t)(ext.base + m.word_offset) : 0;
@@ -651,6 +620,10 @@ extern "C" adacom_status adacom_column_from_packed(adacom_ctx *ctx, adacom_ptype
 	if (n_segments) {
 		CK(ctx, cudaMemcpyAsync(col->d_desc, col->h_desc.data(), n_segments * sizeof(SegDesc), cudaMemcpyHostToDevice,
 		                        ctx->stream));
+	}
+	st = build_tiles(col);
+	if (st != ADACOM_OK) {
+		return st;
 	}
 	*out = col;
 	return ADACOM_OK;
@@ -721,9 +694,26 @@ extern "C" adacom_status adacom_encode(adacom_column *col, uint64_t seg_begin, u
 	}
 	const uint32_t extent_id = (uint32_t)col->extents.size();
 	// 1. widths, repack decisions and payload offsets, all on the device
-	LAUNCH(ctx, launch_layout(col->t, col->d_desc, (uint32_t)seg_begin, n, flags, extent_id, ctx->d_totals, ctx->stream));
-	CK(ctx, cudaMemcpyAsync(ctx->h_totals, ctx->d_totals, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
-	CK(ctx, cudaStreamSynchronize(ctx->stream));  // the only host round trip: 8 bytes, sizes the new extent
+	const unsigned long long ticket = ++ctx->ticket;
+	LAUNCH(ctx, launch_layout(col->t, col->d_desc, (uint32_t)seg_begin, n, flags, extent_id, ctx->d_totals, ticket,
+	                          ctx->stream));
+	// the only host round trip of an encode: 8 bytes that size the new extent, polled from mapped memory
+	{
+		volatile unsigned long long *t = ctx->h_totals;
+		uint32_t spins = 0;
+		while (t[1] != ticket) {
+			if ((++spins & 0x3ffu) == 0) {
+				cudaError_t q = cudaStreamQuery(ctx->stream);
+				if (q != cudaSuccess && q != cudaErrorNotReady) {
+					CK(ctx, q);
+				}
+				if (q == cudaSuccess && t[1] != ticket) {
+					return fail(ctx, ADACOM_ERR_CUDA, "adacom_encode: layout kernel finished without publishing its total");
+				}
+			}
+		}
+		std::atomic_thread_fence(std::memory_order_acquire);
+	}
 	Extent ext;
 	ext.words = ctx->h_totals[0];
 	ext.seg_begin = seg_begin;
@@ -747,12 +737,9 @@ extern "C" adacom_status adacom_encode(adacom_column *col, uint64_t seg_begin, u
 			CK(ctx, cudaMallocAsync((void **)&ext.base, ext.capacity * 8 + kArenaPad, ctx->stream));
 		}
 		LAUNCH(ctx, launch_bind_extent(col->d_desc, (uint32_t)seg_begin, n, ext.base, extent_id, ctx->stream));
-		adacom_status st = get_tiles(col, seg_begin, seg_end);
-		if (st != ADACOM_OK) {
-			return st;
-		}
 		// 3. pack
-		LAUNCH(ctx, launch_encode(col->t, col->d_desc, col->tiles.d_jobs, col->tiles.n, col->raw, extent_id, ctx->sm_count,
+		LAUNCH(ctx, launch_encode(col->t, col->d_desc, col->d_tiles + col->tile_first[seg_begin],
+		                          col->tile_first[seg_end] - col->tile_first[seg_begin], col->raw, extent_id, ctx->sm_count,
 		                          ctx->stream));
 	}
 	col->extents.push_back(ext);
@@ -878,19 +865,14 @@ extern "C" adacom_status adacom_decode(adacom_column *col, uint64_t seg_begin, u
 	if (rows == 0) {
 		return ADACOM_OK;
 	}
-	adacom_status st = get_tiles(col, seg_begin, seg_end);
-	if (st != ADACOM_OK) {
-		return st;
-	}
 	void *d_out = out;
 	if (!out_on_device) {
 		CK(ctx, cudaMallocAsync(&d_out, rows * col->t.size, ctx->stream));
 	}
 	DecodeArgs a;
 	a.desc = col->d_desc;
-	a.jobs = col->tiles.d_jobs;
-	a.n_jobs = col->tiles.n;
-	a.tile_granularity = kVectorSize;
+	a.jobs = col->d_tiles + col->tile_first[seg_begin];
+	a.n_jobs = col->tile_first[seg_end] - col->tile_first[seg_begin];
 	a.raw = col->raw;
 	a.literal = (flags & ADACOM_LITERAL) ? 1 : 0;
 	a.out = d_out;
@@ -947,18 +929,13 @@ extern "C" adacom_status adacom_uncompact(adacom_column *col, uint64_t seg_begin
 	if (st != ADACOM_OK) {
 		return st;
 	}
-	st = get_tiles(col, seg_begin, seg_end);
-	if (st != ADACOM_OK) {
-		return st;
-	}
 	// fully asynchronous: decode the compacted segments of the range back into the raw arena (the kernel
 	// skips the others), then flip their descriptors on the device.  Dead extents are reclaimed the next time
 	// the host mirror is refreshed.
 	DecodeArgs a;
 	a.desc = col->d_desc;
-	a.jobs = col->tiles.d_jobs;
-	a.n_jobs = col->tiles.n;
-	a.tile_granularity = kVectorSize;
+	a.jobs = col->d_tiles + col->tile_first[seg_begin];
+	a.n_jobs = col->tile_first[seg_end] - col->tile_first[seg_begin];
 	a.raw = col->raw;
 	a.literal = (flags & ADACOM_LITERAL) ? 1 : 0;
 	a.uncompact = 1;
@@ -985,10 +962,6 @@ extern "C" adacom_status adacom_uncompact(adacom_column *col, uint64_t seg_begin
 static adacom_status run_agg(adacom_column *col, uint64_t b, uint64_t e, int flags, DecodeMode mode, uint32_t op_mask,
                              uint64_t constant, uint32_t *bitmap32, Agg *device_out) {
 	adacom_ctx *ctx = col->ctx;
-	adacom_status st = ensure_chunks(col);
-	if (st != ADACOM_OK) {
-		return st;
-	}
 	CK(ctx, cudaMemsetAsync(device_out, 0, sizeof(Agg), ctx->stream));
 	if (b == e) {
 		return ADACOM_OK;
@@ -996,8 +969,6 @@ static adacom_status run_agg(adacom_column *col, uint64_t b, uint64_t e, int fla
 	if (mode == kModeSum) {
 		ScanSumArgs f;
 		f.desc = col->d_desc;
-		f.jobs = col->d_chunks;
-		f.chunk_first = col->d_chunk_first;
 		f.seg_b = (uint32_t)b;
 		f.seg_e = (uint32_t)e;
 		f.raw = col->raw;
@@ -1010,11 +981,8 @@ static adacom_status run_agg(adacom_column *col, uint64_t b, uint64_t e, int fla
 	}
 	DecodeArgs a;
 	a.desc = col->d_desc;
-	a.jobs = col->d_chunks;
-	a.chunk_first = col->d_chunk_first;
 	a.seg_b = (uint32_t)b;
-	a.seg_e = (uint32_t)e;
-	a.tile_granularity = 0;
+	a.n_units = (uint32_t)(e - b);
 	a.raw = col->raw;
 	a.literal = (flags & ADACOM_LITERAL) ? 1 : 0;
 	a.agg = device_out;
@@ -1085,63 +1053,39 @@ extern "C" adacom_status adacom_point_filter_batch(adacom_column *col, uint64_t 
 	if (n_queries == 0) {
 		return ADACOM_OK;
 	}
-	adacom_status st = sync_mirror(col);
-	if (st != ADACOM_OK) {
-		return st;
-	}
-	std::vector<Job> jobs;
-	std::vector<uint32_t> job_query;
 	for (uint64_t q = 0; q < n_queries; q++) {
 		if (seg_idx[q] >= col->n_segs) {
 			return fail(ctx, ADACOM_ERR_INVALID, "adacom_point_filter_batch: segment index out of range");
 		}
-		const SegDesc &d = col->h_desc[seg_idx[q]];
-		uint32_t gran = scan_chunk_values(d.width);
-		uint32_t n = (d.count + gran - 1) / gran;
-		for (uint32_t k = 0; k < n; k++) {
-			jobs.push_back({seg_idx[q], k});
-			job_query.push_back((uint32_t)q);
-		}
 	}
-	JobTable tmp;
-	st = upload_jobs(col, tmp, jobs);
-	if (st != ADACOM_OK) {
-		return st;
-	}
-	uint32_t *d_job_query = nullptr;
+	// one unit per query; the kernel walks the chunks of seg_idx[q] from the descriptors (no host-built table)
+	uint32_t *d_unit_seg = nullptr;
 	int64_t *d_const = nullptr;
 	unsigned long long *d_count = nullptr, *d_first = nullptr;
-	CK(ctx, cudaMallocAsync((void **)&d_job_query, std::max<size_t>(job_query.size(), 1) * 4, ctx->stream));
+	CK(ctx, cudaMallocAsync((void **)&d_unit_seg, n_queries * 4, ctx->stream));
 	CK(ctx, cudaMallocAsync((void **)&d_const, n_queries * 8, ctx->stream));
 	CK(ctx, cudaMallocAsync((void **)&d_count, n_queries * 8, ctx->stream));
 	CK(ctx, cudaMallocAsync((void **)&d_first, n_queries * 8, ctx->stream));
-	if (!job_query.empty()) {
-		CK(ctx, cudaMemcpyAsync(d_job_query, job_query.data(), job_query.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
-	}
+	CK(ctx, cudaMemcpyAsync(d_unit_seg, seg_idx, n_queries * 4, cudaMemcpyHostToDevice, ctx->stream));
 	CK(ctx, cudaMemcpyAsync(d_const, constants, n_queries * 8, cudaMemcpyHostToDevice, ctx->stream));
 	CK(ctx, cudaMemsetAsync(d_count, 0, n_queries * 8, ctx->stream));
 	CK(ctx, cudaMemsetAsync(d_first, 0xff, n_queries * 8, ctx->stream));
 	DecodeArgs a;
 	a.desc = col->d_desc;
-	a.jobs = tmp.d_jobs;
-	a.n_jobs = tmp.n;
-	a.tile_granularity = 0;
+	a.n_units = (uint32_t)n_queries;
+	a.unit_seg = d_unit_seg;
 	a.raw = col->raw;
 	a.literal = (flags & ADACOM_LITERAL) ? 1 : 0;
-	a.job_query = d_job_query;
 	a.q_const = d_const;
 	a.q_count = d_count;
 	a.q_first = d_first;
 	LAUNCH(ctx, launch_decode(col->t, kModePoint, a, ctx->sm_count, ctx->stream));
 	CK(ctx, cudaMemcpyAsync(out_count, d_count, n_queries * 8, cudaMemcpyDeviceToHost, ctx->stream));
 	CK(ctx, cudaMemcpyAsync(out_first_row, d_first, n_queries * 8, cudaMemcpyDeviceToHost, ctx->stream));
-	CK(ctx, cudaFreeAsync(d_job_query, ctx->stream));
+	CK(ctx, cudaFreeAsync(d_unit_seg, ctx->stream));
 	CK(ctx, cudaFreeAsync(d_const, ctx->stream));
 	CK(ctx, cudaFreeAsync(d_count, ctx->stream));
 	CK(ctx, cudaFreeAsync(d_first, ctx->stream));
-	if (tmp.d_jobs) {
-		CK(ctx, cudaFreeAsync(tmp.d_jobs, ctx->stream));
-	}
 	CK(ctx, cudaStreamSynchronize(ctx->stream));
 	return ADACOM_OK;
 }

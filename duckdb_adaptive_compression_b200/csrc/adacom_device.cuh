@@ -5,6 +5,7 @@
 // [i*w, (i+1)*w) of the concatenated bit string, LSB first, and may straddle two words.
 #pragma once
 
+#include <cstddef>
 #include <cstdint>
 #include <cuda_runtime.h>
 
@@ -33,6 +34,41 @@ struct __align__(16) SegDesc {
 	uint8_t pad[6];
 };
 static_assert(sizeof(SegDesc) == 64, "SegDesc must stay 64 bytes");
+// the kernels read descriptors as four 16-byte quarters
+static_assert(offsetof(SegDesc, packed_ptr) == 8 && offsetof(SegDesc, min_factor) == 24 &&
+                  offsetof(SegDesc, max_factor) == 32 && offsetof(SegDesc, count) == 40 &&
+                  offsetof(SegDesc, extent) == 48 && offsetof(SegDesc, width) == 56 && offsetof(SegDesc, state) == 57,
+              "SegDesc field offsets are baked into the quarter loads");
+
+// A descriptor as the kernels read it: four independent 16-byte loads (one memory round trip), decoded later
+// so that a producer can fetch the descriptors of its NEXT batch of jobs while it issues the current one.
+struct DescQ {
+	uint4 q0;  // row_start, packed_ptr
+	uint4 q1;  // word_offset, min_factor
+	uint4 q2;  // max_factor, count, capacity
+	uint4 q3;  // extent, reserved, width | state << 8 | pad, pad
+#ifdef __CUDACC__
+	__device__ __forceinline__ uint64_t row_start() const { return ((uint64_t)q0.y << 32) | q0.x; }
+	__device__ __forceinline__ uint64_t packed_ptr() const { return ((uint64_t)q0.w << 32) | q0.z; }
+	__device__ __forceinline__ uint64_t min_factor() const { return ((uint64_t)q1.w << 32) | q1.z; }
+	__device__ __forceinline__ uint32_t count() const { return q2.z; }
+	__device__ __forceinline__ uint32_t extent() const { return q3.x; }
+	__device__ __forceinline__ uint32_t width() const { return q3.z & 0xffu; }
+	__device__ __forceinline__ uint32_t state() const { return (q3.z >> 8) & 0xffu; }
+#endif
+};
+
+#ifdef __CUDACC__
+__device__ __forceinline__ DescQ load_desc(const SegDesc *d) {
+	DescQ q;
+	const uint4 *p = (const uint4 *)d;
+	q.q0 = __ldg(p);
+	q.q1 = __ldg(p + 1);
+	q.q2 = __ldg(p + 2);
+	q.q3 = __ldg(p + 3);
+	return q;
+}
+#endif
 
 // A unit of work for the tile kernels: (segment, index of the tile/chunk inside the segment).
 struct Job {
@@ -45,6 +81,9 @@ struct Job {
 __host__ __device__ inline uint32_t scan_chunk_values(uint32_t w) {
 	return 128u * (1024u / w);
 }
+// A segment holds <= 262136 payload bytes, a chunk >= 15.4 KiB: never more than 16 chunks per segment
+// (checked for every (S, w) in tests/test_capi_boundary.py).
+constexpr uint32_t kScanParts = 16;
 
 __host__ __device__ inline uint64_t lo_set64(uint32_t len) {
 	return len >= 64 ? ~0ull : ((1ull << len) - 1ull);

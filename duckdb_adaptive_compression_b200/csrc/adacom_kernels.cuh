@@ -15,13 +15,15 @@ struct TypeInfo {
 
 struct DecodeArgs {
 	const SegDesc *desc = nullptr;
-	const Job *jobs = nullptr;       // (segment, k) work units
+	// kModeFlat: (segment, tile) pairs of 2048 values from the column's static tile table
+	const Job *jobs = nullptr;
 	uint32_t n_jobs = 0;
-	// device-built chunk table: when chunk_first != nullptr the kernel takes the jobs
-	// [chunk_first[seg_b], chunk_first[seg_e]) of `jobs` (n_jobs is ignored)
-	const uint32_t *chunk_first = nullptr;
-	uint32_t seg_b = 0, seg_e = 0;
-	uint32_t tile_granularity = 0;   // kVectorSize -> 2048-value tiles; 0 -> scan chunks (scan_chunk_values(w))
+	// fused scans: n_units segments, seg_b + unit (unit_seg == nullptr) or unit_seg[unit]; the kernel enumerates
+	// the <= kScanParts chunks of <= 16 KiB of every segment from its descriptor (their number depends on the
+	// current width, so there is no table)
+	uint32_t n_units = 0;
+	uint32_t seg_b = 0;
+	const uint32_t *unit_seg = nullptr;
 	const uint8_t *raw = nullptr;    // raw arena (source for segments that are not repacked)
 	int literal = 0;                 // ADACOM_LITERAL: add min even when the segment was not repacked (Q1)
 	int uncompact = 0;               // UncompressSuccinct mode: skip segments that are not compacted
@@ -33,8 +35,7 @@ struct DecodeArgs {
 	uint32_t op_mask = 0;
 	uint64_t constant = 0;
 	uint32_t *bitmap32 = nullptr;    // optional, bit (row - out_row0)
-	// kModePoint
-	const uint32_t *job_query = nullptr;
+	// kModePoint: unit == query
 	const int64_t *q_const = nullptr;
 	unsigned long long *q_count = nullptr;
 	unsigned long long *q_first = nullptr;
@@ -46,9 +47,7 @@ cudaError_t launch_decode(TypeInfo t, DecodeMode mode, const DecodeArgs &args, i
 // width-specialised fused scan+SUM over re-packed segments whose decoded interval is sign/truncation linear
 struct ScanSumArgs {
 	const SegDesc *desc = nullptr;
-	const Job *jobs = nullptr;            // the column's device-built chunk table (Job.k bit 31 = fast path)
-	const uint32_t *chunk_first = nullptr;  // first chunk of every segment (+ total at [n_segs])
-	uint32_t seg_b = 0, seg_e = 0;        // segment range to scan
+	uint32_t seg_b = 0, seg_e = 0;        // segment range to scan (chunks are derived from the descriptors)
 	const uint8_t *raw = nullptr;         // raw arena (source of segments that are not re-packed)
 	int literal = 0;
 	int type_size = 8;
@@ -56,11 +55,6 @@ struct ScanSumArgs {
 	Agg *agg = nullptr;
 };
 
-constexpr uint32_t kJobFastBit = 0x80000000u;
-
-// chunk table of the whole column, built on the device from the current descriptors (no host round trip)
-cudaError_t launch_build_chunks(const SegDesc *desc, uint32_t n_segs, int type_size, int is_signed, Job *jobs_out,
-                                uint32_t *chunk_first, cudaStream_t stream);
 cudaError_t launch_scan_sum_fields(const ScanSumArgs &args, int sm_count, cudaStream_t stream);
 
 // scan_vector / scan_partial of one segment, arbitrary start (generic unaligned path, no staging)
@@ -76,9 +70,10 @@ cudaError_t launch_fetch_rows(TypeInfo t, const SegDesc *desc, const uint8_t *ra
 cudaError_t launch_analyze(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, uint8_t *raw,
                            const uint64_t *validity, int zero_ext, cudaStream_t stream);
 
-// layout: widths, repack decision, 128-byte aligned word offsets (exclusive scan), totals[0] = words
+// layout: widths, repack decision, 128-byte aligned word offsets (exclusive scan); totals (host-mapped) =
+// {words, ticket}
 cudaError_t launch_layout(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int flags, uint32_t extent,
-                          unsigned long long *totals, cudaStream_t stream);
+                          unsigned long long *totals, unsigned long long ticket, cudaStream_t stream);
 
 // bind packed_ptr = base + word_offset for the repacked segments of the range
 cudaError_t launch_bind_extent(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, uint64_t *base, uint32_t extent,
@@ -88,7 +83,8 @@ cudaError_t launch_bind_extent(SegDesc *desc, uint32_t seg_begin, uint32_t n_seg
 cudaError_t launch_reset_uncompacted(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int type_size,
                                      cudaStream_t stream);
 
-// encode: TMA-staged raw tiles -> FOR subtract + bit-pack into the packed extent
+// encode: FOR subtract + width-specialised bit-pack of the tiles whose segment the preceding layout bound to
+// `extent`
 cudaError_t launch_encode(TypeInfo t, const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw,
                           uint32_t extent, int sm_count, cudaStream_t stream);
 

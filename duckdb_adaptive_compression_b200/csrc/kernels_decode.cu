@@ -37,7 +37,9 @@ struct StageInfo {
 	uint32_t w;
 	uint32_t seg;
 	uint32_t first_value;  // index of the unit's first value inside its segment
-	uint32_t job;
+	uint32_t unit;         // fused scans: index of the scanned segment inside the call (== query for kModePoint)
+	uint32_t done;         // sentinel: the producer has no more work for this CTA
+	uint32_t pad;
 };
 
 struct Resolved {
@@ -46,24 +48,24 @@ struct Resolved {
 	uint32_t bytes;
 };
 
-// job -> segment descriptor -> what to stage (two dependent global loads; the producer warp resolves
-// kStages units in parallel, one per lane, so this latency is paid once per ring revolution)
+// (segment, k) -> segment descriptor -> what to stage.  `gran` = values per work unit: 2048-value tiles for the
+// flat decode, scan_chunk_values(w) (gran == 0) for the fused scans.  bytes == 0: nothing to stage.
 template <int S>
-__device__ __forceinline__ Resolved resolve_unit(const DecodeArgs &a, uint32_t job_idx) {
+__device__ __forceinline__ Resolved resolve_unit(const DecodeArgs &a, uint32_t seg, uint32_t k, uint32_t gran,
+                                                 const DescQ &dq) {
 	Resolved r;
-	Job j = a.jobs[job_idx];
-	j.k &= ~kJobFastBit;
-	const SegDesc *dp = a.desc + j.seg;
-	uint64_t row_start = dp->row_start;
-	uint64_t packed_ptr = dp->packed_ptr;
-	uint64_t min_factor = dp->min_factor;
-	uint32_t count = dp->count;
-	uint32_t w = dp->width;
-	uint32_t state = dp->state;
-	bool repacked = state & kSegRepacked;
-	uint32_t gran = a.tile_granularity ? a.tile_granularity : scan_chunk_values(w);
-	uint32_t first = j.k * gran;
-	uint32_t cnt = min(gran, count - first);
+	const uint64_t row_start = dq.row_start();
+	const uint64_t packed_ptr = dq.packed_ptr();
+	const uint64_t min_factor = dq.min_factor();
+	const uint32_t count = dq.count();
+	const uint32_t w = dq.width();
+	const uint32_t state = dq.state();
+	const bool repacked = state & kSegRepacked;
+	if (gran == 0) {
+		gran = scan_chunk_values(w);
+	}
+	const uint32_t first = k * gran;
+	uint32_t cnt = first < count ? min(gran, count - first) : 0u;
 	if (a.uncompact) {
 		// Uncompact() is a no-op for segments that are not compacted (column_segment.cpp:327-330); a compacted
 		// segment that kept its slot width already sits in the raw arena (unless literal mode adds min, Q1)
@@ -72,20 +74,22 @@ __device__ __forceinline__ Resolved resolve_unit(const DecodeArgs &a, uint32_t j
 			cnt = 0;
 		}
 	}
-	uint64_t src = repacked ? packed_ptr + (((uint64_t)first * w) >> 3)
-	                        : (uint64_t)a.raw + (row_start + first) * (uint64_t)S;
+	const uint64_t src = repacked ? packed_ptr + (((uint64_t)first * w) >> 3)
+	                              : (uint64_t)a.raw + (row_start + first) * (uint64_t)S;
 	r.src16 = src & ~15ull;
-	uint32_t byte_base = (uint32_t)(src - r.src16);
+	const uint32_t byte_base = (uint32_t)(src - r.src16);
 	r.bytes = cnt ? ((byte_base + ((cnt * w + 7u) >> 3) + 15u) & ~15u) : 0u;
-	bool add = (min_factor != ~0ull) && (repacked || a.literal);
+	const bool add = (min_factor != ~0ull) && (repacked || a.literal);
 	r.info.min_add = add ? min_factor : 0ull;
 	r.info.row = row_start + first;
 	r.info.bit_base = byte_base * 8u;
 	r.info.cnt = cnt;
 	r.info.w = w;
-	r.info.seg = j.seg;
+	r.info.seg = seg;
 	r.info.first_value = first;
-	r.info.job = job_idx;
+	r.info.unit = 0;
+	r.info.done = 0;
+	r.info.pad = 0;
 	return r;
 }
 
@@ -101,11 +105,11 @@ __global__ void __launch_bounds__(kThreads) decode_kernel(DecodeArgs a) {
 	const uint32_t tid = threadIdx.x;
 	const uint32_t lane = tid & 31u;
 	const uint32_t warp = tid >> 5;
-	if (a.chunk_first != nullptr) {  // job range read from the device-built chunk table
-		const uint32_t j0 = a.chunk_first[a.seg_b];
-		a.n_jobs = a.chunk_first[a.seg_e] - j0;
-		a.jobs += j0;
-	}
+	// Flat decode: jobs come from the column's static (segment, tile) table.  Fused scans: no table -- job j =
+	// (unit j / kScanParts, chunk index j % kScanParts), unit -> segment seg_b + unit or unit_seg[unit]; chunks
+	// that do not exist cost one descriptor read by one producer lane, and the launch uses an odd grid so that a
+	// CTA's strided job sequence cycles through every chunk index (even load).
+	const uint32_t n_jobs = MODE == kModeFlat ? a.n_jobs : a.n_units * kScanParts;
 
 	if (tid == 0) {
 		for (int s = 0; s < kStages; s++) {
@@ -120,41 +124,80 @@ __global__ void __launch_bounds__(kThreads) decode_kernel(DecodeArgs a) {
 	uint32_t n_pass = 0;
 
 	if (warp == kConsumerWarps) {
-		// ---------------- producer warp: lane s feeds stage s ----------------
-		for (uint32_t it0 = 0;; it0 += kStages) {
-			if (blockIdx.x + it0 * gridDim.x >= a.n_jobs) {
-				break;
+		// ---------------- producer warp: every lane resolves one job; existing units are issued in job order ----
+		uint32_t seq = 0;  // stage sequence number, uniform across the warp
+		const uint32_t batch = 32u * gridDim.x;
+		// job -> (segment, k) -> descriptor, fetched ahead: the pair two batches ahead (flat: a table read), the
+		// descriptor one batch ahead, so neither latency sits between two issue loops
+		auto job_pair = [&](uint32_t job) -> Job {
+			if (MODE == kModeFlat) {
+				return a.jobs[job];
 			}
-			const uint32_t my_it = it0 + lane;
-			const uint32_t job = blockIdx.x + my_it * gridDim.x;
-			const bool have = lane < kStages && job < a.n_jobs;
+			const uint32_t unit = job / kScanParts;
+			Job j;
+			j.seg = a.unit_seg != nullptr ? __ldg(a.unit_seg + unit) : a.seg_b + unit;
+			j.k = job - unit * kScanParts;
+			return j;
+		};
+		const uint32_t job0 = blockIdx.x + lane * gridDim.x;
+		Job jb = {0u, 0u}, jb_next = {0u, 0u};
+		DescQ dq_next;
+		if (job0 < n_jobs) {
+			jb = job_pair(job0);
+			dq_next = load_desc(a.desc + jb.seg);
+		}
+		if (job0 + batch < n_jobs) {
+			jb_next = job_pair(job0 + batch);
+		}
+		for (uint32_t j0 = blockIdx.x; j0 < n_jobs; j0 += batch) {
+			const uint32_t job = j0 + lane * gridDim.x;
+			const DescQ dq = dq_next;
+			const Job cur = jb;
+			jb = jb_next;
+			if (job + batch < n_jobs) {
+				dq_next = load_desc(a.desc + jb.seg);
+				if (job + 2u * batch < n_jobs) {
+					jb_next = job_pair(job + 2u * batch);
+				}
+			}
 			Resolved r;
-			if (have) {
-				r = resolve_unit<S>(a, job);
+			r.bytes = 0;
+			if (job < n_jobs) {
+				r = resolve_unit<S>(a, cur.seg, cur.k, MODE == kModeFlat ? kVectorSize : 0u, dq);
+				r.info.unit = MODE == kModeFlat ? 0u : job / kScanParts;
 			}
-#pragma unroll
-			for (int s = 0; s < kStages; s++) {
-				if ((int)lane == s && have) {
-					mbar_wait(&empty_bar[s], ((my_it / kStages) & 1u) ^ 1u);  // slot drained by all consumer warps
+			// one lane at a time, in job order: the slot's previous user (seq - kStages) has then already been
+			// issued, so the parity wait is never more than one phase ahead
+			uint32_t todo = __ballot_sync(0xffffffffu, r.bytes != 0);
+			while (todo) {
+				const uint32_t l = (uint32_t)__ffs((int)todo) - 1u;
+				todo &= todo - 1u;
+				if (lane == l) {
+					const uint32_t s = seq % kStages;
+					mbar_wait(&empty_bar[s], ((seq / kStages) & 1u) ^ 1u);  // slot drained by the consumers
 					infos[s] = r.info;
 					mbar_arrive_expect_tx(&full_bar[s], r.bytes);
-					if (r.bytes) {
-						tma_load_1d(stage_mem + s * kStageBytes, (const void *)r.src16, r.bytes, &full_bar[s]);
-					}
+					tma_load_1d(stage_mem + s * kStageBytes, (const void *)r.src16, r.bytes, &full_bar[s]);
 				}
+				seq++;
 				__syncwarp();
 			}
+		}
+		if (lane == 0) {
+			const uint32_t s = seq % kStages;
+			mbar_wait(&empty_bar[s], ((seq / kStages) & 1u) ^ 1u);
+			infos[s].done = 1;
+			mbar_arrive(&full_bar[s]);
 		}
 	} else {
 		// ---------------- consumer warps ----------------
 		for (uint32_t it = 0;; it++) {
-			const uint32_t job = blockIdx.x + it * gridDim.x;
-			if (job >= a.n_jobs) {
-				break;
-			}
 			const uint32_t s = it % kStages;
 			mbar_wait(&full_bar[s], (it / kStages) & 1u);
 			const StageInfo in = infos[s];
+			if (in.done) {
+				break;
+			}
 			const uint64_t *words = (const uint64_t *)(stage_mem + s * kStageBytes);
 			const uint32_t *words32 = (const uint32_t *)words;
 			const uint32_t w = in.w;
@@ -165,7 +208,7 @@ __global__ void __launch_bounds__(kThreads) decode_kernel(DecodeArgs a) {
 			uint64_t constant = a.constant;
 			uint32_t query = 0;
 			if (MODE == kModePoint) {
-				query = a.job_query[job];
+				query = in.unit;
 				constant = (uint64_t)a.q_const[query];
 			}
 
@@ -242,12 +285,17 @@ cudaError_t launch_one(const DecodeArgs &args, int sm_count, cudaStream_t stream
 		}
 		configured[dev & 63] = true;
 	}
-	if (args.n_jobs == 0 && args.chunk_first == nullptr) {
+	const uint32_t n_jobs = MODE == kModeFlat ? args.n_jobs : args.n_units * kScanParts;
+	if (n_jobs == 0) {
 		return cudaSuccess;
 	}
-	uint32_t grid = (uint32_t)sm_count * 3u;  // 3 CTAs x 64.1 KiB of stages per SM
-	if (args.chunk_first == nullptr && grid > args.n_jobs) {
-		grid = args.n_jobs;
+	// 3 CTAs x 64.1 KiB of stages per SM, all resident; fused scans: odd (see the kernel)
+	uint32_t grid = (uint32_t)sm_count * 3u;
+	if (MODE != kModeFlat) {
+		grid = (grid - 1u) | 1u;
+	}
+	if (grid > n_jobs) {
+		grid = n_jobs;
 	}
 	kernel<<<grid, kThreads, smem, stream>>>(args);
 	return cudaGetLastError();
@@ -259,7 +307,7 @@ cudaError_t launch_mode(DecodeMode mode, const DecodeArgs &args, int sm_count, c
 	case kModeFlat:
 		return launch_one<S, false, kModeFlat>(args, sm_count, stream);
 	case kModeSum:
-		return launch_one<S, SIGNED, kModeSum>(args, sm_count, stream);
+		return cudaErrorInvalidValue;  // fused SUM lives in kernels_scan.cu (width-specialised)
 	case kModeFilter:
 		return launch_one<S, SIGNED, kModeFilter>(args, sm_count, stream);
 	default:

@@ -172,62 +172,117 @@ __global__ void __launch_bounds__(kAnalyzeThreads) analyze_kernel(SegDesc *desc,
 // ---------------------------------------------------------------------------------------------------
 
 constexpr int kLayoutThreads = 1024;
+constexpr int kLayoutItems = 5;  // descriptors per thread and pass, all loaded before the first dependent use
 
+// Single CTA.  Thread t owns kLayoutItems consecutive segments per pass: their descriptor quarters are loaded
+// up front (independent 128-bit loads, one memory round trip), the aligned payload sizes go through ONE block
+// scan per pass, and the results are written back with vector stores.  `totals` is host-mapped pinned memory:
+// {words, ticket}; the host spins on the ticket instead of paying a stream synchronisation.
 __global__ void __launch_bounds__(kLayoutThreads) layout_kernel(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs,
                                                                 int type_size, int flags, uint32_t extent,
-                                                                unsigned long long *totals) {
-	__shared__ unsigned long long partial[kLayoutThreads];
+                                                                volatile unsigned long long *totals,
+                                                                unsigned long long ticket) {
+	__shared__ unsigned long long warp_tot[kLayoutThreads / 32];
+	__shared__ unsigned long long running_s;
 	const uint32_t tid = threadIdx.x;
-	const uint32_t per = (n_segs + kLayoutThreads - 1) / kLayoutThreads;
-	const uint32_t lo = min(n_segs, tid * per), hi = min(n_segs, lo + per);
+	const uint32_t lane = tid & 31u, warp = tid >> 5;
 	const bool padded = flags & kFlagPadded;
 	const bool zero_ext = flags & kFlagZeroExt;
 	const uint32_t slot_w = 8u * (uint32_t)type_size;
-
-	unsigned long long mine = 0;
-	for (uint32_t g = lo; g < hi; g++) {
-		SegDesc *d = desc + seg_begin + g;
-		uint32_t count = d->count;
-		if (count == 0 || (d->state & kSegCompacted)) {
-			continue;  // Compact() returns early for empty or already compacted segments (column_segment.cpp:278)
-		}
-		uint64_t mn = d->min_factor, mx = d->max_factor;
-		uint64_t range;
-		if (zero_ext) {
-			// BitCompressFromUncompressed only subtracts when max > min (column_segment.cpp:408-411)
-			range = (mx != 0 && mn != ~0ull && mx > mn) ? mx - mn : mx;
-		} else {
-			range = mx - mn;
-		}
-		uint32_t w = width_for_range(range, padded);
-		bool repack = slot_w > w;
-		uint64_t words = repack ? ((uint64_t)count * w + 63) >> 6 : 0;
-		uint64_t aligned = (words + kSegAlignWords - 1) & ~(uint64_t)(kSegAlignWords - 1);
-		d->width = (uint8_t)(repack ? w : slot_w);
-		d->state = (uint8_t)((d->state & kSegAnalyzed) | kSegCompacted | (repack ? kSegRepacked : 0));
-		d->word_offset = mine;  // local offset, rebased below
-		d->extent = extent;
-		d->packed_ptr = 0;
-		mine += aligned;
+	if (tid == 0) {
+		running_s = 0;
 	}
-	partial[tid] = mine;
 	__syncthreads();
-	// inclusive Hillis-Steele scan over the 1024 partials
-	for (uint32_t off = 1; off < kLayoutThreads; off <<= 1) {
-		unsigned long long v = tid >= off ? partial[tid - off] : 0;
-		__syncthreads();
-		partial[tid] += v;
-		__syncthreads();
-	}
-	unsigned long long base = partial[tid] - mine;
-	for (uint32_t g = lo; g < hi; g++) {
-		SegDesc *d = desc + seg_begin + g;
-		if (d->count != 0 && d->extent == extent && d->packed_ptr == 0 && (d->state & kSegRepacked)) {
-			d->word_offset += base;
+
+	for (uint32_t base = 0; base < n_segs; base += kLayoutThreads * kLayoutItems) {
+		const uint32_t g0 = base + tid * kLayoutItems;
+		uint64_t mn_r[kLayoutItems], mx_r[kLayoutItems];
+		uint32_t count_r[kLayoutItems], wst_r[kLayoutItems];  // wst = width | state << 8 | pad
+#pragma unroll
+		for (int i = 0; i < kLayoutItems; i++) {
+			if (g0 + i < n_segs) {
+				const SegDesc *d = desc + seg_begin + g0 + i;
+				mn_r[i] = d->min_factor;
+				mx_r[i] = d->max_factor;
+				count_r[i] = d->count;
+				wst_r[i] = ((const uint32_t *)d)[14];
+			}
 		}
+		unsigned long long aligned[kLayoutItems];
+		unsigned long long mine = 0;
+#pragma unroll
+		for (int i = 0; i < kLayoutItems; i++) {
+			aligned[i] = ~0ull;  // ~0: descriptor left untouched
+			if (g0 + i < n_segs) {
+				const uint32_t count = count_r[i];
+				const uint32_t state = (wst_r[i] >> 8) & 0xffu;
+				// Compact() returns early for empty or already compacted segments (column_segment.cpp:278)
+				if (count != 0 && !(state & kSegCompacted)) {
+					const uint64_t mn = mn_r[i], mx = mx_r[i];
+					uint64_t range;
+					if (zero_ext) {
+						// BitCompressFromUncompressed only subtracts when max > min (column_segment.cpp:408-411)
+						range = (mx != 0 && mn != ~0ull && mx > mn) ? mx - mn : mx;
+					} else {
+						range = mx - mn;
+					}
+					const uint32_t w = width_for_range(range, padded);
+					const bool repack = slot_w > w;
+					const uint64_t words = repack ? ((uint64_t)count * w + 63) >> 6 : 0;
+					aligned[i] = (words + kSegAlignWords - 1) & ~(uint64_t)(kSegAlignWords - 1);
+					const uint32_t new_state = (state & kSegAnalyzed) | kSegCompacted | (repack ? kSegRepacked : 0);
+					wst_r[i] = (wst_r[i] & 0xffff0000u) | (new_state << 8) | (repack ? w : slot_w);
+					mine += aligned[i];
+				}
+			}
+		}
+		// block-wide exclusive scan of `mine`
+		unsigned long long incl = mine;
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) {
+			unsigned long long v = __shfl_up_sync(0xffffffffu, incl, d);
+			if ((int)lane >= d) {
+				incl += v;
+			}
+		}
+		if (lane == 31) {
+			warp_tot[warp] = incl;
+		}
+		__syncthreads();
+		const unsigned long long running = running_s;
+		if (warp == 0) {
+			unsigned long long t = warp_tot[lane], ti = t;
+#pragma unroll
+			for (int d = 1; d < 32; d <<= 1) {
+				unsigned long long v = __shfl_up_sync(0xffffffffu, ti, d);
+				if ((int)lane >= d) {
+					ti += v;
+				}
+			}
+			warp_tot[lane] = ti - t;  // exclusive
+			if (lane == 31) {
+				running_s = running + ti;
+			}
+		}
+		__syncthreads();
+		unsigned long long off = running + warp_tot[warp] + incl - mine;
+#pragma unroll
+		for (int i = 0; i < kLayoutItems; i++) {
+			if (g0 + i < n_segs && aligned[i] != ~0ull) {
+				SegDesc *d = desc + seg_begin + g0 + i;
+				d->packed_ptr = 0;
+				d->word_offset = off;
+				d->extent = extent;
+				((uint32_t *)d)[14] = wst_r[i];
+				off += aligned[i];
+			}
+		}
+		__syncthreads();  // warp_tot / running_s are reused by the next pass
 	}
-	if (tid == kLayoutThreads - 1) {
-		totals[0] = partial[tid];
+	if (tid == 0) {
+		totals[0] = running_s;
+		__threadfence_system();
+		totals[1] = ticket;
 	}
 }
 
@@ -255,219 +310,6 @@ __global__ void reset_uncompacted_kernel(SegDesc *desc, uint32_t seg_begin, uint
 			d->word_offset = 0;
 		}
 	}
-}
-
-// ---------------------------------------------------------------------------------------------------
-// encode
-// ---------------------------------------------------------------------------------------------------
-
-constexpr int kEncodeConsumerWarps = 8;
-constexpr int kEncodeConsumers = kEncodeConsumerWarps * 32;
-constexpr int kEncodeThreads = kEncodeConsumers + 32;  // + one producer warp feeding the TMA ring
-constexpr int kEncodeStages = 3;
-template <int S> struct EncodeStage { static constexpr uint32_t kBytes = kVectorSize * S + 32; };
-
-struct EncodeInfo {
-	uint64_t sub;        // value subtracted from every slot (0 when min_factor is unset)
-	uint64_t *out;       // first output word of this tile
-	uint32_t byte_base;  // offset of the tile's first value inside the staged bytes (0..15)
-	uint32_t cnt;        // values in the tile (0: segment not repacked, nothing to do)
-	uint32_t w;
-	uint32_t gap;        // last tile of a segment: zero words up to the next 128-byte boundary
-	uint32_t magic;      // ceil(2^24 / w): n / w == (n * magic) >> 24 for n < 2^17, w <= 64
-	uint32_t pad;
-};
-
-struct EncodeResolved {
-	EncodeInfo info;
-	uint64_t src16;
-	uint32_t bytes;
-};
-
-template <int S>
-__device__ __forceinline__ EncodeResolved resolve_encode_tile(const SegDesc *desc, const Job *tiles, uint32_t tile_idx,
-                                                              const uint8_t *raw, uint32_t extent) {
-	EncodeResolved r;
-	Job j = tiles[tile_idx];
-	const SegDesc *d = desc + j.seg;
-	uint32_t count = d->count;
-	uint32_t w = d->width;
-	uint32_t first = j.k * kVectorSize;
-	bool repacked = (d->state & kSegRepacked) && d->extent == extent && d->packed_ptr != 0;
-	uint32_t cnt = repacked ? min(kVectorSize, count - first) : 0u;
-	uint64_t src = (uint64_t)raw + (d->row_start + first) * (uint64_t)S;
-	r.src16 = src & ~15ull;
-	uint32_t byte_base = (uint32_t)(src - r.src16);
-	r.bytes = cnt ? ((byte_base + cnt * S + 15u) & ~15u) : 0u;
-	uint64_t mn = d->min_factor;
-	r.info.sub = mn == ~0ull ? 0ull : mn;
-	r.info.out = (uint64_t *)d->packed_ptr + (uint64_t)j.k * (kVectorSize / 64) * w;
-	r.info.byte_base = byte_base;
-	r.info.cnt = cnt;
-	r.info.w = w;
-	uint32_t gap = 0;
-	if (cnt && first + cnt == count) {
-		uint64_t total = ((uint64_t)count * w + 63) >> 6;
-		gap = (uint32_t)(((total + kSegAlignWords - 1) & ~(uint64_t)(kSegAlignWords - 1)) - total);
-	}
-	r.info.gap = gap;
-	r.info.magic = ((1u << 24) + w - 1u) / w;
-	r.info.pad = 0;
-	return r;
-}
-
-template <int S>
-__device__ __forceinline__ uint64_t load_slot(const uint8_t *base, uint32_t i) {
-	// the slot-width int_vector read: zero-extended S raw bytes (bits::read_int at width 8*S)
-	using T = typename UIntOf<S>::type;
-	return (uint64_t)((const T *)base)[i];
-}
-
-__device__ __forceinline__ uint32_t div_magic(uint32_t n, uint32_t magic) {
-	return (uint32_t)(((uint64_t)n * magic) >> 24);
-}
-
-template <int S>
-__global__ void __launch_bounds__(kEncodeThreads) encode_kernel(const SegDesc *desc, const Job *tiles, uint32_t n_tiles,
-                                                                const uint8_t *raw, uint32_t extent) {
-	extern __shared__ __align__(128) uint8_t stage_mem[];
-	__shared__ __align__(8) uint64_t full_bar[kEncodeStages];
-	__shared__ __align__(8) uint64_t empty_bar[kEncodeStages];
-	__shared__ EncodeInfo infos[kEncodeStages];
-	constexpr uint32_t kStage = EncodeStage<S>::kBytes;
-	const uint32_t tid = threadIdx.x;
-	const uint32_t lane = tid & 31u;
-	const uint32_t warp = tid >> 5;
-
-	if (tid == 0) {
-		for (int s = 0; s < kEncodeStages; s++) {
-			mbar_init(&full_bar[s], 1);
-			mbar_init(&empty_bar[s], 1);
-		}
-		mbar_fence_init();
-	}
-	__syncthreads();
-
-	if (warp == kEncodeConsumerWarps) {
-		// ---------------- producer warp: lane s feeds stage s ----------------
-		for (uint32_t it0 = 0;; it0 += kEncodeStages) {
-			if (blockIdx.x + it0 * gridDim.x >= n_tiles) {
-				break;
-			}
-			const uint32_t my_it = it0 + lane;
-			const uint32_t t = blockIdx.x + my_it * gridDim.x;
-			const bool have = lane < kEncodeStages && t < n_tiles;
-			EncodeResolved r;
-			if (have) {
-				r = resolve_encode_tile<S>(desc, tiles, t, raw, extent);
-			}
-#pragma unroll
-			for (int s = 0; s < kEncodeStages; s++) {
-				if ((int)lane == s && have) {
-					mbar_wait(&empty_bar[s], ((my_it / kEncodeStages) & 1u) ^ 1u);
-					infos[s] = r.info;
-					mbar_arrive_expect_tx(&full_bar[s], r.bytes);
-					if (r.bytes) {
-						tma_load_1d(stage_mem + s * kStage, (const void *)r.src16, r.bytes, &full_bar[s]);
-					}
-				}
-				__syncwarp();
-			}
-		}
-		return;
-	}
-
-	// ---------------- consumer warps ----------------
-	for (uint32_t it = 0;; it++) {
-		uint32_t t = blockIdx.x + it * gridDim.x;
-		if (t >= n_tiles) {
-			break;
-		}
-		const uint32_t s = it % kEncodeStages;
-		mbar_wait(&full_bar[s], (it / kEncodeStages) & 1u);
-		const EncodeInfo in = infos[s];
-		const uint8_t *vals = stage_mem + s * kStage + in.byte_base;
-		const uint32_t w = in.w;
-		const uint32_t cnt = in.cnt;
-
-		if (cnt) {
-			if (w <= 32u) {
-				// 32-bit output units: unit j holds bits [32j, 32j+32) of the tile's stream
-				const uint32_t n_units = (((cnt * w + 63u) >> 6) << 1);
-				const uint32_t mask = (uint32_t)lo_set64(w);
-				const uint32_t sub = (uint32_t)in.sub;
-				uint32_t *out32 = (uint32_t *)in.out;
-				for (uint32_t j = tid; j < n_units; j += kEncodeConsumers) {
-					const uint32_t bit0 = j * 32u;
-					const uint32_t i0 = div_magic(bit0, in.magic);
-					const uint32_t i1 = min(cnt - 1u, div_magic(bit0 + 31u, in.magic));
-					uint32_t acc = 0;
-					if (i0 < cnt) {
-						const uint32_t c = i1 - i0 + 1u;
-						uint32_t r = (lane * c) >> 5;  // rotate the start so the lanes of a warp hit different banks
-						for (uint32_t n = 0; n < c; n++) {
-							const uint32_t i = i0 + r;
-							const uint32_t f = ((uint32_t)load_slot<S>(vals, i) - sub) & mask;
-							const int p = (int)(i * w) - (int)bit0;
-							acc |= p >= 0 ? (f << p) : (f >> (-p));
-							r = (r + 1u == c) ? 0u : r + 1u;
-						}
-					}
-					out32[j] = acc;
-				}
-			} else {
-				const uint32_t n_words = (cnt * w + 63u) >> 6;
-				const uint64_t mask = lo_set64(w);
-				for (uint32_t j = tid; j < n_words; j += kEncodeConsumers) {
-					const uint32_t bit0 = j * 64u;
-					const uint32_t i0 = div_magic(bit0, in.magic);
-					const uint32_t i1 = min(cnt - 1u, div_magic(bit0 + 63u, in.magic));
-					uint64_t acc = 0;
-					for (uint32_t i = i0; i <= i1; i++) {  // at most 3 values touch one word when w > 32
-						const uint64_t f = (load_slot<S>(vals, i) - in.sub) & mask;
-						const int p = (int)(i * w) - (int)bit0;
-						acc |= p >= 0 ? (f << p) : (f >> (-p));
-					}
-					in.out[j] = acc;
-				}
-			}
-			if (tid < in.gap) {  // keep the alignment gap behind the payload deterministic (zero)
-				in.out[((cnt * w + 63u) >> 6) + tid] = 0ull;
-			}
-		}
-		// consumers in lockstep (named barrier 1), then one of them frees the stage for the producer
-		asm volatile("bar.sync 1, %0;" ::"n"(kEncodeConsumers) : "memory");
-		if (tid == 0) {
-			mbar_arrive(&empty_bar[s]);
-		}
-	}
-}
-
-template <int S>
-cudaError_t launch_encode_s(const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw,
-                            uint32_t extent, int sm_count, cudaStream_t stream) {
-	static bool configured[64] = {};
-	const size_t smem = (size_t)kEncodeStages * EncodeStage<S>::kBytes;
-	auto kernel = encode_kernel<S>;
-	int dev = 0;
-	cudaGetDevice(&dev);
-	if (!configured[dev & 63]) {
-		cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-		if (e != cudaSuccess) {
-			return e;
-		}
-		configured[dev & 63] = true;
-	}
-	if (n_tiles == 0) {
-		return cudaSuccess;
-	}
-	uint32_t per_sm = S == 8 ? 4u : (S == 4 ? 6u : 8u);
-	uint32_t grid = (uint32_t)sm_count * per_sm;
-	if (grid > n_tiles) {
-		grid = n_tiles;
-	}
-	kernel<<<grid, kEncodeThreads, smem, stream>>>(desc, tiles, n_tiles, raw, extent);
-	return cudaGetLastError();
 }
 
 template <int S>
@@ -503,8 +345,8 @@ cudaError_t launch_analyze(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32
 }
 
 cudaError_t launch_layout(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int flags, uint32_t extent,
-                          unsigned long long *totals, cudaStream_t stream) {
-	layout_kernel<<<1, kLayoutThreads, 0, stream>>>(desc, seg_begin, n_segs, t.size, flags, extent, totals);
+                          unsigned long long *totals, unsigned long long ticket, cudaStream_t stream) {
+	layout_kernel<<<1, kLayoutThreads, 0, stream>>>(desc, seg_begin, n_segs, t.size, flags, extent, totals, ticket);
 	return cudaGetLastError();
 }
 
@@ -524,22 +366,6 @@ cudaError_t launch_reset_uncompacted(SegDesc *desc, uint32_t seg_begin, uint32_t
 	}
 	reset_uncompacted_kernel<<<(n_segs + 255) / 256, 256, 0, stream>>>(desc, seg_begin, n_segs, type_size);
 	return cudaGetLastError();
-}
-
-cudaError_t launch_encode(TypeInfo t, const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw,
-                          uint32_t extent, int sm_count, cudaStream_t stream) {
-	switch (t.size) {
-	case 1:
-		return launch_encode_s<1>(desc, tiles, n_tiles, raw, extent, sm_count, stream);
-	case 2:
-		return launch_encode_s<2>(desc, tiles, n_tiles, raw, extent, sm_count, stream);
-	case 4:
-		return launch_encode_s<4>(desc, tiles, n_tiles, raw, extent, sm_count, stream);
-	case 8:
-		return launch_encode_s<8>(desc, tiles, n_tiles, raw, extent, sm_count, stream);
-	default:
-		return cudaErrorInvalidValue;
-	}
 }
 
 }  // namespace adacom

@@ -1,0 +1,314 @@
+// kernels_pack.cu -- the re-pack loop of the succinct codec, width-specialised for sm_100a.
+//
+// Replaces the scalar in-place loop of ColumnSegment::BitCompressFromSuccinct / BitCompressFromUncompressed
+// (src/storage/table/column_segment.cpp:365-378, 427-446): for i < count
+//     field = (slot[i] - min_factor) & lo_set[w];  bits::write_int_and_move(field, w)
+// (third_party/sdsl/include/sdsl/bits.hpp:478-499), LSB first, tail bits of the last word zero
+// (memory_management.hpp:360-365).
+//
+// Work unit = one 2048-value tile counted from the segment start (256*w output bytes, 16-byte aligned).
+// 64 consecutive values always fill exactly w whole 64-bit words, so a tile is 32 independent "rows" of
+// 64 values -> w words.  One CTA (8 warps) per tile, three phases:
+//
+//   A  every thread loads 8 raw values with coalesced global loads, subtracts the frame of reference,
+//      masks to w bits and parks the field in shared memory at an XOR-swizzled position
+//      (pos = i ^ (row & 31|15)): conflict-free both for this linear write and for phase B's strided read;
+//   B  lane = row, warp q = the q-th eighth of the row's w output words.  The template fixes (w, q), so the
+//      list of fields touching those words and every shift amount are compile-time constants: a field costs
+//      one shared load and one or two shift/or (gather formulation: no atomics, no inter-thread carries,
+//      boundary fields are simply read by both neighbours).  Words go to a staging row of odd stride
+//      (w | 1 words): conflict-free 64-bit shared stores;
+//   C  the tile's packed words leave as coalesced 64-bit global stores (+ the zeroed gap up to the next
+//      128-byte boundary behind the last tile of a segment).
+//
+// Algorithmic HBM bytes per tile: cnt*S read + 8*ceil(cnt*w/64) written; nothing is re-read.
+#include "adacom_kernels.cuh"
+
+namespace adacom {
+
+namespace {
+
+constexpr int kPackThreads = 256;
+constexpr int kRowValues = 64;                        // values per row: always w whole output words
+constexpr int kRows = kVectorSize / kRowValues;       // 32 rows per tile == lanes of a warp
+constexpr int kSubs = kPackThreads / 32;              // 8 warps share the words of a row
+
+struct PackTile {
+	uint64_t sub;        // value subtracted from every slot (0 when min_factor is unset)
+	uint64_t *out;       // first output word of this tile
+	const uint8_t *src;  // first raw value of this tile
+	uint32_t cnt;        // values in the tile (0: segment not repacked by this encode call)
+	uint32_t w;
+	uint32_t gap;        // last tile of a segment: zero words up to the next 128-byte boundary
+};
+
+template <int S>
+__device__ __forceinline__ PackTile resolve_pack_tile(const DescQ &dq, uint32_t k, const uint8_t *raw, uint32_t extent) {
+	PackTile t;
+	const uint64_t row_start = dq.row_start();
+	const uint64_t packed_ptr = dq.packed_ptr();
+	const uint64_t mn = dq.min_factor();
+	const uint32_t count = dq.count();
+	const uint32_t w = dq.width();
+	const uint32_t state = dq.state();
+	const uint32_t first = k * kVectorSize;
+	const bool repacked = (state & kSegRepacked) && dq.extent() == extent && packed_ptr != 0 && first < count;
+	t.cnt = repacked ? min(kVectorSize, count - first) : 0u;
+	t.src = raw + (row_start + first) * (uint64_t)S;
+	t.sub = mn == ~0ull ? 0ull : mn;
+	t.out = (uint64_t *)packed_ptr + (uint64_t)k * (kVectorSize / 64) * w;
+	t.w = w;
+	uint32_t gap = 0;
+	if (t.cnt && first + t.cnt == count) {
+		const uint64_t total = ((uint64_t)count * w + 63) >> 6;
+		gap = (uint32_t)(((total + kSegAlignWords - 1) & ~(uint64_t)(kSegAlignWords - 1)) - total);
+	}
+	t.gap = gap;
+	return t;
+}
+
+// ---- phase A: raw slots -> swizzled fields ------------------------------------------------------------
+
+// raw slots are read exactly once: evict-first
+__device__ __forceinline__ uint8_t load_stream(const uint8_t *p) { return __ldcs(p); }
+__device__ __forceinline__ uint16_t load_stream(const uint16_t *p) { return __ldcs(p); }
+__device__ __forceinline__ uint32_t load_stream(const uint32_t *p) { return __ldcs(p); }
+__device__ __forceinline__ uint64_t load_stream(const uint64_t *p) { return (uint64_t)__ldcs((const unsigned long long *)p); }
+
+template <typename F> struct Swz { static constexpr uint32_t kMask = sizeof(F) == 4 ? 31u : 15u; };
+
+template <int S, typename F>
+__device__ __forceinline__ void phase_a(const PackTile &t, F *fld, uint32_t tid) {
+	using T = typename UIntOf<S>::type;
+	const T *vals = (const T *)t.src;  // the slot-width int_vector read: zero-extended S raw bytes
+	const F mask = (F)lo_set64(t.w);
+	const F sub = (F)t.sub;
+	constexpr uint32_t XM = Swz<F>::kMask;
+	constexpr int PER = kVectorSize / kPackThreads;  // 8 values per thread
+	T r[PER];
+	if (t.cnt == kVectorSize) {
+#pragma unroll
+		for (int j = 0; j < PER; j++) {
+			r[j] = load_stream(vals + j * kPackThreads + tid);
+		}
+	} else {
+#pragma unroll
+		for (int j = 0; j < PER; j++) {
+			const uint32_t i = j * kPackThreads + tid;
+			r[j] = i < t.cnt ? load_stream(vals + i) : (T)sub;  // padding packs to zero fields
+		}
+	}
+#pragma unroll
+	for (int j = 0; j < PER; j++) {
+		const uint32_t i = j * kPackThreads + tid;
+		const uint32_t row = i / kRowValues;
+		fld[i ^ (row & XM)] = ((F)r[j] - sub) & mask;
+	}
+}
+
+// ---- phase B: fields of one row -> the words of sub-range q -------------------------------------------
+
+template <int W, int Q, typename F>
+__device__ __forceinline__ void pack_sub(const F *fld_row, uint32_t x, uint64_t *out_row) {
+	constexpr int K0 = Q * W / kSubs, K1 = (Q + 1) * W / kSubs;  // output words [K0, K1) of the row
+	if constexpr (K1 > K0) {
+		constexpr int V0 = 64 * K0 / W, V1 = (64 * K1 - 1) / W;  // fields touching them (inclusive)
+		constexpr int NU = 2 * (K1 - K0);
+		constexpr uint32_t XM = Swz<F>::kMask;
+		uint32_t unit[NU];  // 32-bit output units, unit n covers bits [64*K0 + 32n, +32) of the row
+#pragma unroll
+		for (int n = 0; n < NU; n++) {
+			unit[n] = 0u;
+		}
+#pragma unroll
+		for (int v = V0; v <= V1; v++) {
+			const F f = fld_row[(v & ~XM) | ((v & XM) ^ x)];
+			const int p = v * W - 64 * K0;      // bit position relative to the first owned word (may be < 0)
+			const int n0 = (p + 64) / 32 - 2;   // floor(p / 32)
+			const int s = (p + 64) & 31;
+			const uint32_t lo = (uint32_t)f;
+			const uint32_t hi = sizeof(F) == 8 ? (uint32_t)((uint64_t)f >> 32) : 0u;
+			// the field as a 96-bit string shifted left by s, cut into three units
+			if (n0 >= 0 && n0 < NU) {
+				unit[n0] |= lo << s;
+			}
+			if (s + W > 32 && n0 + 1 >= 0 && n0 + 1 < NU) {
+				unit[n0 + 1] |= s == 0 ? hi : __funnelshift_l(lo, hi, s);
+			}
+			if (s + W > 64 && n0 + 2 >= 0 && n0 + 2 < NU) {
+				unit[n0 + 2] |= hi >> (32 - s);
+			}
+		}
+#pragma unroll
+		for (int k = 0; k < K1 - K0; k++) {
+			out_row[K0 + k] = ((uint64_t)unit[2 * k + 1] << 32) | unit[2 * k];
+		}
+	}
+}
+
+template <int W, typename F>
+__device__ __forceinline__ void phase_b(const F *fld, uint64_t *ostage, uint32_t cnt, uint32_t warp, uint32_t lane) {
+	constexpr uint32_t WP = W | 1;  // odd row stride: conflict-free 64-bit stores across the lanes
+	if (lane * kRowValues >= cnt) {
+		return;
+	}
+	const F *fld_row = fld + lane * kRowValues;
+	const uint32_t x = lane & Swz<F>::kMask;
+	uint64_t *out_row = ostage + lane * WP;
+	switch (warp) {
+	case 0: pack_sub<W, 0, F>(fld_row, x, out_row); break;
+	case 1: pack_sub<W, 1, F>(fld_row, x, out_row); break;
+	case 2: pack_sub<W, 2, F>(fld_row, x, out_row); break;
+	case 3: pack_sub<W, 3, F>(fld_row, x, out_row); break;
+	case 4: pack_sub<W, 4, F>(fld_row, x, out_row); break;
+	case 5: pack_sub<W, 5, F>(fld_row, x, out_row); break;
+	case 6: pack_sub<W, 6, F>(fld_row, x, out_row); break;
+	default: pack_sub<W, 7, F>(fld_row, x, out_row); break;
+	}
+}
+
+template <int W>
+__device__ __forceinline__ void phase_b_w(const void *fld, uint64_t *ostage, uint32_t cnt, uint32_t warp, uint32_t lane) {
+	if constexpr (W <= 32) {
+		phase_b<W, uint32_t>((const uint32_t *)fld, ostage, cnt, warp, lane);
+	} else {
+		phase_b<W, uint64_t>((const uint64_t *)fld, ostage, cnt, warp, lane);
+	}
+}
+
+// widths a type of S bytes can be re-packed to: 1 .. 8*S - 1 (re-pack iff 8*S > w, column_segment.cpp:363)
+template <int S, int W>
+__device__ __forceinline__ void phase_b_case(const void *fld, uint64_t *ostage, uint32_t cnt, uint32_t warp, uint32_t lane) {
+	if constexpr (W >= 1 && W < 8 * S) {
+		phase_b_w<W>(fld, ostage, cnt, warp, lane);
+	}
+}
+
+#define PACK_CASE(W) case W: phase_b_case<S, W>(fld, ostage, t.cnt, warp, lane); break;
+#define PACK_CASES_8(B) PACK_CASE(B) PACK_CASE(B + 1) PACK_CASE(B + 2) PACK_CASE(B + 3) PACK_CASE(B + 4) PACK_CASE(B + 5) PACK_CASE(B + 6) PACK_CASE(B + 7)
+
+template <int S> struct PackSmem {
+	static constexpr uint32_t kFieldBytes = kVectorSize * (S == 8 ? 8u : 4u);
+	static constexpr uint32_t kMaxW = 8 * S - 1;
+	static constexpr uint32_t kStageBytes = kRows * (kMaxW | 1u) * 8u;
+	static constexpr uint32_t kBytes = kFieldBytes + kStageBytes;
+};
+
+template <int S>
+__global__ void __launch_bounds__(kPackThreads, 5) pack_kernel(const SegDesc *desc, const Job *tiles, uint32_t n_tiles,
+                                                               const uint8_t *raw, uint32_t extent) {
+	extern __shared__ __align__(16) uint8_t pack_smem[];
+	void *fld = pack_smem;
+	uint64_t *ostage = (uint64_t *)(pack_smem + PackSmem<S>::kFieldBytes);
+	const uint32_t tid = threadIdx.x;
+	const uint32_t lane = tid & 31u;
+	const uint32_t warp = tid >> 5;
+
+	// static tile table -> descriptor: both fetched ahead (the pair two tiles ahead, the descriptor one tile ahead)
+	uint32_t ti = blockIdx.x;
+	if (ti >= n_tiles) {
+		return;
+	}
+	Job job = tiles[ti];
+	Job job_next = ti + gridDim.x < n_tiles ? tiles[ti + gridDim.x] : job;
+	DescQ dq = load_desc(desc + job.seg);
+	for (;;) {
+		const PackTile t = resolve_pack_tile<S>(dq, job.k, raw, extent);
+		const uint32_t next = ti + gridDim.x;
+		job = job_next;
+		if (next < n_tiles) {
+			dq = load_desc(desc + job.seg);
+			if (next + gridDim.x < n_tiles) {
+				job_next = tiles[next + gridDim.x];
+			}
+		}
+		if (t.cnt) {
+			if (S < 8 || t.w <= 32u) {
+				phase_a<S, uint32_t>(t, (uint32_t *)fld, tid);
+			} else {
+				phase_a<S, uint64_t>(t, (uint64_t *)fld, tid);
+			}
+			__syncthreads();
+			switch (t.w) {
+				PACK_CASES_8(0)
+				PACK_CASES_8(8)
+				PACK_CASES_8(16)
+				PACK_CASES_8(24)
+				PACK_CASES_8(32)
+				PACK_CASES_8(40)
+				PACK_CASES_8(48)
+				PACK_CASES_8(56)
+			default:
+				break;
+			}
+			__syncthreads();
+			// phase C: staging rows (stride w | 1) -> linear words
+			const uint32_t w = t.w;
+			const uint32_t n_words = (t.cnt * w + 63u) >> 6;
+			const uint32_t magic = ((1u << 20) + w - 1u) / w;  // m / w == (m * magic) >> 20 for m < 2^14
+			const uint32_t pad = (w & 1u) ^ 1u;
+			for (uint32_t m = tid; m < n_words; m += kPackThreads) {
+				const uint32_t row = (m * magic) >> 20;
+				t.out[m] = ostage[m + row * pad];
+			}
+			if (tid < t.gap) {  // keep the alignment gap behind the payload deterministic (zero)
+				t.out[n_words + tid] = 0ull;
+			}
+		}
+		if (next >= n_tiles) {
+			break;
+		}
+		ti = next;
+	}
+}
+
+template <int S>
+cudaError_t launch_pack_s(const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw, uint32_t extent,
+                          int sm_count, cudaStream_t stream) {
+	static int per_sm[64] = {};  // per device: resident CTAs per SM (0 = not configured yet)
+	const size_t smem = PackSmem<S>::kBytes;
+	auto kernel = pack_kernel<S>;
+	int dev = 0;
+	cudaGetDevice(&dev);
+	if (per_sm[dev & 63] == 0) {
+		cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		if (e != cudaSuccess) {
+			return e;
+		}
+		int n = 0;
+		e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kPackThreads, smem);
+		if (e != cudaSuccess) {
+			return e;
+		}
+		per_sm[dev & 63] = n > 0 ? n : 1;
+	}
+	if (n_tiles == 0) {
+		return cudaSuccess;
+	}
+	uint32_t grid = (uint32_t)sm_count * (uint32_t)per_sm[dev & 63];  // persistent, all resident
+	if (grid > n_tiles) {
+		grid = n_tiles;
+	}
+	kernel<<<grid, kPackThreads, smem, stream>>>(desc, tiles, n_tiles, raw, extent);
+	return cudaGetLastError();
+}
+
+}  // namespace
+
+cudaError_t launch_encode(TypeInfo t, const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw,
+                          uint32_t extent, int sm_count, cudaStream_t stream) {
+	switch (t.size) {
+	case 1:
+		return launch_pack_s<1>(desc, tiles, n_tiles, raw, extent, sm_count, stream);
+	case 2:
+		return launch_pack_s<2>(desc, tiles, n_tiles, raw, extent, sm_count, stream);
+	case 4:
+		return launch_pack_s<4>(desc, tiles, n_tiles, raw, extent, sm_count, stream);
+	case 8:
+		return launch_pack_s<8>(desc, tiles, n_tiles, raw, extent, sm_count, stream);
+	default:
+		return cudaErrorInvalidValue;
+	}
+}
+
+}  // namespace adacom

@@ -37,7 +37,7 @@ struct ChunkInfo {
 	uint32_t min_is_negative;  // fast: ext_min is to be read as a negative int64 (signed T)
 	uint32_t bit_base;         // slow: bit position of the first field inside the staged bytes (0..127)
 	uint32_t fast;
-	uint32_t pad;
+	uint32_t done;             // sentinel: the producer has no more chunks for this CTA
 };
 
 __host__ __device__ constexpr int gcd64(int w) {
@@ -248,7 +248,7 @@ struct WidthSwitch<64> {
 struct ResolvedChunk {
 	ChunkInfo info;
 	uint64_t src16;
-	uint32_t bytes;
+	uint32_t bytes;  // 0: this (segment, chunk index) does not exist
 };
 
 __device__ __forceinline__ uint64_t extend_runtime(uint64_t x, int type_size, int is_signed) {
@@ -256,25 +256,58 @@ __device__ __forceinline__ uint64_t extend_runtime(uint64_t x, int type_size, in
 	return is_signed ? (uint64_t)(((int64_t)(x << shift)) >> shift) : ((x << shift) >> shift);
 }
 
-__device__ __forceinline__ ResolvedChunk resolve_chunk(const ScanSumArgs &a, const Job *jobs, uint32_t job_idx) {
+// sum(decoded) == sum(fields) + count * extend(min) iff [min, min + 2^w - 1] stays inside one sign /
+// truncation zone of T
+__device__ __forceinline__ bool linear_zone_dev(uint64_t min_factor, uint32_t width, bool repacked, int type_size,
+                                                int is_signed) {
+	if (!repacked || width >= 64) {
+		return false;
+	}
+	const uint64_t lo = min_factor == ~0ull ? 0 : min_factor;
+	const uint64_t range = (1ull << width) - 1;
+	const uint64_t hi = lo + range;
+	if (hi < lo) {
+		return false;
+	}
+	const uint64_t e_lo = extend_runtime(lo, type_size, is_signed), e_hi = extend_runtime(hi, type_size, is_signed);
+	if (e_hi - e_lo != range) {
+		return false;
+	}
+	return is_signed ? (int64_t)e_lo <= (int64_t)e_hi : e_lo <= e_hi;
+}
+
+// Work decomposition without any table: job j = (segment seg_b + j / kScanParts, chunk index j % kScanParts).
+// A segment has at most kScanParts chunks (16 KiB stages vs <= 256 KiB segments); jobs whose chunk does not
+// exist cost one descriptor read by one producer lane.  The launch uses an odd grid so that every CTA's strided
+// job sequence cycles through all chunk indices (even load).
+__device__ __forceinline__ uint32_t job_segment(const ScanSumArgs &a, uint32_t job) {
+	return a.seg_b + job / kScanParts;
+}
+
+__device__ __forceinline__ ResolvedChunk resolve_chunk(const ScanSumArgs &a, uint32_t job, const DescQ &dq) {
 	ResolvedChunk r;
-	Job j = jobs[job_idx];
-	const uint32_t fast = j.k & kJobFastBit;
-	j.k &= ~kJobFastBit;
-	const SegDesc *dp = a.desc + j.seg;
-	const uint32_t w = dp->width;
-	const uint32_t count = dp->count;
-	const uint64_t mn = dp->min_factor;
-	const bool repacked = dp->state & kSegRepacked;
+	const uint32_t k = job % kScanParts;
+	const uint64_t row_start = dq.row_start();
+	const uint64_t packed_ptr = dq.packed_ptr();
+	const uint64_t mn = dq.min_factor();
+	const uint32_t count = dq.count();
+	const uint32_t w = dq.width();
+	const bool repacked = dq.state() & kSegRepacked;
 	const uint32_t gran = scan_chunk_values(w);
-	const uint32_t first = j.k * gran;
+	const uint32_t first = k * gran;
+	r.bytes = 0;
+	r.src16 = 0;
+	if (first >= count) {
+		return r;
+	}
 	const uint32_t cnt = min(gran, count - first);
-	const uint64_t src = repacked ? dp->packed_ptr + (((uint64_t)first * w) >> 3)
-	                              : (uint64_t)a.raw + (dp->row_start + first) * (uint64_t)a.type_size;
+	const uint64_t src = repacked ? packed_ptr + (((uint64_t)first * w) >> 3)
+	                              : (uint64_t)a.raw + (row_start + first) * (uint64_t)a.type_size;
 	r.src16 = src & ~15ull;
 	const uint32_t byte_base = (uint32_t)(src - r.src16);
 	r.bytes = (byte_base + ((cnt * w + 7u) >> 3) + 15u) & ~15u;
 	const bool add = (mn != ~0ull) && (repacked || a.literal);  // succinct.cpp:138-140 (+ Q1 in literal mode)
+	const uint32_t fast = linear_zone_dev(mn, w, repacked, a.type_size, a.is_signed) ? 1u : 0u;
 	uint64_t ext = 0;
 	uint32_t neg = 0;
 	if (fast) {
@@ -291,7 +324,7 @@ __device__ __forceinline__ ResolvedChunk resolve_chunk(const ScanSumArgs &a, con
 	r.info.min_is_negative = neg;
 	r.info.bit_base = byte_base * 8u;
 	r.info.fast = fast;
-	r.info.pad = 0;
+	r.info.done = 0;
 	return r;
 }
 
@@ -304,9 +337,8 @@ __global__ void __launch_bounds__(kThreads, 3) scan_sum_fields_kernel(const Scan
 	const uint32_t tid = threadIdx.x;
 	const uint32_t lane = tid & 31u;
 	const uint32_t warp = tid >> 5;
-	const uint32_t j0 = a.chunk_first[a.seg_b];
-	const uint32_t n_jobs = a.chunk_first[a.seg_e] - j0;
-	const Job *jobs = a.jobs + j0;
+	const uint32_t n_units = a.seg_e - a.seg_b;
+	const uint32_t n_jobs = n_units * kScanParts;
 
 	if (tid == 0) {
 		for (int s = 0; s < kStages; s++) {
@@ -324,37 +356,58 @@ __global__ void __launch_bounds__(kThreads, 3) scan_sum_fields_kernel(const Scan
 	uint64_t n_values = 0;
 
 	if (warp == kConsumerWarps) {
-		for (uint32_t it0 = 0;; it0 += kStages) {
-			if (blockIdx.x + it0 * gridDim.x >= n_jobs) {
-				break;
+		// ---------------- producer warp: every lane resolves one job, the existing chunks are issued in order ----
+		uint32_t seq = 0;  // stage sequence number, uniform across the warp
+		const uint32_t batch = 32u * gridDim.x;
+		DescQ dq_next;
+		{
+			const uint32_t job = blockIdx.x + lane * gridDim.x;
+			if (job < n_jobs) {
+				dq_next = load_desc(a.desc + job_segment(a, job));
 			}
-			const uint32_t my_it = it0 + lane;
-			const uint32_t job = blockIdx.x + my_it * gridDim.x;
-			const bool have = lane < kStages && job < n_jobs;
+		}
+		for (uint32_t j0 = blockIdx.x; j0 < n_jobs; j0 += batch) {
+			const uint32_t job = j0 + lane * gridDim.x;
+			const DescQ dq = dq_next;
+			if (job + batch < n_jobs) {  // descriptors of the next batch: in flight while this batch is issued
+				dq_next = load_desc(a.desc + job_segment(a, job + batch));
+			}
 			ResolvedChunk r;
-			if (have) {
-				r = resolve_chunk(a, jobs, job);
+			r.bytes = 0;
+			if (job < n_jobs) {
+				r = resolve_chunk(a, job, dq);
 			}
-#pragma unroll
-			for (int s = 0; s < kStages; s++) {
-				if ((int)lane == s && have) {
-					mbar_wait(&empty_bar[s], ((my_it / kStages) & 1u) ^ 1u);
+			// publish in job order, one lane at a time: the slot's previous user (seq - kStages) has then
+			// already been issued, so the parity wait below is never more than one phase ahead
+			uint32_t todo = __ballot_sync(0xffffffffu, r.bytes != 0);
+			while (todo) {
+				const uint32_t l = (uint32_t)__ffs((int)todo) - 1u;
+				todo &= todo - 1u;
+				if (lane == l) {
+					const uint32_t s = seq % kStages;
+					mbar_wait(&empty_bar[s], ((seq / kStages) & 1u) ^ 1u);
 					infos[s] = r.info;
 					mbar_arrive_expect_tx(&full_bar[s], r.bytes);
 					tma_load_1d(stage_mem + s * kStageBytes, (const void *)r.src16, r.bytes, &full_bar[s]);
 				}
+				seq++;
 				__syncwarp();
 			}
 		}
+		if (lane == 0) {
+			const uint32_t s = seq % kStages;
+			mbar_wait(&empty_bar[s], ((seq / kStages) & 1u) ^ 1u);
+			infos[s].done = 1;
+			mbar_arrive(&full_bar[s]);
+		}
 	} else {
 		for (uint32_t it = 0;; it++) {
-			uint32_t job = blockIdx.x + it * gridDim.x;
-			if (job >= n_jobs) {
-				break;
-			}
 			const uint32_t s = it % kStages;
 			mbar_wait(&full_bar[s], (it / kStages) & 1u);
 			const ChunkInfo in = infos[s];
+			if (in.done) {
+				break;
+			}
 			const uint64_t *words = (const uint64_t *)(stage_mem + s * kStageBytes);
 			if (in.fast) {
 				WidthSwitch<1>::run(in.w, words, in.cnt, tid, acc);
@@ -399,93 +452,7 @@ __global__ void __launch_bounds__(kThreads, 3) scan_sum_fields_kernel(const Scan
 	block_reduce_agg(lo, hi, n_values, red, a.agg);
 }
 
-// ---------------------------------------------------------------------------------------------------
-// chunk table builder (single CTA): per segment ceil(count / scan_chunk_values(width)) chunks, exclusive
-// scan -> chunk_first[], then the (segment, k | fast) pairs.  Runs after every encode / uncompact epoch.
-// ---------------------------------------------------------------------------------------------------
-
-constexpr int kBuildThreads = 1024;
-
-__device__ __forceinline__ bool linear_zone_dev(const SegDesc &d, int type_size, int is_signed) {
-	if (!(d.state & kSegRepacked) || d.width >= 64) {
-		return false;
-	}
-	const uint64_t lo = d.min_factor == ~0ull ? 0 : d.min_factor;
-	const uint64_t range = (1ull << d.width) - 1;
-	const uint64_t hi = lo + range;
-	if (hi < lo) {
-		return false;
-	}
-	const uint64_t e_lo = extend_runtime(lo, type_size, is_signed), e_hi = extend_runtime(hi, type_size, is_signed);
-	if (e_hi - e_lo != range) {
-		return false;
-	}
-	return is_signed ? (int64_t)e_lo <= (int64_t)e_hi : e_lo <= e_hi;
-}
-
-__global__ void __launch_bounds__(kBuildThreads) build_chunks_kernel(const SegDesc *desc, uint32_t n_segs, int type_size,
-                                                                    int is_signed, Job *jobs_out,
-                                                                    uint32_t *chunk_first) {
-	__shared__ uint32_t warp_tot[kBuildThreads / 32];
-	const uint32_t tid = threadIdx.x;
-	const uint32_t lane = tid & 31u, warp = tid >> 5;
-	const uint32_t per = (n_segs + kBuildThreads - 1) / kBuildThreads;
-	const uint32_t lo = min(n_segs, tid * per), hi = min(n_segs, lo + per);
-	uint32_t mine = 0;
-	for (uint32_t g = lo; g < hi; g++) {
-		const uint32_t gran = scan_chunk_values(desc[g].width);
-		mine += (desc[g].count + gran - 1) / gran;
-	}
-	// block-wide exclusive scan: warp shuffle scan + scan of the 32 warp totals
-	uint32_t incl = mine;
-#pragma unroll
-	for (int d = 1; d < 32; d <<= 1) {
-		uint32_t v = __shfl_up_sync(0xffffffffu, incl, d);
-		if ((int)lane >= d) {
-			incl += v;
-		}
-	}
-	if (lane == 31) {
-		warp_tot[warp] = incl;
-	}
-	__syncthreads();
-	if (warp == 0) {
-		uint32_t t = warp_tot[lane];
-		uint32_t ti = t;
-#pragma unroll
-		for (int d = 1; d < 32; d <<= 1) {
-			uint32_t v = __shfl_up_sync(0xffffffffu, ti, d);
-			if ((int)lane >= d) {
-				ti += v;
-			}
-		}
-		warp_tot[lane] = ti - t;  // exclusive
-		if (lane == 31) {
-			chunk_first[n_segs] = ti;
-		}
-	}
-	__syncthreads();
-	uint32_t next = warp_tot[warp] + incl - mine;
-	for (uint32_t g = lo; g < hi; g++) {
-		const SegDesc d = desc[g];
-		const uint32_t gran = scan_chunk_values(d.width);
-		const uint32_t n = (d.count + gran - 1) / gran;
-		const uint32_t fast = linear_zone_dev(d, type_size, is_signed) ? kJobFastBit : 0u;
-		chunk_first[g] = next;
-		for (uint32_t k = 0; k < n; k++) {
-			jobs_out[next + k] = Job {g, k | fast};
-		}
-		next += n;
-	}
-}
-
 }  // namespace
-
-cudaError_t launch_build_chunks(const SegDesc *desc, uint32_t n_segs, int type_size, int is_signed, Job *jobs_out,
-                                uint32_t *chunk_first, cudaStream_t stream) {
-	build_chunks_kernel<<<1, kBuildThreads, 0, stream>>>(desc, n_segs, type_size, is_signed, jobs_out, chunk_first);
-	return cudaGetLastError();
-}
 
 cudaError_t launch_scan_sum_fields(const ScanSumArgs &args, int sm_count, cudaStream_t stream) {
 	static bool configured[64] = {};
@@ -502,7 +469,8 @@ cudaError_t launch_scan_sum_fields(const ScanSumArgs &args, int sm_count, cudaSt
 	if (args.seg_b >= args.seg_e) {
 		return cudaSuccess;
 	}
-	const uint32_t grid = (uint32_t)sm_count * 3u;  // persistent; CTAs beyond the chunk count exit at once
+	// persistent CTAs; an odd grid makes every CTA's strided job sequence cycle through all 16 chunk indices
+	const uint32_t grid = ((uint32_t)sm_count * 3u - 1u) | 1u;  // odd and <= the resident capacity
 	scan_sum_fields_kernel<<<grid, kThreads, smem, stream>>>(args);
 	return cudaGetLastError();
 }

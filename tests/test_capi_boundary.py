@@ -73,3 +73,14 @@ def test_segment_layout_helpers():
     c = adacom.row_group_segment_counts(200000, np.uint32)
     assert list(c) == [65534, 57346, 65534, 11586]
     assert adacom.segment_capacity(np.int8) == 262136
+
+
+def test_a_segment_never_has_more_than_16_scan_chunks():
+    """kScanParts (csrc/adacom_device.cuh): the table-free scan kernels enumerate <= 16 chunks per segment."""
+    worst = 0
+    for size in (1, 2, 4, 8):
+        cap = 262136 // size
+        for w in range(1, 8 * size + 1):
+            gran = 128 * (1024 // w)
+            worst = max(worst, -(-cap // gran))
+    assert worst == 16
