@@ -179,7 +179,7 @@ adacom_status build_tiles(adacom_column *col) {
 		}
 	}
 	col->tile_first[col->n_segs] = (uint32_t)jobs.size();
-	CK(ctx, cudaMalloc((void **)&col->d_tiles, (jobs.size() + 1) * sizeof(Job)));
+	CK(ctx, cudaMallocAsync((void **)&col->d_tiles, (jobs.size() + 1) * sizeof(Job), ctx->stream));
 	if (!jobs.empty()) {
 		// pageable source: staged before the call returns
 		CK(ctx, cudaMemcpyAsync(col->d_tiles, jobs.data(), jobs.size() * sizeof(Job), cudaMemcpyHostToDevice, ctx->stream));
@@ -218,7 +218,7 @@ void fill_meta(const adacom_column *col, uint64_t g, adacom_segment_meta *m) {
 
 adacom_status ensure_raw(adacom_column *col) {
 	if (!col->raw) {
-		CK(col->ctx, cudaMalloc((void **)&col->raw, col->n_values * col->t.size + kArenaPad));
+		CK(col->ctx, cudaMallocAsync((void **)&col->raw, col->n_values * col->t.size + kArenaPad, col->ctx->stream));
 	}
 	return ADACOM_OK;
 }
@@ -440,25 +440,33 @@ extern "C" adacom_status adacom_column_create(adacom_ctx *ctx, adacom_ptype type
 		row += seg_counts[g];
 	}
 	col->n_values = row;
-	cudaError_t e = cudaMalloc((void **)&col->raw, row * col->t.size + kArenaPad);
+	cudaError_t e = cudaMallocAsync((void **)&col->raw, row * col->t.size + kArenaPad, ctx->stream);
 	if (e == cudaSuccess) {
-		e = cudaMalloc((void **)&col->d_desc, std::max<uint64_t>(n_segments, 1) * sizeof(SegDesc));
+		e = cudaMallocAsync((void **)&col->d_desc, std::max<uint64_t>(n_segments, 1) * sizeof(SegDesc), ctx->stream);
 	}
 	if (e == cudaSuccess && n_segments) {
 		e = cudaMemcpyAsync(col->d_desc, col->h_desc.data(), n_segments * sizeof(SegDesc), cudaMemcpyHostToDevice,
 		                    ctx->stream);
 	}
 	if (e != cudaSuccess) {
-		cudaFree(col->raw);
-		cudaFree(col->d_desc);
+		if (col->raw) {
+			cudaFreeAsync(col->raw, ctx->stream);
+		}
+		if (col->d_desc) {
+			cudaFreeAsync(col->d_desc, ctx->stream);
+		}
 		delete col;
 		return fail(ctx, e == cudaErrorMemoryAllocation ? ADACOM_ERR_NOMEM : ADACOM_ERR_CUDA,
 		            std::string("adacom_column_create: ") + cudaGetErrorString(e));
 	}
 	st = build_tiles(col);
 	if (st != ADACOM_OK) {
-		cudaFree(col->raw);
-		cudaFree(col->d_desc);
+		if (col->raw) {
+			cudaFreeAsync(col->raw, ctx->stream);
+		}
+		if (col->d_desc) {
+			cudaFreeAsync(col->d_desc, ctx->stream);
+		}
 		delete col;
 		return st;
 	}
@@ -485,10 +493,13 @@ extern "C" void adacom_column_destroy(adacom_column *col) {
 		}
 	}
 
+	// stream-ordered frees: no device-wide synchronisation (other contexts keep their copies in flight)
+	for (void *p : {(void *)col->raw, (void *)col->d_desc, (void *)col->d_tiles}) {
+		if (p) {
+			cudaFreeAsync(p, ctx->stream);
+		}
+	}
 	cudaStreamSynchronize(ctx->stream);
-	cudaFree(col->raw);
-	cudaFree(col->d_desc);
-	cudaFree(col->d_tiles);
 	delete col;
 }
 
@@ -543,7 +554,7 @@ extern "C" adacom_status adacom_column_release_raw(adacom_column *col) {
 		}
 	}
 	CK(ctx, cudaStreamSynchronize(ctx->stream));
-	CK(ctx, cudaFree(col->raw));
+	CK(ctx, cudaFreeAsync(col->raw, ctx->stream));
 	col->raw = nullptr;
 	return ADACOM_OK;
 }
@@ -568,7 +579,7 @@ extern "C" adacom_status adacom_column_from_packed(adacom_ctx *ctx, adacom_ptype
 	ext.seg_end = n_segments;
 	cudaError_t e = cudaMallocAsync((void **)&ext.base, total_words * 8 + kArenaPad, ctx->stream);
 	if (e == cudaSuccess) {
-		e = cudaMalloc((void **)&col->d_desc, std::max<uint64_t>(n_segments, 1) * sizeof(SegDesc));
+		e = cudaMallocAsync((void **)&col->d_desc, std::max<uint64_t>(n_segments, 1) * sizeof(SegDesc), ctx->stream);
 	}
 	if (e != cudaSuccess) {
 		delete col;
@@ -582,20 +593,20 @@ extern "C" adacom_status adacom_column_from_packed(adacom_ctx *ctx, adacom_ptype
 		bool repacked = m.state & ADACOM_SEG_REPACKED;
 		if (m.count && !repacked) {
 			cudaFreeAsync(ext.base, ctx->stream);
-			cudaFree(col->d_desc);
+			cudaFreeAsync(col->d_desc, ctx->stream);
 			delete col;
 			return fail(ctx, ADACOM_ERR_INVALID, "adacom_column_from_packed: segment is not repacked (no packed image)");
 		}
 		if (repacked && (m.word_offset % kSegAlignWords != 0 ||
 		                 m.word_offset + (((uint64_t)m.count * m.width + 63) >> 6) > total_words)) {
 			cudaFreeAsync(ext.base, ctx->stream);
-			cudaFree(col->d_desc);
+			cudaFreeAsync(col->d_desc, ctx->stream);
 			delete col;
 			return fail(ctx, ADACOM_ERR_INVALID, "adacom_column_from_packed: bad word_offset");
 		}
 		if (m.count * (uint64_t)col->t.size > kBlockSize || (uint64_t)m.capacity * col->t.size > kBlockSize) {
 			cudaFreeAsync(ext.base, ctx->stream);
-			cudaFree(col->d_desc);
+			cudaFreeAsync(col->d_desc, ctx->stream);
 			delete col;
 			return fail(ctx, ADACOM_ERR_INVALID, "adacom_column_from_packed: segment exceeds one block");
 		}
