@@ -6,8 +6,10 @@ Importing it does not need a GPU; creating a `Context` does, and fails loudly wi
 """
 from . import _capi  # noqa: F401
 from .codec import (BLOCK_SIZE, ROW_GROUP_SIZE, VECTOR_SIZE, AdacomError, AggResult, Column, Context,  # noqa: F401
-                    row_group_segment_counts, segment_capacity)
+                    row_group_segment_counts, scan_columns, segment_capacity)
+from . import tpch  # noqa: F401
 from ._capi import (CMP_EQ, CMP_GE, CMP_GT, CMP_LE, CMP_LT, CMP_NE, LITERAL, PADDED, SEG_COMPACTED,  # noqa: F401
                     SEG_REPACKED, SEG_ANALYZED, SEG_UNCOMPRESSED, ZERO_EXT_MINMAX)
 
-__all__ = ["Context", "Column", "AdacomError", "AggResult", "row_group_segment_counts", "segment_capacity"]
+__all__ = ["Context", "Column", "AdacomError", "AggResult", "row_group_segment_counts", "segment_capacity", "scan_columns",
+           "tpch"]

@@ -33,7 +33,16 @@ class Agg(C.Structure):
     _fields_ = [("sum_lo", C.c_uint64), ("sum_hi", C.c_uint64), ("count", C.c_uint64), ("reserved", C.c_uint64)]
 
 
-assert C.sizeof(SegmentMeta) == 64 and C.sizeof(Agg) == 32
+class ScanTerm(C.Structure):
+    _fields_ = [("col", C.c_void_p), ("has_predicate", C.c_int32), ("reserved", C.c_int32), ("lo", C.c_int64),
+                ("hi", C.c_int64)]
+
+
+class SumExpr(C.Structure):
+    _fields_ = [("n_factors", C.c_uint32), ("term", C.c_uint32 * 3), ("add", C.c_int64 * 3), ("mul", C.c_int64 * 3)]
+
+
+assert C.sizeof(SegmentMeta) == 64 and C.sizeof(Agg) == 32 and C.sizeof(ScanTerm) == 32 and C.sizeof(SumExpr) == 64
 
 _vp, _u64, _u32, _i = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int
 _PROTOTYPES = {
@@ -75,6 +84,8 @@ _PROTOTYPES = {
     "adacom_scan_sum_async": (_i, [_vp, _u64, _u64, _i, _vp]),
     "adacom_scan_filter": (_i, [_vp, _u64, _u64, _i, _i, C.c_int64, C.POINTER(Agg), _vp]),
     "adacom_point_filter_batch": (_i, [_vp, _u64, _vp, _vp, _i, _vp, _vp]),
+    "adacom_scan_columns": (_i, [_vp, _vp, _u32, _vp, _u32, _u64, _u64, _i, _vp, _vp, _vp]),
+    "adacom_scan_columns_async": (_i, [_vp, _vp, _u32, _vp, _u32, _u64, _u64, _i, _vp, _vp, _vp]),
     "adacom_fetch_rows": (_i, [_vp, _u64, _vp, _vp, _i, _vp, _i]),
     "adacom_compress_host": (_i, [_vp, _i, _vp, _u64, _vp, _u32, _i, _vp, _vp, _u64, C.POINTER(_u64), C.POINTER(_vp)]),
 }

@@ -181,6 +181,45 @@ class Context:
         return Column(self, h, dt), metas, int(total.value)
 
 
+def _wrap_i64(v: int) -> int:
+    v = int(v)
+    return v - (1 << 64) if v >= 1 << 63 else v
+
+
+def scan_columns(ctx: "Context", terms, sums, row_begin: int = 0, row_end: int | None = None, flags: int = 0,
+                 bitmap_in: int | None = None, bitmap_out: int | None = None, device_out: int | None = None):
+    """Fused multi-column scan (adacom_scan_columns).
+
+    terms: list of (Column, None) or (Column, (lo, hi)) -- inclusive range predicate on the decoded value;
+    sums:  list of lists of (term_index, add, mul): SUM over the selected rows of prod (add + mul * value);
+           an empty list is COUNT(*).
+    Returns one AggResult per sum (None when device_out is given: asynchronous, results stay on the device)."""
+    from ._capi import ScanTerm, SumExpr
+    n_t, n_s = len(terms), len(sums)
+    t_arr = (ScanTerm * max(n_t, 1))()
+    for i, (col, pred) in enumerate(terms):
+        t_arr[i].col = col.h.value if hasattr(col.h, "value") else col.h
+        t_arr[i].has_predicate = 0 if pred is None else 1
+        if pred is not None:
+            t_arr[i].lo, t_arr[i].hi = _wrap_i64(pred[0]), _wrap_i64(pred[1])
+    s_arr = (SumExpr * max(n_s, 1))()
+    for g, factors in enumerate(sums):
+        s_arr[g].n_factors = len(factors)
+        for k, (ti, add, mul) in enumerate(factors):
+            s_arr[g].term[k], s_arr[g].add[k], s_arr[g].mul[k] = ti, _wrap_i64(add), _wrap_i64(mul)
+    if row_end is None:
+        row_end = terms[0][0].n_values
+    b_in = C.c_void_p(bitmap_in) if bitmap_in else None
+    b_out = C.c_void_p(bitmap_out) if bitmap_out else None
+    if device_out is not None:
+        ctx.check(ctx.lib.adacom_scan_columns_async(ctx.h, t_arr, n_t, s_arr, n_s, row_begin, row_end, flags, b_in,
+                                                    b_out, C.c_void_p(device_out)))
+        return None
+    out = (Agg * max(n_s, 1))()
+    ctx.check(ctx.lib.adacom_scan_columns(ctx.h, t_arr, n_t, s_arr, n_s, row_begin, row_end, flags, b_in, b_out, out))
+    return [_agg_to_py(out[g], True) for g in range(n_s)]
+
+
 class Column:
     def __init__(self, ctx: Context, handle, dtype: np.dtype):
         self.ctx, self.h, self.dtype = ctx, handle, dtype

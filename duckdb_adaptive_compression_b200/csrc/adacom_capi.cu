@@ -37,6 +37,8 @@ struct adacom_ctx {
 	Agg *d_agg = nullptr;
 	unsigned long long *d_totals = nullptr;  // device alias of h_totals (host-mapped)
 	unsigned long long ticket = 0;           // sequence number of the last layout launch
+	Agg *d_aggs = nullptr;                // adacom_scan_columns: kQueryMaxAggs aggregates (lazily allocated)
+	Agg *h_aggs = nullptr;                // pinned
 	Agg *h_agg = nullptr;                 // pinned
 	unsigned long long *h_totals = nullptr;  // pinned
 };
@@ -65,6 +67,9 @@ struct adacom_column {
 	// so it is built once; the tiles of the segments [b, e) are d_tiles[tile_first[b] .. tile_first[e])
 	Job *d_tiles = nullptr;
 	std::vector<uint32_t> tile_first;
+	// segment holding row 2048*v (static, like the tile table): entry point of the multi-column row-block scans
+	uint32_t *d_vec_seg = nullptr;
+	std::vector<uint32_t> vec_seg;
 	uint64_t epoch = 0;
 };
 
@@ -179,6 +184,23 @@ adacom_status build_tiles(adacom_column *col) {
 		}
 	}
 	col->tile_first[col->n_segs] = (uint32_t)jobs.size();
+	{
+		const uint64_t n_vec = (col->n_values + kVectorSize - 1) / kVectorSize;
+		col->vec_seg.assign(n_vec + 1, 0);
+		uint64_t g = 0;
+		for (uint64_t v = 0; v < n_vec; v++) {
+			const uint64_t row = v * kVectorSize;
+			while (g + 1 < col->n_segs && row >= col->h_desc[g].row_start + col->h_desc[g].count) {
+				g++;
+			}
+			col->vec_seg[v] = (uint32_t)g;
+		}
+		CK(ctx, cudaMallocAsync((void **)&col->d_vec_seg, (n_vec + 1) * sizeof(uint32_t), ctx->stream));
+		if (n_vec) {
+			CK(ctx, cudaMemcpyAsync(col->d_vec_seg, col->vec_seg.data(), n_vec * sizeof(uint32_t), cudaMemcpyHostToDevice,
+			                        ctx->stream));
+		}
+	}
 	CK(ctx, cudaMallocAsync((void **)&col->d_tiles, (jobs.size() + 1) * sizeof(Job), ctx->stream));
 	if (!jobs.empty()) {
 		// pageable source: staged before the call returns
@@ -292,6 +314,8 @@ extern "C" void adacom_ctx_destroy(adacom_ctx *ctx) {
 	cudaStreamSynchronize(ctx->stream);
 	cudaFree(ctx->flush_buf);
 	cudaFree(ctx->d_agg);
+	cudaFree(ctx->d_aggs);
+	cudaFreeHost(ctx->h_aggs);
 	cudaFreeHost(ctx->h_agg);
 	cudaFreeHost(ctx->h_totals);
 	cudaStreamDestroy(ctx->stream);
@@ -494,7 +518,7 @@ extern "C" void adacom_column_destroy(adacom_column *col) {
 	}
 
 	// stream-ordered frees: no device-wide synchronisation (other contexts keep their copies in flight)
-	for (void *p : {(void *)col->raw, (void *)col->d_desc, (void *)col->d_tiles}) {
+	for (void *p : {(void *)col->raw, (void *)col->d_desc, (void *)col->d_tiles, (void *)col->d_vec_seg}) {
 		if (p) {
 			cudaFreeAsync(p, ctx->stream);
 		}
@@ -1098,6 +1122,158 @@ extern "C" adacom_status adacom_point_filter_batch(adacom_column *col, uint64_t 
 	CK(ctx, cudaFreeAsync(d_count, ctx->stream));
 	CK(ctx, cudaFreeAsync(d_first, ctx->stream));
 	CK(ctx, cudaStreamSynchronize(ctx->stream));
+	return ADACOM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// fused multi-column scan
+// ---------------------------------------------------------------------------------------------------
+
+static adacom_status plan_scan_columns(adacom_ctx *ctx, const adacom_scan_term *terms, uint32_t n_terms,
+                                       const adacom_sum_expr *sums, uint32_t n_sums, uint64_t row_begin, uint64_t row_end,
+                                       int flags, QueryArgs &q) {
+	if (!terms || n_terms == 0 || n_terms > (uint32_t)kQueryMaxCols || !sums || n_sums == 0 ||
+	    n_sums > (uint32_t)kQueryMaxAggs || row_begin > row_end || (row_begin % kVectorSize) != 0) {
+		return fail(ctx, ADACOM_ERR_INVALID,
+		            "adacom_scan_columns: 1..8 terms, 1..8 sums, row_begin a multiple of 2048 and <= row_end");
+	}
+	uint64_t width_bits = 0;
+	for (uint32_t c = 0; c < n_terms; c++) {
+		adacom_column *col = terms[c].col;
+		if (!col || col->ctx != ctx || row_end > col->n_values) {
+			return fail(ctx, ADACOM_ERR_INVALID, "adacom_scan_columns: column missing, of another context, or too short");
+		}
+		adacom_status st = sync_mirror(col);  // query planning reads the live widths
+		if (st != ADACOM_OK) {
+			return st;
+		}
+		uint32_t wmax = 1;
+		for (const SegDesc &d : col->h_desc) {
+			if (!(d.state & kSegRepacked) && d.count && !col->raw) {
+				return fail(ctx, ADACOM_ERR_STATE, "adacom_scan_columns: the raw arena was released");
+			}
+			wmax = std::max<uint32_t>(wmax, d.width);
+		}
+		width_bits += wmax;
+		QueryCol &qc = q.cols[c];
+		qc.desc = col->d_desc;
+		qc.vec_seg = col->d_vec_seg;
+		qc.raw = col->raw;
+		qc.n_segs = (uint32_t)col->n_segs;
+		qc.type_size = (uint32_t)col->t.size;
+		qc.is_signed = col->t.is_signed ? 1u : 0u;
+		qc.has_pred = terms[c].has_predicate ? 1u : 0u;
+		qc.lo = terms[c].lo;
+		qc.hi = terms[c].hi;
+	}
+	for (uint32_t g = 0; g < n_sums; g++) {
+		if (sums[g].n_factors > (uint32_t)kQueryMaxFactors) {
+			return fail(ctx, ADACOM_ERR_INVALID, "adacom_scan_columns: at most 3 factors per sum");
+		}
+		QueryAgg &qa = q.aggs[g];
+		qa.n_factors = sums[g].n_factors;
+		for (uint32_t k = 0; k < sums[g].n_factors; k++) {
+			if (sums[g].term[k] >= n_terms) {
+				return fail(ctx, ADACOM_ERR_INVALID, "adacom_scan_columns: factor refers to a missing term");
+			}
+			qa.col[k] = sums[g].term[k];
+			qa.add[k] = sums[g].add[k];
+			qa.mul[k] = sums[g].mul[k];
+		}
+	}
+	// row-block size and pipeline depth: the largest block whose worst-case staged bytes leave room for two
+	// CTAs per SM (shrunk while the table offers fewer than ~4 blocks per SM)
+	const uint64_t n_rows = row_end - row_begin;
+	auto stage_bytes = [&](uint32_t R) -> uint64_t {
+		return ((uint64_t)R * width_bits / 8 + (uint64_t)n_terms * kQueryMaxPieces * 32 + 64 + 127) & ~127ull;
+	};
+	uint32_t R = 0, stages = 0;
+	for (uint32_t r : {8192u, 4096u, 2048u}) {
+		for (uint32_t st : {3u, 2u}) {
+			if (!R && st * stage_bytes(r) <= 100u * 1024u) {
+				R = r;
+				stages = st;
+			}
+		}
+	}
+	if (!R && 2 * stage_bytes(2048) <= 200u * 1024u) {
+		R = 2048;
+		stages = 2;
+	}
+	if (!R) {
+		return fail(ctx, ADACOM_ERR_UNSUPPORTED, "adacom_scan_columns: the referenced columns are too wide to stage together");
+	}
+	while (R > 2048 && n_rows / R < 4ull * (uint64_t)ctx->sm_count) {
+		R /= 2;
+	}
+	// a row block may touch at most kQueryMaxPieces consecutive segments of a column
+	for (uint32_t c = 0; c < n_terms; c++) {
+		const adacom_column *col = terms[c].col;
+		for (uint64_t r0 = row_begin; r0 < row_end; r0 += R) {
+			const uint64_t last = std::min<uint64_t>(r0 + R, row_end) - 1;
+			uint64_t g = col->vec_seg[last / kVectorSize];
+			while (g + 1 < col->n_segs && last >= col->h_desc[g].row_start + col->h_desc[g].count) {
+				g++;
+			}
+			if (g - col->vec_seg[r0 / kVectorSize] + 1 > (uint64_t)kQueryMaxPieces) {
+				return fail(ctx, ADACOM_ERR_UNSUPPORTED,
+				            "adacom_scan_columns: a row block spans more than 3 segments of one column");
+			}
+		}
+	}
+	q.n_cols = n_terms;
+	q.n_aggs = n_sums;
+	q.row_begin = row_begin;
+	q.row_end = row_end;
+	q.block_rows = R;
+	q.stages = stages;
+	q.stage_bytes = (uint32_t)stage_bytes(R);
+	q.literal = (flags & ADACOM_LITERAL) ? 1 : 0;
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_scan_columns_async(adacom_ctx *ctx, const adacom_scan_term *terms, uint32_t n_terms,
+                                                   const adacom_sum_expr *sums, uint32_t n_sums, uint64_t row_begin,
+                                                   uint64_t row_end, int flags, const uint64_t *device_bitmap_in,
+                                                   uint64_t *device_bitmap_out, adacom_agg *device_out) {
+	if (!ctx || !device_out) {
+		return fail(ctx, ADACOM_ERR_INVALID, "adacom_scan_columns_async: NULL argument");
+	}
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	QueryArgs q;
+	adacom_status st = plan_scan_columns(ctx, terms, n_terms, sums, n_sums, row_begin, row_end, flags, q);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	q.in_bitmap = (const uint32_t *)device_bitmap_in;
+	q.out_bitmap = (uint32_t *)device_bitmap_out;
+	q.out = (Agg *)device_out;
+	CK(ctx, cudaMemsetAsync(device_out, 0, n_sums * sizeof(Agg), ctx->stream));
+	LAUNCH(ctx, launch_scan_columns(q, ctx->sm_count, ctx->stream));
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_scan_columns(adacom_ctx *ctx, const adacom_scan_term *terms, uint32_t n_terms,
+                                             const adacom_sum_expr *sums, uint32_t n_sums, uint64_t row_begin,
+                                             uint64_t row_end, int flags, const uint64_t *device_bitmap_in,
+                                             uint64_t *device_bitmap_out, adacom_agg *out) {
+	if (!ctx || !out || n_sums > (uint32_t)kQueryMaxAggs) {
+		return fail(ctx, ADACOM_ERR_INVALID, "adacom_scan_columns: NULL argument");
+	}
+	if (!ctx->d_aggs) {
+		std::lock_guard<std::mutex> lock(ctx->mu);
+		CK(ctx, cudaMalloc((void **)&ctx->d_aggs, kQueryMaxAggs * sizeof(Agg)));
+		CK(ctx, cudaHostAlloc((void **)&ctx->h_aggs, kQueryMaxAggs * sizeof(Agg), cudaHostAllocDefault));
+	}
+	adacom_status st = adacom_scan_columns_async(ctx, terms, n_terms, sums, n_sums, row_begin, row_end, flags,
+	                                             device_bitmap_in, device_bitmap_out, (adacom_agg *)ctx->d_aggs);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	CK(ctx, cudaMemcpyAsync(ctx->h_aggs, ctx->d_aggs, n_sums * sizeof(Agg), cudaMemcpyDeviceToHost, ctx->stream));
+	CK(ctx, cudaStreamSynchronize(ctx->stream));
+	memcpy(out, ctx->h_aggs, n_sums * sizeof(Agg));
 	return ADACOM_OK;
 }
 

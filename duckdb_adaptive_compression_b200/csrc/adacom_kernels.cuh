@@ -57,6 +57,46 @@ struct ScanSumArgs {
 
 cudaError_t launch_scan_sum_fields(const ScanSumArgs &args, int sm_count, cudaStream_t stream);
 
+// ---- fused multi-column scan (conjunctive range filters + SUM of affine products), kernels_query.cu ----
+constexpr int kQueryMaxCols = 8;
+constexpr int kQueryMaxPieces = 3;   // segments of one column a row block may touch
+constexpr int kQueryMaxAggs = 8;
+constexpr int kQueryMaxFactors = 3;
+
+struct QueryCol {
+	const SegDesc *desc = nullptr;
+	const uint32_t *vec_seg = nullptr;  // segment holding row 2048*v of the column, v = 0 .. ceil(rows / 2048)
+	const uint8_t *raw = nullptr;
+	uint32_t n_segs = 0;
+	uint32_t type_size = 8;
+	uint32_t is_signed = 1;
+	uint32_t has_pred = 0;
+	int64_t lo = 0, hi = 0;             // inclusive range on the decoded T value (compared as T)
+};
+
+struct QueryAgg {  // sum over the selected rows of prod_k (add[k] + mul[k] * value(col[k])); 0 factors = COUNT(*)
+	uint32_t n_factors = 0;
+	uint32_t col[kQueryMaxFactors] = {0, 0, 0};
+	int64_t add[kQueryMaxFactors] = {0, 0, 0};
+	int64_t mul[kQueryMaxFactors] = {0, 0, 0};
+};
+
+struct QueryArgs {
+	QueryCol cols[kQueryMaxCols];
+	QueryAgg aggs[kQueryMaxAggs];
+	uint32_t n_cols = 0, n_aggs = 0;
+	uint64_t row_begin = 0, row_end = 0;  // table rows; row_begin is a multiple of 2048
+	uint32_t block_rows = 2048;           // 2048 | 4096 | 8192
+	uint32_t stages = 2;
+	uint32_t stage_bytes = 0;             // multiple of 128: worst-case staged bytes of one row block
+	int literal = 0;
+	const uint32_t *in_bitmap = nullptr;  // optional selection (bit r - row_begin), AND-ed
+	uint32_t *out_bitmap = nullptr;       // optional: the resulting selection
+	Agg *out = nullptr;                   // n_aggs aggregates (zeroed by the caller); count = selected rows
+};
+
+cudaError_t launch_scan_columns(const QueryArgs &args, int sm_count, cudaStream_t stream);
+
 // scan_vector / scan_partial of one segment, arbitrary start (generic unaligned path, no staging)
 cudaError_t launch_scan_range(TypeInfo t, const SegDesc *desc, uint32_t seg, const uint8_t *raw, uint64_t start,
                               uint64_t scan_count, int literal, void *result, uint64_t result_offset,

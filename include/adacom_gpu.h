@@ -217,6 +217,39 @@ adacom_status adacom_point_filter_batch(adacom_column *col, uint64_t n_queries, 
                                         const int64_t *constants, int flags, uint64_t *out_count,
                                         uint64_t *out_first_row);
 
+/* ---- fused multi-column scan --------------------------------------------------------------------------- */
+/* What DuckDB runs above the codec for a filter + aggregate query (RowGroup::TemplatedScan,
+ * src/storage/table/row_group.cpp:391-447: scan every referenced column vector by vector, refine the selection
+ * filter by filter -- ColumnSegment::FilterSelection, column_segment.cpp:575-658, AND conjunctions :685-844 --
+ * then aggregate the survivors), as ONE pass over the packed columns.  All columns hold the same table rows
+ * (their segment boundaries differ: capacities are 262136/S values).
+ *   selection = AND over the terms with has_predicate of (lo <= value <= hi), compared as the column's type T
+ *               (>=, >, <=, <, = on integers are all inclusive ranges), AND the optional input bitmap;
+ *   out[g]    = {SUM over the selected rows of prod_k (add[k] + mul[k] * value(term[k])) mod 2^128, COUNT}.
+ * TPC-H Q6 = terms {shipdate in [a, b-1], discount in [5, 7], quantity <= 23, extendedprice} and one sum
+ * {extendedprice * discount}.  Bitmaps: 1 bit per row, bit (row - row_begin), device pointers, row_begin a
+ * multiple of 2048.  ADACOM_ERR_UNSUPPORTED when a block of rows would span more than 3 segments of a column. */
+typedef struct {
+	adacom_column *col;
+	int32_t has_predicate; /* 0: the column is only read by the sums */
+	int32_t reserved;
+	int64_t lo, hi;        /* inclusive; for unsigned T the bit patterns are compared unsigned */
+} adacom_scan_term;
+typedef struct {
+	uint32_t n_factors;    /* 0..3; 0 = COUNT(*) (sum of 1) */
+	uint32_t term[3];      /* index into terms[] */
+	int64_t add[3];
+	int64_t mul[3];
+} adacom_sum_expr;
+adacom_status adacom_scan_columns(adacom_ctx *ctx, const adacom_scan_term *terms, uint32_t n_terms,
+                                  const adacom_sum_expr *sums, uint32_t n_sums, uint64_t row_begin, uint64_t row_end,
+                                  int flags, const uint64_t *device_bitmap_in, uint64_t *device_bitmap_out,
+                                  adacom_agg *out);
+/* same, asynchronous: n_sums aggregates are left in device memory */
+adacom_status adacom_scan_columns_async(adacom_ctx *ctx, const adacom_scan_term *terms, uint32_t n_terms,
+                                        const adacom_sum_expr *sums, uint32_t n_sums, uint64_t row_begin,
+                                        uint64_t row_end, int flags, const uint64_t *device_bitmap_in,
+                                        uint64_t *device_bitmap_out, adacom_agg *device_out);
 /* ---- fetch_row ------------------------------------------------------------------------------------------ */
 /* batched random access: out[q] = T(vec(seg_idx[q])[row_in_seg[q]] + min).  Host pointers unless
  * on_device (then all three are device pointers). */
