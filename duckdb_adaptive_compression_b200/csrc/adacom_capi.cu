@@ -70,6 +70,9 @@ struct adacom_column {
 	// segment holding row 2048*v (static, like the tile table): entry point of the multi-column row-block scans
 	uint32_t *d_vec_seg = nullptr;
 	std::vector<uint32_t> vec_seg;
+	uint32_t max_span[3] = {0, 0, 0};  // most segments any aligned block of 2048 / 4096 / 8192 rows touches (static)
+	uint32_t wmax = 0;                 // widest live payload, refreshed with the host mirror
+	bool any_raw = false;              // some non-empty segment still lives in the raw arena (mirror)
 	uint64_t epoch = 0;
 };
 
@@ -167,9 +170,25 @@ adacom_status sync_mirror(adacom_column *col) {
 		                        ctx->stream));
 		CK(ctx, cudaStreamSynchronize(ctx->stream));
 		col->mirror_dirty = false;
+		col->wmax = 0;
 		return gc_extents(col);
 	}
 	return ADACOM_OK;
+}
+
+// widest live payload / raw residency of the column, cached per mirror refresh (query planning)
+void refresh_widths(adacom_column *col) {
+	if (col->wmax) {
+		return;
+	}
+	uint32_t wmax = 1;
+	bool any_raw = false;
+	for (const SegDesc &d : col->h_desc) {
+		wmax = std::max<uint32_t>(wmax, d.width);
+		any_raw = any_raw || (d.count && !(d.state & kSegRepacked));
+	}
+	col->wmax = wmax;
+	col->any_raw = any_raw;
 }
 
 adacom_status build_tiles(adacom_column *col) {
@@ -194,6 +213,20 @@ adacom_status build_tiles(adacom_column *col) {
 				g++;
 			}
 			col->vec_seg[v] = (uint32_t)g;
+		}
+		for (int ri = 0; ri < 3; ri++) {
+			const uint64_t R = (uint64_t)kVectorSize << ri;
+			uint32_t worst = 0;
+			uint64_t gl = 0;
+			for (uint64_t r0 = 0; r0 < col->n_values; r0 += R) {
+				const uint64_t last = std::min<uint64_t>(r0 + R, col->n_values) - 1;
+				gl = std::max<uint64_t>(gl, col->vec_seg[last / kVectorSize]);
+				while (gl + 1 < col->n_segs && last >= col->h_desc[gl].row_start + col->h_desc[gl].count) {
+					gl++;
+				}
+				worst = std::max<uint32_t>(worst, (uint32_t)(gl - col->vec_seg[r0 / kVectorSize] + 1));
+			}
+			col->max_span[ri] = worst;
 		}
 		CK(ctx, cudaMallocAsync((void **)&col->d_vec_seg, (n_vec + 1) * sizeof(uint32_t), ctx->stream));
 		if (n_vec) {
@@ -1147,14 +1180,11 @@ static adacom_status plan_scan_columns(adacom_ctx *ctx, const adacom_scan_term *
 		if (st != ADACOM_OK) {
 			return st;
 		}
-		uint32_t wmax = 1;
-		for (const SegDesc &d : col->h_desc) {
-			if (!(d.state & kSegRepacked) && d.count && !col->raw) {
-				return fail(ctx, ADACOM_ERR_STATE, "adacom_scan_columns: the raw arena was released");
-			}
-			wmax = std::max<uint32_t>(wmax, d.width);
+		refresh_widths(col);
+		if (col->any_raw && !col->raw) {
+			return fail(ctx, ADACOM_ERR_STATE, "adacom_scan_columns: the raw arena was released");
 		}
-		width_bits += wmax;
+		width_bits += col->wmax;
 		QueryCol &qc = q.cols[c];
 		qc.desc = col->d_desc;
 		qc.vec_seg = col->d_vec_seg;
@@ -1177,6 +1207,7 @@ static adacom_status plan_scan_columns(adacom_ctx *ctx, const adacom_scan_term *
 				return fail(ctx, ADACOM_ERR_INVALID, "adacom_scan_columns: factor refers to a missing term");
 			}
 			qa.col[k] = sums[g].term[k];
+			q.factor_mask |= 1u << sums[g].term[k];
 			qa.add[k] = sums[g].add[k];
 			qa.mul[k] = sums[g].mul[k];
 		}
@@ -1190,15 +1221,17 @@ static adacom_status plan_scan_columns(adacom_ctx *ctx, const adacom_scan_term *
 	uint32_t R = 0, stages = 0;
 	for (uint32_t r : {8192u, 4096u, 2048u}) {
 		for (uint32_t st : {3u, 2u}) {
-			if (!R && st * stage_bytes(r) <= 100u * 1024u) {
+			if (!R && st * stage_bytes(r) <= 48u * 1024u) {  // + ~26 KiB static: three CTAs per SM
 				R = r;
 				stages = st;
 			}
 		}
 	}
-	if (!R && 2 * stage_bytes(2048) <= 200u * 1024u) {
-		R = 2048;
-		stages = 2;
+	for (uint32_t limit : {84u * 1024u, 196u * 1024u}) {  // two CTAs per SM, then one
+		if (!R && 2 * stage_bytes(2048) <= limit) {
+			R = 2048;
+			stages = 2;
+		}
 	}
 	if (!R) {
 		return fail(ctx, ADACOM_ERR_UNSUPPORTED, "adacom_scan_columns: the referenced columns are too wide to stage together");
@@ -1207,8 +1240,12 @@ static adacom_status plan_scan_columns(adacom_ctx *ctx, const adacom_scan_term *
 		R /= 2;
 	}
 	// a row block may touch at most kQueryMaxPieces consecutive segments of a column
+	const int ri = R == 8192 ? 2 : (R == 4096 ? 1 : 0);
 	for (uint32_t c = 0; c < n_terms; c++) {
 		const adacom_column *col = terms[c].col;
+		if (row_begin % R == 0 && col->max_span[ri] <= (uint32_t)kQueryMaxPieces) {
+			continue;  // no aligned block of the whole column spans more (precomputed with the tile table)
+		}
 		for (uint64_t r0 = row_begin; r0 < row_end; r0 += R) {
 			const uint64_t last = std::min<uint64_t>(r0 + R, row_end) - 1;
 			uint64_t g = col->vec_seg[last / kVectorSize];

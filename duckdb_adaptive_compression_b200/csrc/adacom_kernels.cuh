@@ -85,6 +85,7 @@ struct QueryArgs {
 	QueryCol cols[kQueryMaxCols];
 	QueryAgg aggs[kQueryMaxAggs];
 	uint32_t n_cols = 0, n_aggs = 0;
+	uint32_t factor_mask = 0;             // columns some sum expression reads
 	uint64_t row_begin = 0, row_end = 0;  // table rows; row_begin is a multiple of 2048
 	uint32_t block_rows = 2048;           // 2048 | 4096 | 8192
 	uint32_t stages = 2;

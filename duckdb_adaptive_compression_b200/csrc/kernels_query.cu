@@ -14,9 +14,13 @@
 //   * producer warp: lane = (column, piece); resolves the pieces of the NEXT block while the current one is in
 //     flight, lays the pieces out back to back in one stage and issues one cp.async.bulk (TMA) per piece, all
 //     completing on the stage's mbarrier;
-//   * 8 consumer warps: thread = row; unpack the referenced columns straight from shared memory (funnel
-//     shift at bit_base + i*w), apply the range predicates (AND), and fold prod_k(add_k + mul_k * value_k)
-//     into 128-bit per-thread accumulators; optional selection bitmap in (AND) / out.
+//   * 8 consumer warps, column at a time like DuckDB's vectorised filters: a warp owns every 8th group of 32
+//     rows and keeps their selection words in shared memory.  Predicate columns are evaluated in the FIELD
+//     domain (the producer turns lo <= min + f <= hi into f - flo <= span per piece, so a value costs a funnel
+//     shift, a mask, a subtract and a compare; groups whose selection word is already 0 are skipped), the
+//     ballots refine the words.  Surviving rows are compacted into a per-warp list and only those rows decode
+//     the factor columns and fold prod_k(add_k + mul_k * value_k) into 128-bit per-thread accumulators.
+//     Optional selection bitmap in (AND) / out.  No barrier between the consumer warps.
 //
 // Algorithmic HBM bytes per row: sum over the columns of w_c / 8 (+ 1/8 per bitmap).
 #include "adacom_kernels.cuh"
@@ -30,13 +34,19 @@ constexpr int kQConsumers = kQConsumerWarps * 32;
 constexpr int kQThreads = kQConsumers + 32;
 constexpr int kQMaxStages = 3;
 constexpr int kQLanesPerCol = 4;  // producer lanes per column: piece 0..2, lane 3 idle
+constexpr uint32_t kQMaxBlockRows = 8192;
+constexpr uint32_t kQListCap = 256;
 
 struct QPiece {
 	uint64_t min_add;   // frame of reference to add (0 when none)
+	uint64_t flo;       // predicate in the field domain: passes iff (f - flo) <= span (unsigned); linear pieces only
+	uint64_t span;
 	uint32_t smem_off;  // byte offset of the staged range inside the stage (16-byte aligned)
 	uint32_t bit_base;  // bit position of the piece's first field inside the staged range (0..127)
 	uint32_t cnt;       // values of this piece inside the block (0: piece unused)
 	uint32_t w;
+	uint32_t linear;    // value == extend(min) + f without wrap-around for every f < 2^w
+	uint32_t pad;
 };
 
 struct QStage {
@@ -77,11 +87,57 @@ __device__ __forceinline__ uint64_t column_value(const QPiece *pc, const uint8_t
 struct PieceRes {
 	uint64_t src16;
 	uint64_t min_add;
+	uint64_t flo, span;
 	uint32_t bytes;  // 16-byte rounded staged range (0: no piece)
 	uint32_t bit_base;
 	uint32_t cnt;
 	uint32_t w;
+	uint32_t linear;
 };
+
+// [lo, hi] on T values -> [flo, flo + span] on fields for a piece whose values are extend(min) + f, f < 2^w
+// (no wrap: the piece's whole interval lies inside one sign / truncation zone of T).  An empty intersection
+// becomes flo = 2^64 - 1 (no field of width < 64 equals it).
+__device__ __forceinline__ void field_range(const QueryCol &c, uint64_t min_add, uint32_t w, uint64_t &flo, uint64_t &span) {
+	const __int128 e = c.is_signed ? (__int128)(int64_t)extend_rt(min_add, c.type_size, 1)
+	                               : (__int128)extend_rt(min_add, c.type_size, 0);
+	const __int128 lo = c.is_signed ? (__int128)c.lo : (__int128)(uint64_t)c.lo;
+	const __int128 hi = c.is_signed ? (__int128)c.hi : (__int128)(uint64_t)c.hi;
+	const __int128 fmax = (__int128)lo_set64(w);
+	__int128 a = lo - e, b = hi - e;
+	if (a < 0) {
+		a = 0;
+	}
+	if (b > fmax) {
+		b = fmax;
+	}
+	if (a > b) {
+		flo = ~0ull;
+		span = 0;
+	} else {
+		flo = (uint64_t)a;
+		span = (uint64_t)(b - a);
+	}
+}
+
+__device__ __forceinline__ bool piece_is_linear(const QueryCol &c, uint64_t min_add, uint32_t w, bool repacked) {
+	if (w >= 64) {
+		return false;
+	}
+	if (!repacked && (c.is_signed || min_add != 0)) {
+		return false;  // raw signed slots: pattern order != value order across the sign
+	}
+	const uint64_t range = (1ull << w) - 1;
+	const uint64_t top = min_add + range;
+	if (top < min_add) {
+		return false;
+	}
+	const uint64_t e_lo = extend_rt(min_add, c.type_size, c.is_signed), e_hi = extend_rt(top, c.type_size, c.is_signed);
+	if (e_hi - e_lo != range) {
+		return false;
+	}
+	return c.is_signed ? (int64_t)e_lo <= (int64_t)e_hi : e_lo <= e_hi;
+}
 
 // piece `dq` (a segment of column c) restricted to the block rows [r0, r0 + rows)
 __device__ __forceinline__ PieceRes resolve_piece(const QueryCol &c, const DescQ &dq, bool valid, uint64_t r0, uint32_t rows,
@@ -93,6 +149,9 @@ __device__ __forceinline__ PieceRes resolve_piece(const QueryCol &c, const DescQ
 	r.min_add = 0;
 	r.bit_base = 0;
 	r.w = 8u * c.type_size;
+	r.flo = ~0ull;
+	r.span = 0;
+	r.linear = 0;
 	if (!valid) {
 		return r;
 	}
@@ -117,15 +176,54 @@ __device__ __forceinline__ PieceRes resolve_piece(const QueryCol &c, const DescQ
 	r.cnt = cnt;
 	r.w = w;
 	r.min_add = (mn != ~0ull && (repacked || literal)) ? mn : 0ull;
+	if (c.has_pred && piece_is_linear(c, r.min_add, w, repacked)) {
+		r.linear = 1;
+		field_range(c, r.min_add, w, r.flo, r.span);
+	}
 	return r;
 }
 
-__global__ void __launch_bounds__(kQThreads, 2) scan_columns_kernel(const QueryArgs a) {
+// Aggregates over the rows a warp has collected: lane e takes list entries e, e + 32, ...; it decodes the
+// factor columns of its row (generic per-value path) and folds every sum expression into its accumulators.
+__device__ __forceinline__ void aggregate_list(const QueryArgs &a, const QStage &st, const uint8_t *stage,
+                                               const uint16_t *my_list, uint32_t n_list,
+                                               uint64_t (*vals)[kQConsumers], uint32_t tid, uint32_t lane,
+                                               unsigned __int128 *acc) {
+	for (uint32_t e = lane; e < n_list; e += 32u) {
+		const uint32_t i = my_list[e];
+#pragma unroll 1
+		for (uint32_t c = 0; c < a.n_cols; c++) {
+			if ((a.factor_mask >> c) & 1u) {
+				const QueryCol &qc = a.cols[c];
+				vals[c][tid] = column_value(st.piece[c], stage, i, qc.type_size, qc.is_signed);
+			}
+		}
+#pragma unroll
+		for (int g = 0; g < kQueryMaxAggs; g++) {
+			if (g < (int)a.n_aggs) {
+				const QueryAgg &qa = a.aggs[g];
+				__int128 term = 1;
+#pragma unroll
+				for (int k = 0; k < kQueryMaxFactors; k++) {
+					if (k < (int)qa.n_factors) {
+						const int64_t v = (int64_t)vals[qa.col[k]][tid];
+						term *= (__int128)qa.add[k] + (__int128)qa.mul[k] * (__int128)v;
+					}
+				}
+				acc[g] += (unsigned __int128)term;
+			}
+		}
+	}
+}
+
+__global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryArgs a) {
 	extern __shared__ __align__(128) uint8_t q_stage_mem[];
 	__shared__ __align__(8) uint64_t full_bar[kQMaxStages];
 	__shared__ __align__(8) uint64_t empty_bar[kQMaxStages];
 	__shared__ QStage stages[kQMaxStages];
 	__shared__ uint64_t vals[kQueryMaxCols][kQConsumers];  // decoded factors of the row a thread is working on
+	__shared__ uint32_t sel[kQMaxBlockRows / 32];           // selection word per 32-row group (owned by g % 8)
+	__shared__ uint16_t list[kQConsumerWarps][kQListCap];   // surviving block rows (< 8192), per warp
 	__shared__ uint64_t red[96];
 	const uint32_t tid = threadIdx.x;
 	const uint32_t lane = tid & 31u;
@@ -211,6 +309,10 @@ __global__ void __launch_bounds__(kQThreads, 2) scan_columns_kernel(const QueryA
 			if (active) {
 				QPiece q;
 				q.min_add = pr.min_add;
+				q.flo = pr.flo;
+				q.span = pr.span;
+				q.linear = pr.linear;
+				q.pad = 0;
 				q.smem_off = incl - pr.bytes;
 				q.bit_base = pr.bit_base;
 				q.cnt = pr.cnt;
@@ -235,7 +337,8 @@ __global__ void __launch_bounds__(kQThreads, 2) scan_columns_kernel(const QueryA
 			mbar_arrive(&full_bar[s]);
 		}
 	} else {
-		// ---------------- consumer warps: thread = row ----------------
+		// ---------------- consumer warps: a warp owns the 32-row groups g with g % 8 == warp ----------------
+		uint16_t *my_list = list[warp];
 		for (uint32_t it = 0;; it++) {
 			const uint32_t s = it % n_stages;
 			mbar_wait(&full_bar[s], (it / n_stages) & 1u);
@@ -245,51 +348,148 @@ __global__ void __launch_bounds__(kQThreads, 2) scan_columns_kernel(const QueryA
 			}
 			const uint8_t *stage = q_stage_mem + (size_t)s * a.stage_bytes;
 			const uint32_t rows = st.rows;
-			const uint64_t rel0 = st.row0 - a.row_begin;  // multiple of 2048
-			for (uint32_t base = 0; base < rows; base += kQConsumers) {
-				const uint32_t i = base + tid;
-				bool pass = i < rows;
+			const uint32_t n_groups = (rows + 31u) >> 5;
+			const uint64_t word0 = (st.row0 - a.row_begin) >> 5;  // bitmap word of the block's first group
+
+			// ---- selection words of my groups: rows that exist, AND the optional input bitmap ----
+			for (uint32_t g = warp + lane * kQConsumerWarps; g < n_groups; g += 32u * kQConsumerWarps) {
+				const uint32_t left = rows - g * 32u;
+				uint32_t word = left >= 32u ? 0xffffffffu : ((1u << left) - 1u);
 				if (a.in_bitmap != nullptr) {
-					const uint32_t word = __ldg(a.in_bitmap + ((rel0 + base + (tid & ~31u)) >> 5));
-					pass = pass && ((word >> lane) & 1u);
+					word &= __ldg(a.in_bitmap + word0 + g);
 				}
-#pragma unroll
-				for (int c = 0; c < kQueryMaxCols; c++) {
-					if (c < (int)a.n_cols && pass) {
-						const QueryCol &qc = a.cols[c];
-						const uint64_t v = column_value(st.piece[c], stage, i, qc.type_size, qc.is_signed);
-						if (qc.has_pred) {
-							pass = qc.is_signed ? ((int64_t)v >= qc.lo && (int64_t)v <= qc.hi)
-							                    : (v >= (uint64_t)qc.lo && v <= (uint64_t)qc.hi);
-						}
-						vals[c][tid] = v;
+				sel[g] = word;
+			}
+			__syncwarp();
+
+			// ---- predicate columns, one after the other; a column is walked piece by piece ----
+#pragma unroll 1
+			for (uint32_t c = 0; c < a.n_cols; c++) {
+				const QueryCol &qc = a.cols[c];
+				if (!qc.has_pred) {
+					continue;
+				}
+				uint32_t off_p = 0;
+#pragma unroll 1
+				for (int p = 0; p < kQueryMaxPieces; p++) {
+					const QPiece q = st.piece[c][p];
+					if (q.cnt == 0) {
+						continue;
 					}
-				}
-				if (a.out_bitmap != nullptr) {
-					const uint32_t ballot = __ballot_sync(0xffffffffu, pass);
-					if (lane == 0 && base + (tid & ~31u) < rows) {
-						a.out_bitmap[(rel0 + base + (tid & ~31u)) >> 5] = ballot;
+					const uint32_t end_p = off_p + q.cnt;
+					const uint8_t *pbase = stage + q.smem_off;
+					const uint64_t mask64 = lo_set64(q.w);
+					uint32_t g = off_p >> 5;
+					g += (warp - g) & (kQConsumerWarps - 1);  // first group >= off_p / 32 that is mine
+					if (q.linear && q.flo == 0 && q.span == mask64) {
+						off_p = end_p;  // zone map: every value of the piece passes
+						continue;
 					}
-				}
-				if (pass) {
-					n_pass++;
+					if (q.linear && q.w <= 32u && (q.flo >> 32) == 0) {
+						// fast path: 32-bit fields, predicate in the field domain, four of my groups per round
+						const uint32_t mask = (uint32_t)mask64, flo = (uint32_t)q.flo, span = (uint32_t)q.span;
+						const uint32_t step = 32u * kQConsumerWarps * q.w;            // bits between two of my groups
+						uint32_t bit = q.bit_base + (g * 32u + lane - off_p) * q.w;   // wraps for lanes before off_p: unused
+						for (; g * 32u < end_p; g += 4u * kQConsumerWarps, bit += 4u * step) {
+							const bool interior = g * 32u >= off_p && (g + 3u * kQConsumerWarps) * 32u + 32u <= end_p;
+							if (interior) {
+								// branch-free round: every lane of the four groups lies inside the piece
+								uint32_t f[4];
 #pragma unroll
-					for (int g = 0; g < kQueryMaxAggs; g++) {
-						if (g < (int)a.n_aggs) {
-							const QueryAgg &qa = a.aggs[g];
-							__int128 term = 1;
+								for (int u = 0; u < 4; u++) {
+									const uint32_t bu = bit + u * step;
+									const uint32_t *p32 = (const uint32_t *)(pbase + ((bu >> 3) & ~3u));
+									f[u] = __funnelshift_r(p32[0], p32[1], bu) & mask;
+								}
+								uint32_t mine = 0;
 #pragma unroll
-							for (int k = 0; k < kQueryMaxFactors; k++) {
-								if (k < (int)qa.n_factors) {
-									const int64_t v = (int64_t)vals[qa.col[k]][tid];
-									term *= (__int128)qa.add[k] + (__int128)qa.mul[k] * (__int128)v;
+								for (int u = 0; u < 4; u++) {
+									const uint32_t keep = __ballot_sync(0xffffffffu, (f[u] - flo) <= span);
+									mine = (int)lane == u ? keep : mine;
+								}
+								if (lane < 4) {
+									sel[g + lane * kQConsumerWarps] &= mine;
+								}
+							} else {
+#pragma unroll 1
+								for (int u = 0; u < 4; u++) {
+									const uint32_t gu = g + u * kQConsumerWarps;
+									if (gu * 32u >= end_p) {
+										break;
+									}
+									const uint32_t i = gu * 32u + lane;
+									const bool inside = i >= off_p && i < end_p;
+									const uint32_t bu = inside ? bit + u * step : q.bit_base;
+									const uint32_t *p32 = (const uint32_t *)(pbase + ((bu >> 3) & ~3u));
+									const uint32_t fu = __funnelshift_r(p32[0], p32[1], bu) & mask;
+									const uint32_t keep = __ballot_sync(0xffffffffu, !inside || (fu - flo) <= span);
+									if (lane == 0) {
+										sel[gu] &= keep;
+									}
 								}
 							}
-							acc[g] += (unsigned __int128)term;
+						}
+						__syncwarp();
+						off_p = end_p;
+						continue;
+					}
+					const uint32_t *words32 = (const uint32_t *)pbase;
+					for (; g * 32u < end_p; g += kQConsumerWarps) {
+						const uint32_t word = sel[g];
+						if (word == 0) {
+							continue;  // nothing left to test in these 32 rows
+						}
+						const uint32_t i = g * 32u + lane;
+						const bool inside = i >= off_p && i < end_p;
+						bool pass = true;
+						if (inside) {
+							const uint32_t bit = q.bit_base + (i - off_p) * q.w;
+							const uint64_t f = q.w <= 32u ? (uint64_t)(read_bits32(words32, bit) & (uint32_t)mask64)
+							                              : (read_bits64((const uint64_t *)words32, bit) & mask64);
+							if (q.linear) {
+								pass = (f - q.flo) <= q.span;
+							} else {
+								const uint64_t v = extend_rt(f + q.min_add, qc.type_size, qc.is_signed);
+								pass = qc.is_signed ? ((int64_t)v >= qc.lo && (int64_t)v <= qc.hi)
+								                    : (v >= (uint64_t)qc.lo && v <= (uint64_t)qc.hi);
+							}
+						}
+						const uint32_t keep = __ballot_sync(0xffffffffu, pass);
+						if (lane == 0) {
+							sel[g] = word & keep;
 						}
 					}
+					__syncwarp();
+					off_p = end_p;
 				}
 			}
+
+			// ---- survivors: bitmap out, count, compaction into the warp's list, aggregates on the list ----
+			uint32_t n_list = 0;
+			for (uint32_t g = warp; g < n_groups; g += kQConsumerWarps) {
+				const uint32_t word = sel[g];
+				if (a.out_bitmap != nullptr && lane == 0) {
+					a.out_bitmap[word0 + g] = word;
+				}
+				if (word == 0) {
+					continue;
+				}
+				if (lane == 0) {
+					n_pass += __popc(word);
+				}
+				if ((word >> lane) & 1u) {
+					my_list[n_list + __popc(word & ((1u << lane) - 1u))] = (uint16_t)(g * 32u + lane);
+				}
+				n_list += __popc(word);
+				if (n_list > kQListCap - 32u) {
+					__syncwarp();
+					aggregate_list(a, st, stage, my_list, n_list, vals, tid, lane, acc);
+					n_list = 0;
+					__syncwarp();
+				}
+			}
+			__syncwarp();
+			aggregate_list(a, st, stage, my_list, n_list, vals, tid, lane, acc);
 			__syncwarp();
 			if (lane == 0) {
 				mbar_arrive(&empty_bar[s]);
