@@ -70,6 +70,8 @@ struct adacom_column {
 	// segment holding row 2048*v (static, like the tile table): entry point of the multi-column row-block scans
 	uint32_t *d_vec_seg = nullptr;
 	std::vector<uint32_t> vec_seg;
+	uint32_t *d_parts = nullptr;       // device word behind d_vec_seg: scan chunks per segment currently needed
+	uint32_t raw_parts = 1;            // that number for slot-width (raw) segments: static
 	uint32_t max_span[3] = {0, 0, 0};  // most segments any aligned block of 2048 / 4096 / 8192 rows touches (static)
 	uint32_t wmax = 0;                 // widest live payload, refreshed with the host mirror
 	bool any_raw = false;              // some non-empty segment still lives in the raw arena (mirror)
@@ -228,11 +230,22 @@ adacom_status build_tiles(adacom_column *col) {
 			}
 			col->max_span[ri] = worst;
 		}
-		CK(ctx, cudaMallocAsync((void **)&col->d_vec_seg, (n_vec + 1) * sizeof(uint32_t), ctx->stream));
-		if (n_vec) {
-			CK(ctx, cudaMemcpyAsync(col->d_vec_seg, col->vec_seg.data(), n_vec * sizeof(uint32_t), cudaMemcpyHostToDevice,
-			                        ctx->stream));
+		// the word behind the table: scan chunks per segment (starts at the live widths; kept current on the device)
+		uint32_t parts = 1;
+		col->raw_parts = 1;
+		for (const SegDesc &d : col->h_desc) {
+			if (d.count) {
+				const uint32_t raw_gran = scan_chunk_values(8u * (uint32_t)col->t.size);
+				col->raw_parts = std::max<uint32_t>(col->raw_parts, (d.count + raw_gran - 1) / raw_gran);
+				const uint32_t gran = scan_chunk_values(d.width ? d.width : 8u * (uint32_t)col->t.size);
+				parts = std::max<uint32_t>(parts, (d.count + gran - 1) / gran);
+			}
 		}
+		col->vec_seg[n_vec] = parts;
+		CK(ctx, cudaMallocAsync((void **)&col->d_vec_seg, (n_vec + 1) * sizeof(uint32_t), ctx->stream));
+		CK(ctx, cudaMemcpyAsync(col->d_vec_seg, col->vec_seg.data(), (n_vec + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice,
+		                        ctx->stream));
+		col->d_parts = col->d_vec_seg + n_vec;
 	}
 	CK(ctx, cudaMallocAsync((void **)&col->d_tiles, (jobs.size() + 1) * sizeof(Job), ctx->stream));
 	if (!jobs.empty()) {
@@ -764,7 +777,7 @@ extern "C" adacom_status adacom_encode(adacom_column *col, uint64_t seg_begin, u
 	// 1. widths, repack decisions and payload offsets, all on the device
 	const unsigned long long ticket = ++ctx->ticket;
 	LAUNCH(ctx, launch_layout(col->t, col->d_desc, (uint32_t)seg_begin, n, flags, extent_id, ctx->d_totals, ticket,
-	                          ctx->stream));
+	                          col->d_parts, (seg_begin == 0 && seg_end == col->n_segs) ? 1 : 0, ctx->stream));
 	// the only host round trip of an encode: 8 bytes that size the new extent, polled from mapped memory
 	{
 		volatile unsigned long long *t = ctx->h_totals;
@@ -1011,7 +1024,7 @@ extern "C" adacom_status adacom_uncompact(adacom_column *col, uint64_t seg_begin
 	a.out_row0 = 0;
 	LAUNCH(ctx, launch_decode(col->t, kModeFlat, a, ctx->sm_count, ctx->stream));
 	LAUNCH(ctx, launch_reset_uncompacted(col->d_desc, (uint32_t)seg_begin, (uint32_t)(seg_end - seg_begin), col->t.size,
-	                                     ctx->stream));
+	                                     col->d_parts, col->raw_parts, ctx->stream));
 	// extents created by encode calls whose range lies inside [seg_begin, seg_end) are dead now (stream order
 	// makes the reuse safe); partially covered ones are reclaimed when the mirror is refreshed
 	for (auto &x : col->extents) {
@@ -1037,6 +1050,7 @@ static adacom_status run_agg(adacom_column *col, uint64_t b, uint64_t e, int fla
 	if (mode == kModeSum) {
 		ScanSumArgs f;
 		f.desc = col->d_desc;
+		f.parts = col->d_parts;
 		f.seg_b = (uint32_t)b;
 		f.seg_e = (uint32_t)e;
 		f.raw = col->raw;
@@ -1049,6 +1063,7 @@ static adacom_status run_agg(adacom_column *col, uint64_t b, uint64_t e, int fla
 	}
 	DecodeArgs a;
 	a.desc = col->d_desc;
+	a.parts = col->d_parts;
 	a.seg_b = (uint32_t)b;
 	a.n_units = (uint32_t)(e - b);
 	a.raw = col->raw;
@@ -1142,6 +1157,7 @@ extern "C" adacom_status adacom_point_filter_batch(adacom_column *col, uint64_t 
 	a.desc = col->d_desc;
 	a.n_units = (uint32_t)n_queries;
 	a.unit_seg = d_unit_seg;
+	a.parts = col->d_parts;
 	a.raw = col->raw;
 	a.literal = (flags & ADACOM_LITERAL) ? 1 : 0;
 	a.q_const = d_const;

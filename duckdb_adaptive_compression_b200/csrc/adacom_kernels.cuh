@@ -24,6 +24,7 @@ struct DecodeArgs {
 	uint32_t n_units = 0;
 	uint32_t seg_b = 0;
 	const uint32_t *unit_seg = nullptr;
+	const uint32_t *parts = nullptr;      // device word: chunks per segment the column currently needs (<= kScanParts)
 	const uint8_t *raw = nullptr;    // raw arena (source for segments that are not repacked)
 	int literal = 0;                 // ADACOM_LITERAL: add min even when the segment was not repacked (Q1)
 	int uncompact = 0;               // UncompressSuccinct mode: skip segments that are not compacted
@@ -48,6 +49,7 @@ cudaError_t launch_decode(TypeInfo t, DecodeMode mode, const DecodeArgs &args, i
 struct ScanSumArgs {
 	const SegDesc *desc = nullptr;
 	uint32_t seg_b = 0, seg_e = 0;        // segment range to scan (chunks are derived from the descriptors)
+	const uint32_t *parts = nullptr;      // device word: chunks per segment the column currently needs (<= kScanParts)
 	const uint8_t *raw = nullptr;         // raw arena (source of segments that are not re-packed)
 	int literal = 0;
 	int type_size = 8;
@@ -114,7 +116,8 @@ cudaError_t launch_analyze(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32
 // layout: widths, repack decision, 128-byte aligned word offsets (exclusive scan); totals (host-mapped) =
 // {words, ticket}
 cudaError_t launch_layout(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int flags, uint32_t extent,
-                          unsigned long long *totals, unsigned long long ticket, cudaStream_t stream);
+                          unsigned long long *totals, unsigned long long ticket, uint32_t *parts, int whole_column,
+                          cudaStream_t stream);
 
 // bind packed_ptr = base + word_offset for the repacked segments of the range
 cudaError_t launch_bind_extent(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, uint64_t *base, uint32_t extent,
@@ -122,7 +125,7 @@ cudaError_t launch_bind_extent(SegDesc *desc, uint32_t seg_begin, uint32_t n_seg
 
 // after an uncompact decode: segments of the range that were compacted go back to slot width / UNCOMPRESSED
 cudaError_t launch_reset_uncompacted(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int type_size,
-                                     cudaStream_t stream);
+                                     uint32_t *parts, uint32_t raw_parts, cudaStream_t stream);
 
 // encode: FOR subtract + width-specialised bit-pack of the tiles whose segment the preceding layout bound to
 // `extent`

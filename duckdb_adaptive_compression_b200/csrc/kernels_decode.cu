@@ -109,7 +109,8 @@ __global__ void __launch_bounds__(kThreads) decode_kernel(DecodeArgs a) {
 	// (unit j / kScanParts, chunk index j % kScanParts), unit -> segment seg_b + unit or unit_seg[unit]; chunks
 	// that do not exist cost one descriptor read by one producer lane, and the launch uses an odd grid so that a
 	// CTA's strided job sequence cycles through every chunk index (even load).
-	const uint32_t n_jobs = MODE == kModeFlat ? a.n_jobs : a.n_units * kScanParts;
+	const uint32_t parts = MODE == kModeFlat ? 1u : min(max(__ldg(a.parts), 1u), kScanParts);
+	const uint32_t n_jobs = MODE == kModeFlat ? a.n_jobs : a.n_units * parts;
 
 	if (tid == 0) {
 		for (int s = 0; s < kStages; s++) {
@@ -133,10 +134,10 @@ __global__ void __launch_bounds__(kThreads) decode_kernel(DecodeArgs a) {
 			if (MODE == kModeFlat) {
 				return a.jobs[job];
 			}
-			const uint32_t unit = job / kScanParts;
+			const uint32_t unit = job / parts;
 			Job j;
 			j.seg = a.unit_seg != nullptr ? __ldg(a.unit_seg + unit) : a.seg_b + unit;
-			j.k = job - unit * kScanParts;
+			j.k = job - unit * parts;
 			return j;
 		};
 		const uint32_t job0 = blockIdx.x + lane * gridDim.x;
@@ -164,7 +165,7 @@ __global__ void __launch_bounds__(kThreads) decode_kernel(DecodeArgs a) {
 			r.bytes = 0;
 			if (job < n_jobs) {
 				r = resolve_unit<S>(a, cur.seg, cur.k, MODE == kModeFlat ? kVectorSize : 0u, dq);
-				r.info.unit = MODE == kModeFlat ? 0u : job / kScanParts;
+				r.info.unit = MODE == kModeFlat ? 0u : job / parts;
 			}
 			// one lane at a time, in job order: the slot's previous user (seq - kStages) has then already been
 			// issued, so the parity wait is never more than one phase ahead

@@ -181,9 +181,12 @@ constexpr int kLayoutItems = 5;  // descriptors per thread and pass, all loaded 
 __global__ void __launch_bounds__(kLayoutThreads) layout_kernel(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs,
                                                                 int type_size, int flags, uint32_t extent,
                                                                 volatile unsigned long long *totals,
-                                                                unsigned long long ticket) {
+                                                                unsigned long long ticket, uint32_t *parts,
+                                                                int whole_column) {
 	__shared__ unsigned long long warp_tot[kLayoutThreads / 32];
 	__shared__ unsigned long long running_s;
+	__shared__ uint32_t parts_s;
+	uint32_t my_parts = 1;  // most scan chunks any of my segments needs at its (new) width
 	const uint32_t tid = threadIdx.x;
 	const uint32_t lane = tid & 31u, warp = tid >> 5;
 	const bool padded = flags & kFlagPadded;
@@ -191,6 +194,7 @@ __global__ void __launch_bounds__(kLayoutThreads) layout_kernel(SegDesc *desc, u
 	const uint32_t slot_w = 8u * (uint32_t)type_size;
 	if (tid == 0) {
 		running_s = 0;
+		parts_s = 1;
 	}
 	__syncthreads();
 
@@ -216,6 +220,7 @@ __global__ void __launch_bounds__(kLayoutThreads) layout_kernel(SegDesc *desc, u
 			if (g0 + i < n_segs) {
 				const uint32_t count = count_r[i];
 				const uint32_t state = (wst_r[i] >> 8) & 0xffu;
+				uint32_t w_now = wst_r[i] & 0xffu;
 				// Compact() returns early for empty or already compacted segments (column_segment.cpp:278)
 				if (count != 0 && !(state & kSegCompacted)) {
 					const uint64_t mn = mn_r[i], mx = mx_r[i];
@@ -233,6 +238,11 @@ __global__ void __launch_bounds__(kLayoutThreads) layout_kernel(SegDesc *desc, u
 					const uint32_t new_state = (state & kSegAnalyzed) | kSegCompacted | (repack ? kSegRepacked : 0);
 					wst_r[i] = (wst_r[i] & 0xffff0000u) | (new_state << 8) | (repack ? w : slot_w);
 					mine += aligned[i];
+					w_now = repack ? w : slot_w;
+				}
+				if (count != 0 && w_now != 0) {
+					const uint32_t gran = scan_chunk_values(w_now);
+					my_parts = max(my_parts, (count + gran - 1) / gran);
 				}
 			}
 		}
@@ -279,7 +289,17 @@ __global__ void __launch_bounds__(kLayoutThreads) layout_kernel(SegDesc *desc, u
 		}
 		__syncthreads();  // warp_tot / running_s are reused by the next pass
 	}
+	my_parts = __reduce_max_sync(0xffffffffu, my_parts);
+	if (lane == 0) {
+		atomicMax(&parts_s, my_parts);
+	}
+	__syncthreads();
 	if (tid == 0) {
+		if (whole_column) {
+			*parts = parts_s;
+		} else {
+			atomicMax(parts, parts_s);
+		}
 		totals[0] = running_s;
 		__threadfence_system();
 		totals[1] = ticket;
@@ -299,8 +319,12 @@ __global__ void bind_extent_kernel(SegDesc *desc, uint32_t seg_begin, uint32_t n
 
 // ColumnSegment::UncompressSuccinct's bookkeeping (column_segment.cpp:494-503): function -> UNCOMPRESSED,
 // compacted = false; the payload was already decoded into the raw arena by the decode kernel.
-__global__ void reset_uncompacted_kernel(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int type_size) {
+__global__ void reset_uncompacted_kernel(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int type_size,
+                                         uint32_t *parts, uint32_t raw_parts) {
 	uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+	if (g == 0) {
+		atomicMax(parts, raw_parts);  // slot-width segments need the most scan chunks
+	}
 	if (g < n_segs) {
 		SegDesc *d = desc + seg_begin + g;
 		if (d->state & kSegCompacted) {
@@ -345,8 +369,10 @@ cudaError_t launch_analyze(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32
 }
 
 cudaError_t launch_layout(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int flags, uint32_t extent,
-                          unsigned long long *totals, unsigned long long ticket, cudaStream_t stream) {
-	layout_kernel<<<1, kLayoutThreads, 0, stream>>>(desc, seg_begin, n_segs, t.size, flags, extent, totals, ticket);
+                          unsigned long long *totals, unsigned long long ticket, uint32_t *parts, int whole_column,
+                          cudaStream_t stream) {
+	layout_kernel<<<1, kLayoutThreads, 0, stream>>>(desc, seg_begin, n_segs, t.size, flags, extent, totals, ticket, parts,
+	                                                whole_column);
 	return cudaGetLastError();
 }
 
@@ -360,11 +386,11 @@ cudaError_t launch_bind_extent(SegDesc *desc, uint32_t seg_begin, uint32_t n_seg
 }
 
 cudaError_t launch_reset_uncompacted(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int type_size,
-                                     cudaStream_t stream) {
+                                     uint32_t *parts, uint32_t raw_parts, cudaStream_t stream) {
 	if (n_segs == 0) {
 		return cudaSuccess;
 	}
-	reset_uncompacted_kernel<<<(n_segs + 255) / 256, 256, 0, stream>>>(desc, seg_begin, n_segs, type_size);
+	reset_uncompacted_kernel<<<(n_segs + 255) / 256, 256, 0, stream>>>(desc, seg_begin, n_segs, type_size, parts, raw_parts);
 	return cudaGetLastError();
 }
 

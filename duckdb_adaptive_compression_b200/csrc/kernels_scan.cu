@@ -280,13 +280,13 @@ __device__ __forceinline__ bool linear_zone_dev(uint64_t min_factor, uint32_t wi
 // A segment has at most kScanParts chunks (16 KiB stages vs <= 256 KiB segments); jobs whose chunk does not
 // exist cost one descriptor read by one producer lane.  The launch uses an odd grid so that every CTA's strided
 // job sequence cycles through all chunk indices (even load).
-__device__ __forceinline__ uint32_t job_segment(const ScanSumArgs &a, uint32_t job) {
-	return a.seg_b + job / kScanParts;
+__device__ __forceinline__ uint32_t job_segment(const ScanSumArgs &a, uint32_t job, uint32_t parts) {
+	return a.seg_b + job / parts;
 }
 
-__device__ __forceinline__ ResolvedChunk resolve_chunk(const ScanSumArgs &a, uint32_t job, const DescQ &dq) {
+__device__ __forceinline__ ResolvedChunk resolve_chunk(const ScanSumArgs &a, uint32_t job, uint32_t parts, const DescQ &dq) {
 	ResolvedChunk r;
-	const uint32_t k = job % kScanParts;
+	const uint32_t k = job % parts;
 	const uint64_t row_start = dq.row_start();
 	const uint64_t packed_ptr = dq.packed_ptr();
 	const uint64_t mn = dq.min_factor();
@@ -338,7 +338,9 @@ __global__ void __launch_bounds__(kThreads, 3) scan_sum_fields_kernel(const Scan
 	const uint32_t lane = tid & 31u;
 	const uint32_t warp = tid >> 5;
 	const uint32_t n_units = a.seg_e - a.seg_b;
-	const uint32_t n_jobs = n_units * kScanParts;
+	// chunks per segment the column currently needs (maintained on the device by layout / uncompact; <= 16)
+	const uint32_t parts = min(max(__ldg(a.parts), 1u), kScanParts);
+	const uint32_t n_jobs = n_units * parts;
 
 	if (tid == 0) {
 		for (int s = 0; s < kStages; s++) {
@@ -363,19 +365,19 @@ __global__ void __launch_bounds__(kThreads, 3) scan_sum_fields_kernel(const Scan
 		{
 			const uint32_t job = blockIdx.x + lane * gridDim.x;
 			if (job < n_jobs) {
-				dq_next = load_desc(a.desc + job_segment(a, job));
+				dq_next = load_desc(a.desc + job_segment(a, job, parts));
 			}
 		}
 		for (uint32_t j0 = blockIdx.x; j0 < n_jobs; j0 += batch) {
 			const uint32_t job = j0 + lane * gridDim.x;
 			const DescQ dq = dq_next;
 			if (job + batch < n_jobs) {  // descriptors of the next batch: in flight while this batch is issued
-				dq_next = load_desc(a.desc + job_segment(a, job + batch));
+				dq_next = load_desc(a.desc + job_segment(a, job + batch, parts));
 			}
 			ResolvedChunk r;
 			r.bytes = 0;
 			if (job < n_jobs) {
-				r = resolve_chunk(a, job, dq);
+				r = resolve_chunk(a, job, parts, dq);
 			}
 			// publish in job order, one lane at a time: the slot's previous user (seq - kStages) has then
 			// already been issued, so the parity wait below is never more than one phase ahead
