@@ -37,6 +37,7 @@ struct adacom_ctx {
 	Agg *d_agg = nullptr;
 	unsigned long long *d_totals = nullptr;  // device alias of h_totals (host-mapped)
 	unsigned long long ticket = 0;           // sequence number of the last layout launch
+	unsigned long long *d_layout_scratch = nullptr;  // chained scan of layout_kernel (128 words)
 	Agg *d_aggs = nullptr;                // adacom_scan_columns: kQueryMaxAggs aggregates (lazily allocated)
 	Agg *h_aggs = nullptr;                // pinned
 	Agg *h_agg = nullptr;                 // pinned
@@ -337,6 +338,8 @@ extern "C" adacom_status adacom_ctx_create(int device, adacom_ctx **out) {
 	CK(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
 	CK(nullptr, cudaMalloc((void **)&ctx->d_agg, sizeof(Agg)));
 	CK(nullptr, cudaHostAlloc((void **)&ctx->h_agg, sizeof(Agg), cudaHostAllocDefault));
+	CK(nullptr, cudaMalloc((void **)&ctx->d_layout_scratch, 128 * sizeof(unsigned long long)));
+	CK(nullptr, cudaMemset(ctx->d_layout_scratch, 0, 128 * sizeof(unsigned long long)));
 	// {payload words, ticket} written by layout_kernel straight into host memory; the encode path spins on the
 	// ticket (a few microseconds) instead of a copy + stream synchronisation
 	CK(nullptr, cudaHostAlloc((void **)&ctx->h_totals, 4 * sizeof(unsigned long long), cudaHostAllocMapped));
@@ -360,6 +363,7 @@ extern "C" void adacom_ctx_destroy(adacom_ctx *ctx) {
 	cudaStreamSynchronize(ctx->stream);
 	cudaFree(ctx->flush_buf);
 	cudaFree(ctx->d_agg);
+	cudaFree(ctx->d_layout_scratch);
 	cudaFree(ctx->d_aggs);
 	cudaFreeHost(ctx->h_aggs);
 	cudaFreeHost(ctx->h_agg);
@@ -777,7 +781,8 @@ extern "C" adacom_status adacom_encode(adacom_column *col, uint64_t seg_begin, u
 	// 1. widths, repack decisions and payload offsets, all on the device
 	const unsigned long long ticket = ++ctx->ticket;
 	LAUNCH(ctx, launch_layout(col->t, col->d_desc, (uint32_t)seg_begin, n, flags, extent_id, ctx->d_totals, ticket,
-	                          col->d_parts, (seg_begin == 0 && seg_end == col->n_segs) ? 1 : 0, ctx->stream));
+	                          col->d_parts, (seg_begin == 0 && seg_end == col->n_segs) ? 1 : 0, ctx->d_layout_scratch,
+	                          ctx->stream));
 	// the only host round trip of an encode: 8 bytes that size the new extent, polled from mapped memory
 	{
 		volatile unsigned long long *t = ctx->h_totals;
@@ -817,11 +822,11 @@ extern "C" adacom_status adacom_encode(adacom_column *col, uint64_t seg_begin, u
 			ext.capacity = ext.words + ext.words / 32 + 64;
 			CK(ctx, cudaMallocAsync((void **)&ext.base, ext.capacity * 8 + kArenaPad, ctx->stream));
 		}
-		LAUNCH(ctx, launch_bind_extent(col->d_desc, (uint32_t)seg_begin, n, ext.base, extent_id, ctx->stream));
-		// 3. pack
+		// 3. pack, then publish packed_ptr = base + word_offset (scans launched later on this stream see it)
 		LAUNCH(ctx, launch_encode(col->t, col->d_desc, col->d_tiles + col->tile_first[seg_begin],
-		                          col->tile_first[seg_end] - col->tile_first[seg_begin], col->raw, extent_id, ctx->sm_count,
-		                          ctx->stream));
+		                          col->tile_first[seg_end] - col->tile_first[seg_begin], col->raw, extent_id, ext.base,
+		                          ctx->sm_count, ctx->stream));
+		LAUNCH(ctx, launch_bind_extent(col->d_desc, (uint32_t)seg_begin, n, ext.base, extent_id, ctx->stream));
 	}
 	col->extents.push_back(ext);
 	col->mirror_dirty = true;

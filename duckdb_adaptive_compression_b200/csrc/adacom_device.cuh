@@ -50,6 +50,7 @@ struct DescQ {
 #ifdef __CUDACC__
 	__device__ __forceinline__ uint64_t row_start() const { return ((uint64_t)q0.y << 32) | q0.x; }
 	__device__ __forceinline__ uint64_t packed_ptr() const { return ((uint64_t)q0.w << 32) | q0.z; }
+	__device__ __forceinline__ uint64_t word_offset() const { return ((uint64_t)q1.y << 32) | q1.x; }
 	__device__ __forceinline__ uint64_t min_factor() const { return ((uint64_t)q1.w << 32) | q1.z; }
 	__device__ __forceinline__ uint32_t count() const { return q2.z; }
 	__device__ __forceinline__ uint32_t extent() const { return q3.x; }

@@ -117,7 +117,7 @@ cudaError_t launch_analyze(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32
 // {words, ticket}
 cudaError_t launch_layout(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int flags, uint32_t extent,
                           unsigned long long *totals, unsigned long long ticket, uint32_t *parts, int whole_column,
-                          cudaStream_t stream);
+                          unsigned long long *scratch /* 128 words of device memory */, cudaStream_t stream);
 
 // bind packed_ptr = base + word_offset for the repacked segments of the range
 cudaError_t launch_bind_extent(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, uint64_t *base, uint32_t extent,
@@ -127,10 +127,10 @@ cudaError_t launch_bind_extent(SegDesc *desc, uint32_t seg_begin, uint32_t n_seg
 cudaError_t launch_reset_uncompacted(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int type_size,
                                      uint32_t *parts, uint32_t raw_parts, cudaStream_t stream);
 
-// encode: FOR subtract + width-specialised bit-pack of the tiles whose segment the preceding layout bound to
-// `extent`
+// encode: FOR subtract + width-specialised bit-pack of the tiles whose segment the preceding layout assigned to
+// `extent` (payload at base + word_offset; launch_bind_extent publishes the pointers afterwards)
 cudaError_t launch_encode(TypeInfo t, const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw,
-                          uint32_t extent, int sm_count, cudaStream_t stream);
+                          uint32_t extent, uint64_t *base, int sm_count, cudaStream_t stream);
 
 // synthetic generator: raw[i] = T(splitmix64(seed + first_index + i) & mask)
 cudaError_t launch_fill_splitmix(TypeInfo t, void *raw, uint64_t n, uint64_t seed, uint64_t first_index, uint64_t mask,

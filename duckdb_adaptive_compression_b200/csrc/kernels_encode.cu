@@ -171,136 +171,162 @@ __global__ void __launch_bounds__(kAnalyzeThreads) analyze_kernel(SegDesc *desc,
 // layout: width + repack decision + exclusive scan of 128-byte aligned payload sizes (single CTA)
 // ---------------------------------------------------------------------------------------------------
 
-constexpr int kLayoutThreads = 1024;
-constexpr int kLayoutItems = 5;  // descriptors per thread and pass, all loaded before the first dependent use
+constexpr int kLayoutThreads = 256;
+constexpr int kLayoutMaxCtas = 128;  // <= SM count: every CTA is resident, a CTA only ever waits for lower-indexed ones
+constexpr int kLayoutTagShift = 48;  // scratch word = ticket tag (16 bits) | scan chunks (5 bits, << 43) | words (43 bits)
 
-// Single CTA.  Thread t owns kLayoutItems consecutive segments per pass: their descriptor quarters are loaded
-// up front (independent 128-bit loads, one memory round trip), the aligned payload sizes go through ONE block
-// scan per pass, and the results are written back with vector stores.  `totals` is host-mapped pinned memory:
-// {words, ticket}; the host spins on the ticket instead of paying a stream synchronisation.
+struct LayoutItem {
+	unsigned long long aligned;  // payload words rounded up to 128 bytes; ~0: descriptor left untouched
+	uint32_t wst;                // new width | state << 8 | pad
+	uint32_t parts;              // scan chunks the segment needs at its (new) width
+};
+
+// the width rule + re-pack decision of one segment (column_segment.cpp:351-363, 408-419)
+__device__ __forceinline__ LayoutItem layout_item(const SegDesc *d, bool padded, bool zero_ext, uint32_t slot_w) {
+	LayoutItem it;
+	const uint64_t mn = d->min_factor, mx = d->max_factor;
+	const uint32_t count = d->count;
+	uint32_t wst = ((const uint32_t *)d)[14];
+	const uint32_t state = (wst >> 8) & 0xffu;
+	uint32_t w_now = wst & 0xffu;
+	it.aligned = ~0ull;
+	// Compact() returns early for empty or already compacted segments (column_segment.cpp:278)
+	if (count != 0 && !(state & kSegCompacted)) {
+		uint64_t range;
+		if (zero_ext) {
+			// BitCompressFromUncompressed only subtracts when max > min (column_segment.cpp:408-411)
+			range = (mx != 0 && mn != ~0ull && mx > mn) ? mx - mn : mx;
+		} else {
+			range = mx - mn;
+		}
+		const uint32_t w = width_for_range(range, padded);
+		const bool repack = slot_w > w;
+		const uint64_t words = repack ? ((uint64_t)count * w + 63) >> 6 : 0;
+		it.aligned = (words + kSegAlignWords - 1) & ~(uint64_t)(kSegAlignWords - 1);
+		const uint32_t new_state = (state & kSegAnalyzed) | kSegCompacted | (repack ? kSegRepacked : 0);
+		w_now = repack ? w : slot_w;
+		wst = (wst & 0xffff0000u) | (new_state << 8) | w_now;
+	}
+	it.wst = wst;
+	it.parts = 1;
+	if (count != 0 && w_now != 0) {
+		const uint32_t gran = scan_chunk_values(w_now);
+		it.parts = (count + gran - 1) / gran;
+	}
+	return it;
+}
+
+// Up to 128 resident CTAs, thread t of CTA b owns `per` consecutive segments.  Pass 1 sizes them, a block scan and
+// a chained scan over the CTAs (each CTA publishes {words, scan chunks} tagged with the call's ticket and sums
+// the words of the CTAs before it -- they were dispatched earlier, so the wait cannot deadlock) give every
+// segment its 128-byte aligned word offset; pass 2 writes the descriptors back.  The last CTA publishes the arena
+// size into host-mapped pinned memory {words, ticket}: the host spins on the ticket instead of paying a stream
+// synchronisation.
 __global__ void __launch_bounds__(kLayoutThreads) layout_kernel(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs,
-                                                                int type_size, int flags, uint32_t extent,
+                                                                uint32_t per, int type_size, int flags, uint32_t extent,
                                                                 volatile unsigned long long *totals,
                                                                 unsigned long long ticket, uint32_t *parts,
-                                                                int whole_column) {
+                                                                int whole_column, volatile unsigned long long *scratch) {
 	__shared__ unsigned long long warp_tot[kLayoutThreads / 32];
-	__shared__ unsigned long long running_s;
+	__shared__ unsigned long long base_s;
 	__shared__ uint32_t parts_s;
-	uint32_t my_parts = 1;  // most scan chunks any of my segments needs at its (new) width
 	const uint32_t tid = threadIdx.x;
 	const uint32_t lane = tid & 31u, warp = tid >> 5;
 	const bool padded = flags & kFlagPadded;
 	const bool zero_ext = flags & kFlagZeroExt;
 	const uint32_t slot_w = 8u * (uint32_t)type_size;
+	const unsigned long long tag = (ticket & 0xffffull) << kLayoutTagShift;
 	if (tid == 0) {
-		running_s = 0;
+		base_s = 0;
 		parts_s = 1;
 	}
-	__syncthreads();
+	const uint32_t g0 = (blockIdx.x * kLayoutThreads + tid) * per;
 
-	for (uint32_t base = 0; base < n_segs; base += kLayoutThreads * kLayoutItems) {
-		const uint32_t g0 = base + tid * kLayoutItems;
-		uint64_t mn_r[kLayoutItems], mx_r[kLayoutItems];
-		uint32_t count_r[kLayoutItems], wst_r[kLayoutItems];  // wst = width | state << 8 | pad
+	// ---- pass 1: sizes ----
+	unsigned long long mine = 0;
+	uint32_t my_parts = 1;
+	LayoutItem first;  // per == 1 (up to 32768 segments): nothing is computed twice
+	for (uint32_t i = 0; i < per && g0 + i < n_segs; i++) {
+		const LayoutItem it = layout_item(desc + seg_begin + g0 + i, padded, zero_ext, slot_w);
+		if (i == 0) {
+			first = it;
+		}
+		if (it.aligned != ~0ull) {
+			mine += it.aligned;
+		}
+		my_parts = max(my_parts, it.parts);
+	}
+	// ---- exclusive scan inside the CTA ----
+	unsigned long long incl = mine;
 #pragma unroll
-		for (int i = 0; i < kLayoutItems; i++) {
-			if (g0 + i < n_segs) {
-				const SegDesc *d = desc + seg_begin + g0 + i;
-				mn_r[i] = d->min_factor;
-				mx_r[i] = d->max_factor;
-				count_r[i] = d->count;
-				wst_r[i] = ((const uint32_t *)d)[14];
-			}
+	for (int d = 1; d < 32; d <<= 1) {
+		unsigned long long v = __shfl_up_sync(0xffffffffu, incl, d);
+		if ((int)lane >= d) {
+			incl += v;
 		}
-		unsigned long long aligned[kLayoutItems];
-		unsigned long long mine = 0;
-#pragma unroll
-		for (int i = 0; i < kLayoutItems; i++) {
-			aligned[i] = ~0ull;  // ~0: descriptor left untouched
-			if (g0 + i < n_segs) {
-				const uint32_t count = count_r[i];
-				const uint32_t state = (wst_r[i] >> 8) & 0xffu;
-				uint32_t w_now = wst_r[i] & 0xffu;
-				// Compact() returns early for empty or already compacted segments (column_segment.cpp:278)
-				if (count != 0 && !(state & kSegCompacted)) {
-					const uint64_t mn = mn_r[i], mx = mx_r[i];
-					uint64_t range;
-					if (zero_ext) {
-						// BitCompressFromUncompressed only subtracts when max > min (column_segment.cpp:408-411)
-						range = (mx != 0 && mn != ~0ull && mx > mn) ? mx - mn : mx;
-					} else {
-						range = mx - mn;
-					}
-					const uint32_t w = width_for_range(range, padded);
-					const bool repack = slot_w > w;
-					const uint64_t words = repack ? ((uint64_t)count * w + 63) >> 6 : 0;
-					aligned[i] = (words + kSegAlignWords - 1) & ~(uint64_t)(kSegAlignWords - 1);
-					const uint32_t new_state = (state & kSegAnalyzed) | kSegCompacted | (repack ? kSegRepacked : 0);
-					wst_r[i] = (wst_r[i] & 0xffff0000u) | (new_state << 8) | (repack ? w : slot_w);
-					mine += aligned[i];
-					w_now = repack ? w : slot_w;
-				}
-				if (count != 0 && w_now != 0) {
-					const uint32_t gran = scan_chunk_values(w_now);
-					my_parts = max(my_parts, (count + gran - 1) / gran);
-				}
-			}
-		}
-		// block-wide exclusive scan of `mine`
-		unsigned long long incl = mine;
-#pragma unroll
-		for (int d = 1; d < 32; d <<= 1) {
-			unsigned long long v = __shfl_up_sync(0xffffffffu, incl, d);
-			if ((int)lane >= d) {
-				incl += v;
-			}
-		}
-		if (lane == 31) {
-			warp_tot[warp] = incl;
-		}
-		__syncthreads();
-		const unsigned long long running = running_s;
-		if (warp == 0) {
-			unsigned long long t = warp_tot[lane], ti = t;
-#pragma unroll
-			for (int d = 1; d < 32; d <<= 1) {
-				unsigned long long v = __shfl_up_sync(0xffffffffu, ti, d);
-				if ((int)lane >= d) {
-					ti += v;
-				}
-			}
-			warp_tot[lane] = ti - t;  // exclusive
-			if (lane == 31) {
-				running_s = running + ti;
-			}
-		}
-		__syncthreads();
-		unsigned long long off = running + warp_tot[warp] + incl - mine;
-#pragma unroll
-		for (int i = 0; i < kLayoutItems; i++) {
-			if (g0 + i < n_segs && aligned[i] != ~0ull) {
-				SegDesc *d = desc + seg_begin + g0 + i;
-				d->packed_ptr = 0;
-				d->word_offset = off;
-				d->extent = extent;
-				((uint32_t *)d)[14] = wst_r[i];
-				off += aligned[i];
-			}
-		}
-		__syncthreads();  // warp_tot / running_s are reused by the next pass
 	}
 	my_parts = __reduce_max_sync(0xffffffffu, my_parts);
+	if (lane == 31) {
+		warp_tot[warp] = incl;
+	}
+	__syncthreads();
 	if (lane == 0) {
 		atomicMax(&parts_s, my_parts);
 	}
+	unsigned long long warp_base = 0, cta_total = 0;
+#pragma unroll
+	for (int wv = 0; wv < kLayoutThreads / 32; wv++) {
+		const unsigned long long t = warp_tot[wv];
+		warp_base += wv < (int)warp ? t : 0ull;
+		cta_total += t;
+	}
 	__syncthreads();
+	// ---- chained scan over the CTAs ----
 	if (tid == 0) {
+		scratch[blockIdx.x] = tag | ((unsigned long long)parts_s << 43) | cta_total;
+	}
+	unsigned long long before = 0;
+	uint32_t parts_before = 1;
+	for (uint32_t j = tid; j < blockIdx.x; j += kLayoutThreads) {
+		unsigned long long v;
+		do {
+			v = scratch[j];
+		} while ((v >> kLayoutTagShift) != (tag >> kLayoutTagShift));
+		before += v & ((1ull << 43) - 1ull);
+		parts_before = max(parts_before, (uint32_t)((v >> 43) & 31u));
+	}
+	if (blockIdx.x != 0) {
+#pragma unroll
+		for (int d = 16; d > 0; d >>= 1) {
+			before += __shfl_down_sync(0xffffffffu, before, d);
+		}
+		parts_before = __reduce_max_sync(0xffffffffu, parts_before);
+		if (lane == 0) {
+			atomicAdd((unsigned long long *)&base_s, before);
+			atomicMax(&parts_s, parts_before);
+		}
+	}
+	__syncthreads();
+	// ---- pass 2: write back ----
+	unsigned long long off = base_s + warp_base + incl - mine;
+	for (uint32_t i = 0; i < per && g0 + i < n_segs; i++) {
+		SegDesc *d = desc + seg_begin + g0 + i;
+		const LayoutItem it = i == 0 ? first : layout_item(d, padded, zero_ext, slot_w);
+		if (it.aligned != ~0ull) {
+			d->packed_ptr = 0;
+			d->word_offset = off;
+			d->extent = extent;
+			((uint32_t *)d)[14] = it.wst;
+			off += it.aligned;
+		}
+	}
+	if (blockIdx.x == gridDim.x - 1 && tid == 0) {
 		if (whole_column) {
 			*parts = parts_s;
 		} else {
 			atomicMax(parts, parts_s);
 		}
-		totals[0] = running_s;
+		totals[0] = base_s + cta_total;
 		__threadfence_system();
 		totals[1] = ticket;
 	}
@@ -370,9 +396,17 @@ cudaError_t launch_analyze(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32
 
 cudaError_t launch_layout(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int flags, uint32_t extent,
                           unsigned long long *totals, unsigned long long ticket, uint32_t *parts, int whole_column,
-                          cudaStream_t stream) {
-	layout_kernel<<<1, kLayoutThreads, 0, stream>>>(desc, seg_begin, n_segs, t.size, flags, extent, totals, ticket, parts,
-	                                                whole_column);
+                          unsigned long long *scratch, cudaStream_t stream) {
+	uint32_t grid = (n_segs + kLayoutThreads - 1) / kLayoutThreads;
+	if (grid > (uint32_t)kLayoutMaxCtas) {
+		grid = kLayoutMaxCtas;
+	}
+	if (grid == 0) {
+		grid = 1;
+	}
+	const uint32_t per = (n_segs + grid * kLayoutThreads - 1) / (grid * kLayoutThreads);
+	layout_kernel<<<grid, kLayoutThreads, 0, stream>>>(desc, seg_begin, n_segs, per ? per : 1, t.size, flags, extent, totals,
+	                                                   ticket, parts, whole_column, scratch);
 	return cudaGetLastError();
 }
 

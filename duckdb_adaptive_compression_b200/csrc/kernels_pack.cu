@@ -43,16 +43,19 @@ struct PackTile {
 };
 
 template <int S>
-__device__ __forceinline__ PackTile resolve_pack_tile(const DescQ &dq, uint32_t k, const uint8_t *raw, uint32_t extent) {
+__device__ __forceinline__ PackTile resolve_pack_tile(const DescQ &dq, uint32_t k, const uint8_t *raw, uint32_t extent,
+                                                      uint64_t *base) {
 	PackTile t;
 	const uint64_t row_start = dq.row_start();
-	const uint64_t packed_ptr = dq.packed_ptr();
+	// segments laid out by this encode call are not bound yet (packed_ptr == 0): their payload goes to
+	// base + word_offset; bind_extent_kernel publishes the pointer behind this kernel, off the critical path
+	const uint64_t packed_ptr = (uint64_t)(base + dq.word_offset());
 	const uint64_t mn = dq.min_factor();
 	const uint32_t count = dq.count();
 	const uint32_t w = dq.width();
 	const uint32_t state = dq.state();
 	const uint32_t first = k * kVectorSize;
-	const bool repacked = (state & kSegRepacked) && dq.extent() == extent && packed_ptr != 0 && first < count;
+	const bool repacked = (state & kSegRepacked) && dq.extent() == extent && dq.packed_ptr() == 0 && first < count;
 	t.cnt = repacked ? min(kVectorSize, count - first) : 0u;
 	t.src = raw + (row_start + first) * (uint64_t)S;
 	t.sub = mn == ~0ull ? 0ull : mn;
@@ -196,7 +199,7 @@ template <int S> struct PackSmem {
 
 template <int S>
 __global__ void __launch_bounds__(kPackThreads, 5) pack_kernel(const SegDesc *desc, const Job *tiles, uint32_t n_tiles,
-                                                               const uint8_t *raw, uint32_t extent) {
+                                                               const uint8_t *raw, uint32_t extent, uint64_t *base) {
 	extern __shared__ __align__(16) uint8_t pack_smem[];
 	void *fld = pack_smem;
 	uint64_t *ostage = (uint64_t *)(pack_smem + PackSmem<S>::kFieldBytes);
@@ -213,7 +216,7 @@ __global__ void __launch_bounds__(kPackThreads, 5) pack_kernel(const SegDesc *de
 	Job job_next = ti + gridDim.x < n_tiles ? tiles[ti + gridDim.x] : job;
 	DescQ dq = load_desc(desc + job.seg);
 	for (;;) {
-		const PackTile t = resolve_pack_tile<S>(dq, job.k, raw, extent);
+		const PackTile t = resolve_pack_tile<S>(dq, job.k, raw, extent, base);
 		const uint32_t next = ti + gridDim.x;
 		job = job_next;
 		if (next < n_tiles) {
@@ -264,7 +267,7 @@ __global__ void __launch_bounds__(kPackThreads, 5) pack_kernel(const SegDesc *de
 
 template <int S>
 cudaError_t launch_pack_s(const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw, uint32_t extent,
-                          int sm_count, cudaStream_t stream) {
+                          uint64_t *base, int sm_count, cudaStream_t stream) {
 	static int per_sm[64] = {};  // per device: resident CTAs per SM (0 = not configured yet)
 	const size_t smem = PackSmem<S>::kBytes;
 	auto kernel = pack_kernel<S>;
@@ -289,23 +292,23 @@ cudaError_t launch_pack_s(const SegDesc *desc, const Job *tiles, uint32_t n_tile
 	if (grid > n_tiles) {
 		grid = n_tiles;
 	}
-	kernel<<<grid, kPackThreads, smem, stream>>>(desc, tiles, n_tiles, raw, extent);
+	kernel<<<grid, kPackThreads, smem, stream>>>(desc, tiles, n_tiles, raw, extent, base);
 	return cudaGetLastError();
 }
 
 }  // namespace
 
 cudaError_t launch_encode(TypeInfo t, const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw,
-                          uint32_t extent, int sm_count, cudaStream_t stream) {
+                          uint32_t extent, uint64_t *base, int sm_count, cudaStream_t stream) {
 	switch (t.size) {
 	case 1:
-		return launch_pack_s<1>(desc, tiles, n_tiles, raw, extent, sm_count, stream);
+		return launch_pack_s<1>(desc, tiles, n_tiles, raw, extent, base, sm_count, stream);
 	case 2:
-		return launch_pack_s<2>(desc, tiles, n_tiles, raw, extent, sm_count, stream);
+		return launch_pack_s<2>(desc, tiles, n_tiles, raw, extent, base, sm_count, stream);
 	case 4:
-		return launch_pack_s<4>(desc, tiles, n_tiles, raw, extent, sm_count, stream);
+		return launch_pack_s<4>(desc, tiles, n_tiles, raw, extent, base, sm_count, stream);
 	case 8:
-		return launch_pack_s<8>(desc, tiles, n_tiles, raw, extent, sm_count, stream);
+		return launch_pack_s<8>(desc, tiles, n_tiles, raw, extent, base, sm_count, stream);
 	default:
 		return cudaErrorInvalidValue;
 	}
