@@ -344,9 +344,18 @@ def run_ours(args):
     dom_ms = float(op_ms["scan"].sum())
     dom_bytes = sum(alg_bytes("scan", b) for b in widths)
     achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
+    # dram__bytes_read.sum + dram__bytes_write.sum of that kernel per launch, from the committed ncu capture of this
+    # command (tools/ncu_round.sh -> tools/traffic_from_ncu.py); null when no capture covers the full sweep
+    traffic = None
+    try:
+        if args.widths == "1-64" and args.log2_values == 27:
+            with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
+                traffic = int(json.load(f)["traffic_bytes_per_launch"])
+    except Exception:
+        traffic = None
     roofline = {"bound": "hbm", "kernel": "decode_kernel<8,false,flat> (scan -> flat vectors)",
                 "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-                "traffic": None, "peak_source": peak_src,
+                "traffic": traffic, "peak_source": peak_src,
                 "launches_per_step": len(widths), "avg_launch_ms": round(dom_ms / len(widths), 5),
                 "algorithmic_bytes_per_launch": int(dom_bytes / len(widths))}
 
