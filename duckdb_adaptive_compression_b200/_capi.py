@@ -10,7 +10,8 @@ import os
 import re
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "csrc", "libadacom_gpu.so")
+# ADACOM_GPU_LIB: developer override to A/B two builds of the library in one GPU session
+LIB_PATH = os.environ.get("ADACOM_GPU_LIB") or os.path.join(HERE, "csrc", "libadacom_gpu.so")
 HEADER_PATH = os.path.join(os.path.dirname(HERE), "include", "adacom_gpu.h")
 
 OK, ERR_INVALID, ERR_CUDA, ERR_NOMEM, ERR_UNSUPPORTED, ERR_STATE, ERR_NO_DEVICE = range(7)
