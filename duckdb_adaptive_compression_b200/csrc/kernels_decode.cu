@@ -26,8 +26,12 @@ constexpr int kConsumers = kConsumerWarps * 32;  // threads that unpack
 constexpr int kThreads = kConsumers + 32;        // + one producer warp that only feeds the TMA ring
 constexpr int kEmptyArrivals = 1;  // the consumers meet on a named barrier, one of them frees the stage
 constexpr int kStages = 6;
-constexpr uint32_t kStagePayload = 16384;
-constexpr uint32_t kStageBytes = kStagePayload + 32;  // + 16 B misalignment + 16 B pad (read_bits over-read)
+// Stage payload: a fused-scan chunk is <= 16 KiB for every type; a flat tile is 2048 values = at most 2048*S bytes
+// (slot width), so the narrower types stage less and fit more CTAs per SM.
+// + 16 B misalignment + 16 B pad (read_bits over-read)
+template <int S, int MODE> struct StageCfg {
+	static constexpr uint32_t kBytes = (MODE == kModeFlat ? kVectorSize * (uint32_t)S : 16384u) + 32u;
+};
 
 struct StageInfo {
 	uint64_t min_add;      // frame of reference to add (0 when none)
@@ -102,6 +106,7 @@ __global__ void __launch_bounds__(kThreads) decode_kernel(DecodeArgs a) {
 	__shared__ uint64_t red[96];
 
 	using T = typename UIntOf<S>::type;
+	constexpr uint32_t kStageBytes = StageCfg<S, MODE>::kBytes;
 	const uint32_t tid = threadIdx.x;
 	const uint32_t lane = tid & 31u;
 	const uint32_t warp = tid >> 5;
@@ -213,7 +218,26 @@ __global__ void __launch_bounds__(kThreads) decode_kernel(DecodeArgs a) {
 				constant = (uint64_t)a.q_const[query];
 			}
 
-			if (MODE == kModeFlat && in.cnt == kVectorSize && (w <= 2u || w >= 28u)) {
+			if (MODE == kModeFlat && S < 8 && in.cnt == kVectorSize &&
+			    ((((uint64_t)a.out + (in.row - a.out_row0) * S) & 7ull) == 0)) {
+				// narrow types, full tile: a lane unpacks 8 / S adjacent values and leaves ONE 8-byte store
+				// (the kernel is bound by values per second here, not by bytes)
+				constexpr int VS = 8 / S;                          // values per store
+				constexpr int GROUPS = kVectorSize / kConsumers / VS;  // stores per thread
+				uint64_t *dst = (uint64_t *)((T *)a.out + (in.row - a.out_row0)) + tid;
+#pragma unroll
+				for (int j = 0; j < GROUPS; j++) {
+					const uint32_t i0 = (j * kConsumers + tid) * VS;
+					uint64_t packed = 0;
+#pragma unroll
+					for (int v = 0; v < VS; v++) {
+						const uint32_t bit = in.bit_base + (i0 + v) * w;  // S < 8: w <= 32
+						const uint64_t x = (uint64_t)(read_bits32(words32, bit) & mask32) + in.min_add;
+						packed |= (x & lo_set64(8 * S)) << (8 * S * v);
+					}
+					dst[j * kConsumers] = packed;
+				}
+			} else if (MODE == kModeFlat && in.cnt == kVectorSize && (w <= 2u || w >= 28u)) {
 				// full tile: the 8 fields of a thread are extracted back to back (independent shared loads in flight
 				// together), then stored; adjacent lanes still own adjacent values (coalesced 8-byte stores).
 				// Measured A/B on B200: -6 % time at w = 1, -1..3 % above 28 bits, but +5..10 % between (the store
@@ -301,7 +325,7 @@ __global__ void __launch_bounds__(kThreads) decode_kernel(DecodeArgs a) {
 template <int S, bool SIGNED, int MODE>
 cudaError_t launch_one(const DecodeArgs &args, int sm_count, cudaStream_t stream) {
 	static bool configured[64] = {};  // per device: the attribute is per (function, device)
-	const size_t smem = (size_t)kStages * kStageBytes;
+	const size_t smem = (size_t)kStages * StageCfg<S, MODE>::kBytes;
 	auto kernel = decode_kernel<S, SIGNED, MODE>;
 	int dev = 0;
 	cudaGetDevice(&dev);
@@ -316,9 +340,11 @@ cudaError_t launch_one(const DecodeArgs &args, int sm_count, cudaStream_t stream
 	if (n_jobs == 0) {
 		return cudaSuccess;
 	}
-	// 2 CTAs x 6 stages x 16 KiB per SM (measured: beats 3 x 4 and 4 x 3 for the write-heavy flat decode), all
-	// resident; fused scans: odd (see the kernel)
-	uint32_t grid = (uint32_t)sm_count * 2u;
+	// 6 stages x 16 KiB x 2 CTAs per SM for INT64 (measured: beats 3 x 4 and 4 x 3 for the write-heavy flat decode).
+	// The narrower types are bound by values per second, not bytes: their flat stages are smaller, so 4 (S = 4) or
+	// 6 (S <= 2) CTAs per SM hide the per-value latency.  All CTAs resident; fused scans: odd (see the kernel)
+	const uint32_t per_sm = MODE == kModeFlat ? (S == 8 ? 2u : (S == 4 ? 4u : 6u)) : 2u;
+	uint32_t grid = (uint32_t)sm_count * per_sm;
 	if (MODE != kModeFlat) {
 		grid = (grid - 1u) | 1u;
 	}
