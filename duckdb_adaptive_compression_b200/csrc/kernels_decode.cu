@@ -25,12 +25,27 @@ constexpr int kConsumerWarps = 8;
 constexpr int kConsumers = kConsumerWarps * 32;  // threads that unpack
 constexpr int kThreads = kConsumers + 32;        // + one producer warp that only feeds the TMA ring
 constexpr int kEmptyArrivals = 1;  // the consumers meet on a named barrier, one of them frees the stage
-constexpr int kStages = 6;
+constexpr int kMaxStages = 8;
 // Stage payload: a fused-scan chunk is <= 16 KiB for every type; a flat tile is 2048 values = at most 2048*S bytes
 // (slot width), so the narrower types stage less and fit more CTAs per SM.
 // + 16 B misalignment + 16 B pad (read_bits over-read)
+//
+// Consumer groups: the 8 consumer warps split into kGroups groups that take alternate stages, so that several tiles
+// are unpacked per CTA at a time.  That hides the per-tile latency chain (barrier wait -> stage info -> extract ->
+// store -> named barrier) which bounds the narrow types, whose 2048-value tiles carry few bytes (measured on B200,
+// flat decode: UTINYINT 0.365 -> 0.258 ms per 2^29 values with 4 groups, UINT32 +2-3 % with 2, INT64 neutral).
+// kStages must be a multiple of kGroups: a stage is then always drained by the same group, and a group's wait on
+// full_bar[s] can never run more than one phase ahead of the barrier (parity aliasing).
 template <int S, int MODE> struct StageCfg {
 	static constexpr uint32_t kBytes = (MODE == kModeFlat ? kVectorSize * (uint32_t)S : 16384u) + 32u;
+	static constexpr int kGroups = MODE != kModeFlat ? 1 : (S == 8 ? 1 : (S == 4 ? 2 : 4));
+	static constexpr int kStages = kGroups == 4 ? 8 : 6;
+#ifndef ADACOM_DECODE_MINB
+#define ADACOM_DECODE_MINB 4
+#endif
+	// resident CTAs per SM the kernel is compiled for (register cap) and launched with
+	static constexpr int kMinCtas = MODE != kModeFlat ? 2 : (S == 8 ? 2 : (S == 4 ? 4 : ADACOM_DECODE_MINB));
+	static_assert(kStages % kGroups == 0 && kStages <= kMaxStages, "a stage belongs to one consumer group");
 };
 
 struct StageInfo {
@@ -98,8 +113,11 @@ __device__ __forceinline__ Resolved resolve_unit(const DecodeArgs &a, uint32_t s
 }
 
 template <int S, bool SIGNED, int MODE>
-__global__ void __launch_bounds__(kThreads) decode_kernel(DecodeArgs a) {
+__global__ void __launch_bounds__(kThreads, StageCfg<S, MODE>::kMinCtas) decode_kernel(DecodeArgs a) {
 	extern __shared__ __align__(128) uint8_t stage_mem[];
+	constexpr int kStages = StageCfg<S, MODE>::kStages;
+	constexpr int kGroups = StageCfg<S, MODE>::kGroups;
+	constexpr int kGroupThreads = kConsumers / kGroups;
 	__shared__ __align__(8) uint64_t full_bar[kStages];
 	__shared__ __align__(8) uint64_t empty_bar[kStages];
 	__shared__ StageInfo infos[kStages];
@@ -190,14 +208,19 @@ __global__ void __launch_bounds__(kThreads) decode_kernel(DecodeArgs a) {
 			}
 		}
 		if (lane == 0) {
-			const uint32_t s = seq % kStages;
-			mbar_wait(&empty_bar[s], ((seq / kStages) & 1u) ^ 1u);
-			infos[s].done = 1;
-			mbar_arrive(&full_bar[s]);
+			for (int g = 0; g < kGroups; g++, seq++) {  // one sentinel per consumer group
+				const uint32_t s = seq % kStages;
+				mbar_wait(&empty_bar[s], ((seq / kStages) & 1u) ^ 1u);
+				infos[s].done = 1;
+				mbar_arrive(&full_bar[s]);
+			}
 		}
 	} else {
 		// ---------------- consumer warps ----------------
-		for (uint32_t it = 0;; it++) {
+		// kGroups independent groups take alternate stages (see StageCfg)
+		const uint32_t group = warp / (kConsumerWarps / kGroups);
+		const uint32_t gtid = tid - group * kGroupThreads;
+		for (uint32_t it = group;; it += kGroups) {
 			const uint32_t s = it % kStages;
 			mbar_wait(&full_bar[s], (it / kStages) & 1u);
 			const StageInfo in = infos[s];
@@ -223,11 +246,11 @@ __global__ void __launch_bounds__(kThreads) decode_kernel(DecodeArgs a) {
 				// narrow types, full tile: a lane unpacks 8 / S adjacent values and leaves ONE 8-byte store
 				// (the kernel is bound by values per second here, not by bytes)
 				constexpr int VS = 8 / S;                          // values per store
-				constexpr int GROUPS = kVectorSize / kConsumers / VS;  // stores per thread
-				uint64_t *dst = (uint64_t *)((T *)a.out + (in.row - a.out_row0)) + tid;
+				constexpr int GROUPS = kVectorSize / kGroupThreads / VS;  // stores per thread
+				uint64_t *dst = (uint64_t *)((T *)a.out + (in.row - a.out_row0)) + gtid;
 #pragma unroll
 				for (int j = 0; j < GROUPS; j++) {
-					const uint32_t i0 = (j * kConsumers + tid) * VS;
+					const uint32_t i0 = (j * kGroupThreads + gtid) * VS;
 					uint64_t packed = 0;
 #pragma unroll
 					for (int v = 0; v < VS; v++) {
@@ -235,36 +258,36 @@ __global__ void __launch_bounds__(kThreads) decode_kernel(DecodeArgs a) {
 						const uint64_t x = (uint64_t)(read_bits32(words32, bit) & mask32) + in.min_add;
 						packed |= (x & lo_set64(8 * S)) << (8 * S * v);
 					}
-					dst[j * kConsumers] = packed;
+					dst[j * kGroupThreads] = packed;
 				}
 			} else if (MODE == kModeFlat && in.cnt == kVectorSize && (w <= 2u || w >= 28u)) {
 				// full tile: the 8 fields of a thread are extracted back to back (independent shared loads in flight
 				// together), then stored; adjacent lanes still own adjacent values (coalesced 8-byte stores).
 				// Measured A/B on B200: -6 % time at w = 1, -1..3 % above 28 bits, but +5..10 % between (the store
 				// bursts of the 3..27-bit tiles collide), hence the width window.
-				constexpr int PER = kVectorSize / kConsumers;
-				T *dst = (T *)a.out + (in.row - a.out_row0) + tid;
+				constexpr int PER = kVectorSize / kGroupThreads;
+				T *dst = (T *)a.out + (in.row - a.out_row0) + gtid;
 				uint64_t x[PER];
 				if (narrow) {
 #pragma unroll
 					for (int j = 0; j < PER; j++) {
-						const uint32_t bit = in.bit_base + (j * kConsumers + tid) * w;
+						const uint32_t bit = in.bit_base + (j * kGroupThreads + gtid) * w;
 						x[j] = (uint64_t)(read_bits32(words32, bit) & mask32) + in.min_add;
 					}
 				} else {
 #pragma unroll
 					for (int j = 0; j < PER; j++) {
-						const uint32_t bit = in.bit_base + (j * kConsumers + tid) * w;
+						const uint32_t bit = in.bit_base + (j * kGroupThreads + gtid) * w;
 						x[j] = (read_bits64(words, bit) & mask64) + in.min_add;
 					}
 				}
 #pragma unroll
 				for (int j = 0; j < PER; j++) {
-					dst[j * kConsumers] = (T)x[j];
+					dst[j * kGroupThreads] = (T)x[j];
 				}
 			} else
-			for (uint32_t base = 0; base < in.cnt; base += kConsumers) {
-				const uint32_t i = base + tid;
+			for (uint32_t base = 0; base < in.cnt; base += kGroupThreads) {
+				const uint32_t i = base + gtid;
 				const bool valid = i < in.cnt;
 				uint64_t x = 0;
 				if (valid) {
@@ -291,7 +314,7 @@ __global__ void __launch_bounds__(kThreads) decode_kernel(DecodeArgs a) {
 					if (a.bitmap32 != nullptr) {
 						uint32_t ballot = __ballot_sync(0xffffffffu, pass);
 						if (lane == 0 && ballot) {
-							uint64_t bit0 = in.row - a.out_row0 + base + (tid & ~31u);
+							uint64_t bit0 = in.row - a.out_row0 + base + (gtid & ~31u);
 							uint32_t sh = (uint32_t)(bit0 & 31u);
 							atomicOr(a.bitmap32 + (bit0 >> 5), ballot << sh);
 							if (sh) {
@@ -310,8 +333,17 @@ __global__ void __launch_bounds__(kThreads) decode_kernel(DecodeArgs a) {
 			// Keep the consumer warps of a CTA in lockstep (named barrier 1, the producer is not involved): their
 			// stores then hit the same 16 KiB output tile close in time, which measured 5-15 % faster on HBM3e
 			// than letting the warps drift apart.
-			asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
-			if (tid == 0) {
+			// (immediate barrier ids: a register id makes ptxas reserve all 16 named barriers)
+			if (kGroups == 1 || group == 0) {
+				asm volatile("bar.sync 1, %0;" ::"n"(kGroupThreads) : "memory");
+			} else if (group == 1) {
+				asm volatile("bar.sync 2, %0;" ::"n"(kGroupThreads) : "memory");
+			} else if (group == 2) {
+				asm volatile("bar.sync 3, %0;" ::"n"(kGroupThreads) : "memory");
+			} else {
+				asm volatile("bar.sync 4, %0;" ::"n"(kGroupThreads) : "memory");
+			}
+			if (gtid == 0) {
 				mbar_arrive(&empty_bar[s]);  // stage s (payload and info) is free again
 			}
 		}
@@ -324,8 +356,8 @@ __global__ void __launch_bounds__(kThreads) decode_kernel(DecodeArgs a) {
 
 template <int S, bool SIGNED, int MODE>
 cudaError_t launch_one(const DecodeArgs &args, int sm_count, cudaStream_t stream) {
-	static bool configured[64] = {};  // per device: the attribute is per (function, device)
-	const size_t smem = (size_t)kStages * StageCfg<S, MODE>::kBytes;
+	static int configured[64] = {};  // per device: the attribute is per (function, device); holds resident CTAs / SM
+	const size_t smem = (size_t)StageCfg<S, MODE>::kStages * StageCfg<S, MODE>::kBytes;
 	auto kernel = decode_kernel<S, SIGNED, MODE>;
 	int dev = 0;
 	cudaGetDevice(&dev);
@@ -334,7 +366,12 @@ cudaError_t launch_one(const DecodeArgs &args, int sm_count, cudaStream_t stream
 		if (e != cudaSuccess) {
 			return e;
 		}
-		configured[dev & 63] = true;
+		int resident = 0;
+		e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, kernel, kThreads, smem);
+		if (e != cudaSuccess) {
+			return e;
+		}
+		configured[dev & 63] = resident > 0 ? resident : 1;
 	}
 	const uint32_t n_jobs = MODE == kModeFlat ? args.n_jobs : args.n_units * kScanParts;
 	if (n_jobs == 0) {
@@ -343,7 +380,9 @@ cudaError_t launch_one(const DecodeArgs &args, int sm_count, cudaStream_t stream
 	// 6 stages x 16 KiB x 2 CTAs per SM for INT64 (measured: beats 3 x 4 and 4 x 3 for the write-heavy flat decode).
 	// The narrower types are bound by values per second, not bytes: their flat stages are smaller, so 4 (S = 4) or
 	// 6 (S <= 2) CTAs per SM hide the per-value latency.  All CTAs resident; fused scans: odd (see the kernel)
-	const uint32_t per_sm = MODE == kModeFlat ? (S == 8 ? 2u : (S == 4 ? 4u : 6u)) : 2u;
+	// Never more CTAs than are resident at once: a persistent grid with a second wave doubles the tail.
+	const uint32_t want_per_sm = (uint32_t)StageCfg<S, MODE>::kMinCtas;
+	const uint32_t per_sm = want_per_sm < (uint32_t)configured[dev & 63] ? want_per_sm : (uint32_t)configured[dev & 63];
 	uint32_t grid = (uint32_t)sm_count * per_sm;
 	if (MODE != kModeFlat) {
 		grid = (grid - 1u) | 1u;
