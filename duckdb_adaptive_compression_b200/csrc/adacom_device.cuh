@@ -52,6 +52,7 @@ struct DescQ {
 	__device__ __forceinline__ uint64_t packed_ptr() const { return ((uint64_t)q0.w << 32) | q0.z; }
 	__device__ __forceinline__ uint64_t word_offset() const { return ((uint64_t)q1.y << 32) | q1.x; }
 	__device__ __forceinline__ uint64_t min_factor() const { return ((uint64_t)q1.w << 32) | q1.z; }
+	__device__ __forceinline__ uint64_t max_factor() const { return ((uint64_t)q2.y << 32) | q2.x; }
 	__device__ __forceinline__ uint32_t count() const { return q2.z; }
 	__device__ __forceinline__ uint32_t extent() const { return q3.x; }
 	__device__ __forceinline__ uint32_t width() const { return q3.z & 0xffu; }
@@ -77,13 +78,16 @@ struct Job {
 	uint32_t k;
 };
 
-// Values per scan chunk for a payload of width w: the largest multiple of 128 values whose packed
-// bytes (16*w*floor(1024/w)) fit one 16 KiB stage and stay 16-byte aligned (cp.async.bulk rule).
+// Values per scan chunk for a payload of width w: the largest multiple of 128 values whose packed bytes
+// (16*w*floor(1024/w)) fit one 16 KiB stage and stay 16-byte aligned (cp.async.bulk rule).  From 43 bits up that
+// would be 46 .. 32 periods of 64 values -- a poor fit for the period-per-lane scan kernels, whose warps take 32
+// periods at a time (measured: odd widths 10-15 % behind the even ones) -- so those widths use exactly 32 periods
+// (2048 values, 10.75 .. 16 KiB).  Below 43 bits the 16 KiB chunk wins (measured both ways).
 __host__ __device__ inline uint32_t scan_chunk_values(uint32_t w) {
-	return 128u * (1024u / w);
+	return w >= 43u ? 2048u : 128u * (1024u / w);
 }
-// A segment holds <= 262136 payload bytes, a chunk >= 15.4 KiB: never more than 16 chunks per segment
-// (checked for every (S, w) in tests/test_capi_boundary.py).
+// A segment holds <= 262136 payload bytes, a chunk >= 15.4 KiB (or 2048 values of an 8-byte type): never more
+// than 16 chunks per segment (checked for every (S, w) in tests/test_capi_boundary.py).
 constexpr uint32_t kScanParts = 16;
 
 __host__ __device__ inline uint64_t lo_set64(uint32_t len) {

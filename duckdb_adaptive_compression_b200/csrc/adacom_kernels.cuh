@@ -54,7 +54,7 @@ struct ScanSumArgs {
 	int literal = 0;
 	int type_size = 8;
 	int is_signed = 1;
-	Agg *agg = nullptr;
+	Agg *agg = nullptr;                   // zeroed by the caller, one atomic triple per CTA
 };
 
 cudaError_t launch_scan_sum_fields(const ScanSumArgs &args, int sm_count, cudaStream_t stream);

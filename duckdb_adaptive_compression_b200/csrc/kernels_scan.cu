@@ -62,7 +62,7 @@ __device__ __forceinline__ uint32_t dp2a_ones(uint32_t x, uint32_t acc) {
 
 // Periods in a full chunk of width w.
 __host__ __device__ constexpr int periods_per_chunk(int w) {
-	return 2 * gcd64(w) * (1024 / w);
+	return (w >= 43 ? 2048 : 128 * (1024 / w)) / (64 / gcd64(w));
 }
 
 // A period is split into Q sub-periods (power of two) so that a full chunk offers at least one piece of work
@@ -200,7 +200,7 @@ __device__ __forceinline__ void sum_chunk_fields(const uint64_t *words, uint32_t
 	}
 }
 
-// A full chunk of width w holds 2 * gcd(w,64) * floor(1024/w) periods.  The period-per-lane path needs at
+// A full chunk of width w holds periods_per_chunk(w) periods.  The period-per-lane path needs at
 // least one period per consumer thread to keep all warps busy; the other widths (odd w >= 9, ...) have a
 // large per-value instruction budget (0.7 * w) and use the fully parallel lane-per-value extraction.
 __host__ __device__ constexpr bool period_path(int w) {
@@ -224,6 +224,46 @@ __device__ __forceinline__ void sum_chunk_generic(const uint64_t *words, uint32_
 #pragma unroll 4
 		for (uint32_t i = tid; i < cnt; i += kConsumers) {
 			acc.add<false>(read_bits64(words, i * w) & mask);
+		}
+	}
+}
+
+// not re-packed: the payload is the slot array itself -- aligned loads of T, sign/zero-extended like DuckDB reads
+// them; `add` (literal mode only) is added before the truncation to T (succinct.cpp:138-143)
+template <typename T, typename WideT>
+__device__ __forceinline__ void sum_raw_typed(const uint8_t *p, uint32_t cnt, uint64_t add, uint32_t tid, Acc96 &acc) {
+	const T *v = (const T *)p;
+	constexpr bool kSigned = ((WideT)-1) < 0;
+	if (sizeof(T) == 8) {
+#pragma unroll 4
+		for (uint32_t i = tid; i < cnt; i += kConsumers) {
+			acc.add<kSigned>((uint64_t)(WideT)(T)(v[i] + (T)add));
+		}
+	} else {
+		WideT s = 0;  // <= 2^14 values of <= 32 bits per thread and chunk: no overflow
+#pragma unroll 4
+		for (uint32_t i = tid; i < cnt; i += kConsumers) {
+			s += (WideT)(T)(v[i] + (T)add);
+		}
+		acc.add<kSigned>((uint64_t)s);
+	}
+}
+
+__device__ __forceinline__ void sum_raw_slots(const uint8_t *p, uint32_t cnt, uint64_t add, int type_size, int is_signed,
+                                              uint32_t tid, Acc96 &acc, Acc96 &sacc) {
+	if (is_signed) {
+		switch (type_size) {
+		case 1: sum_raw_typed<int8_t, int64_t>(p, cnt, add, tid, sacc); break;
+		case 2: sum_raw_typed<int16_t, int64_t>(p, cnt, add, tid, sacc); break;
+		case 4: sum_raw_typed<int32_t, int64_t>(p, cnt, add, tid, sacc); break;
+		default: sum_raw_typed<int64_t, int64_t>(p, cnt, add, tid, sacc); break;
+		}
+	} else {
+		switch (type_size) {
+		case 1: sum_raw_typed<uint8_t, uint64_t>(p, cnt, add, tid, acc); break;
+		case 2: sum_raw_typed<uint16_t, uint64_t>(p, cnt, add, tid, acc); break;
+		case 4: sum_raw_typed<uint32_t, uint64_t>(p, cnt, add, tid, acc); break;
+		default: sum_raw_typed<uint64_t, uint64_t>(p, cnt, add, tid, acc); break;
 		}
 	}
 }
@@ -256,15 +296,19 @@ __device__ __forceinline__ uint64_t extend_runtime(uint64_t x, int type_size, in
 	return is_signed ? (uint64_t)(((int64_t)(x << shift)) >> shift) : ((x << shift) >> shift);
 }
 
-// sum(decoded) == sum(fields) + count * extend(min) iff [min, min + 2^w - 1] stays inside one sign /
-// truncation zone of T
-__device__ __forceinline__ bool linear_zone_dev(uint64_t min_factor, uint32_t width, bool repacked, int type_size,
-                                                int is_signed) {
+// sum(decoded) == sum(fields) + count * extend(min) iff every decoded value min + field stays inside the sign /
+// truncation zone of T that min lies in.  Fields never exceed max - min when the descriptor carries the analyzed
+// maximum (they are (v - min) & mask for v in [min, max]); otherwise the bound is the full field range 2^w - 1.
+__device__ __forceinline__ bool linear_zone_dev(uint64_t min_factor, uint64_t max_factor, bool analyzed, uint32_t width,
+                                                bool repacked, int type_size, int is_signed) {
 	if (!repacked || width >= 64) {
 		return false;
 	}
 	const uint64_t lo = min_factor == ~0ull ? 0 : min_factor;
-	const uint64_t range = (1ull << width) - 1;
+	uint64_t range = (1ull << width) - 1;
+	if (analyzed && min_factor != ~0ull && max_factor >= lo && max_factor - lo <= range) {
+		range = max_factor - lo;
+	}
 	const uint64_t hi = lo + range;
 	if (hi < lo) {
 		return false;
@@ -307,10 +351,15 @@ __device__ __forceinline__ ResolvedChunk resolve_chunk(const ScanSumArgs &a, uin
 	const uint32_t byte_base = (uint32_t)(src - r.src16);
 	r.bytes = (byte_base + ((cnt * w + 7u) >> 3) + 15u) & ~15u;
 	const bool add = (mn != ~0ull) && (repacked || a.literal);  // succinct.cpp:138-140 (+ Q1 in literal mode)
-	const uint32_t fast = linear_zone_dev(mn, w, repacked, a.type_size, a.is_signed) ? 1u : 0u;
+	// fast: 1 = field sums (linear zone), 2 = raw slots of T (not re-packed), 0 = generic per-value extraction
+	const uint32_t fast = !repacked ? 2u
+	                                : (linear_zone_dev(mn, dq.max_factor(), dq.state() & kSegAnalyzed, w, repacked,
+	                                                   a.type_size, a.is_signed)
+	                                       ? 1u
+	                                       : 0u);
 	uint64_t ext = 0;
 	uint32_t neg = 0;
-	if (fast) {
+	if (fast == 1u) {
 		if (add) {
 			ext = extend_runtime(mn, a.type_size, a.is_signed);
 			neg = a.is_signed && (int64_t)ext < 0;
@@ -411,7 +460,11 @@ __global__ void __launch_bounds__(kThreads, 3) scan_sum_fields_kernel(const Scan
 				break;
 			}
 			const uint64_t *words = (const uint64_t *)(stage_mem + s * kStageBytes);
-			if (in.fast) {
+			if (in.fast == 2u) {
+				// raw slots of T (segment not re-packed, Q1: `min` is only added in literal mode)
+				sum_raw_slots((const uint8_t *)words + (in.bit_base >> 3), in.cnt, in.ext_min, a.type_size, a.is_signed, tid,
+				              acc, sacc);
+			} else if (in.fast) {
 				WidthSwitch<1>::run(in.w, words, in.cnt, tid, acc);
 				if (tid == 0) {
 					const uint64_t c = in.cnt;

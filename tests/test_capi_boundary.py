@@ -81,6 +81,6 @@ def test_a_segment_never_has_more_than_16_scan_chunks():
     for size in (1, 2, 4, 8):
         cap = 262136 // size
         for w in range(1, 8 * size + 1):
-            gran = 128 * (1024 // w)
+            gran = 2048 if w >= 43 else 128 * (1024 // w)
             worst = max(worst, -(-cap // gran))
     assert worst == 16
