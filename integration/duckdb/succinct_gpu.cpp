@@ -1,0 +1,404 @@
+// succinct_gpu.cpp -- see succinct_gpu.hpp.  Compiled against the reference's headers; forwards every
+// CompressionFunction slot of the succinct codec to the C ABI in include/adacom_gpu.h.
+#include "succinct_gpu.hpp"
+
+#include "adacom_gpu.h"
+#include "duckdb/common/types/null_value.hpp"
+#include "duckdb/common/types/vector.hpp"
+#include "duckdb/main/config.hpp"
+#include "duckdb/storage/buffer_manager.hpp"
+#include "duckdb/storage/segment/uncompressed.hpp"
+#include "duckdb/storage/statistics/numeric_statistics.hpp"
+#include "duckdb/storage/table/append_state.hpp"
+#include "duckdb/storage/table/column_data_checkpointer.hpp"
+#include "duckdb/storage/table/column_segment.hpp"
+#include "duckdb/storage/table/scan_state.hpp"
+
+#include <cstring>
+#include <mutex>
+#include <new>
+
+namespace duckdb {
+
+namespace {
+
+//===--------------------------------------------------------------------===//
+// Runtime: one codec context per process (one GPU), errors -> the reference's two exception types
+//===--------------------------------------------------------------------===//
+adacom_ctx *GpuContext() {
+	static std::once_flag once;
+	static adacom_ctx *ctx = nullptr;
+	static adacom_status status = ADACOM_OK;
+	std::call_once(once, [] { status = adacom_ctx_create(/*device=*/0, &ctx); });
+	if (status != ADACOM_OK) {
+		// no CPU fallback: without the GPU library the codec is unavailable, loudly
+		throw InternalException("succinct GPU codec unavailable: %s", adacom_last_error(nullptr));
+	}
+	return ctx;
+}
+
+void Check(adacom_status st, const char *what) {
+	if (st == ADACOM_OK) {
+		return;
+	}
+	if (st == ADACOM_ERR_NOMEM) {
+		throw std::bad_alloc(); // sdsl memory_management.hpp:326-329
+	}
+	throw InternalException("succinct GPU codec, %s: %s", what, adacom_last_error(GpuContext()));
+}
+
+adacom_ptype GpuTypeOf(PhysicalType type) {
+	// the enumerators of adacom_ptype ARE duckdb::PhysicalType values (types.hpp), checked here
+	static_assert((int)PhysicalType::UINT8 == ADACOM_UINT8 && (int)PhysicalType::INT8 == ADACOM_INT8 &&
+	                  (int)PhysicalType::UINT16 == ADACOM_UINT16 && (int)PhysicalType::INT16 == ADACOM_INT16 &&
+	                  (int)PhysicalType::UINT32 == ADACOM_UINT32 && (int)PhysicalType::INT32 == ADACOM_INT32 &&
+	                  (int)PhysicalType::UINT64 == ADACOM_UINT64 && (int)PhysicalType::INT64 == ADACOM_INT64,
+	              "adacom_ptype mirrors duckdb::PhysicalType");
+	return (adacom_ptype)(int)type;
+}
+
+//===--------------------------------------------------------------------===//
+// Per-segment state (ColumnSegment::segment_state): host slots while appending, device column afterwards
+//===--------------------------------------------------------------------===//
+struct SuccinctGpuSegmentState : public CompressedSegmentState {
+	~SuccinctGpuSegmentState() override {
+		if (column) {
+			adacom_column_destroy(column);
+		}
+	}
+
+	//! one-segment device column (raw slots and, once compacted, the packed payload)
+	adacom_column *column = nullptr;
+	//! the slot-width array of an open segment (what succinct_vec holds in the reference, column_segment.cpp:101-105)
+	unique_ptr<data_t[]> slots;
+	//! values of `slots` that are already on the device
+	idx_t resident = 0;
+	//! serialises upload / re-encode against concurrent scans (the reference's bit_compression_lock)
+	std::mutex lock;
+};
+
+SuccinctGpuSegmentState &StateOf(ColumnSegment &segment) {
+	auto state = segment.GetSegmentState();
+	if (!state) {
+		throw InternalException("succinct GPU codec: segment without device state");
+	}
+	return (SuccinctGpuSegmentState &)*state;
+}
+
+//! make the first segment.count slots resident on the device (no-op once uploaded)
+void EnsureResident(ColumnSegment &segment, SuccinctGpuSegmentState &state) {
+	if (state.column && state.resident == segment.count) {
+		return;
+	}
+	if (state.column) { // the segment grew since the last upload: rebuild (appends and scans rarely interleave)
+		adacom_column_destroy(state.column);
+		state.column = nullptr;
+	}
+	uint64_t count = segment.count;
+	auto capacity = (uint32_t)(segment.SegmentSize() / segment.type_size);
+	Check(adacom_column_create(GpuContext(), GpuTypeOf(segment.type.InternalType()), 1, &count, capacity, &state.column),
+	      "column_create");
+	if (count) {
+		Check(adacom_column_upload_raw(state.column, state.slots.get(), 0, count), "upload");
+	}
+	state.resident = count;
+}
+
+unique_ptr<CompressedSegmentState> SuccinctGpuInitSegment(ColumnSegment &segment, block_id_t block_id) {
+	auto state = make_unique<SuccinctGpuSegmentState>();
+	state->slots = unique_ptr<data_t[]>(new data_t[segment.SegmentSize()]);
+	return move(state);
+}
+
+//===--------------------------------------------------------------------===//
+// Analyze (checkpoint entry points; the reference only counts rows, succinct.cpp:19-42)
+//===--------------------------------------------------------------------===//
+struct SuccinctGpuAnalyzeState : public AnalyzeState {
+	idx_t count = 0;
+	uint64_t min_factor = NumericLimits<uint64_t>::Maximum();
+	uint64_t max_factor = 0;
+};
+
+unique_ptr<AnalyzeState> SuccinctGpuInitAnalyze(ColumnData &col_data, PhysicalType type) {
+	return make_unique<SuccinctGpuAnalyzeState>();
+}
+
+template <class T>
+bool SuccinctGpuAnalyze(AnalyzeState &state_p, Vector &input, idx_t count) {
+	auto &state = (SuccinctGpuAnalyzeState &)state_p;
+	UnifiedVectorFormat vdata;
+	input.ToUnifiedFormat(count, vdata);
+	auto values = (T *)vdata.data;
+	for (idx_t i = 0; i < count; i++) {
+		auto idx = vdata.sel->get_index(i);
+		if (vdata.validity.RowIsValid(idx)) { // NULLs do not take part in min/max (succinct.cpp:284-292)
+			state.min_factor = MinValue<uint64_t>(state.min_factor, uint64_t(values[idx]));
+			state.max_factor = MaxValue<uint64_t>(state.max_factor, uint64_t(values[idx]));
+		}
+	}
+	state.count += count;
+	return true;
+}
+
+//! score = the bytes the column will occupy: 9 + 8 * ceil(n * w / 64) per segment (sdsl size_in_bytes)
+template <class T>
+idx_t SuccinctGpuFinalAnalyze(AnalyzeState &state_p) {
+	auto &state = (SuccinctGpuAnalyzeState &)state_p;
+	uint64_t range = state.max_factor >= state.min_factor ? state.max_factor - state.min_factor : 0;
+	idx_t width = 1;
+	while (width < 64 && (range >> width) != 0) {
+		width++;
+	}
+	if (width >= 8 * sizeof(T)) {
+		return sizeof(T) * state.count; // no re-pack (column_segment.cpp:363)
+	}
+	idx_t per_segment = Storage::BLOCK_SIZE / sizeof(T);
+	idx_t segments = (state.count + per_segment - 1) / per_segment;
+	return 9 * segments + 8 * ((state.count * width + 63) / 64);
+}
+
+//===--------------------------------------------------------------------===//
+// Compress (checkpoint entry points): append into transient succinct segments, flush each full one
+//===--------------------------------------------------------------------===//
+struct SuccinctGpuCompressState : public CompressionState {
+	explicit SuccinctGpuCompressState(ColumnDataCheckpointer &checkpointer_p) : checkpointer(checkpointer_p) {
+		NewSegment(checkpointer.GetRowGroup().start);
+	}
+
+	void NewSegment(idx_t row_start) {
+		segment = ColumnSegment::CreateTransientSegment(checkpointer.GetDatabase(), checkpointer.GetType(), row_start);
+		segment->InitializeAppend(append_state);
+	}
+	void Flush() {
+		idx_t bytes = segment->FinalizeAppend(append_state);
+		checkpointer.GetCheckpointState().FlushSegment(move(segment), bytes);
+	}
+
+	ColumnDataCheckpointer &checkpointer;
+	unique_ptr<ColumnSegment> segment;
+	ColumnAppendState append_state;
+};
+
+unique_ptr<CompressionState> SuccinctGpuInitCompression(ColumnDataCheckpointer &checkpointer,
+                                                        unique_ptr<AnalyzeState> state) {
+	return make_unique<SuccinctGpuCompressState>(checkpointer);
+}
+
+void SuccinctGpuCompress(CompressionState &state_p, Vector &data, idx_t count) {
+	auto &state = (SuccinctGpuCompressState &)state_p;
+	UnifiedVectorFormat vdata;
+	data.ToUnifiedFormat(count, vdata);
+	idx_t offset = 0;
+	while (count > 0) {
+		idx_t appended = state.segment->Append(state.append_state, vdata, offset, count);
+		offset += appended;
+		count -= appended;
+		if (count > 0) { // segment full: hand it to the checkpoint state and open the next one
+			idx_t next_start = state.segment->start + state.segment->count;
+			state.Flush();
+			state.NewSegment(next_start);
+		}
+	}
+}
+
+void SuccinctGpuFinalizeCompress(CompressionState &state_p) {
+	auto &state = (SuccinctGpuCompressState &)state_p;
+	state.Flush();
+}
+
+//===--------------------------------------------------------------------===//
+// Scan: one batched decode of the segment per scan state, then 2048-value slices
+//===--------------------------------------------------------------------===//
+struct SuccinctGpuScanState : public SegmentScanState {
+	//! the decoded segment (count * sizeof(T) bytes), filled by the first scan call
+	unique_ptr<data_t[]> decoded;
+	idx_t decoded_count = 0;
+};
+
+unique_ptr<SegmentScanState> SuccinctGpuInitScan(ColumnSegment &segment) {
+	return make_unique<SuccinctGpuScanState>();
+}
+
+template <class T>
+void SuccinctGpuScanPartial(ColumnSegment &segment, ColumnScanState &state, idx_t scan_count, Vector &result,
+                            idx_t result_offset) {
+	auto &seg_state = StateOf(segment);
+	auto start = segment.GetRelativeIndex(state.row_index);
+	result.SetVectorType(VectorType::FLAT_VECTOR);
+	auto target = FlatVector::GetData(result);
+	auto scan = (SuccinctGpuScanState *)state.scan_state.get();
+	std::lock_guard<std::mutex> guard(seg_state.lock);
+	EnsureResident(segment, seg_state);
+	if (!scan) { // no scan state (index fetch paths): decode just the requested slice
+		Check(adacom_scan_partial(seg_state.column, 0, start, scan_count, 0, target, result_offset, 0), "scan_partial");
+		return;
+	}
+	if (scan->decoded_count != segment.count) { // first pull of this segment: one launch decodes all of it
+		scan->decoded = unique_ptr<data_t[]>(new data_t[segment.count * sizeof(T) + 8]);
+		Check(adacom_decode(seg_state.column, 0, 1, 0, scan->decoded.get(), 0), "decode");
+		scan->decoded_count = segment.count;
+	}
+	memcpy(target + result_offset * sizeof(T), scan->decoded.get() + start * sizeof(T), scan_count * sizeof(T));
+}
+
+template <class T>
+void SuccinctGpuScan(ColumnSegment &segment, ColumnScanState &state, idx_t scan_count, Vector &result) {
+	SuccinctGpuScanPartial<T>(segment, state, scan_count, result, 0);
+}
+
+//===--------------------------------------------------------------------===//
+// Fetch (the intended semantics of succinct.cpp:244-260: ONE value, the one at row_id)
+//===--------------------------------------------------------------------===//
+template <class T>
+void SuccinctGpuFetchRow(ColumnSegment &segment, ColumnFetchState &state, row_t row_id, Vector &result,
+                         idx_t result_idx) {
+	auto &seg_state = StateOf(segment);
+	std::lock_guard<std::mutex> guard(seg_state.lock);
+	EnsureResident(segment, seg_state);
+	uint32_t seg = 0, row = (uint32_t)row_id;
+	Check(adacom_fetch_rows(seg_state.column, 1, &seg, &row, 0, FlatVector::GetData(result) + result_idx * sizeof(T), 0),
+	      "fetch_rows");
+}
+
+//===--------------------------------------------------------------------===//
+// Append (succinct.cpp:262-330): slots on the host while the segment is open, min/max kept on the segment
+//===--------------------------------------------------------------------===//
+unique_ptr<CompressionAppendState> SuccinctGpuInitAppend(ColumnSegment &segment) {
+	auto &buffer_manager = BufferManager::GetBufferManager(segment.db);
+	return make_unique<CompressionAppendState>(buffer_manager.Pin(segment.block));
+}
+
+template <class T>
+idx_t SuccinctGpuAppend(CompressionAppendState &append_state, ColumnSegment &segment, SegmentStatistics &stats,
+                        UnifiedVectorFormat &data, idx_t offset, idx_t count) {
+	auto &seg_state = StateOf(segment);
+	idx_t capacity = segment.SegmentSize() / sizeof(T);
+	idx_t copied = MinValue<idx_t>(count, capacity - segment.count);
+	auto source = (T *)data.data;
+	auto target = (T *)seg_state.slots.get() + segment.count;
+	uint64_t min_factor = NumericLimits<uint64_t>::Maximum(), max_factor = 0;
+	for (idx_t i = 0; i < copied; i++) {
+		auto idx = data.sel->get_index(offset + i);
+		if (data.validity.RowIsValid(idx)) {
+			NumericStatistics::Update<T>(stats, source[idx]);
+			target[i] = source[idx];
+			min_factor = MinValue<uint64_t>(min_factor, uint64_t(source[idx]));
+			max_factor = MaxValue<uint64_t>(max_factor, uint64_t(source[idx]));
+		} else {
+			target[i] = NullValue<T>(); // the NULL gap (succinct.cpp:288-292)
+		}
+	}
+	segment.UpdateMinFactor(min_factor);
+	segment.UpdateMaxFactor(max_factor);
+	segment.count += copied; // Q6: rows copied, not rows requested
+	return copied;
+}
+
+//! the segment is complete: move it to the device; eager mode compacts right away (column_segment.cpp:273-293)
+template <class T>
+idx_t SuccinctGpuFinalizeAppend(ColumnSegment &segment, SegmentStatistics &stats) {
+	auto &seg_state = StateOf(segment);
+	{
+		std::lock_guard<std::mutex> guard(seg_state.lock);
+		EnsureResident(segment, seg_state);
+	}
+	if (!DBConfig::GetConfig(segment.db).adaptive_succinct_compression_enabled) {
+		SuccinctGpuFun::Compact(segment, /*zero_extended_minmax=*/false);
+	}
+	return segment.count * sizeof(T);
+}
+
+template <class T>
+CompressionFunction SuccinctGpuGetFunction(PhysicalType type) {
+	return CompressionFunction(CompressionType::COMPRESSION_SUCCINCT, type, SuccinctGpuInitAnalyze,
+	                           SuccinctGpuAnalyze<T>, SuccinctGpuFinalAnalyze<T>, SuccinctGpuInitCompression,
+	                           SuccinctGpuCompress, SuccinctGpuFinalizeCompress, SuccinctGpuInitScan, SuccinctGpuScan<T>,
+	                           SuccinctGpuScanPartial<T>, SuccinctGpuFetchRow<T>, UncompressedFunctions::EmptySkip,
+	                           SuccinctGpuInitSegment, SuccinctGpuInitAppend, SuccinctGpuAppend<T>,
+	                           SuccinctGpuFinalizeAppend<T>, nullptr);
+}
+
+} // namespace
+
+//===--------------------------------------------------------------------===//
+// Public: function table + the policy-side bodies
+//===--------------------------------------------------------------------===//
+CompressionFunction SuccinctGpuFun::GetFunction(PhysicalType type) {
+	switch (type) {
+	case PhysicalType::INT8:
+		return SuccinctGpuGetFunction<int8_t>(type);
+	case PhysicalType::UINT8:
+		return SuccinctGpuGetFunction<uint8_t>(type);
+	case PhysicalType::INT16:
+		return SuccinctGpuGetFunction<int16_t>(type);
+	case PhysicalType::UINT16:
+		return SuccinctGpuGetFunction<uint16_t>(type);
+	case PhysicalType::INT32:
+		return SuccinctGpuGetFunction<int32_t>(type);
+	case PhysicalType::UINT32:
+		return SuccinctGpuGetFunction<uint32_t>(type);
+	case PhysicalType::INT64:
+		return SuccinctGpuGetFunction<int64_t>(type);
+	case PhysicalType::UINT64:
+		return SuccinctGpuGetFunction<uint64_t>(type);
+	default: // INT128 included (Q6): stays uncompressed
+		throw InternalException("Unsupported type for SuccinctGpuFun::GetFunction");
+	}
+}
+
+bool SuccinctGpuFun::TypeIsSupported(PhysicalType type) {
+	switch (type) {
+	case PhysicalType::INT8:
+	case PhysicalType::UINT8:
+	case PhysicalType::INT16:
+	case PhysicalType::UINT16:
+	case PhysicalType::INT32:
+	case PhysicalType::UINT32:
+	case PhysicalType::INT64:
+	case PhysicalType::UINT64:
+		return true;
+	default:
+		return false;
+	}
+}
+
+idx_t SuccinctGpuFun::Compact(ColumnSegment &segment, bool zero_extended_minmax) {
+	auto &seg_state = StateOf(segment);
+	std::lock_guard<std::mutex> guard(seg_state.lock);
+	EnsureResident(segment, seg_state);
+	int flags = 0;
+	if (DBConfig::GetConfig(segment.db).succinct_padded_to_next_byte_enabled) {
+		flags |= ADACOM_PADDED; // column_segment.cpp:356-359
+	}
+	if (zero_extended_minmax) {
+		flags |= ADACOM_ZERO_EXT_MINMAX; // BitCompressFromUncompressed, column_segment.cpp:390-400
+	}
+	Check(adacom_analyze(seg_state.column, 0, 1, flags, nullptr, 0), "analyze");
+	Check(adacom_encode(seg_state.column, 0, 1, flags), "encode");
+	segment.SetBitCompressed();
+	uint64_t bytes = 0;
+	Check(adacom_column_data_size(seg_state.column, 0, 1, &bytes), "data_size");
+	return bytes;
+}
+
+idx_t SuccinctGpuFun::Uncompact(ColumnSegment &segment) {
+	auto &seg_state = StateOf(segment);
+	std::lock_guard<std::mutex> guard(seg_state.lock);
+	EnsureResident(segment, seg_state);
+	Check(adacom_uncompact(seg_state.column, 0, 1, 0), "uncompact");
+	segment.SetBitUncompressed();
+	return segment.SegmentSize();
+}
+
+idx_t SuccinctGpuFun::DataSize(ColumnSegment &segment) {
+	auto &seg_state = StateOf(segment);
+	std::lock_guard<std::mutex> guard(seg_state.lock);
+	if (!seg_state.column) {
+		return segment.SegmentSize();
+	}
+	uint64_t bytes = 0;
+	Check(adacom_column_data_size(seg_state.column, 0, 1, &bytes), "data_size");
+	return bytes;
+}
+
+} // namespace duckdb
