@@ -265,6 +265,198 @@ __global__ void __launch_bounds__(kPackThreads, 5) pack_kernel(const SegDesc *de
 	}
 }
 
+// ---- narrow types (S < 8): raw tiles staged by the TMA engine ---------------------------------------------
+//
+// A 2048-value tile of a 1/2/4-byte type is only 2-8 KiB of input: with register loads issued at the top of every
+// tile a CTA had 2-8 KiB in flight for a third of the time and the kernel settled at ~650 Gvalues/s for every
+// type (the latency chain load -> park -> pack -> store per tile, not bytes).  Here a producer warp walks the tile
+// table, resolves descriptors and keeps a ring of raw tiles in flight with cp.async.bulk; the 8 consumer warps
+// never wait on global memory: phase A reads the slots from shared memory.
+constexpr int kStagedThreads = kPackThreads + 32;
+constexpr int kRing = 3;
+
+struct PackStage {
+	PackTile t;
+	uint32_t mis;   // byte offset of the tile's first slot inside the staged (16-byte aligned) bytes
+	uint32_t done;  // sentinel
+};
+
+template <int S> struct StagedSmem {
+	static constexpr uint32_t kFieldBytes = kVectorSize * 4u;
+	static constexpr uint32_t kOstageBytes = kRows * ((8 * S - 1) | 1u) * 8u;
+	static constexpr uint32_t kRawBytes = kVectorSize * S + 32u;  // + misalignment + rounding to 16
+	static constexpr uint32_t kBytes = kFieldBytes + kOstageBytes + kRing * kRawBytes;
+};
+
+template <int S>
+__global__ void __launch_bounds__(kStagedThreads, 4) pack_staged_kernel(const SegDesc *desc, const Job *tiles,
+                                                                        uint32_t n_tiles, const uint8_t *raw,
+                                                                        uint32_t extent, uint64_t *base) {
+	extern __shared__ __align__(128) uint8_t pack_smem[];
+	__shared__ __align__(8) uint64_t full_bar[kRing];
+	__shared__ __align__(8) uint64_t empty_bar[kRing];
+	__shared__ PackStage infos[kRing];
+	uint32_t *fld = (uint32_t *)pack_smem;
+	uint64_t *ostage = (uint64_t *)(pack_smem + StagedSmem<S>::kFieldBytes);
+	uint8_t *ring = pack_smem + StagedSmem<S>::kFieldBytes + StagedSmem<S>::kOstageBytes;
+	const uint32_t tid = threadIdx.x;
+	const uint32_t lane = tid & 31u;
+	const uint32_t warp = tid >> 5;
+	using T = typename UIntOf<S>::type;
+
+	if (tid == 0) {
+		for (int s = 0; s < kRing; s++) {
+			mbar_init(&full_bar[s], 1);
+			mbar_init(&empty_bar[s], 1);
+		}
+		mbar_fence_init();
+	}
+	__syncthreads();
+
+	if (warp == kSubs) {
+		// ---------------- producer warp: 32 tiles resolved per batch, published in table order ----------------
+		uint32_t seq = 0;
+		const uint32_t batch = 32u * gridDim.x;
+		Job job_next;
+		DescQ dq_next;
+		{
+			const uint32_t ti = blockIdx.x + lane * gridDim.x;
+			if (ti < n_tiles) {
+				job_next = tiles[ti];
+				dq_next = load_desc(desc + job_next.seg);
+			}
+		}
+		for (uint32_t t0 = blockIdx.x; t0 < n_tiles; t0 += batch) {
+			const uint32_t ti = t0 + lane * gridDim.x;
+			const Job job = job_next;
+			const DescQ dq = dq_next;
+			if (ti + batch < n_tiles) {  // table entry and descriptor of the next batch: in flight meanwhile
+				job_next = tiles[ti + batch];
+				dq_next = load_desc(desc + job_next.seg);
+			}
+			PackStage st;
+			st.t.cnt = 0;
+			uint64_t src16 = 0;
+			uint32_t bytes = 0;
+			if (ti < n_tiles) {
+				st.t = resolve_pack_tile<S>(dq, job.k, raw, extent, base);
+				src16 = (uint64_t)st.t.src & ~15ull;
+				st.mis = (uint32_t)((uint64_t)st.t.src - src16);
+				bytes = (st.mis + st.t.cnt * S + 15u) & ~15u;  // the raw arena is padded: the tail over-read stays inside
+				st.done = 0;
+			}
+			uint32_t todo = __ballot_sync(0xffffffffu, st.t.cnt != 0);
+			while (todo) {
+				const uint32_t l = (uint32_t)__ffs((int)todo) - 1u;
+				todo &= todo - 1u;
+				if (lane == l) {
+					const uint32_t s = seq % kRing;
+					mbar_wait(&empty_bar[s], ((seq / kRing) & 1u) ^ 1u);
+					infos[s] = st;
+					mbar_arrive_expect_tx(&full_bar[s], bytes);
+					tma_load_1d(ring + s * StagedSmem<S>::kRawBytes, (const void *)src16, bytes, &full_bar[s]);
+				}
+				seq++;
+				__syncwarp();
+			}
+		}
+		if (lane == 0) {
+			const uint32_t s = seq % kRing;
+			mbar_wait(&empty_bar[s], ((seq / kRing) & 1u) ^ 1u);
+			infos[s].done = 1;
+			mbar_arrive(&full_bar[s]);
+		}
+		return;
+	}
+
+	// ---------------- consumer warps ----------------
+	for (uint32_t it = 0;; it++) {
+		const uint32_t s = it % kRing;
+		mbar_wait(&full_bar[s], (it / kRing) & 1u);
+		if (infos[s].done) {
+			break;
+		}
+		const PackTile t = infos[s].t;
+		{
+			// phase A from shared memory: slot -> field, parked at its swizzled position.  Value i = j*256 + tid sits
+			// in row j*4 + tid/64, so its position i ^ (row & 31) is j*256 + ((tid ^ tid/64) ^ 4j): one XOR with a
+			// constant per value, everything else folds into immediate offsets.
+			const T *vals = (const T *)(ring + s * StagedSmem<S>::kRawBytes + infos[s].mis) + tid;
+			const uint32_t mask = (uint32_t)lo_set64(t.w);
+			const uint32_t sub = (uint32_t)t.sub;
+			const uint32_t sw = tid ^ (tid >> 6);
+			constexpr int PER = kVectorSize / kPackThreads;
+			if (t.cnt == kVectorSize) {
+#pragma unroll
+				for (int j = 0; j < PER; j++) {
+					fld[j * kPackThreads + (sw ^ (4 * j))] = ((uint32_t)vals[j * kPackThreads] - sub) & mask;
+				}
+			} else {
+#pragma unroll
+				for (int j = 0; j < PER; j++) {
+					const uint32_t v = j * kPackThreads + tid < t.cnt ? (uint32_t)vals[j * kPackThreads] : sub;
+					fld[j * kPackThreads + (sw ^ (4 * j))] = (v - sub) & mask;  // padding packs to zero fields
+				}
+			}
+		}
+		asm volatile("bar.sync 1, %0;" ::"n"(kPackThreads) : "memory");
+		if (tid == 0) {
+			mbar_arrive(&empty_bar[s]);  // raw stage s (and its info) may be refilled
+		}
+		switch (t.w) {
+			PACK_CASES_8(0)
+			PACK_CASES_8(8)
+			PACK_CASES_8(16)
+			PACK_CASES_8(24)
+		default:
+			break;
+		}
+		asm volatile("bar.sync 1, %0;" ::"n"(kPackThreads) : "memory");
+		const uint32_t w = t.w;
+		const uint32_t n_words = (t.cnt * w + 63u) >> 6;
+		const uint32_t magic = ((1u << 20) + w - 1u) / w;
+		const uint32_t pad = (w & 1u) ^ 1u;
+		for (uint32_t m = tid; m < n_words; m += kPackThreads) {
+			const uint32_t row = (m * magic) >> 20;
+			t.out[m] = ostage[m + row * pad];
+		}
+		if (tid < t.gap) {
+			t.out[n_words + tid] = 0ull;
+		}
+	}
+}
+
+template <int S>
+cudaError_t launch_pack_staged(const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw,
+                               uint32_t extent, uint64_t *base, int sm_count, cudaStream_t stream) {
+	static int per_sm[64] = {};
+	const size_t smem = StagedSmem<S>::kBytes;
+	auto kernel = pack_staged_kernel<S>;
+	int dev = 0;
+	cudaGetDevice(&dev);
+	if (per_sm[dev & 63] == 0) {
+		cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		if (e != cudaSuccess) {
+			return e;
+		}
+		int n = 0;
+		e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kStagedThreads, smem);
+		if (e != cudaSuccess) {
+			return e;
+		}
+		per_sm[dev & 63] = n > 0 ? n : 1;
+	}
+	if (n_tiles == 0) {
+		return cudaSuccess;
+	}
+	uint32_t grid = (uint32_t)sm_count * (uint32_t)per_sm[dev & 63];
+	if (grid > n_tiles) {
+		grid = n_tiles;
+	}
+	kernel<<<grid, kStagedThreads, smem, stream>>>(desc, tiles, n_tiles, raw, extent, base);
+	return cudaGetLastError();
+}
+
 template <int S>
 cudaError_t launch_pack_s(const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw, uint32_t extent,
                           uint64_t *base, int sm_count, cudaStream_t stream) {
@@ -301,12 +493,21 @@ cudaError_t launch_pack_s(const SegDesc *desc, const Job *tiles, uint32_t n_tile
 cudaError_t launch_encode(TypeInfo t, const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw,
                           uint32_t extent, uint64_t *base, int sm_count, cudaStream_t stream) {
 	switch (t.size) {
+#ifndef ADACOM_PACK_DIRECT
+	case 1:
+		return launch_pack_staged<1>(desc, tiles, n_tiles, raw, extent, base, sm_count, stream);
+	case 2:
+		return launch_pack_staged<2>(desc, tiles, n_tiles, raw, extent, base, sm_count, stream);
+	case 4:
+		return launch_pack_staged<4>(desc, tiles, n_tiles, raw, extent, base, sm_count, stream);
+#else
 	case 1:
 		return launch_pack_s<1>(desc, tiles, n_tiles, raw, extent, base, sm_count, stream);
 	case 2:
 		return launch_pack_s<2>(desc, tiles, n_tiles, raw, extent, base, sm_count, stream);
 	case 4:
 		return launch_pack_s<4>(desc, tiles, n_tiles, raw, extent, base, sm_count, stream);
+#endif
 	case 8:
 		return launch_pack_s<8>(desc, tiles, n_tiles, raw, extent, base, sm_count, stream);
 	default:
