@@ -83,7 +83,7 @@ template <typename F> struct Swz { static constexpr uint32_t kMask = sizeof(F) =
 template <int S, typename F>
 __device__ __forceinline__ void phase_a(const PackTile &t, F *fld, uint32_t tid) {
 	using T = typename UIntOf<S>::type;
-	const T *vals = (const T *)t.src;  // the slot-width int_vector read: zero-extended S raw bytes
+	const T *vals = (const T *)t.src + tid;  // the slot-width int_vector read: zero-extended S raw bytes
 	const F mask = (F)lo_set64(t.w);
 	const F sub = (F)t.sub;
 	constexpr uint32_t XM = Swz<F>::kMask;
@@ -92,20 +92,21 @@ __device__ __forceinline__ void phase_a(const PackTile &t, F *fld, uint32_t tid)
 	if (t.cnt == kVectorSize) {
 #pragma unroll
 		for (int j = 0; j < PER; j++) {
-			r[j] = load_stream(vals + j * kPackThreads + tid);
+			r[j] = load_stream(vals + j * kPackThreads);
 		}
 	} else {
 #pragma unroll
 		for (int j = 0; j < PER; j++) {
-			const uint32_t i = j * kPackThreads + tid;
-			r[j] = i < t.cnt ? load_stream(vals + i) : (T)sub;  // padding packs to zero fields
+			r[j] = j * kPackThreads + tid < t.cnt ? load_stream(vals + j * kPackThreads) : (T)sub;  // padding -> zero fields
 		}
 	}
+	// value i = j*256 + tid sits in row j*4 + tid/64, so its swizzled position i ^ (row & XM) is
+	// j*256 + ((tid ^ tid/64) ^ (4j & XM)): one XOR with a constant per value, the rest are immediate offsets
+	F *dst = fld;
+	const uint32_t sw = tid ^ (tid >> 6);
 #pragma unroll
 	for (int j = 0; j < PER; j++) {
-		const uint32_t i = j * kPackThreads + tid;
-		const uint32_t row = i / kRowValues;
-		fld[i ^ (row & XM)] = ((F)r[j] - sub) & mask;
+		dst[j * kPackThreads + (sw ^ ((4 * j) & XM))] = ((F)r[j] - sub) & mask;
 	}
 }
 
