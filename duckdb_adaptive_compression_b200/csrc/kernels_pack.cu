@@ -8,11 +8,12 @@
 //
 // Work unit = one 2048-value tile counted from the segment start (256*w output bytes, 16-byte aligned).
 // 64 consecutive values always fill exactly w whole 64-bit words, so a tile is 32 independent "rows" of
-// 64 values -> w words.  One CTA (8 warps) per tile, three phases:
+// 64 values -> w words.  A producer warp stages the raw tiles of a CTA in shared memory (TMA ring, see
+// pack_staged_kernel); the 8 consumer warps take one tile at a time through three phases:
 //
-//   A  every thread loads 8 raw values with coalesced global loads, subtracts the frame of reference,
-//      masks to w bits and parks the field in shared memory at an XOR-swizzled position
-//      (pos = i ^ (row & 31|15)): conflict-free both for this linear write and for phase B's strided read;
+//   A  every thread reads 8 raw slots of the staged tile, subtracts the frame of reference, masks to w bits
+//      and parks the field in shared memory at an XOR-swizzled position (pos = i ^ (row & 31|15)):
+//      conflict-free both for this linear write and for phase B's strided read;
 //   B  lane = row, warp q = the q-th eighth of the row's w output words.  The template fixes (w, q), so the
 //      list of fields touching those words and every shift amount are compile-time constants: a field costs
 //      one shared load and one or two shift/or (gather formulation: no atomics, no inter-thread carries,
@@ -70,45 +71,9 @@ __device__ __forceinline__ PackTile resolve_pack_tile(const DescQ &dq, uint32_t 
 	return t;
 }
 
-// ---- phase A: raw slots -> swizzled fields ------------------------------------------------------------
-
-// raw slots are read exactly once: evict-first
-__device__ __forceinline__ uint8_t load_stream(const uint8_t *p) { return __ldcs(p); }
-__device__ __forceinline__ uint16_t load_stream(const uint16_t *p) { return __ldcs(p); }
-__device__ __forceinline__ uint32_t load_stream(const uint32_t *p) { return __ldcs(p); }
-__device__ __forceinline__ uint64_t load_stream(const uint64_t *p) { return (uint64_t)__ldcs((const unsigned long long *)p); }
+// ---- phase A helpers ------------------------------------------------------------------------------------
 
 template <typename F> struct Swz { static constexpr uint32_t kMask = sizeof(F) == 4 ? 31u : 15u; };
-
-template <int S, typename F>
-__device__ __forceinline__ void phase_a(const PackTile &t, F *fld, uint32_t tid) {
-	using T = typename UIntOf<S>::type;
-	const T *vals = (const T *)t.src + tid;  // the slot-width int_vector read: zero-extended S raw bytes
-	const F mask = (F)lo_set64(t.w);
-	const F sub = (F)t.sub;
-	constexpr uint32_t XM = Swz<F>::kMask;
-	constexpr int PER = kVectorSize / kPackThreads;  // 8 values per thread
-	T r[PER];
-	if (t.cnt == kVectorSize) {
-#pragma unroll
-		for (int j = 0; j < PER; j++) {
-			r[j] = load_stream(vals + j * kPackThreads);
-		}
-	} else {
-#pragma unroll
-		for (int j = 0; j < PER; j++) {
-			r[j] = j * kPackThreads + tid < t.cnt ? load_stream(vals + j * kPackThreads) : (T)sub;  // padding -> zero fields
-		}
-	}
-	// value i = j*256 + tid sits in row j*4 + tid/64, so its swizzled position i ^ (row & XM) is
-	// j*256 + ((tid ^ tid/64) ^ (4j & XM)): one XOR with a constant per value, the rest are immediate offsets
-	F *dst = fld;
-	const uint32_t sw = tid ^ (tid >> 6);
-#pragma unroll
-	for (int j = 0; j < PER; j++) {
-		dst[j * kPackThreads + (sw ^ ((4 * j) & XM))] = ((F)r[j] - sub) & mask;
-	}
-}
 
 // ---- phase B: fields of one row -> the words of sub-range q -------------------------------------------
 
@@ -191,90 +156,16 @@ __device__ __forceinline__ void phase_b_case(const void *fld, uint64_t *ostage, 
 #define PACK_CASE(W) case W: phase_b_case<S, W>(fld, ostage, t.cnt, warp, lane); break;
 #define PACK_CASES_8(B) PACK_CASE(B) PACK_CASE(B + 1) PACK_CASE(B + 2) PACK_CASE(B + 3) PACK_CASE(B + 4) PACK_CASE(B + 5) PACK_CASE(B + 6) PACK_CASE(B + 7)
 
-template <int S> struct PackSmem {
-	static constexpr uint32_t kFieldBytes = kVectorSize * (S == 8 ? 8u : 4u);
-	static constexpr uint32_t kMaxW = 8 * S - 1;
-	static constexpr uint32_t kStageBytes = kRows * (kMaxW | 1u) * 8u;
-	static constexpr uint32_t kBytes = kFieldBytes + kStageBytes;
-};
-
-template <int S>
-__global__ void __launch_bounds__(kPackThreads, 5) pack_kernel(const SegDesc *desc, const Job *tiles, uint32_t n_tiles,
-                                                               const uint8_t *raw, uint32_t extent, uint64_t *base) {
-	extern __shared__ __align__(16) uint8_t pack_smem[];
-	void *fld = pack_smem;
-	uint64_t *ostage = (uint64_t *)(pack_smem + PackSmem<S>::kFieldBytes);
-	const uint32_t tid = threadIdx.x;
-	const uint32_t lane = tid & 31u;
-	const uint32_t warp = tid >> 5;
-
-	// static tile table -> descriptor: both fetched ahead (the pair two tiles ahead, the descriptor one tile ahead)
-	uint32_t ti = blockIdx.x;
-	if (ti >= n_tiles) {
-		return;
-	}
-	Job job = tiles[ti];
-	Job job_next = ti + gridDim.x < n_tiles ? tiles[ti + gridDim.x] : job;
-	DescQ dq = load_desc(desc + job.seg);
-	for (;;) {
-		const PackTile t = resolve_pack_tile<S>(dq, job.k, raw, extent, base);
-		const uint32_t next = ti + gridDim.x;
-		job = job_next;
-		if (next < n_tiles) {
-			dq = load_desc(desc + job.seg);
-			if (next + gridDim.x < n_tiles) {
-				job_next = tiles[next + gridDim.x];
-			}
-		}
-		if (t.cnt) {
-			if (S < 8 || t.w <= 32u) {
-				phase_a<S, uint32_t>(t, (uint32_t *)fld, tid);
-			} else {
-				phase_a<S, uint64_t>(t, (uint64_t *)fld, tid);
-			}
-			__syncthreads();
-			switch (t.w) {
-				PACK_CASES_8(0)
-				PACK_CASES_8(8)
-				PACK_CASES_8(16)
-				PACK_CASES_8(24)
-				PACK_CASES_8(32)
-				PACK_CASES_8(40)
-				PACK_CASES_8(48)
-				PACK_CASES_8(56)
-			default:
-				break;
-			}
-			__syncthreads();
-			// phase C: staging rows (stride w | 1) -> linear words
-			const uint32_t w = t.w;
-			const uint32_t n_words = (t.cnt * w + 63u) >> 6;
-			const uint32_t magic = ((1u << 20) + w - 1u) / w;  // m / w == (m * magic) >> 20 for m < 2^14
-			const uint32_t pad = (w & 1u) ^ 1u;
-			for (uint32_t m = tid; m < n_words; m += kPackThreads) {
-				const uint32_t row = (m * magic) >> 20;
-				t.out[m] = ostage[m + row * pad];
-			}
-			if (tid < t.gap) {  // keep the alignment gap behind the payload deterministic (zero)
-				t.out[n_words + tid] = 0ull;
-			}
-		}
-		if (next >= n_tiles) {
-			break;
-		}
-		ti = next;
-	}
-}
-
-// ---- narrow types (S < 8): raw tiles staged by the TMA engine ---------------------------------------------
+// ---- the kernel: raw tiles staged by the TMA engine, 8 consumer warps pack -------------------------------
 //
-// A 2048-value tile of a 1/2/4-byte type is only 2-8 KiB of input: with register loads issued at the top of every
-// tile a CTA had 2-8 KiB in flight for a third of the time and the kernel settled at ~650 Gvalues/s for every
-// type (the latency chain load -> park -> pack -> store per tile, not bytes).  Here a producer warp walks the tile
-// table, resolves descriptors and keeps a ring of raw tiles in flight with cp.async.bulk; the 8 consumer warps
-// never wait on global memory: phase A reads the slots from shared memory.
+// With register loads issued at the top of every tile (the first version of this kernel) a CTA had its 2-16 KiB of
+// input in flight for about a third of the time and every thread re-derived the tile from the descriptor: ~650
+// Gvalues/s for every type, 0.80 of the HBM peak for INT64.  Here a producer warp walks the tile table, resolves the
+// descriptors (32 tiles per batch, the next batch's table entries and descriptors already in flight) and keeps a
+// ring of raw tiles in flight with cp.async.bulk; the consumer warps never wait on global memory and never touch a
+// descriptor: phase A reads the slots from shared memory (measured: INT64 encode 5.2 -> 5.9 TB/s at 17 bits,
+// UINT8 0.79 -> 0.55 ms per 2^29 values).
 constexpr int kStagedThreads = kPackThreads + 32;
-constexpr int kRing = 3;
 
 struct PackStage {
 	PackTile t;
@@ -282,22 +173,47 @@ struct PackStage {
 	uint32_t done;  // sentinel
 };
 
+// staged phase A: slots (already in shared memory) -> swizzled fields
+template <typename T, typename F>
+__device__ __forceinline__ void park_fields(const T *vals, F *fld, const PackTile &t, uint32_t tid) {
+	const F mask = (F)lo_set64(t.w);
+	const F sub = (F)t.sub;
+	constexpr uint32_t XM = Swz<F>::kMask;
+	const uint32_t sw = tid ^ (tid >> 6);
+	constexpr int PER = kVectorSize / kPackThreads;
+	if (t.cnt == kVectorSize) {
+#pragma unroll
+		for (int j = 0; j < PER; j++) {
+			fld[j * kPackThreads + (sw ^ ((4 * j) & XM))] = ((F)vals[j * kPackThreads] - sub) & mask;
+		}
+	} else {
+#pragma unroll
+		for (int j = 0; j < PER; j++) {
+			const F v = j * kPackThreads + tid < t.cnt ? (F)vals[j * kPackThreads] : sub;  // padding -> zero fields
+			fld[j * kPackThreads + (sw ^ ((4 * j) & XM))] = (v - sub) & mask;
+		}
+	}
+}
+
 template <int S> struct StagedSmem {
-	static constexpr uint32_t kFieldBytes = kVectorSize * 4u;
+	static constexpr int kRing = S == 8 ? 2 : 3;      // raw tiles in flight per CTA
+	static constexpr int kMinCtas = S == 8 ? 3 : 4;   // resident CTAs per SM the kernel is compiled for
+	static constexpr uint32_t kFieldBytes = kVectorSize * (S == 8 ? 8u : 4u);
 	static constexpr uint32_t kOstageBytes = kRows * ((8 * S - 1) | 1u) * 8u;
 	static constexpr uint32_t kRawBytes = kVectorSize * S + 32u;  // + misalignment + rounding to 16
 	static constexpr uint32_t kBytes = kFieldBytes + kOstageBytes + kRing * kRawBytes;
 };
 
 template <int S>
-__global__ void __launch_bounds__(kStagedThreads, 4) pack_staged_kernel(const SegDesc *desc, const Job *tiles,
+__global__ void __launch_bounds__(kStagedThreads, StagedSmem<S>::kMinCtas) pack_staged_kernel(const SegDesc *desc, const Job *tiles,
                                                                         uint32_t n_tiles, const uint8_t *raw,
                                                                         uint32_t extent, uint64_t *base) {
+	constexpr int kRing = StagedSmem<S>::kRing;
 	extern __shared__ __align__(128) uint8_t pack_smem[];
 	__shared__ __align__(8) uint64_t full_bar[kRing];
 	__shared__ __align__(8) uint64_t empty_bar[kRing];
 	__shared__ PackStage infos[kRing];
-	uint32_t *fld = (uint32_t *)pack_smem;
+	void *fld = pack_smem;
 	uint64_t *ostage = (uint64_t *)(pack_smem + StagedSmem<S>::kFieldBytes);
 	uint8_t *ring = pack_smem + StagedSmem<S>::kFieldBytes + StagedSmem<S>::kOstageBytes;
 	const uint32_t tid = threadIdx.x;
@@ -383,21 +299,10 @@ __global__ void __launch_bounds__(kStagedThreads, 4) pack_staged_kernel(const Se
 			// in row j*4 + tid/64, so its position i ^ (row & 31) is j*256 + ((tid ^ tid/64) ^ 4j): one XOR with a
 			// constant per value, everything else folds into immediate offsets.
 			const T *vals = (const T *)(ring + s * StagedSmem<S>::kRawBytes + infos[s].mis) + tid;
-			const uint32_t mask = (uint32_t)lo_set64(t.w);
-			const uint32_t sub = (uint32_t)t.sub;
-			const uint32_t sw = tid ^ (tid >> 6);
-			constexpr int PER = kVectorSize / kPackThreads;
-			if (t.cnt == kVectorSize) {
-#pragma unroll
-				for (int j = 0; j < PER; j++) {
-					fld[j * kPackThreads + (sw ^ (4 * j))] = ((uint32_t)vals[j * kPackThreads] - sub) & mask;
-				}
+			if (S < 8 || t.w <= 32u) {
+				park_fields<T, uint32_t>(vals, (uint32_t *)fld, t, tid);
 			} else {
-#pragma unroll
-				for (int j = 0; j < PER; j++) {
-					const uint32_t v = j * kPackThreads + tid < t.cnt ? (uint32_t)vals[j * kPackThreads] : sub;
-					fld[j * kPackThreads + (sw ^ (4 * j))] = (v - sub) & mask;  // padding packs to zero fields
-				}
+				park_fields<T, uint64_t>(vals, (uint64_t *)fld, t, tid);
 			}
 		}
 		asm volatile("bar.sync 1, %0;" ::"n"(kPackThreads) : "memory");
@@ -409,6 +314,10 @@ __global__ void __launch_bounds__(kStagedThreads, 4) pack_staged_kernel(const Se
 			PACK_CASES_8(8)
 			PACK_CASES_8(16)
 			PACK_CASES_8(24)
+			PACK_CASES_8(32)
+			PACK_CASES_8(40)
+			PACK_CASES_8(48)
+			PACK_CASES_8(56)
 		default:
 			break;
 		}
@@ -458,59 +367,19 @@ cudaError_t launch_pack_staged(const SegDesc *desc, const Job *tiles, uint32_t n
 	return cudaGetLastError();
 }
 
-template <int S>
-cudaError_t launch_pack_s(const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw, uint32_t extent,
-                          uint64_t *base, int sm_count, cudaStream_t stream) {
-	static int per_sm[64] = {};  // per device: resident CTAs per SM (0 = not configured yet)
-	const size_t smem = PackSmem<S>::kBytes;
-	auto kernel = pack_kernel<S>;
-	int dev = 0;
-	cudaGetDevice(&dev);
-	if (per_sm[dev & 63] == 0) {
-		cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-		if (e != cudaSuccess) {
-			return e;
-		}
-		int n = 0;
-		e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kPackThreads, smem);
-		if (e != cudaSuccess) {
-			return e;
-		}
-		per_sm[dev & 63] = n > 0 ? n : 1;
-	}
-	if (n_tiles == 0) {
-		return cudaSuccess;
-	}
-	uint32_t grid = (uint32_t)sm_count * (uint32_t)per_sm[dev & 63];  // persistent, all resident
-	if (grid > n_tiles) {
-		grid = n_tiles;
-	}
-	kernel<<<grid, kPackThreads, smem, stream>>>(desc, tiles, n_tiles, raw, extent, base);
-	return cudaGetLastError();
-}
-
 }  // namespace
 
 cudaError_t launch_encode(TypeInfo t, const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw,
                           uint32_t extent, uint64_t *base, int sm_count, cudaStream_t stream) {
 	switch (t.size) {
-#ifndef ADACOM_PACK_DIRECT
 	case 1:
 		return launch_pack_staged<1>(desc, tiles, n_tiles, raw, extent, base, sm_count, stream);
 	case 2:
 		return launch_pack_staged<2>(desc, tiles, n_tiles, raw, extent, base, sm_count, stream);
 	case 4:
 		return launch_pack_staged<4>(desc, tiles, n_tiles, raw, extent, base, sm_count, stream);
-#else
-	case 1:
-		return launch_pack_s<1>(desc, tiles, n_tiles, raw, extent, base, sm_count, stream);
-	case 2:
-		return launch_pack_s<2>(desc, tiles, n_tiles, raw, extent, base, sm_count, stream);
-	case 4:
-		return launch_pack_s<4>(desc, tiles, n_tiles, raw, extent, base, sm_count, stream);
-#endif
 	case 8:
-		return launch_pack_s<8>(desc, tiles, n_tiles, raw, extent, base, sm_count, stream);
+		return launch_pack_staged<8>(desc, tiles, n_tiles, raw, extent, base, sm_count, stream);
 	default:
 		return cudaErrorInvalidValue;
 	}
