@@ -194,6 +194,25 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
 	} while (!done);
 }
 
+// shared -> global bulk copy (TMA store): dst/src 16-byte aligned, bytes % 16 == 0; completion via bulk groups
+__device__ __forceinline__ void tma_store_1d(void *gmem_dst, const void *smem_src, uint32_t bytes) {
+	asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem_dst), "r"(smem_addr(smem_src)),
+	             "r"(bytes)
+	             : "memory");
+	asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+// all bulk stores of this thread have finished READING shared memory (the source may be overwritten)
+__device__ __forceinline__ void tma_store_wait_read() {
+	asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+__device__ __forceinline__ void tma_store_wait_all() {
+	asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+// make this thread's generic-proxy writes to shared memory visible to the async proxy (TMA) before a bulk store
+__device__ __forceinline__ void fence_proxy_async_smem() {
+	asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
 // global -> shared bulk copy (TMA engine, SASS UBLKCP); src/dst 16-byte aligned, bytes % 16 == 0
 __device__ __forceinline__ void tma_load_1d(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar) {
 	asm volatile(

@@ -39,7 +39,13 @@ constexpr int kMaxStages = 8;
 template <int S, int MODE> struct StageCfg {
 	static constexpr uint32_t kBytes = (MODE == kModeFlat ? kVectorSize * (uint32_t)S : 16384u) + 32u;
 	static constexpr int kGroups = MODE != kModeFlat ? 1 : (S == 8 ? 1 : (S == 4 ? 2 : 4));
-	static constexpr int kStages = kGroups == 4 ? 8 : 6;
+	// INT64 flat decode: decoded tiles leave through the TMA engine (two 16 KiB output buffers per CTA, 4 input
+	// stages).  Measured on B200 against 8-byte stores from the consumer lanes with 6 input stages: -3 % time at 1-3
+	// bits, +2-4 % at 8-13 bits, -2.5..-6 % from 17 bits up; -2.4 % over the sweep.
+	static constexpr bool kTmaStore = MODE == kModeFlat && S == 8;
+	static constexpr uint32_t kOutBytes = kTmaStore ? kVectorSize * (uint32_t)S + 16u : 0u;
+	static constexpr int kStages = kTmaStore ? 4 : (kGroups == 4 ? 8 : 6);
+	static constexpr uint32_t kSmem = (uint32_t)kStages * kBytes + 2u * kOutBytes;
 #ifndef ADACOM_DECODE_MINB
 #define ADACOM_DECODE_MINB 4
 #endif
@@ -241,6 +247,68 @@ __global__ void __launch_bounds__(kThreads, StageCfg<S, MODE>::kMinCtas) decode_
 				constant = (uint64_t)a.q_const[query];
 			}
 
+			if (StageCfg<S, MODE>::kTmaStore) {
+				// decoded values go to a shared output tile placed so that shared and global addresses agree mod 16;
+				// the 16-byte aligned middle leaves as ONE bulk store, the (at most one each) head / tail elements
+				// as ordinary stores
+				constexpr uint32_t EPB = 16u / S;  // elements per 16 bytes
+				uint8_t *obuf = stage_mem + kStages * kStageBytes + (it & 1u) * StageCfg<S, MODE>::kOutBytes;
+				T *gdst = (T *)a.out + (in.row - a.out_row0);
+				const uint32_t sh = (uint32_t)(((uint64_t)gdst & 15ull) / S);
+				const uint32_t head = sh ? min(EPB - sh, in.cnt) : 0u;
+				const uint32_t bulk = ((in.cnt - head) / EPB) * EPB;  // elements in the bulk store
+				const uint32_t bulk_end = head + bulk;
+				T *ob = (T *)obuf + sh;
+				if (in.cnt == kVectorSize) {
+					constexpr int PER = kVectorSize / kGroupThreads;
+					uint64_t x[PER];
+					if (narrow) {
+#pragma unroll
+						for (int j = 0; j < PER; j++) {
+							const uint32_t bit = in.bit_base + (j * kGroupThreads + gtid) * w;
+							x[j] = (uint64_t)(read_bits32(words32, bit) & mask32) + in.min_add;
+						}
+					} else {
+#pragma unroll
+						for (int j = 0; j < PER; j++) {
+							const uint32_t bit = in.bit_base + (j * kGroupThreads + gtid) * w;
+							x[j] = (read_bits64(words, bit) & mask64) + in.min_add;
+						}
+					}
+#pragma unroll
+					for (int j = 0; j < PER; j++) {
+						ob[j * kGroupThreads + gtid] = (T)x[j];
+					}
+					if (gtid < head) {
+						gdst[gtid] = (T)x[0];
+					}
+					if ((PER - 1) * kGroupThreads + gtid >= bulk_end) {  // tail elements live in the last slice
+						gdst[(PER - 1) * kGroupThreads + gtid] = (T)x[PER - 1];
+					}
+				} else {
+					for (uint32_t i = gtid; i < in.cnt; i += kGroupThreads) {
+						const uint32_t bit = in.bit_base + i * w;
+						const uint64_t f = narrow ? (uint64_t)(read_bits32(words32, bit) & mask32) : (read_bits64(words, bit) & mask64);
+						const T v = (T)(f + in.min_add);
+						ob[i] = v;
+						if (i < head || i >= bulk_end) {
+							gdst[i] = v;
+						}
+					}
+				}
+				fence_proxy_async_smem();
+				if (gtid == 0) {
+					tma_store_wait_read();  // the previous tile's store no longer reads the other buffer
+				}
+				asm volatile("bar.sync 1, %0;" ::"n"(kGroupThreads) : "memory");
+				if (gtid == 0) {
+					mbar_arrive(&empty_bar[s]);
+					if (bulk) {
+						tma_store_1d(gdst + head, ob + head, bulk * S);
+					}
+				}
+				continue;
+			}
 			if (MODE == kModeFlat && S < 8 && in.cnt == kVectorSize &&
 			    ((((uint64_t)a.out + (in.row - a.out_row0) * S) & 7ull) == 0)) {
 				// narrow types, full tile: a lane unpacks 8 / S adjacent values and leaves ONE 8-byte store
@@ -347,6 +415,9 @@ __global__ void __launch_bounds__(kThreads, StageCfg<S, MODE>::kMinCtas) decode_
 				mbar_arrive(&empty_bar[s]);  // stage s (payload and info) is free again
 			}
 		}
+		if (StageCfg<S, MODE>::kTmaStore && tid == 0) {
+			tma_store_wait_all();
+		}
 	}
 
 	if (MODE == kModeSum || MODE == kModeFilter) {
@@ -357,7 +428,7 @@ __global__ void __launch_bounds__(kThreads, StageCfg<S, MODE>::kMinCtas) decode_
 template <int S, bool SIGNED, int MODE>
 cudaError_t launch_one(const DecodeArgs &args, int sm_count, cudaStream_t stream) {
 	static int configured[64] = {};  // per device: the attribute is per (function, device); holds resident CTAs / SM
-	const size_t smem = (size_t)StageCfg<S, MODE>::kStages * StageCfg<S, MODE>::kBytes;
+	const size_t smem = StageCfg<S, MODE>::kSmem;
 	auto kernel = decode_kernel<S, SIGNED, MODE>;
 	int dev = 0;
 	cudaGetDevice(&dev);
@@ -377,9 +448,9 @@ cudaError_t launch_one(const DecodeArgs &args, int sm_count, cudaStream_t stream
 	if (n_jobs == 0) {
 		return cudaSuccess;
 	}
-	// 6 stages x 16 KiB x 2 CTAs per SM for INT64 (measured: beats 3 x 4 and 4 x 3 for the write-heavy flat decode).
-	// The narrower types are bound by values per second, not bytes: their flat stages are smaller, so 4 (S = 4) or
-	// 6 (S <= 2) CTAs per SM hide the per-value latency.  All CTAs resident; fused scans: odd (see the kernel)
+	// INT64 flat: (4 input stages + 2 output tiles) x 16 KiB x 2 CTAs per SM; fused scans: 6 stages x 16 KiB x 2.
+	// The narrower types are bound by values per second, not bytes: their flat stages are smaller, so 4 CTAs per
+	// SM hide the per-value latency.  All CTAs resident; fused scans: odd grid (see the kernel)
 	// Never more CTAs than are resident at once: a persistent grid with a second wave doubles the tail.
 	const uint32_t want_per_sm = (uint32_t)StageCfg<S, MODE>::kMinCtas;
 	const uint32_t per_sm = want_per_sm < (uint32_t)configured[dev & 63] ? want_per_sm : (uint32_t)configured[dev & 63];
