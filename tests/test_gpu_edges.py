@@ -260,3 +260,55 @@ def test_argument_errors_are_reported(gpu_ctx):
         gpu_ctx.column_from_values(np.arange(10, dtype=np.int64), [10], seg_capacity=5)  # count > capacity
     assert col.scan_sum().count == 1000  # the context is still usable afterwards
     col.close()
+
+
+def test_concurrent_readers_and_a_recompacting_writer(gpu_ctx, port_oracle):
+    """SURVEY 8(b) threading: scans / fetches arrive from N worker threads while the policy thread compacts and
+    uncompacts the same segments (column_segment_catalog.cpp:64-116).  Every read must see either representation
+    completely -- the values never change."""
+    import threading
+
+    dtype = np.int32
+    vals = [width_values(dtype, 5 + 3 * g, 20000 + 11 * g, 1000 * g, seed=g) for g in range(8)]
+    flat = np.concatenate(vals)
+    starts = np.concatenate([[0], np.cumsum([len(v) for v in vals])])
+    col = gpu_ctx.column_from_values(flat, [len(v) for v in vals])
+    col.compact()
+    want_sum = int(flat.astype(np.int64).sum())
+    errors, stop = [], threading.Event()
+
+    def reader(seed):
+        rng = np.random.default_rng(seed)
+        try:
+            while not stop.is_set():
+                g = int(rng.integers(0, len(vals)))
+                start = int(rng.integers(0, len(vals[g]) - 100))
+                got = col.scan_partial(g, start, 100)
+                if not np.array_equal(got, vals[g][start:start + 100]):
+                    errors.append(("scan_partial", g, start))
+                rows = rng.integers(0, len(vals[g]), size=64)
+                if not np.array_equal(col.fetch_rows(np.full(64, g), rows), vals[g][rows]):
+                    errors.append(("fetch_rows", g))
+                s = col.scan_sum()
+                if (s.sum, s.count) != (want_sum, len(flat)):
+                    errors.append(("scan_sum", s.sum, s.count))
+                if not np.array_equal(col.decode(g, g + 1), flat[starts[g]:starts[g + 1]]):
+                    errors.append(("decode", g))
+        except Exception as exc:  # noqa: BLE001 -- reported below
+            errors.append(("exception", repr(exc)))
+
+    threads = [threading.Thread(target=reader, args=(i,)) for i in range(4)]
+    for t in threads:
+        t.start()
+    try:
+        for rnd in range(30):
+            b = rnd % 5
+            col.uncompact(b, b + 3)
+            col.compact(b, b + 3)
+    finally:
+        stop.set()
+        for t in threads:
+            t.join()
+    assert not errors, errors[:5]
+    assert np.array_equal(col.decode(), flat)
+    col.close()
