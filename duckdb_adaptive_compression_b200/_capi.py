@@ -87,6 +87,7 @@ _PROTOTYPES = {
     "adacom_point_filter_batch": (_i, [_vp, _u64, _vp, _vp, _i, _vp, _vp]),
     "adacom_scan_columns": (_i, [_vp, _vp, _u32, _vp, _u32, _u64, _u64, _i, _vp, _vp, _vp]),
     "adacom_scan_columns_async": (_i, [_vp, _vp, _u32, _vp, _u32, _u64, _u64, _i, _vp, _vp, _vp]),
+    "adacom_scan_columns_grouped": (_i, [_vp, _vp, _u32, _u32, _u32, _vp, _u32, _u64, _u64, _i, _vp, _vp, _vp, _i]),
     "adacom_fetch_rows": (_i, [_vp, _u64, _vp, _vp, _i, _vp, _i]),
     "adacom_compress_host": (_i, [_vp, _i, _vp, _u64, _vp, _u32, _i, _vp, _vp, _u64, C.POINTER(_u64), C.POINTER(_vp)]),
 }

@@ -187,8 +187,12 @@ def _wrap_i64(v: int) -> int:
 
 
 def scan_columns(ctx: "Context", terms, sums, row_begin: int = 0, row_end: int | None = None, flags: int = 0,
-                 bitmap_in: int | None = None, bitmap_out: int | None = None, device_out: int | None = None):
-    """Fused multi-column scan (adacom_scan_columns).
+                 bitmap_in: int | None = None, bitmap_out: int | None = None, device_out: int | None = None,
+                 group_by: tuple[int, int] | None = None):
+    """Fused multi-column scan (adacom_scan_columns / adacom_scan_columns_grouped).
+
+    group_by: (term_index, n_groups) -- GROUP BY the decoded value (0 .. n_groups-1) of that term in the same
+              pass; the result is then a list of n_groups lists of AggResult (device_out: group-major aggregates).
 
     terms: list of (Column, None) or (Column, (lo, hi)) -- inclusive range predicate on the decoded value;
     sums:  list of lists of (term_index, add, mul): SUM over the selected rows of prod (add + mul * value);
@@ -211,6 +215,16 @@ def scan_columns(ctx: "Context", terms, sums, row_begin: int = 0, row_end: int |
         row_end = terms[0][0].n_values
     b_in = C.c_void_p(bitmap_in) if bitmap_in else None
     b_out = C.c_void_p(bitmap_out) if bitmap_out else None
+    if group_by is not None:
+        g_term, n_g = group_by
+        if device_out is not None:
+            ctx.check(ctx.lib.adacom_scan_columns_grouped(ctx.h, t_arr, n_t, g_term, n_g, s_arr, n_s, row_begin, row_end,
+                                                          flags, b_in, b_out, C.c_void_p(device_out), 1))
+            return None
+        out = (Agg * max(n_s * n_g, 1))()
+        ctx.check(ctx.lib.adacom_scan_columns_grouped(ctx.h, t_arr, n_t, g_term, n_g, s_arr, n_s, row_begin, row_end,
+                                                      flags, b_in, b_out, out, 0))
+        return [[_agg_to_py(out[g * n_s + k], True) for k in range(n_s)] for g in range(n_g)]
     if device_out is not None:
         ctx.check(ctx.lib.adacom_scan_columns_async(ctx.h, t_arr, n_t, s_arr, n_s, row_begin, row_end, flags, b_in,
                                                     b_out, C.c_void_p(device_out)))

@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstring>
 #include <atomic>
+#include <cmath>
 #include <mutex>
 #include <new>
 #include <string>
@@ -1185,7 +1186,12 @@ extern "C" adacom_status adacom_point_filter_batch(adacom_column *col, uint64_t 
 
 static adacom_status plan_scan_columns(adacom_ctx *ctx, const adacom_scan_term *terms, uint32_t n_terms,
                                        const adacom_sum_expr *sums, uint32_t n_sums, uint64_t row_begin, uint64_t row_end,
-                                       int flags, QueryArgs &q) {
+                                       int flags, QueryArgs &q, uint32_t group_term = 0, uint32_t n_groups = 0) {
+	if (n_groups && (group_term >= n_terms || n_groups > (uint32_t)kQueryMaxGroups)) {
+		return fail(ctx, ADACOM_ERR_INVALID, "adacom_scan_columns_grouped: group term missing or more than 8 groups");
+	}
+	q.group_col = group_term;
+	q.n_groups = n_groups;
 	if (!terms || n_terms == 0 || n_terms > (uint32_t)kQueryMaxCols || !sums || n_sums == 0 ||
 	    n_sums > (uint32_t)kQueryMaxAggs || row_begin > row_end || (row_begin % kVectorSize) != 0) {
 		return fail(ctx, ADACOM_ERR_INVALID,
@@ -1233,6 +1239,44 @@ static adacom_status plan_scan_columns(adacom_ctx *ctx, const adacom_scan_term *
 			qa.mul[k] = sums[g].mul[k];
 		}
 	}
+	// 64-bit products: bound |value| per term from the analyzed min / max of the scanned segments (type range when a
+	// segment was never analyzed or mixes signs), then every prod_k (|add| + |mul| * bound) against 2^62
+	{
+		long double bound[kQueryMaxCols];
+		for (uint32_t c = 0; c < n_terms; c++) {
+			const adacom_column *col = terms[c].col;
+			const long double type_bound = col->t.is_signed ? ldexpl(1.0L, 8 * col->t.size - 1) : ldexpl(1.0L, 8 * col->t.size);
+			long double b = 0;
+			for (uint64_t g = 0; g < col->n_segs && b < type_bound; g++) {
+				const SegDesc &d = col->h_desc[g];
+				if (d.count == 0 || d.row_start + d.count <= row_begin || d.row_start >= row_end) {
+					continue;
+				}
+				if (!(d.state & kSegAnalyzed) || d.min_factor == ~0ull) {
+					b = type_bound;
+				} else if (col->t.is_signed) {
+					const int64_t lo = (int64_t)d.min_factor, hi = (int64_t)d.max_factor;
+					if (lo >= 0 && hi < 0) {
+						b = type_bound;  // unsigned order of sign-extended patterns: the segment mixes signs
+					} else {
+						b = fmaxl(b, fmaxl(fabsl((long double)lo), fabsl((long double)hi)));
+					}
+				} else {
+					b = fmaxl(b, (long double)d.max_factor);
+				}
+			}
+			bound[c] = fminl(b, type_bound);
+		}
+		bool narrow = true;
+		for (uint32_t g = 0; g < n_sums && narrow; g++) {
+			long double prod = 1;
+			for (uint32_t k = 0; k < sums[g].n_factors; k++) {
+				prod *= fabsl((long double)sums[g].add[k]) + fabsl((long double)sums[g].mul[k]) * bound[sums[g].term[k]];
+			}
+			narrow = prod < ldexpl(1.0L, 62);
+		}
+		q.narrow_products = narrow ? 1u : 0u;
+	}
 	// row-block size and pipeline depth: the largest block whose worst-case staged bytes leave room for two
 	// CTAs per SM (shrunk while the table offers fewer than ~4 blocks per SM)
 	const uint64_t n_rows = row_end - row_begin;
@@ -1242,14 +1286,15 @@ static adacom_status plan_scan_columns(adacom_ctx *ctx, const adacom_scan_term *
 	uint32_t R = 0, stages = 0;
 	for (uint32_t r : {8192u, 4096u, 2048u}) {
 		for (uint32_t st : {3u, 2u}) {
-			if (!R && st * stage_bytes(r) <= 48u * 1024u) {  // + ~26 KiB static: three CTAs per SM
+			// + ~26 KiB static (+ the GROUP BY scratch): three CTAs per SM
+			if (!R && st * stage_bytes(r) + (n_groups ? scan_columns_group_smem() : 0u) <= 48u * 1024u) {
 				R = r;
 				stages = st;
 			}
 		}
 	}
 	for (uint32_t limit : {84u * 1024u, 196u * 1024u}) {  // two CTAs per SM, then one
-		if (!R && 2 * stage_bytes(2048) <= limit) {
+		if (!R && 2 * stage_bytes(2048) + (n_groups ? scan_columns_group_smem() : 0u) <= limit) {
 			R = 2048;
 			stages = 2;
 		}
@@ -1320,8 +1365,8 @@ extern "C" adacom_status adacom_scan_columns(adacom_ctx *ctx, const adacom_scan_
 	}
 	if (!ctx->d_aggs) {
 		std::lock_guard<std::mutex> lock(ctx->mu);
-		CK(ctx, cudaMalloc((void **)&ctx->d_aggs, kQueryMaxAggs * sizeof(Agg)));
-		CK(ctx, cudaHostAlloc((void **)&ctx->h_aggs, kQueryMaxAggs * sizeof(Agg), cudaHostAllocDefault));
+		CK(ctx, cudaMalloc((void **)&ctx->d_aggs, kQueryMaxAggs * kQueryMaxGroups * sizeof(Agg)));
+		CK(ctx, cudaHostAlloc((void **)&ctx->h_aggs, kQueryMaxAggs * kQueryMaxGroups * sizeof(Agg), cudaHostAllocDefault));
 	}
 	adacom_status st = adacom_scan_columns_async(ctx, terms, n_terms, sums, n_sums, row_begin, row_end, flags,
 	                                             device_bitmap_in, device_bitmap_out, (adacom_agg *)ctx->d_aggs);
@@ -1332,6 +1377,38 @@ extern "C" adacom_status adacom_scan_columns(adacom_ctx *ctx, const adacom_scan_
 	CK(ctx, cudaMemcpyAsync(ctx->h_aggs, ctx->d_aggs, n_sums * sizeof(Agg), cudaMemcpyDeviceToHost, ctx->stream));
 	CK(ctx, cudaStreamSynchronize(ctx->stream));
 	memcpy(out, ctx->h_aggs, n_sums * sizeof(Agg));
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_scan_columns_grouped(adacom_ctx *ctx, const adacom_scan_term *terms, uint32_t n_terms,
+                                                     uint32_t group_term, uint32_t n_groups,
+                                                     const adacom_sum_expr *sums, uint32_t n_sums, uint64_t row_begin,
+                                                     uint64_t row_end, int flags, const uint64_t *device_bitmap_in,
+                                                     uint64_t *device_bitmap_out, adacom_agg *out, int out_on_device) {
+	if (!ctx || !out || n_groups == 0 || n_sums > (uint32_t)kQueryMaxAggs) {
+		return fail(ctx, ADACOM_ERR_INVALID, "adacom_scan_columns_grouped: NULL argument, no groups or more than 8 sums");
+	}
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	if (!ctx->d_aggs) {
+		CK(ctx, cudaMalloc((void **)&ctx->d_aggs, kQueryMaxAggs * kQueryMaxGroups * sizeof(Agg)));
+		CK(ctx, cudaHostAlloc((void **)&ctx->h_aggs, kQueryMaxAggs * kQueryMaxGroups * sizeof(Agg), cudaHostAllocDefault));
+	}
+	QueryArgs q;
+	adacom_status st = plan_scan_columns(ctx, terms, n_terms, sums, n_sums, row_begin, row_end, flags, q, group_term, n_groups);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	const size_t bytes = (size_t)n_groups * n_sums * sizeof(Agg);
+	q.in_bitmap = (const uint32_t *)device_bitmap_in;
+	q.out_bitmap = (uint32_t *)device_bitmap_out;
+	q.out = out_on_device ? (Agg *)out : ctx->d_aggs;
+	CK(ctx, cudaMemsetAsync(q.out, 0, bytes, ctx->stream));
+	LAUNCH(ctx, launch_scan_columns(q, ctx->sm_count, ctx->stream));
+	if (!out_on_device) {
+		CK(ctx, cudaMemcpyAsync(ctx->h_aggs, ctx->d_aggs, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(ctx, cudaStreamSynchronize(ctx->stream));
+		memcpy(out, ctx->h_aggs, bytes);
+	}
 	return ADACOM_OK;
 }
 

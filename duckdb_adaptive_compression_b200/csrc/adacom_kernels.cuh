@@ -64,6 +64,7 @@ constexpr int kQueryMaxCols = 8;
 constexpr int kQueryMaxPieces = 3;   // segments of one column a row block may touch
 constexpr int kQueryMaxAggs = 8;
 constexpr int kQueryMaxFactors = 3;
+constexpr int kQueryMaxGroups = 8;
 
 struct QueryCol {
 	const SegDesc *desc = nullptr;
@@ -93,12 +94,17 @@ struct QueryArgs {
 	uint32_t stages = 2;
 	uint32_t stage_bytes = 0;             // multiple of 128: worst-case staged bytes of one row block
 	int literal = 0;
+	uint32_t narrow_products = 0;         // every prod_k (add + mul * value) provably fits int64: 64-bit products
+	uint32_t group_col = 0;               // GROUP BY: column whose decoded value (0 .. n_groups-1) is the group key
+	uint32_t n_groups = 0;                // 0: no grouping; rows whose key is outside the range are dropped
 	const uint32_t *in_bitmap = nullptr;  // optional selection (bit r - row_begin), AND-ed
 	uint32_t *out_bitmap = nullptr;       // optional: the resulting selection
-	Agg *out = nullptr;                   // n_aggs aggregates (zeroed by the caller); count = selected rows
+	Agg *out = nullptr;                   // n_aggs (x n_groups, group-major) aggregates, zeroed by the caller;
+	                                      // count = selected rows (of the group)
 };
 
 cudaError_t launch_scan_columns(const QueryArgs &args, int sm_count, cudaStream_t stream);
+uint32_t scan_columns_group_smem();  // extra dynamic shared memory of a grouped launch (bytes)
 
 // scan_vector / scan_partial of one segment, arbitrary start (generic unaligned path, no staging)
 cudaError_t launch_scan_range(TypeInfo t, const SegDesc *desc, uint32_t seg, const uint8_t *raw, uint64_t start,

@@ -198,6 +198,25 @@ __device__ __forceinline__ void aggregate_list(const QueryArgs &a, const QStage 
 				vals[c][tid] = column_value(st.piece[c], stage, i, qc.type_size, qc.is_signed);
 			}
 		}
+		if (a.narrow_products) {
+			// the planner bounded every product below 2^63 from the segments' min / max: plain 64-bit multiplies
+			// (a 128 x 128-bit product costs ~40 instructions, Q1 has 16 of them per row)
+#pragma unroll
+			for (int g = 0; g < kQueryMaxAggs; g++) {
+				if (g < (int)a.n_aggs) {
+					const QueryAgg &qa = a.aggs[g];
+					int64_t term = 1;
+#pragma unroll
+					for (int k = 0; k < kQueryMaxFactors; k++) {
+						if (k < (int)qa.n_factors) {
+							term *= qa.add[k] + qa.mul[k] * (int64_t)vals[qa.col[k]][tid];
+						}
+					}
+					acc[g] += (unsigned __int128)(__int128)term;
+				}
+			}
+			continue;
+		}
 #pragma unroll
 		for (int g = 0; g < kQueryMaxAggs; g++) {
 			if (g < (int)a.n_aggs) {
@@ -214,6 +233,111 @@ __device__ __forceinline__ void aggregate_list(const QueryArgs &a, const QStage 
 			}
 		}
 	}
+}
+
+// GROUP BY a small-domain column: the warp's survivor list is split by group key into dense sub-lists (ballot
+// compaction), every sub-list is folded with the per-thread register accumulators exactly like the ungrouped
+// case, and the warp's partial sums are then reduced and added to its private row of shared accumulators -- no
+// atomics, no divergent per-row group dispatch.
+struct GroupAcc {
+	unsigned long long sum[kQConsumerWarps][kQueryMaxGroups][kQueryMaxAggs][2];
+	unsigned long long cnt[kQConsumerWarps][kQueryMaxGroups];
+};
+
+struct GroupScratch {
+	GroupAcc acc;
+	uint16_t list[kQConsumerWarps][kQListCap];  // the warp's surviving rows, sorted by group
+	uint8_t keys[kQConsumerWarps][kQListCap];
+};
+
+__device__ __forceinline__ void aggregate_grouped(const QueryArgs &a, const QStage &st, const uint8_t *stage,
+                                                  const uint16_t *my_list, uint32_t n_list, uint16_t *sub_list,
+                                                  uint8_t *keys, GroupAcc &ga, uint64_t (*vals)[kQConsumers],
+                                                  uint32_t tid, uint32_t lane, uint32_t warp, unsigned __int128 *acc) {
+	if (n_list == 0) {
+		return;
+	}
+	const QueryCol &gc = a.cols[a.group_col];
+	uint32_t count[kQueryMaxGroups];
+#pragma unroll
+	for (int g = 0; g < kQueryMaxGroups; g++) {
+		count[g] = 0;
+	}
+	for (uint32_t e0 = 0; e0 < n_list; e0 += 32u) {  // pass 1: keys and group sizes
+		const uint32_t e = e0 + lane;
+		uint32_t key = 0xffu;
+		if (e < n_list) {
+			const uint64_t v = column_value(st.piece[a.group_col], stage, my_list[e], gc.type_size, gc.is_signed);
+			key = v < (uint64_t)a.n_groups ? (uint32_t)v : 0xffu;
+			keys[e] = (uint8_t)key;
+		}
+#pragma unroll
+		for (int g = 0; g < kQueryMaxGroups; g++) {
+			if (g < (int)a.n_groups) {
+				count[g] += __popc(__ballot_sync(0xffffffffu, key == (uint32_t)g));
+			}
+		}
+	}
+	uint32_t offset[kQueryMaxGroups];
+	uint32_t run = 0;
+#pragma unroll
+	for (int g = 0; g < kQueryMaxGroups; g++) {
+		offset[g] = run;
+		run += count[g];
+	}
+	__syncwarp();
+	for (uint32_t e0 = 0; e0 < n_list; e0 += 32u) {  // pass 2: scatter into the group's slice
+		const uint32_t e = e0 + lane;
+		const uint32_t key = e < n_list ? keys[e] : 0xffu;
+		const uint16_t row = e < n_list ? my_list[e] : 0;
+#pragma unroll
+		for (int g = 0; g < kQueryMaxGroups; g++) {
+			if (g < (int)a.n_groups) {
+				const uint32_t m = __ballot_sync(0xffffffffu, key == (uint32_t)g);
+				if (key == (uint32_t)g) {
+					sub_list[offset[g] + __popc(m & ((1u << lane) - 1u))] = row;
+				}
+				offset[g] += __popc(m);
+			}
+		}
+	}
+	__syncwarp();
+	uint32_t begin = 0;
+#pragma unroll 1
+	for (uint32_t g = 0; g < a.n_groups; g++) {
+		const uint32_t n = count[g];
+		if (n == 0) {
+			continue;
+		}
+#pragma unroll
+		for (int k = 0; k < kQueryMaxAggs; k++) {
+			acc[k] = 0;
+		}
+		aggregate_list(a, st, stage, sub_list + begin, n, vals, tid, lane, acc);
+		begin += n;
+#pragma unroll
+		for (int k = 0; k < kQueryMaxAggs; k++) {
+			if (k < (int)a.n_aggs) {
+				uint64_t lo = (uint64_t)acc[k], hi = (uint64_t)(acc[k] >> 64);
+#pragma unroll
+				for (int d = 16; d > 0; d >>= 1) {
+					const uint64_t olo = __shfl_down_sync(0xffffffffu, lo, d);
+					const uint64_t ohi = __shfl_down_sync(0xffffffffu, hi, d);
+					add128(lo, hi, olo, ohi);
+				}
+				if (lane == 0) {
+					uint64_t slo = ga.sum[warp][g][k][0], shi = ga.sum[warp][g][k][1];
+					add128(slo, shi, lo, hi);
+					ga.sum[warp][g][k][0] = slo;
+					ga.sum[warp][g][k][1] = shi;
+				}
+			}
+		}
+		if (lane == 0) {
+			ga.cnt[warp][g] += n;
+		}
+	}
+	__syncwarp();
 }
 
 __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryArgs a) {
@@ -239,6 +363,15 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 			mbar_init(&empty_bar[s], kQConsumerWarps);
 		}
 		mbar_fence_init();
+	}
+	// GROUP BY scratch lives behind the stages in dynamic shared memory (only allocated for grouped launches)
+	GroupScratch &gs = *(GroupScratch *)(q_stage_mem + (size_t)n_stages * a.stage_bytes);
+	GroupAcc &gacc = gs.acc;
+	if (a.n_groups) {
+		unsigned long long *z = (unsigned long long *)&gacc;
+		for (uint32_t i = tid; i < sizeof(GroupAcc) / 8; i += kQThreads) {
+			z[i] = 0ull;
+		}
 	}
 	__syncthreads();
 
@@ -483,18 +616,47 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 				n_list += __popc(word);
 				if (n_list > kQListCap - 32u) {
 					__syncwarp();
-					aggregate_list(a, st, stage, my_list, n_list, vals, tid, lane, acc);
+					if (a.n_groups) {
+						aggregate_grouped(a, st, stage, my_list, n_list, gs.list[warp], gs.keys[warp], gacc, vals, tid, lane, warp,
+						                  acc);
+					} else {
+						aggregate_list(a, st, stage, my_list, n_list, vals, tid, lane, acc);
+					}
 					n_list = 0;
 					__syncwarp();
 				}
 			}
 			__syncwarp();
-			aggregate_list(a, st, stage, my_list, n_list, vals, tid, lane, acc);
+			if (a.n_groups) {
+				aggregate_grouped(a, st, stage, my_list, n_list, gs.list[warp], gs.keys[warp], gacc, vals, tid, lane, warp, acc);
+			} else {
+				aggregate_list(a, st, stage, my_list, n_list, vals, tid, lane, acc);
+			}
 			__syncwarp();
 			if (lane == 0) {
 				mbar_arrive(&empty_bar[s]);
 			}
 		}
+	}
+	if (a.n_groups) {
+		// one thread per (group, aggregate): add up the 8 warp rows, one atomic triple per CTA
+		__syncthreads();
+		if (tid < a.n_groups * a.n_aggs) {
+			const uint32_t g = tid / a.n_aggs, k = tid % a.n_aggs;
+			uint64_t lo = 0, hi = 0, cnt = 0;
+			for (int wv = 0; wv < kQConsumerWarps; wv++) {
+				add128(lo, hi, gacc.sum[wv][g][k][0], gacc.sum[wv][g][k][1]);
+				cnt += gacc.cnt[wv][g];
+			}
+			if (cnt | lo | hi) {
+				Agg *out = a.out + g * a.n_aggs + k;
+				const unsigned long long old = atomicAdd((unsigned long long *)&out->sum_lo, (unsigned long long)lo);
+				const unsigned long long carry = (old + lo < old) ? 1ull : 0ull;
+				atomicAdd((unsigned long long *)&out->sum_hi, (unsigned long long)(hi + carry));
+				atomicAdd((unsigned long long *)&out->count, (unsigned long long)cnt);
+			}
+		}
+		return;
 	}
 #pragma unroll
 	for (int g = 0; g < kQueryMaxAggs; g++) {
@@ -506,9 +668,13 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 
 }  // namespace
 
+uint32_t scan_columns_group_smem() {
+	return (uint32_t)((sizeof(GroupScratch) + 127u) & ~127u);
+}
+
 cudaError_t launch_scan_columns(const QueryArgs &args, int sm_count, cudaStream_t stream) {
 	static size_t configured[64] = {};
-	const size_t smem = (size_t)args.stages * args.stage_bytes;
+	const size_t smem = (size_t)args.stages * args.stage_bytes + (args.n_groups ? sizeof(GroupScratch) : 0);
 	int dev = 0;
 	cudaGetDevice(&dev);
 	if (configured[dev & 63] < smem) {

@@ -101,18 +101,29 @@ class LineitemTable:
     Q1_COLUMNS = ("l_shipdate", "l_rfls", "l_quantity", "l_extendedprice", "l_discount", "l_tax")
     Q1_SUMS = ("sum_qty", "sum_base_price", "sum_disc_price", "sum_charge", "sum_disc")
 
-    def q1(self) -> dict:
-        """{group code: {sum_qty, sum_base_price, sum_disc_price (x100^1 scale 4), sum_charge (scale 6), sum_disc,
-        count}} -- integer sums at DuckDB's DECIMAL scales; the averages are sum / count.  One fused pass per group
-        (the group code is one more range predicate); a single-pass grouped accumulator is a later step."""
+    Q1_SUM_EXPRS = [[(2, 0, 1)], [(3, 0, 1)], [(3, 0, 1), (4, 100, -1)], [(3, 0, 1), (4, 100, -1), (5, 100, 1)], [(4, 0, 1)]]
+
+    def _q1_terms(self, code=None):
         c = self.cols
+        return [(c["l_shipdate"], (-(1 << 31), D_1998_09_02)), (c["l_rfls"], None if code is None else (code, code)),
+                (c["l_quantity"], None), (c["l_extendedprice"], None), (c["l_discount"], None), (c["l_tax"], None)]
+
+    def q1(self, device_out: int | None = None) -> dict:
+        """{group code: {sum_qty, sum_base_price, sum_disc_price (x100^1 scale 4), sum_charge (scale 6), sum_disc,
+        count}} -- integer sums at DuckDB's DECIMAL scales; the averages are sum / count.  ONE fused pass: the
+        (returnflag, linestatus) code is the GROUP BY key of the scan (4 groups x 5 sums)."""
+        res = scan_columns(self.ctx, self._q1_terms(), self.Q1_SUM_EXPRS, 0, self.n_rows, group_by=(1, 4),
+                           device_out=device_out)
+        if res is None:
+            return None
+        return {code: dict(zip(self.Q1_SUMS, (r.sum for r in grp)), count=grp[0].count)
+                for code, grp in enumerate(res) if grp[0].count}
+
+    def q1_per_group_passes(self) -> dict:
+        """The same answer from one filtered pass per group (the group code as a fourth predicate)."""
         out = {}
         for code in range(4):
-            terms = [(c["l_shipdate"], (-(1 << 31), D_1998_09_02)), (c["l_rfls"], (code, code)), (c["l_quantity"], None),
-                     (c["l_extendedprice"], None), (c["l_discount"], None), (c["l_tax"], None)]
-            sums = [[(2, 0, 1)], [(3, 0, 1)], [(3, 0, 1), (4, 100, -1)], [(3, 0, 1), (4, 100, -1), (5, 100, 1)],
-                    [(4, 0, 1)]]
-            res = scan_columns(self.ctx, terms, sums, 0, self.n_rows)
+            res = scan_columns(self.ctx, self._q1_terms(code), self.Q1_SUM_EXPRS, 0, self.n_rows)
             if res[0].count:
                 out[code] = dict(zip(self.Q1_SUMS, (r.sum for r in res)), count=res[0].count)
         return out

@@ -250,6 +250,15 @@ adacom_status adacom_scan_columns_async(adacom_ctx *ctx, const adacom_scan_term 
                                         const adacom_sum_expr *sums, uint32_t n_sums, uint64_t row_begin,
                                         uint64_t row_end, int flags, const uint64_t *device_bitmap_in,
                                         uint64_t *device_bitmap_out, adacom_agg *device_out);
+/* GROUP BY a small-domain column in the same pass (TPC-H Q1: extension/tpch/dbgen/queries/q01.sql): the decoded
+ * value of terms[group_term] (0 .. n_groups-1, n_groups <= 8; rows with any other value are dropped) selects the
+ * group; out[g * n_sums + s] = aggregate s of group g.  out: host pointer, or device pointer when out_on_device
+ * (then the call is asynchronous). */
+adacom_status adacom_scan_columns_grouped(adacom_ctx *ctx, const adacom_scan_term *terms, uint32_t n_terms,
+                                          uint32_t group_term, uint32_t n_groups, const adacom_sum_expr *sums,
+                                          uint32_t n_sums, uint64_t row_begin, uint64_t row_end, int flags,
+                                          const uint64_t *device_bitmap_in, uint64_t *device_bitmap_out,
+                                          adacom_agg *out, int out_on_device);
 /* ---- fetch_row ------------------------------------------------------------------------------------------ */
 /* batched random access: out[q] = T(vec(seg_idx[q])[row_in_seg[q]] + min).  Host pointers unless
  * on_device (then all three are device pointers). */

@@ -30,9 +30,60 @@ def test_q6_matches_numpy(table):
     assert t.cols["l_discount"].meta()[0].width == 4 and t.cols["l_quantity"].meta()[0].width == 6
 
 
+def test_grouped_scan_matches_per_group_passes_on_ragged_data(gpu_ctx):
+    """GROUP BY in the fused scan: keys outside 0..n_groups-1 are dropped, groups may be empty, the predicate and the
+    bitmap still apply; compared with numpy and with one filtered pass per group."""
+    rng = np.random.default_rng(3)
+    n = 3 * 122880 + 777
+    key = rng.integers(0, 7, size=n).astype(np.uint8)          # 7 distinct values, only 0..4 are groups
+    key[rng.random(n) < 0.5] = 2                                # skewed; group 4 stays rare
+    key[key == 3] = 6                                           # group 3 empty
+    a = rng.integers(-1000, 1000, size=n).astype(np.int32)
+    b = rng.integers(0, 1 << 40, size=n).astype(np.int64)
+    c = rng.integers(0, 50, size=n).astype(np.int16)
+    cols = {}
+    for name, v in (("key", key), ("a", a), ("b", b), ("c", c)):
+        cols[name] = gpu_ctx.column_from_values(v, adacom.row_group_segment_counts(n, v.dtype))
+        cols[name].compact()
+    terms = [(cols["c"], (5, 40)), (cols["key"], None), (cols["a"], None), (cols["b"], None)]
+    sums = [[(2, 0, 1)], [(3, 0, 1), (2, 7, -1)], []]
+    got = adacom.scan_columns(gpu_ctx, terms, sums, 0, n, group_by=(1, 5))
+    sel = (c >= 5) & (c <= 40)
+    for g in range(5):
+        m = sel & (key == g)
+        want = [int(a[m].astype(object).sum()), int((b[m].astype(object) * (7 - a[m].astype(object))).sum()), int(m.sum())]
+        assert [r.sum for r in got[g]] == want, g
+        assert all(r.count == int(m.sum()) for r in got[g]), g
+        per = adacom.scan_columns(gpu_ctx, [(cols["c"], (5, 40)), (cols["key"], (g, g)), (cols["a"], None), (cols["b"], None)],
+                                  sums, 0, n)
+        assert [r.sum for r in per] == want and per[0].count == int(m.sum())
+    # a sub-range that starts inside the table
+    r0, r1 = 2048 * 31, n - 5
+    got = adacom.scan_columns(gpu_ctx, terms, sums, r0, r1, group_by=(1, 5))
+    for g in range(5):
+        m = sel[r0:r1] & (key[r0:r1] == g)
+        assert got[g][0].sum == int(a[r0:r1][m].astype(object).sum()) and got[g][2].sum == int(m.sum())
+    # a product that needs more than 64 bits switches the whole query to 128-bit products
+    wide = sums + [[(3, 0, 1), (3, 5, 1), (2, 0, 1)]]
+    got = adacom.scan_columns(gpu_ctx, terms, wide, 0, n, group_by=(1, 5))
+    flat = adacom.scan_columns(gpu_ctx, terms, wide, 0, n)
+    for g in range(5):
+        m = sel & (key == g)
+        bo, ao = b[m].astype(object), a[m].astype(object)
+        assert got[g][3].sum == int((bo * (5 + bo) * ao).sum()), g
+        assert got[g][0].sum == int(ao.sum())
+    bo, ao = b[sel].astype(object), a[sel].astype(object)
+    assert flat[3].sum == int((bo * (5 + bo) * ao).sum()) and flat[3].count == int(sel.sum())
+    with pytest.raises(adacom.AdacomError):
+        adacom.scan_columns(gpu_ctx, terms, sums, 0, n, group_by=(1, 9))
+    for col in cols.values():
+        col.close()
+
+
 def test_q1_matches_numpy(table):
     cols, t = table
     assert t.q1() == tpch.q1_expected(cols)
+    assert t.q1_per_group_passes() == tpch.q1_expected(cols)
 
 
 def test_bitmaps_and_row_ranges(gpu_ctx, table):
