@@ -16,7 +16,7 @@ ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum 
 QB="python tools/quick_bench.py 27 17,40"
 $QB > $OUT/${TAG}_qb_plain.log 2>&1 &&
 ncu --set full --clock-control none \
-    -k regex:"decode_kernel|pack_kernel|analyze_kernel|scan_sum_fields|layout_kernel" -c 20 -o $OUT/${TAG}_prof \
+    -k regex:"decode_kernel|pack_staged_kernel|analyze_kernel|scan_sum_fields|layout_kernel" -c 20 -o $OUT/${TAG}_prof \
     $QB > $OUT/${TAG}_ncu_full.log 2>&1
 tail -c 400 $OUT/${TAG}_plain.log; echo
 tail -2 $OUT/${TAG}_qb_plain.log | cut -c1-300
