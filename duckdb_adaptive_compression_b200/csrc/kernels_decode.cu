@@ -247,6 +247,59 @@ __global__ void __launch_bounds__(kThreads, StageCfg<S, MODE>::kMinCtas) decode_
 				constant = (uint64_t)a.q_const[query];
 			}
 
+			bool point_done = false;
+			if (MODE == kModePoint) {
+				// Equality look-up in the FIELD domain: value == c  <=>  field == (c - min) mod 2^(8S), and a field
+				// is < 2^w -- a chunk whose target does not fit w bits cannot match and is not touched at all.
+				// Byte-aligned widths (8 / 16 / 32 bits: the reference's benchmark columns pack to 16) are compared
+				// 16 bytes per lane and step with the SIMD-in-a-word compares; a hit (rare) is resolved per field.
+				const uint64_t tf = (constant - in.min_add) & lo_set64(8 * S);
+				if (w < 64u && (tf >> w) != 0) {
+					point_done = true;
+				} else if ((w == 8u || w == 16u || w == 32u) && (in.bit_base & 127u) == 0) {
+					const uint4 *vec = (const uint4 *)((const uint8_t *)words + (in.bit_base >> 3));
+					const uint32_t per = 128u / w;  // fields per 16 bytes
+					const uint32_t n_vec = (in.cnt + per - 1u) / per;
+					const uint32_t t32 = (uint32_t)tf;
+					const uint32_t kk = w == 32u ? t32 : (w == 16u ? t32 * 0x00010001u : t32 * 0x01010101u);
+					for (uint32_t j = gtid; j < n_vec; j += kGroupThreads) {
+						const uint4 x = vec[j];
+						uint32_t m0, m1, m2, m3;
+						if (w == 32u) {
+							m0 = x.x == kk;
+							m1 = x.y == kk;
+							m2 = x.z == kk;
+							m3 = x.w == kk;
+						} else if (w == 16u) {
+							m0 = __vcmpeq2(x.x, kk);
+							m1 = __vcmpeq2(x.y, kk);
+							m2 = __vcmpeq2(x.z, kk);
+							m3 = __vcmpeq2(x.w, kk);
+						} else {
+							m0 = __vcmpeq4(x.x, kk);
+							m1 = __vcmpeq4(x.y, kk);
+							m2 = __vcmpeq4(x.z, kk);
+							m3 = __vcmpeq4(x.w, kk);
+						}
+						if (m0 | m1 | m2 | m3) {
+							const uint32_t xs[4] = {x.x, x.y, x.z, x.w};
+							for (uint32_t f = 0; f < per; f++) {
+								const uint32_t i = j * per + f;
+								const uint32_t fb = f * w;  // bit of the field inside the 16 bytes
+								const uint32_t fv = w == 32u ? xs[fb >> 5] : ((xs[fb >> 5] >> (fb & 31u)) & mask32);
+								if (i < in.cnt && fv == t32) {
+									atomicAdd(a.q_count + query, 1ull);
+									atomicMin(a.q_first + query, (unsigned long long)(in.first_value + i));
+								}
+							}
+						}
+					}
+					point_done = true;
+				}
+			}
+			if (MODE == kModePoint && point_done) {
+				// fall through to the barrier / stage release below
+			} else
 			if (StageCfg<S, MODE>::kTmaStore) {
 				// decoded values go to a shared output tile placed so that shared and global addresses agree mod 16;
 				// the 16-byte aligned middle leaves as ONE bulk store, the (at most one each) head / tail elements
@@ -354,7 +407,7 @@ __global__ void __launch_bounds__(kThreads, StageCfg<S, MODE>::kMinCtas) decode_
 					dst[j * kGroupThreads] = (T)x[j];
 				}
 			} else
-			for (uint32_t base = 0; base < in.cnt; base += kGroupThreads) {
+			for (uint32_t base = 0; base < in.cnt && !(MODE == kModePoint && point_done); base += kGroupThreads) {
 				const uint32_t i = base + gtid;
 				const bool valid = i < in.cnt;
 				uint64_t x = 0;

@@ -312,3 +312,41 @@ def test_concurrent_readers_and_a_recompacting_writer(gpu_ctx, port_oracle):
     assert not errors, errors[:5]
     assert np.array_equal(col.decode(), flat)
     col.close()
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.int16, np.uint32, np.int32, np.int64], ids=lambda d: np.dtype(d).name)
+def test_point_lookups_hits_misses_duplicates(gpu_ctx, dtype):
+    """adacom_point_filter_batch == `value = k` on one segment (the reference's zipf_distribution.cpp look-up):
+    byte-aligned widths take the SIMD field compare, the others the generic path; keys that are absent, below the
+    frame of reference, beyond the field range or duplicated must all give numpy's count and first row."""
+    dt = np.dtype(dtype)
+    bits = 8 * dt.itemsize
+    rng = np.random.default_rng(9)
+    info = np.iinfo(dt)
+    segs = []
+    for w in sorted({1, 7, 8, 13, 16, 24, 32, bits - 1, bits} & set(range(1, bits + 1))):
+        for base in (0, 1000, int(info.min) if dt.kind == "i" else 3):
+            n = int(rng.integers(3000, 9000))
+            lo = min(max(int(info.min), base), int(info.max) - 1)
+            hi = min(int(info.max), lo + (1 << w) - 1) if w < 64 else int(info.max)
+            v = rng.integers(lo, hi, size=n, endpoint=True, dtype=np.int64 if bits < 64 or dt.kind == "i" else np.uint64)
+            v = v.astype(dtype)
+            v[: n // 50] = v[0]  # duplicates
+            segs.append(v)
+    col = gpu_ctx.column_from_values(np.concatenate(segs), [len(v) for v in segs])
+    col.compact()
+    q_seg, q_key = [], []
+    for g, v in enumerate(segs):
+        present = [int(v[0]), int(v[-1]), int(v[len(v) // 2])]
+        absent = [int(v.min()) - 1, int(v.max()) + 1, int(info.min), int(info.max), 0]
+        for k in present + absent:
+            if int(info.min) <= k <= int(info.max):
+                q_seg.append(g)
+                q_key.append(k)
+    cnt, first = col.point_filter_batch(np.array(q_seg), np.array(q_key, dtype=np.int64 if dt.kind == "i" or bits < 64 else np.uint64).astype(np.int64))
+    for j, (g, k) in enumerate(zip(q_seg, q_key)):
+        hit = np.nonzero(segs[g] == np.array(k).astype(dtype))[0]
+        assert cnt[j] == len(hit), (g, k, col.meta(g, g + 1)[0].width)
+        if len(hit):
+            assert first[j] == hit[0], (g, k)
+    col.close()
