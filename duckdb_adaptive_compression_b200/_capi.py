@@ -14,8 +14,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("ADACOM_GPU_LIB") or os.path.join(HERE, "csrc", "libadacom_gpu.so")
 HEADER_PATH = os.path.join(os.path.dirname(HERE), "include", "adacom_gpu.h")
 
-OK, ERR_INVALID, ERR_CUDA, ERR_NOMEM, ERR_UNSUPPORTED, ERR_STATE, ERR_NO_DEVICE = range(7)
-STATUS_NAMES = ["OK", "ERR_INVALID", "ERR_CUDA", "ERR_NOMEM", "ERR_UNSUPPORTED", "ERR_STATE", "ERR_NO_DEVICE"]
+OK, ERR_INVALID, ERR_CUDA, ERR_NOMEM, ERR_UNSUPPORTED, ERR_STATE, ERR_NO_DEVICE, ERR_CORRUPT = range(8)
+STATUS_NAMES = ["OK", "ERR_INVALID", "ERR_CUDA", "ERR_NOMEM", "ERR_UNSUPPORTED", "ERR_STATE", "ERR_NO_DEVICE",
+                "ERR_CORRUPT"]
 
 UINT8, INT8, UINT16, INT16, UINT32, INT32, UINT64, INT64 = 2, 3, 4, 5, 6, 7, 8, 9
 CMP_EQ, CMP_NE, CMP_LT, CMP_GT, CMP_LE, CMP_GE = range(6)
@@ -43,6 +44,20 @@ class SumExpr(C.Structure):
     _fields_ = [("n_factors", C.c_uint32), ("term", C.c_uint32 * 3), ("add", C.c_int64 * 3), ("mul", C.c_int64 * 3)]
 
 
+class ImageHeader(C.Structure):
+    _fields_ = [("magic", C.c_char * 8), ("version", C.c_uint32), ("ptype", C.c_uint32), ("n_segments", C.c_uint64),
+                ("n_blocks", C.c_uint64), ("n_values", C.c_uint64), ("blocks_offset", C.c_uint64),
+                ("total_bytes", C.c_uint64), ("meta_checksum", C.c_uint64)]
+
+
+class DataPointer(C.Structure):
+    _fields_ = [("row_start", C.c_uint64), ("tuple_count", C.c_uint64), ("block_id", C.c_int64),
+                ("offset", C.c_uint32), ("payload_bytes", C.c_uint32), ("min_factor", C.c_uint64),
+                ("max_factor", C.c_uint64), ("capacity", C.c_uint32), ("compression_type", C.c_uint8),
+                ("width", C.c_uint8), ("state", C.c_uint8), ("type_size", C.c_uint8), ("reserved", C.c_uint64)]
+
+
+assert C.sizeof(ImageHeader) == 64 and C.sizeof(DataPointer) == 64
 assert C.sizeof(SegmentMeta) == 64 and C.sizeof(Agg) == 32 and C.sizeof(ScanTerm) == 32 and C.sizeof(SumExpr) == 64
 
 _vp, _u64, _u32, _i = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int
@@ -89,6 +104,9 @@ _PROTOTYPES = {
     "adacom_scan_columns_async": (_i, [_vp, _vp, _u32, _vp, _u32, _u64, _u64, _i, _vp, _vp, _vp]),
     "adacom_scan_columns_grouped": (_i, [_vp, _vp, _u32, _u32, _u32, _vp, _u32, _u64, _u64, _i, _vp, _vp, _vp, _i]),
     "adacom_fetch_rows": (_i, [_vp, _u64, _vp, _vp, _i, _vp, _i]),
+    "adacom_column_checkpoint_size": (_i, [_vp, C.POINTER(_u64)]),
+    "adacom_column_checkpoint": (_i, [_vp, _vp, _u64, _i, C.POINTER(_u64)]),
+    "adacom_column_restore": (_i, [_vp, _vp, _u64, _i, C.POINTER(_vp)]),
     "adacom_compress_host": (_i, [_vp, _i, _vp, _u64, _vp, _u32, _i, _vp, _vp, _u64, C.POINTER(_u64), C.POINTER(_vp)]),
 }
 

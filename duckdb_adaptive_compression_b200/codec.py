@@ -27,7 +27,7 @@ _PTYPE = {np.dtype(np.uint8): _capi.UINT8, np.dtype(np.int8): _capi.INT8, np.dty
 
 class AdacomError(RuntimeError):
     def __init__(self, status: int, message: str):
-        super().__init__(f"adacom {_capi.STATUS_NAMES[status] if 0 <= status < 7 else status}: {message}")
+        super().__init__(f"adacom {_capi.STATUS_NAMES[status] if 0 <= status < len(_capi.STATUS_NAMES) else status}: {message}")
         self.status = status
 
 
@@ -165,6 +165,23 @@ class Context:
         self.check(self.lib.adacom_column_from_packed(self.h, _PTYPE[dt], len(metas), arr, _np_ptr(words), len(words),
                                                       C.byref(h)))
         return Column(self, h, dt)
+
+    def restore(self, image, dtype=None, device_bytes: int | None = None) -> "Column":
+        """Rebuild a column from a checkpoint image: a numpy uint8 array, or a device pointer (int) of
+        `device_bytes` bytes.  Raises AdacomError(ERR_CORRUPT) when a checksum fails."""
+        h = C.c_void_p()
+        if isinstance(image, np.ndarray):
+            image = np.ascontiguousarray(image, dtype=np.uint8)
+            self.check(self.lib.adacom_column_restore(self.h, _np_ptr(image), image.nbytes, 0, C.byref(h)))
+            ptype = int(image[12:16].view(np.uint32)[0])
+        else:
+            self.check(self.lib.adacom_column_restore(self.h, C.c_void_p(int(image)), int(device_bytes), 1, C.byref(h)))
+            ptype = None
+        if dtype is None:
+            if ptype is None:
+                raise ValueError("dtype is required for a device image")
+            dtype = {v: k for k, v in _PTYPE.items()}[ptype]
+        return Column(self, h, np.dtype(dtype))
 
     def compress_host(self, values: np.ndarray, seg_counts, seg_capacity: int = 0, flags: int = 0,
                       words_out: np.ndarray | None = None):
@@ -324,6 +341,24 @@ class Column:
         buf = (C.c_uint8 * n.value)()
         self.ctx.check(self.lib.adacom_segment_serialize(self.h, seg, buf, n.value, C.byref(n)))
         return bytes(buf)
+
+    def checkpoint_size(self) -> int:
+        n = C.c_uint64()
+        self.ctx.check(self.lib.adacom_column_checkpoint_size(self.h, C.byref(n)))
+        return int(n.value)
+
+    def checkpoint(self, device_out: int | None = None, capacity: int | None = None):
+        """Checkpoint image of the column (include/adacom_gpu.h "checkpoint image"): numpy uint8 array, or written
+        to the device pointer `device_out` (then the byte count is returned)."""
+        n = C.c_uint64()
+        if device_out is not None:
+            self.ctx.check(self.lib.adacom_column_checkpoint(self.h, C.c_void_p(int(device_out)), int(capacity), 1,
+                                                             C.byref(n)))
+            return int(n.value)
+        out = np.empty(self.checkpoint_size(), dtype=np.uint8)
+        self.ctx.check(self.lib.adacom_column_checkpoint(self.h, _np_ptr(out), out.nbytes, 0, C.byref(n)))
+        assert n.value == out.nbytes
+        return out
 
     def decode(self, seg_begin=0, seg_end=None, flags=0, out: np.ndarray | None = None, device_out: int | None = None):
         """Batched decode.  Returns a numpy array unless device_out (a device pointer) is given."""

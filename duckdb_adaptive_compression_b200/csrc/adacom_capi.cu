@@ -11,6 +11,7 @@
 #include <cstring>
 #include <atomic>
 #include <cmath>
+#include <map>
 #include <mutex>
 #include <new>
 #include <string>
@@ -1505,5 +1506,435 @@ extern "C" adacom_status adacom_compress_host(adacom_ctx *ctx, adacom_ptype type
 		}
 	}
 	*col_out = col;
+	return ADACOM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// checkpoint image (persisted form of a column): layout planning on the host (metadata-sized, what
+// ColumnCheckpointState / PartialBlockManager do in the reference), block assembly + checksums on the device
+// ---------------------------------------------------------------------------------------------------
+
+static_assert(sizeof(adacom_image_header) == 64 && sizeof(adacom_data_pointer) == 64, "image records are 64 bytes");
+static_assert(ADACOM_BLOCK_ALLOC_SIZE == kBlockAllocSize && ADACOM_BLOCK_SIZE == kBlockSize, "block geometry");
+
+namespace {
+
+// duckdb::Checksum over whole words (src/common/checksum.cpp:6-25); only used for the few KiB of image metadata
+uint64_t meta_checksum(const adacom_image_header &h, const std::vector<adacom_data_pointer> &ptrs) {
+	adacom_image_header hz = h;
+	hz.meta_checksum = 0;
+	uint64_t r = 5381;
+	const uint64_t *p = (const uint64_t *)&hz;
+	for (size_t i = 0; i < sizeof(hz) / 8; i++) {
+		r ^= p[i] * 0xbf58476d1ce4e5b9ull;
+	}
+	p = (const uint64_t *)ptrs.data();
+	for (size_t i = 0; i < ptrs.size() * sizeof(adacom_data_pointer) / 8; i++) {
+		r ^= p[i] * 0xbf58476d1ce4e5b9ull;
+	}
+	return r;
+}
+
+struct ImagePlan {
+	adacom_image_header header;
+	std::vector<adacom_data_pointer> ptrs;
+	std::vector<CkPiece> pieces;        // grouped by block, increasing offset inside a block
+	std::vector<uint32_t> piece_begin;  // n_blocks + 1
+};
+
+// Block placement of FlushSegment + PartialBlockManager::{GetBlockAllocation, RegisterPartialBlock}
+// (column_checkpoint_state.cpp:107-139, partial_block_manager.cpp:14-77) with the default limits.
+struct BlockPlacer {
+	static constexpr uint32_t kMaxPartial = kBlockSize / 5 * 4;  // DEFAULT_MAX_PARTIAL_BLOCK_SIZE
+	std::multimap<uint32_t, std::pair<int64_t, uint32_t>> partial;  // space left -> (block id, offset in block)
+	int64_t n_blocks = 0;
+	void place(uint32_t segment_size, int64_t &block_id, uint32_t &offset) {
+		bool found = false;
+		if (segment_size <= kMaxPartial) {
+			auto it = partial.lower_bound(segment_size);
+			if (it != partial.end()) {
+				block_id = it->second.first;
+				offset = it->second.second;
+				partial.erase(it);
+				found = true;
+			}
+		}
+		if (!found) {
+			block_id = n_blocks++;
+			offset = 0;
+		}
+		const uint32_t new_size = (segment_size + offset + 7u) & ~7u;  // AlignValue
+		const uint32_t left = kBlockSize - new_size;
+		if (left >= kBlockSize - kMaxPartial) {
+			partial.insert({left, {block_id, new_size}});
+		}
+	}
+};
+
+adacom_status plan_image(adacom_column *col, ImagePlan &plan) {
+	adacom_status st = sync_mirror(col);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	const uint32_t S = (uint32_t)col->t.size;
+	plan.ptrs.assign(col->n_segs, adacom_data_pointer());
+	std::vector<std::vector<CkPiece>> per_block;
+	BlockPlacer placer;
+	for (uint64_t g = 0; g < col->n_segs; g++) {
+		const SegDesc &d = col->h_desc[g];
+		adacom_data_pointer &p = plan.ptrs[g];
+		memset(&p, 0, sizeof(p));
+		const bool repacked = d.state & kSegRepacked;
+		p.row_start = d.row_start;
+		p.tuple_count = d.count;
+		p.block_id = ADACOM_INVALID_BLOCK;
+		p.min_factor = d.min_factor;
+		p.max_factor = d.max_factor;
+		p.capacity = d.capacity;
+		p.compression_type = (d.state & kSegUncompressedFn) ? 1 : 10;
+		p.width = d.width;
+		p.state = d.state;
+		p.type_size = (uint8_t)S;
+		if (d.count == 0) {
+			continue;  // FlushSegment returns before allocating anything (column_checkpoint_state.cpp:94-96)
+		}
+		p.payload_bytes = repacked ? (uint32_t)(8 * (((uint64_t)d.count * d.width + 63) >> 6)) : d.count * S;
+		if (!repacked && !col->raw) {
+			return fail(col->ctx, ADACOM_ERR_STATE, "adacom_column_checkpoint: a slot-width segment has no raw arena");
+		}
+		placer.place(p.payload_bytes, p.block_id, p.offset);
+		CkPiece pc;
+		pc.addr = repacked ? d.packed_ptr : (uint64_t)(col->raw + d.row_start * S);
+		pc.block_off = p.offset;
+		pc.bytes = p.payload_bytes;
+		pc.pad_words = 0;
+		pc.elem_size = repacked ? 8 : S;
+		if ((size_t)p.block_id >= per_block.size()) {
+			per_block.resize(p.block_id + 1);
+		}
+		per_block[p.block_id].push_back(pc);
+	}
+	plan.piece_begin.assign(per_block.size() + 1, 0);
+	plan.pieces.clear();
+	for (size_t b = 0; b < per_block.size(); b++) {
+		plan.piece_begin[b] = (uint32_t)plan.pieces.size();
+		plan.pieces.insert(plan.pieces.end(), per_block[b].begin(), per_block[b].end());
+	}
+	plan.piece_begin[per_block.size()] = (uint32_t)plan.pieces.size();
+	adacom_image_header &h = plan.header;
+	memset(&h, 0, sizeof(h));
+	memcpy(h.magic, ADACOM_IMAGE_MAGIC, 8);
+	h.version = ADACOM_IMAGE_VERSION;
+	h.ptype = (uint32_t)col->ptype;
+	h.n_segments = col->n_segs;
+	h.n_blocks = per_block.size();
+	h.n_values = col->n_values;
+	h.blocks_offset = (sizeof(h) + col->n_segs * sizeof(adacom_data_pointer) + 4095) & ~4095ull;
+	h.total_bytes = h.blocks_offset + h.n_blocks * (uint64_t)kBlockAllocSize;
+	h.meta_checksum = meta_checksum(h, plan.ptrs);
+	return ADACOM_OK;
+}
+
+// pieces + piece_begin in one stream-ordered allocation
+adacom_status upload_pieces(adacom_ctx *ctx, const std::vector<CkPiece> &pieces, const std::vector<uint32_t> &begin,
+                            CkPiece **d_pieces, uint32_t **d_begin) {
+	const size_t pb = (pieces.size() * sizeof(CkPiece) + 15) & ~(size_t)15;
+	uint8_t *buf = nullptr;
+	CK(ctx, cudaMallocAsync((void **)&buf, pb + begin.size() * sizeof(uint32_t) + 16, ctx->stream));
+	if (!pieces.empty()) {
+		CK(ctx, cudaMemcpyAsync(buf, pieces.data(), pieces.size() * sizeof(CkPiece), cudaMemcpyHostToDevice, ctx->stream));
+	}
+	CK(ctx, cudaMemcpyAsync(buf + pb, begin.data(), begin.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+	*d_pieces = (CkPiece *)buf;
+	*d_begin = (uint32_t *)(buf + pb);
+	return ADACOM_OK;
+}
+
+}  // namespace
+
+extern "C" adacom_status adacom_column_checkpoint_size(adacom_column *col, uint64_t *bytes_out) {
+	if (!col || !bytes_out) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_column_checkpoint_size: NULL argument");
+	}
+	std::lock_guard<std::mutex> lock(col->ctx->mu);
+	ImagePlan plan;
+	adacom_status st = plan_image(col, plan);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	*bytes_out = plan.header.total_bytes;
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_column_checkpoint(adacom_column *col, void *out, uint64_t capacity, int out_on_device,
+                                                  uint64_t *bytes_out) {
+	if (!col || !out) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_column_checkpoint: NULL argument");
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	CK(ctx, cudaSetDevice(ctx->device));
+	ImagePlan plan;
+	adacom_status st = plan_image(col, plan);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	const adacom_image_header &h = plan.header;
+	if (capacity < h.total_bytes) {
+		return fail(ctx, ADACOM_ERR_INVALID, "adacom_column_checkpoint: capacity below adacom_column_checkpoint_size");
+	}
+	if (h.n_blocks >= (1ull << 32)) {
+		return fail(ctx, ADACOM_ERR_INVALID, "adacom_column_checkpoint: too many blocks");
+	}
+	// metadata area: header, pointer table, zero padding
+	std::vector<uint8_t> meta(h.blocks_offset, 0);
+	memcpy(meta.data(), &h, sizeof(h));
+	if (!plan.ptrs.empty()) {
+		memcpy(meta.data() + sizeof(h), plan.ptrs.data(), plan.ptrs.size() * sizeof(adacom_data_pointer));
+	}
+	CkPiece *d_pieces = nullptr;
+	uint32_t *d_begin = nullptr;
+	st = upload_pieces(ctx, plan.pieces, plan.piece_begin, &d_pieces, &d_begin);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	const uint64_t block_bytes = h.n_blocks * (uint64_t)kBlockAllocSize;
+	uint8_t *d_blocks = nullptr;
+	if (out_on_device) {
+		if ((uintptr_t)out % 8 != 0) {
+			return fail(ctx, ADACOM_ERR_INVALID, "adacom_column_checkpoint: device image must be 8-byte aligned");
+		}
+		d_blocks = (uint8_t *)out + h.blocks_offset;
+		CK(ctx, cudaMemcpyAsync(out, meta.data(), meta.size(), cudaMemcpyHostToDevice, ctx->stream));
+	} else {
+		memcpy(out, meta.data(), meta.size());
+		CK(ctx, cudaMallocAsync((void **)&d_blocks, block_bytes ? block_bytes : 8, ctx->stream));
+	}
+	LAUNCH(ctx, launch_checkpoint_blocks(d_pieces, d_begin, d_blocks, (uint32_t)h.n_blocks, ctx->sm_count, ctx->stream));
+	if (!out_on_device) {
+		if (block_bytes) {
+			CK(ctx, cudaMemcpyAsync((uint8_t *)out + h.blocks_offset, d_blocks, block_bytes, cudaMemcpyDeviceToHost,
+			                        ctx->stream));
+		}
+		CK(ctx, cudaFreeAsync(d_blocks, ctx->stream));
+	}
+	CK(ctx, cudaFreeAsync(d_pieces, ctx->stream));
+	// the staging vectors above are pageable: the copies were staged before the calls returned; the image itself
+	// must be complete when a host caller reads it
+	CK(ctx, cudaStreamSynchronize(ctx->stream));
+	if (bytes_out) {
+		*bytes_out = h.total_bytes;
+	}
+	return ADACOM_OK;
+}
+
+static adacom_status restore_locked(adacom_ctx *ctx, const void *image, uint64_t bytes, int image_on_device,
+                                    adacom_column **col_io) {
+	CK(ctx, cudaSetDevice(ctx->device));
+	adacom_image_header h;
+	if (bytes < sizeof(h)) {
+		return fail(ctx, ADACOM_ERR_CORRUPT, "adacom_column_restore: image shorter than its header");
+	}
+	if (image_on_device) {
+		CK(ctx, cudaMemcpyAsync(&h, image, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+		CK(ctx, cudaStreamSynchronize(ctx->stream));
+	} else {
+		memcpy(&h, image, sizeof(h));
+	}
+	TypeInfo t;
+	if (memcmp(h.magic, ADACOM_IMAGE_MAGIC, 8) != 0 || h.version != ADACOM_IMAGE_VERSION) {
+		return fail(ctx, ADACOM_ERR_CORRUPT, "adacom_column_restore: bad magic / version");
+	}
+	if (!type_info((adacom_ptype)h.ptype, t)) {
+		return fail(ctx, ADACOM_ERR_CORRUPT, "adacom_column_restore: unknown physical type");
+	}
+	if (h.n_segments >= (1ull << 32) || h.n_blocks >= (1ull << 32) ||
+	    h.blocks_offset != ((sizeof(h) + h.n_segments * sizeof(adacom_data_pointer) + 4095) & ~4095ull) ||
+	    h.total_bytes != h.blocks_offset + h.n_blocks * (uint64_t)kBlockAllocSize || h.total_bytes > bytes) {
+		return fail(ctx, ADACOM_ERR_CORRUPT, "adacom_column_restore: inconsistent header / truncated image");
+	}
+	std::vector<adacom_data_pointer> ptrs(h.n_segments);
+	if (h.n_segments) {
+		const uint8_t *src = (const uint8_t *)image + sizeof(h);
+		if (image_on_device) {
+			CK(ctx, cudaMemcpyAsync(ptrs.data(), src, ptrs.size() * sizeof(adacom_data_pointer), cudaMemcpyDeviceToHost,
+			                        ctx->stream));
+			CK(ctx, cudaStreamSynchronize(ctx->stream));
+		} else {
+			memcpy(ptrs.data(), src, ptrs.size() * sizeof(adacom_data_pointer));
+		}
+	}
+	if (meta_checksum(h, ptrs) != h.meta_checksum) {
+		return fail(ctx, ADACOM_ERR_CORRUPT, "adacom_column_restore: metadata checksum mismatch");
+	}
+	// validate the pointers, lay out the packed extent
+	const uint32_t S = (uint32_t)t.size;
+	uint64_t row = 0, words = 0;
+	bool any_raw = false;
+	for (uint64_t g = 0; g < h.n_segments; g++) {
+		const adacom_data_pointer &p = ptrs[g];
+		const bool repacked = p.state & kSegRepacked;
+		const uint64_t expect = repacked ? 8 * ((p.tuple_count * p.width + 63) >> 6) : p.tuple_count * S;
+		bool ok = p.row_start == row && p.type_size == S && p.width >= 1 && p.width <= 64 &&
+		          (uint64_t)p.capacity * S <= kBlockSize && p.tuple_count <= p.capacity && p.payload_bytes == expect &&
+		          (repacked ? p.width < 8 * S : p.width == 8 * S);
+		if (p.tuple_count == 0) {
+			ok = ok && p.block_id == ADACOM_INVALID_BLOCK;
+		} else {
+			ok = ok && p.block_id >= 0 && (uint64_t)p.block_id < h.n_blocks && p.offset % 8 == 0 &&
+			     (uint64_t)p.offset + p.payload_bytes <= kBlockSize;
+		}
+		if (!ok) {
+			return fail(ctx, ADACOM_ERR_CORRUPT, "adacom_column_restore: bad data pointer " + std::to_string(g));
+		}
+		row += p.tuple_count;
+		if (repacked) {
+			words += ((p.payload_bytes / 8 + kSegAlignWords - 1) / kSegAlignWords) * kSegAlignWords;
+		} else if (p.tuple_count) {
+			any_raw = true;
+		}
+	}
+	if (row != h.n_values) {
+		return fail(ctx, ADACOM_ERR_CORRUPT, "adacom_column_restore: row count mismatch");
+	}
+	adacom_column *col = nullptr;
+	adacom_status st = column_alloc(ctx, (adacom_ptype)h.ptype, h.n_segments, &col);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	*col_io = col;
+	col->n_values = row;
+	Extent ext;
+	ext.words = words;
+	ext.capacity = words;
+	ext.seg_end = h.n_segments;
+	CK(ctx, cudaMallocAsync((void **)&ext.base, words * 8 + kArenaPad, ctx->stream));
+	col->extents.push_back(ext);
+	CK(ctx, cudaMallocAsync((void **)&col->d_desc, std::max<uint64_t>(h.n_segments, 1) * sizeof(SegDesc), ctx->stream));
+	if (any_raw) {
+		st = ensure_raw(col);
+		if (st != ADACOM_OK) {
+			return st;
+		}
+	}
+	std::vector<std::vector<CkPiece>> per_block(h.n_blocks);
+	uint64_t woff = 0;
+	for (uint64_t g = 0; g < h.n_segments; g++) {
+		const adacom_data_pointer &p = ptrs[g];
+		SegDesc &d = col->h_desc[g];
+		memset(&d, 0, sizeof(d));
+		const bool repacked = p.state & kSegRepacked;
+		d.row_start = p.row_start;
+		d.min_factor = p.min_factor;
+		d.max_factor = p.max_factor;
+		d.count = (uint32_t)p.tuple_count;
+		d.capacity = p.capacity;
+		d.width = p.width;
+		d.state = p.state;
+		CkPiece pc;
+		pc.block_off = p.offset;
+		pc.bytes = p.payload_bytes;
+		if (repacked) {
+			const uint64_t padded = ((p.payload_bytes / 8 + kSegAlignWords - 1) / kSegAlignWords) * kSegAlignWords;
+			d.word_offset = woff;
+			d.packed_ptr = (uint64_t)(ext.base + woff);
+			pc.addr = d.packed_ptr;
+			pc.pad_words = (uint32_t)padded;
+			pc.elem_size = 8;
+			woff += padded;
+			col->extents[0].live++;
+		} else {
+			pc.addr = (uint64_t)(col->raw + p.row_start * S);
+			pc.pad_words = 0;
+			pc.elem_size = S;
+		}
+		if (p.tuple_count) {
+			per_block[p.block_id].push_back(pc);
+		}
+	}
+	std::vector<CkPiece> pieces;
+	std::vector<uint32_t> begin(h.n_blocks + 1, 0);
+	for (uint64_t b = 0; b < h.n_blocks; b++) {
+		begin[b] = (uint32_t)pieces.size();
+		std::sort(per_block[b].begin(), per_block[b].end(),
+		          [](const CkPiece &a, const CkPiece &c) { return a.block_off < c.block_off; });
+		uint32_t end = 0;
+		for (const CkPiece &pc : per_block[b]) {
+			if (pc.block_off < end) {
+				return fail(ctx, ADACOM_ERR_CORRUPT, "adacom_column_restore: overlapping payloads in block " + std::to_string(b));
+			}
+			end = pc.block_off + ((pc.bytes + 7u) & ~7u);
+		}
+		pieces.insert(pieces.end(), per_block[b].begin(), per_block[b].end());
+	}
+	begin[h.n_blocks] = (uint32_t)pieces.size();
+	if (h.n_segments) {
+		CK(ctx, cudaMemcpyAsync(col->d_desc, col->h_desc.data(), h.n_segments * sizeof(SegDesc), cudaMemcpyHostToDevice,
+		                        ctx->stream));
+	}
+	st = build_tiles(col);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	CkPiece *d_pieces = nullptr;
+	uint32_t *d_begin = nullptr;
+	st = upload_pieces(ctx, pieces, begin, &d_pieces, &d_begin);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	const uint64_t block_bytes = h.n_blocks * (uint64_t)kBlockAllocSize;
+	const uint8_t *d_blocks = (const uint8_t *)image + h.blocks_offset;
+	uint8_t *temp = nullptr;
+	if (!image_on_device) {
+		CK(ctx, cudaMallocAsync((void **)&temp, block_bytes ? block_bytes : 8, ctx->stream));
+		if (block_bytes) {
+			CK(ctx, cudaMemcpyAsync(temp, d_blocks, block_bytes, cudaMemcpyHostToDevice, ctx->stream));
+		}
+		d_blocks = temp;
+	} else if ((uintptr_t)image % 8 != 0) {
+		return fail(ctx, ADACOM_ERR_INVALID, "adacom_column_restore: device image must be 8-byte aligned");
+	}
+	// verdict word: host-mapped totals slot 2 would race with an encode's ticket spin on other columns; use the
+	// context's aggregate scratch instead (device) and copy it back
+	unsigned long long *d_bad = (unsigned long long *)ctx->d_agg;
+	CK(ctx, cudaMemsetAsync(d_bad, 0xff, sizeof(unsigned long long), ctx->stream));
+	LAUNCH(ctx, launch_restore_blocks(d_pieces, d_begin, d_blocks, (uint32_t)h.n_blocks, d_bad, ctx->sm_count, ctx->stream));
+	unsigned long long bad = 0;
+	CK(ctx, cudaMemcpyAsync(&bad, d_bad, sizeof(bad), cudaMemcpyDeviceToHost, ctx->stream));
+	if (temp) {
+		CK(ctx, cudaFreeAsync(temp, ctx->stream));
+	}
+	CK(ctx, cudaFreeAsync(d_pieces, ctx->stream));
+	CK(ctx, cudaStreamSynchronize(ctx->stream));
+	if (bad != ~0ull) {
+		return fail(ctx, ADACOM_ERR_CORRUPT,
+		            "adacom_column_restore: computed checksum does not match stored checksum in block " +
+		                std::to_string(bad));
+	}
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_column_restore(adacom_ctx *ctx, const void *image, uint64_t bytes, int image_on_device,
+                                               adacom_column **out) {
+	if (!ctx || !image || !out) {
+		return fail(ctx, ADACOM_ERR_INVALID, "adacom_column_restore: NULL argument");
+	}
+	*out = nullptr;
+	adacom_column *col = nullptr;
+	adacom_status st;
+	std::string err;
+	{
+		std::lock_guard<std::mutex> lock(ctx->mu);
+		st = restore_locked(ctx, image, bytes, image_on_device, &col);
+		err = ctx->err;
+	}
+	if (st != ADACOM_OK) {
+		if (col) {
+			adacom_column_destroy(col);
+			ctx->err = err;
+		}
+		return st;
+	}
+	*out = col;
 	return ADACOM_OK;
 }

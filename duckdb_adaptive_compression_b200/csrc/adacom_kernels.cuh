@@ -142,4 +142,26 @@ cudaError_t launch_encode(TypeInfo t, const SegDesc *desc, const Job *tiles, uin
 cudaError_t launch_fill_splitmix(TypeInfo t, void *raw, uint64_t n, uint64_t seed, uint64_t first_index, uint64_t mask,
                                  cudaStream_t stream);
 
+// ---- checkpoint image (kernels_checkpoint.cu) ----
+constexpr uint32_t kBlockAllocSize = 262144;  // Storage::BLOCK_ALLOC_SIZE: 8-byte checksum + Storage::BLOCK_SIZE payload
+
+// One payload inside one block.  checkpoint: addr = source (device address of the packed words / the slot-width
+// values, only sizeof(T)-aligned for the latter); restore: addr = destination.
+struct CkPiece {
+	uint64_t addr;
+	uint32_t block_off;  // byte offset inside the block payload (multiple of 8)
+	uint32_t bytes;      // payload bytes (8 * words, or count * sizeof(T))
+	uint32_t pad_words;  // restore into the packed extent: words up to the next 128-byte boundary (zero filled)
+	uint32_t elem_size;  // sizeof(T) for slot-width payloads, 8 for packed words
+};
+static_assert(sizeof(CkPiece) == 24, "CkPiece layout");
+
+// payloads -> 256 KiB block images with DuckDB block checksums; pieces of block b = [piece_begin[b], piece_begin[b+1])
+cudaError_t launch_checkpoint_blocks(const CkPiece *pieces, const uint32_t *piece_begin, uint8_t *blocks,
+                                     uint32_t n_blocks, int sm_count, cudaStream_t stream);
+// block images -> payloads, every block checksum verified in the same pass (*bad_block = lowest failing block id,
+// initialised to ~0 by the caller)
+cudaError_t launch_restore_blocks(const CkPiece *pieces, const uint32_t *piece_begin, const uint8_t *blocks,
+                                  uint32_t n_blocks, unsigned long long *bad_block, int sm_count, cudaStream_t stream);
+
 }  // namespace adacom

@@ -47,7 +47,9 @@ typedef enum {
 	ADACOM_ERR_NOMEM = 3,       /* device or pinned-host allocation failed (reference: std::bad_alloc) */
 	ADACOM_ERR_UNSUPPORTED = 4, /* physical type not supported by SuccinctFun::TypeIsSupported */
 	ADACOM_ERR_STATE = 5,       /* call not valid in the column's current state */
-	ADACOM_ERR_NO_DEVICE = 6    /* no CUDA device / not an sm_100 part */
+	ADACOM_ERR_NO_DEVICE = 6,   /* no CUDA device / not an sm_100 part */
+	ADACOM_ERR_CORRUPT = 7      /* checkpoint image fails its checksums (reference: IOException "Corrupt database
+	                               file", src/common/file_buffer.cpp:95-106) or is malformed */
 } adacom_status;
 
 /* duckdb::PhysicalType values of the supported types (src/include/duckdb/common/types.hpp) */
@@ -264,6 +266,70 @@ adacom_status adacom_scan_columns_grouped(adacom_ctx *ctx, const adacom_scan_ter
  * on_device (then all three are device pointers). */
 adacom_status adacom_fetch_rows(adacom_column *col, uint64_t n, const uint32_t *seg_idx, const uint32_t *row_in_seg,
                                 int flags, void *out, int on_device);
+
+/* ---- checkpoint image (persisted form of a column) ------------------------------------ */
+/* The reference cannot checkpoint succinct segments (column_segment.cpp:529-533; init_compression / compress /
+ * compress_finalize are stubs, succinct.cpp:86-119).  This gives those slots a real layout, the one DuckDB uses for
+ * every other codec: ColumnCheckpointState::FlushSegment (src/storage/table/column_checkpoint_state.cpp:91-163) puts
+ * each segment payload into a 256 KiB block, small payloads share blocks under the PartialBlockManager policy
+ * (src/storage/partial_block_manager.cpp:14-77: payloads <= 80 % of a block go to the partially filled block with the
+ * least sufficient space left, offsets 8-byte aligned), every block carries Checksum(payload)
+ * (src/common/checksum.cpp:6-25) in its first 8 bytes (FileBuffer::ChecksumAndWrite, file_buffer.cpp:113-119), and a
+ * DataPointer per segment (src/include/duckdb/storage/data_pointer.hpp:20-27) records {row_start, tuple_count,
+ * block_id, offset, compression_type} -- extended here by the ColumnSegment members the succinct scan needs
+ * (width, min_factor, max_factor, compacted/repacked).  The payload of a segment is its int_vector data words (the
+ * 9-byte serialize header is recomputable from tuple_count and width) or, for a segment that was not re-packed, its
+ * tuple_count slot-width values.
+ *
+ * image = adacom_image_header | n_segments x adacom_data_pointer | zero padding to blocks_offset |
+ *         n_blocks x { uint64 checksum, 262136 payload bytes }          (all little endian)
+ * The blocks are assembled and checksummed on the GPU in one pass (checkpoint_blocks_kernel); restore verifies every
+ * checksum while it scatters the payloads back into HBM (restore_blocks_kernel). */
+#define ADACOM_IMAGE_MAGIC "ADACOMCK"
+#define ADACOM_IMAGE_VERSION 1u
+#define ADACOM_BLOCK_ALLOC_SIZE 262144u /* Storage::BLOCK_ALLOC_SIZE (constants.hpp:101-106) */
+#define ADACOM_BLOCK_SIZE 262136u       /* Storage::BLOCK_SIZE = BLOCK_ALLOC_SIZE - BLOCK_HEADER_SIZE */
+#define ADACOM_INVALID_BLOCK (-1)       /* INVALID_BLOCK: empty segment, nothing written */
+
+typedef struct {
+	char magic[8];            /* ADACOM_IMAGE_MAGIC */
+	uint32_t version;
+	uint32_t ptype;           /* adacom_ptype */
+	uint64_t n_segments;
+	uint64_t n_blocks;
+	uint64_t n_values;
+	uint64_t blocks_offset;   /* byte offset of block 0 (multiple of 4096) */
+	uint64_t total_bytes;     /* blocks_offset + n_blocks * ADACOM_BLOCK_ALLOC_SIZE */
+	uint64_t meta_checksum;   /* Checksum() over the header with this field zero, then the pointer table */
+} adacom_image_header;        /* 64 bytes */
+
+typedef struct {
+	uint64_t row_start;       /* DataPointer::row_start */
+	uint64_t tuple_count;     /* DataPointer::tuple_count */
+	int64_t block_id;         /* BlockPointer::block_id, ADACOM_INVALID_BLOCK when tuple_count == 0 */
+	uint32_t offset;          /* BlockPointer::offset inside the block payload (multiple of 8) */
+	uint32_t payload_bytes;   /* 8 * ceil(count * width / 64) when re-packed, else count * type_size */
+	uint64_t min_factor;
+	uint64_t max_factor;
+	uint32_t capacity;
+	uint8_t compression_type; /* CompressionType: 10 = COMPRESSION_SUCCINCT, 1 = COMPRESSION_UNCOMPRESSED */
+	uint8_t width;
+	uint8_t state;            /* ADACOM_SEG_* */
+	uint8_t type_size;
+	uint64_t reserved;
+} adacom_data_pointer;        /* 64 bytes */
+
+/* size of the image the column would be checkpointed to right now */
+adacom_status adacom_column_checkpoint_size(adacom_column *col, uint64_t *bytes_out);
+/* write the image to `out` (host pointer, or device pointer when out_on_device; capacity in bytes);
+ * ADACOM_ERR_INVALID when capacity is too small.  The column is unchanged. */
+adacom_status adacom_column_checkpoint(adacom_column *col, void *out, uint64_t capacity, int out_on_device,
+                                       uint64_t *bytes_out);
+/* rebuild a column from an image (host or device pointer): every block checksum and the metadata checksum are
+ * verified, ADACOM_ERR_CORRUPT otherwise.  Re-packed payloads land in one packed extent, slot-width payloads in the raw
+ * arena; the column answers scans exactly like the one that was checkpointed. */
+adacom_status adacom_column_restore(adacom_ctx *ctx, const void *image, uint64_t bytes, int image_on_device,
+                                    adacom_column **out);
 
 /* ---- host-buffer convenience paths (what bench.py's e2e leg times) ------------------------------------ */
 /* host T values -> analyze + encode on the GPU -> metas (+ packed words when host_words_out != NULL,
