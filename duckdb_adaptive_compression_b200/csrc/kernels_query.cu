@@ -505,10 +505,10 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 				uint32_t off_p = 0;
 #pragma unroll 1
 				for (int p = 0; p < kQueryMaxPieces; p++) {
-					const QPiece q = st.piece[c][p];
-					if (q.cnt == 0) {
+					if (st.piece[c][p].cnt == 0) {
 						continue;
 					}
+					const QPiece q = st.piece[c][p];
 					const uint32_t end_p = off_p + q.cnt;
 					const uint8_t *pbase = stage + q.smem_off;
 					const uint64_t mask64 = lo_set64(q.w);
@@ -523,16 +523,20 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 						const uint32_t mask = (uint32_t)mask64, flo = (uint32_t)q.flo, span = (uint32_t)q.span;
 						const uint32_t step = 32u * kQConsumerWarps * q.w;            // bits between two of my groups
 						uint32_t bit = q.bit_base + (g * 32u + lane - off_p) * q.w;   // wraps for lanes before off_p: unused
+						// step is 8*w whole 32-bit words: a lane's funnel shift amount is the same in every group of the
+						// piece, and the four loads of a round sit at fixed word strides from one pointer
+						const uint32_t sh = bit & 31u;
+						const uint32_t wstride = (uint32_t)kQConsumerWarps * q.w;     // 32-bit words between two of my groups
+						uint32_t *my_sel = sel + lane * kQConsumerWarps;               // lanes 0..3 publish the four ballots
 						for (; g * 32u < end_p; g += 4u * kQConsumerWarps, bit += 4u * step) {
 							const bool interior = g * 32u >= off_p && (g + 3u * kQConsumerWarps) * 32u + 32u <= end_p;
 							if (interior) {
 								// branch-free round: every lane of the four groups lies inside the piece
+								const uint32_t *p32 = (const uint32_t *)pbase + (bit >> 5);
 								uint32_t f[4];
 #pragma unroll
 								for (int u = 0; u < 4; u++) {
-									const uint32_t bu = bit + u * step;
-									const uint32_t *p32 = (const uint32_t *)(pbase + ((bu >> 3) & ~3u));
-									f[u] = __funnelshift_r(p32[0], p32[1], bu) & mask;
+									f[u] = __funnelshift_r(p32[u * wstride], p32[u * wstride + 1], sh) & mask;
 								}
 								uint32_t mine = 0;
 #pragma unroll
@@ -541,7 +545,7 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 									mine = (int)lane == u ? keep : mine;
 								}
 								if (lane < 4) {
-									sel[g + lane * kQConsumerWarps] &= mine;
+									my_sel[g] &= mine;
 								}
 							} else {
 #pragma unroll 1
@@ -599,7 +603,42 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 
 			// ---- survivors: bitmap out, count, compaction into the warp's list, aggregates on the list ----
 			uint32_t n_list = 0;
-			for (uint32_t g = warp; g < n_groups; g += kQConsumerWarps) {
+			// sparse selections (Q6 keeps ~2 % of the rows): lane j owns my j-th group (8192 rows = 32 groups per warp),
+			// an exclusive scan of the survivor counts places every lane's rows, each lane then emits its own set bits.
+			// Same list order as the group-at-a-time loop below, which remains for dense selections.
+			uint32_t g_first = warp;
+			{
+				const uint32_t g = warp + lane * kQConsumerWarps;
+				const uint32_t word = g < n_groups ? sel[g] : 0u;
+				const uint32_t cnt = __popc(word);
+				uint32_t incl = cnt;
+#pragma unroll
+				for (int d = 1; d < 32; d <<= 1) {
+					const uint32_t v = __shfl_up_sync(0xffffffffu, incl, d);
+					if ((int)lane >= d) {
+						incl += v;
+					}
+				}
+				const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+				if (total <= kQListCap) {
+					if (a.out_bitmap != nullptr && g < n_groups) {
+						a.out_bitmap[word0 + g] = word;
+					}
+					uint32_t pos = incl - cnt;
+					uint32_t rest = word;
+					while (rest) {
+						const uint32_t bpos = (uint32_t)__ffs((int)rest) - 1u;
+						my_list[pos++] = (uint16_t)(g * 32u + bpos);
+						rest &= rest - 1u;
+					}
+					if (lane == 0) {
+						n_pass += total;
+					}
+					n_list = total;
+					g_first = n_groups;  // the loop below has nothing left to do
+				}
+			}
+			for (uint32_t g = g_first; g < n_groups; g += kQConsumerWarps) {
 				const uint32_t word = sel[g];
 				if (a.out_bitmap != nullptr && lane == 0) {
 					a.out_bitmap[word0 + g] = word;
