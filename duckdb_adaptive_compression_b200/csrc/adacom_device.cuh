@@ -194,6 +194,28 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
 	} while (!done);
 }
 
+// The same wait for a warp that may have to wait long (a producer far ahead of slow consumers): a spinning warp is
+// always eligible and takes issue slots from the warps it is waiting for, so retries back off with nanosleep.
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t *bar, uint32_t parity, uint32_t ns) {
+	uint32_t addr = smem_addr(bar);
+	uint32_t done;
+	for (;;) {
+		asm volatile(
+		    "{\n"
+		    ".reg .pred p;\n"
+		    "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+		    "selp.u32 %0, 1, 0, p;\n"
+		    "}\n"
+		    : "=r"(done)
+		    : "r"(addr), "r"(parity)
+		    : "memory");
+		if (done) {
+			break;
+		}
+		__nanosleep(ns);
+	}
+}
+
 // shared -> global bulk copy (TMA store): dst/src 16-byte aligned, bytes % 16 == 0; completion via bulk groups
 __device__ __forceinline__ void tma_store_1d(void *gmem_dst, const void *smem_src, uint32_t bytes) {
 	asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem_dst), "r"(smem_addr(smem_src)),

@@ -433,7 +433,7 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 			const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
 			const uint32_t s = seq % n_stages;
 			if (lane == 0) {
-				mbar_wait(&empty_bar[s], ((seq / n_stages) & 1u) ^ 1u);
+				mbar_wait_backoff(&empty_bar[s], ((seq / n_stages) & 1u) ^ 1u, 200);
 				stages[s].row0 = r0;
 				stages[s].rows = rows;
 				stages[s].done = 0;
@@ -465,7 +465,7 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 		}
 		if (lane == 0) {
 			const uint32_t s = seq % n_stages;
-			mbar_wait(&empty_bar[s], ((seq / n_stages) & 1u) ^ 1u);
+			mbar_wait_backoff(&empty_bar[s], ((seq / n_stages) & 1u) ^ 1u, 200);
 			stages[s].done = 1;
 			mbar_arrive(&full_bar[s]);
 		}
@@ -474,7 +474,7 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 		uint16_t *my_list = list[warp];
 		for (uint32_t it = 0;; it++) {
 			const uint32_t s = it % n_stages;
-			mbar_wait(&full_bar[s], (it / n_stages) & 1u);
+			mbar_wait_backoff(&full_bar[s], (it / n_stages) & 1u, 64);
 			const QStage &st = stages[s];
 			if (st.done) {
 				break;
