@@ -1242,6 +1242,7 @@ static adacom_status plan_scan_columns(adacom_ctx *ctx, const adacom_scan_term *
 	}
 	// 64-bit products: bound |value| per term from the analyzed min / max of the scanned segments (type range when a
 	// segment was never analyzed or mixes signs), then every prod_k (|add| + |mul| * bound) against 2^62
+	long double max_prod = ldexpl(1.0L, 70);
 	{
 		long double bound[kQueryMaxCols];
 		for (uint32_t c = 0; c < n_terms; c++) {
@@ -1277,6 +1278,14 @@ static adacom_status plan_scan_columns(adacom_ctx *ctx, const adacom_scan_term *
 			narrow = prod < ldexpl(1.0L, 62);
 		}
 		q.narrow_products = narrow ? 1u : 0u;
+		max_prod = 0;
+		for (uint32_t g = 0; g < n_sums; g++) {
+			long double prod = 1;
+			for (uint32_t k = 0; k < sums[g].n_factors; k++) {
+				prod *= fabsl((long double)sums[g].add[k]) + fabsl((long double)sums[g].mul[k]) * bound[sums[g].term[k]];
+			}
+			max_prod = fmaxl(max_prod, prod);
+		}
 	}
 	// row-block size and pipeline depth: the largest block whose worst-case staged bytes leave room for two
 	// CTAs per SM (shrunk while the table offers fewer than ~4 blocks per SM)
@@ -1285,17 +1294,36 @@ static adacom_status plan_scan_columns(adacom_ctx *ctx, const adacom_scan_term *
 		return ((uint64_t)R * width_bits / 8 + (uint64_t)n_terms * kQueryMaxPieces * 32 + 64 + 127) & ~127ull;
 	};
 	uint32_t R = 0, stages = 0;
+	// GROUP BY with per-thread int64 accumulators in shared memory (dense selections skip the survivor lists): allowed
+	// when no thread's partial sum can leave int64 -- a thread adds one row per 32-row group of its warp, R / 256 rows
+	// per block, over at most ceil(blocks / SMs) blocks -- and the accumulators fit beside two stages (two CTAs per SM:
+	// 228 KiB - 2 x (1 KiB reserved + ~26 KiB static) leaves 87 KiB of dynamic shared memory each)
+	q.dense_groups = 0;
+	if (n_groups && q.narrow_products) {
+		const uint32_t dense_smem = scan_columns_group_smem(n_groups, n_sums, 1);
+		for (uint32_t r : {4096u, 2048u}) {
+			const uint64_t blocks = (n_rows + r - 1) / r;
+			const uint64_t ctas = std::min<uint64_t>(std::max<uint64_t>(blocks, 1), (uint64_t)ctx->sm_count);
+			const long double rows_per_thread = (long double)((blocks + ctas - 1) / ctas) * (r / 256u);
+			if (!R && 2 * stage_bytes(r) + dense_smem <= 87u * 1024u && max_prod * rows_per_thread < ldexpl(1.0L, 62)) {
+				R = r;
+				stages = 2;
+				q.dense_groups = 1;
+			}
+		}
+	}
+	const uint32_t group_smem = n_groups ? scan_columns_group_smem(n_groups, n_sums, 0) : 0u;
 	for (uint32_t r : {8192u, 4096u, 2048u}) {
 		for (uint32_t st : {3u, 2u}) {
 			// + ~26 KiB static (+ the GROUP BY scratch): three CTAs per SM
-			if (!R && st * stage_bytes(r) + (n_groups ? scan_columns_group_smem() : 0u) <= 48u * 1024u) {
+			if (!R && st * stage_bytes(r) + group_smem <= 48u * 1024u) {
 				R = r;
 				stages = st;
 			}
 		}
 	}
 	for (uint32_t limit : {84u * 1024u, 196u * 1024u}) {  // two CTAs per SM, then one
-		if (!R && 2 * stage_bytes(2048) + (n_groups ? scan_columns_group_smem() : 0u) <= limit) {
+		if (!R && 2 * stage_bytes(2048) + group_smem <= limit) {
 			R = 2048;
 			stages = 2;
 		}

@@ -97,6 +97,8 @@ struct QueryArgs {
 	uint32_t narrow_products = 0;         // every prod_k (add + mul * value) provably fits int64: 64-bit products
 	uint32_t group_col = 0;               // GROUP BY: column whose decoded value (0 .. n_groups-1) is the group key
 	uint32_t n_groups = 0;                // 0: no grouping; rows whose key is outside the range are dropped
+	uint32_t dense_groups = 0;            // grouped launches: per-thread int64 accumulators in shared memory are safe
+	                                      // (every partial sum provably fits) -> dense selections skip the lists
 	const uint32_t *in_bitmap = nullptr;  // optional selection (bit r - row_begin), AND-ed
 	uint32_t *out_bitmap = nullptr;       // optional: the resulting selection
 	Agg *out = nullptr;                   // n_aggs (x n_groups, group-major) aggregates, zeroed by the caller;
@@ -104,7 +106,8 @@ struct QueryArgs {
 };
 
 cudaError_t launch_scan_columns(const QueryArgs &args, int sm_count, cudaStream_t stream);
-uint32_t scan_columns_group_smem();  // extra dynamic shared memory of a grouped launch (bytes)
+// extra dynamic shared memory of a grouped launch (bytes); dense: + the per-thread accumulators
+uint32_t scan_columns_group_smem(uint32_t n_groups, uint32_t n_aggs, uint32_t dense);
 
 // scan_vector / scan_partial of one segment, arbitrary start (generic unaligned path, no staging)
 cudaError_t launch_scan_range(TypeInfo t, const SegDesc *desc, uint32_t seg, const uint8_t *raw, uint64_t start,

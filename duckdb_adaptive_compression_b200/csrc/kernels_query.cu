@@ -84,6 +84,33 @@ __device__ __forceinline__ uint64_t column_value(const QPiece *pc, const uint8_t
 	return extend_rt(f + q.min_add, type_size, is_signed);
 }
 
+// the same for a row of the 32-row group starting at block row g32, when the whole group lies inside one piece (the
+// piece search and the piece record are then warp-uniform); groups that straddle a piece boundary take column_value
+__device__ __forceinline__ uint64_t group_value(const QPiece *pc, const uint8_t *stage, uint32_t g32, uint32_t i,
+                                                uint32_t type_size, uint32_t is_signed) {
+	uint32_t p = 0, start = 0;
+	const uint32_t c0 = pc[0].cnt;
+	if (g32 >= c0) {
+		p = 1;
+		start = c0;
+		const uint32_t c1 = pc[1].cnt;
+		if (g32 - c0 >= c1) {
+			p = 2;
+			start = c0 + c1;
+		}
+	}
+	if (g32 + 31u - start >= pc[p].cnt) {
+		return column_value(pc, stage, i, type_size, is_signed);
+	}
+	const uint32_t w = pc[p].w;
+	const uint32_t bit = pc[p].bit_base + (i - start) * w;
+	const uint8_t *base = stage + pc[p].smem_off;
+	const uint64_t mask = lo_set64(w);
+	const uint64_t f = w <= 32u ? (uint64_t)(read_bits32((const uint32_t *)base, bit) & (uint32_t)mask)
+	                            : (read_bits64((const uint64_t *)base, bit) & mask);
+	return extend_rt(f + pc[p].min_add, type_size, is_signed);
+}
+
 struct PieceRes {
 	uint64_t src16;
 	uint64_t min_add;
@@ -367,10 +394,22 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 	// GROUP BY scratch lives behind the stages in dynamic shared memory (only allocated for grouped launches)
 	GroupScratch &gs = *(GroupScratch *)(q_stage_mem + (size_t)n_stages * a.stage_bytes);
 	GroupAcc &gacc = gs.acc;
+	// dense grouped launches: int64 accumulator per (group, aggregate, consumer thread) + a row counter per (group,
+	// thread) behind the scratch: a row costs one shared read-modify-write per aggregate, no list, no reduction
+	long long *dacc = (long long *)(q_stage_mem + (size_t)n_stages * a.stage_bytes + ((sizeof(GroupScratch) + 127u) & ~127u));
+	uint32_t *dcnt = (uint32_t *)(dacc + (size_t)a.n_groups * a.n_aggs * kQConsumers);
 	if (a.n_groups) {
 		unsigned long long *z = (unsigned long long *)&gacc;
 		for (uint32_t i = tid; i < sizeof(GroupAcc) / 8; i += kQThreads) {
 			z[i] = 0ull;
+		}
+		if (a.dense_groups) {
+			for (uint32_t i = tid; i < a.n_groups * a.n_aggs * kQConsumers; i += kQThreads) {
+				dacc[i] = 0ll;
+			}
+			for (uint32_t i = tid; i < a.n_groups * kQConsumers; i += kQThreads) {
+				dcnt[i] = 0u;
+			}
 		}
 	}
 	__syncthreads();
@@ -620,7 +659,47 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 					}
 				}
 				const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
-				if (total <= kQListCap) {
+				const uint32_t my_groups = n_groups > warp ? (n_groups - warp + kQConsumerWarps - 1u) / kQConsumerWarps : 0u;
+				if (a.dense_groups && total * 4u >= my_groups * 32u) {
+					// dense selection of a grouped scan: group at a time, lane = row, values straight into the thread's
+					// shared accumulators of the row's group
+					for (uint32_t gd = warp; gd < n_groups; gd += kQConsumerWarps) {
+						const uint32_t wd = sel[gd];
+						if (a.out_bitmap != nullptr && lane == 0) {
+							a.out_bitmap[word0 + gd] = wd;
+						}
+						if (wd == 0) {
+							continue;
+						}
+						const bool on = (wd >> lane) & 1u;
+						const uint32_t i = gd * 32u + (on ? lane : (uint32_t)__ffs((int)wd) - 1u);  // idle lanes shadow a live row
+#pragma unroll 1
+						for (uint32_t c = 0; c < a.n_cols; c++) {
+							if (((a.factor_mask >> c) & 1u) || c == a.group_col) {
+								const QueryCol &qc = a.cols[c];
+								vals[c][tid] = group_value(st.piece[c], stage, gd * 32u, i, qc.type_size, qc.is_signed);
+							}
+						}
+						const uint64_t kv = vals[a.group_col][tid];
+						if (on && kv < (uint64_t)a.n_groups) {
+							long long *slot = dacc + (size_t)kv * a.n_aggs * kQConsumers + tid;
+#pragma unroll 1
+							for (uint32_t k = 0; k < a.n_aggs; k++) {
+								const QueryAgg &qa = a.aggs[k];
+								long long term = 1;
+#pragma unroll
+								for (int f = 0; f < kQueryMaxFactors; f++) {
+									if (f < (int)qa.n_factors) {
+										term *= qa.add[f] + qa.mul[f] * (long long)vals[qa.col[f]][tid];
+									}
+								}
+								slot[(size_t)k * kQConsumers] += term;
+							}
+							dcnt[(uint32_t)kv * kQConsumers + tid] += 1u;
+						}
+					}
+					g_first = n_groups;
+				} else if (total <= kQListCap) {
 					if (a.out_bitmap != nullptr && g < n_groups) {
 						a.out_bitmap[word0 + g] = word;
 					}
@@ -678,8 +757,41 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 		}
 	}
 	if (a.n_groups) {
-		// one thread per (group, aggregate): add up the 8 warp rows, one atomic triple per CTA
 		__syncthreads();
+		if (a.dense_groups && warp < (uint32_t)kQConsumerWarps) {
+			// fold the per-thread accumulators: a warp per (group, aggregate) slot, into row 0 of the warp accumulators
+			for (uint32_t sidx = warp; sidx < a.n_groups * a.n_aggs; sidx += kQConsumerWarps) {
+				const uint32_t g = sidx / a.n_aggs, k = sidx % a.n_aggs;
+				uint64_t lo = 0, hi = 0;
+				uint32_t cnt = 0;
+				for (uint32_t j = lane; j < (uint32_t)kQConsumers; j += 32u) {
+					const long long v = dacc[(size_t)sidx * kQConsumers + j];
+					add128(lo, hi, (uint64_t)v, v < 0 ? ~0ull : 0ull);
+					cnt += dcnt[g * kQConsumers + j];
+				}
+#pragma unroll
+				for (int d = 16; d > 0; d >>= 1) {
+					const uint64_t olo = __shfl_down_sync(0xffffffffu, lo, d);
+					const uint64_t ohi = __shfl_down_sync(0xffffffffu, hi, d);
+					add128(lo, hi, olo, ohi);
+					cnt += __shfl_down_sync(0xffffffffu, cnt, d);
+				}
+				if (lane == 0) {
+					// slot (g, k) of warp row 0 is touched by this warp only here: the main loop is behind the barrier
+					uint64_t slo = gacc.sum[0][g][k][0], shi = gacc.sum[0][g][k][1];
+					add128(slo, shi, lo, hi);
+					gacc.sum[0][g][k][0] = slo;
+					gacc.sum[0][g][k][1] = shi;
+					if (k == 0) {
+						gacc.cnt[0][g] += cnt;
+					}
+				}
+			}
+		}
+		if (a.dense_groups) {
+			__syncthreads();
+		}
+		// one thread per (group, aggregate): add up the 8 warp rows, one atomic triple per CTA
 		if (tid < a.n_groups * a.n_aggs) {
 			const uint32_t g = tid / a.n_aggs, k = tid % a.n_aggs;
 			uint64_t lo = 0, hi = 0, cnt = 0;
@@ -707,13 +819,18 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 
 }  // namespace
 
-uint32_t scan_columns_group_smem() {
-	return (uint32_t)((sizeof(GroupScratch) + 127u) & ~127u);
+uint32_t scan_columns_group_smem(uint32_t n_groups, uint32_t n_aggs, uint32_t dense) {
+	uint32_t bytes = (uint32_t)((sizeof(GroupScratch) + 127u) & ~127u);
+	if (dense) {
+		bytes += n_groups * n_aggs * (uint32_t)kQConsumers * 8u + n_groups * (uint32_t)kQConsumers * 4u;
+	}
+	return bytes;
 }
 
 cudaError_t launch_scan_columns(const QueryArgs &args, int sm_count, cudaStream_t stream) {
 	static size_t configured[64] = {};
-	const size_t smem = (size_t)args.stages * args.stage_bytes + (args.n_groups ? sizeof(GroupScratch) : 0);
+	const size_t smem = (size_t)args.stages * args.stage_bytes +
+	                    (args.n_groups ? scan_columns_group_smem(args.n_groups, args.n_aggs, args.dense_groups) : 0);
 	int dev = 0;
 	cudaGetDevice(&dev);
 	if (configured[dev & 63] < smem) {
