@@ -47,6 +47,7 @@ struct QPiece {
 	uint32_t w;
 	uint32_t linear;    // value == extend(min) + f without wrap-around for every f < 2^w
 	uint32_t pad;
+	uint64_t vbase;     // extend(min) of a linear piece: value = vbase + f
 };
 
 struct QStage {
@@ -75,9 +76,12 @@ __device__ __forceinline__ uint64_t column_value(const QPiece *pc, const uint8_t
 			p = 2;
 		}
 	}
-	const QPiece q = pc[p];
+	const QPiece &q = pc[p];
 	const uint64_t *words = (const uint64_t *)(stage + q.smem_off);
 	const uint32_t bit = q.bit_base + off * q.w;
+	if (q.linear && q.w <= 32u) {
+		return q.vbase + (uint64_t)(read_bits32((const uint32_t *)words, bit) & (0xffffffffu >> (32u - q.w)));
+	}
 	const uint64_t mask = lo_set64(q.w);
 	const uint64_t f = q.w <= 32u ? (uint64_t)(read_bits32((const uint32_t *)words, bit) & (uint32_t)mask)
 	                              : (read_bits64(words, bit) & mask);
@@ -105,6 +109,10 @@ __device__ __forceinline__ uint64_t group_value(const QPiece *pc, const uint8_t 
 	const uint32_t w = pc[p].w;
 	const uint32_t bit = pc[p].bit_base + (i - start) * w;
 	const uint8_t *base = stage + pc[p].smem_off;
+	if (pc[p].linear && w <= 32u) {
+		// the common case: a narrow field on a frame of reference that cannot wrap
+		return pc[p].vbase + (uint64_t)(read_bits32((const uint32_t *)base, bit) & (0xffffffffu >> (32u - w)));
+	}
 	const uint64_t mask = lo_set64(w);
 	const uint64_t f = w <= 32u ? (uint64_t)(read_bits32((const uint32_t *)base, bit) & (uint32_t)mask)
 	                            : (read_bits64((const uint64_t *)base, bit) & mask);
@@ -203,9 +211,11 @@ __device__ __forceinline__ PieceRes resolve_piece(const QueryCol &c, const DescQ
 	r.cnt = cnt;
 	r.w = w;
 	r.min_add = (mn != ~0ull && (repacked || literal)) ? mn : 0ull;
-	if (c.has_pred && piece_is_linear(c, r.min_add, w, repacked)) {
+	if (piece_is_linear(c, r.min_add, w, repacked)) {
 		r.linear = 1;
-		field_range(c, r.min_add, w, r.flo, r.span);
+		if (c.has_pred) {
+			field_range(c, r.min_add, w, r.flo, r.span);
+		}
 	}
 	return r;
 }
@@ -485,6 +495,7 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 				q.span = pr.span;
 				q.linear = pr.linear;
 				q.pad = 0;
+				q.vbase = extend_rt(pr.min_add, col.type_size, col.is_signed);
 				q.smem_off = incl - pr.bytes;
 				q.bit_base = pr.bit_base;
 				q.cnt = pr.cnt;
