@@ -88,6 +88,9 @@ _PROTOTYPES = {
     "adacom_column_fill_splitmix": (_i, [_vp, _u64, _u64, _u64]),
     "adacom_analyze": (_i, [_vp, _u64, _u64, _i, _vp, _i]),
     "adacom_encode": (_i, [_vp, _u64, _u64, _i]),
+    "adacom_analyze_list": (_i, [_vp, _u64, _vp, _i, _vp]),
+    "adacom_encode_list": (_i, [_vp, _u64, _vp, _i]),
+    "adacom_uncompact_list": (_i, [_vp, _u64, _vp, _i]),
     "adacom_column_get_meta": (_i, [_vp, _u64, _u64, _vp]),
     "adacom_column_data_size": (_i, [_vp, _u64, _u64, C.POINTER(_u64)]),
     "adacom_column_packed_words": (_u64, [_vp]),

@@ -312,6 +312,17 @@ class Column:
         self.analyze(seg_begin, seg_end, flags, validity)
         self.encode(seg_begin, seg_end, flags)
 
+    # ---- segment-list forms (policy epochs): ids strictly ascending ----
+    def compact_list(self, segs, flags=0, analyze=True):
+        segs = np.ascontiguousarray(segs, dtype=np.uint32)
+        if analyze:
+            self.ctx.check(self.lib.adacom_analyze_list(self.h, len(segs), _np_ptr(segs), flags, None))
+        self.ctx.check(self.lib.adacom_encode_list(self.h, len(segs), _np_ptr(segs), flags))
+
+    def uncompact_list(self, segs, flags=0):
+        segs = np.ascontiguousarray(segs, dtype=np.uint32)
+        self.ctx.check(self.lib.adacom_uncompact_list(self.h, len(segs), _np_ptr(segs), flags))
+
     def meta(self, seg_begin=0, seg_end=None):
         b, e = self._range(seg_begin, seg_end)
         arr = (SegmentMeta * max(e - b, 1))()

@@ -766,25 +766,18 @@ extern "C" adacom_status adacom_analyze(adacom_column *col, uint64_t seg_begin, 
 	return ADACOM_OK;
 }
 
-extern "C" adacom_status adacom_encode(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags) {
-	if (!range_ok(col, seg_begin, seg_end)) {
-		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_encode: bad segment range");
-	}
+// the encode of the segments [seg_begin, seg_begin + n) or, with d_list, of the n listed segments whose 2048-value
+// tiles are d_jobs[0 .. n_jobs) (the caller holds the context lock)
+static adacom_status encode_locked(adacom_column *col, uint64_t seg_begin, uint32_t n, int flags, const uint32_t *d_list,
+                                   const Job *d_jobs, uint32_t n_jobs) {
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
-	if (!col->raw) {
-		return fail(ctx, ADACOM_ERR_STATE, "adacom_encode: the raw arena was released");
-	}
-	const uint32_t n = (uint32_t)(seg_end - seg_begin);
-	if (n == 0) {
-		return ADACOM_OK;
-	}
+	const uint64_t seg_end = d_list ? seg_begin : seg_begin + n;  // a list owns no segment range (extent retirement)
 	const uint32_t extent_id = (uint32_t)col->extents.size();
 	// 1. widths, repack decisions and payload offsets, all on the device
 	const unsigned long long ticket = ++ctx->ticket;
 	LAUNCH(ctx, launch_layout(col->t, col->d_desc, (uint32_t)seg_begin, n, flags, extent_id, ctx->d_totals, ticket,
-	                          col->d_parts, (seg_begin == 0 && seg_end == col->n_segs) ? 1 : 0, ctx->d_layout_scratch,
-	                          ctx->stream));
+	                          col->d_parts, (!d_list && seg_begin == 0 && seg_end == col->n_segs) ? 1 : 0,
+	                          ctx->d_layout_scratch, ctx->stream, d_list));
 	// the only host round trip of an encode: 8 bytes that size the new extent, polled from mapped memory
 	{
 		volatile unsigned long long *t = ctx->h_totals;
@@ -804,8 +797,8 @@ extern "C" adacom_status adacom_encode(adacom_column *col, uint64_t seg_begin, u
 	}
 	Extent ext;
 	ext.words = ctx->h_totals[0];
-	ext.seg_begin = seg_begin;
-	ext.seg_end = seg_end;
+	ext.seg_begin = d_list ? ~0ull : seg_begin;  // a list extent is never retired by range (only by gc_extents)
+	ext.seg_end = d_list ? ~0ull : seg_end;
 	if (ext.words) {
 		// 2. a fresh extent: scans keep reading the old payloads until the descriptors are re-bound.
 		//    Prefer a retired extent of this column (smallest that fits) over an allocator call.
@@ -825,12 +818,151 @@ extern "C" adacom_status adacom_encode(adacom_column *col, uint64_t seg_begin, u
 			CK(ctx, cudaMallocAsync((void **)&ext.base, ext.capacity * 8 + kArenaPad, ctx->stream));
 		}
 		// 3. pack, then publish packed_ptr = base + word_offset (scans launched later on this stream see it)
-		LAUNCH(ctx, launch_encode(col->t, col->d_desc, col->d_tiles + col->tile_first[seg_begin],
-		                          col->tile_first[seg_end] - col->tile_first[seg_begin], col->raw, extent_id, ext.base,
-		                          ctx->sm_count, ctx->stream));
-		LAUNCH(ctx, launch_bind_extent(col->d_desc, (uint32_t)seg_begin, n, ext.base, extent_id, ctx->stream));
+		LAUNCH(ctx, launch_encode(col->t, col->d_desc, d_jobs, n_jobs, col->raw, extent_id, ext.base, ctx->sm_count,
+		                          ctx->stream));
+		LAUNCH(ctx, launch_bind_extent(col->d_desc, (uint32_t)seg_begin, n, ext.base, extent_id, ctx->stream, d_list));
 	}
 	col->extents.push_back(ext);
+	col->mirror_dirty = true;
+	col->epoch++;
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_encode(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags) {
+	if (!range_ok(col, seg_begin, seg_end)) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_encode: bad segment range");
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	if (!col->raw) {
+		return fail(ctx, ADACOM_ERR_STATE, "adacom_encode: the raw arena was released");
+	}
+	const uint32_t n = (uint32_t)(seg_end - seg_begin);
+	if (n == 0) {
+		return ADACOM_OK;
+	}
+	return encode_locked(col, seg_begin, n, flags, nullptr, col->d_tiles + col->tile_first[seg_begin],
+	                     col->tile_first[seg_end] - col->tile_first[seg_begin]);
+}
+
+// ---- segment-list forms: what the access-frequency policy needs (ColumnSegmentCatalog::CompactSegments,
+// src/catalog/catalog_entry/column_segment_catalog.cpp:64-116: the coldest 90 % of the segments, in read-count order,
+// are Compact()ed one by one and the rest Uncompact()ed -- arbitrary subsets, not ranges).  One launch set per call.
+
+namespace {
+
+struct SegList {
+	uint32_t *d_list = nullptr;  // device copy of the segment ids, the tile jobs behind it
+	Job *d_jobs = nullptr;
+	uint32_t n_jobs = 0;
+};
+
+adacom_status stage_seg_list(adacom_column *col, uint64_t n, const uint32_t *segs, const char *who, SegList &out) {
+	adacom_ctx *ctx = col->ctx;
+	std::vector<Job> jobs;
+	for (uint64_t i = 0; i < n; i++) {
+		if (segs[i] >= col->n_segs || (i && segs[i] <= segs[i - 1])) {
+			return fail(ctx, ADACOM_ERR_INVALID, std::string(who) + ": segment ids must be strictly ascending and in range");
+		}
+		for (uint32_t t = col->tile_first[segs[i]]; t < col->tile_first[segs[i] + 1]; t++) {
+			jobs.push_back({segs[i], t - col->tile_first[segs[i]]});
+		}
+	}
+	const size_t list_bytes = ((size_t)n * sizeof(uint32_t) + 15) & ~(size_t)15;
+	uint8_t *buf = nullptr;
+	CK(ctx, cudaMallocAsync((void **)&buf, list_bytes + (jobs.size() + 1) * sizeof(Job), ctx->stream));
+	CK(ctx, cudaMemcpyAsync(buf, segs, n * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+	if (!jobs.empty()) {
+		CK(ctx, cudaMemcpyAsync(buf + list_bytes, jobs.data(), jobs.size() * sizeof(Job), cudaMemcpyHostToDevice, ctx->stream));
+	}
+	// both sources are pageable: staged before the copies return
+	out.d_list = (uint32_t *)buf;
+	out.d_jobs = (Job *)(buf + list_bytes);
+	out.n_jobs = (uint32_t)jobs.size();
+	return ADACOM_OK;
+}
+
+}  // namespace
+
+extern "C" adacom_status adacom_analyze_list(adacom_column *col, uint64_t n, const uint32_t *segs, int flags,
+                                             const uint64_t *device_validity) {
+	if (!col || (n && !segs) || n >= (1ull << 32)) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_analyze_list: bad arguments");
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	if (!col->raw) {
+		return fail(ctx, ADACOM_ERR_STATE, "adacom_analyze_list: the raw arena was released");
+	}
+	if (n == 0) {
+		return ADACOM_OK;
+	}
+	SegList sl;
+	adacom_status st = stage_seg_list(col, n, segs, "adacom_analyze_list", sl);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	LAUNCH(ctx, launch_analyze(col->t, col->d_desc, 0, (uint32_t)n, col->raw, device_validity,
+	                           (flags & ADACOM_ZERO_EXT_MINMAX) ? 1 : 0, ctx->stream, sl.d_list));
+	CK(ctx, cudaFreeAsync(sl.d_list, ctx->stream));
+	col->mirror_dirty = true;
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_encode_list(adacom_column *col, uint64_t n, const uint32_t *segs, int flags) {
+	if (!col || (n && !segs) || n >= (1ull << 32)) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_encode_list: bad arguments");
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	if (!col->raw) {
+		return fail(ctx, ADACOM_ERR_STATE, "adacom_encode_list: the raw arena was released");
+	}
+	if (n == 0) {
+		return ADACOM_OK;
+	}
+	SegList sl;
+	adacom_status st = stage_seg_list(col, n, segs, "adacom_encode_list", sl);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	st = encode_locked(col, 0, (uint32_t)n, flags, sl.d_list, sl.d_jobs, sl.n_jobs);
+	cudaFreeAsync(sl.d_list, ctx->stream);
+	return st;
+}
+
+extern "C" adacom_status adacom_uncompact_list(adacom_column *col, uint64_t n, const uint32_t *segs, int flags) {
+	if (!col || (n && !segs) || n >= (1ull << 32)) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_uncompact_list: bad arguments");
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	if (n == 0) {
+		return ADACOM_OK;
+	}
+	adacom_status st = ensure_raw(col);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	SegList sl;
+	st = stage_seg_list(col, n, segs, "adacom_uncompact_list", sl);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	DecodeArgs a;
+	a.desc = col->d_desc;
+	a.jobs = sl.d_jobs;
+	a.n_jobs = sl.n_jobs;
+	a.raw = col->raw;
+	a.literal = (flags & ADACOM_LITERAL) ? 1 : 0;
+	a.uncompact = 1;
+	a.out = col->raw;
+	a.out_row0 = 0;
+	LAUNCH(ctx, launch_decode(col->t, kModeFlat, a, ctx->sm_count, ctx->stream));
+	LAUNCH(ctx, launch_reset_uncompacted(col->d_desc, 0, (uint32_t)n, col->t.size, col->d_parts, col->raw_parts, ctx->stream,
+	                                     sl.d_list));
+	CK(ctx, cudaFreeAsync(sl.d_list, ctx->stream));
+	// dead extents are reclaimed when the host mirror is refreshed (gc_extents)
 	col->mirror_dirty = true;
 	col->epoch++;
 	return ADACOM_OK;

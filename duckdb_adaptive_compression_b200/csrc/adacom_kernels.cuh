@@ -120,21 +120,24 @@ cudaError_t launch_fetch_rows(TypeInfo t, const SegDesc *desc, const uint8_t *ra
 
 // analyze: per-segment unsigned min/max (+ optional validity / NullValue fill); one CTA per segment
 cudaError_t launch_analyze(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, uint8_t *raw,
-                           const uint64_t *validity, int zero_ext, cudaStream_t stream);
+                           const uint64_t *validity, int zero_ext, cudaStream_t stream,
+                           const uint32_t *seg_list = nullptr /* device: the segments, instead of the range */);
 
 // layout: widths, repack decision, 128-byte aligned word offsets (exclusive scan); totals (host-mapped) =
 // {words, ticket}
 cudaError_t launch_layout(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int flags, uint32_t extent,
                           unsigned long long *totals, unsigned long long ticket, uint32_t *parts, int whole_column,
-                          unsigned long long *scratch /* 128 words of device memory */, cudaStream_t stream);
+                          unsigned long long *scratch /* 128 words of device memory */, cudaStream_t stream,
+                          const uint32_t *seg_list = nullptr);
 
 // bind packed_ptr = base + word_offset for the repacked segments of the range
 cudaError_t launch_bind_extent(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, uint64_t *base, uint32_t extent,
-                               cudaStream_t stream);
+                               cudaStream_t stream, const uint32_t *seg_list = nullptr);
 
 // after an uncompact decode: segments of the range that were compacted go back to slot width / UNCOMPRESSED
 cudaError_t launch_reset_uncompacted(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int type_size,
-                                     uint32_t *parts, uint32_t raw_parts, cudaStream_t stream);
+                                     uint32_t *parts, uint32_t raw_parts, cudaStream_t stream,
+                                     const uint32_t *seg_list = nullptr);
 
 // encode: FOR subtract + width-specialised bit-pack of the tiles whose segment the preceding layout assigned to
 // `extent` (payload at base + word_offset; launch_bind_extent publishes the pointers afterwards)

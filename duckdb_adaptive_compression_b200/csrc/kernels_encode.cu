@@ -53,9 +53,10 @@ __device__ __forceinline__ uint64_t null_pattern() {
 // uint64_t(sign_extend(v)) and zero_extend(v), so min/max are taken on the patterns and extended once.
 template <int S, bool SIGNED>
 __global__ void __launch_bounds__(kAnalyzeThreads) analyze_kernel(SegDesc *desc, uint32_t seg_begin, uint8_t *raw,
-                                                                  const uint64_t *validity, int zero_ext) {
+                                                                  const uint64_t *validity, int zero_ext,
+                                                                  const uint32_t *seg_list) {
 	using T = typename UIntOf<S>::type;
-	SegDesc *d = desc + seg_begin + blockIdx.x;
+	SegDesc *d = desc + (seg_list ? __ldg(seg_list + blockIdx.x) : seg_begin + blockIdx.x);
 	const uint64_t row_start = d->row_start;
 	const uint32_t count = d->count;
 	T *vals = (T *)raw + row_start;
@@ -226,7 +227,8 @@ __global__ void __launch_bounds__(kLayoutThreads) layout_kernel(SegDesc *desc, u
                                                                 uint32_t per, int type_size, int flags, uint32_t extent,
                                                                 volatile unsigned long long *totals,
                                                                 unsigned long long ticket, uint32_t *parts,
-                                                                int whole_column, volatile unsigned long long *scratch) {
+                                                                int whole_column, volatile unsigned long long *scratch,
+                                                                const uint32_t *seg_list) {
 	__shared__ unsigned long long warp_tot[kLayoutThreads / 32];
 	__shared__ unsigned long long base_s;
 	__shared__ uint32_t parts_s;
@@ -247,7 +249,7 @@ __global__ void __launch_bounds__(kLayoutThreads) layout_kernel(SegDesc *desc, u
 	uint32_t my_parts = 1;
 	LayoutItem first;  // per == 1 (up to 32768 segments): nothing is computed twice
 	for (uint32_t i = 0; i < per && g0 + i < n_segs; i++) {
-		const LayoutItem it = layout_item(desc + seg_begin + g0 + i, padded, zero_ext, slot_w);
+		const LayoutItem it = layout_item(desc + (seg_list ? __ldg(seg_list + g0 + i) : seg_begin + g0 + i), padded, zero_ext, slot_w);
 		if (i == 0) {
 			first = it;
 		}
@@ -310,7 +312,7 @@ __global__ void __launch_bounds__(kLayoutThreads) layout_kernel(SegDesc *desc, u
 	// ---- pass 2: write back ----
 	unsigned long long off = base_s + warp_base + incl - mine;
 	for (uint32_t i = 0; i < per && g0 + i < n_segs; i++) {
-		SegDesc *d = desc + seg_begin + g0 + i;
+		SegDesc *d = desc + (seg_list ? __ldg(seg_list + g0 + i) : seg_begin + g0 + i);
 		const LayoutItem it = i == 0 ? first : layout_item(d, padded, zero_ext, slot_w);
 		if (it.aligned != ~0ull) {
 			d->packed_ptr = 0;
@@ -333,10 +335,10 @@ __global__ void __launch_bounds__(kLayoutThreads) layout_kernel(SegDesc *desc, u
 }
 
 __global__ void bind_extent_kernel(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, uint64_t *base,
-                                   uint32_t extent) {
+                                   uint32_t extent, const uint32_t *seg_list) {
 	uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
 	if (g < n_segs) {
-		SegDesc *d = desc + seg_begin + g;
+		SegDesc *d = desc + (seg_list ? __ldg(seg_list + g) : seg_begin + g);
 		if ((d->state & kSegRepacked) && d->extent == extent && d->packed_ptr == 0) {
 			d->packed_ptr = (uint64_t)(base + d->word_offset);
 		}
@@ -346,13 +348,13 @@ __global__ void bind_extent_kernel(SegDesc *desc, uint32_t seg_begin, uint32_t n
 // ColumnSegment::UncompressSuccinct's bookkeeping (column_segment.cpp:494-503): function -> UNCOMPRESSED,
 // compacted = false; the payload was already decoded into the raw arena by the decode kernel.
 __global__ void reset_uncompacted_kernel(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int type_size,
-                                         uint32_t *parts, uint32_t raw_parts) {
+                                         uint32_t *parts, uint32_t raw_parts, const uint32_t *seg_list) {
 	uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
 	if (g == 0) {
 		atomicMax(parts, raw_parts);  // slot-width segments need the most scan chunks
 	}
 	if (g < n_segs) {
-		SegDesc *d = desc + seg_begin + g;
+		SegDesc *d = desc + (seg_list ? __ldg(seg_list + g) : seg_begin + g);
 		if (d->state & kSegCompacted) {
 			d->state = (uint8_t)((d->state & kSegAnalyzed) | kSegUncompressedFn);
 			d->width = (uint8_t)(8 * type_size);
@@ -364,14 +366,14 @@ __global__ void reset_uncompacted_kernel(SegDesc *desc, uint32_t seg_begin, uint
 
 template <int S>
 cudaError_t launch_analyze_s(bool is_signed, SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, uint8_t *raw,
-                             const uint64_t *validity, int zero_ext, cudaStream_t stream) {
+                             const uint64_t *validity, int zero_ext, cudaStream_t stream, const uint32_t *seg_list) {
 	if (n_segs == 0) {
 		return cudaSuccess;
 	}
 	if (is_signed) {
-		analyze_kernel<S, true><<<n_segs, kAnalyzeThreads, 0, stream>>>(desc, seg_begin, raw, validity, zero_ext);
+		analyze_kernel<S, true><<<n_segs, kAnalyzeThreads, 0, stream>>>(desc, seg_begin, raw, validity, zero_ext, seg_list);
 	} else {
-		analyze_kernel<S, false><<<n_segs, kAnalyzeThreads, 0, stream>>>(desc, seg_begin, raw, validity, zero_ext);
+		analyze_kernel<S, false><<<n_segs, kAnalyzeThreads, 0, stream>>>(desc, seg_begin, raw, validity, zero_ext, seg_list);
 	}
 	return cudaGetLastError();
 }
@@ -379,16 +381,16 @@ cudaError_t launch_analyze_s(bool is_signed, SegDesc *desc, uint32_t seg_begin, 
 }  // namespace
 
 cudaError_t launch_analyze(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, uint8_t *raw,
-                           const uint64_t *validity, int zero_ext, cudaStream_t stream) {
+                           const uint64_t *validity, int zero_ext, cudaStream_t stream, const uint32_t *seg_list) {
 	switch (t.size) {
 	case 1:
-		return launch_analyze_s<1>(t.is_signed, desc, seg_begin, n_segs, raw, validity, zero_ext, stream);
+		return launch_analyze_s<1>(t.is_signed, desc, seg_begin, n_segs, raw, validity, zero_ext, stream, seg_list);
 	case 2:
-		return launch_analyze_s<2>(t.is_signed, desc, seg_begin, n_segs, raw, validity, zero_ext, stream);
+		return launch_analyze_s<2>(t.is_signed, desc, seg_begin, n_segs, raw, validity, zero_ext, stream, seg_list);
 	case 4:
-		return launch_analyze_s<4>(t.is_signed, desc, seg_begin, n_segs, raw, validity, zero_ext, stream);
+		return launch_analyze_s<4>(t.is_signed, desc, seg_begin, n_segs, raw, validity, zero_ext, stream, seg_list);
 	case 8:
-		return launch_analyze_s<8>(t.is_signed, desc, seg_begin, n_segs, raw, validity, zero_ext, stream);
+		return launch_analyze_s<8>(t.is_signed, desc, seg_begin, n_segs, raw, validity, zero_ext, stream, seg_list);
 	default:
 		return cudaErrorInvalidValue;
 	}
@@ -396,7 +398,7 @@ cudaError_t launch_analyze(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32
 
 cudaError_t launch_layout(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int flags, uint32_t extent,
                           unsigned long long *totals, unsigned long long ticket, uint32_t *parts, int whole_column,
-                          unsigned long long *scratch, cudaStream_t stream) {
+                          unsigned long long *scratch, cudaStream_t stream, const uint32_t *seg_list) {
 	uint32_t grid = (n_segs + kLayoutThreads - 1) / kLayoutThreads;
 	if (grid > (uint32_t)kLayoutMaxCtas) {
 		grid = kLayoutMaxCtas;
@@ -406,25 +408,27 @@ cudaError_t launch_layout(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32_
 	}
 	const uint32_t per = (n_segs + grid * kLayoutThreads - 1) / (grid * kLayoutThreads);
 	layout_kernel<<<grid, kLayoutThreads, 0, stream>>>(desc, seg_begin, n_segs, per ? per : 1, t.size, flags, extent, totals,
-	                                                   ticket, parts, whole_column, scratch);
+	                                                   ticket, parts, whole_column, scratch, seg_list);
 	return cudaGetLastError();
 }
 
 cudaError_t launch_bind_extent(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, uint64_t *base, uint32_t extent,
-                               cudaStream_t stream) {
+                               cudaStream_t stream, const uint32_t *seg_list) {
 	if (n_segs == 0) {
 		return cudaSuccess;
 	}
-	bind_extent_kernel<<<(n_segs + 255) / 256, 256, 0, stream>>>(desc, seg_begin, n_segs, base, extent);
+	bind_extent_kernel<<<(n_segs + 255) / 256, 256, 0, stream>>>(desc, seg_begin, n_segs, base, extent, seg_list);
 	return cudaGetLastError();
 }
 
 cudaError_t launch_reset_uncompacted(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int type_size,
-                                     uint32_t *parts, uint32_t raw_parts, cudaStream_t stream) {
+                                     uint32_t *parts, uint32_t raw_parts, cudaStream_t stream,
+                                     const uint32_t *seg_list) {
 	if (n_segs == 0) {
 		return cudaSuccess;
 	}
-	reset_uncompacted_kernel<<<(n_segs + 255) / 256, 256, 0, stream>>>(desc, seg_begin, n_segs, type_size, parts, raw_parts);
+	reset_uncompacted_kernel<<<(n_segs + 255) / 256, 256, 0, stream>>>(desc, seg_begin, n_segs, type_size, parts, raw_parts,
+	                                                                   seg_list);
 	return cudaGetLastError();
 }
 

@@ -177,6 +177,16 @@ adacom_status adacom_analyze(adacom_column *col, uint64_t seg_begin, uint64_t se
  * packed arena (epoch swap: scans never observe a half-written payload). */
 adacom_status adacom_encode(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags);
 
+/* ---- segment-list forms (the access-frequency policy) -------------------------------------------------- */
+/* ColumnSegmentCatalog::CompactSegments (src/catalog/catalog_entry/column_segment_catalog.cpp:64-116) sorts the segments
+ * by read count, Compact()s the coldest 90 % and Uncompact()s the rest: arbitrary subsets of a column, not ranges.
+ * These calls take such a subset (host array of segment ids, strictly ascending) and run ONE launch set for it,
+ * with the semantics of the range forms.  device_validity: as adacom_analyze, device pointer or NULL. */
+adacom_status adacom_analyze_list(adacom_column *col, uint64_t n, const uint32_t *segs, int flags,
+                                  const uint64_t *device_validity);
+adacom_status adacom_encode_list(adacom_column *col, uint64_t n, const uint32_t *segs, int flags);
+adacom_status adacom_uncompact_list(adacom_column *col, uint64_t n, const uint32_t *segs, int flags);
+
 /* ---- metadata / accounting --------------------------------------------------------------------------- */
 adacom_status adacom_column_get_meta(adacom_column *col, uint64_t seg_begin, uint64_t seg_end,
                                      adacom_segment_meta *out);

@@ -91,9 +91,10 @@ def main():
         hot = np.sort(order[n_cold:])
         t0 = time.perf_counter()
         runs = np.split(hot, np.where(np.diff(hot) != 1)[0] + 1) if len(hot) else []
-        for r in runs:  # contiguous runs of hot segments -> one launch each
-            col.uncompact(int(r[0]), int(r[-1]) + 1)
+        launches0 = ctx.launch_count
+        col.uncompact_list(hot)  # the whole hot subset in one launch set (adacom_uncompact_list)
         ctx.synchronize()
+        epoch_launches = ctx.launch_count - launches0
         t_epoch = time.perf_counter() - t0
         size_after = col.data_size()
         got = col.fetch_rows(seg, row)
@@ -101,12 +102,12 @@ def main():
         cnt, first = col.point_filter_batch(seg[:2000], keys[:2000])
         assert np.all(cnt == 1) and np.array_equal(starts[seg[:2000]] + first.astype(np.int64), keys[:2000])
         t0 = time.perf_counter()
-        col.compact()  # next epoch start: everything cold again
+        col.compact_list(hot, analyze=False)  # next epoch start: the hot subset becomes cold again (adacom_encode_list)
         ctx.synchronize()
         t_recompact = time.perf_counter() - t0
         sweep.append({"q": q, "distinct_segments_hit": int((reads > 0).sum()),
                       "Mfetch_per_s_e2e": round(len(keys) / t_fetch / 1e6, 2),
-                      "hot_segments_uncompacted": int(len(hot)), "uncompact_launches": len(runs),
+                      "hot_segments_uncompacted": int(len(hot)), "hot_runs": len(runs), "epoch_launches": int(epoch_launches),
                       "epoch_ms": round(t_epoch * 1e3, 3), "data_size_hot_cold": size_after,
                       "recompact_ms": round(t_recompact * 1e3, 3)})
     out["config3"] = {"rows": n, "keys_per_skew": 100_000, "sweep": sweep}
