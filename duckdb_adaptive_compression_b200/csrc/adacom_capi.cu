@@ -1280,6 +1280,70 @@ extern "C" adacom_status adacom_point_filter_batch(adacom_column *col, uint64_t 
 			return fail(ctx, ADACOM_ERR_INVALID, "adacom_point_filter_batch: segment index out of range");
 		}
 	}
+	// Shared scan: when every touched segment is re-packed to a byte-aligned width (8 / 16 / 32 bits -- the reference's
+	// benchmark columns pack to 16), the queries are counting-sorted by segment and each 16 KiB chunk of a segment is
+	// read once per slice of kPointSlice of its queries instead of once per query.
+	if (!(flags & ADACOM_LITERAL)) {
+		adacom_status st = sync_mirror(col);
+		if (st != ADACOM_OK) {
+			return st;
+		}
+		std::vector<uint32_t> start(col->n_segs + 1, 0);
+		bool eligible = true;
+		for (uint64_t q = 0; q < n_queries && eligible; q++) {
+			const SegDesc &d = col->h_desc[seg_idx[q]];
+			eligible = (d.state & kSegRepacked) && (d.width == 8 || d.width == 16 || d.width == 32) && d.count > 0;
+			start[seg_idx[q] + 1]++;
+		}
+		if (eligible) {
+			for (uint64_t g = 0; g < col->n_segs; g++) {
+				start[g + 1] += start[g];
+			}
+			std::vector<uint32_t> perm(n_queries), fill(start.begin(), start.end() - 1);
+			std::vector<int64_t> sorted(n_queries);
+			for (uint64_t q = 0; q < n_queries; q++) {
+				const uint32_t pos = fill[seg_idx[q]]++;
+				perm[pos] = (uint32_t)q;
+				sorted[pos] = constants[q];
+			}
+			std::vector<PointJob> jobs;
+			for (uint64_t g = 0; g < col->n_segs; g++) {
+				const uint32_t lo = start[g], hi = start[g + 1];
+				if (lo == hi) {
+					continue;
+				}
+				const SegDesc &d = col->h_desc[g];
+				const uint32_t chunk_vals = 16384u * 8u / d.width;
+				const uint32_t chunks = (d.count + chunk_vals - 1) / chunk_vals;
+				for (uint32_t c = 0; c < chunks; c++) {
+					for (uint32_t q0 = lo; q0 < hi; q0 += kPointSlice) {
+						jobs.push_back({(uint32_t)g, c, q0, std::min(hi, q0 + kPointSlice)});
+					}
+				}
+			}
+			const size_t jb = (jobs.size() * sizeof(PointJob) + 15) & ~(size_t)15;
+			uint8_t *buf = nullptr;
+			CK(ctx, cudaMallocAsync((void **)&buf, jb + 3 * n_queries * 8, ctx->stream));
+			int64_t *d_const = (int64_t *)(buf + jb);
+			unsigned long long *d_count = (unsigned long long *)(d_const + n_queries);
+			unsigned long long *d_first = d_count + n_queries;
+			CK(ctx, cudaMemcpyAsync(buf, jobs.data(), jobs.size() * sizeof(PointJob), cudaMemcpyHostToDevice, ctx->stream));
+			CK(ctx, cudaMemcpyAsync(d_const, sorted.data(), n_queries * 8, cudaMemcpyHostToDevice, ctx->stream));
+			CK(ctx, cudaMemsetAsync(d_count, 0, n_queries * 8, ctx->stream));
+			CK(ctx, cudaMemsetAsync(d_first, 0xff, n_queries * 8, ctx->stream));
+			LAUNCH(ctx, launch_point_shared(col->d_desc, (const PointJob *)buf, (uint32_t)jobs.size(), d_const, d_count, d_first,
+			                                col->t.size, ctx->sm_count, ctx->stream));
+			std::vector<uint64_t> res(2 * n_queries);
+			CK(ctx, cudaMemcpyAsync(res.data(), d_count, 2 * n_queries * 8, cudaMemcpyDeviceToHost, ctx->stream));
+			CK(ctx, cudaFreeAsync(buf, ctx->stream));
+			CK(ctx, cudaStreamSynchronize(ctx->stream));
+			for (uint64_t pos = 0; pos < n_queries; pos++) {
+				out_count[perm[pos]] = res[pos];
+				out_first_row[perm[pos]] = res[n_queries + pos];
+			}
+			return ADACOM_OK;
+		}
+	}
 	// one unit per query; the kernel walks the chunks of seg_idx[q] from the descriptors (no host-built table)
 	uint32_t *d_unit_seg = nullptr;
 	int64_t *d_const = nullptr;

@@ -118,6 +118,19 @@ cudaError_t launch_scan_range(TypeInfo t, const SegDesc *desc, uint32_t seg, con
 cudaError_t launch_fetch_rows(TypeInfo t, const SegDesc *desc, const uint8_t *raw, uint64_t n, const uint32_t *seg_idx,
                               const uint32_t *row_in_seg, int literal, void *out, cudaStream_t stream);
 
+// batched equality look-ups whose queries share the chunks of their segment (byte-aligned widths 8 / 16 / 32 of
+// re-packed segments only; the host falls back to launch_decode(kModePoint) otherwise).  Queries are sorted by segment;
+// q_const / q_count / q_first are in that order.
+constexpr uint32_t kPointSlice = 64;  // queries per job
+struct PointJob {
+	uint32_t seg;
+	uint32_t chunk;       // 16 KiB chunk of the segment's payload
+	uint32_t q_lo, q_hi;  // slice of the sorted queries
+};
+cudaError_t launch_point_shared(const SegDesc *desc, const PointJob *jobs, uint32_t n_jobs, const int64_t *q_const,
+                                unsigned long long *q_count, unsigned long long *q_first, int type_size, int sm_count,
+                                cudaStream_t stream);
+
 // analyze: per-segment unsigned min/max (+ optional validity / NullValue fill); one CTA per segment
 cudaError_t launch_analyze(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, uint8_t *raw,
                            const uint64_t *validity, int zero_ext, cudaStream_t stream,

@@ -76,7 +76,97 @@ __global__ void fill_splitmix_kernel(void *raw, uint64_t n, uint64_t seed, uint6
 	}
 }
 
+// ---- batched equality look-ups on byte-aligned widths, queries of a segment share its chunks -------------------
+// The Zipf look-up benchmarks (benchmark/micro/succinct/zipf_distribution.cpp:13-61) send most of their keys to a few
+// segments (q = 1: 60 % of 10 000 look-ups land in the first one).  One job = (segment, 16 KiB chunk of its payload,
+// slice of <= kPointSlice of the segment's queries): the chunk is read ONCE into registers (4 x 16 bytes per thread)
+// and compared against every target of the slice in the FIELD domain (value == c  <=>  field == (c - min) mod 2^(8S),
+// and the target must fit w bits) with the SIMD-in-a-word compares; a hit (rare) is resolved per field.
+constexpr int kPointThreads = 256;
+constexpr uint32_t kPointChunkBytes = 16384;
+
+__global__ void __launch_bounds__(kPointThreads) point_shared_kernel(const SegDesc *desc, const PointJob *jobs,
+                                                                      uint32_t n_jobs, const int64_t *q_const,
+                                                                      unsigned long long *q_count,
+                                                                      unsigned long long *q_first, uint32_t type_bits) {
+	__shared__ uint32_t target[kPointSlice];
+	__shared__ uint32_t target_ok[kPointSlice];
+	const uint32_t tid = threadIdx.x;
+	for (uint32_t jb = blockIdx.x; jb < n_jobs; jb += gridDim.x) {
+		const PointJob job = jobs[jb];
+		const SegDesc *d = desc + job.seg;
+		const uint32_t w = d->width;  // 8, 16 or 32 (checked by the host against its mirror)
+		const uint32_t count = d->count;
+		const uint64_t mn = d->min_factor;
+		const uint64_t min_add = mn == ~0ull ? 0ull : mn;
+		const uint32_t per = 128u / w;                        // fields per 16 bytes
+		const uint32_t chunk_vals = kPointChunkBytes * 8u / w;
+		const uint32_t first = job.chunk * chunk_vals;
+		const uint32_t cnt = min(chunk_vals, count - first);
+		const uint32_t n_vec = (cnt + per - 1u) / per;        // <= 1024
+		const uint4 *vec = (const uint4 *)(d->packed_ptr + (uint64_t)job.chunk * kPointChunkBytes);
+		uint4 x[4];
+#pragma unroll
+		for (int u = 0; u < 4; u++) {
+			const uint32_t j = tid + u * kPointThreads;
+			x[u] = j < n_vec ? __ldg(vec + j) : make_uint4(0u, 0u, 0u, 0u);
+		}
+		const uint32_t nq = job.q_hi - job.q_lo;
+		if (tid < nq) {
+			const uint64_t tf = ((uint64_t)__ldg(q_const + job.q_lo + tid) - min_add) & lo_set64(type_bits);
+			target[tid] = (uint32_t)tf;
+			target_ok[tid] = (tf >> w) == 0 ? 1u : 0u;  // a target that does not fit w bits cannot match
+		}
+		__syncthreads();
+		const uint32_t mask32 = w == 32u ? 0xffffffffu : ((1u << w) - 1u);
+		for (uint32_t q = 0; q < nq; q++) {
+			if (!target_ok[q]) {
+				continue;
+			}
+			const uint32_t t32 = target[q];
+			const uint32_t kk = w == 32u ? t32 : (w == 16u ? t32 * 0x00010001u : t32 * 0x01010101u);
+#pragma unroll
+			for (int u = 0; u < 4; u++) {
+				uint32_t m;
+				if (w == 32u) {
+					m = (x[u].x == kk) | (x[u].y == kk) | (x[u].z == kk) | (x[u].w == kk);
+				} else if (w == 16u) {
+					m = __vcmpeq2(x[u].x, kk) | __vcmpeq2(x[u].y, kk) | __vcmpeq2(x[u].z, kk) | __vcmpeq2(x[u].w, kk);
+				} else {
+					m = __vcmpeq4(x[u].x, kk) | __vcmpeq4(x[u].y, kk) | __vcmpeq4(x[u].z, kk) | __vcmpeq4(x[u].w, kk);
+				}
+				if (m) {
+					const uint32_t xs[4] = {x[u].x, x[u].y, x[u].z, x[u].w};
+					const uint32_t j = tid + u * kPointThreads;
+					for (uint32_t f = 0; f < per; f++) {
+						const uint32_t i = j * per + f;
+						const uint32_t fb = f * w;
+						const uint32_t fv = w == 32u ? xs[fb >> 5] : ((xs[fb >> 5] >> (fb & 31u)) & mask32);
+						if (i < cnt && fv == t32) {
+							atomicAdd(q_count + job.q_lo + q, 1ull);
+							atomicMin(q_first + job.q_lo + q, (unsigned long long)(first + i));
+						}
+					}
+				}
+			}
+		}
+		__syncthreads();  // the targets are rewritten by the next job
+	}
+}
+
 }  // namespace
+
+cudaError_t launch_point_shared(const SegDesc *desc, const PointJob *jobs, uint32_t n_jobs, const int64_t *q_const,
+                                unsigned long long *q_count, unsigned long long *q_first, int type_size, int sm_count,
+                                cudaStream_t stream) {
+	if (n_jobs == 0) {
+		return cudaSuccess;
+	}
+	const uint32_t resident = (uint32_t)sm_count * 8u;
+	point_shared_kernel<<<n_jobs < resident ? n_jobs : resident, kPointThreads, 0, stream>>>(
+	    desc, jobs, n_jobs, q_const, q_count, q_first, 8u * (uint32_t)type_size);
+	return cudaGetLastError();
+}
 
 #define ADACOM_DISPATCH_SIZE(size, CALL) \
 	switch (size) {                      \

@@ -124,3 +124,58 @@ def test_policy_epoch_two_calls(gpu_ctx):
     assert col.data_size() == size_all
     assert np.array_equal(col.decode(), values)
     col.close()
+
+
+@pytest.mark.parametrize("dtype", [np.int16, np.uint32, np.int32, np.int64], ids=lambda d: np.dtype(d).name)
+def test_point_lookups_shared_scan(gpu_ctx, dtype):
+    """Batches whose segments all pack to 8 / 16 / 32 bits take the shared scan (queries counting-sorted by segment,
+    a 16 KiB chunk read once per slice of 64 queries): hot segments with hundreds of queries in arbitrary order,
+    multi-chunk segments, duplicates, misses, keys outside the field range, negative frames of reference --
+    numpy's count and first row for every query, ONE kernel launch."""
+    dt = np.dtype(dtype)
+    bits = 8 * dt.itemsize
+    info = np.iinfo(dt)
+    rng = np.random.default_rng(11)
+    cap = 262136 // dt.itemsize
+    segs = []
+    for w in [x for x in (8, 16, 32) if x < bits]:
+        for base in (0, 1000, int(info.min) if dt.kind == "i" else 7):
+            for n in (cap, 5000, 1):
+                lo = base
+                hi = lo + (1 << w) - 1
+                v = rng.integers(lo, hi, size=n, endpoint=True, dtype=np.int64).astype(dtype)
+                if n > 2:
+                    v[0], v[1] = np.array(lo).astype(dtype), np.array(hi).astype(dtype)  # exact width
+                    v[n // 2: n // 2 + 5] = v[0]
+                segs.append(v)
+    col = gpu_ctx.column_from_values(np.concatenate(segs), [len(v) for v in segs])
+    col.compact()
+    widths = {m.width for m in col.meta() if m.count > 2}
+    assert widths <= {8, 16, 32}
+    q_seg, q_key = [], []
+    for g, v in enumerate(segs):
+        k_here = 300 if g % 4 == 0 else 5
+        picks = rng.integers(0, len(v), size=k_here)
+        for i in picks:
+            q_seg.append(g)
+            q_key.append(int(v[i]))
+        for k in (int(v.min()) - 1, int(v.max()) + 1, int(info.min), int(info.max), 0, int(v[0])):
+            if int(info.min) <= k <= int(info.max):
+                q_seg.append(g)
+                q_key.append(k)
+    order = rng.permutation(len(q_seg))
+    q_seg = np.array(q_seg, dtype=np.uint32)[order]
+    q_key = np.array(q_key, dtype=np.int64)[order]
+    # single-value segments keep their slot width or pack to 1 bit: leave them out of the eligible batch
+    keep = np.array([len(segs[g]) > 2 for g in q_seg])
+    launches = gpu_ctx.launch_count
+    cnt, first = col.point_filter_batch(q_seg[keep], q_key[keep])
+    assert gpu_ctx.launch_count - launches == 1
+    for j, (g, k) in enumerate(zip(q_seg[keep], q_key[keep])):
+        hit = np.nonzero(segs[g] == np.array(k).astype(dtype))[0]
+        assert cnt[j] == len(hit), (g, k, j)
+        assert first[j] == (hit[0] if len(hit) else (1 << 64) - 1), (g, k, j)
+    # a batch that also touches an ineligible segment falls back to the per-query kernel: same answers
+    cnt2, first2 = col.point_filter_batch(q_seg, q_key)
+    assert np.array_equal(cnt2[keep], cnt) and np.array_equal(first2[keep], first)
+    col.close()
