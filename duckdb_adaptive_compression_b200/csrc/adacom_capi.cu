@@ -44,6 +44,9 @@ struct adacom_ctx {
 	Agg *h_aggs = nullptr;                // pinned
 	Agg *h_agg = nullptr;                 // pinned
 	unsigned long long *h_totals = nullptr;  // pinned
+	// staging pair of the batched look-ups (pinned host + device, grown on demand): one H2D, one kernel, one D2H
+	uint8_t *h_stage = nullptr, *d_stage = nullptr;
+	size_t stage_bytes = 0;
 };
 
 struct Extent {
@@ -370,6 +373,8 @@ extern "C" void adacom_ctx_destroy(adacom_ctx *ctx) {
 	cudaFreeHost(ctx->h_aggs);
 	cudaFreeHost(ctx->h_agg);
 	cudaFreeHost(ctx->h_totals);
+	cudaFreeHost(ctx->h_stage);
+	cudaFree(ctx->d_stage);
 	cudaStreamDestroy(ctx->stream);
 	delete ctx;
 }
@@ -1299,14 +1304,45 @@ extern "C" adacom_status adacom_point_filter_batch(adacom_column *col, uint64_t 
 			for (uint64_t g = 0; g < col->n_segs; g++) {
 				start[g + 1] += start[g];
 			}
+			// job count first, then everything is written straight into the pinned staging buffer:
+			// [jobs | sorted constants | counts (0) | first rows (~0)]
+			size_t n_jobs = 0;
+			for (uint64_t g = 0; g < col->n_segs; g++) {
+				const uint32_t k = start[g + 1] - start[g];
+				if (k) {
+					const SegDesc &d = col->h_desc[g];
+					const uint32_t chunk_vals = 16384u * 8u / d.width;
+					n_jobs += (size_t)((d.count + chunk_vals - 1) / chunk_vals) * ((k + kPointSlice - 1) / kPointSlice);
+				}
+			}
+			if (n_jobs >= (1ull << 32)) {
+				return fail(ctx, ADACOM_ERR_INVALID, "adacom_point_filter_batch: too many look-up jobs");
+			}
+			const size_t jb = (n_jobs * sizeof(PointJob) + 15) & ~(size_t)15;
+			const size_t need = jb + 3 * n_queries * 8;
+			if (ctx->stage_bytes < need) {
+				CK(ctx, cudaStreamSynchronize(ctx->stream));
+				cudaFreeHost(ctx->h_stage);
+				cudaFree(ctx->d_stage);
+				ctx->h_stage = ctx->d_stage = nullptr;
+				ctx->stage_bytes = 0;
+				const size_t cap = need + need / 2 + 4096;
+				CK(ctx, cudaHostAlloc((void **)&ctx->h_stage, cap, cudaHostAllocDefault));
+				CK(ctx, cudaMalloc((void **)&ctx->d_stage, cap));
+				ctx->stage_bytes = cap;
+			}
+			PointJob *jobs = (PointJob *)ctx->h_stage;
+			int64_t *sorted = (int64_t *)(ctx->h_stage + jb);
+			uint64_t *res = (uint64_t *)(sorted + n_queries);  // counts, then first rows
 			std::vector<uint32_t> perm(n_queries), fill(start.begin(), start.end() - 1);
-			std::vector<int64_t> sorted(n_queries);
 			for (uint64_t q = 0; q < n_queries; q++) {
 				const uint32_t pos = fill[seg_idx[q]]++;
 				perm[pos] = (uint32_t)q;
 				sorted[pos] = constants[q];
 			}
-			std::vector<PointJob> jobs;
+			memset(res, 0, n_queries * 8);
+			memset(res + n_queries, 0xff, n_queries * 8);
+			size_t j = 0;
 			for (uint64_t g = 0; g < col->n_segs; g++) {
 				const uint32_t lo = start[g], hi = start[g + 1];
 				if (lo == hi) {
@@ -1317,25 +1353,16 @@ extern "C" adacom_status adacom_point_filter_batch(adacom_column *col, uint64_t 
 				const uint32_t chunks = (d.count + chunk_vals - 1) / chunk_vals;
 				for (uint32_t c = 0; c < chunks; c++) {
 					for (uint32_t q0 = lo; q0 < hi; q0 += kPointSlice) {
-						jobs.push_back({(uint32_t)g, c, q0, std::min(hi, q0 + kPointSlice)});
+						jobs[j++] = {(uint32_t)g, c, q0, std::min(hi, q0 + kPointSlice)};
 					}
 				}
 			}
-			const size_t jb = (jobs.size() * sizeof(PointJob) + 15) & ~(size_t)15;
-			uint8_t *buf = nullptr;
-			CK(ctx, cudaMallocAsync((void **)&buf, jb + 3 * n_queries * 8, ctx->stream));
-			int64_t *d_const = (int64_t *)(buf + jb);
+			CK(ctx, cudaMemcpyAsync(ctx->d_stage, ctx->h_stage, need, cudaMemcpyHostToDevice, ctx->stream));
+			int64_t *d_const = (int64_t *)(ctx->d_stage + jb);
 			unsigned long long *d_count = (unsigned long long *)(d_const + n_queries);
-			unsigned long long *d_first = d_count + n_queries;
-			CK(ctx, cudaMemcpyAsync(buf, jobs.data(), jobs.size() * sizeof(PointJob), cudaMemcpyHostToDevice, ctx->stream));
-			CK(ctx, cudaMemcpyAsync(d_const, sorted.data(), n_queries * 8, cudaMemcpyHostToDevice, ctx->stream));
-			CK(ctx, cudaMemsetAsync(d_count, 0, n_queries * 8, ctx->stream));
-			CK(ctx, cudaMemsetAsync(d_first, 0xff, n_queries * 8, ctx->stream));
-			LAUNCH(ctx, launch_point_shared(col->d_desc, (const PointJob *)buf, (uint32_t)jobs.size(), d_const, d_count, d_first,
-			                                col->t.size, ctx->sm_count, ctx->stream));
-			std::vector<uint64_t> res(2 * n_queries);
-			CK(ctx, cudaMemcpyAsync(res.data(), d_count, 2 * n_queries * 8, cudaMemcpyDeviceToHost, ctx->stream));
-			CK(ctx, cudaFreeAsync(buf, ctx->stream));
+			LAUNCH(ctx, launch_point_shared(col->d_desc, (const PointJob *)ctx->d_stage, (uint32_t)n_jobs, d_const, d_count,
+			                                d_count + n_queries, col->t.size, ctx->sm_count, ctx->stream));
+			CK(ctx, cudaMemcpyAsync(res, d_count, 2 * n_queries * 8, cudaMemcpyDeviceToHost, ctx->stream));
 			CK(ctx, cudaStreamSynchronize(ctx->stream));
 			for (uint64_t pos = 0; pos < n_queries; pos++) {
 				out_count[perm[pos]] = res[pos];
