@@ -290,6 +290,23 @@ void fill_meta(const adacom_column *col, uint64_t g, adacom_segment_meta *m) {
 	m->capacity = d.capacity;
 }
 
+// pinned host + device staging pair of the batched look-up paths, grown on demand (the caller holds the lock)
+adacom_status ensure_stage(adacom_ctx *ctx, size_t need) {
+	if (ctx->stage_bytes >= need) {
+		return ADACOM_OK;
+	}
+	CK(ctx, cudaStreamSynchronize(ctx->stream));
+	cudaFreeHost(ctx->h_stage);
+	cudaFree(ctx->d_stage);
+	ctx->h_stage = ctx->d_stage = nullptr;
+	ctx->stage_bytes = 0;
+	const size_t cap = need + need / 2 + 4096;
+	CK(ctx, cudaHostAlloc((void **)&ctx->h_stage, cap, cudaHostAllocDefault));
+	CK(ctx, cudaMalloc((void **)&ctx->d_stage, cap));
+	ctx->stage_bytes = cap;
+	return ADACOM_OK;
+}
+
 adacom_status ensure_raw(adacom_column *col) {
 	if (!col->raw) {
 		CK(col->ctx, cudaMallocAsync((void **)&col->raw, col->n_values * col->t.size + kArenaPad, col->ctx->stream));
@@ -1320,16 +1337,9 @@ extern "C" adacom_status adacom_point_filter_batch(adacom_column *col, uint64_t 
 			}
 			const size_t jb = (n_jobs * sizeof(PointJob) + 15) & ~(size_t)15;
 			const size_t need = jb + 3 * n_queries * 8;
-			if (ctx->stage_bytes < need) {
-				CK(ctx, cudaStreamSynchronize(ctx->stream));
-				cudaFreeHost(ctx->h_stage);
-				cudaFree(ctx->d_stage);
-				ctx->h_stage = ctx->d_stage = nullptr;
-				ctx->stage_bytes = 0;
-				const size_t cap = need + need / 2 + 4096;
-				CK(ctx, cudaHostAlloc((void **)&ctx->h_stage, cap, cudaHostAllocDefault));
-				CK(ctx, cudaMalloc((void **)&ctx->d_stage, cap));
-				ctx->stage_bytes = cap;
+			st = ensure_stage(ctx, need);
+			if (st != ADACOM_OK) {
+				return st;
 			}
 			PointJob *jobs = (PointJob *)ctx->h_stage;
 			int64_t *sorted = (int64_t *)(ctx->h_stage + jb);
@@ -1683,24 +1693,27 @@ extern "C" adacom_status adacom_fetch_rows(adacom_column *col, uint64_t n, const
 		LAUNCH(ctx, launch_fetch_rows(col->t, col->d_desc, col->raw, n, seg_idx, row_in_seg, literal, out, ctx->stream));
 		return ADACOM_OK;
 	}
+	// validated and copied into the pinned staging buffer in one pass: [segments | rows | answers]
+	const size_t in_bytes = (size_t)n * 8;
+	adacom_status st = ensure_stage(ctx, in_bytes + (size_t)n * col->t.size);
+	if (st != ADACOM_OK) {
+		return st;
+	}
+	uint32_t *h_seg = (uint32_t *)ctx->h_stage, *h_row = h_seg + n;
 	for (uint64_t q = 0; q < n; q++) {
 		if (seg_idx[q] >= col->n_segs || row_in_seg[q] >= col->h_desc[seg_idx[q]].count) {
 			return fail(ctx, ADACOM_ERR_INVALID, "adacom_fetch_rows: (segment, row) out of range");
 		}
+		h_seg[q] = seg_idx[q];
+		h_row[q] = row_in_seg[q];
 	}
-	uint32_t *d_seg = nullptr, *d_row = nullptr;
-	void *d_out = nullptr;
-	CK(ctx, cudaMallocAsync((void **)&d_seg, n * 4, ctx->stream));
-	CK(ctx, cudaMallocAsync((void **)&d_row, n * 4, ctx->stream));
-	CK(ctx, cudaMallocAsync(&d_out, n * col->t.size, ctx->stream));
-	CK(ctx, cudaMemcpyAsync(d_seg, seg_idx, n * 4, cudaMemcpyHostToDevice, ctx->stream));
-	CK(ctx, cudaMemcpyAsync(d_row, row_in_seg, n * 4, cudaMemcpyHostToDevice, ctx->stream));
-	LAUNCH(ctx, launch_fetch_rows(col->t, col->d_desc, col->raw, n, d_seg, d_row, literal, d_out, ctx->stream));
-	CK(ctx, cudaMemcpyAsync(out, d_out, n * col->t.size, cudaMemcpyDeviceToHost, ctx->stream));
-	CK(ctx, cudaFreeAsync(d_seg, ctx->stream));
-	CK(ctx, cudaFreeAsync(d_row, ctx->stream));
-	CK(ctx, cudaFreeAsync(d_out, ctx->stream));
+	uint32_t *d_seg = (uint32_t *)ctx->d_stage;
+	void *d_out = ctx->d_stage + in_bytes;
+	CK(ctx, cudaMemcpyAsync(d_seg, h_seg, in_bytes, cudaMemcpyHostToDevice, ctx->stream));
+	LAUNCH(ctx, launch_fetch_rows(col->t, col->d_desc, col->raw, n, d_seg, d_seg + n, literal, d_out, ctx->stream));
+	CK(ctx, cudaMemcpyAsync(ctx->h_stage + in_bytes, d_out, n * col->t.size, cudaMemcpyDeviceToHost, ctx->stream));
 	CK(ctx, cudaStreamSynchronize(ctx->stream));
+	memcpy(out, ctx->h_stage + in_bytes, n * col->t.size);
 	return ADACOM_OK;
 }
 
