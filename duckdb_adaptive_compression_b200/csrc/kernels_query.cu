@@ -546,10 +546,36 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 			__syncwarp();
 
 			// ---- predicate columns, one after the other; a column is walked piece by piece ----
+			bool list_mode = false;
+			uint32_t n_list = 0;
 #pragma unroll 1
 			for (uint32_t c = 0; c < a.n_cols; c++) {
 				const QueryCol &qc = a.cols[c];
 				if (!qc.has_pred) {
+					continue;
+				}
+				if (list_mode) {
+					// the earlier predicates left few rows: this one is tested on the compacted survivors only
+					// (a row costs one field read; a full round costs every row of the block)
+					uint32_t kept = 0;
+					for (uint32_t e0 = 0; e0 < n_list; e0 += 32u) {
+						const uint32_t e = e0 + lane;
+						bool keep = false;
+						uint16_t row = 0;
+						if (e < n_list) {
+							row = my_list[e];
+							const uint64_t v = column_value(st.piece[c], stage, row, qc.type_size, qc.is_signed);
+							keep = qc.is_signed ? ((int64_t)v >= qc.lo && (int64_t)v <= qc.hi)
+							                    : (v >= (uint64_t)qc.lo && v <= (uint64_t)qc.hi);
+						}
+						const uint32_t m = __ballot_sync(0xffffffffu, keep);  // every read of this round is done
+						if (keep) {
+							my_list[kept + __popc(m & ((1u << lane) - 1u))] = row;
+						}
+						kept += __popc(m);
+					}
+					__syncwarp();
+					n_list = kept;
 					continue;
 				}
 				uint32_t off_p = 0;
@@ -649,15 +675,48 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 					__syncwarp();
 					off_p = end_p;
 				}
+				if (a.out_bitmap == nullptr && c + 1 < a.n_cols) {
+					// survivors so far; at <= 25 % of my rows (and within the list) the remaining predicate columns
+					// run on the compacted list
+					const uint32_t g = warp + lane * kQConsumerWarps;
+					const uint32_t word = g < n_groups ? sel[g] : 0u;
+					const uint32_t cnt = __popc(word);
+					uint32_t incl = cnt;
+#pragma unroll
+					for (int d = 1; d < 32; d <<= 1) {
+						const uint32_t v = __shfl_up_sync(0xffffffffu, incl, d);
+						if ((int)lane >= d) {
+							incl += v;
+						}
+					}
+					const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+					const uint32_t my_groups = n_groups > warp ? (n_groups - warp + kQConsumerWarps - 1u) / kQConsumerWarps : 0u;
+					if (total <= kQListCap && total * 4u <= my_groups * 32u) {
+						uint32_t pos = incl - cnt;
+						uint32_t rest = word;
+						while (rest) {
+							const uint32_t bpos = (uint32_t)__ffs((int)rest) - 1u;
+							my_list[pos++] = (uint16_t)(g * 32u + bpos);
+							rest &= rest - 1u;
+						}
+						__syncwarp();
+						n_list = total;
+						list_mode = true;
+					}
+				}
 			}
 
 			// ---- survivors: bitmap out, count, compaction into the warp's list, aggregates on the list ----
-			uint32_t n_list = 0;
 			// sparse selections (Q6 keeps ~2 % of the rows): lane j owns my j-th group (8192 rows = 32 groups per warp),
 			// an exclusive scan of the survivor counts places every lane's rows, each lane then emits its own set bits.
 			// Same list order as the group-at-a-time loop below, which remains for dense selections.
 			uint32_t g_first = warp;
-			{
+			if (list_mode) {
+				if (lane == 0) {
+					n_pass += n_list;
+				}
+				g_first = n_groups;  // the list already holds the survivors of every predicate
+			} else {
 				const uint32_t g = warp + lane * kQConsumerWarps;
 				const uint32_t word = g < n_groups ? sel[g] : 0u;
 				const uint32_t cnt = __popc(word);
