@@ -125,15 +125,18 @@ __global__ void __launch_bounds__(kPointThreads) point_shared_kernel(const SegDe
 			}
 			const uint32_t t32 = target[q];
 			const uint32_t kk = w == 32u ? t32 : (w == 16u ? t32 * 0x00010001u : t32 * 0x01010101u);
+			// "some field of the word equals the target" as a zero-field test of x ^ kk: (t - ones) & ~t & highs is
+			// non-zero iff t has a zero field (a filter: the exact fields are resolved below), three instructions a word
+			const uint32_t ones = w == 16u ? 0x00010001u : 0x01010101u;
+			const uint32_t highs = ones << (w - 1u);
 #pragma unroll
 			for (int u = 0; u < 4; u++) {
 				uint32_t m;
 				if (w == 32u) {
 					m = (x[u].x == kk) | (x[u].y == kk) | (x[u].z == kk) | (x[u].w == kk);
-				} else if (w == 16u) {
-					m = __vcmpeq2(x[u].x, kk) | __vcmpeq2(x[u].y, kk) | __vcmpeq2(x[u].z, kk) | __vcmpeq2(x[u].w, kk);
 				} else {
-					m = __vcmpeq4(x[u].x, kk) | __vcmpeq4(x[u].y, kk) | __vcmpeq4(x[u].z, kk) | __vcmpeq4(x[u].w, kk);
+					const uint32_t t0 = x[u].x ^ kk, t1 = x[u].y ^ kk, t2 = x[u].z ^ kk, t3 = x[u].w ^ kk;
+					m = (((t0 - ones) & ~t0) | ((t1 - ones) & ~t1) | ((t2 - ones) & ~t2) | ((t3 - ones) & ~t3)) & highs;
 				}
 				if (m) {
 					const uint32_t xs[4] = {x[u].x, x[u].y, x[u].z, x[u].w};

@@ -119,6 +119,30 @@ __device__ __forceinline__ uint64_t group_value(const QPiece *pc, const uint8_t 
 	return extend_rt(f + pc[p].min_add, type_size, is_signed);
 }
 
+// predicate of column qc on block row i: field-domain compare on linear narrow pieces, decoded compare otherwise
+__device__ __forceinline__ bool row_passes(const QPiece *pc, const uint8_t *stage, uint32_t i, const QueryCol &qc) {
+	uint32_t p = 0, off = i;
+	const uint32_t c0 = pc[0].cnt;
+	if (off >= c0) {
+		off -= c0;
+		p = 1;
+		const uint32_t c1 = pc[1].cnt;
+		if (off >= c1) {
+			off -= c1;
+			p = 2;
+		}
+	}
+	const QPiece &q = pc[p];
+	const uint32_t w = q.w;
+	const uint32_t bit = q.bit_base + off * w;
+	if (q.linear && w <= 32u && (q.flo >> 32) == 0) {
+		const uint32_t f = read_bits32((const uint32_t *)(stage + q.smem_off), bit) & (0xffffffffu >> (32u - w));
+		return (f - (uint32_t)q.flo) <= (uint32_t)q.span;
+	}
+	const uint64_t v = column_value(pc, stage, i, qc.type_size, qc.is_signed);
+	return qc.is_signed ? ((int64_t)v >= qc.lo && (int64_t)v <= qc.hi) : (v >= (uint64_t)qc.lo && v <= (uint64_t)qc.hi);
+}
+
 struct PieceRes {
 	uint64_t src16;
 	uint64_t min_add;
@@ -564,9 +588,7 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 						uint16_t row = 0;
 						if (e < n_list) {
 							row = my_list[e];
-							const uint64_t v = column_value(st.piece[c], stage, row, qc.type_size, qc.is_signed);
-							keep = qc.is_signed ? ((int64_t)v >= qc.lo && (int64_t)v <= qc.hi)
-							                    : (v >= (uint64_t)qc.lo && v <= (uint64_t)qc.hi);
+							keep = row_passes(st.piece[c], stage, row, qc);
 						}
 						const uint32_t m = __ballot_sync(0xffffffffu, keep);  // every read of this round is done
 						if (keep) {
