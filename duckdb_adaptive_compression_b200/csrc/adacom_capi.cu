@@ -1222,6 +1222,28 @@ static adacom_status run_agg(adacom_column *col, uint64_t b, uint64_t e, int fla
 		LAUNCH(ctx, launch_scan_sum_fields(f, ctx->sm_count, ctx->stream));
 		return ADACOM_OK;
 	}
+	if (mode == kModeFilter) {
+		// field-domain filter kernel when every re-packed payload of the range is <= 32 bits wide (always true for the
+		// 1/2/4-byte types; for the 8-byte types the host mirror decides, raw 8-byte segments stay on decode_kernel)
+		bool narrow = col->t.size <= 4;
+		if (!narrow) {
+			adacom_status st = sync_mirror(col);
+			if (st != ADACOM_OK) {
+				return st;
+			}
+			narrow = true;
+			for (uint64_t g = b; g < e && narrow; g++) {
+				const SegDesc &d = col->h_desc[g];
+				narrow = d.count == 0 || ((d.state & kSegRepacked) && d.width <= 32);
+			}
+		}
+		if (narrow) {
+			LAUNCH(ctx, launch_filter_fields(col->t, col->d_desc, (uint32_t)b, (uint32_t)(e - b), kBlockSize / (uint32_t)col->t.size,
+			                                 col->raw, (flags & ADACOM_LITERAL) ? 1 : 0, op_mask, constant, bitmap32,
+			                                 col->h_desc[b].row_start, device_out, ctx->sm_count, ctx->stream));
+			return ADACOM_OK;
+		}
+	}
 	DecodeArgs a;
 	a.desc = col->d_desc;
 	a.parts = col->d_parts;

@@ -259,6 +259,14 @@ struct Acc96 {
 		    : "+r"(a0), "+r"(a1), "+r"(a2)
 		    : "r"(lo), "r"(hi), "r"(ext));
 	}
+	// + (hi : lo) as a 96-bit two's-complement number
+	__device__ __forceinline__ void add96(uint64_t lo, uint32_t hi) {
+		asm("add.cc.u32 %0, %0, %3;\n\t"
+		    "addc.cc.u32 %1, %1, %4;\n\t"
+		    "addc.u32 %2, %2, %5;"
+		    : "+r"(a0), "+r"(a1), "+r"(a2)
+		    : "r"((uint32_t)lo), "r"((uint32_t)(lo >> 32)), "r"(hi));
+	}
 	__device__ __forceinline__ uint64_t lo64() const { return ((uint64_t)a1 << 32) | a0; }
 	__device__ __forceinline__ uint64_t hi64() const { return (uint64_t)(int64_t)(int32_t)a2; }
 };

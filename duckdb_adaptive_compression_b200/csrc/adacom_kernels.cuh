@@ -161,6 +161,12 @@ cudaError_t launch_encode(TypeInfo t, const SegDesc *desc, const Job *tiles, uin
 cudaError_t launch_fill_splitmix(TypeInfo t, void *raw, uint64_t n, uint64_t seed, uint64_t first_index, uint64_t mask,
                                  cudaStream_t stream);
 
+// fused decode + compare + SUM/COUNT (+ bitmap) in the field domain, for ranges whose re-packed payloads are all
+// <= 32 bits wide (kernels_filter.cu); seg_capacity: upper bound of the values per segment
+cudaError_t launch_filter_fields(TypeInfo t, const SegDesc *desc, uint32_t seg_b, uint32_t n_segs, uint32_t seg_capacity,
+                                 const uint8_t *raw, int literal, uint32_t op_mask, uint64_t constant, uint32_t *bitmap32,
+                                 uint64_t out_row0, Agg *agg, int sm_count, cudaStream_t stream);
+
 // ---- checkpoint image (kernels_checkpoint.cu) ----
 constexpr uint32_t kBlockAllocSize = 262144;  // Storage::BLOCK_ALLOC_SIZE: 8-byte checksum + Storage::BLOCK_SIZE payload
 

@@ -1,0 +1,234 @@
+// kernels_filter.cu -- fused decode + (value <op> constant) + SUM/COUNT (+ selection bitmap) for columns whose live
+// payloads are all <= 32 bits wide, evaluated in the FIELD domain.
+//
+// Reference: ColumnData::Select = scan, then ColumnSegment::FilterSelection -> TemplatedFilterSelection
+// (src/storage/table/column_data.cpp:199-204, src/storage/table/column_segment.cpp:575-658), then the aggregate.
+// decode_kernel<..., filter> does that per value (decode, extend, compare as T, 96-bit add) and is bound by its
+// per-value instruction budget (~400 Gvalues/s).  Here, for a chunk whose values are extend(min) + f without wrap-around
+// (the whole interval [min, min + 2^w - 1] lies inside one sign / truncation zone of T):
+//     value <op> c   <=>   f <op> (c - extend(min))          (a constant outside the interval decides the whole chunk)
+//     SUM(passing)    =    SUM(f) + n * extend(min)
+// so a value costs a funnel shift, a mask, two compares, a select and a 64-bit add.  Chunks that are not linear (raw
+// signed slots, wrap-around frames) take the per-value path inside the same kernel.
+//
+// Job = (segment, chunk of 4096 values): 512 * w payload bytes (16-byte aligned: 64 values are w whole words), staged
+// in shared memory with 16-byte loads; 128 threads, 32 values each, lane = consecutive rows so that a ballot is 32
+// consecutive selection bits.  Algorithmic bytes: the packed payload (+ 1 bit per row for the bitmap).
+#include "adacom_kernels.cuh"
+
+namespace adacom {
+
+namespace {
+
+constexpr int kFiltThreads = 128;  // small CTAs, 8 per SM: a job is a chain of dependent loads (descriptor -> payload)
+constexpr uint32_t kFiltChunk = 4096;                      // values per job
+constexpr uint32_t kFiltStageBytes = kFiltChunk * 32 / 8;  // widest staged chunk (w = 32)
+
+template <int S, bool SIGNED>
+__global__ void __launch_bounds__(kFiltThreads, 8) filter_fields_kernel(const SegDesc *desc, uint32_t seg_b, uint32_t n_segs,
+                                                                        uint32_t chunks_per_seg, const uint8_t *raw,
+                                                                        int literal, uint32_t op_mask, uint64_t constant,
+                                                                        uint32_t *bitmap32, uint64_t out_row0, Agg *agg) {
+	using T = typename UIntOf<S>::type;
+	__shared__ __align__(16) uint32_t stage[kFiltStageBytes / 4 + 4];
+	__shared__ uint64_t red[96];  // block_reduce_agg scratch
+	const uint32_t tid = threadIdx.x, lane = tid & 31u;
+	Acc96 acc;
+	uint32_t n_pass = 0;
+	const uint32_t n_jobs = n_segs * chunks_per_seg;
+	for (uint32_t job = blockIdx.x; job < n_jobs; job += gridDim.x) {
+		const SegDesc *d = desc + seg_b + job / chunks_per_seg;
+		const uint32_t first = (job % chunks_per_seg) * kFiltChunk;
+		const uint32_t count = d->count;
+		if (first >= count) {
+			continue;  // uniform per CTA
+		}
+		const uint32_t cnt = min(kFiltChunk, count - first);
+		const uint32_t state = d->state;
+		const bool repacked = state & kSegRepacked;
+		const uint32_t w = repacked ? d->width : 8u * S;
+		const uint64_t mn = d->min_factor;
+		const uint64_t min_add = (mn != ~0ull && (repacked || literal)) ? mn : 0ull;
+		const uint64_t row0 = d->row_start + first;  // column row of the chunk's first value
+		const uint64_t mask64 = lo_set64(w);
+		const uint64_t e_min = extend_low<S, SIGNED>(min_add);
+		const uint64_t top = min_add + mask64;
+		const uint64_t e_top = extend_low<S, SIGNED>(top);
+		const bool linear = repacked && w <= 32u && top >= min_add && e_top - e_min == mask64 &&
+		                    (SIGNED ? (int64_t)e_min <= (int64_t)e_top : e_min <= e_top);
+		if (repacked && w <= 32u) {
+			// stage the chunk: 512 * w bytes rounded up to 16 (the payload is followed by its alignment gap / arena pad)
+			const uint4 *src = (const uint4 *)(d->packed_ptr + (uint64_t)(first / 64u) * w * 8u);
+			const uint32_t n16 = (cnt * w + 127u) >> 7;
+			__syncthreads();  // the previous chunk has been consumed
+			for (uint32_t j = tid; j < n16; j += kFiltThreads) {
+				((uint4 *)stage)[j] = __ldg(src + j);
+			}
+			if (tid == 0) {
+				stage[n16 * 4] = 0u;  // the funnel's second word behind the last field
+			}
+			__syncthreads();
+		}
+		if (linear) {
+			const bool below = SIGNED ? (int64_t)constant < (int64_t)e_min : constant < e_min;
+			const bool above = SIGNED ? (int64_t)constant > (int64_t)e_top : constant > e_top;
+			const bool p_lt = op_mask & 1u, p_gt = (op_mask >> 2) & 1u;
+			// a constant below the interval: every value is greater; above: every value is smaller
+			const int whole = below ? (p_gt ? 1 : 0) : (above ? (p_lt ? 1 : 0) : 2);
+			if (whole == 0) {
+				continue;  // nothing passes, the bitmap was zeroed by the caller
+			}
+			const uint32_t fc = (uint32_t)(constant - e_min);
+			const uint32_t mask32 = (uint32_t)mask64;
+			// the operator as one inclusive field range [flo, flo + span] (inv: its complement), one compare per value
+			uint32_t flo = 0, span = mask32;
+			bool inv = false, none = false;
+			if (whole == 2) {
+				switch (op_mask & 7u) {
+				case 1u: none = fc == 0u; span = fc - 1u; break;                      // <
+				case 3u: span = fc; break;                                            // <=
+				case 4u: none = fc == mask32; flo = fc + 1u; span = mask32 - flo; break;  // >
+				case 6u: flo = fc; span = mask32 - fc; break;                         // >=
+				case 2u: flo = fc; span = 0u; break;                                  // =
+				case 5u: flo = fc; span = 0u; inv = true; break;                      // <>
+				case 0u: none = true; break;
+				default: break;                                                       // everything passes
+				}
+			}
+			if (none) {
+				continue;
+			}
+			uint64_t fsum = 0;
+			uint32_t n = 0;
+			if (cnt == kFiltChunk && bitmap32 == nullptr) {
+				// full chunk, no bitmap: the distance between a thread's values is kFiltThreads * w bits, whole 32-bit
+				// words, so its funnel shift never changes and the loads sit at fixed strides from one pointer
+				const uint32_t bit0 = tid * w;
+				const uint32_t *p32 = stage + (bit0 >> 5);
+				const uint32_t sh = bit0 & 31u;
+				const uint32_t stride = (uint32_t)kFiltThreads / 32u * w;
+#pragma unroll
+				for (int jj = 0; jj < (int)(kFiltChunk / kFiltThreads); jj++) {
+					const uint32_t f = __funnelshift_r(p32[jj * stride], p32[jj * stride + 1], sh) & mask32;
+					const bool pass = ((f - flo) <= span) != inv;
+					fsum += pass ? (uint64_t)f : 0ull;
+					n += pass ? 1u : 0u;
+				}
+			} else {
+				for (uint32_t base = 0; base < cnt; base += kFiltThreads) {
+					const uint32_t i = base + tid;
+					const bool valid = i < cnt;
+					const uint32_t bit = (valid ? i : 0u) * w;
+					const uint32_t f = __funnelshift_r(stage[bit >> 5], stage[(bit >> 5) + 1], bit) & mask32;
+					const bool pass = valid && (((f - flo) <= span) != inv);
+					fsum += pass ? (uint64_t)f : 0ull;
+					n += pass ? 1u : 0u;
+					if (bitmap32 != nullptr) {
+						const uint32_t ballot = __ballot_sync(0xffffffffu, pass);
+						if (lane == 0 && ballot) {
+							const uint64_t bit0 = row0 - out_row0 + base + (tid & ~31u);
+							const uint32_t sh = (uint32_t)(bit0 & 31u);
+							atomicOr(bitmap32 + (bit0 >> 5), ballot << sh);
+							if (sh) {
+								atomicOr(bitmap32 + (bit0 >> 5) + 1, ballot >> (32u - sh));
+							}
+						}
+					}
+				}
+			}
+			// + fsum + n * extend(min) as a 96-bit two's-complement number
+			const uint64_t plo = e_min * (uint64_t)n;
+			uint64_t phi = __umul64hi(e_min, (uint64_t)n);
+			if (SIGNED && (int64_t)e_min < 0) {
+				phi -= (uint64_t)n;  // signed x unsigned high part
+			}
+			uint64_t lo = plo, hi = phi;
+			add128(lo, hi, fsum, 0ull);
+			acc.add96(lo, (uint32_t)hi);
+			n_pass += n;
+		} else {
+			// per-value path: raw slots (read from the raw arena) or a frame of reference that wraps inside T
+			const T *slots = (const T *)raw + row0;
+			for (uint32_t base = 0; base < cnt; base += kFiltThreads) {
+				const uint32_t i = base + tid;
+				const bool valid = i < cnt;
+				bool pass = false;
+				uint64_t v = 0;
+				if (valid) {
+					uint64_t f;
+					if (repacked && w <= 32u) {
+						const uint32_t bit = i * w;
+						f = (uint64_t)(__funnelshift_r(stage[bit >> 5], stage[(bit >> 5) + 1], bit) & (uint32_t)mask64);
+					} else if (repacked) {
+						// wide payloads are not staged (the host routes such columns to decode_kernel): two words from HBM
+						const uint64_t *words = (const uint64_t *)d->packed_ptr;
+						const uint64_t bit = (uint64_t)(first + i) * w;
+						const uint32_t off = (uint32_t)(bit & 63u);
+						f = __ldg(words + (bit >> 6)) >> off;
+						if (off + w > 64u) {
+							f |= __ldg(words + (bit >> 6) + 1) << (64u - off);
+						}
+						f &= mask64;
+					} else {
+						f = (uint64_t)__ldg(slots + i);
+					}
+					v = extend_low<S, SIGNED>(f + min_add);
+					pass = cmp_passes<SIGNED>(v, constant, op_mask);
+				}
+				if (pass) {
+					acc.add<SIGNED>(v);
+					n_pass++;
+				}
+				if (bitmap32 != nullptr) {
+					const uint32_t ballot = __ballot_sync(0xffffffffu, pass);
+					if (lane == 0 && ballot) {
+						const uint64_t bit0 = row0 - out_row0 + base + (tid & ~31u);
+						const uint32_t sh = (uint32_t)(bit0 & 31u);
+						atomicOr(bitmap32 + (bit0 >> 5), ballot << sh);
+						if (sh) {
+							atomicOr(bitmap32 + (bit0 >> 5) + 1, ballot >> (32u - sh));
+						}
+					}
+				}
+			}
+		}
+	}
+	block_reduce_agg(acc.lo64(), acc.hi64(), (uint64_t)n_pass, red, agg);
+}
+
+template <int S>
+cudaError_t launch_s(bool is_signed, const SegDesc *desc, uint32_t seg_b, uint32_t n_segs, uint32_t cps, const uint8_t *raw,
+                     int literal, uint32_t op_mask, uint64_t constant, uint32_t *bitmap32, uint64_t out_row0, Agg *agg,
+                     int sm_count, cudaStream_t stream) {
+	const uint64_t jobs = (uint64_t)n_segs * cps;
+	const uint32_t resident = (uint32_t)sm_count * 8u;
+	const uint32_t grid = (uint32_t)(jobs < resident ? jobs : resident);
+	if (is_signed) {
+		filter_fields_kernel<S, true><<<grid, kFiltThreads, 0, stream>>>(desc, seg_b, n_segs, cps, raw, literal, op_mask,
+		                                                                 constant, bitmap32, out_row0, agg);
+	} else {
+		filter_fields_kernel<S, false><<<grid, kFiltThreads, 0, stream>>>(desc, seg_b, n_segs, cps, raw, literal, op_mask,
+		                                                                  constant, bitmap32, out_row0, agg);
+	}
+	return cudaGetLastError();
+}
+
+}  // namespace
+
+cudaError_t launch_filter_fields(TypeInfo t, const SegDesc *desc, uint32_t seg_b, uint32_t n_segs, uint32_t seg_capacity,
+                                 const uint8_t *raw, int literal, uint32_t op_mask, uint64_t constant, uint32_t *bitmap32,
+                                 uint64_t out_row0, Agg *agg, int sm_count, cudaStream_t stream) {
+	if (n_segs == 0) {
+		return cudaSuccess;
+	}
+	const uint32_t cps = (seg_capacity + kFiltChunk - 1) / kFiltChunk;
+	switch (t.size) {
+	case 1: return launch_s<1>(t.is_signed, desc, seg_b, n_segs, cps, raw, literal, op_mask, constant, bitmap32, out_row0, agg, sm_count, stream);
+	case 2: return launch_s<2>(t.is_signed, desc, seg_b, n_segs, cps, raw, literal, op_mask, constant, bitmap32, out_row0, agg, sm_count, stream);
+	case 4: return launch_s<4>(t.is_signed, desc, seg_b, n_segs, cps, raw, literal, op_mask, constant, bitmap32, out_row0, agg, sm_count, stream);
+	case 8: return launch_s<8>(t.is_signed, desc, seg_b, n_segs, cps, raw, literal, op_mask, constant, bitmap32, out_row0, agg, sm_count, stream);
+	default: return cudaErrorInvalidValue;
+	}
+}
+
+}  // namespace adacom
