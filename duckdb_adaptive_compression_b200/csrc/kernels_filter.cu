@@ -26,7 +26,7 @@ constexpr uint32_t kFiltStageBytes = kFiltChunk * 32 / 8;  // widest staged chun
 
 template <int S, bool SIGNED>
 __global__ void __launch_bounds__(kFiltThreads, 8) filter_fields_kernel(const SegDesc *desc, uint32_t seg_b, uint32_t n_segs,
-                                                                        uint32_t chunks_per_seg, const uint8_t *raw,
+                                                                        uint32_t cps_shift, const uint8_t *raw,
                                                                         int literal, uint32_t op_mask, uint64_t constant,
                                                                         uint32_t *bitmap32, uint64_t out_row0, Agg *agg) {
 	using T = typename UIntOf<S>::type;
@@ -35,10 +35,10 @@ __global__ void __launch_bounds__(kFiltThreads, 8) filter_fields_kernel(const Se
 	const uint32_t tid = threadIdx.x, lane = tid & 31u;
 	Acc96 acc;
 	uint32_t n_pass = 0;
-	const uint32_t n_jobs = n_segs * chunks_per_seg;
+	const uint32_t n_jobs = n_segs << cps_shift;  // chunks per segment rounded up to a power of two, empty ones skipped
 	for (uint32_t job = blockIdx.x; job < n_jobs; job += gridDim.x) {
-		const SegDesc *d = desc + seg_b + job / chunks_per_seg;
-		const uint32_t first = (job % chunks_per_seg) * kFiltChunk;
+		const SegDesc *d = desc + seg_b + (job >> cps_shift);
+		const uint32_t first = (job & ((1u << cps_shift) - 1u)) * kFiltChunk;
 		const uint32_t count = d->count;
 		if (first >= count) {
 			continue;  // uniform per CTA
@@ -107,12 +107,24 @@ __global__ void __launch_bounds__(kFiltThreads, 8) filter_fields_kernel(const Se
 				const uint32_t *p32 = stage + (bit0 >> 5);
 				const uint32_t sh = bit0 & 31u;
 				const uint32_t stride = (uint32_t)kFiltThreads / 32u * w;
+				if (w <= 26u) {
+					uint32_t s32 = 0;  // 32 fields below 2^26 cannot overflow 32 bits
 #pragma unroll
-				for (int jj = 0; jj < (int)(kFiltChunk / kFiltThreads); jj++) {
-					const uint32_t f = __funnelshift_r(p32[jj * stride], p32[jj * stride + 1], sh) & mask32;
-					const bool pass = ((f - flo) <= span) != inv;
-					fsum += pass ? (uint64_t)f : 0ull;
-					n += pass ? 1u : 0u;
+					for (int jj = 0; jj < (int)(kFiltChunk / kFiltThreads); jj++) {
+						const uint32_t f = __funnelshift_r(p32[jj * stride], p32[jj * stride + 1], sh) & mask32;
+						const bool pass = ((f - flo) <= span) != inv;
+						s32 += pass ? f : 0u;
+						n += pass ? 1u : 0u;
+					}
+					fsum = s32;
+				} else {
+#pragma unroll
+					for (int jj = 0; jj < (int)(kFiltChunk / kFiltThreads); jj++) {
+						const uint32_t f = __funnelshift_r(p32[jj * stride], p32[jj * stride + 1], sh) & mask32;
+						const bool pass = ((f - flo) <= span) != inv;
+						fsum += pass ? (uint64_t)f : 0ull;
+						n += pass ? 1u : 0u;
+					}
 				}
 			} else {
 				for (uint32_t base = 0; base < cnt; base += kFiltThreads) {
@@ -200,14 +212,21 @@ template <int S>
 cudaError_t launch_s(bool is_signed, const SegDesc *desc, uint32_t seg_b, uint32_t n_segs, uint32_t cps, const uint8_t *raw,
                      int literal, uint32_t op_mask, uint64_t constant, uint32_t *bitmap32, uint64_t out_row0, Agg *agg,
                      int sm_count, cudaStream_t stream) {
-	const uint64_t jobs = (uint64_t)n_segs * cps;
+	uint32_t cps_shift = 0;
+	while ((1u << cps_shift) < cps) {
+		cps_shift++;
+	}
+	const uint64_t jobs = (uint64_t)n_segs << cps_shift;
+	if (jobs >= (1ull << 32)) {
+		return cudaErrorInvalidValue;
+	}
 	const uint32_t resident = (uint32_t)sm_count * 8u;
 	const uint32_t grid = (uint32_t)(jobs < resident ? jobs : resident);
 	if (is_signed) {
-		filter_fields_kernel<S, true><<<grid, kFiltThreads, 0, stream>>>(desc, seg_b, n_segs, cps, raw, literal, op_mask,
+		filter_fields_kernel<S, true><<<grid, kFiltThreads, 0, stream>>>(desc, seg_b, n_segs, cps_shift, raw, literal, op_mask,
 		                                                                 constant, bitmap32, out_row0, agg);
 	} else {
-		filter_fields_kernel<S, false><<<grid, kFiltThreads, 0, stream>>>(desc, seg_b, n_segs, cps, raw, literal, op_mask,
+		filter_fields_kernel<S, false><<<grid, kFiltThreads, 0, stream>>>(desc, seg_b, n_segs, cps_shift, raw, literal, op_mask,
 		                                                                  constant, bitmap32, out_row0, agg);
 	}
 	return cudaGetLastError();
