@@ -32,6 +32,10 @@ __global__ void __launch_bounds__(kFiltThreads, 8) filter_fields_kernel(const Se
 	using T = typename UIntOf<S>::type;
 	__shared__ __align__(16) uint32_t stage[kFiltStageBytes / 4 + 4];
 	__shared__ uint64_t red[96];  // block_reduce_agg scratch
+	// selection bits of the chunk at their position inside the output words (the chunk's first row is not 32-aligned):
+	// ballots are OR-ed in here, interior words then leave as plain stores, only the two boundary words (shared with the
+	// neighbouring chunks) as global atomics
+	__shared__ uint32_t bm[kFiltChunk / 32 + 2];
 	const uint32_t tid = threadIdx.x, lane = tid & 31u;
 	Acc96 acc;
 	uint32_t n_pass = 0;
@@ -56,6 +60,15 @@ __global__ void __launch_bounds__(kFiltThreads, 8) filter_fields_kernel(const Se
 		const uint64_t e_top = extend_low<S, SIGNED>(top);
 		const bool linear = repacked && w <= 32u && top >= min_add && e_top - e_min == mask64 &&
 		                    (SIGNED ? (int64_t)e_min <= (int64_t)e_top : e_min <= e_top);
+		const uint64_t rel0 = row0 - out_row0;  // chunk's first row relative to the bitmap
+		const uint32_t bsh = (uint32_t)(rel0 & 31u);
+		if (bitmap32 != nullptr) {
+			__syncthreads();  // the previous chunk's words have been written out
+			for (uint32_t t = tid; t < kFiltChunk / 32 + 2; t += kFiltThreads) {
+				bm[t] = 0u;
+			}
+			__syncthreads();
+		}
 		if (repacked && w <= 32u) {
 			// stage the chunk: 512 * w bytes rounded up to 16 (the payload is followed by its alignment gap / arena pad)
 			const uint4 *src = (const uint4 *)(d->packed_ptr + (uint64_t)(first / 64u) * w * 8u);
@@ -138,11 +151,10 @@ __global__ void __launch_bounds__(kFiltThreads, 8) filter_fields_kernel(const Se
 					if (bitmap32 != nullptr) {
 						const uint32_t ballot = __ballot_sync(0xffffffffu, pass);
 						if (lane == 0 && ballot) {
-							const uint64_t bit0 = row0 - out_row0 + base + (tid & ~31u);
-							const uint32_t sh = (uint32_t)(bit0 & 31u);
-							atomicOr(bitmap32 + (bit0 >> 5), ballot << sh);
-							if (sh) {
-								atomicOr(bitmap32 + (bit0 >> 5) + 1, ballot >> (32u - sh));
+							const uint32_t k = (base + (tid & ~31u)) >> 5;
+							atomicOr(&bm[k], ballot << bsh);
+							if (bsh) {
+								atomicOr(&bm[k + 1], ballot >> (32u - bsh));
 							}
 						}
 					}
@@ -194,12 +206,26 @@ __global__ void __launch_bounds__(kFiltThreads, 8) filter_fields_kernel(const Se
 				if (bitmap32 != nullptr) {
 					const uint32_t ballot = __ballot_sync(0xffffffffu, pass);
 					if (lane == 0 && ballot) {
-						const uint64_t bit0 = row0 - out_row0 + base + (tid & ~31u);
-						const uint32_t sh = (uint32_t)(bit0 & 31u);
-						atomicOr(bitmap32 + (bit0 >> 5), ballot << sh);
-						if (sh) {
-							atomicOr(bitmap32 + (bit0 >> 5) + 1, ballot >> (32u - sh));
+						const uint32_t k = (base + (tid & ~31u)) >> 5;
+						atomicOr(&bm[k], ballot << bsh);
+						if (bsh) {
+							atomicOr(&bm[k + 1], ballot >> (32u - bsh));
 						}
+					}
+				}
+			}
+		}
+		if (bitmap32 != nullptr) {
+			__syncthreads();  // every ballot of the chunk is in bm
+			const uint32_t words = (bsh + cnt + 31u) >> 5;
+			uint32_t *dst = bitmap32 + (rel0 >> 5);
+			for (uint32_t t = tid; t < words; t += kFiltThreads) {
+				const uint32_t v = bm[t];
+				if (v) {
+					if (t == 0 || t == words - 1u) {
+						atomicOr(dst + t, v);
+					} else {
+						dst[t] = v;
 					}
 				}
 			}
