@@ -35,6 +35,14 @@ class Agg(C.Structure):
     _fields_ = [("sum_lo", C.c_uint64), ("sum_hi", C.c_uint64), ("count", C.c_uint64), ("reserved", C.c_uint64)]
 
 
+class Pred(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("op", C.c_int32), ("constant", C.c_int64)]
+
+
+PRED_COMPARE, PRED_IS_NULL, PRED_IS_NOT_NULL = 0, 1, 2
+CONJ_AND, CONJ_OR = 0, 1
+
+
 class ScanTerm(C.Structure):
     _fields_ = [("col", C.c_void_p), ("has_predicate", C.c_int32), ("reserved", C.c_int32), ("lo", C.c_int64),
                 ("hi", C.c_int64)]
@@ -102,6 +110,8 @@ _PROTOTYPES = {
     "adacom_scan_sum": (_i, [_vp, _u64, _u64, _i, C.POINTER(Agg)]),
     "adacom_scan_sum_async": (_i, [_vp, _u64, _u64, _i, _vp]),
     "adacom_scan_filter": (_i, [_vp, _u64, _u64, _i, _i, C.c_int64, C.POINTER(Agg), _vp]),
+    "adacom_scan_select": (_i, [_vp, _u64, _u64, _i, _vp, _u32, _i, _vp, _i, _vp, _vp, C.POINTER(Agg)]),
+    "adacom_scan_sum_valid": (_i, [_vp, _u64, _u64, _i, _vp, _i, C.POINTER(Agg)]),
     "adacom_point_filter_batch": (_i, [_vp, _u64, _vp, _vp, _i, _vp, _vp]),
     "adacom_scan_columns": (_i, [_vp, _vp, _u32, _vp, _u32, _u64, _u64, _i, _vp, _vp, _vp]),
     "adacom_scan_columns_async": (_i, [_vp, _vp, _u32, _vp, _u32, _u64, _u64, _i, _vp, _vp, _vp]),

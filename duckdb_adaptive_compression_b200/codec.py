@@ -425,6 +425,39 @@ class Column:
                                                    C.c_void_p(device_bitmap) if device_bitmap else None))
         return _agg_to_py(a, self.signed)
 
+    def scan_select(self, preds, conj: int = 0, validity=None, seg_begin=0, seg_end=None, flags=0,
+                    bitmap_in: int | None = None, bitmap_out: int | None = None, validity_on_device: bool = False):
+        """adacom_scan_select: preds = list of ("cmp", op, constant) | ("is_null",) | ("is_not_null",); conj 0 = AND,
+        1 = OR; validity = numpy uint64 words of the whole column (or a device pointer with validity_on_device).
+        Returns (AggResult over the selected valid rows with count = selected rows, selected valid rows)."""
+        from ._capi import Pred
+        b, e = self._range(seg_begin, seg_end)
+        arr = (Pred * max(len(preds), 1))()
+        for i, p in enumerate(preds):
+            if p[0] == "cmp":
+                arr[i].kind, arr[i].op, arr[i].constant = 0, p[1], _wrap_i64(int(p[2]) & (2**64 - 1))
+            else:
+                arr[i].kind = 1 if p[0] == "is_null" else 2
+        a = Agg()
+        if validity is None:
+            vp = None
+        elif validity_on_device:
+            vp = C.c_void_p(int(validity))
+        else:
+            assert validity.dtype == np.uint64 and validity.flags.c_contiguous
+            vp = _np_ptr(validity)
+        self.ctx.check(self.lib.adacom_scan_select(self.h, b, e, flags, arr, len(preds), conj, vp,
+                                                   1 if validity_on_device else 0,
+                                                   C.c_void_p(bitmap_in) if bitmap_in else None,
+                                                   C.c_void_p(bitmap_out) if bitmap_out else None, C.byref(a)))
+        return _agg_to_py(a, self.signed), int(a.reserved)
+
+    def scan_sum_valid(self, validity, seg_begin=0, seg_end=None, flags=0):
+        b, e = self._range(seg_begin, seg_end)
+        a = Agg()
+        self.ctx.check(self.lib.adacom_scan_sum_valid(self.h, b, e, flags, _np_ptr(validity), 0, C.byref(a)))
+        return _agg_to_py(a, self.signed), int(a.reserved)
+
     def point_filter_batch(self, seg_idx, constants, flags=0):
         seg_idx = np.ascontiguousarray(seg_idx, dtype=np.uint32)
         constants = np.ascontiguousarray(constants, dtype=np.int64)

@@ -1308,6 +1308,85 @@ extern "C" adacom_status adacom_scan_filter(adacom_column *col, uint64_t seg_beg
 	return ADACOM_OK;
 }
 
+extern "C" adacom_status adacom_scan_select(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags,
+                                            const adacom_pred *preds, uint32_t n_preds, adacom_conj conj,
+                                            const uint64_t *validity, int validity_on_device,
+                                            const uint64_t *device_bitmap_in, uint64_t *device_bitmap_out,
+                                            adacom_agg *out) {
+	if (!range_ok(col, seg_begin, seg_end) || !out || n_preds > ADACOM_MAX_PREDS || (n_preds && !preds) ||
+	    ((int)conj != ADACOM_CONJ_AND && (int)conj != ADACOM_CONJ_OR)) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_scan_select: bad arguments");
+	}
+	adacom_ctx *ctx = col->ctx;
+	SelectArgs a;
+	for (uint32_t p = 0; p < n_preds; p++) {
+		const adacom_pred &pr = preds[p];
+		if (pr.kind < ADACOM_PRED_COMPARE || pr.kind > ADACOM_PRED_IS_NOT_NULL ||
+		    (pr.kind == ADACOM_PRED_COMPARE && (pr.op < 0 || pr.op > 5))) {
+			return fail(ctx, ADACOM_ERR_INVALID, "adacom_scan_select: unknown predicate kind / comparison");
+		}
+		a.preds[p].kind = (uint32_t)pr.kind;
+		a.preds[p].op_mask = pr.kind == ADACOM_PRED_COMPARE ? cmp_mask_for_op(pr.op) : 0u;
+		a.preds[p].constant = (uint64_t)pr.constant;
+	}
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	const uint64_t rows = range_rows(col, seg_begin, seg_end);
+	if (device_bitmap_out && rows) {
+		CK(ctx, cudaMemsetAsync(device_bitmap_out, 0, ((rows + 63) / 64) * 8, ctx->stream));
+	}
+	CK(ctx, cudaMemsetAsync(ctx->d_agg, 0, sizeof(Agg), ctx->stream));
+	uint64_t *d_validity = nullptr;
+	if (rows) {
+		if (validity) {
+			if (validity_on_device) {
+				d_validity = const_cast<uint64_t *>(validity);
+			} else {
+				// only the words the range touches travel; the kernel indexes by column row
+				const uint64_t r0 = col->h_desc[seg_begin].row_start;
+				const uint64_t w0 = r0 >> 6, w1 = (r0 + rows + 63) >> 6;
+				uint64_t *d_part = nullptr;
+				CK(ctx, cudaMallocAsync((void **)&d_part, (w1 - w0) * 8, ctx->stream));
+				CK(ctx, cudaMemcpyAsync(d_part, validity + w0, (w1 - w0) * 8, cudaMemcpyHostToDevice, ctx->stream));
+				d_validity = d_part - w0;
+			}
+		}
+		a.desc = col->d_desc;
+		a.jobs = col->d_tiles + col->tile_first[seg_begin];
+		a.n_jobs = col->tile_first[seg_end] - col->tile_first[seg_begin];
+		a.raw = col->raw;
+		a.literal = (flags & ADACOM_LITERAL) ? 1 : 0;
+		a.n_preds = n_preds;
+		a.conj_or = conj == ADACOM_CONJ_OR ? 1u : 0u;
+		a.validity = d_validity;
+		a.in_bitmap = device_bitmap_in;
+		a.out_bitmap32 = (uint32_t *)device_bitmap_out;
+		a.out_row0 = col->h_desc[seg_begin].row_start;
+		a.agg = ctx->d_agg;
+		LAUNCH(ctx, launch_select(col->t, a, ctx->sm_count, ctx->stream));
+		if (validity && !validity_on_device) {
+			CK(ctx, cudaFreeAsync(d_validity + (col->h_desc[seg_begin].row_start >> 6), ctx->stream));
+		}
+	}
+	CK(ctx, cudaMemcpyAsync(ctx->h_agg, ctx->d_agg, sizeof(Agg), cudaMemcpyDeviceToHost, ctx->stream));
+	CK(ctx, cudaStreamSynchronize(ctx->stream));
+	memcpy(out, ctx->h_agg, sizeof(Agg));
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_scan_sum_valid(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags,
+                                               const uint64_t *validity, int validity_on_device, adacom_agg *out) {
+	if (!validity) {
+		// mask.AllValid(): the width-specialised kernel
+		adacom_status st = adacom_scan_sum(col, seg_begin, seg_end, flags, out);
+		if (st == ADACOM_OK) {
+			out->reserved = out->count;
+		}
+		return st;
+	}
+	return adacom_scan_select(col, seg_begin, seg_end, flags, nullptr, 0, ADACOM_CONJ_AND, validity, validity_on_device,
+	                          nullptr, nullptr, out);
+}
+
 extern "C" adacom_status adacom_point_filter_batch(adacom_column *col, uint64_t n_queries, const uint32_t *seg_idx,
                                                    const int64_t *constants, int flags, uint64_t *out_count,
                                                    uint64_t *out_first_row) {

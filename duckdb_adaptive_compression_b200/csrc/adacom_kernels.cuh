@@ -167,6 +167,31 @@ cudaError_t launch_filter_fields(TypeInfo t, const SegDesc *desc, uint32_t seg_b
                                  const uint8_t *raw, int literal, uint32_t op_mask, uint64_t constant, uint32_t *bitmap32,
                                  uint64_t out_row0, Agg *agg, int sm_count, cudaStream_t stream);
 
+// ---- general single-column table filter (kernels_select.cu): conjunction of comparisons / IS [NOT] NULL, validity
+// mask, selection bitmap in / out; per-value decode, any width
+constexpr uint32_t kSelectMaxPreds = 8;
+struct SelectPred {
+	uint32_t kind;       // 0 comparison, 1 IS NULL, 2 IS NOT NULL
+	uint32_t op_mask;    // cmp_mask_for_op
+	uint64_t constant;   // sign/zero-extended T value
+};
+struct SelectArgs {
+	const SegDesc *desc = nullptr;
+	const Job *jobs = nullptr;             // 2048-value tiles of the segment range (static tile table)
+	uint32_t n_jobs = 0;
+	const uint8_t *raw = nullptr;
+	int literal = 0;
+	uint32_t n_preds = 0;
+	uint32_t conj_or = 0;
+	SelectPred preds[kSelectMaxPreds];
+	const uint64_t *validity = nullptr;    // column-wide validity words (bit = column row), device; nullptr = all valid
+	const uint64_t *in_bitmap = nullptr;   // incoming selection, bit (row - out_row0)
+	uint32_t *out_bitmap32 = nullptr;      // resulting selection (zeroed by the caller)
+	uint64_t out_row0 = 0;
+	Agg *agg = nullptr;                    // sum over selected valid rows, count = selected rows, reserved = selected valid rows
+};
+cudaError_t launch_select(TypeInfo t, const SelectArgs &args, int sm_count, cudaStream_t stream);
+
 // ---- checkpoint image (kernels_checkpoint.cu) ----
 constexpr uint32_t kBlockAllocSize = 262144;  // Storage::BLOCK_ALLOC_SIZE: 8-byte checksum + Storage::BLOCK_SIZE payload
 

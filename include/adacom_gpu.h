@@ -110,7 +110,7 @@ typedef struct {
 	uint64_t sum_lo;
 	uint64_t sum_hi;
 	uint64_t count;
-	uint64_t reserved;
+	uint64_t reserved;     /* adacom_scan_select / adacom_scan_sum_valid: selected rows that are not NULL; else 0 */
 } adacom_agg;
 
 typedef struct adacom_ctx adacom_ctx;
@@ -222,6 +222,44 @@ adacom_status adacom_scan_sum_async(adacom_column *col, uint64_t seg_begin, uint
  * (1 bit per row of the range, bit r - row_start(seg_begin); device pointer, zeroed by the call). */
 adacom_status adacom_scan_filter(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags, adacom_cmp op,
                                  int64_t constant, adacom_agg *out, uint64_t *device_bitmap);
+/* NULL semantics of the two fused single-column calls above: they take no validity mask and treat every slot as a
+ * value -- a NULL row (whose slot holds NullValue<T>() = numeric_limits<T>::min(), succinct.cpp:288-292) would enter
+ * SUM / COUNT.  For nullable columns, IS [NOT] NULL, OR-conjunctions and selection refinement use adacom_scan_select /
+ * adacom_scan_sum_valid below. */
+
+/* ---- table filter on one column: ColumnSegment::FilterSelection (column_segment.cpp:575-683, 685-844) -------------- */
+typedef enum {
+	ADACOM_PRED_COMPARE = 0,     /* TableFilterType::CONSTANT_COMPARISON: value <op> constant, NULL rows never pass */
+	ADACOM_PRED_IS_NULL = 1,     /* TableFilterType::IS_NULL (TemplatedNullSelection<true>) */
+	ADACOM_PRED_IS_NOT_NULL = 2  /* TableFilterType::IS_NOT_NULL */
+} adacom_pred_kind;
+typedef enum {
+	ADACOM_CONJ_AND = 0,         /* TableFilterType::CONJUNCTION_AND (column_segment.cpp:717-723) */
+	ADACOM_CONJ_OR = 1           /* TableFilterType::CONJUNCTION_OR  (column_segment.cpp:688-716) */
+} adacom_conj;
+typedef struct {
+	int32_t kind;                /* adacom_pred_kind */
+	int32_t op;                  /* adacom_cmp (ADACOM_PRED_COMPARE only) */
+	int64_t constant;            /* compared as the column's type T */
+} adacom_pred;
+#define ADACOM_MAX_PREDS 8
+/* Fused decode + FilterSelection + aggregate over [seg_begin, seg_end):
+ *   selected(row) = conj over preds[0 .. n_preds) (n_preds == 0: every row) AND bit(row) of device_bitmap_in (the
+ *                   incoming selection vector `sel`; NULL = all rows)
+ *   validity: DuckDB validity words for the WHOLE column (bit i = column row i valid; same convention as
+ *             adacom_analyze), device or host pointer per validity_on_device; NULL = all valid (mask.AllValid()).
+ *   out->count    = selected rows (approved_tuple_count), out->reserved = selected rows that are valid (COUNT(col)),
+ *   out->sum      = SUM over the selected valid rows (DuckDB's aggregates skip NULLs),
+ *   device_bitmap_out (optional, zeroed by the call): the new selection, bit (row - row_start(seg_begin)).
+ * Nested filters (AND of ORs) chain calls through the bitmaps, like the recursion of FilterSelection. */
+adacom_status adacom_scan_select(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags,
+                                 const adacom_pred *preds, uint32_t n_preds, adacom_conj conj, const uint64_t *validity,
+                                 int validity_on_device, const uint64_t *device_bitmap_in, uint64_t *device_bitmap_out,
+                                 adacom_agg *out);
+/* NULL-aware fused decode + SUM: sum / reserved over the valid rows, count = all rows of the range */
+adacom_status adacom_scan_sum_valid(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags,
+                                    const uint64_t *validity, int validity_on_device, adacom_agg *out);
+
 /* batch of point filters (the Zipf look-up benchmarks): query q scans segment seg_idx[q] for
  * value == constants[q]; out_count[q] = matches, out_first_row[q] = first matching row in the segment
  * (UINT64_MAX when none).  All four arrays are host pointers. */

@@ -53,6 +53,10 @@ class _BenchResult(C.Structure):
                 ("packed_bytes", C.c_uint64)]
 
 
+class _Pred(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("op", C.c_int32), ("constant", C.c_int64)]
+
+
 class _Sum128(C.Structure):
     _fields_ = [("lo", C.c_uint64), ("hi", C.c_uint64), ("count", C.c_uint64)]
 
@@ -114,6 +118,8 @@ class Oracle:
             f("segment_sum", None, [C.c_void_p, C.c_int, C.POINTER(_Sum128)])
             f("segment_filter", None, [C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.POINTER(_Sum128), C.c_void_p])
             f("fetch_row", None, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_int])
+            f("segment_select", None, [C.c_void_p, C.c_int, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_uint64,
+                                       C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(_Sum128), C.POINTER(C.c_uint64)])
 
     def _f(self, name, restype, argtypes):
         fn = getattr(self.lib, self.p + name)
@@ -257,6 +263,26 @@ class OracleSegment:
         self.o._segment_filter(self.h, flags, op, constant & 0xFFFFFFFFFFFFFFFF, C.byref(r),
                                _ptr(bm) if bm is not None else None)
         return ((r.hi << 64) | r.lo), int(r.count), bm
+
+    def select(self, preds, conj: int = 0, validity: np.ndarray | None = None, validity_row0: int = 0,
+               bitmap_in: np.ndarray | None = None, bitmap_out: np.ndarray | None = None, bitmap_row0: int = 0,
+               flags: int = 0):
+        """FilterSelection + NULL-skipping aggregate.  preds: ("cmp", op, constant) | ("is_null",) | ("is_not_null",).
+        Returns (sum, selected rows, selected valid rows); bitmap_out (uint64 words) is OR-ed into."""
+        arr = (_Pred * max(len(preds), 1))()
+        for i, p in enumerate(preds):
+            if p[0] == "cmp":
+                c = int(p[2]) & 0xFFFFFFFFFFFFFFFF
+                arr[i].kind, arr[i].op, arr[i].constant = 0, p[1], c - (1 << 64) if c >= 1 << 63 else c
+            else:
+                arr[i].kind = 1 if p[0] == "is_null" else 2
+        r = _Sum128()
+        nv = C.c_uint64()
+        self.o._segment_select(self.h, flags, arr, len(preds), conj, _ptr(validity) if validity is not None else None,
+                               validity_row0, _ptr(bitmap_in) if bitmap_in is not None else None,
+                               _ptr(bitmap_out) if bitmap_out is not None else None, bitmap_row0, C.byref(r),
+                               C.byref(nv))
+        return ((r.hi << 64) | r.lo), int(r.count), int(nv.value)
 
     def fetch_row(self, row_id: int, flags: int = 0):
         out = np.zeros(1, dtype=self.dtype)

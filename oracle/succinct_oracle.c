@@ -520,6 +520,95 @@ void orc_segment_filter(const orc_segment *s, int flags, int op, uint64_t consta
 	}
 }
 
+/* ColumnSegment::FilterSelection restated over one segment, vector by vector (column_segment.cpp:685-844):
+ * the selection vector `sel` is refined child by child (CONJUNCTION_AND, :717-723) or the children's results are
+ * united (CONJUNCTION_OR, :688-716); CONSTANT_COMPARISON = TemplatedFilterSelection (:575-586: a row passes when
+ * `(!HAS_NULL || mask.RowIsValid(idx)) && OP(vec[idx], constant)`), IS_NULL / IS_NOT_NULL = TemplatedNullSelection
+ * (:660-683).  Afterwards the aggregate DuckDB runs above the scan: SUM / COUNT(col) over the selected rows that are
+ * valid, COUNT(*) = approved_tuple_count. */
+static uint32_t select_child(const orc_segment *s, const uint8_t *vec, const orc_pred *p, const uint32_t *sel, uint32_t n,
+                             const uint64_t *validity, uint64_t vrow0, uint32_t *result_sel) {
+	uint32_t m = 0;
+	for (uint32_t i = 0; i < n; i++) {
+		uint32_t idx = sel[i];
+		int valid = 1;
+		if (validity) {
+			uint64_t r = vrow0 + idx;
+			valid = (int)((validity[r >> 6] >> (r & 63)) & 1);
+		}
+		int pass;
+		if (p->kind == ORC_PRED_COMPARE) {
+			uint64_t v = extend_T(vec + (uint64_t)idx * s->type_size, s->type_size, s->is_signed);
+			pass = valid && compare_T(v, (uint64_t)p->constant, p->op, s->is_signed);
+		} else {
+			pass = valid != (p->kind == ORC_PRED_IS_NULL);
+		}
+		if (pass) {
+			result_sel[m++] = idx;
+		}
+	}
+	return m;
+}
+
+void orc_segment_select(const orc_segment *s, int flags, const orc_pred *preds, uint32_t n_preds, int conj_or,
+                        const uint64_t *validity, uint64_t validity_row0, const uint64_t *bitmap_in,
+                        uint64_t *bitmap_out, uint64_t bitmap_row0, orc_sum128 *out, uint64_t *valid_count) {
+	uint8_t buf[ORC_VECTOR_SIZE * 8];
+	static __thread uint32_t sel[ORC_VECTOR_SIZE], tmp[ORC_VECTOR_SIZE], res[ORC_VECTOR_SIZE];
+	static __thread uint8_t seen[ORC_VECTOR_SIZE];
+	memset(out, 0, sizeof(*out));
+	*valid_count = 0;
+	for (uint64_t start = 0; start < s->count; start += ORC_VECTOR_SIZE) {
+		uint32_t n = (uint32_t)(s->count - start < ORC_VECTOR_SIZE ? s->count - start : ORC_VECTOR_SIZE);
+		orc_scan_partial(s, start, n, buf, 0, flags);
+		/* incoming selection */
+		uint32_t approved = 0;
+		for (uint32_t i = 0; i < n; i++) {
+			uint64_t r = bitmap_row0 + start + i;
+			if (!bitmap_in || ((bitmap_in[r >> 6] >> (r & 63)) & 1)) {
+				sel[approved++] = i;
+			}
+		}
+		uint64_t vrow0 = validity_row0 + start;
+		if (n_preds > 0 && !conj_or) {
+			for (uint32_t p = 0; p < n_preds; p++) {
+				approved = select_child(s, buf, &preds[p], sel, approved, validity, vrow0, tmp);
+				memcpy(sel, tmp, approved * sizeof(uint32_t));
+			}
+		} else if (n_preds > 0) {
+			uint32_t total = 0;
+			memset(seen, 0, sizeof(seen));
+			for (uint32_t p = 0; p < n_preds; p++) {
+				uint32_t m = select_child(s, buf, &preds[p], sel, approved, validity, vrow0, tmp);
+				for (uint32_t i = 0; i < m; i++) {
+					if (!seen[tmp[i]]) { /* the reference de-duplicates with a linear search, :701-711 */
+						seen[tmp[i]] = 1;
+						res[total++] = tmp[i];
+					}
+				}
+			}
+			memcpy(sel, res, total * sizeof(uint32_t));
+			approved = total;
+		}
+		for (uint32_t i = 0; i < approved; i++) {
+			uint32_t idx = sel[i];
+			uint64_t r = vrow0 + idx;
+			int valid = !validity || ((validity[r >> 6] >> (r & 63)) & 1);
+			out->count++;
+			if (valid) {
+				uint64_t c = out->count;
+				sum128_add(out, extend_T(buf + (uint64_t)idx * s->type_size, s->type_size, s->is_signed), s->is_signed);
+				out->count = c;
+				(*valid_count)++;
+			}
+			if (bitmap_out) {
+				uint64_t b = bitmap_row0 + start + idx;
+				bitmap_out[b >> 6] |= 1ULL << (b & 63);
+			}
+		}
+	}
+}
+
 /* ------------------------------------------------------------------------------------------- */
 /* Timed CPU baseline: the reference's loop structure, one segment per task, T threads          */
 /* ------------------------------------------------------------------------------------------- */

@@ -119,6 +119,19 @@ void orc_segment_sum(const orc_segment *s, int flags, orc_sum128 *out);
 void orc_segment_filter(const orc_segment *s, int flags, int op, uint64_t constant, orc_sum128 *out,
                         uint64_t *bitmap_words);
 
+/* general table filter on one column (ColumnSegment::FilterSelection, column_segment.cpp:685-844) + NULL-skipping
+ * aggregate: conjunction (AND / OR) of comparisons, IS NULL, IS NOT NULL over an incoming selection.
+ * validity / bitmaps: bit (row0 + segment row); NULL pointers = all valid / all selected / no output.
+ * out->count = selected rows, *valid_count = selected valid rows, out->lo/hi = SUM over the selected valid rows */
+enum { ORC_PRED_COMPARE = 0, ORC_PRED_IS_NULL = 1, ORC_PRED_IS_NOT_NULL = 2 };
+typedef struct {
+	int32_t kind, op;
+	int64_t constant;
+} orc_pred;
+void orc_segment_select(const orc_segment *s, int flags, const orc_pred *preds, uint32_t n_preds, int conj_or,
+                        const uint64_t *validity, uint64_t validity_row0, const uint64_t *bitmap_in,
+                        uint64_t *bitmap_out, uint64_t bitmap_row0, orc_sum128 *out, uint64_t *valid_count);
+
 /* ---- timed CPU baseline: one task per segment, T pthreads, segments dealt round-robin ---- */
 typedef struct {
 	double analyze_s, encode_s, scan_s, sum_s, uncompact_s; /* wall seconds, max over threads */
