@@ -13,10 +13,14 @@
 #include "duckdb/storage/table/column_data_checkpointer.hpp"
 #include "duckdb/storage/table/column_segment.hpp"
 #include "duckdb/storage/table/scan_state.hpp"
+#include "duckdb/storage/table/row_group.hpp"
 
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
+#include <string>
+#include <vector>
 
 namespace duckdb {
 
@@ -25,16 +29,57 @@ namespace {
 //===--------------------------------------------------------------------===//
 // Runtime: one codec context per process (one GPU), errors -> the reference's two exception types
 //===--------------------------------------------------------------------===//
-adacom_ctx *GpuContext() {
-	static std::once_flag once;
-	static adacom_ctx *ctx = nullptr;
-	static adacom_status status = ADACOM_OK;
-	std::call_once(once, [] { status = adacom_ctx_create(/*device=*/0, &ctx); });
-	if (status != ADACOM_OK) {
-		// no CPU fallback: without the GPU library the codec is unavailable, loudly
-		throw InternalException("succinct GPU codec unavailable: %s", adacom_last_error(nullptr));
+//! A pool of codec contexts: ADACOM_DEVICES GPUs (default 1) x ADACOM_STREAMS contexts per GPU (default 4).  Every
+//! context owns its stream and serialises only its own calls, so DuckDB's scan workers (one row group per task,
+//! row_group_collection.cpp:119-153) run concurrently.  Row group g lives on GPU g mod G: all segments of a
+//! row group are on the same device, nothing moves between GPUs.
+struct GpuRuntime {
+	std::vector<adacom_ctx *> contexts; // [device * streams + k]
+	idx_t devices = 1, streams = 4;
+	adacom_status status = ADACOM_OK;
+	std::string error;
+
+	GpuRuntime() {
+		if (const char *env = getenv("ADACOM_DEVICES")) {
+			devices = MaxValue<idx_t>(1, (idx_t)atoi(env));
+		}
+		if (const char *env = getenv("ADACOM_STREAMS")) {
+			streams = MaxValue<idx_t>(1, (idx_t)atoi(env));
+		}
+		idx_t first = 0;
+		if (const char *env = getenv("ADACOM_FIRST_DEVICE")) {
+			first = (idx_t)atoi(env);
+		}
+		for (idx_t d = 0; d < devices && status == ADACOM_OK; d++) {
+			for (idx_t k = 0; k < streams && status == ADACOM_OK; k++) {
+				adacom_ctx *ctx = nullptr;
+				status = adacom_ctx_create((int)(first + d), &ctx);
+				if (status == ADACOM_OK) {
+					contexts.push_back(ctx);
+				} else {
+					error = adacom_last_error(nullptr);
+				}
+			}
+		}
 	}
-	return ctx;
+};
+
+GpuRuntime &Runtime() {
+	static GpuRuntime runtime;
+	if (runtime.status != ADACOM_OK) {
+		// no CPU fallback: without the GPU library / device the codec is unavailable, loudly
+		throw InternalException("succinct GPU codec unavailable: %s", runtime.error);
+	}
+	return runtime;
+}
+
+//! context of a segment: device = row group mod G, stream slot spread over the segments of the device
+adacom_ctx *GpuContextFor(idx_t row_start) {
+	auto &rt = Runtime();
+	idx_t row_group = row_start / RowGroup::ROW_GROUP_SIZE;
+	idx_t device = row_group % rt.devices;
+	idx_t slot = (row_start / 32768) % rt.streams;
+	return rt.contexts[device * rt.streams + slot];
 }
 
 void Check(adacom_status st, const char *what) {
@@ -44,7 +89,7 @@ void Check(adacom_status st, const char *what) {
 	if (st == ADACOM_ERR_NOMEM) {
 		throw std::bad_alloc(); // sdsl memory_management.hpp:326-329
 	}
-	throw InternalException("succinct GPU codec, %s: %s", what, adacom_last_error(GpuContext()));
+	throw InternalException("succinct GPU codec, %s failed with status %d", what, (int)st);
 }
 
 adacom_ptype GpuTypeOf(PhysicalType type) {
@@ -67,12 +112,20 @@ struct SuccinctGpuSegmentState : public CompressedSegmentState {
 		}
 	}
 
+	//! the context (GPU + stream) this segment lives on
+	adacom_ctx *ctx = nullptr;
 	//! one-segment device column (raw slots and, once compacted, the packed payload)
 	adacom_column *column = nullptr;
-	//! the slot-width array of an open segment (what succinct_vec holds in the reference, column_segment.cpp:101-105)
+	//! the slot-width array of an open segment (what succinct_vec holds in the reference, column_segment.cpp:101-105);
+	//! released once the segment is compacted on the device
 	unique_ptr<data_t[]> slots;
+	//! validity words of the slots (bit i = row i valid), allocated when the first NULL is appended: the reference
+	//! keeps NULL rows out of min/max (succinct.cpp:284-292), so adacom_analyze needs the mask
+	std::vector<uint64_t> validity;
 	//! values of `slots` that are already on the device
 	idx_t resident = 0;
+	//! ColumnSegment::GetDataSize() of the device state (0 = not known yet)
+	idx_t data_size = 0;
 	//! serialises upload / re-encode against concurrent scans (the reference's bit_compression_lock)
 	std::mutex lock;
 };
@@ -96,18 +149,24 @@ void EnsureResident(ColumnSegment &segment, SuccinctGpuSegmentState &state) {
 	}
 	uint64_t count = segment.count;
 	auto capacity = (uint32_t)(segment.SegmentSize() / segment.type_size);
-	Check(adacom_column_create(GpuContext(), GpuTypeOf(segment.type.InternalType()), 1, &count, capacity, &state.column),
+	if (!state.ctx) {
+		state.ctx = GpuContextFor(segment.start);
+	}
+	Check(adacom_column_create(state.ctx, GpuTypeOf(segment.type.InternalType()), 1, &count, capacity, &state.column),
 	      "column_create");
 	if (count) {
+		if (!state.slots) {
+			throw InternalException("succinct GPU codec: segment has neither host slots nor a device column");
+		}
 		Check(adacom_column_upload_raw(state.column, state.slots.get(), 0, count), "upload");
 	}
 	state.resident = count;
+	state.data_size = 0;
 }
 
 unique_ptr<CompressedSegmentState> SuccinctGpuInitSegment(ColumnSegment &segment, block_id_t block_id) {
-	auto state = make_unique<SuccinctGpuSegmentState>();
-	state->slots = unique_ptr<data_t[]>(new data_t[segment.SegmentSize()]);
-	return move(state);
+	// the slot array is allocated by the first append (scan-only segments never need one)
+	return make_unique<SuccinctGpuSegmentState>();
 }
 
 //===--------------------------------------------------------------------===//
@@ -209,10 +268,52 @@ void SuccinctGpuFinalizeCompress(CompressionState &state_p) {
 //===--------------------------------------------------------------------===//
 // Scan: one batched decode of the segment per scan state, then 2048-value slices
 //===--------------------------------------------------------------------===//
+//! pinned host buffers for the per-segment decode (cudaHostAlloc is expensive: keep them)
+struct PinnedPool {
+	std::mutex lock;
+	std::vector<std::pair<data_ptr_t, idx_t>> free_list;
+
+	data_ptr_t Get(adacom_ctx *ctx, idx_t bytes, idx_t &capacity) {
+		{
+			std::lock_guard<std::mutex> guard(lock);
+			for (idx_t i = 0; i < free_list.size(); i++) {
+				if (free_list[i].second >= bytes) {
+					auto entry = free_list[i];
+					free_list[i] = free_list.back();
+					free_list.pop_back();
+					capacity = entry.second;
+					return entry.first;
+				}
+			}
+		}
+		void *ptr = nullptr;
+		capacity = MaxValue<idx_t>(bytes, Storage::BLOCK_ALLOC_SIZE);
+		Check(adacom_host_alloc(ctx, capacity, &ptr), "host_alloc");
+		return (data_ptr_t)ptr;
+	}
+	void Put(data_ptr_t ptr, idx_t capacity) {
+		std::lock_guard<std::mutex> guard(lock);
+		free_list.emplace_back(ptr, capacity);
+	}
+};
+
+PinnedPool &Pool() {
+	static PinnedPool pool;
+	return pool;
+}
+
 struct SuccinctGpuScanState : public SegmentScanState {
-	//! the decoded segment (count * sizeof(T) bytes), filled by the first scan call
-	unique_ptr<data_t[]> decoded;
+	~SuccinctGpuScanState() override {
+		if (decoded) {
+			Pool().Put(decoded, capacity);
+		}
+	}
+	//! the decoded segment (count * sizeof(T) bytes, pinned), filled by the first scan call
+	data_ptr_t decoded = nullptr;
+	idx_t capacity = 0;
 	idx_t decoded_count = 0;
+	//! the segment the buffer belongs to (a scan state moves from segment to segment)
+	ColumnSegment *owner = nullptr;
 };
 
 unique_ptr<SegmentScanState> SuccinctGpuInitScan(ColumnSegment &segment) {
@@ -227,18 +328,30 @@ void SuccinctGpuScanPartial(ColumnSegment &segment, ColumnScanState &state, idx_
 	result.SetVectorType(VectorType::FLAT_VECTOR);
 	auto target = FlatVector::GetData(result);
 	auto scan = (SuccinctGpuScanState *)state.scan_state.get();
+	if (scan && scan->owner == &segment && scan->decoded_count == segment.count) {
+		// every pull after the first: a slice of the decoded segment
+		memcpy(target + result_offset * sizeof(T), scan->decoded + start * sizeof(T), scan_count * sizeof(T));
+		return;
+	}
 	std::lock_guard<std::mutex> guard(seg_state.lock);
 	EnsureResident(segment, seg_state);
 	if (!scan) { // no scan state (index fetch paths): decode just the requested slice
 		Check(adacom_scan_partial(seg_state.column, 0, start, scan_count, 0, target, result_offset, 0), "scan_partial");
 		return;
 	}
-	if (scan->decoded_count != segment.count) { // first pull of this segment: one launch decodes all of it
-		scan->decoded = unique_ptr<data_t[]>(new data_t[segment.count * sizeof(T) + 8]);
-		Check(adacom_decode(seg_state.column, 0, 1, 0, scan->decoded.get(), 0), "decode");
-		scan->decoded_count = segment.count;
+	// first pull of this segment: ONE launch decodes all of it into a pinned buffer
+	idx_t bytes = segment.count * sizeof(T) + 8;
+	if (scan->decoded && scan->capacity < bytes) {
+		Pool().Put(scan->decoded, scan->capacity);
+		scan->decoded = nullptr;
 	}
-	memcpy(target + result_offset * sizeof(T), scan->decoded.get() + start * sizeof(T), scan_count * sizeof(T));
+	if (!scan->decoded) {
+		scan->decoded = Pool().Get(seg_state.ctx, bytes, scan->capacity);
+	}
+	Check(adacom_decode(seg_state.column, 0, 1, 0, scan->decoded, 0), "decode");
+	scan->decoded_count = segment.count;
+	scan->owner = &segment;
+	memcpy(target + result_offset * sizeof(T), scan->decoded + start * sizeof(T), scan_count * sizeof(T));
 }
 
 template <class T>
@@ -275,17 +388,35 @@ idx_t SuccinctGpuAppend(CompressionAppendState &append_state, ColumnSegment &seg
 	idx_t capacity = segment.SegmentSize() / sizeof(T);
 	idx_t copied = MinValue<idx_t>(count, capacity - segment.count);
 	auto source = (T *)data.data;
+	if (!seg_state.slots) {
+		seg_state.slots = unique_ptr<data_t[]>(new data_t[segment.SegmentSize()]);
+	}
 	auto target = (T *)seg_state.slots.get() + segment.count;
 	uint64_t min_factor = NumericLimits<uint64_t>::Maximum(), max_factor = 0;
-	for (idx_t i = 0; i < copied; i++) {
-		auto idx = data.sel->get_index(offset + i);
-		if (data.validity.RowIsValid(idx)) {
+	if (data.validity.AllValid()) {
+		for (idx_t i = 0; i < copied; i++) {
+			auto idx = data.sel->get_index(offset + i);
 			NumericStatistics::Update<T>(stats, source[idx]);
 			target[i] = source[idx];
 			min_factor = MinValue<uint64_t>(min_factor, uint64_t(source[idx]));
 			max_factor = MaxValue<uint64_t>(max_factor, uint64_t(source[idx]));
-		} else {
-			target[i] = NullValue<T>(); // the NULL gap (succinct.cpp:288-292)
+		}
+	} else {
+		for (idx_t i = 0; i < copied; i++) {
+			auto idx = data.sel->get_index(offset + i);
+			if (data.validity.RowIsValid(idx)) {
+				NumericStatistics::Update<T>(stats, source[idx]);
+				target[i] = source[idx];
+				min_factor = MinValue<uint64_t>(min_factor, uint64_t(source[idx]));
+				max_factor = MaxValue<uint64_t>(max_factor, uint64_t(source[idx]));
+			} else {
+				target[i] = NullValue<T>(); // the NULL gap (succinct.cpp:288-292)
+				if (seg_state.validity.empty()) {
+					seg_state.validity.assign((capacity + 63) / 64, ~uint64_t(0));
+				}
+				idx_t row = segment.count + i;
+				seg_state.validity[row >> 6] &= ~(uint64_t(1) << (row & 63));
+			}
 		}
 	}
 	segment.UpdateMinFactor(min_factor);
@@ -294,17 +425,10 @@ idx_t SuccinctGpuAppend(CompressionAppendState &append_state, ColumnSegment &seg
 	return copied;
 }
 
-//! the segment is complete: move it to the device; eager mode compacts right away (column_segment.cpp:273-293)
+//! succinct.cpp:324-330: bytes of the segment.  Compaction is triggered by ColumnSegment::Append (segment full,
+//! column_segment.cpp:266-268), by the first scan (:157-160) or by the policy -- never here.
 template <class T>
 idx_t SuccinctGpuFinalizeAppend(ColumnSegment &segment, SegmentStatistics &stats) {
-	auto &seg_state = StateOf(segment);
-	{
-		std::lock_guard<std::mutex> guard(seg_state.lock);
-		EnsureResident(segment, seg_state);
-	}
-	if (!DBConfig::GetConfig(segment.db).adaptive_succinct_compression_enabled) {
-		SuccinctGpuFun::Compact(segment, /*zero_extended_minmax=*/false);
-	}
 	return segment.count * sizeof(T);
 }
 
@@ -362,6 +486,27 @@ bool SuccinctGpuFun::TypeIsSupported(PhysicalType type) {
 	}
 }
 
+idx_t SuccinctGpuFun::SlotWidthSize(idx_t segment_size, idx_t type_size) {
+	// sdsl::size_in_bytes of the slot-width int_vector the reference allocates (column_segment.cpp:101-105)
+	idx_t bits = (segment_size / type_size) * type_size * 8;
+	return 9 + 8 * ((bits + 63) / 64);
+}
+
+unique_ptr<CompressedSegmentState> SuccinctGpuFun::InitSegmentFromBlock(ColumnSegment &segment, data_ptr_t block_ptr) {
+	auto state = make_unique<SuccinctGpuSegmentState>();
+	state->ctx = GpuContextFor(segment.start);
+	uint64_t count = segment.count;
+	auto capacity = (uint32_t)(segment.SegmentSize() / segment.type_size);
+	Check(adacom_column_create(state->ctx, GpuTypeOf(segment.type.InternalType()), 1, &count, capacity, &state->column),
+	      "column_create");
+	if (count) {
+		Check(adacom_column_upload_raw(state->column, block_ptr, 0, count), "upload");
+		Check(adacom_ctx_synchronize(state->ctx), "synchronize"); // the block may be evicted once we return
+	}
+	state->resident = count;
+	return move(state);
+}
+
 idx_t SuccinctGpuFun::Compact(ColumnSegment &segment, bool zero_extended_minmax) {
 	auto &seg_state = StateOf(segment);
 	std::lock_guard<std::mutex> guard(seg_state.lock);
@@ -373,32 +518,40 @@ idx_t SuccinctGpuFun::Compact(ColumnSegment &segment, bool zero_extended_minmax)
 	if (zero_extended_minmax) {
 		flags |= ADACOM_ZERO_EXT_MINMAX; // BitCompressFromUncompressed, column_segment.cpp:390-400
 	}
-	Check(adacom_analyze(seg_state.column, 0, 1, flags, nullptr, 0), "analyze");
+	// NULL rows stay out of min/max on the append path (succinct.cpp:284-292); the adaptive encoder looks at every
+	// slot of the block (column_segment.cpp:392-399), so it gets no mask
+	const uint64_t *validity = (!zero_extended_minmax && !seg_state.validity.empty()) ? seg_state.validity.data() : nullptr;
+	Check(adacom_analyze(seg_state.column, 0, 1, flags, validity, 0), "analyze");
 	Check(adacom_encode(seg_state.column, 0, 1, flags), "encode");
-	segment.SetBitCompressed();
 	uint64_t bytes = 0;
 	Check(adacom_column_data_size(seg_state.column, 0, 1, &bytes), "data_size");
+	seg_state.data_size = bytes;
+	adacom_segment_meta meta;
+	Check(adacom_column_get_meta(seg_state.column, 0, 1, &meta), "get_meta");
+	if (meta.state & ADACOM_SEG_REPACKED) {
+		// the payload lives in the packed arena now: drop the slot copies on both sides
+		Check(adacom_column_release_raw(seg_state.column), "release_raw");
+		seg_state.slots.reset();
+	}
 	return bytes;
 }
 
-idx_t SuccinctGpuFun::Uncompact(ColumnSegment &segment) {
+void SuccinctGpuFun::UncompactToBlock(ColumnSegment &segment, data_ptr_t block_ptr) {
 	auto &seg_state = StateOf(segment);
 	std::lock_guard<std::mutex> guard(seg_state.lock);
 	EnsureResident(segment, seg_state);
-	Check(adacom_uncompact(seg_state.column, 0, 1, 0), "uncompact");
-	segment.SetBitUncompressed();
-	return segment.SegmentSize();
+	if (segment.count) {
+		Check(adacom_decode(seg_state.column, 0, 1, 0, block_ptr, 0), "decode");
+	}
 }
 
 idx_t SuccinctGpuFun::DataSize(ColumnSegment &segment) {
-	auto &seg_state = StateOf(segment);
-	std::lock_guard<std::mutex> guard(seg_state.lock);
-	if (!seg_state.column) {
-		return segment.SegmentSize();
+	auto state = (SuccinctGpuSegmentState *)segment.GetSegmentState();
+	if (!state || !state->column || !state->data_size) {
+		// open segment: the slot-width vector of the reference
+		return SlotWidthSize(segment.SegmentSize(), segment.type_size);
 	}
-	uint64_t bytes = 0;
-	Check(adacom_column_data_size(seg_state.column, 0, 1, &bytes), "data_size");
-	return bytes;
+	return state->data_size;
 }
 
 } // namespace duckdb

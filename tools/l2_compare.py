@@ -1,0 +1,63 @@
+"""Run the reference's own benchmark bodies (oracle/l2/l2_driver.cpp) through BOTH builds of the reference:
+  oracle/_ref/l2/l2_driver_ref  the unmodified reference (CPU SDSL codec)
+  oracle/_ref/l2/l2_driver_gpu  the reference + integration/duckdb/reference.patch + succinct_gpu.cpp + libadacom_gpu.so
+and compare answers (checksums, data sizes) and wall times.  One JSON line per case.  Needs a B200 for the GPU arm.
+
+usage: python tools/l2_compare.py [small|full] > log
+"""
+import json
+import os
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+L2 = os.path.join(ROOT, "oracle", "_ref", "l2")
+
+SMALL = [
+    ["nulls", "200000", "succinct"],
+    ["zipf", "10000000", "2000", "42", "succinct"],
+    ["zipf", "10000000", "2000", "42", "padded"],
+    ["sequential", "1000000", "10", "succinct"],
+    ["tpch", "0.1", "-", "1", "3"],
+    ["skews", "1000000", "100000", "52", "adaptive", "1.0", "4", "0"],
+    ["skews", "1000000", "100000", "52", "non_adaptive", "1.0", "4", "0"],
+]
+FULL = [
+    # benchmark/micro/succinct/zipf_distribution.cpp:13-15: NUM_INSERTS 100000000, NUM_LOOKUPS 10000, ZIPF_K 1
+    ["zipf", "100000000", "10000", "42", "succinct"],
+    # sequential.cpp:11-12 at its checked-in size, and at 10^8 rows
+    ["sequential", "1000000", "10", "succinct"],
+    ["sequential", "100000000", "2", "succinct"],
+    ["tpch", "1", "-", "1", "3"],
+]
+SAME = {"nulls": ["size", "checksum"], "zipf": ["size_before_compact", "size_loaded", "size_after", "result_rows", "checksum"],
+        "sequential": ["size_loaded", "size_after", "result_rows", "checksum"],
+        "tpch": ["rows", "size_before_compact", "size_after_compact", "q6_revenue", "q1"], "skews": []}
+
+
+def run(arm, args, env=None):
+    t0 = time.time()
+    p = subprocess.run([os.path.join(L2, f"l2_driver_{arm}")] + args, capture_output=True, text=True,
+                       env=dict(os.environ, **(env or {})))
+    wall = time.time() - t0
+    if p.returncode != 0:
+        return {"error": p.stderr[-400:], "rc": p.returncode}, wall
+    return json.loads(p.stdout.strip().splitlines()[-1]), wall
+
+
+def main():
+    cases = FULL if (len(sys.argv) > 1 and sys.argv[1] == "full") else SMALL
+    ok = True
+    for args in cases:
+        ref, wr = run("ref", args)
+        gpu, wg = run("gpu", args)
+        same = all(ref.get(k) == gpu.get(k) for k in SAME[args[0]]) and "error" not in ref and "error" not in gpu
+        ok &= same
+        timing = {k: (ref.get(k), gpu.get(k)) for k in ref if k.endswith("_s") or k.endswith("per_s")}
+        print(json.dumps({"case": " ".join(args), "answers_equal": same, "ref_vs_gpu": timing, "wall_s": (round(wr, 2), round(wg, 2)),
+                          "ref": ref, "gpu": gpu}), flush=True)
+    sys.exit(0 if ok else 1)
+
+
+main()
