@@ -15,6 +15,9 @@
 #include "duckdb/storage/table/scan_state.hpp"
 #include "duckdb/storage/table/row_group.hpp"
 
+#include <atomic>
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -60,6 +63,42 @@ struct GpuRuntime {
 					error = adacom_last_error(nullptr);
 				}
 			}
+		}
+	}
+};
+
+//! ADACOM_BINDING_STATS=1: wall time spent inside the C-ABI calls, printed when the process exits
+struct BindingStats {
+	std::atomic<uint64_t> decode_ns {0}, decode_calls {0}, compact_ns {0}, compact_calls {0}, upload_ns {0},
+	    upload_calls {0}, slice_ns {0}, slice_calls {0};
+	bool enabled = getenv("ADACOM_BINDING_STATS") != nullptr;
+	~BindingStats() {
+		if (enabled) {
+			fprintf(stderr,
+			        "[adacom binding] decode %llu calls %.3f ms | compact %llu calls %.3f ms | upload %llu calls %.3f ms | "
+			        "slices %llu calls %.3f ms\n",
+			        (unsigned long long)decode_calls, decode_ns / 1e6, (unsigned long long)compact_calls, compact_ns / 1e6,
+			        (unsigned long long)upload_calls, upload_ns / 1e6, (unsigned long long)slice_calls, slice_ns / 1e6);
+		}
+	}
+};
+BindingStats &Stats() {
+	static BindingStats stats;
+	return stats;
+}
+struct StatTimer {
+	std::atomic<uint64_t> &ns, &calls;
+	std::chrono::steady_clock::time_point t0;
+	bool on;
+	StatTimer(std::atomic<uint64_t> &ns_p, std::atomic<uint64_t> &calls_p) : ns(ns_p), calls(calls_p), on(Stats().enabled) {
+		if (on) {
+			t0 = std::chrono::steady_clock::now();
+		}
+	}
+	~StatTimer() {
+		if (on) {
+			ns += (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count();
+			calls++;
 		}
 	}
 };
@@ -143,6 +182,7 @@ void EnsureResident(ColumnSegment &segment, SuccinctGpuSegmentState &state) {
 	if (state.column && state.resident == segment.count) {
 		return;
 	}
+	StatTimer timer(Stats().upload_ns, Stats().upload_calls);
 	if (state.column) { // the segment grew since the last upload: rebuild (appends and scans rarely interleave)
 		adacom_column_destroy(state.column);
 		state.column = nullptr;
@@ -330,6 +370,7 @@ void SuccinctGpuScanPartial(ColumnSegment &segment, ColumnScanState &state, idx_
 	auto scan = (SuccinctGpuScanState *)state.scan_state.get();
 	if (scan && scan->owner == &segment && scan->decoded_count == segment.count) {
 		// every pull after the first: a slice of the decoded segment
+		StatTimer timer(Stats().slice_ns, Stats().slice_calls);
 		memcpy(target + result_offset * sizeof(T), scan->decoded + start * sizeof(T), scan_count * sizeof(T));
 		return;
 	}
@@ -340,6 +381,7 @@ void SuccinctGpuScanPartial(ColumnSegment &segment, ColumnScanState &state, idx_
 		return;
 	}
 	// first pull of this segment: ONE launch decodes all of it into a pinned buffer
+	StatTimer timer(Stats().decode_ns, Stats().decode_calls);
 	idx_t bytes = segment.count * sizeof(T) + 8;
 	if (scan->decoded && scan->capacity < bytes) {
 		Pool().Put(scan->decoded, scan->capacity);
@@ -510,6 +552,7 @@ unique_ptr<CompressedSegmentState> SuccinctGpuFun::InitSegmentFromBlock(ColumnSe
 idx_t SuccinctGpuFun::Compact(ColumnSegment &segment, bool zero_extended_minmax) {
 	auto &seg_state = StateOf(segment);
 	std::lock_guard<std::mutex> guard(seg_state.lock);
+	StatTimer timer(Stats().compact_ns, Stats().compact_calls);
 	EnsureResident(segment, seg_state);
 	int flags = 0;
 	if (DBConfig::GetConfig(segment.db).succinct_padded_to_next_byte_enabled) {

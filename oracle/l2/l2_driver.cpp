@@ -19,9 +19,24 @@
 //                                 libadacom_gpu.so                                   (the drop-in run, needs a B200)
 // The only difference from the reference bodies: std::mt19937 is seeded with a fixed number (the reference seeds from
 // std::random_device, zipf_distribution.cpp:29-30), so both arms draw identical look-up keys.
+#include <algorithm>
+#include <atomic>
+#include <functional>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <set>
+#include <string>
+#include <thread>
+#include <unordered_map>
+#include <unordered_set>
+#include <vector>
+#define private public // debugging aid (L2_DUMP_SEGMENTS): read-only walk over the catalog's segment map
+#include "duckdb/catalog/catalog_entry/column_segment_catalog.hpp"
+#undef private
+#include "duckdb/storage/table/column_segment.hpp"
 #include "duckdb.hpp"
 #include "duckdb/catalog/catalog.hpp"
-#include "duckdb/catalog/catalog_entry/column_segment_catalog.hpp"
 #include "duckdb/main/appender.hpp"
 #include "duckdb/main/database_manager.hpp"
 #include "duckdb/storage/buffer_manager.hpp"
@@ -50,6 +65,21 @@ double Now() {
 
 ColumnSegmentCatalog *SegmentCatalog(DuckDB &db) {
 	return db.instance->GetDatabaseManager().GetSystemCatalog().GetColumnSegmentCatalog();
+}
+
+//! L2_DUMP_SEGMENTS=<file>: one line per data segment (type, start, count, size, compacted, function), sorted by the caller
+void DumpSegments(DuckDB &db) {
+	const char *path = getenv("L2_DUMP_SEGMENTS");
+	if (!path) {
+		return;
+	}
+	std::ofstream out(path);
+	for (auto &entry : SegmentCatalog(db)->statistics) {
+		auto seg = entry.first;
+		out << seg->type.ToString() << " start=" << seg->start << " count=" << seg->count << " size=" << seg->GetDataSize()
+		    << " segment_size=" << seg->SegmentSize() << " compacted=" << seg->IsBitCompressed()
+		    << " fn=" << (int)seg->function->type << " min=" << seg->GetMinFactor() << " max=" << seg->GetMax() << "\n";
+	}
 }
 
 void MustSucceed(unique_ptr<MaterializedQueryResult> &result, const std::string &what) {
@@ -284,6 +314,7 @@ int RunTpch(double sf, const std::string &outdir, int threads, int reps) {
 	SegmentCatalog(db)->CompactAllSegments();
 	uint64_t size_after = SegmentCatalog(db)->GetTotalDataSize();
 	double t2 = Now();
+	DumpSegments(db);
 	std::string q6_text = TPCHExtension::GetQuery(6), q1_text = TPCHExtension::GetQuery(1);
 	double q6_best = 1e30, q1_best = 1e30;
 	unique_ptr<MaterializedQueryResult> q6, q1;
@@ -344,14 +375,16 @@ int RunTpch(double sf, const std::string &outdir, int threads, int reps) {
 int RunNulls(size_t n, const std::string &variant) {
 	DuckDB db(nullptr);
 	Connection conn(db);
-	ApplyVariant(db, variant);
+	ApplyVariant(db, variant == "zeros" ? "succinct" : variant == "zeros_plain" ? "nonsuccinct" : variant);
 	auto r = conn.Query("CREATE TABLE t1(i INTEGER);");
 	MustSucceed(r, "create");
 	{
 		Appender appender(conn, "t1");
 		for (size_t i = 0; i < n; i++) {
 			appender.BeginRow();
-			if (i % 7 == 3) {
+			if (variant == "zeros" || variant == "zeros_plain") {
+				appender.Append<int32_t>(0);
+			} else if (i % 7 == 3) {
 				appender.Append<std::nullptr_t>(nullptr);
 			} else {
 				appender.Append<int32_t>((int32_t)(1000 + (i * 2654435761u) % 5000));
@@ -362,6 +395,7 @@ int RunNulls(size_t n, const std::string &variant) {
 	}
 	SegmentCatalog(db)->CompactAllSegments();
 	uint64_t size = SegmentCatalog(db)->GetTotalDataSize();
+	DumpSegments(db);
 	Checksum sum;
 	for (const char *sql : {"SELECT sum(i), count(i), count(*), min(i), max(i) FROM t1",
 	                        "SELECT sum(i), count(*) FROM t1 WHERE i < 3000",
