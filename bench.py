@@ -53,6 +53,9 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-log2-values", type=int, default=21)
     ap.add_argument("--detail", default="", help="write the per-width table to this JSON file")
+    ap.add_argument("--configs", default="1,3,4,5", help="the other BASELINE.json workload shapes to run after the "
+                    "headline sweep (1 Zipf point filters, 3 skew sweep + policy epochs, 4 TPC-H SF10 Q6/Q1, "
+                    "5 TPC-H SF100 sharded Q6 over NCCL); '' = none")
     return ap.parse_args()
 
 
@@ -164,6 +167,18 @@ def cpu_sweep(widths, log2_values, threads, steps=1, warmup=0):
                 ops_GBs=ops)
 
 
+def shared_config(args, n_segments=None):
+    """the `config` object, identical in both arms (--impl ours / reference): names the workload and states how the CPU
+    arm samples it"""
+    cfg = {"workload": WORKLOAD, "widths": args.widths, "values_per_gpu_per_width": 1 << args.log2_values,
+           "ops_per_width": list(OPS),
+           "cpu_arm_sample": f"2^{args.cpu_log2_values} values per width per step (same generator, same segmentation, same "
+                             f"five ops; the GPU arm runs 2^{args.log2_values})",
+           "value_definition": "logical bytes = ops * n * 8 per width, / time",
+           "l2": "every op streams >= 1 GiB (> 126 MB L2) between reuses of any line"}
+    return cfg
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -178,7 +193,7 @@ def run_reference(args):
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": round(res["seconds_per_step"] * 1e3, 3), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "int64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "widths": args.widths, "sample": res["sample"]},
+        "config": shared_config(args),
         "cpu_baseline": {"value": round(res["value"], 3), "unit": "GB/s", "cores": threads, "kind": res["kind"],
                          "sample": res["sample"], "ops_GBs": res["ops_GBs"]},
         "e2e": {"value": round(res["value"], 3), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -390,17 +405,21 @@ def run_ours(args):
         cpu = {"value": round(r["value"], 3), "unit": "GB/s", "cores": threads, "kind": r["kind"],
                "sample": r["sample"], "ops_GBs": r["ops_GBs"]}
 
+    # ---- the other workload shapes of BASELINE.json (configs 1, 3, 4 on one GPU; 5 = sharded Q6 over NCCL) ----
+    for c in cols.values():
+        c.close()
+    cols = {}
+    configs = run_configs(args, ctx, rank, world, peak)
+
     if rank == 0:
         line = {
             "metric": METRIC, "value": round(value, 1), "unit": "GB/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(ms_per_step, 3), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "values_per_gpu_per_width": n, "widths": args.widths,
-                       "segments_per_column": int(len(counts)), "ops_per_width": list(OPS),
-                       "value_definition": "logical bytes = ops * n * 8 per width, / wall time on device",
-                       "l2": "every op streams >= 1 GiB (> 126 MB L2) between reuses of any line",
-                       "parallelism": f"row groups sharded, {world} rank(s), NCCL all-gather of 64 aggregates/step"},
-            "ops": op_summary, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+            "config": shared_config(args),
+            "parallelism": f"row groups sharded, {world} rank(s), NCCL all-gather of 64 aggregates/step",
+            "segments_per_column": int(len(counts)),
+            "ops": op_summary, "configs": configs, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
             "gpu_launches": int(launches), "clocks": clocks,
         }
         print(json.dumps(line), flush=True)
@@ -413,6 +432,41 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def run_configs(args, ctx, rank, world, peak):
+    wanted = [x for x in args.configs.split(",") if x]
+    if not wanted:
+        return None
+    from tools import workloads
+    threads = os.cpu_count() or 1
+    out = {}
+
+    def leg(key, fn, needs_single):
+        if needs_single and world > 1:
+            return  # one-GPU workloads: measured by the N = 1 run
+        sampler = ClockSampler(int(os.environ.get("LOCAL_RANK", "0")))
+        if rank == 0:
+            sampler.start()
+        t0 = time.time()
+        try:
+            res = fn()
+        except Exception as ex:  # a failing leg must not take the headline line with it, but it must be visible
+            res = {"error": f"{type(ex).__name__}: {ex}"}
+        if rank == 0:
+            res["clocks"] = sampler.stop()
+            res["wall_s"] = round(time.time() - t0, 1)
+            out[key] = res
+
+    if "1" in wanted:
+        leg("1_zipf_point_filters", lambda: workloads.config1_zipf(ctx, peak, threads), True)
+    if "3" in wanted:
+        leg("3_zipf_skew_sweep", lambda: workloads.config3_skews(ctx, peak, threads), True)
+    if "4" in wanted:
+        leg("4_tpch_sf10", lambda: workloads.config4_tpch(ctx, peak, threads), True)
+    if "5" in wanted:
+        leg("5_tpch_sf100_sharded", lambda: workloads.config5_tpch_sharded(ctx, peak, rank, world), False)
+    return out if rank == 0 else None
 
 
 def run_e2e(args, ctx, cols, widths, counts, n, S, rank, world, dev):

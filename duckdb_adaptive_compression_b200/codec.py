@@ -105,6 +105,11 @@ class Context:
         self.check(self.lib.adacom_flush_l2(self.h))
 
     @property
+    def stream_ptr(self) -> int:
+        """cudaStream_t of the context's compute stream (for torch.cuda.ExternalStream)"""
+        return int(self.lib.adacom_ctx_stream(self.h) or 0)
+
+    @property
     def launch_count(self) -> int:
         return int(self.lib.adacom_ctx_launch_count(self.h))
 

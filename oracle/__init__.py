@@ -114,6 +114,15 @@ class Oracle:
         f("bits_hi", C.c_uint32, [C.c_uint64])
         f("bench_column", C.c_int, [C.c_void_p, C.c_uint64, C.c_uint8, C.c_int, C.c_uint64, C.c_int, C.c_int,
                                     C.POINTER(_BenchResult)])
+        if kind == "reference":
+            f("bench_lookups", C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_void_p,
+                                         C.c_void_p, C.POINTER(C.c_double)])
+            f("bench_fetch", C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p,
+                                       C.POINTER(C.c_double)])
+            f("bench_epoch", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.POINTER(C.c_double),
+                                       C.POINTER(C.c_double)])
+            f("bench_query", C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_int32, C.c_uint32, C.c_uint64,
+                                       C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_double)])
         if kind == "port":
             f("segment_sum", None, [C.c_void_p, C.c_int, C.POINTER(_Sum128)])
             f("segment_filter", None, [C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.POINTER(_Sum128), C.c_void_p])
@@ -172,6 +181,103 @@ class Oracle:
             raise RuntimeError("bench_column failed")
         return dict(analyze_s=res.analyze_s, encode_s=res.encode_s, scan_s=res.scan_s, sum_s=res.sum_s, uncompact_s=res.uncompact_s,
                     values=res.values, sum=(res.sum_hi << 64) | res.sum_lo, packed_bytes=res.packed_bytes)
+
+
+class _QueryCol(C.Structure):
+    _fields_ = [("segs", C.c_void_p), ("n_segs", C.c_uint64), ("seg_start", C.c_void_p), ("has_pred", C.c_int32),
+                ("reserved", C.c_int32), ("lo", C.c_int64), ("hi", C.c_int64)]
+
+
+class _SumExpr(C.Structure):
+    _fields_ = [("n_factors", C.c_uint32), ("col", C.c_uint32 * 3), ("add", C.c_int64 * 3), ("mul", C.c_int64 * 3)]
+
+
+class _Agg(C.Structure):
+    _fields_ = [("sum_lo", C.c_uint64), ("sum_hi", C.c_uint64), ("count", C.c_uint64), ("reserved", C.c_uint64)]
+
+
+class RefColumn:
+    """A column the way the reference holds it: DuckDB segmentation (seg_counts), every listed segment appended vector by
+    vector and compacted (BitCompressFromSuccinct).  Workload CPU baselines (kind="reference" only) run on these."""
+
+    def __init__(self, oracle: "Oracle", values: np.ndarray, seg_counts, only_segments=None, value_of_rows=None,
+                 flags: int = 0):
+        self.o = oracle
+        counts = np.asarray(seg_counts, dtype=np.int64)
+        self.starts = np.concatenate([[0], np.cumsum(counts)]).astype(np.uint64)
+        self.segs = [None] * len(counts)
+        todo = range(len(counts)) if only_segments is None else sorted(set(int(g) for g in only_segments))
+        for g in todo:
+            a, b = int(self.starts[g]), int(self.starts[g + 1])
+            v = values[a:b] if values is not None else value_of_rows(a, b)
+            self.segs[g] = oracle.encode(np.ascontiguousarray(v), flags)
+        self.handles = (C.c_void_p * len(counts))(*[(s.h if s is not None else None) for s in self.segs])
+
+    def packed_bytes(self, segs=None) -> int:
+        ids = range(len(self.segs)) if segs is None else segs
+        return sum(self.segs[g].get("words") * 8 for g in ids if self.segs[g] is not None)
+
+
+def bench_lookups(col: RefColumn, seg_idx, constants, threads: int, copy_per_call: bool = True):
+    """config 1 on the reference's SDSL: (match counts, first rows, seconds)."""
+    seg_idx = np.ascontiguousarray(seg_idx, dtype=np.uint32)
+    constants = np.ascontiguousarray(constants, dtype=np.int64)
+    n = len(seg_idx)
+    cnt = np.zeros(n, dtype=np.uint64)
+    first = np.zeros(n, dtype=np.uint64)
+    secs = C.c_double()
+    rc = col.o._bench_lookups(col.handles, _ptr(seg_idx), _ptr(constants), n, threads, int(copy_per_call), _ptr(cnt),
+                              _ptr(first), C.byref(secs))
+    assert rc == 0
+    return cnt, first, float(secs.value)
+
+
+def bench_fetch(col: RefColumn, seg_idx, rows, dtype, threads: int):
+    seg_idx = np.ascontiguousarray(seg_idx, dtype=np.uint32)
+    rows = np.ascontiguousarray(rows, dtype=np.uint32)
+    out = np.zeros(len(seg_idx), dtype=dtype)
+    secs = C.c_double()
+    rc = col.o._bench_fetch(col.handles, _ptr(seg_idx), _ptr(rows), len(seg_idx), threads, _ptr(out), C.byref(secs))
+    assert rc == 0
+    return out, float(secs.value)
+
+
+def bench_epoch(col: RefColumn, hot, flags: int = 0):
+    hot = np.ascontiguousarray(hot, dtype=np.uint32)
+    a, b = C.c_double(), C.c_double()
+    rc = col.o._bench_epoch(col.handles, _ptr(hot), len(hot), flags, C.byref(a), C.byref(b))
+    assert rc == 0
+    return float(a.value), float(b.value)
+
+
+def bench_query(o: "Oracle", cols, sums, n_rows: int, threads: int, group_by=None, copy_per_call: bool = True):
+    """configs 4/5 on the reference's SDSL.  cols: list of (RefColumn, None | (lo, hi)); sums: list of lists of
+    (col_index, add, mul); group_by: (col_index, n_groups).  Returns ([(sum, count)] group-major, seconds)."""
+    qc = (_QueryCol * len(cols))()
+    for i, (col, pred) in enumerate(cols):
+        qc[i].segs = C.cast(col.handles, C.c_void_p)
+        qc[i].n_segs = len(col.segs)
+        qc[i].seg_start = col.starts.ctypes.data
+        qc[i].has_pred = 0 if pred is None else 1
+        if pred is not None:
+            qc[i].lo, qc[i].hi = int(pred[0]), int(pred[1])
+    se = (_SumExpr * max(len(sums), 1))()
+    for s, factors in enumerate(sums):
+        se[s].n_factors = len(factors)
+        for k, (ci, add, mul) in enumerate(factors):
+            se[s].col[k], se[s].add[k], se[s].mul[k] = ci, add, mul
+    g_col, n_g = (-1, 0) if group_by is None else group_by
+    out = (_Agg * (max(n_g, 1) * max(len(sums), 1)))()
+    secs = C.c_double()
+    rc = o._bench_query(qc, len(cols), se, len(sums), g_col, n_g, n_rows, threads, int(copy_per_call), out, C.byref(secs))
+    assert rc == 0
+    res = []
+    for a in out:
+        v = (a.sum_hi << 64) | a.sum_lo
+        if v >= 1 << 127:
+            v -= 1 << 128
+        res.append((v, int(a.count)))
+    return res, float(secs.value)
 
 
 class OracleSegment:

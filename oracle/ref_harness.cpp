@@ -388,6 +388,270 @@ int ref_bench_column(const void *values, uint64_t n, uint8_t type_size, int is_s
 	return 0;
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Timed CPU baselines of the reference's WORKLOADS (BASELINE.json configs 1, 3, 4, 5) on segment handles built with the
+// entry points above: every value goes through the reference's SDSL int_vector exactly like SuccinctScanPartial does
+// (succinct.cpp:123-144, incl. the per-call deep copy of the packed vector, quirk Q4, when copy_per_call != 0), the
+// filter is TemplatedFilterSelection's loop (column_segment.cpp:575-586) and the aggregate a HUGEINT sum.  Work is dealt
+// round-robin over `threads` host threads (DuckDB: one row group per task, row_group_collection.cpp:119-153).
+// ---------------------------------------------------------------------------------------------------------------------
+
+static inline uint64_t ExtendLow(uint64_t v, uint8_t type_size, bool is_signed) {
+	if (type_size >= 8) {
+		return v;
+	}
+	unsigned sh = 64 - 8 * type_size;
+	return is_signed ? (uint64_t)(((int64_t)(v << sh)) >> sh) : ((v << sh) >> sh);
+}
+
+static void ScanVectorCall(RefSegment &seg, uint64_t start, uint64_t n, void *result, uint64_t result_offset,
+                           int copy_per_call) {
+	if (copy_per_call) {
+		RefSegment copy = seg; // `auto source = segment.succinct_vec;` (succinct.cpp:127)
+		ref_scan_partial(&copy, start, n, result, result_offset, 0);
+	} else {
+		ref_scan_partial(&seg, start, n, result, result_offset, 0);
+	}
+}
+
+} // extern "C"
+template <class F>
+static double RunThreads(int threads, F &&body) {
+	std::vector<std::thread> pool;
+	std::vector<double> secs(threads, 0.0);
+	for (int tid = 0; tid < threads; tid++) {
+		pool.emplace_back([&, tid]() {
+			auto t0 = std::chrono::steady_clock::now();
+			body(tid);
+			secs[tid] = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+		});
+	}
+	for (auto &t : pool) {
+		t.join();
+	}
+	return *std::max_element(secs.begin(), secs.end());
+}
+extern "C" {
+
+// config 1: point filter `value == k` = scan every vector of the (zone-map selected) segment + equality filter
+int ref_bench_lookups(void **segs, const uint32_t *seg_idx, const int64_t *constants, uint64_t n_lookups, int threads,
+                      int copy_per_call, uint64_t *out_count, uint64_t *out_first_row, double *secs_out) {
+	if (threads < 1) {
+		return -1;
+	}
+	*secs_out = RunThreads(threads, [&](int tid) {
+		std::vector<uint8_t> vec(2048 * 8);
+		std::vector<uint32_t> sel(2048);
+		for (uint64_t q = tid; q < n_lookups; q += threads) {
+			auto &seg = *(RefSegment *)segs[seg_idx[q]];
+			uint64_t matches = 0, first = UINT64_MAX;
+			uint64_t c = ExtendLow((uint64_t)constants[q], seg.type_size, seg.is_signed);
+			for (uint64_t off = 0; off < seg.count; off += 2048) {
+				uint64_t m = std::min<uint64_t>(seg.count - off, 2048);
+				ScanVectorCall(seg, off, m, vec.data(), 0, copy_per_call);
+				uint64_t hits = 0;
+				for (uint64_t i = 0; i < m; i++) { // TemplatedFilterSelection<T, Equals, false>
+					uint64_t v = 0;
+					memcpy(&v, vec.data() + i * seg.type_size, seg.type_size);
+					if (ExtendLow(v, seg.type_size, seg.is_signed) == c) {
+						sel[hits++] = (uint32_t)i;
+					}
+				}
+				if (hits && first == UINT64_MAX) {
+					first = off + sel[0];
+				}
+				matches += hits;
+			}
+			out_count[q] = matches;
+			out_first_row[q] = first;
+		}
+	});
+	return 0;
+}
+
+// config 3: fetch_row with the intended semantics (FixedSizeFetchRow shape): result = T(vec[row] + min)
+int ref_bench_fetch(void **segs, const uint32_t *seg_idx, const uint32_t *row_in_seg, uint64_t n, int threads,
+                    void *out, double *secs_out) {
+	if (threads < 1) {
+		return -1;
+	}
+	*secs_out = RunThreads(threads, [&](int tid) {
+		uint64_t lo = n * tid / threads, hi = n * (tid + 1) / threads;
+		for (uint64_t q = lo; q < hi; q++) {
+			auto &seg = *(RefSegment *)segs[seg_idx[q]];
+			uint64_t v = uint64_t(seg.succinct_vec[row_in_seg[q]]);
+			if (AddsMin(seg, 0)) {
+				v += seg.min_factor;
+			}
+			memcpy((uint8_t *)out + q * seg.type_size, &v, seg.type_size);
+		}
+	});
+	return 0;
+}
+
+// config 3: one policy epoch on the compactor thread (column_segment_catalog.cpp:64-116 is single-threaded):
+// Uncompact() the hot segments, later Compact() them again (BitCompressFromUncompressed: they are UNCOMPRESSED now)
+int ref_bench_epoch(void **segs, const uint32_t *hot, uint64_t n_hot, int flags, double *uncompact_s, double *recompact_s) {
+	auto t0 = std::chrono::steady_clock::now();
+	for (uint64_t i = 0; i < n_hot; i++) {
+		ref_uncompress_succinct(segs[hot[i]], flags);
+	}
+	auto t1 = std::chrono::steady_clock::now();
+	for (uint64_t i = 0; i < n_hot; i++) {
+		ref_bit_compress_from_uncompressed(segs[hot[i]], flags);
+	}
+	auto t2 = std::chrono::steady_clock::now();
+	*uncompact_s = std::chrono::duration<double>(t1 - t0).count();
+	*recompact_s = std::chrono::duration<double>(t2 - t1).count();
+	return 0;
+}
+
+// configs 4/5: RowGroup::TemplatedScan with table filters + the aggregate above it (row_group.cpp:391-447): per
+// 2048-row vector, every filter column is scanned WHOLE (ColumnData::Select = Scan + FilterSelection,
+// column_data.cpp:199-204) and the selection refined; the remaining columns are scanned and the survivors aggregated.
+struct ref_query_col {
+	void **segs;          // the column's segments in row order
+	uint64_t n_segs;
+	const uint64_t *seg_start; // first table row of every segment (+ one past the end), n_segs + 1 entries
+	int32_t has_pred, reserved;
+	int64_t lo, hi;       // inclusive range on the decoded T value
+};
+struct ref_sum_expr {
+	uint32_t n_factors;
+	uint32_t col[3];
+	int64_t add[3], mul[3];
+};
+struct ref_agg {
+	uint64_t sum_lo, sum_hi, count, reserved;
+};
+
+int ref_bench_query(const ref_query_col *cols, uint32_t n_cols, const ref_sum_expr *sums, uint32_t n_sums,
+                    int32_t group_col, uint32_t n_groups, uint64_t n_rows, int threads, int copy_per_call,
+                    ref_agg *out, double *secs_out) {
+	if (threads < 1 || n_cols > 8 || n_sums > 8 || n_groups > 8) {
+		return -1;
+	}
+	const uint32_t G = n_groups ? n_groups : 1;
+	const uint64_t rg_rows = 122880, n_rg = (n_rows + rg_rows - 1) / rg_rows;
+	std::vector<std::vector<__int128>> part_sum(threads, std::vector<__int128>(G * n_sums, 0));
+	std::vector<std::vector<uint64_t>> part_cnt(threads, std::vector<uint64_t>(G * n_sums, 0));
+	*secs_out = RunThreads(threads, [&](int tid) {
+		std::vector<std::vector<int64_t>> vals(n_cols, std::vector<int64_t>(2048));
+		std::vector<uint8_t> raw(2048 * 8);
+		std::vector<uint32_t> sel(2048), next(2048);
+		std::vector<uint64_t> cursor(n_cols, 0); // segment cursor per column (monotone within a task)
+		for (uint64_t rg = tid; rg < n_rg; rg += threads) {
+			for (uint32_t c = 0; c < n_cols; c++) {
+				cursor[c] = std::upper_bound(cols[c].seg_start, cols[c].seg_start + cols[c].n_segs, rg * rg_rows) -
+				            cols[c].seg_start - 1;
+			}
+			uint64_t rg_end = std::min(n_rows, (rg + 1) * rg_rows);
+			for (uint64_t row = rg * rg_rows; row < rg_end; row += 2048) {
+				uint32_t m = (uint32_t)std::min<uint64_t>(2048, rg_end - row);
+				auto scan_col = [&](uint32_t c) {
+					// ColumnData::ScanVector: a vector may straddle two segments -> two scan calls (column_data.cpp:112-135)
+					const auto &qc = cols[c];
+					uint32_t done = 0;
+					while (done < m) {
+						while (qc.seg_start[cursor[c] + 1] <= row + done) {
+							cursor[c]++;
+						}
+						auto &seg = *(RefSegment *)qc.segs[cursor[c]];
+						uint64_t start = row + done - qc.seg_start[cursor[c]];
+						uint32_t take = (uint32_t)std::min<uint64_t>(m - done, seg.count - start);
+						ScanVectorCall(seg, start, take, raw.data(), done, copy_per_call);
+						done += take;
+					}
+					auto &seg0 = *(RefSegment *)qc.segs[cursor[c]];
+					for (uint32_t i = 0; i < m; i++) {
+						uint64_t v = 0;
+						memcpy(&v, raw.data() + (uint64_t)i * seg0.type_size, seg0.type_size);
+						vals[c][i] = (int64_t)ExtendLow(v, seg0.type_size, seg0.is_signed);
+					}
+				};
+				uint32_t approved = m;
+				for (uint32_t i = 0; i < m; i++) {
+					sel[i] = i;
+				}
+				uint32_t scanned = 0;
+				for (uint32_t c = 0; c < n_cols && approved; c++) {
+					if (!cols[c].has_pred) {
+						continue;
+					}
+					scan_col(c);
+					scanned |= 1u << c;
+					auto &seg0 = *(RefSegment *)cols[c].segs[cursor[c]];
+					uint32_t k = 0;
+					if (seg0.is_signed) {
+						for (uint32_t i = 0; i < approved; i++) {
+							int64_t v = vals[c][sel[i]];
+							if (v >= cols[c].lo && v <= cols[c].hi) {
+								next[k++] = sel[i];
+							}
+						}
+					} else {
+						for (uint32_t i = 0; i < approved; i++) {
+							uint64_t v = (uint64_t)vals[c][sel[i]];
+							if (v >= (uint64_t)cols[c].lo && v <= (uint64_t)cols[c].hi) {
+								next[k++] = sel[i];
+							}
+						}
+					}
+					sel.swap(next);
+					approved = k;
+				}
+				if (!approved) {
+					continue;
+				}
+				for (uint32_t c = 0; c < n_cols; c++) {
+					bool needed = (int32_t)c == group_col;
+					for (uint32_t s = 0; s < n_sums; s++) {
+						for (uint32_t f = 0; f < sums[s].n_factors; f++) {
+							needed |= sums[s].col[f] == c;
+						}
+					}
+					if (needed && !(scanned & (1u << c))) {
+						scan_col(c);
+					}
+				}
+				for (uint32_t i = 0; i < approved; i++) {
+					uint32_t r = sel[i];
+					uint32_t g = 0;
+					if (group_col >= 0) {
+						int64_t key = vals[group_col][r];
+						if (key < 0 || key >= (int64_t)n_groups) {
+							continue;
+						}
+						g = (uint32_t)key;
+					}
+					for (uint32_t s = 0; s < n_sums; s++) {
+						__int128 prod = 1;
+						for (uint32_t f = 0; f < sums[s].n_factors; f++) {
+							prod *= (__int128)sums[s].add[f] + (__int128)sums[s].mul[f] * (__int128)vals[sums[s].col[f]][r];
+						}
+						part_sum[tid][g * n_sums + s] += prod;
+						part_cnt[tid][g * n_sums + s]++;
+					}
+				}
+			}
+		}
+	});
+	for (uint32_t k = 0; k < G * n_sums; k++) {
+		__int128 total = 0;
+		uint64_t cnt = 0;
+		for (int t = 0; t < threads; t++) {
+			total += part_sum[t][k];
+			cnt += part_cnt[t][k];
+		}
+		out[k].sum_lo = (uint64_t)(unsigned __int128)total;
+		out[k].sum_hi = (uint64_t)((unsigned __int128)total >> 64);
+		out[k].count = cnt;
+		out[k].reserved = 0;
+	}
+	return 0;
+}
+
 } // extern "C"
 
 // ---- block checksum: the reference's own duckdb::Checksum (src/common/checksum.cpp:6-25), compiled from the
