@@ -68,6 +68,47 @@ class Zipf:
                 return k
 
 
-def zipf_keys(n: int, q: float, count: int, seed: int = 42) -> np.ndarray:
+def zipf_keys_scalar(n: int, q: float, count: int, seed: int = 42) -> np.ndarray:
     z = Zipf(n, q, seed)
     return np.fromiter((z() for _ in range(count)), dtype=np.int64, count=count)
+
+
+def zipf_keys(n: int, q: float, count: int, seed: int = 42) -> np.ndarray:
+    """The same key stream as `zipf_keys_scalar`, vectorised: every attempt of the rejection loop consumes exactly one
+    uniform (two 32-bit draws), so evaluating the acceptance test on a whole block of uniforms and keeping the accepted
+    ones in order reproduces the sequential sampler draw for draw."""
+    z = Zipf(n, q, seed)
+    one_minus_q = 1.0 - z.q
+
+    def expxm1bx(x):
+        small = np.abs(x) <= _EPS
+        xs = np.where(small, 1.0, x)
+        return np.where(small, 1.0 + x / 2.0 * (1.0 + x / 3.0 * (1.0 + x / 4.0)), np.expm1(xs) / xs)
+
+    def H(x):
+        log_x = np.log(x)
+        return expxm1bx(one_minus_q * log_x) * log_x
+
+    def log1pxbx(x):
+        small = np.abs(x) <= _EPS
+        xs = np.where(small, 1.0, x)
+        return np.where(small, 1.0 - x * (0.5 - x * (1.0 / 3.0 - x * 0.25)), np.log1p(xs) / xs)
+
+    out = np.zeros(0, dtype=np.int64)
+    while len(out) < count:
+        m = max(1024, int((count - len(out)) * 1.2))
+        raw = z.rs.randint(0, 1 << 32, size=2 * m, dtype=np.uint64).astype(np.float64)
+        r = (raw[0::2] + raw[1::2] * 4294967296.0) / 18446744073709551616.0
+        r = np.where(r >= 1.0, np.nextafter(1.0, 0.0), r)
+        u = r * (z.h_n - z.h_x1) + z.h_x1
+        t = np.maximum(-1.0, u * one_minus_q)
+        x = np.exp(log1pxbx(t) * u)
+        k = np.clip(np.floor(x + 0.5), 1, z.n)
+        ok = u >= H(k + 0.5) - np.exp(-z.q * np.log(k))
+        acc = k[ok].astype(np.int64)
+        need = count - len(out)
+        if len(acc) >= need:
+            # the sequential sampler would stop right after its `need`-th acceptance; later draws are simply unused
+            acc = acc[:need]
+        out = np.concatenate([out, acc])
+    return out

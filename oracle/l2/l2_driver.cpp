@@ -420,8 +420,9 @@ int main(int argc, char **argv) {
 		        "       %s sequential <n_inserts> <n_scans> <succinct|padded|nonsuccinct>\n"
 		        "       %s skews <n_inserts> <n_lookups> <seed> <adaptive|non_adaptive|non_succinct> <skew> <seconds> [background=1]\n"
 		        "       %s tpch <sf> <outdir|-> [threads=1] [reps=3]\n"
-		        "       %s nulls <n> <variant>\n",
-		        argv[0], argv[0], argv[0], argv[0], argv[0]);
+		        "       %s nulls <n> <variant>\n"
+		        "       %s zipfkeys <n> <skew> <count> <seed>\n",
+		        argv[0], argv[0], argv[0], argv[0], argv[0], argv[0]);
 		return 2;
 	}
 	std::string mode = argv[1];
@@ -439,6 +440,17 @@ int main(int argc, char **argv) {
 		}
 		if (mode == "tpch" && argc >= 4) {
 			return RunTpch(atof(argv[2]), argv[3], argc > 4 ? atoi(argv[4]) : 1, argc > 5 ? atoi(argv[5]) : 3);
+		}
+		if (mode == "zipfkeys" && argc >= 6) {
+			// the reference's sampler (benchmark/micro/succinct/zipf.cpp) driven exactly like zipf_distribution.cpp:29-33
+			std::mt19937 gen {(uint32_t)atoi(argv[5])};
+			Zipf<uint32_t, double> zipf(strtoull(argv[2], nullptr, 10), atof(argv[3]));
+			printf("[");
+			for (size_t i = 0, n = strtoull(argv[4], nullptr, 10); i < n; i++) {
+				printf("%s%u", i ? ", " : "", uint32_t(std::round(zipf(gen))));
+			}
+			printf("]\n");
+			return 0;
 		}
 		if (mode == "nulls" && argc >= 4) {
 			return RunNulls(strtoull(argv[2], nullptr, 10), argv[3]);

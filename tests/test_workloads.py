@@ -46,3 +46,16 @@ def test_lineitem_generator_shapes_and_widths():
     assert 0.012 < rows / n < 0.028 and rev > 0                                      # TPC-H Q6 selects ~1.9 %
     q1 = tpch.q1_expected(cols)
     assert sum(g["count"] for g in q1.values()) == int((cols["l_shipdate"] <= tpch.D_1998_09_02).sum())
+
+
+def test_zipf_keys_match_the_reference_sampler():
+    """golden: keys drawn by the reference's own zipf.cpp + std::mt19937 (l2_driver zipfkeys, tests/golden/zipf_keys.json)"""
+    import json
+    import os
+    from duckdb_adaptive_compression_b200.zipf import zipf_keys_scalar
+    gold = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "zipf_keys.json")))["keys"]
+    for spec, want in gold.items():
+        n, q, c, seed = spec.split(",")
+        got = zipf_keys(int(n), float(q), int(c), seed=int(seed))
+        assert got.tolist() == want, spec
+        assert zipf_keys_scalar(int(n), float(q), int(c), seed=int(seed)).tolist() == want
