@@ -39,6 +39,7 @@ class Pred(C.Structure):
     _fields_ = [("kind", C.c_int32), ("op", C.c_int32), ("constant", C.c_int64)]
 
 
+CODEC_BITPACKING, CODEC_RLE = 0, 1
 PRED_COMPARE, PRED_IS_NULL, PRED_IS_NOT_NULL = 0, 1, 2
 CONJ_AND, CONJ_OR = 0, 1
 
@@ -120,6 +121,13 @@ _PROTOTYPES = {
     "adacom_column_checkpoint_size": (_i, [_vp, C.POINTER(_u64)]),
     "adacom_column_checkpoint": (_i, [_vp, _vp, _u64, _i, C.POINTER(_u64)]),
     "adacom_column_restore": (_i, [_vp, _vp, _u64, _i, C.POINTER(_vp)]),
+    "adacom_codec_column_create": (_i, [_vp, _i, _i, _u64, _vp, _vp, _vp, C.POINTER(_vp)]),
+    "adacom_codec_column_destroy": (None, [_vp]),
+    "adacom_codec_column_num_values": (_u64, [_vp]),
+    "adacom_codec_column_image_bytes": (_u64, [_vp]),
+    "adacom_codec_decode": (_i, [_vp, _u64, _u64, _vp, _i]),
+    "adacom_codec_scan_sum": (_i, [_vp, _u64, _u64, C.POINTER(Agg)]),
+    "adacom_codec_fetch_rows": (_i, [_vp, _u64, _vp, _vp, _vp, _i]),
     "adacom_compress_host": (_i, [_vp, _i, _vp, _u64, _vp, _u32, _i, _vp, _vp, _u64, C.POINTER(_u64), C.POINTER(_vp)]),
 }
 

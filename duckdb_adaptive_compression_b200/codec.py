@@ -203,6 +203,66 @@ class Context:
         return Column(self, h, dt), metas, int(total.value)
 
 
+class CodecColumn:
+    """DuckDB bitpacking / RLE segments (block images as DuckDB writes them) resident on the GPU: batched scan,
+    fused SUM and fetch_row (adacom_codec_*)."""
+
+    def __init__(self, ctx: "Context", codec: int, dtype, images, counts):
+        self.ctx, self.dtype = ctx, np.dtype(dtype)
+        self.signed = self.dtype.kind == "i"
+        images = [np.ascontiguousarray(im, dtype=np.uint8) for im in images]
+        n = len(images)
+        ptrs = (C.c_void_p * max(n, 1))(*[im.ctypes.data for im in images])
+        sizes = np.array([im.nbytes for im in images], dtype=np.uint64)
+        cnts = np.ascontiguousarray(counts, dtype=np.uint64)
+        h = C.c_void_p()
+        ctx.check(ctx.lib.adacom_codec_column_create(ctx.h, codec, _PTYPE[self.dtype], n, ptrs, _np_ptr(sizes), _np_ptr(cnts),
+                                                     C.byref(h)))
+        self.h, self.n_segments, self.counts = h, n, [int(c) for c in cnts]
+
+    def close(self):
+        if getattr(self, "h", None) and self.ctx.h:
+            self.ctx.lib.adacom_codec_column_destroy(self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def n_values(self) -> int:
+        return int(self.ctx.lib.adacom_codec_column_num_values(self.h))
+
+    @property
+    def image_bytes(self) -> int:
+        return int(self.ctx.lib.adacom_codec_column_image_bytes(self.h))
+
+    def decode(self, seg_begin=0, seg_end=None, device_out: int | None = None):
+        e = self.n_segments if seg_end is None else seg_end
+        if device_out is not None:
+            self.ctx.check(self.ctx.lib.adacom_codec_decode(self.h, seg_begin, e, C.c_void_p(device_out), 1))
+            return None
+        out = np.zeros(sum(self.counts[seg_begin:e]), dtype=self.dtype)
+        self.ctx.check(self.ctx.lib.adacom_codec_decode(self.h, seg_begin, e, _np_ptr(out), 0))
+        return out
+
+    def scan_sum(self, seg_begin=0, seg_end=None) -> AggResult:
+        e = self.n_segments if seg_end is None else seg_end
+        a = Agg()
+        self.ctx.check(self.ctx.lib.adacom_codec_scan_sum(self.h, seg_begin, e, C.byref(a)))
+        return _agg_to_py(a, self.signed)
+
+    def fetch_rows(self, seg_idx, row_in_seg) -> np.ndarray:
+        seg_idx = np.ascontiguousarray(seg_idx, dtype=np.uint32)
+        row_in_seg = np.ascontiguousarray(row_in_seg, dtype=np.uint32)
+        out = np.zeros(len(seg_idx), dtype=self.dtype)
+        self.ctx.check(self.ctx.lib.adacom_codec_fetch_rows(self.h, len(seg_idx), _np_ptr(seg_idx), _np_ptr(row_in_seg),
+                                                            _np_ptr(out), 0))
+        return out
+
+
 def _wrap_i64(v: int) -> int:
     v = int(v)
     return v - (1 << 64) if v >= 1 << 63 else v

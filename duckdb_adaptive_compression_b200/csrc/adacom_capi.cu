@@ -12,6 +12,7 @@
 #include <atomic>
 #include <cmath>
 #include <map>
+#include <memory>
 #include <mutex>
 #include <new>
 #include <string>
@@ -2301,5 +2302,268 @@ extern "C" adacom_status adacom_column_restore(adacom_ctx *ctx, const void *imag
 		return st;
 	}
 	*out = col;
+	return ADACOM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// neighbour codecs: DuckDB bitpacking / RLE segment images (kernels_codecs.cu)
+// ---------------------------------------------------------------------------------------------------
+
+struct adacom_codec_column {
+	adacom_ctx *ctx = nullptr;
+	int codec = 0;
+	TypeInfo t {4, false};
+	uint64_t n_segs = 0, n_values = 0, image_bytes = 0;
+	uint8_t *d_images = nullptr;
+	CodecSeg *d_segs = nullptr;
+	std::vector<CodecSeg> h_segs;
+	Job *d_jobs = nullptr;        // (segment, 2048-value group) in segment order
+	std::vector<uint32_t> job_first;
+	Job *d_sum_jobs = nullptr;    // RLE SUM: (segment, tile of 2048 runs)
+	std::vector<uint32_t> sum_job_first;
+	uint32_t *d_run_start = nullptr;
+};
+
+extern "C" adacom_status adacom_codec_column_create(adacom_ctx *ctx, adacom_codec codec, adacom_ptype type,
+                                                    uint64_t n_segments, const uint8_t *const *segment_images,
+                                                    const uint64_t *segment_bytes, const uint64_t *tuple_counts,
+                                                    adacom_codec_column **out) {
+	if (!ctx || !out || (n_segments && (!segment_images || !segment_bytes || !tuple_counts)) ||
+	    ((int)codec != ADACOM_CODEC_BITPACKING && (int)codec != ADACOM_CODEC_RLE) || n_segments >= (1ull << 31)) {
+		return fail(ctx, ADACOM_ERR_INVALID, "adacom_codec_column_create: bad arguments");
+	}
+	TypeInfo t;
+	if (!type_info(type, t)) {
+		return fail(ctx, ADACOM_ERR_UNSUPPORTED, "adacom_codec_column_create: unsupported physical type");
+	}
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	CK(ctx, cudaSetDevice(ctx->device));
+	std::unique_ptr<adacom_codec_column> col(new adacom_codec_column());
+	col->ctx = ctx;
+	col->codec = (int)codec;
+	col->t = t;
+	col->n_segs = n_segments;
+	col->h_segs.resize(n_segments);
+	std::vector<Job> jobs, sum_jobs;
+	col->job_first.assign(n_segments + 1, 0);
+	col->sum_job_first.assign(n_segments + 1, 0);
+	uint64_t offset = 0, row = 0, runs = 0;
+	for (uint64_t g = 0; g < n_segments; g++) {
+		const uint64_t bytes = segment_bytes[g], count = tuple_counts[g];
+		if (bytes < 8 || bytes > kBlockSize || count >= (1ull << 32) || !segment_images[g]) {
+			return fail(ctx, ADACOM_ERR_INVALID, "adacom_codec_column_create: malformed segment image");
+		}
+		uint64_t head;
+		memcpy(&head, segment_images[g], 8);
+		CodecSeg &sd = col->h_segs[g];
+		sd.image_offset = offset;
+		sd.row_start = row;
+		sd.bytes = (uint32_t)bytes;
+		sd.count = (uint32_t)count;
+		sd.first_run = (uint32_t)runs;
+		sd.reserved = 0;
+		const uint64_t n_groups = (count + kVectorSize - 1) / kVectorSize;
+		if (codec == ADACOM_CODEC_BITPACKING) {
+			// the metadata entries sit right below `head`: one per group, all inside the image
+			if (head > bytes || head < 8 + 4 * n_groups) {
+				return fail(ctx, ADACOM_ERR_CORRUPT, "adacom_codec_column_create: bitpacking metadata offset out of range");
+			}
+			for (uint64_t k = 0; k < n_groups; k++) {
+				uint32_t entry;
+				memcpy(&entry, segment_images[g] + head - 4 * (k + 1), 4);
+				const uint32_t mode = entry >> 24, off = entry & 0x00FFFFFFu;
+				if (mode < 1 || mode > 4 || off < 8 || off + (uint64_t)t.size > head) {
+					return fail(ctx, ADACOM_ERR_CORRUPT, "adacom_codec_column_create: bitpacking group metadata malformed");
+				}
+			}
+		} else {
+			if (head > bytes || head < 8 || ((bytes - head) & 1)) {
+				return fail(ctx, ADACOM_ERR_CORRUPT, "adacom_codec_column_create: RLE count offset out of range");
+			}
+			const uint64_t n_runs = (bytes - head) / 2;
+			if (8 + n_runs * (uint64_t)t.size > head) {
+				return fail(ctx, ADACOM_ERR_CORRUPT, "adacom_codec_column_create: RLE values overlap the run lengths");
+			}
+			uint64_t total = 0;
+			for (uint64_t k = 0; k < n_runs; k++) {
+				uint16_t c;
+				memcpy(&c, segment_images[g] + head + 2 * k, 2);
+				total += c;
+			}
+			if (total < count) {
+				return fail(ctx, ADACOM_ERR_CORRUPT, "adacom_codec_column_create: RLE runs shorter than the tuple count");
+			}
+			for (uint64_t k = 0; k < (n_runs + kVectorSize - 1) / kVectorSize; k++) {
+				sum_jobs.push_back(Job {(uint32_t)g, (uint32_t)k});
+			}
+			runs += n_runs;
+		}
+		for (uint64_t k = 0; k < n_groups; k++) {
+			jobs.push_back(Job {(uint32_t)g, (uint32_t)k});
+		}
+		col->job_first[g + 1] = (uint32_t)jobs.size();
+		col->sum_job_first[g + 1] = (uint32_t)sum_jobs.size();
+		offset += (bytes + 15) & ~15ull;
+		row += count;
+	}
+	col->n_values = row;
+	col->image_bytes = offset;
+	CK(ctx, cudaMallocAsync((void **)&col->d_images, offset + kArenaPad, ctx->stream));
+	CK(ctx, cudaMemsetAsync(col->d_images + offset, 0, kArenaPad, ctx->stream));
+	for (uint64_t g = 0; g < n_segments; g++) {
+		CK(ctx, cudaMemcpyAsync(col->d_images + col->h_segs[g].image_offset, segment_images[g], segment_bytes[g],
+		                        cudaMemcpyHostToDevice, ctx->stream));
+	}
+	CK(ctx, cudaMallocAsync((void **)&col->d_segs, std::max<size_t>(n_segments, 1) * sizeof(CodecSeg), ctx->stream));
+	CK(ctx, cudaMemcpyAsync(col->d_segs, col->h_segs.data(), n_segments * sizeof(CodecSeg), cudaMemcpyHostToDevice, ctx->stream));
+	CK(ctx, cudaMallocAsync((void **)&col->d_jobs, std::max<size_t>(jobs.size(), 1) * sizeof(Job), ctx->stream));
+	CK(ctx, cudaMemcpyAsync(col->d_jobs, jobs.data(), jobs.size() * sizeof(Job), cudaMemcpyHostToDevice, ctx->stream));
+	if (codec == ADACOM_CODEC_RLE) {
+		CK(ctx, cudaMallocAsync((void **)&col->d_sum_jobs, std::max<size_t>(sum_jobs.size(), 1) * sizeof(Job), ctx->stream));
+		CK(ctx, cudaMemcpyAsync(col->d_sum_jobs, sum_jobs.data(), sum_jobs.size() * sizeof(Job), cudaMemcpyHostToDevice, ctx->stream));
+		CK(ctx, cudaMallocAsync((void **)&col->d_run_start, std::max<uint64_t>(runs, 1) * sizeof(uint32_t), ctx->stream));
+		CodecArgs a;
+		a.images = col->d_images;
+		a.segs = col->d_segs;
+		a.run_start = col->d_run_start;
+		LAUNCH(ctx, launch_rle_run_starts(a, 0, (uint32_t)n_segments, ctx->sm_count, ctx->stream));
+	}
+	CK(ctx, cudaStreamSynchronize(ctx->stream));  // the host vectors and the caller's images may go away now
+	*out = col.release();
+	return ADACOM_OK;
+}
+
+extern "C" void adacom_codec_column_destroy(adacom_codec_column *col) {
+	if (!col) {
+		return;
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	cudaSetDevice(ctx->device);
+	for (void *p : {(void *)col->d_images, (void *)col->d_segs, (void *)col->d_jobs, (void *)col->d_sum_jobs,
+	                (void *)col->d_run_start}) {
+		if (p) {
+			cudaFreeAsync(p, ctx->stream);
+		}
+	}
+	cudaStreamSynchronize(ctx->stream);
+	delete col;
+}
+
+extern "C" uint64_t adacom_codec_column_num_values(const adacom_codec_column *col) {
+	return col ? col->n_values : 0;
+}
+
+extern "C" uint64_t adacom_codec_column_image_bytes(const adacom_codec_column *col) {
+	return col ? col->image_bytes : 0;
+}
+
+static bool codec_range_ok(const adacom_codec_column *col, uint64_t b, uint64_t e) {
+	return col && b <= e && e <= col->n_segs;
+}
+
+static CodecArgs codec_args(adacom_codec_column *col, uint64_t b, uint64_t e, bool sum_jobs) {
+	CodecArgs a;
+	a.images = col->d_images;
+	a.segs = col->d_segs;
+	a.run_start = col->d_run_start;
+	if (sum_jobs) {
+		a.jobs = col->d_sum_jobs + col->sum_job_first[b];
+		a.n_jobs = col->sum_job_first[e] - col->sum_job_first[b];
+	} else {
+		a.jobs = col->d_jobs + col->job_first[b];
+		a.n_jobs = col->job_first[e] - col->job_first[b];
+	}
+	a.out_row0 = b < col->n_segs ? col->h_segs[b].row_start : 0;
+	return a;
+}
+
+extern "C" adacom_status adacom_codec_decode(adacom_codec_column *col, uint64_t seg_begin, uint64_t seg_end, void *out,
+                                             int out_on_device) {
+	if (!codec_range_ok(col, seg_begin, seg_end) || !out) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_codec_decode: bad arguments");
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	if (seg_begin == seg_end) {
+		return ADACOM_OK;
+	}
+	const CodecSeg &last = col->h_segs[seg_end - 1];
+	const uint64_t rows = last.row_start + last.count - col->h_segs[seg_begin].row_start;
+	if (rows == 0) {
+		return ADACOM_OK;
+	}
+	void *d_out = out;
+	if (!out_on_device) {
+		CK(ctx, cudaMallocAsync(&d_out, rows * col->t.size, ctx->stream));
+	}
+	CodecArgs a = codec_args(col, seg_begin, seg_end, false);
+	a.out = d_out;
+	LAUNCH(ctx, launch_codec_scan(col->t, col->codec, 0, a, ctx->sm_count, ctx->stream));
+	if (!out_on_device) {
+		CK(ctx, cudaMemcpyAsync(out, d_out, rows * col->t.size, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(ctx, cudaFreeAsync(d_out, ctx->stream));
+		CK(ctx, cudaStreamSynchronize(ctx->stream));
+	}
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_codec_scan_sum(adacom_codec_column *col, uint64_t seg_begin, uint64_t seg_end,
+                                               adacom_agg *out) {
+	if (!codec_range_ok(col, seg_begin, seg_end) || !out) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_codec_scan_sum: bad arguments");
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	CK(ctx, cudaMemsetAsync(ctx->d_agg, 0, sizeof(Agg), ctx->stream));
+	if (seg_begin != seg_end) {
+		CodecArgs a = codec_args(col, seg_begin, seg_end, col->codec == ADACOM_CODEC_RLE);
+		a.agg = ctx->d_agg;
+		LAUNCH(ctx, launch_codec_scan(col->t, col->codec, 1, a, ctx->sm_count, ctx->stream));
+	}
+	CK(ctx, cudaMemcpyAsync(ctx->h_agg, ctx->d_agg, sizeof(Agg), cudaMemcpyDeviceToHost, ctx->stream));
+	CK(ctx, cudaStreamSynchronize(ctx->stream));
+	memcpy(out, ctx->h_agg, sizeof(Agg));
+	if (col->codec == ADACOM_CODEC_RLE && seg_begin != seg_end) {
+		// the last run of a segment may be longer than the tuples it still covers; COUNT is the tuple count
+		const CodecSeg &last = col->h_segs[seg_end - 1];
+		out->count = last.row_start + last.count - col->h_segs[seg_begin].row_start;
+	}
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_codec_fetch_rows(adacom_codec_column *col, uint64_t n, const uint32_t *seg_idx,
+                                                 const uint32_t *row_in_seg, void *out, int on_device) {
+	if (!col || (n && (!seg_idx || !row_in_seg || !out)) || n >= (1ull << 26)) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_codec_fetch_rows: bad arguments");
+	}
+	adacom_ctx *ctx = col->ctx;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	if (n == 0) {
+		return ADACOM_OK;
+	}
+	CodecArgs a = codec_args(col, 0, 0, false);
+	if (on_device) {
+		a.out = out;
+		LAUNCH(ctx, launch_codec_fetch(col->t, col->codec, a, seg_idx, row_in_seg, n, ctx->stream));
+		return ADACOM_OK;
+	}
+	for (uint64_t q = 0; q < n; q++) {
+		if (seg_idx[q] >= col->n_segs || row_in_seg[q] >= col->h_segs[seg_idx[q]].count) {
+			return fail(ctx, ADACOM_ERR_INVALID, "adacom_codec_fetch_rows: (segment, row) out of range");
+		}
+	}
+	uint32_t *d_ids = nullptr;
+	void *d_out = nullptr;
+	CK(ctx, cudaMallocAsync((void **)&d_ids, 2 * n * sizeof(uint32_t), ctx->stream));
+	CK(ctx, cudaMallocAsync(&d_out, n * col->t.size, ctx->stream));
+	CK(ctx, cudaMemcpyAsync(d_ids, seg_idx, n * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+	CK(ctx, cudaMemcpyAsync(d_ids + n, row_in_seg, n * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+	a.out = d_out;
+	LAUNCH(ctx, launch_codec_fetch(col->t, col->codec, a, d_ids, d_ids + n, n, ctx->stream));
+	CK(ctx, cudaMemcpyAsync(out, d_out, n * col->t.size, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(ctx, cudaFreeAsync(d_ids, ctx->stream));
+	CK(ctx, cudaFreeAsync(d_out, ctx->stream));
+	CK(ctx, cudaStreamSynchronize(ctx->stream));
 	return ADACOM_OK;
 }

@@ -192,6 +192,31 @@ struct SelectArgs {
 };
 cudaError_t launch_select(TypeInfo t, const SelectArgs &args, int sm_count, cudaStream_t stream);
 
+// ---- neighbour codecs: DuckDB bitpacking / RLE segment images (kernels_codecs.cu) ----
+struct CodecSeg {
+	uint64_t image_offset;  // of the segment's block image inside the device arena (multiple of 16)
+	uint64_t row_start;     // first row of the segment inside the column
+	uint32_t bytes;         // image size
+	uint32_t count;         // tuples
+	uint32_t first_run;     // RLE: index of the segment's first run in the run_start array
+	uint32_t reserved;
+};
+struct CodecArgs {
+	const uint8_t *images = nullptr;
+	const CodecSeg *segs = nullptr;
+	const Job *jobs = nullptr;      // (segment, 2048-value group) -- or (segment, tile of 2048 runs) for the RLE SUM
+	uint32_t n_jobs = 0;
+	void *out = nullptr;            // decode: flat T values, out[row - out_row0]; fetch: one value per query
+	uint64_t out_row0 = 0;
+	Agg *agg = nullptr;
+	uint32_t *run_start = nullptr;  // RLE: exclusive prefix sums of the run lengths
+};
+// codec 0 = bitpacking, 1 = RLE; mode 0 = decode to flat values, 1 = fused SUM/COUNT
+cudaError_t launch_codec_scan(TypeInfo t, int codec, int mode, const CodecArgs &args, int sm_count, cudaStream_t stream);
+cudaError_t launch_codec_fetch(TypeInfo t, int codec, const CodecArgs &args, const uint32_t *seg_idx,
+                               const uint32_t *row_in_seg, uint64_t n, cudaStream_t stream);
+cudaError_t launch_rle_run_starts(const CodecArgs &args, uint32_t seg_b, uint32_t n_segs, int sm_count, cudaStream_t stream);
+
 // ---- checkpoint image (kernels_checkpoint.cu) ----
 constexpr uint32_t kBlockAllocSize = 262144;  // Storage::BLOCK_ALLOC_SIZE: 8-byte checksum + Storage::BLOCK_SIZE payload
 

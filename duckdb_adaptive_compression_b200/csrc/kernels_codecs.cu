@@ -1,0 +1,449 @@
+// kernels_codecs.cu -- SURVEY 8(f) row 4: the neighbour codecs of the succinct function, decoded on the GPU from the
+// segment images DuckDB itself writes.
+//
+//   bitpacking  src/storage/compression/bitpacking.cpp: a segment = [u64 offset of the metadata end | group payloads growing
+//               up | u32 metadata entries growing down (mode << 24 | payload offset), :60-73, :456-513]; every 2048 values
+//               (BITPACKING_METADATA_GROUP_SIZE) form a group in one of four modes (:576-632):
+//                 CONSTANT        [T constant]
+//                 CONSTANT_DELTA  [T frame_of_reference][T delta]                  value_i = i * delta + for
+//                 FOR             [T for][T width][packed]                         value_i = field_i + for
+//                 DELTA_FOR       [T for][T width][T delta_offset][packed]         value_i = delta_offset + sum_{j<=i}(field_j + for)
+//               packed = 32-value blocks of `width` bits, LSB first, in little-endian words (third_party/fastpforlib):
+//               one contiguous bit string per group, field i at bits [i*w, (i+1)*w) -- the same layout as the succinct
+//               codec's int_vector, only byte- instead of word-addressed (the payload is merely sizeof(T)-aligned).
+//               Scan / fetch semantics: BitpackingScanPartial :729-811, BitpackingFetchRow :823-866.
+//   RLE         src/storage/compression/rle.cpp: [u64 offset of the counts | T values[runs] | u16 counts[runs]] (:170-215);
+//               RLEScanPartial / RLEFetchRow :298-331.
+//
+// One CTA works on one metadata group (bitpacking) or one 2048-row tile (RLE) at a time: the group's payload is staged in
+// shared memory with aligned 4-byte loads (the misalignment becomes a bit offset), lanes take consecutive values, so the
+// stores are coalesced; DELTA_FOR runs a block-wide prefix sum.  Fused SUM never materialises the values.
+#include "adacom_kernels.cuh"
+
+namespace adacom {
+
+namespace {
+
+constexpr int kCodecThreads = 256;
+constexpr uint32_t kGroupValues = 2048;
+enum : uint32_t { kBpConstant = 1, kBpConstantDelta = 2, kBpDeltaFor = 3, kBpFor = 4 };
+
+__device__ __forceinline__ uint64_t load_bytes(const uint8_t *p, int n) {
+	uint64_t v = 0;
+	for (int b = 0; b < n; b++) {
+		v |= (uint64_t)__ldg(p + b) << (8 * b);
+	}
+	return v;
+}
+
+// header of one bitpacking group, resolved by one thread and broadcast through shared memory
+struct GroupHeader {
+	uint64_t frame, constant, delta_offset;
+	uint32_t mode, width, data_off, count;
+};
+
+template <int S>
+__device__ __forceinline__ GroupHeader read_group_header(const uint8_t *img, uint32_t seg_count, uint32_t g) {
+	GroupHeader h;
+	const uint64_t meta_end = *(const uint64_t *)img;  // images start 16-byte aligned
+	const uint32_t entry = (uint32_t)load_bytes(img + meta_end - 4ull * (g + 1), 4);
+	h.mode = entry >> 24;
+	uint32_t off = entry & 0x00FFFFFFu;
+	h.frame = h.constant = h.delta_offset = 0;
+	h.width = 0;
+	h.count = min(kGroupValues, seg_count - g * kGroupValues);
+	if (h.mode == kBpConstant) {
+		h.constant = load_bytes(img + off, S);
+		off += S;
+	} else {
+		h.frame = load_bytes(img + off, S);
+		off += S;
+		if (h.mode == kBpConstantDelta) {
+			h.constant = load_bytes(img + off, S);
+			off += S;
+		} else {
+			h.width = (uint32_t)load_bytes(img + off, S) & 0xffu;
+			off += S;
+			if (h.mode == kBpDeltaFor) {
+				h.delta_offset = load_bytes(img + off, S);
+				off += S;
+			}
+		}
+	}
+	h.data_off = off;
+	return h;
+}
+
+// w-bit field at bit position `bit` of a staged 32-bit word array (w <= 64; two pad words behind the data)
+__device__ __forceinline__ uint64_t field_at(const uint32_t *words, uint32_t bit, uint32_t w) {
+	const uint32_t idx = bit >> 5, sh = bit & 31u;
+	const uint32_t a = words[idx], b = words[idx + 1], c = words[idx + 2];
+	const uint64_t v = ((uint64_t)__funnelshift_r(b, c, sh) << 32) | __funnelshift_r(a, b, sh);
+	return v & lo_set64(w);
+}
+
+template <int S>
+__device__ __forceinline__ uint64_t trunc_T(uint64_t v) {
+	return S == 8 ? v : (v & ((1ull << (8 * (S & 7))) - 1ull));
+}
+
+// MODE 0: decode into out[(row_start + i) - out_row0]; MODE 1: fused SUM/COUNT
+template <int S, bool SIGNED, int MODE>
+__global__ void __launch_bounds__(kCodecThreads) bitpacking_groups_kernel(CodecArgs a) {
+	using T = typename UIntOf<S>::type;
+	__shared__ __align__(16) uint32_t stage[kGroupValues * 64 / 32 + 8];
+	__shared__ GroupHeader hdr;
+	__shared__ uint64_t warp_tot[kCodecThreads / 32];
+	__shared__ uint64_t red[96];
+	const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+	Acc96 acc;
+	uint32_t n_rows = 0;
+	for (uint32_t j = blockIdx.x; j < a.n_jobs; j += gridDim.x) {
+		const Job job = a.jobs[j];
+		const CodecSeg seg = a.segs[job.seg];
+		const uint8_t *img = a.images + seg.image_offset;
+		__syncthreads();  // the previous group has been consumed
+		if (tid == 0) {
+			hdr = read_group_header<S>(img, seg.count, job.k);
+		}
+		__syncthreads();
+		const GroupHeader h = hdr;
+		const uint32_t cnt = h.count, w = h.width;
+		T *out = MODE == 0 ? (T *)a.out + (seg.row_start + (uint64_t)job.k * kGroupValues - a.out_row0) : nullptr;
+		uint32_t mis_bits = 0;
+		if (h.mode == kBpFor || h.mode == kBpDeltaFor) {
+			// stage ceil(cnt / 32) * 4 * w payload bytes; the source is only sizeof(T)-aligned
+			const uint8_t *src = img + h.data_off;
+			const uint32_t mis = (uint32_t)((uintptr_t)src & 3u);
+			const uint32_t *src4 = (const uint32_t *)(src - mis);
+			const uint32_t n_words = (mis + ((cnt + 31u) / 32u) * 4u * w + 3u) / 4u;
+			for (uint32_t t = tid; t < n_words; t += kCodecThreads) {
+				stage[t] = __ldg(src4 + t);
+			}
+			if (tid < 4) {
+				stage[n_words + tid] = 0u;  // the funnel's look-ahead words
+			}
+			mis_bits = mis * 8u;
+			__syncthreads();
+		}
+		if (h.mode == kBpDeltaFor) {
+			// blocked: thread t owns values [8t, 8t + 8); running sum of (field + for) in T arithmetic
+			uint64_t d[8];
+			uint64_t run = 0;
+#pragma unroll
+			for (int k = 0; k < 8; k++) {
+				const uint32_t i = tid * 8u + k;
+				const uint64_t f = i < cnt ? field_at(stage, mis_bits + i * w, w) + h.frame : 0ull;
+				run += f;
+				d[k] = run;
+			}
+			uint64_t incl = run;
+#pragma unroll
+			for (int s = 1; s < 32; s <<= 1) {
+				const uint64_t o = __shfl_up_sync(0xffffffffu, incl, s);
+				if (lane >= (uint32_t)s) {
+					incl += o;
+				}
+			}
+			if (lane == 31) {
+				warp_tot[warp] = incl;
+			}
+			__syncthreads();
+			uint64_t base = h.delta_offset + incl - run;
+			for (uint32_t wi = 0; wi < warp; wi++) {
+				base += warp_tot[wi];
+			}
+#pragma unroll
+			for (int k = 0; k < 8; k++) {
+				const uint32_t i = tid * 8u + k;
+				if (i < cnt) {
+					const uint64_t v = trunc_T<S>(base + d[k]);
+					if (MODE == 0) {
+						out[i] = (T)v;
+					} else {
+						acc.add<SIGNED>(extend_low<S, SIGNED>(v));
+						n_rows++;
+					}
+				}
+			}
+		} else {
+			for (uint32_t i = tid; i < cnt; i += kCodecThreads) {
+				uint64_t v;
+				if (h.mode == kBpFor) {
+					v = field_at(stage, mis_bits + i * w, w) + h.frame;
+				} else if (h.mode == kBpConstant) {
+					v = h.constant;
+				} else {
+					// (group_offset + i) * constant + frame in idx_t arithmetic, truncated to T (bitpacking.cpp:757-760)
+					v = (uint64_t)i * extend_low<S, SIGNED>(h.constant) + extend_low<S, SIGNED>(h.frame);
+				}
+				v = trunc_T<S>(v);
+				if (MODE == 0) {
+					out[i] = (T)v;
+				} else {
+					acc.add<SIGNED>(extend_low<S, SIGNED>(v));
+					n_rows++;
+				}
+			}
+		}
+	}
+	if (MODE == 1) {
+		block_reduce_agg(acc.lo64(), acc.hi64(), (uint64_t)n_rows, red, a.agg);
+	}
+}
+
+// one warp per (segment, row): BitpackingFetchRow
+template <int S, bool SIGNED>
+__global__ void __launch_bounds__(kCodecThreads) bitpacking_fetch_kernel(CodecArgs a, const uint32_t *seg_idx,
+                                                                         const uint32_t *row_in_seg, uint64_t n) {
+	using T = typename UIntOf<S>::type;
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint64_t q = ((uint64_t)blockIdx.x * kCodecThreads + threadIdx.x) >> 5;
+	if (q >= n) {
+		return;
+	}
+	const CodecSeg seg = a.segs[seg_idx[q]];
+	const uint8_t *img = a.images + seg.image_offset;
+	const uint32_t row = row_in_seg[q], g = row / kGroupValues, r = row % kGroupValues;
+	GroupHeader h;
+	if (lane == 0) {
+		h = read_group_header<S>(img, seg.count, g);
+	}
+	h.frame = __shfl_sync(0xffffffffu, h.frame, 0);
+	h.constant = __shfl_sync(0xffffffffu, h.constant, 0);
+	h.delta_offset = __shfl_sync(0xffffffffu, h.delta_offset, 0);
+	h.mode = __shfl_sync(0xffffffffu, h.mode, 0);
+	h.width = __shfl_sync(0xffffffffu, h.width, 0);
+	h.data_off = __shfl_sync(0xffffffffu, h.data_off, 0);
+	const uint8_t *src = img + h.data_off;
+	const uint32_t w = h.width;
+	auto field = [&](uint32_t i) -> uint64_t {
+		const uint64_t bit = (uint64_t)i * w;
+		const uint8_t *p = src + (bit >> 3);
+		const uint32_t sh = (uint32_t)(bit & 7u);
+		const uint32_t need = (sh + w + 7u) >> 3;  // <= 9 bytes
+		uint64_t lo = load_bytes(p, need < 8 ? (int)need : 8);
+		uint64_t v = lo >> sh;
+		if (need > 8) {
+			v |= (uint64_t)__ldg(p + 8) << (64u - sh);
+		}
+		return v & lo_set64(w);
+	};
+	uint64_t v = 0;
+	if (h.mode == kBpConstant) {
+		v = h.constant;
+	} else if (h.mode == kBpConstantDelta) {
+		v = (uint64_t)r * extend_low<S, SIGNED>(h.constant) + extend_low<S, SIGNED>(h.frame);
+	} else if (h.mode == kBpFor) {
+		v = lane == 0 ? field(r) + h.frame : 0ull;
+	} else {
+		uint64_t part = 0;
+		for (uint32_t i = lane; i <= r; i += 32u) {
+			part += field(i) + h.frame;
+		}
+#pragma unroll
+		for (int s = 16; s > 0; s >>= 1) {
+			part += __shfl_down_sync(0xffffffffu, part, s);
+		}
+		v = part + h.delta_offset;
+	}
+	if (lane == 0) {
+		((T *)a.out)[q] = (T)trunc_T<S>(v);
+	}
+}
+
+// ---- RLE ----
+// exclusive prefix sums of the run lengths of every segment (one CTA per segment): run_start[first_run + k]
+__global__ void __launch_bounds__(kCodecThreads) rle_run_starts_kernel(CodecArgs a, uint32_t seg_b, uint32_t n_segs) {
+	__shared__ uint32_t warp_tot[kCodecThreads / 32];
+	__shared__ uint32_t carry;
+	const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+	for (uint32_t s = seg_b + blockIdx.x; s < seg_b + n_segs; s += gridDim.x) {
+		const CodecSeg seg = a.segs[s];
+		const uint8_t *img = a.images + seg.image_offset;
+		const uint64_t counts_off = *(const uint64_t *)img;
+		const uint16_t *counts = (const uint16_t *)(img + counts_off);
+		const uint32_t n_runs = (seg.bytes - (uint32_t)counts_off) / 2u;
+		if (tid == 0) {
+			carry = 0;
+		}
+		__syncthreads();
+		for (uint32_t base = 0; base < n_runs; base += kCodecThreads) {
+			const uint32_t k = base + tid;
+			const uint32_t c = k < n_runs ? (uint32_t)__ldg(counts + k) : 0u;
+			uint32_t incl = c;
+#pragma unroll
+			for (int d = 1; d < 32; d <<= 1) {
+				const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+				if (lane >= (uint32_t)d) {
+					incl += o;
+				}
+			}
+			if (lane == 31) {
+				warp_tot[warp] = incl;
+			}
+			__syncthreads();
+			uint32_t off = carry;
+			for (uint32_t wi = 0; wi < warp; wi++) {
+				off += warp_tot[wi];
+			}
+			if (k < n_runs) {
+				a.run_start[seg.first_run + k] = off + incl - c;
+			}
+			__syncthreads();
+			if (tid == kCodecThreads - 1) {
+				carry = off + incl;
+			}
+			__syncthreads();
+		}
+	}
+}
+
+__device__ __forceinline__ uint32_t rle_find_run(const uint32_t *starts, uint32_t n_runs, uint32_t row) {
+	uint32_t lo = 0, hi = n_runs;  // last run whose start <= row
+	while (hi - lo > 1) {
+		const uint32_t mid = (lo + hi) >> 1;
+		if (__ldg(starts + mid) <= row) {
+			lo = mid;
+		} else {
+			hi = mid;
+		}
+	}
+	return lo;
+}
+
+// MODE 0: decode 2048-row tiles; MODE 1: SUM = sum_runs value * length (job = 2048 runs of a segment)
+template <int S, bool SIGNED, int MODE>
+__global__ void __launch_bounds__(kCodecThreads) rle_kernel(CodecArgs a) {
+	using T = typename UIntOf<S>::type;
+	__shared__ uint64_t red[96];
+	const uint32_t tid = threadIdx.x;
+	uint64_t lo = 0, hi = 0, rows = 0;
+	for (uint32_t j = blockIdx.x; j < a.n_jobs; j += gridDim.x) {
+		const Job job = a.jobs[j];
+		const CodecSeg seg = a.segs[job.seg];
+		const uint8_t *img = a.images + seg.image_offset;
+		const uint64_t counts_off = *(const uint64_t *)img;
+		const uint32_t n_runs = (seg.bytes - (uint32_t)counts_off) / 2u;
+		const T *values = (const T *)(img + 8);
+		const uint32_t *starts = a.run_start + seg.first_run;
+		if (MODE == 0) {
+			const uint32_t first = job.k * kGroupValues;
+			if (first >= seg.count) {
+				continue;
+			}
+			const uint32_t cnt = min(kGroupValues, seg.count - first);
+			T *out = (T *)a.out + (seg.row_start + first - a.out_row0);
+			for (uint32_t i = tid; i < cnt; i += kCodecThreads) {
+				out[i] = __ldg(values + rle_find_run(starts, n_runs, first + i));
+			}
+		} else {
+			const uint16_t *counts = (const uint16_t *)(img + counts_off);
+			const uint32_t first = job.k * kGroupValues;
+			for (uint32_t k = first + tid; k < min(n_runs, first + kGroupValues); k += kCodecThreads) {
+				const uint64_t v = extend_low<S, SIGNED>((uint64_t)__ldg(values + k));
+				const uint64_t c = (uint64_t)__ldg(counts + k);
+				// 128-bit v * c (c < 2^16)
+				uint64_t plo = v * c;
+				uint64_t phi = __umul64hi(v, c);
+				if (SIGNED && (int64_t)v < 0) {
+					phi -= c;
+				}
+				add128(lo, hi, plo, phi);
+				rows += c;
+			}
+		}
+	}
+	if (MODE == 1) {
+		block_reduce_agg(lo, hi, rows, red, a.agg);
+	}
+}
+
+template <int S, bool SIGNED>
+__global__ void __launch_bounds__(kCodecThreads) rle_fetch_kernel(CodecArgs a, const uint32_t *seg_idx,
+                                                                  const uint32_t *row_in_seg, uint64_t n) {
+	using T = typename UIntOf<S>::type;
+	const uint64_t q = (uint64_t)blockIdx.x * kCodecThreads + threadIdx.x;
+	if (q >= n) {
+		return;
+	}
+	const CodecSeg seg = a.segs[seg_idx[q]];
+	const uint8_t *img = a.images + seg.image_offset;
+	const uint64_t counts_off = *(const uint64_t *)img;
+	const uint32_t n_runs = (seg.bytes - (uint32_t)counts_off) / 2u;
+	((T *)a.out)[q] = __ldg((const T *)(img + 8) + rle_find_run(a.run_start + seg.first_run, n_runs, row_in_seg[q]));
+}
+
+template <int S, bool SIGNED>
+cudaError_t launch_typed(int codec, int mode, const CodecArgs &a, uint32_t grid, cudaStream_t stream) {
+	if (codec == 0) {
+		if (mode == 0) {
+			bitpacking_groups_kernel<S, SIGNED, 0><<<grid, kCodecThreads, 0, stream>>>(a);
+		} else {
+			bitpacking_groups_kernel<S, SIGNED, 1><<<grid, kCodecThreads, 0, stream>>>(a);
+		}
+	} else {
+		if (mode == 0) {
+			rle_kernel<S, SIGNED, 0><<<grid, kCodecThreads, 0, stream>>>(a);
+		} else {
+			rle_kernel<S, SIGNED, 1><<<grid, kCodecThreads, 0, stream>>>(a);
+		}
+	}
+	return cudaGetLastError();
+}
+
+template <int S, bool SIGNED>
+cudaError_t fetch_typed(int codec, const CodecArgs &a, const uint32_t *seg_idx, const uint32_t *row_in_seg, uint64_t n,
+                        cudaStream_t stream) {
+	if (codec == 0) {
+		const uint64_t blocks = (n * 32 + kCodecThreads - 1) / kCodecThreads;
+		bitpacking_fetch_kernel<S, SIGNED><<<(uint32_t)blocks, kCodecThreads, 0, stream>>>(a, seg_idx, row_in_seg, n);
+	} else {
+		const uint64_t blocks = (n + kCodecThreads - 1) / kCodecThreads;
+		rle_fetch_kernel<S, SIGNED><<<(uint32_t)blocks, kCodecThreads, 0, stream>>>(a, seg_idx, row_in_seg, n);
+	}
+	return cudaGetLastError();
+}
+
+#define CODEC_DISPATCH(fn, ...)                                                                             \
+	switch (t.size * 2 + (t.is_signed ? 1 : 0)) {                                                           \
+	case 2: return fn<1, false>(__VA_ARGS__);                                                               \
+	case 3: return fn<1, true>(__VA_ARGS__);                                                                \
+	case 4: return fn<2, false>(__VA_ARGS__);                                                               \
+	case 5: return fn<2, true>(__VA_ARGS__);                                                                \
+	case 8: return fn<4, false>(__VA_ARGS__);                                                               \
+	case 9: return fn<4, true>(__VA_ARGS__);                                                                \
+	case 16: return fn<8, false>(__VA_ARGS__);                                                              \
+	case 17: return fn<8, true>(__VA_ARGS__);                                                               \
+	default: return cudaErrorInvalidValue;                                                                  \
+	}
+
+}  // namespace
+
+cudaError_t launch_codec_scan(TypeInfo t, int codec, int mode, const CodecArgs &a, int sm_count, cudaStream_t stream) {
+	if (a.n_jobs == 0) {
+		return cudaSuccess;
+	}
+	const uint32_t resident = (uint32_t)sm_count * 4u;
+	const uint32_t grid = a.n_jobs < resident ? a.n_jobs : resident;
+	CODEC_DISPATCH(launch_typed, codec, mode, a, grid, stream)
+}
+
+cudaError_t launch_codec_fetch(TypeInfo t, int codec, const CodecArgs &a, const uint32_t *seg_idx, const uint32_t *row_in_seg,
+                               uint64_t n, cudaStream_t stream) {
+	if (n == 0) {
+		return cudaSuccess;
+	}
+	CODEC_DISPATCH(fetch_typed, codec, a, seg_idx, row_in_seg, n, stream)
+}
+
+cudaError_t launch_rle_run_starts(const CodecArgs &a, uint32_t seg_b, uint32_t n_segs, int sm_count, cudaStream_t stream) {
+	if (n_segs == 0) {
+		return cudaSuccess;
+	}
+	const uint32_t resident = (uint32_t)sm_count * 4u;
+	rle_run_starts_kernel<<<n_segs < resident ? n_segs : resident, kCodecThreads, 0, stream>>>(a, seg_b, n_segs);
+	return cudaGetLastError();
+}
+
+}  // namespace adacom

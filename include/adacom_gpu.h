@@ -379,6 +379,34 @@ adacom_status adacom_column_checkpoint(adacom_column *col, void *out, uint64_t c
 adacom_status adacom_column_restore(adacom_ctx *ctx, const void *image, uint64_t bytes, int image_on_device,
                                     adacom_column **out);
 
+/* ---- neighbour codecs on the same GPU ------------------------------------------------------- */
+/* DuckDB's BitpackingFun and RLEFun segments, decoded from the block images DuckDB itself writes at checkpoint time
+ * (the `compress` slots of src/storage/compression/bitpacking.cpp:350-528 and rle.cpp:117-245):
+ *   bitpacking: [u64 end of metadata | group payloads | u32 metadata entries (mode << 24 | offset)], 2048-value groups in
+ *               CONSTANT / CONSTANT_DELTA / DELTA_FOR / FOR mode, payload packed by third_party/fastpforlib;
+ *   RLE:        [u64 offset of the run lengths | T values[runs] | u16 lengths[runs]].
+ * Entry points replace BitpackingScan / BitpackingScanPartial (bitpacking.cpp:729-816), BitpackingFetchRow (:823-866),
+ * RLEScan / RLEScanPartial (rle.cpp:298-322) and RLEFetchRow (:327-341); the fused SUM replaces scan + aggregate.
+ * Validity lives in a separate column in DuckDB, so every slot decodes to whatever the compressor stored. */
+typedef enum { ADACOM_CODEC_BITPACKING = 0, ADACOM_CODEC_RLE = 1 } adacom_codec;
+typedef struct adacom_codec_column adacom_codec_column;
+/* n_segments block images (host pointers, segment_bytes[g] bytes each, as handed to ColumnCheckpointState::FlushSegment)
+ * holding tuple_counts[g] values each; the images are copied into one device arena. */
+adacom_status adacom_codec_column_create(adacom_ctx *ctx, adacom_codec codec, adacom_ptype type, uint64_t n_segments,
+                                         const uint8_t *const *segment_images, const uint64_t *segment_bytes,
+                                         const uint64_t *tuple_counts, adacom_codec_column **out);
+void adacom_codec_column_destroy(adacom_codec_column *col);
+uint64_t adacom_codec_column_num_values(const adacom_codec_column *col);
+uint64_t adacom_codec_column_image_bytes(const adacom_codec_column *col);
+/* batched scan of [seg_begin, seg_end) into a flat T array (device pointer when out_on_device, then asynchronous) */
+adacom_status adacom_codec_decode(adacom_codec_column *col, uint64_t seg_begin, uint64_t seg_end, void *out,
+                                  int out_on_device);
+/* fused decode + SUM/COUNT (RLE: sum of value * run length, the rows are never expanded) */
+adacom_status adacom_codec_scan_sum(adacom_codec_column *col, uint64_t seg_begin, uint64_t seg_end, adacom_agg *out);
+/* batched fetch_row: out[q] = value(seg_idx[q], row_in_seg[q]); host pointers unless on_device */
+adacom_status adacom_codec_fetch_rows(adacom_codec_column *col, uint64_t n, const uint32_t *seg_idx,
+                                      const uint32_t *row_in_seg, void *out, int on_device);
+
 /* ---- host-buffer convenience paths (what bench.py's e2e leg times) ------------------------------------ */
 /* host T values -> analyze + encode on the GPU -> metas (+ packed words when host_words_out != NULL,
  * capacity in words; *total_words_out receives the arena size). The column stays resident in *col_out. */

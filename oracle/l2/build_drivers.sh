@@ -80,4 +80,8 @@ ar r "$GPU/libduckdb_gpu.a" "$GPU/ub_duckdb_storage_table.cpp.o" "$GPU/ub_duckdb
 CSRC="$REPO/duckdb_adaptive_compression_b200/csrc"
 $CXX -o "$BIN/l2_driver_gpu" "$GPU/l2_driver.o" "$GPU/succinct_gpu.o" -Wl,--start-group "$GPU/libduckdb_gpu.a" $LIBS_COMMON -Wl,--end-group \
   -L"$CSRC" -ladacom_gpu -Wl,-rpath,'$ORIGIN/../../../duckdb_adaptive_compression_b200/csrc' -lpthread -ldl -static-libstdc++ -static-libgcc
-ls -la "$BIN"
+# ---- oracle for the neighbour codecs: the reference's bitpacking.cpp / rle.cpp + fastpforlib ----
+$CXX $FLAGS -I"$REFERENCE" -shared -o "$OUT/libadacom_codecs_ref.so" "$HERE/codecs_ref.cpp" \
+  -Wl,--allow-multiple-definition -Wl,--start-group "$BUILD/src/libduckdb_static.a" $LIBS_COMMON -Wl,--end-group \
+  -lpthread -ldl -static-libstdc++ -static-libgcc
+ls -la "$BIN" "$OUT/libadacom_codecs_ref.so"
