@@ -19,7 +19,7 @@ def _need_oracle():
         pytest.skip("oracle/_ref/libadacom_codecs_ref.so not built (needs /root/reference + oracle/l2/build_drivers.sh)")
 
 
-def _width_sweep_values(dtype, n_per_width=2048 * 2 + 100):
+def _width_sweep_values(dtype, n_per_width=2048 * 2):
     """groups whose FOR width sweeps 1 .. 8S (value = base + U[0, 2^w)), plus constant, constant-delta and sorted
     (delta-friendly) stretches and a ragged tail"""
     dt = np.dtype(dtype)
