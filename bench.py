@@ -53,7 +53,7 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-log2-values", type=int, default=21)
     ap.add_argument("--detail", default="", help="write the per-width table to this JSON file")
-    ap.add_argument("--configs", default="1,3,4,5", help="the other BASELINE.json workload shapes to run after the "
+    ap.add_argument("--configs", default="1,3,4,5,codecs", help="the other BASELINE.json workload shapes to run after the "
                     "headline sweep (1 Zipf point filters, 3 skew sweep + policy epochs, 4 TPC-H SF10 Q6/Q1, "
                     "5 TPC-H SF100 sharded Q6 over NCCL); '' = none")
     return ap.parse_args()
@@ -464,6 +464,8 @@ def run_configs(args, ctx, rank, world, peak):
         leg("3_zipf_skew_sweep", lambda: workloads.config3_skews(ctx, peak, threads), True)
     if "4" in wanted:
         leg("4_tpch_sf10", lambda: workloads.config4_tpch(ctx, peak, threads), True)
+    if "codecs" in wanted:
+        leg("f4_neighbour_codecs", lambda: workloads.neighbour_codecs(ctx, peak, threads), True)
     if "5" in wanted:
         leg("5_tpch_sf100_sharded", lambda: workloads.config5_tpch_sharded(ctx, peak, rank, world), False)
     return out if rank == 0 else None

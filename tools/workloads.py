@@ -109,7 +109,7 @@ def config1_zipf(ctx, peak, threads, rows=100_000_000, lookups=10_000, steps=5, 
 # ---------------------------------------------------------------------------------------------------------------------
 # config 3
 # ---------------------------------------------------------------------------------------------------------------------
-def config3_skews(ctx, peak, threads, rows=1 << 28, keys_per_skew=20_000, epochs=3, skews=SKEWS, cpu_skews=(0.0, 1.0, 2.0)):
+def config3_skews(ctx, peak, threads, rows=1 << 28, keys_per_skew=100_000, epochs=3, skews=SKEWS, cpu_skews=(0.0, 1.0, 2.0)):
     import duckdb_adaptive_compression_b200 as adacom
     from duckdb_adaptive_compression_b200.zipf import zipf_keys
     import oracle
@@ -380,3 +380,68 @@ def config5_tpch_sharded(ctx, peak, rank, world, sf=100.0, steps=10, warmup=3, d
                                                            "roofline": roof, "revenue_scale4": str(total_sum)},
             "value": round(rows_all / (ms * 1e-3)), "unit": "rows/s (Q6, all GPUs)",
             "timed": "CUDA events on the codec's stream around scan_columns + all_gather, max over ranks"}
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# the neighbour codecs (DuckDB bitpacking / RLE segments) on the same GPU
+# ---------------------------------------------------------------------------------------------------------------------
+def neighbour_codecs(ctx, peak, threads, log2_values=26, steps=5, warmup=3):
+    """bitpacking (FOR groups, 17-bit payloads) and RLE (runs of 1..8) over 2^log2_values INT32 values: batched scan to
+    flat vectors and fused SUM, device-timed; CPU baseline = the reference's own BitpackingScanPartial / RLEScanPartial
+    loops (oracle/_ref/libadacom_codecs_ref.so) over `threads` host threads, one segment per task."""
+    import concurrent.futures as cf
+    import torch
+    import duckdb_adaptive_compression_b200 as adacom
+    from oracle import codecs
+    from tests.cases import splitmix64
+    if not codecs.available():
+        return {"error": "oracle/_ref/libadacom_codecs_ref.so not built (needs /root/reference)"}
+    n = 1 << log2_values
+    dev = torch.device("cuda", ctx.device)
+    flat = torch.empty(n * 4 + 256, dtype=torch.uint8, device=dev)
+    out = {"workload": f"DuckDB bitpacking (FOR, 17-bit) and RLE (runs of 1..8) segments, 2^{log2_values} INT32 values, "
+                       f"scan -> flat vectors and fused SUM", "values": n}
+    r = splitmix64(np.arange(n, dtype=np.uint64) + np.uint64(0xB17)).astype(np.uint64)
+    inputs = {"bitpacking": ((r & np.uint64((1 << 17) - 1)).astype(np.int64) + 1000).astype(np.int32),
+              "rle": np.repeat(((r[: n // 4] >> np.uint64(20)) & np.uint64(0xFFFFF)).astype(np.int32),
+                               (r[: n // 4] & np.uint64(7)).astype(np.int64) + 1)[:n]}
+    for name, vals in inputs.items():
+        codec = adacom.CODEC_BITPACKING if name == "bitpacking" else adacom.CODEC_RLE
+        vals = np.ascontiguousarray(vals)
+        ref = codecs.RefCodecColumn(vals, codec=codecs.BITPACKING if name == "bitpacking" else codecs.RLE)
+        col = adacom.CodecColumn(ctx, codec, np.int32, ref.images, ref.counts)
+        m = len(vals)
+        col.decode(device_out=flat.data_ptr())
+        ctx.synchronize()
+        got = flat[: m * 4].view(torch.int32).cpu().numpy()
+        assert np.array_equal(got, vals), f"{name}: GPU decode differs from the input"
+        agg = col.scan_sum()
+        assert agg.sum == int(vals.astype(np.int64).sum()) and agg.count == m, f"{name}: fused SUM wrong"
+        dec_ms = _dev_timed(ctx, lambda: col.decode(device_out=flat.data_ptr()), steps, warmup)
+        sum_ms = _dev_timed(ctx, lambda: col.scan_sum(), steps, warmup)
+        img = col.image_bytes
+        entry = {"segments": len(ref.counts), "image_bytes": int(img),
+                 "decode": {"ms": round(dec_ms, 4), "roofline": _roof(img + m * 4, dec_ms, peak)},
+                 "scan_sum": {"ms": round(sum_ms, 4), "roofline": _roof(img, sum_ms, peak),
+                              "timed": "incl. the D2H of the aggregate (synchronous call)"}}
+        col.close()
+        # CPU: the reference's scan loop per segment in 2048-value vectors, segments dealt over the host threads
+        k_seg = min(len(ref.counts), max(threads * 2, 8))
+        def scan_seg(s):
+            c = ref.counts[s]
+            for off in range(0, c, 2048 * 16):
+                ref.scan(s, off, min(2048 * 16, c - off))
+            return c
+        t0 = time.perf_counter()
+        with cf.ThreadPoolExecutor(threads) as ex:
+            rows = sum(ex.map(scan_seg, range(k_seg)))
+        secs = time.perf_counter() - t0
+        entry["cpu_baseline"] = {"value": round(rows * 4 / secs / 1e9, 3), "unit": "GB/s decoded", "cores": threads,
+                                 "kind": "reference", "sample": f"the first {k_seg} segments ({rows} values) through the "
+                                 f"reference's own scan loop (fresh scan state + Skip per 32768-value slice), one segment per "
+                                 f"task over {threads} threads"}
+        entry["decode"]["logical_GBs"] = round(m * 4 / (dec_ms * 1e-3) / 1e9, 1)
+        out[name] = entry
+    out["value"] = out["bitpacking"]["decode"]["logical_GBs"]
+    out["unit"] = "GB/s decoded (bitpacking scan -> flat)"
+    return out
