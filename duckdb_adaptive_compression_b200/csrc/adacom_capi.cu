@@ -1636,10 +1636,10 @@ static adacom_status plan_scan_columns(adacom_ctx *ctx, const adacom_scan_term *
 	q.dense_groups = 0;
 	if (n_groups && q.narrow_products) {
 		const uint32_t dense_smem = scan_columns_group_smem(n_groups, n_sums, 1);
-		for (uint32_t r : {4096u, 2048u}) {
+		for (uint32_t r : {2048u, 4096u}) {  // lane = row in the dense path: the small block leaves room for a third CTA
 			const uint64_t blocks = (n_rows + r - 1) / r;
 			const uint64_t ctas = std::min<uint64_t>(std::max<uint64_t>(blocks, 1), (uint64_t)ctx->sm_count);
-			const long double rows_per_thread = (long double)((blocks + ctas - 1) / ctas) * (r / 256u);
+			const long double rows_per_thread = (long double)((blocks + ctas - 1) / ctas) * (r / (32u * kQueryConsumerWarps));
 			if (!R && 2 * stage_bytes(r) + dense_smem <= 87u * 1024u && max_prod * rows_per_thread < ldexpl(1.0L, 62)) {
 				R = r;
 				stages = 2;
@@ -1648,7 +1648,7 @@ static adacom_status plan_scan_columns(adacom_ctx *ctx, const adacom_scan_term *
 		}
 	}
 	const uint32_t group_smem = n_groups ? scan_columns_group_smem(n_groups, n_sums, 0) : 0u;
-	for (uint32_t r : {8192u, 4096u, 2048u}) {
+	for (uint32_t r : {4096u, 2048u}) {  // <= kQueryMaxBlockRows: one 32-row group per consumer lane
 		for (uint32_t st : {3u, 2u}) {
 			// + ~26 KiB static (+ the GROUP BY scratch): three CTAs per SM
 			if (!R && st * stage_bytes(r) + group_smem <= 48u * 1024u) {

@@ -65,6 +65,8 @@ constexpr int kQueryMaxPieces = 3;   // segments of one column a row block may t
 constexpr int kQueryMaxAggs = 8;
 constexpr int kQueryMaxFactors = 3;
 constexpr int kQueryMaxGroups = 8;
+constexpr int kQueryConsumerWarps = 4;   // consumer warps per CTA of scan_columns_kernel (+ one producer warp)
+constexpr uint32_t kQueryMaxBlockRows = 4096;  // a consumer lane owns one 32-row group of the block
 
 struct QueryCol {
 	const SegDesc *desc = nullptr;

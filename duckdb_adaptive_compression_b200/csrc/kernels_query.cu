@@ -14,11 +14,11 @@
 //   * producer warp: lane = (column, piece); resolves the pieces of the NEXT block while the current one is in
 //     flight, lays the pieces out back to back in one stage and issues one cp.async.bulk (TMA) per piece, all
 //     completing on the stage's mbarrier;
-//   * 8 consumer warps, column at a time like DuckDB's vectorised filters: a warp owns every 8th group of 32
-//     rows and keeps their selection words in shared memory.  Predicate columns are evaluated in the FIELD
-//     domain (the producer turns lo <= min + f <= hi into f - flo <= span per piece, so a value costs a funnel
-//     shift, a mask, a subtract and a compare; groups whose selection word is already 0 are skipped), the
-//     ballots refine the words.  Surviving rows are compacted into a per-warp list and only those rows decode
+//   * 4 consumer warps, column at a time like DuckDB's vectorised filters: a warp owns a contiguous quarter of the
+//     block's 32-row groups and keeps their selection words in shared memory.  Predicate columns are evaluated in
+//     the FIELD domain (the producer turns lo <= min + f <= hi into f - flo <= span per piece); a LANE owns a whole
+//     32-row group = w whole words of the piece, realigned once, so every field sits at a compile-time position
+//     (pred32<W>: shift, mask, subtract, compare, select per row; no address arithmetic, no ballot).  Surviving rows are compacted into a per-warp list and only those rows decode
 //     the factor columns and fold prod_k(add_k + mul_k * value_k) into 128-bit per-thread accumulators.
 //     Optional selection bitmap in (AND) / out.  No barrier between the consumer warps.
 //
@@ -29,7 +29,7 @@ namespace adacom {
 
 namespace {
 
-constexpr int kQConsumerWarps = 8;
+constexpr int kQConsumerWarps = kQueryConsumerWarps;  // 4: a warp owns 32 consecutive 32-row groups of a 4096-row block
 constexpr int kQConsumers = kQConsumerWarps * 32;
 constexpr int kQThreads = kQConsumers + 32;
 constexpr int kQMaxStages = 3;
@@ -141,6 +141,53 @@ __device__ __forceinline__ bool row_passes(const QPiece *pc, const uint8_t *stag
 	}
 	const uint64_t v = column_value(pc, stage, i, qc.type_size, qc.is_signed);
 	return qc.is_signed ? ((int64_t)v >= qc.lo && (int64_t)v <= qc.hi) : (v >= (uint64_t)qc.lo && v <= (uint64_t)qc.hi);
+}
+
+// ---- predicate on 32 consecutive rows of one lane, width known at compile time -----------------------------------
+// 32 fields of W bits are exactly W 32-bit words.  The lane loads its W (+1) words, realigns them by the piece's bit
+// offset with W funnel shifts, and every field then sits at a compile-time position: a row costs a shift, a mask, a
+// subtract, a compare and a select (the lane = row formulation pays two shared loads, an address computation and a
+// ballot share on top).  Consecutive lanes own consecutive groups (stride W words: conflict-free for odd W).
+template <int W>
+__device__ __forceinline__ uint32_t pred32(const uint32_t *p, uint32_t s0, uint32_t flo, uint32_t span) {
+	uint32_t r[W + 1];
+#pragma unroll
+	for (int t = 0; t <= W; t++) {
+		r[t] = p[t];
+	}
+#pragma unroll
+	for (int t = 0; t < W; t++) {
+		r[t] = __funnelshift_r(r[t], r[t + 1], s0);  // s0 == 0 leaves r[t]
+	}
+	constexpr uint32_t mask = W >= 32 ? 0xffffffffu : ((1u << (W & 31)) - 1u);
+	uint32_t word = 0;
+#pragma unroll
+	for (int k = 0; k < 32; k++) {
+		const int bit = k * W, wi = bit >> 5, sh = bit & 31;
+		uint32_t f;
+		if (sh + W <= 32) {
+			f = r[wi] >> sh;
+			if (sh + W < 32) {
+				f &= mask;
+			}
+		} else {
+			f = __funnelshift_r(r[wi], r[wi + 1 < W ? wi + 1 : wi], sh) & mask;
+		}
+		word |= (f - flo) <= span ? (1u << k) : 0u;
+	}
+	return word;
+}
+
+__device__ __forceinline__ uint32_t pred32_any(uint32_t w, const uint32_t *p, uint32_t s0, uint32_t flo, uint32_t span) {
+	switch (w) {
+#define ADACOM_P32(W) case W: return pred32<W>(p, s0, flo, span);
+	ADACOM_P32(1) ADACOM_P32(2) ADACOM_P32(3) ADACOM_P32(4) ADACOM_P32(5) ADACOM_P32(6) ADACOM_P32(7) ADACOM_P32(8)
+	ADACOM_P32(9) ADACOM_P32(10) ADACOM_P32(11) ADACOM_P32(12) ADACOM_P32(13) ADACOM_P32(14) ADACOM_P32(15) ADACOM_P32(16)
+	ADACOM_P32(17) ADACOM_P32(18) ADACOM_P32(19) ADACOM_P32(20) ADACOM_P32(21) ADACOM_P32(22) ADACOM_P32(23) ADACOM_P32(24)
+	ADACOM_P32(25) ADACOM_P32(26) ADACOM_P32(27) ADACOM_P32(28) ADACOM_P32(29) ADACOM_P32(30) ADACOM_P32(31) ADACOM_P32(32)
+#undef ADACOM_P32
+	default: return 0xffffffffu;
+	}
 }
 
 struct PieceRes {
@@ -401,7 +448,7 @@ __device__ __forceinline__ void aggregate_grouped(const QueryArgs &a, const QSta
 	__syncwarp();
 }
 
-__global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryArgs a) {
+__global__ void __launch_bounds__(kQThreads, 4) scan_columns_kernel(const QueryArgs a) {
 	extern __shared__ __align__(128) uint8_t q_stage_mem[];
 	__shared__ __align__(8) uint64_t full_bar[kQMaxStages];
 	__shared__ __align__(8) uint64_t empty_bar[kQMaxStages];
@@ -558,8 +605,11 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 			const uint32_t n_groups = (rows + 31u) >> 5;
 			const uint64_t word0 = (st.row0 - a.row_begin) >> 5;  // bitmap word of the block's first group
 
+			// ---- my groups: a contiguous range of 32-row groups (one per lane for blocks of <= 4096 rows) ----
+			const uint32_t gpw = (n_groups + kQConsumerWarps - 1u) / kQConsumerWarps;
+			const uint32_t g_lo = min(warp * gpw, n_groups), g_hi = min(g_lo + gpw, n_groups);
 			// ---- selection words of my groups: rows that exist, AND the optional input bitmap ----
-			for (uint32_t g = warp + lane * kQConsumerWarps; g < n_groups; g += 32u * kQConsumerWarps) {
+			for (uint32_t g = g_lo + lane; g < g_hi; g += 32u) {
 				const uint32_t left = rows - g * 32u;
 				uint32_t word = left >= 32u ? 0xffffffffu : ((1u << left) - 1u);
 				if (a.in_bitmap != nullptr) {
@@ -610,66 +660,46 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 					const uint32_t end_p = off_p + q.cnt;
 					const uint8_t *pbase = stage + q.smem_off;
 					const uint64_t mask64 = lo_set64(q.w);
-					uint32_t g = off_p >> 5;
-					g += (warp - g) & (kQConsumerWarps - 1);  // first group >= off_p / 32 that is mine
 					if (q.linear && q.flo == 0 && q.span == mask64) {
 						off_p = end_p;  // zone map: every value of the piece passes
 						continue;
 					}
+					const uint32_t *words32 = (const uint32_t *)pbase;
 					if (q.linear && q.w <= 32u && (q.flo >> 32) == 0) {
-						// fast path: 32-bit fields, predicate in the field domain, four of my groups per round
+						// fast path: 32-bit fields, predicate in the field domain; lane = one of my 32-row groups
+						// (pred32: compile-time field positions), groups cut by a piece boundary lane = row
 						const uint32_t mask = (uint32_t)mask64, flo = (uint32_t)q.flo, span = (uint32_t)q.span;
-						const uint32_t step = 32u * kQConsumerWarps * q.w;            // bits between two of my groups
-						uint32_t bit = q.bit_base + (g * 32u + lane - off_p) * q.w;   // wraps for lanes before off_p: unused
-						// step is 8*w whole 32-bit words: a lane's funnel shift amount is the same in every group of the
-						// piece, and the four loads of a round sit at fixed word strides from one pointer
-						const uint32_t sh = bit & 31u;
-						const uint32_t wstride = (uint32_t)kQConsumerWarps * q.w;     // 32-bit words between two of my groups
-						uint32_t *my_sel = sel + lane * kQConsumerWarps;               // lanes 0..3 publish the four ballots
-						for (; g * 32u < end_p; g += 4u * kQConsumerWarps, bit += 4u * step) {
-							const bool interior = g * 32u >= off_p && (g + 3u * kQConsumerWarps) * 32u + 32u <= end_p;
-							if (interior) {
-								// branch-free round: every lane of the four groups lies inside the piece
-								const uint32_t *p32 = (const uint32_t *)pbase + (bit >> 5);
-								uint32_t f[4];
-#pragma unroll
-								for (int u = 0; u < 4; u++) {
-									f[u] = __funnelshift_r(p32[u * wstride], p32[u * wstride + 1], sh) & mask;
-								}
-								uint32_t mine = 0;
-#pragma unroll
-								for (int u = 0; u < 4; u++) {
-									const uint32_t keep = __ballot_sync(0xffffffffu, (f[u] - flo) <= span);
-									mine = (int)lane == u ? keep : mine;
-								}
-								if (lane < 4) {
-									my_sel[g] &= mine;
-								}
-							} else {
-#pragma unroll 1
-								for (int u = 0; u < 4; u++) {
-									const uint32_t gu = g + u * kQConsumerWarps;
-									if (gu * 32u >= end_p) {
-										break;
-									}
-									const uint32_t i = gu * 32u + lane;
-									const bool inside = i >= off_p && i < end_p;
-									const uint32_t bu = inside ? bit + u * step : q.bit_base;
-									const uint32_t *p32 = (const uint32_t *)(pbase + ((bu >> 3) & ~3u));
-									const uint32_t fu = __funnelshift_r(p32[0], p32[1], bu) & mask;
-									const uint32_t keep = __ballot_sync(0xffffffffu, !inside || (fu - flo) <= span);
-									if (lane == 0) {
-										sel[gu] &= keep;
-									}
-								}
+						for (uint32_t gb = g_lo; gb < g_hi; gb += 32u) {
+							const uint32_t g = gb + lane;
+							const uint32_t r_lo = g * 32u;
+							if (g < g_hi && r_lo >= off_p && r_lo + 32u <= end_p) {
+								const uint32_t bit = q.bit_base + (r_lo - off_p) * q.w;
+								sel[g] &= pred32_any(q.w, words32 + (bit >> 5), bit & 31u, flo, span);
 							}
 						}
 						__syncwarp();
+#pragma unroll 1
+						for (int e = 0; e < 2; e++) {
+							const uint32_t edge = e == 0 ? off_p : end_p;
+							const uint32_t g = edge >> 5;
+							if ((edge & 31u) == 0 || g < g_lo || g >= g_hi) {
+								continue;  // warp-uniform
+							}
+							const uint32_t i = g * 32u + lane;
+							const bool inside = i >= off_p && i < end_p;
+							const uint32_t bit = inside ? q.bit_base + (i - off_p) * q.w : q.bit_base;
+							const uint32_t f = read_bits32(words32, bit) & mask;
+							const uint32_t keep = __ballot_sync(0xffffffffu, !inside || (f - flo) <= span);
+							if (lane == 0) {
+								sel[g] &= keep;
+							}
+							__syncwarp();
+						}
 						off_p = end_p;
 						continue;
 					}
-					const uint32_t *words32 = (const uint32_t *)pbase;
-					for (; g * 32u < end_p; g += kQConsumerWarps) {
+					uint32_t g = max(off_p >> 5, g_lo);  // first of my groups that touches the piece
+					for (; g * 32u < end_p && g < g_hi; g++) {
 						const uint32_t word = sel[g];
 						if (word == 0) {
 							continue;  // nothing left to test in these 32 rows
@@ -700,8 +730,8 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 				if (a.out_bitmap == nullptr && c + 1 < a.n_cols) {
 					// survivors so far; at <= 25 % of my rows (and within the list) the remaining predicate columns
 					// run on the compacted list
-					const uint32_t g = warp + lane * kQConsumerWarps;
-					const uint32_t word = g < n_groups ? sel[g] : 0u;
+					const uint32_t g = g_lo + lane;  // gpw <= 32: blocks of <= 4096 rows
+					const uint32_t word = g < g_hi ? sel[g] : 0u;
 					const uint32_t cnt = __popc(word);
 					uint32_t incl = cnt;
 #pragma unroll
@@ -712,7 +742,7 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 						}
 					}
 					const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
-					const uint32_t my_groups = n_groups > warp ? (n_groups - warp + kQConsumerWarps - 1u) / kQConsumerWarps : 0u;
+					const uint32_t my_groups = g_hi - g_lo;
 					if (total <= kQListCap && total * 4u <= my_groups * 32u) {
 						uint32_t pos = incl - cnt;
 						uint32_t rest = word;
@@ -732,15 +762,15 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 			// sparse selections (Q6 keeps ~2 % of the rows): lane j owns my j-th group (8192 rows = 32 groups per warp),
 			// an exclusive scan of the survivor counts places every lane's rows, each lane then emits its own set bits.
 			// Same list order as the group-at-a-time loop below, which remains for dense selections.
-			uint32_t g_first = warp;
+			uint32_t g_first = g_lo;
 			if (list_mode) {
 				if (lane == 0) {
 					n_pass += n_list;
 				}
-				g_first = n_groups;  // the list already holds the survivors of every predicate
+				g_first = g_hi;  // the list already holds the survivors of every predicate
 			} else {
-				const uint32_t g = warp + lane * kQConsumerWarps;
-				const uint32_t word = g < n_groups ? sel[g] : 0u;
+				const uint32_t g = g_lo + lane;
+				const uint32_t word = g < g_hi ? sel[g] : 0u;
 				const uint32_t cnt = __popc(word);
 				uint32_t incl = cnt;
 #pragma unroll
@@ -751,11 +781,11 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 					}
 				}
 				const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
-				const uint32_t my_groups = n_groups > warp ? (n_groups - warp + kQConsumerWarps - 1u) / kQConsumerWarps : 0u;
+				const uint32_t my_groups = g_hi - g_lo;
 				if (a.dense_groups && total * 4u >= my_groups * 32u) {
 					// dense selection of a grouped scan: group at a time, lane = row, values straight into the thread's
 					// shared accumulators of the row's group
-					for (uint32_t gd = warp; gd < n_groups; gd += kQConsumerWarps) {
+					for (uint32_t gd = g_lo; gd < g_hi; gd++) {
 						const uint32_t wd = sel[gd];
 						if (a.out_bitmap != nullptr && lane == 0) {
 							a.out_bitmap[word0 + gd] = wd;
@@ -790,9 +820,9 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 							dcnt[(uint32_t)kv * kQConsumers + tid] += 1u;
 						}
 					}
-					g_first = n_groups;
+					g_first = g_hi;
 				} else if (total <= kQListCap) {
-					if (a.out_bitmap != nullptr && g < n_groups) {
+					if (a.out_bitmap != nullptr && g < g_hi) {
 						a.out_bitmap[word0 + g] = word;
 					}
 					uint32_t pos = incl - cnt;
@@ -806,10 +836,10 @@ __global__ void __launch_bounds__(kQThreads, 3) scan_columns_kernel(const QueryA
 						n_pass += total;
 					}
 					n_list = total;
-					g_first = n_groups;  // the loop below has nothing left to do
+					g_first = g_hi;  // the loop below has nothing left to do
 				}
 			}
-			for (uint32_t g = g_first; g < n_groups; g += kQConsumerWarps) {
+			for (uint32_t g = g_first; g < g_hi; g++) {
 				const uint32_t word = sel[g];
 				if (a.out_bitmap != nullptr && lane == 0) {
 					a.out_bitmap[word0 + g] = word;
