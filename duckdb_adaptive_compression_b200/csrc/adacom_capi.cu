@@ -1648,9 +1648,15 @@ static adacom_status plan_scan_columns(adacom_ctx *ctx, const adacom_scan_term *
 		}
 	}
 	const uint32_t group_smem = n_groups ? scan_columns_group_smem(n_groups, n_sums, 0) : 0u;
+	// ADACOM_QUERY_STAGES (developer knob): pipeline depth per CTA; with one stage the overlap of copy and compute comes
+	// from the other resident CTAs of the SM (more consumer warps per SM for the same shared memory)
+	static const uint32_t forced_stages = getenv("ADACOM_QUERY_STAGES") ? (uint32_t)atoi(getenv("ADACOM_QUERY_STAGES")) : 0u;
 	for (uint32_t r : {4096u, 2048u}) {  // <= kQueryMaxBlockRows: one 32-row group per consumer lane
-		for (uint32_t st : {3u, 2u}) {
-			// + ~26 KiB static (+ the GROUP BY scratch): three CTAs per SM
+		for (uint32_t st : {3u, 2u, 1u}) {
+			if (forced_stages && st != forced_stages) {
+				continue;
+			}
+			// + ~16 KiB static (+ the GROUP BY scratch): three or more CTAs per SM
 			if (!R && st * stage_bytes(r) + group_smem <= 48u * 1024u) {
 				R = r;
 				stages = st;
@@ -1686,6 +1692,22 @@ static adacom_status plan_scan_columns(adacom_ctx *ctx, const adacom_scan_term *
 				return fail(ctx, ADACOM_ERR_UNSUPPORTED,
 				            "adacom_scan_columns: a row block spans more than 3 segments of one column");
 			}
+		}
+	}
+	// ungrouped scans run warp-per-block (scan_columns_sparse_kernel): a warp stages the predicate columns of 1024 rows
+	// (<= 3 pieces per column, each rounded out to 16 bytes on both sides) in its own shared-memory window
+	q.sparse_window = 0;
+	if (n_groups == 0 && !getenv("ADACOM_QUERY_PIPELINED")) {
+		uint64_t win = 0;
+		for (uint32_t c = 0; c < n_terms; c++) {
+			if (terms[c].has_predicate) {
+				win += 1024ull * std::min<uint32_t>(terms[c].col->wmax ? terms[c].col->wmax : 8u * terms[c].col->t.size, 32u) / 8 +
+				       (uint64_t)kQueryMaxPieces * 48;
+			}
+		}
+		win = (win + 127) & ~127ull;
+		if (win * 8 <= 160u * 1024u) {
+			q.sparse_window = (uint32_t)std::max<uint64_t>(win, 2048);  // >= the survivor list of a block (1024 x u16)
 		}
 	}
 	q.n_cols = n_terms;

@@ -101,6 +101,8 @@ struct QueryArgs {
 	uint32_t n_groups = 0;                // 0: no grouping; rows whose key is outside the range are dropped
 	uint32_t dense_groups = 0;            // grouped launches: per-thread int64 accumulators in shared memory are safe
 	                                      // (every partial sum provably fits) -> dense selections skip the lists
+	uint32_t sparse_window = 0;           // ungrouped launches: bytes of shared memory a warp needs for the predicate
+	                                      // columns of 1024 rows (0: use the pipelined kernel)
 	const uint32_t *in_bitmap = nullptr;  // optional selection (bit r - row_begin), AND-ed
 	uint32_t *out_bitmap = nullptr;       // optional: the resulting selection
 	Agg *out = nullptr;                   // n_aggs (x n_groups, group-major) aggregates, zeroed by the caller;

@@ -160,7 +160,7 @@ __device__ __forceinline__ uint32_t pred32(const uint32_t *p, uint32_t s0, uint3
 		r[t] = __funnelshift_r(r[t], r[t + 1], s0);  // s0 == 0 leaves r[t]
 	}
 	constexpr uint32_t mask = W >= 32 ? 0xffffffffu : ((1u << (W & 31)) - 1u);
-	uint32_t word = 0;
+	uint32_t part[4] = {0u, 0u, 0u, 0u};  // four independent chains instead of one 32-deep one
 #pragma unroll
 	for (int k = 0; k < 32; k++) {
 		const int bit = k * W, wi = bit >> 5, sh = bit & 31;
@@ -173,9 +173,9 @@ __device__ __forceinline__ uint32_t pred32(const uint32_t *p, uint32_t s0, uint3
 		} else {
 			f = __funnelshift_r(r[wi], r[wi + 1 < W ? wi + 1 : wi], sh) & mask;
 		}
-		word |= (f - flo) <= span ? (1u << k) : 0u;
+		part[k & 3] |= (f - flo) <= span ? (1u << k) : 0u;
 	}
-	return word;
+	return (part[0] | part[1]) | (part[2] | part[3]);
 }
 
 __device__ __forceinline__ uint32_t pred32_any(uint32_t w, const uint32_t *p, uint32_t s0, uint32_t flo, uint32_t span) {
@@ -743,7 +743,7 @@ __global__ void __launch_bounds__(kQThreads, 4) scan_columns_kernel(const QueryA
 					}
 					const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
 					const uint32_t my_groups = g_hi - g_lo;
-					if (total <= kQListCap && total * 4u <= my_groups * 32u) {
+					if (total <= kQListCap && total * 16u <= my_groups * 32u) {
 						uint32_t pos = incl - cnt;
 						uint32_t rest = word;
 						while (rest) {
@@ -939,6 +939,360 @@ __global__ void __launch_bounds__(kQThreads, 4) scan_columns_kernel(const QueryA
 	}
 }
 
+
+// =====================================================================================================================
+// scan_columns_sparse_kernel -- the ungrouped form (TPC-H Q6 shape: conjunctive ranges, few survivors, SUM of products)
+// without the producer / consumer pipeline.  Every WARP works alone on blocks of 1024 table rows:
+//   A  lane = (column, piece) resolves the <= 3 segments of every column that overlap the block (like the producer above);
+//   B  the packed bytes of the predicate columns' pieces are copied into the warp's private shared-memory window with
+//      16-byte cp.async, all columns at once (one wait per block);
+//   C  lane = one 32-row group: pred32<W> per predicate piece (compile-time field positions), groups cut by a piece
+//      boundary and pieces that are not field-comparable (wrap-around frames, > 32 bits, raw signed slots) lane = row;
+//   D  the few survivors are compacted into a list and their factor values are read straight from global memory.
+// No CTA barrier, no mbarrier, no shared selection state: latency is hidden by the 32 independent warps an SM holds.
+// =====================================================================================================================
+constexpr int kSWarps = 8;
+constexpr uint32_t kSRows = 1024;
+
+struct SPiece {
+	PieceRes r;
+	uint32_t smem_off;   // of the staged bytes inside the warp's window
+	uint32_t row_lo;     // first block row of the piece
+	uint64_t words;      // global address of the segment's payload (packed words or raw slots)
+	uint32_t first;      // first value of the piece inside its segment
+	uint32_t repacked;
+};
+
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src) {
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+	asm volatile("cp.async.wait_all;" ::: "memory");
+}
+
+// decoded value of table row `row` of column c, straight from global memory (descriptor walk + <= 2 words)
+__device__ __forceinline__ uint64_t row_value_global(const QueryCol &c, uint64_t row, int literal) {
+	uint32_t s = __ldg(c.vec_seg + (row >> 11));
+	DescQ dq = load_desc(c.desc + s);
+	while (dq.row_start() + dq.count() <= row && s + 1 < c.n_segs) {
+		s++;
+		dq = load_desc(c.desc + s);
+	}
+	const uint32_t i = (uint32_t)(row - dq.row_start());
+	const bool repacked = dq.state() & kSegRepacked;
+	const uint64_t mn = dq.min_factor();
+	const uint64_t min_add = (mn != ~0ull && (repacked || literal)) ? mn : 0ull;
+	uint64_t f;
+	if (repacked) {
+		const uint32_t w = dq.width();
+		const uint64_t *words = (const uint64_t *)dq.packed_ptr();
+		const uint64_t bit = (uint64_t)i * w;
+		const uint32_t off = (uint32_t)(bit & 63u);
+		f = __ldg(words + (bit >> 6)) >> off;
+		if (off + w > 64u) {
+			f |= __ldg(words + (bit >> 6) + 1) << (64u - off);
+		}
+		f &= lo_set64(w);
+	} else {
+		const uint8_t *p = c.raw + (dq.row_start() + i) * (uint64_t)c.type_size;
+		f = c.type_size == 8 ? *(const uint64_t *)p
+		                     : (c.type_size == 4 ? (uint64_t) * (const uint32_t *)p
+		                                         : (c.type_size == 2 ? (uint64_t) * (const uint16_t *)p : (uint64_t)*p));
+	}
+	return extend_rt(f + min_add, c.type_size, c.is_signed);
+}
+
+__device__ __forceinline__ bool in_range(const QueryCol &c, uint64_t v) {
+	return c.is_signed ? ((int64_t)v >= c.lo && (int64_t)v <= c.hi) : (v >= (uint64_t)c.lo && v <= (uint64_t)c.hi);
+}
+
+template <int NA>  // upper bound of a.n_aggs (1, 2, 4, 8): the 128-bit accumulators live in registers
+__global__ void __launch_bounds__(kSWarps * 32) scan_columns_sparse_kernel(const QueryArgs a, uint32_t window_bytes) {
+	extern __shared__ __align__(128) uint8_t s_mem[];
+	__shared__ SPiece s_piece[kSWarps][kQueryMaxCols][kQueryMaxPieces];
+	__shared__ uint64_t red[96];
+	const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+	uint8_t *window = s_mem + (size_t)warp * window_bytes;
+	SPiece(*pieces)[kQueryMaxPieces] = s_piece[warp];
+	uint16_t *my_list = (uint16_t *)window;  // the survivor list reuses the window once the predicates are done (>= 2 KiB)
+	const uint64_t n_rows = a.row_end - a.row_begin;
+	const uint32_t n_blocks = (uint32_t)((n_rows + kSRows - 1) / kSRows);
+	const uint32_t ci = lane / kQLanesPerCol, pi = lane % kQLanesPerCol;
+	const bool active = ci < a.n_cols && pi < (uint32_t)kQueryMaxPieces;
+	const QueryCol &mycol = a.cols[active ? ci : 0];
+
+	unsigned __int128 acc[NA];
+#pragma unroll
+	for (int g = 0; g < NA; g++) {
+		acc[g] = 0;
+	}
+	uint64_t n_pass = 0;
+
+	for (uint32_t b = blockIdx.x * kSWarps + warp; b < n_blocks; b += gridDim.x * kSWarps) {
+		const uint64_t r0 = a.row_begin + (uint64_t)b * kSRows;
+		const uint32_t rows = (uint32_t)(a.row_end - r0 < kSRows ? a.row_end - r0 : kSRows);
+		const uint32_t n_groups = (rows + 31u) >> 5;
+		// ---- A: pieces ----
+		PieceRes pr;
+		pr.bytes = 0;
+		pr.cnt = 0;
+		uint32_t row_lo = 0, first = 0, repacked = 0;
+		uint64_t words = 0;
+		if (active) {
+			uint32_t s0 = __ldg(mycol.vec_seg + (r0 >> 11));
+			DescQ d0 = load_desc(mycol.desc + s0);
+			while (d0.row_start() + d0.count() <= r0 && s0 + 1 < mycol.n_segs) {  // r0 is only 1024-aligned
+				s0++;
+				d0 = load_desc(mycol.desc + s0);
+			}
+			const bool valid = s0 + pi < mycol.n_segs;
+			const DescQ dq = pi == 0 ? d0 : (valid ? load_desc(mycol.desc + s0 + pi) : d0);
+			pr = resolve_piece(mycol, dq, valid, r0, rows, a.literal);
+			if (pr.cnt) {
+				const uint64_t rs = dq.row_start();
+				row_lo = (uint32_t)((rs > r0 ? rs : r0) - r0);
+				first = (uint32_t)((rs > r0 ? rs : r0) - rs);
+				repacked = (dq.state() & kSegRepacked) ? 1u : 0u;
+				words = repacked ? dq.packed_ptr() : (uint64_t)mycol.raw + rs * (uint64_t)mycol.type_size;
+			}
+		}
+		// a predicate piece is staged iff pred32 can take it
+		const bool fast = active && pr.cnt && mycol.has_pred && pr.linear && pr.w <= 32u && (pr.flo >> 32) == 0 &&
+		                  !(pr.flo == 0 && pr.span == lo_set64(pr.w));
+		const uint32_t my_bytes = fast ? pr.bytes : 0u;
+		uint32_t incl = my_bytes;
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) {
+			const uint32_t v = __shfl_up_sync(0xffffffffu, incl, d);
+			if ((int)lane >= d) {
+				incl += v;
+			}
+		}
+		// every column must be covered by its three pieces, else the block takes the row-at-a-time path
+		uint32_t covered = pr.cnt;
+		covered += __shfl_xor_sync(0xffffffffu, covered, 1);
+		covered += __shfl_xor_sync(0xffffffffu, covered, 2);
+		const bool slow_block = __any_sync(0xffffffffu, active && covered != rows);
+		__syncwarp();
+		if (active) {
+			SPiece sp;
+			sp.r = pr;
+			sp.smem_off = incl - my_bytes;
+			sp.row_lo = row_lo;
+			sp.words = words;
+			sp.first = first;
+			sp.repacked = repacked;
+			if (!fast) {
+				sp.r.bytes = 0;
+			}
+			pieces[ci][pi] = sp;
+		}
+		__syncwarp();
+		// ---- B: stage the predicate pieces (whole warp per piece, 16 bytes per lane and round) ----
+		if (!slow_block) {
+#pragma unroll 1
+			for (uint32_t c = 0; c < a.n_cols; c++) {
+				if (!a.cols[c].has_pred) {
+					continue;
+				}
+#pragma unroll 1
+				for (int p = 0; p < kQueryMaxPieces; p++) {
+					const uint32_t bytes = pieces[c][p].r.bytes;
+					if (bytes == 0) {
+						continue;
+					}
+					const uint8_t *src = (const uint8_t *)pieces[c][p].r.src16;
+					uint8_t *dst = window + pieces[c][p].smem_off;
+					for (uint32_t off = lane * 16u; off < bytes; off += 512u) {
+						cp_async16(dst + off, src + off);
+					}
+				}
+			}
+			cp_async_wait_all();
+			__syncwarp();
+		}
+		// ---- C: selection word of my group ----
+		const uint32_t g = lane;
+		uint32_t sel = 0;
+		if (g < n_groups) {
+			const uint32_t left = rows - g * 32u;
+			sel = left >= 32u ? 0xffffffffu : ((1u << left) - 1u);
+			if (a.in_bitmap != nullptr) {
+				sel &= __ldg(a.in_bitmap + ((r0 - a.row_begin) >> 5) + g);
+			}
+		}
+#pragma unroll 1
+		for (uint32_t c = 0; c < a.n_cols; c++) {
+			const QueryCol &qc = a.cols[c];
+			if (!qc.has_pred) {
+				continue;
+			}
+			if (slow_block) {
+				for (uint32_t gg = 0; gg < n_groups; gg++) {
+					const uint32_t i = gg * 32u + lane;
+					const bool pass = i >= rows || in_range(qc, row_value_global(qc, r0 + i, a.literal));
+					const uint32_t keep = __ballot_sync(0xffffffffu, pass);
+					if (lane == gg) {
+						sel &= keep;
+					}
+				}
+				continue;
+			}
+#pragma unroll 1
+			for (int p = 0; p < kQueryMaxPieces; p++) {
+				const SPiece &sp = pieces[c][p];
+				const uint32_t cnt = sp.r.cnt;
+				if (cnt == 0) {
+					continue;
+				}
+				const uint32_t off_p = sp.row_lo, end_p = off_p + cnt, w = sp.r.w;
+				const uint64_t mask64 = lo_set64(w);
+				if (sp.r.linear && sp.r.flo == 0 && sp.r.span == mask64) {
+					continue;  // zone map: every value of the piece passes
+				}
+				if (sp.r.bytes) {
+					const uint32_t *words32 = (const uint32_t *)(window + sp.smem_off);
+					const uint32_t flo = (uint32_t)sp.r.flo, span = (uint32_t)sp.r.span, mask = (uint32_t)mask64;
+					const uint32_t r_lo = g * 32u;
+					if (g < n_groups && r_lo >= off_p && r_lo + 32u <= end_p) {
+						const uint32_t bit = sp.r.bit_base + (r_lo - off_p) * w;
+						sel &= pred32_any(w, words32 + (bit >> 5), bit & 31u, flo, span);
+					}
+#pragma unroll 1
+					for (int e = 0; e < 2; e++) {
+						const uint32_t edge = e == 0 ? off_p : end_p;
+						if ((edge & 31u) == 0 || (edge >> 5) >= n_groups) {
+							continue;
+						}
+						const uint32_t ge = edge >> 5;
+						const uint32_t i = ge * 32u + lane;
+						const bool inside = i >= off_p && i < end_p;
+						const uint32_t bit = inside ? sp.r.bit_base + (i - off_p) * w : sp.r.bit_base;
+						const uint32_t f = read_bits32(words32, bit) & mask;
+						const uint32_t keep = __ballot_sync(0xffffffffu, !inside || (f - flo) <= span);
+						if (lane == ge) {
+							sel &= keep;
+						}
+					}
+				} else {
+					// not field-comparable: decode the rows of the piece from global memory, lane = row
+					const uint64_t *gw = (const uint64_t *)sp.words;
+					for (uint32_t gg = off_p >> 5; gg * 32u < end_p; gg++) {
+						const uint32_t i = gg * 32u + lane;
+						bool pass = true;
+						if (i >= off_p && i < end_p) {
+							const uint32_t k = sp.first + (i - off_p);
+							uint64_t f;
+							if (sp.repacked) {
+								const uint64_t bit = (uint64_t)k * w;
+								const uint32_t off = (uint32_t)(bit & 63u);
+								f = __ldg(gw + (bit >> 6)) >> off;
+								if (off + w > 64u) {
+									f |= __ldg(gw + (bit >> 6) + 1) << (64u - off);
+								}
+								f &= mask64;
+							} else {
+								const uint8_t *ptr = (const uint8_t *)sp.words + (uint64_t)k * qc.type_size;
+								f = qc.type_size == 8 ? *(const uint64_t *)ptr
+								                      : (qc.type_size == 4 ? (uint64_t) * (const uint32_t *)ptr
+								                                           : (qc.type_size == 2 ? (uint64_t) * (const uint16_t *)ptr
+								                                                                : (uint64_t)*ptr));
+							}
+							pass = in_range(qc, extend_rt(f + sp.r.min_add, qc.type_size, qc.is_signed));
+						}
+						const uint32_t keep = __ballot_sync(0xffffffffu, pass);
+						if (lane == gg) {
+							sel &= keep;
+						}
+					}
+				}
+			}
+		}
+		// ---- D: survivors ----
+		if (a.out_bitmap != nullptr && g < n_groups) {
+			a.out_bitmap[((r0 - a.row_begin) >> 5) + g] = sel;
+		}
+		const uint32_t cnt = __popc(sel);
+		uint32_t incl_c = cnt;
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) {
+			const uint32_t v = __shfl_up_sync(0xffffffffu, incl_c, d);
+			if ((int)lane >= d) {
+				incl_c += v;
+			}
+		}
+		const uint32_t total = __shfl_sync(0xffffffffu, incl_c, 31);
+		if (total == 0) {
+			continue;
+		}
+		if (lane == 0) {
+			n_pass += total;
+		}
+		__syncwarp();
+		uint32_t pos = incl_c - cnt;
+		uint32_t rest = sel;
+		while (rest) {
+			const uint32_t bpos = (uint32_t)__ffs((int)rest) - 1u;
+			my_list[pos++] = (uint16_t)(g * 32u + bpos);
+			rest &= rest - 1u;
+		}
+		__syncwarp();  // (the list overwrites the staged columns: every lane is past its last predicate read)
+		for (uint32_t e = lane; e < total; e += 32u) {
+			const uint64_t row = r0 + my_list[e];
+			int64_t v[kQueryMaxCols];
+#pragma unroll
+			for (int c = 0; c < kQueryMaxCols; c++) {
+				v[c] = 0;
+				if (c < (int)a.n_cols && ((a.factor_mask >> c) & 1u)) {
+					v[c] = (int64_t)row_value_global(a.cols[c], row, a.literal);
+				}
+			}
+#pragma unroll
+			for (int k = 0; k < NA; k++) {
+				if (k < (int)a.n_aggs) {
+					const QueryAgg &qa = a.aggs[k];
+					if (a.narrow_products) {
+						int64_t term = 1;
+#pragma unroll
+						for (int f = 0; f < kQueryMaxFactors; f++) {
+							if (f < (int)qa.n_factors) {
+								int64_t x = 0;
+#pragma unroll
+								for (int c = 0; c < kQueryMaxCols; c++) {
+									x = (int)qa.col[f] == c ? v[c] : x;
+								}
+								term *= qa.add[f] + qa.mul[f] * x;
+							}
+						}
+						acc[k] += (unsigned __int128)(__int128)term;
+					} else {
+						__int128 term = 1;
+#pragma unroll
+						for (int f = 0; f < kQueryMaxFactors; f++) {
+							if (f < (int)qa.n_factors) {
+								int64_t x = 0;
+#pragma unroll
+								for (int c = 0; c < kQueryMaxCols; c++) {
+									x = (int)qa.col[f] == c ? v[c] : x;
+								}
+								term *= (__int128)qa.add[f] + (__int128)qa.mul[f] * (__int128)x;
+							}
+						}
+						acc[k] += (unsigned __int128)term;
+					}
+				}
+			}
+		}
+		__syncwarp();
+	}
+#pragma unroll
+	for (int g = 0; g < NA; g++) {
+		if (g < (int)a.n_aggs) {  // uniform
+			block_reduce_agg((uint64_t)acc[g], (uint64_t)(acc[g] >> 64), n_pass, red, a.out + g);
+		}
+	}
+}
+
 }  // namespace
 
 uint32_t scan_columns_group_smem(uint32_t n_groups, uint32_t n_aggs, uint32_t dense) {
@@ -950,20 +1304,45 @@ uint32_t scan_columns_group_smem(uint32_t n_groups, uint32_t n_aggs, uint32_t de
 }
 
 cudaError_t launch_scan_columns(const QueryArgs &args, int sm_count, cudaStream_t stream) {
+	if (args.row_end <= args.row_begin || args.n_aggs == 0) {
+		return cudaSuccess;
+	}
+	int dev = 0;
+	cudaGetDevice(&dev);
+	if (args.n_groups == 0 && args.sparse_window) {
+		// ungrouped: the warp-per-block kernel; window = staged bytes of the predicate columns of 1024 rows
+		const size_t smem = (size_t)kSWarps * args.sparse_window;
+		void (*kernel)(const QueryArgs, uint32_t) =
+		    args.n_aggs <= 1 ? scan_columns_sparse_kernel<1>
+		                     : (args.n_aggs <= 2 ? scan_columns_sparse_kernel<2>
+		                                         : (args.n_aggs <= 4 ? scan_columns_sparse_kernel<4> : scan_columns_sparse_kernel<8>));
+		cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		if (e != cudaSuccess) {
+			return e;
+		}
+		int per_sm = 0;
+		e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kSWarps * 32, smem);
+		if (e != cudaSuccess) {
+			return e;
+		}
+		const uint64_t n_blocks = (args.row_end - args.row_begin + kSRows - 1) / kSRows;
+		uint64_t grid = (uint64_t)sm_count * (uint64_t)(per_sm > 0 ? per_sm : 1);
+		const uint64_t need = (n_blocks + kSWarps - 1) / kSWarps;
+		if (grid > need) {
+			grid = need;
+		}
+		kernel<<<(uint32_t)grid, kSWarps * 32, smem, stream>>>(args, args.sparse_window);
+		return cudaGetLastError();
+	}
 	static size_t configured[64] = {};
 	const size_t smem = (size_t)args.stages * args.stage_bytes +
 	                    (args.n_groups ? scan_columns_group_smem(args.n_groups, args.n_aggs, args.dense_groups) : 0);
-	int dev = 0;
-	cudaGetDevice(&dev);
 	if (configured[dev & 63] < smem) {
 		cudaError_t e = cudaFuncSetAttribute(scan_columns_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 		if (e != cudaSuccess) {
 			return e;
 		}
 		configured[dev & 63] = smem;
-	}
-	if (args.row_end <= args.row_begin || args.n_aggs == 0) {
-		return cudaSuccess;
 	}
 	const uint64_t n_blocks = (args.row_end - args.row_begin + args.block_rows - 1) / args.block_rows;
 	int per_sm = 0;
