@@ -1694,20 +1694,20 @@ static adacom_status plan_scan_columns(adacom_ctx *ctx, const adacom_scan_term *
 			}
 		}
 	}
-	// ungrouped scans run warp-per-block (scan_columns_sparse_kernel): a warp stages the predicate columns of 1024 rows
+	// ungrouped scans run warp-per-block (scan_columns_sparse_kernel): a warp stages the predicate columns of 2048 rows
 	// (<= 3 pieces per column, each rounded out to 16 bytes on both sides) in its own shared-memory window
 	q.sparse_window = 0;
 	if (n_groups == 0 && !getenv("ADACOM_QUERY_PIPELINED")) {
 		uint64_t win = 0;
 		for (uint32_t c = 0; c < n_terms; c++) {
 			if (terms[c].has_predicate) {
-				win += 1024ull * std::min<uint32_t>(terms[c].col->wmax ? terms[c].col->wmax : 8u * terms[c].col->t.size, 32u) / 8 +
+				win += 2048ull * std::min<uint32_t>(terms[c].col->wmax ? terms[c].col->wmax : 8u * terms[c].col->t.size, 32u) / 8 +
 				       (uint64_t)kQueryMaxPieces * 48;
 			}
 		}
 		win = (win + 127) & ~127ull;
-		if (win * 8 <= 160u * 1024u) {
-			q.sparse_window = (uint32_t)std::max<uint64_t>(win, 2048);  // >= the survivor list of a block (1024 x u16)
+		if (std::max<uint64_t>(win, 4096) * 8 <= 200u * 1024u) {
+			q.sparse_window = (uint32_t)std::max<uint64_t>(win, 4096);  // >= the survivor list of a block (2048 x u16)
 		}
 	}
 	q.n_cols = n_terms;

@@ -942,32 +942,50 @@ __global__ void __launch_bounds__(kQThreads, 4) scan_columns_kernel(const QueryA
 
 // =====================================================================================================================
 // scan_columns_sparse_kernel -- the ungrouped form (TPC-H Q6 shape: conjunctive ranges, few survivors, SUM of products)
-// without the producer / consumer pipeline.  Every WARP works alone on blocks of 1024 table rows:
-//   A  lane = (column, piece) resolves the <= 3 segments of every column that overlap the block (like the producer above);
-//   B  the packed bytes of the predicate columns' pieces are copied into the warp's private shared-memory window with
-//      16-byte cp.async, all columns at once (one wait per block);
-//   C  lane = one 32-row group: pred32<W> per predicate piece (compile-time field positions), groups cut by a piece
-//      boundary and pieces that are not field-comparable (wrap-around frames, > 32 bits, raw signed slots) lane = row;
-//   D  the few survivors are compacted into a list and their factor values are read straight from global memory.
+// without the producer / consumer pipeline.  Every WARP works alone on blocks of 2048 table rows (runs of four
+// consecutive blocks, so the segment state of a column is mostly reused):
+//   A  lane = (column, piece) resolves the <= 3 segments of its column that overlap the block; the per-segment part
+//      (frame of reference, field-domain predicate range) is cached in the lane's registers until the segment changes;
+//   B  the packed bytes of the predicate pieces are copied into the warp's private shared-memory window with 16-byte
+//      cp.async, all columns at once (one wait per block); piece parameters travel by shuffle, not through memory;
+//   C  a lane owns two 32-row groups: pred32<W> per predicate piece (compile-time field positions); groups cut by a
+//      piece boundary and pieces that are not field-comparable (wrap-around frames, > 32 bits, raw signed slots) are
+//      evaluated lane = row;
+//   D  the few survivors are compacted into a list (in the window) and their factor values are read from global memory.
 // No CTA barrier, no mbarrier, no shared selection state: latency is hidden by the 32 independent warps an SM holds.
+// The integer pipe bounds this kernel (ncu: math-pipe throttle), so the design minimises instructions per row.
 // =====================================================================================================================
 constexpr int kSWarps = 8;
-constexpr uint32_t kSRows = 1024;
-
-struct SPiece {
-	PieceRes r;
-	uint32_t smem_off;   // of the staged bytes inside the warp's window
-	uint32_t row_lo;     // first block row of the piece
-	uint64_t words;      // global address of the segment's payload (packed words or raw slots)
-	uint32_t first;      // first value of the piece inside its segment
-	uint32_t repacked;
-};
+constexpr uint32_t kSRows = 2048;
+constexpr int kSGroupsPerLane = (int)(kSRows / 1024u);
+constexpr uint32_t kSRun = 4;  // consecutive blocks a warp takes at a time
 
 __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src) {
 	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr(smem_dst)), "l"(gmem_src) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all() {
 	asm volatile("cp.async.wait_all;" ::: "memory");
+}
+
+__device__ __forceinline__ uint64_t load_slot(const uint8_t *p, uint32_t type_size) {
+	return type_size == 8 ? *(const uint64_t *)p
+	                      : (type_size == 4 ? (uint64_t) * (const uint32_t *)p
+	                                        : (type_size == 2 ? (uint64_t) * (const uint16_t *)p : (uint64_t)*p));
+}
+
+// field k of a segment payload in global memory (packed words) or slot k of the raw arena
+__device__ __forceinline__ uint64_t field_global(uint64_t words, uint32_t repacked, uint32_t k, uint32_t w, uint32_t type_size) {
+	if (!repacked) {
+		return load_slot((const uint8_t *)words + (uint64_t)k * type_size, type_size);
+	}
+	const uint64_t *gw = (const uint64_t *)words;
+	const uint64_t bit = (uint64_t)k * w;
+	const uint32_t off = (uint32_t)(bit & 63u);
+	uint64_t f = __ldg(gw + (bit >> 6)) >> off;
+	if (off + w > 64u) {
+		f |= __ldg(gw + (bit >> 6) + 1) << (64u - off);
+	}
+	return f & lo_set64(w);
 }
 
 // decoded value of table row `row` of column c, straight from global memory (descriptor walk + <= 2 words)
@@ -982,24 +1000,8 @@ __device__ __forceinline__ uint64_t row_value_global(const QueryCol &c, uint64_t
 	const bool repacked = dq.state() & kSegRepacked;
 	const uint64_t mn = dq.min_factor();
 	const uint64_t min_add = (mn != ~0ull && (repacked || literal)) ? mn : 0ull;
-	uint64_t f;
-	if (repacked) {
-		const uint32_t w = dq.width();
-		const uint64_t *words = (const uint64_t *)dq.packed_ptr();
-		const uint64_t bit = (uint64_t)i * w;
-		const uint32_t off = (uint32_t)(bit & 63u);
-		f = __ldg(words + (bit >> 6)) >> off;
-		if (off + w > 64u) {
-			f |= __ldg(words + (bit >> 6) + 1) << (64u - off);
-		}
-		f &= lo_set64(w);
-	} else {
-		const uint8_t *p = c.raw + (dq.row_start() + i) * (uint64_t)c.type_size;
-		f = c.type_size == 8 ? *(const uint64_t *)p
-		                     : (c.type_size == 4 ? (uint64_t) * (const uint32_t *)p
-		                                         : (c.type_size == 2 ? (uint64_t) * (const uint16_t *)p : (uint64_t)*p));
-	}
-	return extend_rt(f + min_add, c.type_size, c.is_signed);
+	const uint64_t words = repacked ? dq.packed_ptr() : (uint64_t)c.raw + dq.row_start() * (uint64_t)c.type_size;
+	return extend_rt(field_global(words, repacked, i, dq.width(), c.type_size) + min_add, c.type_size, c.is_signed);
 }
 
 __device__ __forceinline__ bool in_range(const QueryCol &c, uint64_t v) {
@@ -1007,19 +1009,22 @@ __device__ __forceinline__ bool in_range(const QueryCol &c, uint64_t v) {
 }
 
 template <int NA>  // upper bound of a.n_aggs (1, 2, 4, 8): the 128-bit accumulators live in registers
-__global__ void __launch_bounds__(kSWarps * 32) scan_columns_sparse_kernel(const QueryArgs a, uint32_t window_bytes) {
+__global__ void __launch_bounds__(kSWarps * 32, 4) scan_columns_sparse_kernel(const QueryArgs a, uint32_t window_bytes) {
 	extern __shared__ __align__(128) uint8_t s_mem[];
-	__shared__ SPiece s_piece[kSWarps][kQueryMaxCols][kQueryMaxPieces];
 	__shared__ uint64_t red[96];
 	const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
 	uint8_t *window = s_mem + (size_t)warp * window_bytes;
-	SPiece(*pieces)[kQueryMaxPieces] = s_piece[warp];
-	uint16_t *my_list = (uint16_t *)window;  // the survivor list reuses the window once the predicates are done (>= 2 KiB)
+	uint16_t *my_list = (uint16_t *)window;  // the survivor list reuses the window once the predicates are done (>= 4 KiB)
 	const uint64_t n_rows = a.row_end - a.row_begin;
 	const uint32_t n_blocks = (uint32_t)((n_rows + kSRows - 1) / kSRows);
 	const uint32_t ci = lane / kQLanesPerCol, pi = lane % kQLanesPerCol;
 	const bool active = ci < a.n_cols && pi < (uint32_t)kQueryMaxPieces;
 	const QueryCol &mycol = a.cols[active ? ci : 0];
+	const uint32_t my_has_pred = active ? mycol.has_pred : 0u;
+
+	// ---- per-lane segment cache ----
+	uint32_t c_seg = ~0u, c_w = 0, c_linear = 0, c_repacked = 0, c_count = 0;
+	uint64_t c_rs = 0, c_words = 0, c_min_add = 0, c_flo = ~0ull, c_span = 0;
 
 	unsigned __int128 acc[NA];
 #pragma unroll
@@ -1028,262 +1033,300 @@ __global__ void __launch_bounds__(kSWarps * 32) scan_columns_sparse_kernel(const
 	}
 	uint64_t n_pass = 0;
 
-	for (uint32_t b = blockIdx.x * kSWarps + warp; b < n_blocks; b += gridDim.x * kSWarps) {
-		const uint64_t r0 = a.row_begin + (uint64_t)b * kSRows;
-		const uint32_t rows = (uint32_t)(a.row_end - r0 < kSRows ? a.row_end - r0 : kSRows);
-		const uint32_t n_groups = (rows + 31u) >> 5;
-		// ---- A: pieces ----
-		PieceRes pr;
-		pr.bytes = 0;
-		pr.cnt = 0;
-		uint32_t row_lo = 0, first = 0, repacked = 0;
-		uint64_t words = 0;
-		if (active) {
-			uint32_t s0 = __ldg(mycol.vec_seg + (r0 >> 11));
-			DescQ d0 = load_desc(mycol.desc + s0);
-			while (d0.row_start() + d0.count() <= r0 && s0 + 1 < mycol.n_segs) {  // r0 is only 1024-aligned
-				s0++;
-				d0 = load_desc(mycol.desc + s0);
+	const uint32_t total_warps = gridDim.x * kSWarps, wg = blockIdx.x * kSWarps + warp;
+	for (uint32_t run = wg; run * kSRun < n_blocks; run += total_warps) {
+		for (uint32_t b = run * kSRun; b < min(n_blocks, (run + 1u) * kSRun); b++) {
+			const uint64_t r0 = a.row_begin + (uint64_t)b * kSRows;  // multiple of 2048: vec_seg is exact
+			const uint32_t rows = (uint32_t)(a.row_end - r0 < kSRows ? a.row_end - r0 : kSRows);
+			const uint32_t n_groups = (rows + 31u) >> 5;
+			// ---- A: my piece ----
+			uint32_t cnt = 0, row_lo = 0, first = 0, bit_base = 0, bytes = 0;
+			uint64_t src16 = 0;
+			if (active) {
+				const uint32_t s = __ldg(mycol.vec_seg + (r0 >> 11)) + pi;
+				if (s < mycol.n_segs) {
+					if (s != c_seg) {
+						const DescQ dq = load_desc(mycol.desc + s);
+						c_seg = s;
+						c_rs = dq.row_start();
+						c_count = dq.count();
+						c_w = dq.width();
+						c_repacked = (dq.state() & kSegRepacked) ? 1u : 0u;
+						const uint64_t mn = dq.min_factor();
+						c_min_add = (mn != ~0ull && (c_repacked || a.literal)) ? mn : 0ull;
+						c_words = c_repacked ? dq.packed_ptr() : (uint64_t)mycol.raw + c_rs * (uint64_t)mycol.type_size;
+						c_linear = piece_is_linear(mycol, c_min_add, c_w, c_repacked) ? 1u : 0u;
+						c_flo = ~0ull;
+						c_span = 0;
+						if (c_linear && my_has_pred) {
+							field_range(mycol, c_min_add, c_w, c_flo, c_span);
+						}
+					}
+					const uint64_t re = c_rs + c_count;
+					const uint64_t lo = c_rs > r0 ? c_rs : r0;
+					const uint64_t hi = re < r0 + rows ? re : r0 + rows;
+					if (hi > lo) {
+						cnt = (uint32_t)(hi - lo);
+						row_lo = (uint32_t)(lo - r0);
+						first = (uint32_t)(lo - c_rs);
+						const uint64_t bit = (uint64_t)first * c_w;
+						const uint64_t src = c_repacked ? c_words + (bit >> 3) : c_words + (uint64_t)first * mycol.type_size;
+						src16 = src & ~15ull;
+						const uint32_t byte_base = (uint32_t)(src - src16);
+						bit_base = byte_base * 8u + (c_repacked ? (uint32_t)(bit & 7u) : 0u);
+						bytes = (byte_base + (((uint32_t)(bit & 7u) + cnt * c_w + 7u) >> 3) + 15u) & ~15u;
+					}
+				}
 			}
-			const bool valid = s0 + pi < mycol.n_segs;
-			const DescQ dq = pi == 0 ? d0 : (valid ? load_desc(mycol.desc + s0 + pi) : d0);
-			pr = resolve_piece(mycol, dq, valid, r0, rows, a.literal);
-			if (pr.cnt) {
-				const uint64_t rs = dq.row_start();
-				row_lo = (uint32_t)((rs > r0 ? rs : r0) - r0);
-				first = (uint32_t)((rs > r0 ? rs : r0) - rs);
-				repacked = (dq.state() & kSegRepacked) ? 1u : 0u;
-				words = repacked ? dq.packed_ptr() : (uint64_t)mycol.raw + rs * (uint64_t)mycol.type_size;
-			}
-		}
-		// a predicate piece is staged iff pred32 can take it
-		const bool fast = active && pr.cnt && mycol.has_pred && pr.linear && pr.w <= 32u && (pr.flo >> 32) == 0 &&
-		                  !(pr.flo == 0 && pr.span == lo_set64(pr.w));
-		const uint32_t my_bytes = fast ? pr.bytes : 0u;
-		uint32_t incl = my_bytes;
+			const uint64_t mask64 = lo_set64(c_w);
+			const bool pred_piece = cnt && my_has_pred;
+			const bool all_pass = pred_piece && c_linear && c_flo == 0 && c_span == mask64;  // zone map
+			const bool fast = pred_piece && !all_pass && c_linear && c_w <= 32u && (c_flo >> 32) == 0;
+			const bool generic = pred_piece && !all_pass && !fast;
+			const uint32_t my_bytes = fast ? bytes : 0u;
+			uint32_t incl = my_bytes;
 #pragma unroll
-		for (int d = 1; d < 32; d <<= 1) {
-			const uint32_t v = __shfl_up_sync(0xffffffffu, incl, d);
-			if ((int)lane >= d) {
-				incl += v;
-			}
-		}
-		// every column must be covered by its three pieces, else the block takes the row-at-a-time path
-		uint32_t covered = pr.cnt;
-		covered += __shfl_xor_sync(0xffffffffu, covered, 1);
-		covered += __shfl_xor_sync(0xffffffffu, covered, 2);
-		const bool slow_block = __any_sync(0xffffffffu, active && covered != rows);
-		__syncwarp();
-		if (active) {
-			SPiece sp;
-			sp.r = pr;
-			sp.smem_off = incl - my_bytes;
-			sp.row_lo = row_lo;
-			sp.words = words;
-			sp.first = first;
-			sp.repacked = repacked;
-			if (!fast) {
-				sp.r.bytes = 0;
-			}
-			pieces[ci][pi] = sp;
-		}
-		__syncwarp();
-		// ---- B: stage the predicate pieces (whole warp per piece, 16 bytes per lane and round) ----
-		if (!slow_block) {
-#pragma unroll 1
-			for (uint32_t c = 0; c < a.n_cols; c++) {
-				if (!a.cols[c].has_pred) {
-					continue;
+			for (int d = 1; d < 32; d <<= 1) {
+				const uint32_t v = __shfl_up_sync(0xffffffffu, incl, d);
+				if ((int)lane >= d) {
+					incl += v;
 				}
-#pragma unroll 1
-				for (int p = 0; p < kQueryMaxPieces; p++) {
-					const uint32_t bytes = pieces[c][p].r.bytes;
-					if (bytes == 0) {
-						continue;
-					}
-					const uint8_t *src = (const uint8_t *)pieces[c][p].r.src16;
-					uint8_t *dst = window + pieces[c][p].smem_off;
-					for (uint32_t off = lane * 16u; off < bytes; off += 512u) {
-						cp_async16(dst + off, src + off);
+			}
+			const uint32_t smem_off = incl - my_bytes;
+			// every column must be covered by its three pieces, else the block takes the row-at-a-time path
+			uint32_t covered = cnt;
+			covered += __shfl_xor_sync(0xffffffffu, covered, 1);
+			covered += __shfl_xor_sync(0xffffffffu, covered, 2);
+			const bool slow_block = __any_sync(0xffffffffu, active && covered != rows);
+			const uint32_t fast_mask = slow_block ? 0u : __ballot_sync(0xffffffffu, fast);
+			const uint32_t generic_mask = slow_block ? 0u : __ballot_sync(0xffffffffu, generic);
+			__syncwarp();  // the previous block's survivor list (in the window) has been consumed
+			// ---- B: stage the predicate pieces ----
+			for (uint32_t m = fast_mask; m; m &= m - 1u) {
+				const int src_lane = __ffs((int)m) - 1;
+				const uint8_t *src = (const uint8_t *)__shfl_sync(0xffffffffu, src16, src_lane);
+				const uint32_t nb = __shfl_sync(0xffffffffu, my_bytes, src_lane);
+				uint8_t *dst = window + __shfl_sync(0xffffffffu, smem_off, src_lane);
+				for (uint32_t off = lane * 16u; off < nb; off += 512u) {
+					cp_async16(dst + off, src + off);
+				}
+			}
+			// ---- selection words of my groups (lane + 32 j) ----
+			uint32_t sel[kSGroupsPerLane];
+#pragma unroll
+			for (int j = 0; j < kSGroupsPerLane; j++) {
+				const uint32_t g = lane + 32u * j;
+				sel[j] = 0;
+				if (g < n_groups) {
+					const uint32_t left = rows - g * 32u;
+					sel[j] = left >= 32u ? 0xffffffffu : ((1u << left) - 1u);
+					if (a.in_bitmap != nullptr) {
+						sel[j] &= __ldg(a.in_bitmap + ((r0 - a.row_begin) >> 5) + g);
 					}
 				}
 			}
-			cp_async_wait_all();
-			__syncwarp();
-		}
-		// ---- C: selection word of my group ----
-		const uint32_t g = lane;
-		uint32_t sel = 0;
-		if (g < n_groups) {
-			const uint32_t left = rows - g * 32u;
-			sel = left >= 32u ? 0xffffffffu : ((1u << left) - 1u);
-			if (a.in_bitmap != nullptr) {
-				sel &= __ldg(a.in_bitmap + ((r0 - a.row_begin) >> 5) + g);
+			if (fast_mask) {
+				cp_async_wait_all();
+				__syncwarp();
 			}
-		}
-#pragma unroll 1
-		for (uint32_t c = 0; c < a.n_cols; c++) {
-			const QueryCol &qc = a.cols[c];
-			if (!qc.has_pred) {
-				continue;
-			}
-			if (slow_block) {
-				for (uint32_t gg = 0; gg < n_groups; gg++) {
-					const uint32_t i = gg * 32u + lane;
-					const bool pass = i >= rows || in_range(qc, row_value_global(qc, r0 + i, a.literal));
-					const uint32_t keep = __ballot_sync(0xffffffffu, pass);
-					if (lane == gg) {
-						sel &= keep;
+			// ---- C: predicates ----
+			for (uint32_t m = fast_mask; m; m &= m - 1u) {
+				const int src_lane = __ffs((int)m) - 1;
+				const uint32_t w = __shfl_sync(0xffffffffu, c_w, src_lane);
+				const uint32_t flo = __shfl_sync(0xffffffffu, (uint32_t)c_flo, src_lane);
+				const uint32_t span = __shfl_sync(0xffffffffu, (uint32_t)c_span, src_lane);
+				const uint32_t bb = __shfl_sync(0xffffffffu, bit_base, src_lane);
+				const uint32_t off_p = __shfl_sync(0xffffffffu, row_lo, src_lane);
+				const uint32_t end_p = off_p + __shfl_sync(0xffffffffu, cnt, src_lane);
+				const uint32_t *words32 = (const uint32_t *)(window + __shfl_sync(0xffffffffu, smem_off, src_lane));
+#pragma unroll
+				for (int j = 0; j < kSGroupsPerLane; j++) {
+					const uint32_t r_lo = (lane + 32u * j) * 32u;
+					if (r_lo >= off_p && r_lo + 32u <= end_p) {  // (groups beyond the block fail this: end_p <= rows)
+						const uint32_t bit = bb + (r_lo - off_p) * w;
+						sel[j] &= pred32_any(w, words32 + (bit >> 5), bit & 31u, flo, span);
 					}
 				}
-				continue;
-			}
-#pragma unroll 1
-			for (int p = 0; p < kQueryMaxPieces; p++) {
-				const SPiece &sp = pieces[c][p];
-				const uint32_t cnt = sp.r.cnt;
-				if (cnt == 0) {
-					continue;
-				}
-				const uint32_t off_p = sp.row_lo, end_p = off_p + cnt, w = sp.r.w;
-				const uint64_t mask64 = lo_set64(w);
-				if (sp.r.linear && sp.r.flo == 0 && sp.r.span == mask64) {
-					continue;  // zone map: every value of the piece passes
-				}
-				if (sp.r.bytes) {
-					const uint32_t *words32 = (const uint32_t *)(window + sp.smem_off);
-					const uint32_t flo = (uint32_t)sp.r.flo, span = (uint32_t)sp.r.span, mask = (uint32_t)mask64;
-					const uint32_t r_lo = g * 32u;
-					if (g < n_groups && r_lo >= off_p && r_lo + 32u <= end_p) {
-						const uint32_t bit = sp.r.bit_base + (r_lo - off_p) * w;
-						sel &= pred32_any(w, words32 + (bit >> 5), bit & 31u, flo, span);
-					}
+				if ((off_p | end_p) & 31u) {  // a piece boundary inside a group: lane = row
+					const uint32_t mask = w >= 32u ? 0xffffffffu : ((1u << w) - 1u);
 #pragma unroll 1
 					for (int e = 0; e < 2; e++) {
 						const uint32_t edge = e == 0 ? off_p : end_p;
-						if ((edge & 31u) == 0 || (edge >> 5) >= n_groups) {
+						if ((edge & 31u) == 0) {
 							continue;
 						}
 						const uint32_t ge = edge >> 5;
 						const uint32_t i = ge * 32u + lane;
 						const bool inside = i >= off_p && i < end_p;
-						const uint32_t bit = inside ? sp.r.bit_base + (i - off_p) * w : sp.r.bit_base;
+						const uint32_t bit = inside ? bb + (i - off_p) * w : bb;
 						const uint32_t f = read_bits32(words32, bit) & mask;
 						const uint32_t keep = __ballot_sync(0xffffffffu, !inside || (f - flo) <= span);
-						if (lane == ge) {
-							sel &= keep;
+#pragma unroll
+						for (int j = 0; j < kSGroupsPerLane; j++) {
+							if (lane + 32u * j == ge) {
+								sel[j] &= keep;
+							}
 						}
 					}
-				} else {
-					// not field-comparable: decode the rows of the piece from global memory, lane = row
-					const uint64_t *gw = (const uint64_t *)sp.words;
-					for (uint32_t gg = off_p >> 5; gg * 32u < end_p; gg++) {
+				}
+			}
+			for (uint32_t m = generic_mask; m; m &= m - 1u) {
+				// not field-comparable: decode the rows of the piece from global memory, lane = row
+				const int src_lane = __ffs((int)m) - 1;
+				const QueryCol &qc = a.cols[src_lane / kQLanesPerCol];
+				const uint32_t w = __shfl_sync(0xffffffffu, c_w, src_lane);
+				const uint64_t words = __shfl_sync(0xffffffffu, c_words, src_lane);
+				const uint64_t min_add = __shfl_sync(0xffffffffu, c_min_add, src_lane);
+				const uint32_t rep = __shfl_sync(0xffffffffu, c_repacked, src_lane);
+				const uint32_t k0 = __shfl_sync(0xffffffffu, first, src_lane);
+				const uint32_t off_p = __shfl_sync(0xffffffffu, row_lo, src_lane);
+				const uint32_t end_p = off_p + __shfl_sync(0xffffffffu, cnt, src_lane);
+				for (uint32_t gg = off_p >> 5; gg * 32u < end_p; gg++) {
+					const uint32_t i = gg * 32u + lane;
+					bool pass = true;
+					if (i >= off_p && i < end_p) {
+						const uint64_t f = field_global(words, rep, k0 + (i - off_p), w, qc.type_size);
+						pass = in_range(qc, extend_rt(f + min_add, qc.type_size, qc.is_signed));
+					}
+					const uint32_t keep = __ballot_sync(0xffffffffu, pass);
+#pragma unroll
+					for (int j = 0; j < kSGroupsPerLane; j++) {
+						if (lane + 32u * j == gg) {
+							sel[j] &= keep;
+						}
+					}
+				}
+			}
+			if (slow_block) {
+#pragma unroll 1
+				for (uint32_t c = 0; c < a.n_cols; c++) {
+					const QueryCol &qc = a.cols[c];
+					if (!qc.has_pred) {
+						continue;
+					}
+					for (uint32_t gg = 0; gg < n_groups; gg++) {
 						const uint32_t i = gg * 32u + lane;
-						bool pass = true;
-						if (i >= off_p && i < end_p) {
-							const uint32_t k = sp.first + (i - off_p);
-							uint64_t f;
-							if (sp.repacked) {
-								const uint64_t bit = (uint64_t)k * w;
-								const uint32_t off = (uint32_t)(bit & 63u);
-								f = __ldg(gw + (bit >> 6)) >> off;
-								if (off + w > 64u) {
-									f |= __ldg(gw + (bit >> 6) + 1) << (64u - off);
-								}
-								f &= mask64;
-							} else {
-								const uint8_t *ptr = (const uint8_t *)sp.words + (uint64_t)k * qc.type_size;
-								f = qc.type_size == 8 ? *(const uint64_t *)ptr
-								                      : (qc.type_size == 4 ? (uint64_t) * (const uint32_t *)ptr
-								                                           : (qc.type_size == 2 ? (uint64_t) * (const uint16_t *)ptr
-								                                                                : (uint64_t)*ptr));
-							}
-							pass = in_range(qc, extend_rt(f + sp.r.min_add, qc.type_size, qc.is_signed));
-						}
+						const bool pass = i >= rows || in_range(qc, row_value_global(qc, r0 + i, a.literal));
 						const uint32_t keep = __ballot_sync(0xffffffffu, pass);
-						if (lane == gg) {
-							sel &= keep;
+#pragma unroll
+						for (int j = 0; j < kSGroupsPerLane; j++) {
+							if (lane + 32u * j == gg) {
+								sel[j] &= keep;
+							}
+						}
+					}
+				}
+			}
+			// ---- D: survivors ----
+			uint32_t my_cnt = 0;
+#pragma unroll
+			for (int j = 0; j < kSGroupsPerLane; j++) {
+				const uint32_t g = lane + 32u * j;
+				if (a.out_bitmap != nullptr && g < n_groups) {
+					a.out_bitmap[((r0 - a.row_begin) >> 5) + g] = sel[j];
+				}
+				my_cnt += __popc(sel[j]);
+			}
+			uint32_t incl_c = my_cnt;
+#pragma unroll
+			for (int d = 1; d < 32; d <<= 1) {
+				const uint32_t v = __shfl_up_sync(0xffffffffu, incl_c, d);
+				if ((int)lane >= d) {
+					incl_c += v;
+				}
+			}
+			const uint32_t total = __shfl_sync(0xffffffffu, incl_c, 31);
+			if (total == 0) {
+				continue;
+			}
+			if (lane == 0) {
+				n_pass += total;
+			}
+			__syncwarp();  // every lane is past its last read of the staged columns: the list may overwrite them
+			uint32_t pos = incl_c - my_cnt;
+#pragma unroll
+			for (int j = 0; j < kSGroupsPerLane; j++) {
+				uint32_t rest = sel[j];
+				while (rest) {
+					const uint32_t bpos = (uint32_t)__ffs((int)rest) - 1u;
+					my_list[pos++] = (uint16_t)((lane + 32u * j) * 32u + bpos);
+					rest &= rest - 1u;
+				}
+			}
+			__syncwarp();
+			for (uint32_t e0 = 0; e0 < total; e0 += 32u) {
+				const uint32_t e = e0 + lane;
+				const bool live = e < total;
+				const uint32_t i = live ? my_list[e] : 0u;  // block row
+				int64_t v[kQueryMaxCols];
+#pragma unroll
+				for (int c = 0; c < kQueryMaxCols; c++) {
+					v[c] = 0;
+					if (c < (int)a.n_cols && ((a.factor_mask >> c) & 1u)) {  // uniform
+						const QueryCol &qc = a.cols[c];
+						if (slow_block) {
+							v[c] = live ? (int64_t)row_value_global(qc, r0 + i, a.literal) : 0;
+						} else {
+							// which of the column's pieces holds row i: their (row_lo, cnt) sit in lanes 4c .. 4c+2
+							const uint32_t lo1 = __shfl_sync(0xffffffffu, row_lo, c * kQLanesPerCol + 1);
+							const uint32_t n1 = __shfl_sync(0xffffffffu, cnt, c * kQLanesPerCol + 1);
+							const uint32_t lo2 = __shfl_sync(0xffffffffu, row_lo, c * kQLanesPerCol + 2);
+							const uint32_t n2 = __shfl_sync(0xffffffffu, cnt, c * kQLanesPerCol + 2);
+							const int p = (n2 && i >= lo2) ? 2 : ((n1 && i >= lo1) ? 1 : 0);
+							const int src_lane = c * kQLanesPerCol + p;
+							const uint32_t w = __shfl_sync(0xffffffffu, c_w, src_lane);
+							const uint64_t words = __shfl_sync(0xffffffffu, c_words, src_lane);
+							const uint64_t min_add = __shfl_sync(0xffffffffu, c_min_add, src_lane);
+							const uint32_t rep = __shfl_sync(0xffffffffu, c_repacked, src_lane);
+							const uint32_t k0 = __shfl_sync(0xffffffffu, first, src_lane);
+							const uint32_t off_p = __shfl_sync(0xffffffffu, row_lo, src_lane);
+							if (live) {
+								const uint64_t f = field_global(words, rep, k0 + (i - off_p), w, qc.type_size);
+								v[c] = (int64_t)extend_rt(f + min_add, qc.type_size, qc.is_signed);
+							}
+						}
+					}
+				}
+				if (!live) {
+					continue;
+				}
+#pragma unroll
+				for (int k = 0; k < NA; k++) {
+					if (k < (int)a.n_aggs) {
+						const QueryAgg &qa = a.aggs[k];
+						if (a.narrow_products) {
+							int64_t term = 1;
+#pragma unroll
+							for (int f = 0; f < kQueryMaxFactors; f++) {
+								if (f < (int)qa.n_factors) {
+									int64_t x = 0;
+#pragma unroll
+									for (int c = 0; c < kQueryMaxCols; c++) {
+										x = (int)qa.col[f] == c ? v[c] : x;
+									}
+									term *= qa.add[f] + qa.mul[f] * x;
+								}
+							}
+							acc[k] += (unsigned __int128)(__int128)term;
+						} else {
+							__int128 term = 1;
+#pragma unroll
+							for (int f = 0; f < kQueryMaxFactors; f++) {
+								if (f < (int)qa.n_factors) {
+									int64_t x = 0;
+#pragma unroll
+									for (int c = 0; c < kQueryMaxCols; c++) {
+										x = (int)qa.col[f] == c ? v[c] : x;
+									}
+									term *= (__int128)qa.add[f] + (__int128)qa.mul[f] * (__int128)x;
+								}
+							}
+							acc[k] += (unsigned __int128)term;
 						}
 					}
 				}
 			}
 		}
-		// ---- D: survivors ----
-		if (a.out_bitmap != nullptr && g < n_groups) {
-			a.out_bitmap[((r0 - a.row_begin) >> 5) + g] = sel;
-		}
-		const uint32_t cnt = __popc(sel);
-		uint32_t incl_c = cnt;
-#pragma unroll
-		for (int d = 1; d < 32; d <<= 1) {
-			const uint32_t v = __shfl_up_sync(0xffffffffu, incl_c, d);
-			if ((int)lane >= d) {
-				incl_c += v;
-			}
-		}
-		const uint32_t total = __shfl_sync(0xffffffffu, incl_c, 31);
-		if (total == 0) {
-			continue;
-		}
-		if (lane == 0) {
-			n_pass += total;
-		}
-		__syncwarp();
-		uint32_t pos = incl_c - cnt;
-		uint32_t rest = sel;
-		while (rest) {
-			const uint32_t bpos = (uint32_t)__ffs((int)rest) - 1u;
-			my_list[pos++] = (uint16_t)(g * 32u + bpos);
-			rest &= rest - 1u;
-		}
-		__syncwarp();  // (the list overwrites the staged columns: every lane is past its last predicate read)
-		for (uint32_t e = lane; e < total; e += 32u) {
-			const uint64_t row = r0 + my_list[e];
-			int64_t v[kQueryMaxCols];
-#pragma unroll
-			for (int c = 0; c < kQueryMaxCols; c++) {
-				v[c] = 0;
-				if (c < (int)a.n_cols && ((a.factor_mask >> c) & 1u)) {
-					v[c] = (int64_t)row_value_global(a.cols[c], row, a.literal);
-				}
-			}
-#pragma unroll
-			for (int k = 0; k < NA; k++) {
-				if (k < (int)a.n_aggs) {
-					const QueryAgg &qa = a.aggs[k];
-					if (a.narrow_products) {
-						int64_t term = 1;
-#pragma unroll
-						for (int f = 0; f < kQueryMaxFactors; f++) {
-							if (f < (int)qa.n_factors) {
-								int64_t x = 0;
-#pragma unroll
-								for (int c = 0; c < kQueryMaxCols; c++) {
-									x = (int)qa.col[f] == c ? v[c] : x;
-								}
-								term *= qa.add[f] + qa.mul[f] * x;
-							}
-						}
-						acc[k] += (unsigned __int128)(__int128)term;
-					} else {
-						__int128 term = 1;
-#pragma unroll
-						for (int f = 0; f < kQueryMaxFactors; f++) {
-							if (f < (int)qa.n_factors) {
-								int64_t x = 0;
-#pragma unroll
-								for (int c = 0; c < kQueryMaxCols; c++) {
-									x = (int)qa.col[f] == c ? v[c] : x;
-								}
-								term *= (__int128)qa.add[f] + (__int128)qa.mul[f] * (__int128)x;
-							}
-						}
-						acc[k] += (unsigned __int128)term;
-					}
-				}
-			}
-		}
-		__syncwarp();
 	}
 #pragma unroll
 	for (int g = 0; g < NA; g++) {
@@ -1327,7 +1370,7 @@ cudaError_t launch_scan_columns(const QueryArgs &args, int sm_count, cudaStream_
 		}
 		const uint64_t n_blocks = (args.row_end - args.row_begin + kSRows - 1) / kSRows;
 		uint64_t grid = (uint64_t)sm_count * (uint64_t)(per_sm > 0 ? per_sm : 1);
-		const uint64_t need = (n_blocks + kSWarps - 1) / kSWarps;
+		const uint64_t need = ((n_blocks + kSRun - 1) / kSRun + kSWarps - 1) / kSWarps;  // a warp takes runs of kSRun blocks
 		if (grid > need) {
 			grid = need;
 		}
