@@ -148,37 +148,53 @@ __device__ __forceinline__ bool row_passes(const QPiece *pc, const uint8_t *stag
 // offset with W funnel shifts, and every field then sits at a compile-time position: a row costs a shift, a mask, a
 // subtract, a compare and a select (the lane = row formulation pays two shared loads, an address computation and a
 // ballot share on top).  Consecutive lanes own consecutive groups (stride W words: conflict-free for odd W).
-template <int W>
-__device__ __forceinline__ uint32_t pred32(const uint32_t *p, uint32_t s0, uint32_t flo, uint32_t span) {
-	uint32_t r[W + 1];
-#pragma unroll
-	for (int t = 0; t <= W; t++) {
-		r[t] = p[t];
-	}
-#pragma unroll
-	for (int t = 0; t < W; t++) {
-		r[t] = __funnelshift_r(r[t], r[t + 1], s0);  // s0 == 0 leaves r[t]
-	}
-	constexpr uint32_t mask = W >= 32 ? 0xffffffffu : ((1u << (W & 31)) - 1u);
-	uint32_t part[4] = {0u, 0u, 0u, 0u};  // four independent chains instead of one 32-deep one
-#pragma unroll
-	for (int k = 0; k < 32; k++) {
-		const int bit = k * W, wi = bit >> 5, sh = bit & 31;
-		uint32_t f;
-		if (sh + W <= 32) {
-			f = r[wi] >> sh;
-			if (sh + W < 32) {
-				f &= mask;
-			}
-		} else {
-			f = __funnelshift_r(r[wi], r[wi + 1 < W ? wi + 1 : wi], sh) & mask;
-		}
-		part[k & 3] |= (f - flo) <= span ? (1u << k) : 0u;
-	}
-	return (part[0] | part[1]) | (part[2] | part[3]);
+__host__ __device__ constexpr int gcd32(int w) {
+	return (w % 32 == 0) ? 32 : ((w % 16 == 0) ? 16 : ((w % 8 == 0) ? 8 : ((w % 4 == 0) ? 4 : ((w % 2 == 0) ? 2 : 1))));
 }
 
-__device__ __forceinline__ uint32_t pred32_any(uint32_t w, const uint32_t *p, uint32_t s0, uint32_t flo, uint32_t span) {
+// The field positions repeat every 32 / gcd(W, 32) fields (= W / gcd words), so the 32 rows are walked as gcd(W, 32)
+// iterations of ONE short loop body with compile-time positions: the straight-line version (230 instructions per
+// width, three widths per query) made instruction fetch the top stall of the kernel (ncu: no_instruction).
+template <int W>
+__device__ __forceinline__ uint32_t pred32(const uint32_t *p, uint32_t s0, uint32_t flo, uint32_t span) {
+	constexpr int G = gcd32(W);   // iterations
+	constexpr int F = 32 / G;     // fields per iteration
+	constexpr int PW = W / G;     // words per iteration
+	constexpr uint32_t mask = W >= 32 ? 0xffffffffu : ((1u << (W & 31)) - 1u);
+	uint32_t word = 0;
+#pragma unroll 1
+	for (int it = 0; it < G; it++, p += PW) {
+		uint32_t r[PW + 1];
+#pragma unroll
+		for (int t = 0; t <= PW; t++) {
+			r[t] = p[t];
+		}
+#pragma unroll
+		for (int t = 0; t < PW; t++) {
+			r[t] = __funnelshift_r(r[t], r[t + 1], s0);  // s0 == 0 leaves r[t]
+		}
+		uint32_t part[2] = {0u, 0u};
+#pragma unroll
+		for (int k = 0; k < F; k++) {
+			const int bit = k * W, wi = bit >> 5, sh = bit & 31;
+			uint32_t f;
+			if (sh + W <= 32) {
+				f = r[wi] >> sh;
+				if (sh + W < 32) {
+					f &= mask;
+				}
+			} else {
+				f = __funnelshift_r(r[wi], r[wi + 1 < PW ? wi + 1 : wi], sh) & mask;
+			}
+			part[k & 1] |= (f - flo) <= span ? (1u << k) : 0u;
+		}
+		word |= (part[0] | part[1]) << (it * F);
+	}
+	return word;
+}
+
+// one copy of every width per kernel (not inlined at each call site): instruction fetch was the top stall
+__device__ __noinline__ uint32_t pred32_any(uint32_t w, const uint32_t *p, uint32_t s0, uint32_t flo, uint32_t span) {
 	switch (w) {
 #define ADACOM_P32(W) case W: return pred32<W>(p, s0, flo, span);
 	ADACOM_P32(1) ADACOM_P32(2) ADACOM_P32(3) ADACOM_P32(4) ADACOM_P32(5) ADACOM_P32(6) ADACOM_P32(7) ADACOM_P32(8)
@@ -1008,13 +1024,79 @@ __device__ __forceinline__ bool in_range(const QueryCol &c, uint64_t v) {
 	return c.is_signed ? ((int64_t)v >= c.lo && (int64_t)v <= c.hi) : (v >= (uint64_t)c.lo && v <= (uint64_t)c.hi);
 }
 
+// value of block row i of column c for a surviving row: the column's <= 3 piece records sit in the registers of lanes
+// 4c .. 4c+2 and are fetched by shuffle (every lane of the warp takes part; `live` lanes read the field)
+__device__ __noinline__ uint64_t sparse_factor_value(uint32_t type_size, uint32_t is_signed, uint32_t c, uint32_t i, bool live, uint32_t row_lo,
+                                                     uint32_t cnt, uint32_t first, uint32_t c_w, uint32_t c_repacked,
+                                                     uint64_t c_words, uint64_t c_min_add) {
+	const uint32_t lo1 = __shfl_sync(0xffffffffu, row_lo, c * kQLanesPerCol + 1);
+	const uint32_t n1 = __shfl_sync(0xffffffffu, cnt, c * kQLanesPerCol + 1);
+	const uint32_t lo2 = __shfl_sync(0xffffffffu, row_lo, c * kQLanesPerCol + 2);
+	const uint32_t n2 = __shfl_sync(0xffffffffu, cnt, c * kQLanesPerCol + 2);
+	const int p = (n2 && i >= lo2) ? 2 : ((n1 && i >= lo1) ? 1 : 0);
+	const int src_lane = c * kQLanesPerCol + p;
+	const uint32_t w = __shfl_sync(0xffffffffu, c_w, src_lane);
+	const uint64_t words = __shfl_sync(0xffffffffu, c_words, src_lane);
+	const uint64_t min_add = __shfl_sync(0xffffffffu, c_min_add, src_lane);
+	const uint32_t rep = __shfl_sync(0xffffffffu, c_repacked, src_lane);
+	const uint32_t k0 = __shfl_sync(0xffffffffu, first, src_lane);
+	const uint32_t off_p = __shfl_sync(0xffffffffu, row_lo, src_lane);
+	if (!live) {
+		return 0;
+	}
+	return extend_rt(field_global(words, rep, k0 + (i - off_p), w, type_size) + min_add, type_size, is_signed);
+}
+
+// predicate of column c on block row i of a surviving row (list mode): piece records by shuffle as above; staged
+// pieces are read from the warp's window with a run-time shift, the others from global memory
+__device__ __noinline__ bool sparse_row_passes(uint32_t type_size, uint32_t is_signed, int64_t lo, int64_t hi, uint32_t c,
+                                               uint32_t i, bool live, const uint8_t *window, uint32_t kind, uint32_t row_lo,
+                                               uint32_t cnt, uint32_t first, uint32_t bit_base, uint32_t smem_off,
+                                               uint32_t c_w, uint32_t c_repacked, uint64_t c_words, uint64_t c_min_add,
+                                               uint32_t flo32, uint32_t span32) {
+	const uint32_t lo1 = __shfl_sync(0xffffffffu, row_lo, c * kQLanesPerCol + 1);
+	const uint32_t n1 = __shfl_sync(0xffffffffu, cnt, c * kQLanesPerCol + 1);
+	const uint32_t lo2 = __shfl_sync(0xffffffffu, row_lo, c * kQLanesPerCol + 2);
+	const uint32_t n2 = __shfl_sync(0xffffffffu, cnt, c * kQLanesPerCol + 2);
+	const int p = (n2 && i >= lo2) ? 2 : ((n1 && i >= lo1) ? 1 : 0);
+	const int src_lane = c * kQLanesPerCol + p;
+	const uint32_t k = __shfl_sync(0xffffffffu, kind, src_lane);
+	const uint32_t w = __shfl_sync(0xffffffffu, c_w, src_lane);
+	const uint32_t off_p = __shfl_sync(0xffffffffu, row_lo, src_lane);
+	const uint32_t bb = __shfl_sync(0xffffffffu, bit_base, src_lane);
+	const uint32_t so = __shfl_sync(0xffffffffu, smem_off, src_lane);
+	const uint32_t flo = __shfl_sync(0xffffffffu, flo32, src_lane);
+	const uint32_t span = __shfl_sync(0xffffffffu, span32, src_lane);
+	const uint64_t words = __shfl_sync(0xffffffffu, c_words, src_lane);
+	const uint64_t min_add = __shfl_sync(0xffffffffu, c_min_add, src_lane);
+	const uint32_t rep = __shfl_sync(0xffffffffu, c_repacked, src_lane);
+	const uint32_t k0 = __shfl_sync(0xffffffffu, first, src_lane);
+	if (!live) {
+		return false;
+	}
+	if (k == 0) {
+		return true;  // zone map: the whole piece passes
+	}
+	if (k == 1) {
+		const uint32_t mask = w >= 32u ? 0xffffffffu : ((1u << w) - 1u);
+		const uint32_t f = read_bits32((const uint32_t *)(window + so), bb + (i - off_p) * w) & mask;
+		return (f - flo) <= span;
+	}
+	const uint64_t v = extend_rt(field_global(words, rep, k0 + (i - off_p), w, type_size) + min_add, type_size, is_signed);
+	return is_signed ? ((int64_t)v >= lo && (int64_t)v <= hi) : (v >= (uint64_t)lo && v <= (uint64_t)hi);
+}
+
+constexpr uint32_t kSSmallCap = 384;  // survivors a warp keeps when the later predicates run on the compacted list
+
 template <int NA>  // upper bound of a.n_aggs (1, 2, 4, 8): the 128-bit accumulators live in registers
 __global__ void __launch_bounds__(kSWarps * 32, 4) scan_columns_sparse_kernel(const QueryArgs a, uint32_t window_bytes) {
 	extern __shared__ __align__(128) uint8_t s_mem[];
 	__shared__ uint64_t red[96];
+	__shared__ uint16_t s_small[kSWarps][kSSmallCap];
 	const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
 	uint8_t *window = s_mem + (size_t)warp * window_bytes;
 	uint16_t *my_list = (uint16_t *)window;  // the survivor list reuses the window once the predicates are done (>= 4 KiB)
+	uint16_t *small = s_small[warp];
 	const uint64_t n_rows = a.row_end - a.row_begin;
 	const uint32_t n_blocks = (uint32_t)((n_rows + kSRows - 1) / kSRows);
 	const uint32_t ci = lane / kQLanesPerCol, pi = lane % kQLanesPerCol;
@@ -1083,6 +1165,7 @@ __global__ void __launch_bounds__(kSWarps * 32, 4) scan_columns_sparse_kernel(co
 			const bool all_pass = pred_piece && c_linear && c_flo == 0 && c_span == mask64;  // zone map
 			const bool fast = pred_piece && !all_pass && c_linear && c_w <= 32u && (c_flo >> 32) == 0;
 			const bool generic = pred_piece && !all_pass && !fast;
+			const uint32_t kind = fast ? 1u : (generic ? 2u : 0u);
 			const uint32_t my_bytes = fast ? bytes : 0u;
 			uint32_t incl = my_bytes;
 #pragma unroll
@@ -1129,8 +1212,36 @@ __global__ void __launch_bounds__(kSWarps * 32, 4) scan_columns_sparse_kernel(co
 				cp_async_wait_all();
 				__syncwarp();
 			}
-			// ---- C: predicates ----
-			for (uint32_t m = fast_mask; m; m &= m - 1u) {
+			// ---- C: predicates, column by column; once few rows are left the remaining columns test the compacted list ----
+			bool list_mode = false;
+			uint32_t n_list = 0;
+#pragma unroll 1
+			for (uint32_t c = 0; c < a.n_cols; c++) {
+			const uint32_t col_bits = 0xfu << (c * kQLanesPerCol);
+			if (((fast_mask | generic_mask) & col_bits) == 0) {
+				continue;
+			}
+			if (list_mode) {
+				const QueryCol &qc = a.cols[c];
+				uint32_t kept = 0;
+				for (uint32_t e0 = 0; e0 < n_list; e0 += 32u) {
+					const uint32_t e = e0 + lane;
+					const bool live = e < n_list;
+					const uint32_t i = live ? small[e] : 0u;
+					const bool keep = sparse_row_passes(qc.type_size, qc.is_signed, qc.lo, qc.hi, c, i, live, window, kind, row_lo, cnt,
+					                                    first, bit_base, smem_off, c_w, c_repacked, c_words, c_min_add,
+					                                    (uint32_t)c_flo, (uint32_t)c_span);
+					const uint32_t mk = __ballot_sync(0xffffffffu, keep);  // every read of this round is done
+					if (keep) {
+						small[kept + __popc(mk & ((1u << lane) - 1u))] = (uint16_t)i;
+					}
+					kept += __popc(mk);
+				}
+				__syncwarp();
+				n_list = kept;
+				continue;
+			}
+			for (uint32_t m = fast_mask & col_bits; m; m &= m - 1u) {
 				const int src_lane = __ffs((int)m) - 1;
 				const uint32_t w = __shfl_sync(0xffffffffu, c_w, src_lane);
 				const uint32_t flo = __shfl_sync(0xffffffffu, (uint32_t)c_flo, src_lane);
@@ -1139,12 +1250,14 @@ __global__ void __launch_bounds__(kSWarps * 32, 4) scan_columns_sparse_kernel(co
 				const uint32_t off_p = __shfl_sync(0xffffffffu, row_lo, src_lane);
 				const uint32_t end_p = off_p + __shfl_sync(0xffffffffu, cnt, src_lane);
 				const uint32_t *words32 = (const uint32_t *)(window + __shfl_sync(0xffffffffu, smem_off, src_lane));
-#pragma unroll
+#pragma unroll 1
 				for (int j = 0; j < kSGroupsPerLane; j++) {
 					const uint32_t r_lo = (lane + 32u * j) * 32u;
 					if (r_lo >= off_p && r_lo + 32u <= end_p) {  // (groups beyond the block fail this: end_p <= rows)
 						const uint32_t bit = bb + (r_lo - off_p) * w;
-						sel[j] &= pred32_any(w, words32 + (bit >> 5), bit & 31u, flo, span);
+						const uint32_t keep = pred32_any(w, words32 + (bit >> 5), bit & 31u, flo, span);
+						sel[0] &= j == 0 ? keep : 0xffffffffu;
+						sel[1] &= j == 1 ? keep : 0xffffffffu;
 					}
 				}
 				if ((off_p | end_p) & 31u) {  // a piece boundary inside a group: lane = row
@@ -1170,7 +1283,7 @@ __global__ void __launch_bounds__(kSWarps * 32, 4) scan_columns_sparse_kernel(co
 					}
 				}
 			}
-			for (uint32_t m = generic_mask; m; m &= m - 1u) {
+			for (uint32_t m = generic_mask & col_bits; m; m &= m - 1u) {
 				// not field-comparable: decode the rows of the piece from global memory, lane = row
 				const int src_lane = __ffs((int)m) - 1;
 				const QueryCol &qc = a.cols[src_lane / kQLanesPerCol];
@@ -1197,6 +1310,37 @@ __global__ void __launch_bounds__(kSWarps * 32, 4) scan_columns_sparse_kernel(co
 					}
 				}
 			}
+			// survivors so far: at <= 1/32 of the rows (and no bitmap wanted) the remaining predicate columns cost less on a
+			// list (measured on TPC-H Q6: switching at 15 % -- after the shipdate range -- is slower than pred32 over
+			// every row, 0.23 against 0.16 ms: a listed row costs ~17 shuffles for its piece record)
+			if (a.out_bitmap == nullptr && c + 1 < a.n_cols && ((fast_mask | generic_mask) >> ((c + 1) * kQLanesPerCol)) != 0) {
+				const uint32_t mine = __popc(sel[0]) + __popc(sel[1]);
+				uint32_t inc2 = mine;
+#pragma unroll
+				for (int d = 1; d < 32; d <<= 1) {
+					const uint32_t v = __shfl_up_sync(0xffffffffu, inc2, d);
+					if ((int)lane >= d) {
+						inc2 += v;
+					}
+				}
+				const uint32_t tot2 = __shfl_sync(0xffffffffu, inc2, 31);
+				if (tot2 <= kSSmallCap && tot2 * 32u <= rows) {
+					uint32_t pos2 = inc2 - mine;
+#pragma unroll
+					for (int j = 0; j < kSGroupsPerLane; j++) {
+						uint32_t rest = sel[j];
+						while (rest) {
+							const uint32_t bpos = (uint32_t)__ffs((int)rest) - 1u;
+							small[pos2++] = (uint16_t)((lane + 32u * j) * 32u + bpos);
+							rest &= rest - 1u;
+						}
+					}
+					__syncwarp();
+					list_mode = true;
+					n_list = tot2;
+				}
+			}
+			}
 			if (slow_block) {
 #pragma unroll 1
 				for (uint32_t c = 0; c < a.n_cols; c++) {
@@ -1218,110 +1362,78 @@ __global__ void __launch_bounds__(kSWarps * 32, 4) scan_columns_sparse_kernel(co
 				}
 			}
 			// ---- D: survivors ----
-			uint32_t my_cnt = 0;
+			uint32_t total = n_list;
+			const uint16_t *lst = small;
+			if (!list_mode) {
+				uint32_t my_cnt = 0;
 #pragma unroll
-			for (int j = 0; j < kSGroupsPerLane; j++) {
-				const uint32_t g = lane + 32u * j;
-				if (a.out_bitmap != nullptr && g < n_groups) {
-					a.out_bitmap[((r0 - a.row_begin) >> 5) + g] = sel[j];
+				for (int j = 0; j < kSGroupsPerLane; j++) {
+					const uint32_t g = lane + 32u * j;
+					if (a.out_bitmap != nullptr && g < n_groups) {
+						a.out_bitmap[((r0 - a.row_begin) >> 5) + g] = sel[j];
+					}
+					my_cnt += __popc(sel[j]);
 				}
-				my_cnt += __popc(sel[j]);
-			}
-			uint32_t incl_c = my_cnt;
+				uint32_t incl_c = my_cnt;
 #pragma unroll
-			for (int d = 1; d < 32; d <<= 1) {
-				const uint32_t v = __shfl_up_sync(0xffffffffu, incl_c, d);
-				if ((int)lane >= d) {
-					incl_c += v;
+				for (int d = 1; d < 32; d <<= 1) {
+					const uint32_t v = __shfl_up_sync(0xffffffffu, incl_c, d);
+					if ((int)lane >= d) {
+						incl_c += v;
+					}
 				}
+				total = __shfl_sync(0xffffffffu, incl_c, 31);
+				if (total) {
+					__syncwarp();  // every lane is past its last read of the staged columns: the list may overwrite them
+					uint32_t pos = incl_c - my_cnt;
+#pragma unroll
+					for (int j = 0; j < kSGroupsPerLane; j++) {
+						uint32_t rest = sel[j];
+						while (rest) {
+							const uint32_t bpos = (uint32_t)__ffs((int)rest) - 1u;
+							my_list[pos++] = (uint16_t)((lane + 32u * j) * 32u + bpos);
+							rest &= rest - 1u;
+						}
+					}
+					__syncwarp();
+				}
+				lst = my_list;
 			}
-			const uint32_t total = __shfl_sync(0xffffffffu, incl_c, 31);
 			if (total == 0) {
 				continue;
 			}
 			if (lane == 0) {
 				n_pass += total;
 			}
-			__syncwarp();  // every lane is past its last read of the staged columns: the list may overwrite them
-			uint32_t pos = incl_c - my_cnt;
-#pragma unroll
-			for (int j = 0; j < kSGroupsPerLane; j++) {
-				uint32_t rest = sel[j];
-				while (rest) {
-					const uint32_t bpos = (uint32_t)__ffs((int)rest) - 1u;
-					my_list[pos++] = (uint16_t)((lane + 32u * j) * 32u + bpos);
-					rest &= rest - 1u;
-				}
-			}
-			__syncwarp();
 			for (uint32_t e0 = 0; e0 < total; e0 += 32u) {
 				const uint32_t e = e0 + lane;
 				const bool live = e < total;
-				const uint32_t i = live ? my_list[e] : 0u;  // block row
-				int64_t v[kQueryMaxCols];
-#pragma unroll
-				for (int c = 0; c < kQueryMaxCols; c++) {
-					v[c] = 0;
-					if (c < (int)a.n_cols && ((a.factor_mask >> c) & 1u)) {  // uniform
-						const QueryCol &qc = a.cols[c];
-						if (slow_block) {
-							v[c] = live ? (int64_t)row_value_global(qc, r0 + i, a.literal) : 0;
-						} else {
-							// which of the column's pieces holds row i: their (row_lo, cnt) sit in lanes 4c .. 4c+2
-							const uint32_t lo1 = __shfl_sync(0xffffffffu, row_lo, c * kQLanesPerCol + 1);
-							const uint32_t n1 = __shfl_sync(0xffffffffu, cnt, c * kQLanesPerCol + 1);
-							const uint32_t lo2 = __shfl_sync(0xffffffffu, row_lo, c * kQLanesPerCol + 2);
-							const uint32_t n2 = __shfl_sync(0xffffffffu, cnt, c * kQLanesPerCol + 2);
-							const int p = (n2 && i >= lo2) ? 2 : ((n1 && i >= lo1) ? 1 : 0);
-							const int src_lane = c * kQLanesPerCol + p;
-							const uint32_t w = __shfl_sync(0xffffffffu, c_w, src_lane);
-							const uint64_t words = __shfl_sync(0xffffffffu, c_words, src_lane);
-							const uint64_t min_add = __shfl_sync(0xffffffffu, c_min_add, src_lane);
-							const uint32_t rep = __shfl_sync(0xffffffffu, c_repacked, src_lane);
-							const uint32_t k0 = __shfl_sync(0xffffffffu, first, src_lane);
-							const uint32_t off_p = __shfl_sync(0xffffffffu, row_lo, src_lane);
-							if (live) {
-								const uint64_t f = field_global(words, rep, k0 + (i - off_p), w, qc.type_size);
-								v[c] = (int64_t)extend_rt(f + min_add, qc.type_size, qc.is_signed);
-							}
-						}
-					}
-				}
-				if (!live) {
-					continue;
-				}
+				const uint32_t i = live ? lst[e] : 0u;  // block row
 #pragma unroll
 				for (int k = 0; k < NA; k++) {
-					if (k < (int)a.n_aggs) {
+					if (k < (int)a.n_aggs) {  // uniform
 						const QueryAgg &qa = a.aggs[k];
-						if (a.narrow_products) {
-							int64_t term = 1;
-#pragma unroll
-							for (int f = 0; f < kQueryMaxFactors; f++) {
-								if (f < (int)qa.n_factors) {
-									int64_t x = 0;
-#pragma unroll
-									for (int c = 0; c < kQueryMaxCols; c++) {
-										x = (int)qa.col[f] == c ? v[c] : x;
-									}
-									term *= qa.add[f] + qa.mul[f] * x;
-								}
+						__int128 term = 1;
+						int64_t term64 = 1;
+#pragma unroll 1
+						for (uint32_t f = 0; f < qa.n_factors; f++) {
+							const uint32_t c = qa.col[f];
+							const QueryCol &qc = a.cols[c];
+							int64_t x;
+							if (slow_block) {
+								x = live ? (int64_t)row_value_global(qc, r0 + i, a.literal) : 0;
+							} else {
+								x = (int64_t)sparse_factor_value(qc.type_size, qc.is_signed, c, i, live, row_lo, cnt, first, c_w, c_repacked, c_words,
+								                                 c_min_add);
 							}
-							acc[k] += (unsigned __int128)(__int128)term;
-						} else {
-							__int128 term = 1;
-#pragma unroll
-							for (int f = 0; f < kQueryMaxFactors; f++) {
-								if (f < (int)qa.n_factors) {
-									int64_t x = 0;
-#pragma unroll
-									for (int c = 0; c < kQueryMaxCols; c++) {
-										x = (int)qa.col[f] == c ? v[c] : x;
-									}
-									term *= (__int128)qa.add[f] + (__int128)qa.mul[f] * (__int128)x;
-								}
+							if (a.narrow_products) {
+								term64 *= qa.add[f] + qa.mul[f] * x;
+							} else {
+								term *= (__int128)qa.add[f] + (__int128)qa.mul[f] * (__int128)x;
 							}
-							acc[k] += (unsigned __int128)term;
+						}
+						if (live) {
+							acc[k] += a.narrow_products ? (unsigned __int128)(__int128)term64 : (unsigned __int128)term;
 						}
 					}
 				}
