@@ -968,6 +968,8 @@ __global__ void __launch_bounds__(kQThreads, 4) scan_columns_kernel(const QueryA
 //      piece boundary and pieces that are not field-comparable (wrap-around frames, > 32 bits, raw signed slots) are
 //      evaluated lane = row;
 //   D  the few survivors are compacted into a list (in the window) and their factor values are read from global memory.
+// (Testing the later predicate columns on the compacted survivors of the first one -- what the pipelined kernel does --
+// was measured slower here: 0.23 against 0.16 ms on TPC-H Q6; a listed row costs ~17 shuffles for its piece record.)
 // No CTA barrier, no mbarrier, no shared selection state: latency is hidden by the 32 independent warps an SM holds.
 // The integer pipe bounds this kernel (ncu: math-pipe throttle), so the design minimises instructions per row.
 // =====================================================================================================================
@@ -1047,56 +1049,13 @@ __device__ __noinline__ uint64_t sparse_factor_value(uint32_t type_size, uint32_
 	return extend_rt(field_global(words, rep, k0 + (i - off_p), w, type_size) + min_add, type_size, is_signed);
 }
 
-// predicate of column c on block row i of a surviving row (list mode): piece records by shuffle as above; staged
-// pieces are read from the warp's window with a run-time shift, the others from global memory
-__device__ __noinline__ bool sparse_row_passes(uint32_t type_size, uint32_t is_signed, int64_t lo, int64_t hi, uint32_t c,
-                                               uint32_t i, bool live, const uint8_t *window, uint32_t kind, uint32_t row_lo,
-                                               uint32_t cnt, uint32_t first, uint32_t bit_base, uint32_t smem_off,
-                                               uint32_t c_w, uint32_t c_repacked, uint64_t c_words, uint64_t c_min_add,
-                                               uint32_t flo32, uint32_t span32) {
-	const uint32_t lo1 = __shfl_sync(0xffffffffu, row_lo, c * kQLanesPerCol + 1);
-	const uint32_t n1 = __shfl_sync(0xffffffffu, cnt, c * kQLanesPerCol + 1);
-	const uint32_t lo2 = __shfl_sync(0xffffffffu, row_lo, c * kQLanesPerCol + 2);
-	const uint32_t n2 = __shfl_sync(0xffffffffu, cnt, c * kQLanesPerCol + 2);
-	const int p = (n2 && i >= lo2) ? 2 : ((n1 && i >= lo1) ? 1 : 0);
-	const int src_lane = c * kQLanesPerCol + p;
-	const uint32_t k = __shfl_sync(0xffffffffu, kind, src_lane);
-	const uint32_t w = __shfl_sync(0xffffffffu, c_w, src_lane);
-	const uint32_t off_p = __shfl_sync(0xffffffffu, row_lo, src_lane);
-	const uint32_t bb = __shfl_sync(0xffffffffu, bit_base, src_lane);
-	const uint32_t so = __shfl_sync(0xffffffffu, smem_off, src_lane);
-	const uint32_t flo = __shfl_sync(0xffffffffu, flo32, src_lane);
-	const uint32_t span = __shfl_sync(0xffffffffu, span32, src_lane);
-	const uint64_t words = __shfl_sync(0xffffffffu, c_words, src_lane);
-	const uint64_t min_add = __shfl_sync(0xffffffffu, c_min_add, src_lane);
-	const uint32_t rep = __shfl_sync(0xffffffffu, c_repacked, src_lane);
-	const uint32_t k0 = __shfl_sync(0xffffffffu, first, src_lane);
-	if (!live) {
-		return false;
-	}
-	if (k == 0) {
-		return true;  // zone map: the whole piece passes
-	}
-	if (k == 1) {
-		const uint32_t mask = w >= 32u ? 0xffffffffu : ((1u << w) - 1u);
-		const uint32_t f = read_bits32((const uint32_t *)(window + so), bb + (i - off_p) * w) & mask;
-		return (f - flo) <= span;
-	}
-	const uint64_t v = extend_rt(field_global(words, rep, k0 + (i - off_p), w, type_size) + min_add, type_size, is_signed);
-	return is_signed ? ((int64_t)v >= lo && (int64_t)v <= hi) : (v >= (uint64_t)lo && v <= (uint64_t)hi);
-}
-
-constexpr uint32_t kSSmallCap = 384;  // survivors a warp keeps when the later predicates run on the compacted list
-
 template <int NA>  // upper bound of a.n_aggs (1, 2, 4, 8): the 128-bit accumulators live in registers
 __global__ void __launch_bounds__(kSWarps * 32, 4) scan_columns_sparse_kernel(const QueryArgs a, uint32_t window_bytes) {
 	extern __shared__ __align__(128) uint8_t s_mem[];
 	__shared__ uint64_t red[96];
-	__shared__ uint16_t s_small[kSWarps][kSSmallCap];
 	const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
 	uint8_t *window = s_mem + (size_t)warp * window_bytes;
 	uint16_t *my_list = (uint16_t *)window;  // the survivor list reuses the window once the predicates are done (>= 4 KiB)
-	uint16_t *small = s_small[warp];
 	const uint64_t n_rows = a.row_end - a.row_begin;
 	const uint32_t n_blocks = (uint32_t)((n_rows + kSRows - 1) / kSRows);
 	const uint32_t ci = lane / kQLanesPerCol, pi = lane % kQLanesPerCol;
@@ -1165,7 +1124,6 @@ __global__ void __launch_bounds__(kSWarps * 32, 4) scan_columns_sparse_kernel(co
 			const bool all_pass = pred_piece && c_linear && c_flo == 0 && c_span == mask64;  // zone map
 			const bool fast = pred_piece && !all_pass && c_linear && c_w <= 32u && (c_flo >> 32) == 0;
 			const bool generic = pred_piece && !all_pass && !fast;
-			const uint32_t kind = fast ? 1u : (generic ? 2u : 0u);
 			const uint32_t my_bytes = fast ? bytes : 0u;
 			uint32_t incl = my_bytes;
 #pragma unroll
@@ -1212,36 +1170,9 @@ __global__ void __launch_bounds__(kSWarps * 32, 4) scan_columns_sparse_kernel(co
 				cp_async_wait_all();
 				__syncwarp();
 			}
-			// ---- C: predicates, column by column; once few rows are left the remaining columns test the compacted list ----
-			bool list_mode = false;
-			uint32_t n_list = 0;
-#pragma unroll 1
-			for (uint32_t c = 0; c < a.n_cols; c++) {
-			const uint32_t col_bits = 0xfu << (c * kQLanesPerCol);
-			if (((fast_mask | generic_mask) & col_bits) == 0) {
-				continue;
-			}
-			if (list_mode) {
-				const QueryCol &qc = a.cols[c];
-				uint32_t kept = 0;
-				for (uint32_t e0 = 0; e0 < n_list; e0 += 32u) {
-					const uint32_t e = e0 + lane;
-					const bool live = e < n_list;
-					const uint32_t i = live ? small[e] : 0u;
-					const bool keep = sparse_row_passes(qc.type_size, qc.is_signed, qc.lo, qc.hi, c, i, live, window, kind, row_lo, cnt,
-					                                    first, bit_base, smem_off, c_w, c_repacked, c_words, c_min_add,
-					                                    (uint32_t)c_flo, (uint32_t)c_span);
-					const uint32_t mk = __ballot_sync(0xffffffffu, keep);  // every read of this round is done
-					if (keep) {
-						small[kept + __popc(mk & ((1u << lane) - 1u))] = (uint16_t)i;
-					}
-					kept += __popc(mk);
-				}
-				__syncwarp();
-				n_list = kept;
-				continue;
-			}
-			for (uint32_t m = fast_mask & col_bits; m; m &= m - 1u) {
+			// ---- C: predicates (pieces in column order) ----
+			{
+			for (uint32_t m = fast_mask; m; m &= m - 1u) {
 				const int src_lane = __ffs((int)m) - 1;
 				const uint32_t w = __shfl_sync(0xffffffffu, c_w, src_lane);
 				const uint32_t flo = __shfl_sync(0xffffffffu, (uint32_t)c_flo, src_lane);
@@ -1283,7 +1214,7 @@ __global__ void __launch_bounds__(kSWarps * 32, 4) scan_columns_sparse_kernel(co
 					}
 				}
 			}
-			for (uint32_t m = generic_mask & col_bits; m; m &= m - 1u) {
+			for (uint32_t m = generic_mask; m; m &= m - 1u) {
 				// not field-comparable: decode the rows of the piece from global memory, lane = row
 				const int src_lane = __ffs((int)m) - 1;
 				const QueryCol &qc = a.cols[src_lane / kQLanesPerCol];
@@ -1310,36 +1241,6 @@ __global__ void __launch_bounds__(kSWarps * 32, 4) scan_columns_sparse_kernel(co
 					}
 				}
 			}
-			// survivors so far: at <= 1/32 of the rows (and no bitmap wanted) the remaining predicate columns cost less on a
-			// list (measured on TPC-H Q6: switching at 15 % -- after the shipdate range -- is slower than pred32 over
-			// every row, 0.23 against 0.16 ms: a listed row costs ~17 shuffles for its piece record)
-			if (a.out_bitmap == nullptr && c + 1 < a.n_cols && ((fast_mask | generic_mask) >> ((c + 1) * kQLanesPerCol)) != 0) {
-				const uint32_t mine = __popc(sel[0]) + __popc(sel[1]);
-				uint32_t inc2 = mine;
-#pragma unroll
-				for (int d = 1; d < 32; d <<= 1) {
-					const uint32_t v = __shfl_up_sync(0xffffffffu, inc2, d);
-					if ((int)lane >= d) {
-						inc2 += v;
-					}
-				}
-				const uint32_t tot2 = __shfl_sync(0xffffffffu, inc2, 31);
-				if (tot2 <= kSSmallCap && tot2 * 32u <= rows) {
-					uint32_t pos2 = inc2 - mine;
-#pragma unroll
-					for (int j = 0; j < kSGroupsPerLane; j++) {
-						uint32_t rest = sel[j];
-						while (rest) {
-							const uint32_t bpos = (uint32_t)__ffs((int)rest) - 1u;
-							small[pos2++] = (uint16_t)((lane + 32u * j) * 32u + bpos);
-							rest &= rest - 1u;
-						}
-					}
-					__syncwarp();
-					list_mode = true;
-					n_list = tot2;
-				}
-			}
 			}
 			if (slow_block) {
 #pragma unroll 1
@@ -1362,53 +1263,46 @@ __global__ void __launch_bounds__(kSWarps * 32, 4) scan_columns_sparse_kernel(co
 				}
 			}
 			// ---- D: survivors ----
-			uint32_t total = n_list;
-			const uint16_t *lst = small;
-			if (!list_mode) {
-				uint32_t my_cnt = 0;
+			uint32_t my_cnt = 0;
 #pragma unroll
-				for (int j = 0; j < kSGroupsPerLane; j++) {
-					const uint32_t g = lane + 32u * j;
-					if (a.out_bitmap != nullptr && g < n_groups) {
-						a.out_bitmap[((r0 - a.row_begin) >> 5) + g] = sel[j];
-					}
-					my_cnt += __popc(sel[j]);
+			for (int j = 0; j < kSGroupsPerLane; j++) {
+				const uint32_t g = lane + 32u * j;
+				if (a.out_bitmap != nullptr && g < n_groups) {
+					a.out_bitmap[((r0 - a.row_begin) >> 5) + g] = sel[j];
 				}
-				uint32_t incl_c = my_cnt;
-#pragma unroll
-				for (int d = 1; d < 32; d <<= 1) {
-					const uint32_t v = __shfl_up_sync(0xffffffffu, incl_c, d);
-					if ((int)lane >= d) {
-						incl_c += v;
-					}
-				}
-				total = __shfl_sync(0xffffffffu, incl_c, 31);
-				if (total) {
-					__syncwarp();  // every lane is past its last read of the staged columns: the list may overwrite them
-					uint32_t pos = incl_c - my_cnt;
-#pragma unroll
-					for (int j = 0; j < kSGroupsPerLane; j++) {
-						uint32_t rest = sel[j];
-						while (rest) {
-							const uint32_t bpos = (uint32_t)__ffs((int)rest) - 1u;
-							my_list[pos++] = (uint16_t)((lane + 32u * j) * 32u + bpos);
-							rest &= rest - 1u;
-						}
-					}
-					__syncwarp();
-				}
-				lst = my_list;
+				my_cnt += __popc(sel[j]);
 			}
+			uint32_t incl_c = my_cnt;
+#pragma unroll
+			for (int d = 1; d < 32; d <<= 1) {
+				const uint32_t v = __shfl_up_sync(0xffffffffu, incl_c, d);
+				if ((int)lane >= d) {
+					incl_c += v;
+				}
+			}
+			const uint32_t total = __shfl_sync(0xffffffffu, incl_c, 31);
 			if (total == 0) {
 				continue;
 			}
 			if (lane == 0) {
 				n_pass += total;
 			}
+			__syncwarp();  // every lane is past its last read of the staged columns: the list may overwrite them
+			uint32_t pos = incl_c - my_cnt;
+#pragma unroll
+			for (int j = 0; j < kSGroupsPerLane; j++) {
+				uint32_t rest = sel[j];
+				while (rest) {
+					const uint32_t bpos = (uint32_t)__ffs((int)rest) - 1u;
+					my_list[pos++] = (uint16_t)((lane + 32u * j) * 32u + bpos);
+					rest &= rest - 1u;
+				}
+			}
+			__syncwarp();
 			for (uint32_t e0 = 0; e0 < total; e0 += 32u) {
 				const uint32_t e = e0 + lane;
 				const bool live = e < total;
-				const uint32_t i = live ? lst[e] : 0u;  // block row
+				const uint32_t i = live ? my_list[e] : 0u;  // block row
 #pragma unroll
 				for (int k = 0; k < NA; k++) {
 					if (k < (int)a.n_aggs) {  // uniform
