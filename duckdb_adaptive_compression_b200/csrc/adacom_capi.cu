@@ -1223,6 +1223,17 @@ static adacom_status run_agg(adacom_column *col, uint64_t b, uint64_t e, int fla
 		LAUNCH(ctx, launch_scan_sum_fields(f, ctx->sm_count, ctx->stream));
 		return ADACOM_OK;
 	}
+	if (mode == kModeFilter && !getenv("ADACOM_FILTER_LEGACY")) {
+		// warp-per-tile filter: field domain (pred32) for re-packed payloads <= 32 bits on a frame of reference that cannot
+		// wrap, per value otherwise -- decided per segment on the device
+		LAUNCH(ctx, launch_filter_words(col->t, col->d_desc, col->d_tiles + col->tile_first[b],
+		                                col->tile_first[e] - col->tile_first[b], col->raw, (flags & ADACOM_LITERAL) ? 1 : 0,
+		                                op_mask, constant, bitmap32, col->h_desc[b].row_start, device_out,
+		                                (col->mirror_dirty || !col->wmax) ? std::min<uint32_t>(8u * (uint32_t)col->t.size, 32u)
+		                                                                  : std::min<uint32_t>(col->wmax, 32u),
+		                                ctx->sm_count, ctx->stream));
+		return ADACOM_OK;
+	}
 	if (mode == kModeFilter) {
 		// field-domain filter kernel when every re-packed payload of the range is <= 32 bits wide (always true for the
 		// 1/2/4-byte types; for the 8-byte types the host mirror decides, raw 8-byte segments stay on decode_kernel)

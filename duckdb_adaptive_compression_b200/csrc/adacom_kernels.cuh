@@ -221,6 +221,12 @@ cudaError_t launch_codec_fetch(TypeInfo t, int codec, const CodecArgs &args, con
                                const uint32_t *row_in_seg, uint64_t n, cudaStream_t stream);
 cudaError_t launch_rle_run_starts(const CodecArgs &args, uint32_t seg_b, uint32_t n_segs, int sm_count, cudaStream_t stream);
 
+// the same operator, warp per 2048-value tile (static tile table), lane per 32-row group (pred32); handles every kind of
+// segment (field-comparable ones in the field domain, the others per value); wmax: widest live payload of the column
+cudaError_t launch_filter_words(TypeInfo t, const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw,
+                                int literal, uint32_t op_mask, uint64_t constant, uint32_t *bitmap32, uint64_t out_row0,
+                                Agg *agg, uint32_t wmax, int sm_count, cudaStream_t stream);
+
 // ---- checkpoint image (kernels_checkpoint.cu) ----
 constexpr uint32_t kBlockAllocSize = 262144;  // Storage::BLOCK_ALLOC_SIZE: 8-byte checksum + Storage::BLOCK_SIZE payload
 

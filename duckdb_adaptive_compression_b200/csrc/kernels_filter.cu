@@ -15,6 +15,7 @@
 // in shared memory with 16-byte loads; 128 threads, 32 values each, lane = consecutive rows so that a ballot is 32
 // consecutive selection bits.  Algorithmic bytes: the packed payload (+ 1 bit per row for the bitmap).
 #include "adacom_kernels.cuh"
+#include "adacom_pred32.cuh"
 
 namespace adacom {
 
@@ -234,6 +235,252 @@ __global__ void __launch_bounds__(kFiltThreads, 8) filter_fields_kernel(const Se
 	block_reduce_agg(acc.lo64(), acc.hi64(), (uint64_t)n_pass, red, agg);
 }
 
+// =====================================================================================================================
+// filter_words_kernel -- the same operator with a LANE per 32-row group (pred32: compile-time field positions, five
+// integer instructions per value instead of thirteen) and a warp per 2048-value tile: no CTA barrier, the tile is staged
+// with cp.async into the warp's own window, the selection words leave as whole 32-bit stores (only the two words a tile
+// shares with its neighbours are atomics).  Segments that are not field-comparable (frames that wrap inside T, payloads
+// wider than 32 bits, slot-width segments) take a lane = row path in the same kernel, straight from global memory.
+// =====================================================================================================================
+constexpr int kFWarps = 8;
+constexpr uint32_t kFRows = 2048;
+constexpr uint32_t kFRun = 4;
+
+__device__ __forceinline__ void f_cp_async16(void *smem_dst, const void *gmem_src) {
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr(smem_dst)), "l"(gmem_src) : "memory");
+}
+
+template <int S, bool SIGNED>
+__global__ void __launch_bounds__(kFWarps * 32, 3) filter_words_kernel(const SegDesc *desc, const Job *tiles, uint32_t n_tiles,
+                                                                       const uint8_t *raw, int literal, uint32_t op_mask,
+                                                                       uint64_t constant, uint32_t *bitmap32, uint64_t out_row0,
+                                                                       Agg *agg, uint32_t window_bytes) {
+	using T = typename UIntOf<S>::type;
+	extern __shared__ __align__(128) uint8_t f_mem[];
+	__shared__ uint64_t red[96];
+	const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+	uint32_t *window = (uint32_t *)(f_mem + (size_t)warp * window_bytes);
+	Acc96 acc;
+	uint32_t n_pass = 0;
+	// per-segment state (warp-uniform), recomputed when the tile belongs to another segment
+	uint32_t c_seg = ~0u, c_w = 0, c_count = 0, c_flo = 0, c_span = 0;
+	uint64_t c_row_start = 0, c_packed = 0, c_min_add = 0, c_emin = 0;
+	int c_kind = 0;  // 0 nothing passes, 1 field range, 2 complement of one field value (<>), 3 per-value path
+	bool c_repacked = false;
+
+	const uint32_t total_warps = gridDim.x * kFWarps, wg = blockIdx.x * kFWarps + warp;
+	for (uint32_t run = wg; run * kFRun < n_tiles; run += total_warps) {
+		for (uint32_t t = run * kFRun; t < min(n_tiles, (run + 1u) * kFRun); t++) {
+			const Job job = tiles[t];
+			if (job.seg != c_seg) {
+				const DescQ dq = load_desc(desc + job.seg);
+				c_seg = job.seg;
+				c_count = dq.count();
+				c_row_start = dq.row_start();
+				c_repacked = dq.state() & kSegRepacked;
+				c_w = c_repacked ? dq.width() : 8u * S;
+				c_packed = dq.packed_ptr();
+				const uint64_t mn = dq.min_factor();
+				c_min_add = (mn != ~0ull && (c_repacked || literal)) ? mn : 0ull;
+				const uint64_t mask64 = lo_set64(c_w);
+				c_emin = extend_low<S, SIGNED>(c_min_add);
+				const uint64_t top = c_min_add + mask64;
+				const uint64_t e_top = extend_low<S, SIGNED>(top);
+				const bool linear = c_repacked && c_w <= 32u && top >= c_min_add && e_top - c_emin == mask64 &&
+				                    (SIGNED ? (int64_t)c_emin <= (int64_t)e_top : c_emin <= e_top);
+				c_kind = 3;
+				if (linear) {
+					const bool below = SIGNED ? (int64_t)constant < (int64_t)c_emin : constant < c_emin;
+					const bool above = SIGNED ? (int64_t)constant > (int64_t)e_top : constant > e_top;
+					const bool p_lt = op_mask & 1u, p_gt = (op_mask >> 2) & 1u;
+					const uint32_t mask32 = (uint32_t)mask64, fc = (uint32_t)(constant - c_emin);
+					c_kind = 1;
+					c_flo = 0;
+					c_span = mask32;
+					if (below || above) {
+						// a constant below the interval: every value is greater; above: every value is smaller
+						c_kind = (below ? p_gt : p_lt) ? 1 : 0;
+					} else {
+						switch (op_mask & 7u) {
+						case 1u: c_kind = fc == 0u ? 0 : 1; c_span = fc - 1u; break;                              // <
+						case 3u: c_span = fc; break;                                                           // <=
+						case 4u: c_kind = fc == mask32 ? 0 : 1; c_flo = fc + 1u; c_span = mask32 - c_flo; break;   // >
+						case 6u: c_flo = fc; c_span = mask32 - fc; break;                                      // >=
+						case 2u: c_flo = fc; c_span = 0u; break;                                               // =
+						case 5u: c_kind = 2; c_flo = fc; c_span = 0u; break;                                   // <>
+						case 0u: c_kind = 0; break;
+						default: break;                                                                        // everything passes
+						}
+					}
+				}
+			}
+			const uint32_t first = job.k * kFRows;
+			if (first >= c_count || c_kind == 0) {
+				continue;  // warp-uniform; the bitmap was zeroed by the caller
+			}
+			const uint32_t cnt = min(kFRows, c_count - first);
+			const uint64_t row0 = c_row_start + first;
+			uint32_t sel[2] = {0u, 0u};
+			if (c_kind != 3) {
+				const uint32_t w = c_w;
+				const uint8_t *src = (const uint8_t *)(c_packed + (uint64_t)(first / 64u) * w * 8u);
+				const uint32_t nbytes = ((cnt * w + 127u) >> 7) * 16u;
+				__syncwarp();  // the previous tile has been consumed
+				for (uint32_t off = lane * 16u; off < nbytes; off += 512u) {
+					f_cp_async16((uint8_t *)window + off, src + off);
+				}
+				asm volatile("cp.async.wait_all;" ::: "memory");
+				if (lane == 0) {
+					window[nbytes >> 2] = 0u;  // the funnel's word behind the last field
+				}
+				__syncwarp();
+				const uint32_t full_groups = cnt >> 5;
+				uint64_t fsum = 0;
+				uint32_t n = 0;
+#pragma unroll 1
+				for (int j = 0; j < 2; j++) {
+					const uint32_t g = lane + 32u * j;
+					if (g < full_groups) {
+						uint32_t word;
+						if (c_kind == 1) {
+							word = pred32_sum_any(w, window + g * w, 0u, c_flo, c_span, fsum);
+						} else {
+							// value <> c: everything but the fields equal to fc; their sum is count_eq * fc
+							const uint32_t eq = pred32_any(w, window + g * w, 0u, c_flo, 0u);
+							uint64_t all = 0;
+							pred32_sum_any(w, window + g * w, 0u, 0u, 0xffffffffu, all);
+							word = ~eq;
+							fsum += all - (uint64_t)__popc(eq) * c_flo;
+						}
+						n += __popc(word);
+						sel[0] = j == 0 ? word : sel[0];
+						sel[1] = j == 1 ? word : sel[1];
+					}
+				}
+				if (cnt & 31u) {  // ragged tail group: lane = row
+					const uint32_t i = full_groups * 32u + lane;
+					const bool inside = i < cnt;
+					const uint32_t mask32 = w >= 32u ? 0xffffffffu : ((1u << w) - 1u);
+					const uint32_t f = read_bits32(window, (inside ? i : 0u) * w) & mask32;
+					const bool pass = inside && (((f - c_flo) <= c_span) != (c_kind == 2));
+					const uint32_t word = __ballot_sync(0xffffffffu, pass);
+					fsum += pass ? (uint64_t)f : 0ull;
+					n += pass ? 1u : 0u;
+					if (lane == (full_groups & 31u)) {
+						sel[full_groups >> 5] = word;
+					}
+				}
+				// + fsum + n * extend(min) as a 96-bit two's-complement number
+				const uint64_t plo = c_emin * (uint64_t)n;
+				uint64_t phi = __umul64hi(c_emin, (uint64_t)n);
+				if (SIGNED && (int64_t)c_emin < 0) {
+					phi -= (uint64_t)n;
+				}
+				uint64_t lo = plo, hi = phi;
+				add128(lo, hi, fsum, 0ull);
+				acc.add96(lo, (uint32_t)hi);
+				n_pass += n;
+			} else {
+				// per-value path: raw slots, frames that wrap inside T, payloads wider than 32 bits
+				const uint32_t w = c_w;
+				const uint64_t *words = (const uint64_t *)c_packed;
+				const T *slots = (const T *)raw + row0;
+				const uint64_t mask64 = lo_set64(w);
+				for (uint32_t gg = 0; gg * 32u < cnt; gg++) {
+					const uint32_t i = gg * 32u + lane;
+					bool pass = false;
+					uint64_t v = 0;
+					if (i < cnt) {
+						uint64_t f;
+						if (c_repacked) {
+							const uint64_t bit = (uint64_t)(first + i) * w;
+							const uint32_t off = (uint32_t)(bit & 63u);
+							f = __ldg(words + (bit >> 6)) >> off;
+							if (off + w > 64u) {
+								f |= __ldg(words + (bit >> 6) + 1) << (64u - off);
+							}
+							f &= mask64;
+						} else {
+							f = (uint64_t)__ldg(slots + i);
+						}
+						v = extend_low<S, SIGNED>(f + c_min_add);
+						pass = cmp_passes<SIGNED>(v, constant, op_mask);
+					}
+					if (pass) {
+						acc.add<SIGNED>(v);
+						n_pass++;
+					}
+					const uint32_t word = __ballot_sync(0xffffffffu, pass);
+					if (lane == (gg & 31u)) {
+						sel[gg >> 5] = word;
+					}
+				}
+			}
+			if (bitmap32 != nullptr) {
+				// selection words S[g] (g = lane + 32 j) -> output words O[t] = S[t] << sh | S[t - 1] >> (32 - sh); the first
+				// and the last word of the tile are shared with its neighbours (atomics), the others are whole stores
+				const uint64_t rel0 = row0 - out_row0;
+				const uint32_t sh = (uint32_t)(rel0 & 31u);
+				uint32_t *dst = bitmap32 + (rel0 >> 5);
+				const uint32_t n_words = (sh + cnt + 31u) >> 5;
+				uint32_t prev0 = __shfl_up_sync(0xffffffffu, sel[0], 1);
+				uint32_t prev1 = __shfl_up_sync(0xffffffffu, sel[1], 1);
+				const uint32_t last0 = __shfl_sync(0xffffffffu, sel[0], 31);
+				const uint32_t last1 = __shfl_sync(0xffffffffu, sel[1], 31);
+				if (lane == 0) {
+					prev0 = 0u;
+					prev1 = last0;
+				}
+#pragma unroll
+				for (int j = 0; j < 3; j++) {
+					const uint32_t tw = lane + 32u * j;  // output word
+					if (j == 2 && lane != 0) {
+						break;
+					}
+					const uint32_t cur = j == 0 ? sel[0] : (j == 1 ? sel[1] : 0u);
+					const uint32_t prv = j == 0 ? prev0 : (j == 1 ? prev1 : last1);
+					const uint32_t o = sh ? ((cur << sh) | (prv >> (32u - sh))) : cur;
+					if (tw < n_words && o) {
+						if (tw == 0 || tw == n_words - 1u) {
+							atomicOr(dst + tw, o);
+						} else {
+							dst[tw] = o;
+						}
+					}
+				}
+			}
+		}
+	}
+	block_reduce_agg(acc.lo64(), acc.hi64(), (uint64_t)n_pass, red, agg);
+}
+
+template <int S>
+cudaError_t launch_w(bool is_signed, const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw, int literal,
+                     uint32_t op_mask, uint64_t constant, uint32_t *bitmap32, uint64_t out_row0, Agg *agg, uint32_t wmax,
+                     int sm_count, cudaStream_t stream) {
+	const uint32_t window = (256u * (wmax < 32u ? wmax : 32u) + 16u + 127u) & ~127u;
+	const size_t smem = (size_t)kFWarps * window;
+	void (*kernel)(const SegDesc *, const Job *, uint32_t, const uint8_t *, int, uint32_t, uint64_t, uint32_t *, uint64_t, Agg *,
+	               uint32_t) = is_signed ? filter_words_kernel<S, true> : filter_words_kernel<S, false>;
+	cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+	if (e != cudaSuccess) {
+		return e;
+	}
+	int per_sm = 0;
+	e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kFWarps * 32, smem);
+	if (e != cudaSuccess) {
+		return e;
+	}
+	uint64_t grid = (uint64_t)sm_count * (uint64_t)(per_sm > 0 ? per_sm : 1);
+	const uint64_t need = ((n_tiles + kFRun - 1) / kFRun + kFWarps - 1) / kFWarps;
+	if (grid > need) {
+		grid = need;
+	}
+	kernel<<<(uint32_t)grid, kFWarps * 32, smem, stream>>>(desc, tiles, n_tiles, raw, literal, op_mask, constant, bitmap32, out_row0,
+	                                                       agg, window);
+	return cudaGetLastError();
+}
+
 template <int S>
 cudaError_t launch_s(bool is_signed, const SegDesc *desc, uint32_t seg_b, uint32_t n_segs, uint32_t cps, const uint8_t *raw,
                      int literal, uint32_t op_mask, uint64_t constant, uint32_t *bitmap32, uint64_t out_row0, Agg *agg,
@@ -259,6 +506,21 @@ cudaError_t launch_s(bool is_signed, const SegDesc *desc, uint32_t seg_b, uint32
 }
 
 }  // namespace
+
+cudaError_t launch_filter_words(TypeInfo t, const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw,
+                                int literal, uint32_t op_mask, uint64_t constant, uint32_t *bitmap32, uint64_t out_row0,
+                                Agg *agg, uint32_t wmax, int sm_count, cudaStream_t stream) {
+	if (n_tiles == 0) {
+		return cudaSuccess;
+	}
+	switch (t.size) {
+	case 1: return launch_w<1>(t.is_signed, desc, tiles, n_tiles, raw, literal, op_mask, constant, bitmap32, out_row0, agg, wmax, sm_count, stream);
+	case 2: return launch_w<2>(t.is_signed, desc, tiles, n_tiles, raw, literal, op_mask, constant, bitmap32, out_row0, agg, wmax, sm_count, stream);
+	case 4: return launch_w<4>(t.is_signed, desc, tiles, n_tiles, raw, literal, op_mask, constant, bitmap32, out_row0, agg, wmax, sm_count, stream);
+	case 8: return launch_w<8>(t.is_signed, desc, tiles, n_tiles, raw, literal, op_mask, constant, bitmap32, out_row0, agg, wmax, sm_count, stream);
+	default: return cudaErrorInvalidValue;
+	}
+}
 
 cudaError_t launch_filter_fields(TypeInfo t, const SegDesc *desc, uint32_t seg_b, uint32_t n_segs, uint32_t seg_capacity,
                                  const uint8_t *raw, int literal, uint32_t op_mask, uint64_t constant, uint32_t *bitmap32,
