@@ -1223,7 +1223,20 @@ static adacom_status run_agg(adacom_column *col, uint64_t b, uint64_t e, int fla
 		LAUNCH(ctx, launch_scan_sum_fields(f, ctx->sm_count, ctx->stream));
 		return ADACOM_OK;
 	}
-	if (mode == kModeFilter && !getenv("ADACOM_FILTER_LEGACY")) {
+	bool words_kernel = mode == kModeFilter && !getenv("ADACOM_FILTER_LEGACY");
+	if (words_kernel && col->t.size == 8) {
+		// 8-byte types: payloads wider than 32 bits and slot-width segments are not field-comparable in 32 bits; a range
+		// that holds any of them stays on the TMA-staged per-value kernel (decode_kernel<filter>)
+		adacom_status st = sync_mirror(col);
+		if (st != ADACOM_OK) {
+			return st;
+		}
+		for (uint64_t g = b; g < e && words_kernel; g++) {
+			const SegDesc &d = col->h_desc[g];
+			words_kernel = d.count == 0 || ((d.state & kSegRepacked) && d.width <= 32);
+		}
+	}
+	if (words_kernel) {
 		// warp-per-tile filter: field domain (pred32) for re-packed payloads <= 32 bits on a frame of reference that cannot
 		// wrap, per value otherwise -- decided per segment on the device
 		LAUNCH(ctx, launch_filter_words(col->t, col->d_desc, col->d_tiles + col->tile_first[b],
@@ -1234,8 +1247,8 @@ static adacom_status run_agg(adacom_column *col, uint64_t b, uint64_t e, int fla
 		                                ctx->sm_count, ctx->stream));
 		return ADACOM_OK;
 	}
-	if (mode == kModeFilter) {
-		// field-domain filter kernel when every re-packed payload of the range is <= 32 bits wide (always true for the
+	if (mode == kModeFilter && getenv("ADACOM_FILTER_LEGACY")) {
+		// (previous generation, kept for A/B runs) field-domain filter kernel when every re-packed payload of the range is <= 32 bits wide (always true for the
 		// 1/2/4-byte types; for the 8-byte types the host mirror decides, raw 8-byte segments stay on decode_kernel)
 		bool narrow = col->t.size <= 4;
 		if (!narrow) {

@@ -27,12 +27,17 @@ __device__ __forceinline__ uint32_t pred32(const uint32_t *p, uint32_t s0, uint3
 	constexpr int PW = W / G;     // words per iteration
 	constexpr uint32_t mask = W >= 32 ? 0xffffffffu : ((1u << (W & 31)) - 1u);
 	uint32_t word = 0;
+	// lanes start at different periods of their group and wrap around: for the widths that share factors with the 32
+	// banks (8, 16, 32 ...) the lanes of a warp would otherwise hit the same bank (W = 32: a 32-way conflict)
+	const uint32_t rot = threadIdx.x & (G - 1);
 #pragma unroll 1
-	for (int it = 0; it < G; it++, p += PW) {
+	for (int step = 0; step < G; step++) {
+		const uint32_t it = (step + rot) & (G - 1);
+		const uint32_t *q = p + it * PW;
 		uint32_t r[PW + 1];
 #pragma unroll
 		for (int t = 0; t <= PW; t++) {
-			r[t] = p[t];
+			r[t] = q[t];
 		}
 #pragma unroll
 		for (int t = 0; t < PW; t++) {
@@ -80,12 +85,15 @@ __device__ __forceinline__ uint32_t pred32_sum(const uint32_t *p, uint32_t s0, u
 	constexpr int PW = W / G;
 	constexpr uint32_t mask = W >= 32 ? 0xffffffffu : ((1u << (W & 31)) - 1u);
 	uint32_t word = 0;
+	const uint32_t rot = threadIdx.x & (G - 1);  // see pred32
 #pragma unroll 1
-	for (int it = 0; it < G; it++, p += PW) {
+	for (int step = 0; step < G; step++) {
+		const uint32_t it = (step + rot) & (G - 1);
+		const uint32_t *q = p + it * PW;
 		uint32_t r[PW + 1];
 #pragma unroll
 		for (int t = 0; t <= PW; t++) {
-			r[t] = p[t];
+			r[t] = q[t];
 		}
 #pragma unroll
 		for (int t = 0; t < PW; t++) {

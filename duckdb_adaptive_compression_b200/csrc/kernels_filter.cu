@@ -334,9 +334,24 @@ __global__ void __launch_bounds__(kFWarps * 32, 3) filter_words_kernel(const Seg
 					window[nbytes >> 2] = 0u;  // the funnel's word behind the last field
 				}
 				__syncwarp();
-				const uint32_t full_groups = cnt >> 5;
+				uint32_t full_groups = cnt >> 5;
 				uint64_t fsum = 0;
 				uint32_t n = 0;
+				if (w == 32u) {
+					// whole-word fields: lane = row is as cheap as pred32 and free of the 32-way bank conflict a lane per
+					// group would have at this width
+					for (uint32_t gg = 0; gg < full_groups; gg++) {
+						const uint32_t f = window[gg * 32u + lane];
+						const bool pass = ((f - c_flo) <= c_span) != (c_kind == 2);
+						const uint32_t word = __ballot_sync(0xffffffffu, pass);
+						fsum += pass ? (uint64_t)f : 0ull;
+						n += pass ? 1u : 0u;
+						if (lane == (gg & 31u)) {
+							sel[gg >> 5] = word;
+						}
+					}
+					full_groups = 0;  // (the loop below has nothing left; the ragged tail uses cnt)
+				}
 #pragma unroll 1
 				for (int j = 0; j < 2; j++) {
 					const uint32_t g = lane + 32u * j;
@@ -358,6 +373,7 @@ __global__ void __launch_bounds__(kFWarps * 32, 3) filter_words_kernel(const Seg
 					}
 				}
 				if (cnt & 31u) {  // ragged tail group: lane = row
+					full_groups = cnt >> 5;
 					const uint32_t i = full_groups * 32u + lane;
 					const bool inside = i < cnt;
 					const uint32_t mask32 = w >= 32u ? 0xffffffffu : ((1u << w) - 1u);
