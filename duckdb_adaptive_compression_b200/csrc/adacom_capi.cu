@@ -45,6 +45,11 @@ struct adacom_ctx {
 	Agg *h_aggs = nullptr;                // pinned
 	Agg *h_agg = nullptr;                 // pinned
 	unsigned long long *h_totals = nullptr;  // pinned
+	// uniform ranges of the last grouped scan (scan_columns_dense_kernel): rebuilt when the columns / epochs / rows change
+	std::vector<uint64_t> dense_key;
+	DenseRange *d_dense_ranges = nullptr;
+	uint32_t dense_n_ranges = 0, dense_blocks = 0;
+	size_t dense_capacity = 0;
 	// staging pair of the batched look-ups (pinned host + device, grown on demand): one H2D, one kernel, one D2H
 	uint8_t *h_stage = nullptr, *d_stage = nullptr;
 	size_t stage_bytes = 0;
@@ -387,6 +392,9 @@ extern "C" void adacom_ctx_destroy(adacom_ctx *ctx) {
 	cudaFree(ctx->flush_buf);
 	cudaFree(ctx->d_agg);
 	cudaFree(ctx->d_layout_scratch);
+	if (ctx->d_dense_ranges) {
+		cudaFree(ctx->d_dense_ranges);
+	}
 	cudaFree(ctx->d_aggs);
 	cudaFreeHost(ctx->h_aggs);
 	cudaFreeHost(ctx->h_agg);
@@ -1716,6 +1724,95 @@ static adacom_status plan_scan_columns(adacom_ctx *ctx, const adacom_scan_term *
 				return fail(ctx, ADACOM_ERR_UNSUPPORTED,
 				            "adacom_scan_columns: a row block spans more than 3 segments of one column");
 			}
+		}
+	}
+	// grouped scans over field-comparable columns run warp-per-block on "uniform ranges" (scan_columns_dense_kernel): the
+	// rows are cut at every segment boundary of every column, so a block sees exactly one segment per column
+	q.dense_ranges = nullptr;
+	if (n_groups && q.narrow_products && !getenv("ADACOM_QUERY_PIPELINED") &&
+	    max_prod * ((long double)n_rows / 32.0L + 1.0L) < ldexpl(1.0L, 62)) {
+		auto host_extend = [](uint64_t x, int size, bool sg) -> uint64_t {
+			const unsigned shift = 64u - 8u * (unsigned)size;
+			return sg ? (uint64_t)(((int64_t)(x << shift)) >> shift) : ((x << shift) >> shift);
+		};
+		bool ok = true;
+		uint64_t win = 0;
+		std::vector<uint64_t> cuts;
+		cuts.push_back(row_begin);
+		cuts.push_back(row_end);
+		for (uint32_t c = 0; c < n_terms && ok; c++) {
+			const adacom_column *col = terms[c].col;
+			uint32_t wmax = 1;
+			for (uint64_t g = 0; g < col->n_segs && ok; g++) {
+				const SegDesc &d = col->h_desc[g];
+				if (d.count == 0 || d.row_start + d.count <= row_begin || d.row_start >= row_end) {
+					continue;
+				}
+				const uint64_t mn = d.min_factor != ~0ull ? d.min_factor : 0ull;
+				const uint64_t range = d.width < 64 ? (1ull << d.width) - 1 : ~0ull, top = mn + range;
+				const uint64_t e_lo = host_extend(mn, col->t.size, col->t.is_signed), e_hi = host_extend(top, col->t.size, col->t.is_signed);
+				ok = (d.state & kSegRepacked) && d.width <= 32 && top >= mn && e_hi - e_lo == range &&
+				     (col->t.is_signed ? (int64_t)e_lo <= (int64_t)e_hi : e_lo <= e_hi);
+				wmax = std::max<uint32_t>(wmax, d.width);
+				if (d.row_start > row_begin) {
+					cuts.push_back(d.row_start);
+				}
+			}
+			win += (uint64_t)kDenseBlockRows * wmax / 8 + 48;
+		}
+		win = (win + 127) & ~127ull;
+		const uint64_t smem = 4 * win + (uint64_t)kQueryMaxCols * kDenseThreads * 8 + (uint64_t)n_groups * n_sums * kDenseThreads * 8 +
+		                      (uint64_t)n_groups * kDenseThreads * 4;
+		if (ok && smem <= 100u * 1024u) {
+			std::vector<uint64_t> key = {row_begin, row_end, n_terms};
+			for (uint32_t c = 0; c < n_terms; c++) {
+				key.push_back((uint64_t)(uintptr_t)terms[c].col);
+				key.push_back(terms[c].col->epoch);
+			}
+			if (key != ctx->dense_key) {
+				std::sort(cuts.begin(), cuts.end());
+				cuts.erase(std::unique(cuts.begin(), cuts.end()), cuts.end());
+				std::vector<DenseRange> ranges;
+				std::vector<uint64_t> cursor(n_terms, 0);
+				uint32_t blocks = 0;
+				for (size_t i = 0; i + 1 < cuts.size(); i++) {
+					DenseRange r;
+					memset(&r, 0, sizeof(r));
+					r.row_begin = cuts[i];
+					r.rows = (uint32_t)(cuts[i + 1] - cuts[i]);
+					r.first_block = blocks;
+					for (uint32_t c = 0; c < n_terms; c++) {
+						const adacom_column *col = terms[c].col;
+						uint64_t &g = cursor[c];
+						if (g == 0) {
+							g = col->vec_seg[cuts[i] / kVectorSize];
+						}
+						while (g + 1 < col->n_segs && cuts[i] >= col->h_desc[g].row_start + col->h_desc[g].count) {
+							g++;
+						}
+						r.seg[c] = (uint32_t)g;
+					}
+					blocks += (r.rows + kDenseBlockRows - 1) / kDenseBlockRows;
+					ranges.push_back(r);
+				}
+				if (ranges.size() > ctx->dense_capacity) {
+					if (ctx->d_dense_ranges) {
+						CK(ctx, cudaFreeAsync(ctx->d_dense_ranges, ctx->stream));
+					}
+					ctx->dense_capacity = ranges.size() * 2;
+					CK(ctx, cudaMallocAsync((void **)&ctx->d_dense_ranges, ctx->dense_capacity * sizeof(DenseRange), ctx->stream));
+				}
+				CK(ctx, cudaMemcpyAsync(ctx->d_dense_ranges, ranges.data(), ranges.size() * sizeof(DenseRange), cudaMemcpyHostToDevice,
+				                        ctx->stream));
+				CK(ctx, cudaStreamSynchronize(ctx->stream));  // `ranges` is a stack vector
+				ctx->dense_n_ranges = (uint32_t)ranges.size();
+				ctx->dense_blocks = blocks;
+				ctx->dense_key = key;
+			}
+			q.dense_ranges = ctx->d_dense_ranges;
+			q.dense_n_ranges = ctx->dense_n_ranges;
+			q.dense_blocks = ctx->dense_blocks;
+			q.dense_window = (uint32_t)win;
 		}
 	}
 	// ungrouped scans run warp-per-block (scan_columns_sparse_kernel): a warp stages the predicate columns of 2048 rows

@@ -86,6 +86,16 @@ struct QueryAgg {  // sum over the selected rows of prod_k (add[k] + mul[k] * va
 	int64_t mul[kQueryMaxFactors] = {0, 0, 0};
 };
 
+// a run of table rows inside which every referenced column is ONE segment (scan_columns_dense_kernel)
+struct DenseRange {
+	uint64_t row_begin;
+	uint32_t rows;
+	uint32_t first_block;            // index of the range's first 1024-row block
+	uint32_t seg[kQueryMaxCols];     // segment of every column
+};
+constexpr uint32_t kDenseBlockRows = 1024;
+constexpr uint32_t kDenseThreads = 128;
+
 struct QueryArgs {
 	QueryCol cols[kQueryMaxCols];
 	QueryAgg aggs[kQueryMaxAggs];
@@ -101,6 +111,9 @@ struct QueryArgs {
 	uint32_t n_groups = 0;                // 0: no grouping; rows whose key is outside the range are dropped
 	uint32_t dense_groups = 0;            // grouped launches: per-thread int64 accumulators in shared memory are safe
 	                                      // (every partial sum provably fits) -> dense selections skip the lists
+	const DenseRange *dense_ranges = nullptr;  // grouped launches on field-comparable columns: the uniform ranges (device)
+	uint32_t dense_n_ranges = 0, dense_blocks = 0;
+	uint32_t dense_window = 0;            // bytes of shared memory a warp needs for all the columns of 1024 rows
 	uint32_t sparse_window = 0;           // ungrouped launches: bytes of shared memory a warp needs for the predicate
 	                                      // columns of 1024 rows (0: use the pipelined kernel)
 	const uint32_t *in_bitmap = nullptr;  // optional selection (bit r - row_begin), AND-ed

@@ -1280,6 +1280,215 @@ __global__ void __launch_bounds__(kSWarps * 32, 4) scan_columns_sparse_kernel(co
 	}
 }
 
+
+// =====================================================================================================================
+// scan_columns_dense_kernel -- GROUP BY a small-domain column with most rows selected (TPC-H Q1 shape), warp per block.
+// The host cuts the table rows at every segment boundary of every referenced column ("uniform ranges": inside one, each
+// column is ONE segment), so a block of <= 1024 rows of a range has exactly one piece per column -- no piece search, no
+// boundary groups.  Per block: lane c resolves column c (cached per segment), all columns are staged with cp.async,
+// predicates run lane = group (pred32), then the 32-row groups are walked lane = row: every needed column is decoded
+// ONCE into the thread's slice of shared memory (value = extend(min) + field on a linear frame of reference), the sum
+// expressions read their factors from there, and every aggregate is one read-modify-write of the thread's own int64
+// accumulator of the row's group.  The planner guarantees (from the analyzed min / max) that every product and every
+// per-thread partial sum fits int64; the 128-bit fold happens once at the end.
+// =====================================================================================================================
+constexpr int kDWarps = 4;
+constexpr int kDThreads = kDWarps * 32;
+constexpr uint32_t kDRows = 1024;
+
+template <int NA>
+__global__ void __launch_bounds__(kDThreads, 4) scan_columns_dense_kernel(const QueryArgs a, const DenseRange *ranges,
+                                                                          uint32_t n_ranges, uint32_t n_blocks,
+                                                                          uint32_t window_bytes) {
+	extern __shared__ __align__(128) uint8_t d_mem[];
+	__shared__ uint64_t red[96];
+	const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+	// dynamic shared memory: windows | per-thread values [col][thread] | accumulators [group][agg][thread] | counts
+	uint8_t *window = d_mem + (size_t)warp * window_bytes;
+	long long *vals = (long long *)(d_mem + (size_t)kDWarps * window_bytes);
+	long long *dacc = vals + (size_t)kQueryMaxCols * kDThreads;
+	uint32_t *dcnt = (uint32_t *)(dacc + (size_t)a.n_groups * a.n_aggs * kDThreads);
+	for (uint32_t i = tid; i < a.n_groups * a.n_aggs * kDThreads; i += kDThreads) {
+		dacc[i] = 0ll;
+	}
+	for (uint32_t i = tid; i < a.n_groups * kDThreads; i += kDThreads) {
+		dcnt[i] = 0u;
+	}
+	__syncthreads();
+	const bool active = lane < a.n_cols;
+	const QueryCol &mycol = a.cols[active ? lane : 0];
+	const uint32_t need_mask = a.factor_mask | (1u << a.group_col);
+	// per-lane segment cache (lane = column)
+	uint32_t c_seg = ~0u, c_w = 0;
+	uint64_t c_rs = 0, c_words = 0, c_vbase = 0, c_flo = ~0ull, c_span = 0;
+
+	const uint32_t total_warps = gridDim.x * kDWarps, wg = blockIdx.x * kDWarps + warp;
+	for (uint32_t run = wg; run * kSRun < n_blocks; run += total_warps) {
+		for (uint32_t b = run * kSRun; b < min(n_blocks, (run + 1u) * kSRun); b++) {
+			// range of block b: last range whose first_block <= b
+			uint32_t lo = 0, hi = n_ranges;
+			while (hi - lo > 1) {
+				const uint32_t mid = (lo + hi) >> 1;
+				if (__ldg(&ranges[mid].first_block) <= b) {
+					lo = mid;
+				} else {
+					hi = mid;
+				}
+			}
+			const DenseRange *rg = ranges + lo;
+			const uint32_t k = b - __ldg(&rg->first_block);
+			const uint64_t r0 = __ldg(&rg->row_begin) + (uint64_t)k * kDRows;
+			const uint32_t left = __ldg(&rg->rows) - k * kDRows;
+			const uint32_t rows = left < kDRows ? left : kDRows;
+			const uint32_t n_groups32 = (rows + 31u) >> 5;
+			// ---- my column's piece ----
+			uint32_t bit_base = 0, bytes = 0;
+			uint64_t src16 = 0;
+			if (active) {
+				const uint32_t sg = __ldg(&rg->seg[lane]);
+				if (sg != c_seg) {
+					const DescQ dq = load_desc(mycol.desc + sg);
+					c_seg = sg;
+					c_rs = dq.row_start();
+					c_w = dq.width();
+					c_words = dq.packed_ptr();
+					const uint64_t mn = dq.min_factor();
+					const uint64_t min_add = mn != ~0ull ? mn : 0ull;  // (every segment here is re-packed: host check)
+					c_vbase = extend_rt(min_add, mycol.type_size, mycol.is_signed);
+					c_flo = ~0ull;
+					c_span = 0;
+					if (mycol.has_pred) {
+						field_range(mycol, min_add, c_w, c_flo, c_span);
+					}
+				}
+				const uint64_t bit = (r0 - c_rs) * (uint64_t)c_w;
+				const uint64_t src = c_words + (bit >> 3);
+				src16 = src & ~15ull;
+				const uint32_t byte_base = (uint32_t)(src - src16);
+				bit_base = byte_base * 8u + (uint32_t)(bit & 7u);
+				bytes = (byte_base + (((uint32_t)(bit & 7u) + rows * c_w + 7u) >> 3) + 15u) & ~15u;
+			}
+			uint32_t incl = bytes;
+#pragma unroll
+			for (int d = 1; d < 32; d <<= 1) {
+				const uint32_t v = __shfl_up_sync(0xffffffffu, incl, d);
+				if ((int)lane >= d) {
+					incl += v;
+				}
+			}
+			const uint32_t smem_off = incl - bytes;
+			__syncwarp();  // the previous block's window has been consumed
+			for (uint32_t c = 0; c < a.n_cols; c++) {
+				const uint8_t *src = (const uint8_t *)__shfl_sync(0xffffffffu, src16, c);
+				const uint32_t nb = __shfl_sync(0xffffffffu, bytes, c);
+				uint8_t *dst = window + __shfl_sync(0xffffffffu, smem_off, c);
+				for (uint32_t off = lane * 16u; off < nb; off += 512u) {
+					cp_async16(dst + off, src + off);
+				}
+			}
+			uint32_t sel = 0;
+			if (lane < n_groups32) {
+				const uint32_t l = rows - lane * 32u;
+				sel = l >= 32u ? 0xffffffffu : ((1u << l) - 1u);
+			}
+			cp_async_wait_all();
+			__syncwarp();
+			// ---- predicates: lane = group ----
+#pragma unroll 1
+			for (uint32_t c = 0; c < a.n_cols; c++) {
+				if (!a.cols[c].has_pred) {
+					continue;
+				}
+				const uint32_t w = __shfl_sync(0xffffffffu, c_w, c);
+				const uint64_t flo = __shfl_sync(0xffffffffu, c_flo, c);
+				const uint64_t span = __shfl_sync(0xffffffffu, c_span, c);
+				const uint32_t bb = __shfl_sync(0xffffffffu, bit_base, c);
+				const uint32_t *words32 = (const uint32_t *)(window + __shfl_sync(0xffffffffu, smem_off, c));
+				if (flo == 0 && span == lo_set64(w)) {
+					continue;  // zone map
+				}
+				if (flo >> 32) {
+					sel = 0;  // empty intersection (flo = 2^64 - 1)
+					continue;
+				}
+				const uint32_t bit = bb + lane * 32u * w;
+				const uint32_t keep = pred32_any(w, words32 + (bit >> 5), bit & 31u, (uint32_t)flo, (uint32_t)span);
+				sel &= keep;
+			}
+			if (!__any_sync(0xffffffffu, sel != 0)) {
+				continue;
+			}
+			// ---- rows: lane = row, group by group ----
+#pragma unroll 1
+			for (uint32_t gg = 0; gg < n_groups32; gg++) {
+				const uint32_t word = __shfl_sync(0xffffffffu, sel, gg);
+				if (word == 0) {
+					continue;
+				}
+				const bool on = (word >> lane) & 1u;
+				const uint32_t i = gg * 32u + lane;
+#pragma unroll
+				for (int c = 0; c < kQueryMaxCols; c++) {
+					if ((need_mask >> c) & 1u) {  // uniform
+						const uint32_t w = __shfl_sync(0xffffffffu, c_w, c);
+						const uint32_t bb = __shfl_sync(0xffffffffu, bit_base, c);
+						const uint32_t so = __shfl_sync(0xffffffffu, smem_off, c);
+						const uint64_t vb = __shfl_sync(0xffffffffu, c_vbase, c);
+						const uint32_t f = read_bits32((const uint32_t *)(window + so), bb + i * w) & (0xffffffffu >> (32u - w));
+						vals[c * kDThreads + tid] = (long long)(vb + (uint64_t)f);
+					}
+				}
+				const uint64_t kv = (uint64_t)vals[a.group_col * kDThreads + tid];
+				if (on && kv < (uint64_t)a.n_groups) {
+					long long *slot = dacc + (size_t)kv * a.n_aggs * kDThreads + tid;
+#pragma unroll
+					for (int kk = 0; kk < NA; kk++) {
+						if (kk < (int)a.n_aggs) {  // uniform
+							const QueryAgg &qa = a.aggs[kk];
+							long long term = 1;
+#pragma unroll
+							for (int f = 0; f < kQueryMaxFactors; f++) {
+								if (f < (int)qa.n_factors) {
+									term *= qa.add[f] + qa.mul[f] * vals[qa.col[f] * kDThreads + tid];
+								}
+							}
+							slot[(size_t)kk * kDThreads] += term;
+						}
+					}
+					dcnt[(uint32_t)kv * kDThreads + tid] += 1u;
+				}
+			}
+		}
+	}
+	__syncthreads();
+	// fold the per-thread accumulators: one warp per (group, aggregate) slot at a time, one atomic triple each
+	for (uint32_t sidx = warp; sidx < a.n_groups * a.n_aggs; sidx += kDWarps) {
+		const uint32_t g = sidx / a.n_aggs, kk = sidx % a.n_aggs;
+		uint64_t lo = 0, hi = 0;
+		uint64_t cnt = 0;
+		for (uint32_t j = lane; j < (uint32_t)kDThreads; j += 32u) {
+			const long long v = dacc[(size_t)sidx * kDThreads + j];
+			add128(lo, hi, (uint64_t)v, v < 0 ? ~0ull : 0ull);
+			cnt += dcnt[g * kDThreads + j];
+		}
+#pragma unroll
+		for (int d = 16; d > 0; d >>= 1) {
+			const uint64_t olo = __shfl_down_sync(0xffffffffu, lo, d);
+			const uint64_t ohi = __shfl_down_sync(0xffffffffu, hi, d);
+			add128(lo, hi, olo, ohi);
+			cnt += __shfl_down_sync(0xffffffffu, cnt, d);
+		}
+		if (lane == 0 && (cnt | lo | hi)) {
+			Agg *out = a.out + g * a.n_aggs + kk;
+			const unsigned long long old = atomicAdd((unsigned long long *)&out->sum_lo, (unsigned long long)lo);
+			const unsigned long long carry = (old + lo < old) ? 1ull : 0ull;
+			atomicAdd((unsigned long long *)&out->sum_hi, (unsigned long long)(hi + carry));
+			atomicAdd((unsigned long long *)&out->count, (unsigned long long)cnt);
+		}
+	}
+	(void)red;
+}
+
 }  // namespace
 
 uint32_t scan_columns_group_smem(uint32_t n_groups, uint32_t n_aggs, uint32_t dense) {
@@ -1296,6 +1505,29 @@ cudaError_t launch_scan_columns(const QueryArgs &args, int sm_count, cudaStream_
 	}
 	int dev = 0;
 	cudaGetDevice(&dev);
+	if (args.n_groups && args.dense_ranges != nullptr && args.in_bitmap == nullptr && args.out_bitmap == nullptr) {
+		const size_t smem = (size_t)kDWarps * args.dense_window + (size_t)kQueryMaxCols * kDThreads * 8 +
+		                    (size_t)args.n_groups * args.n_aggs * kDThreads * 8 + (size_t)args.n_groups * kDThreads * 4;
+		void (*kernel)(const QueryArgs, const DenseRange *, uint32_t, uint32_t, uint32_t) =
+		    args.n_aggs <= 2 ? scan_columns_dense_kernel<2> : (args.n_aggs <= 4 ? scan_columns_dense_kernel<4> : scan_columns_dense_kernel<8>);
+		cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		if (e != cudaSuccess) {
+			return e;
+		}
+		int per_sm = 0;
+		e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kDThreads, smem);
+		if (e != cudaSuccess) {
+			return e;
+		}
+		uint64_t grid = (uint64_t)sm_count * (uint64_t)(per_sm > 0 ? per_sm : 1);
+		const uint64_t need = ((args.dense_blocks + kSRun - 1) / kSRun + kDWarps - 1) / kDWarps;
+		if (grid > need) {
+			grid = need;
+		}
+		kernel<<<(uint32_t)grid, kDThreads, smem, stream>>>(args, args.dense_ranges, args.dense_n_ranges, args.dense_blocks,
+		                                                     args.dense_window);
+		return cudaGetLastError();
+	}
 	if (args.n_groups == 0 && args.sparse_window) {
 		// ungrouped: the warp-per-block kernel; window = staged bytes of the predicate columns of 1024 rows
 		const size_t smem = (size_t)kSWarps * args.sparse_window;
