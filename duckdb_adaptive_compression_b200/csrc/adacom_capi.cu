@@ -1645,6 +1645,19 @@ static adacom_status plan_scan_columns(adacom_ctx *ctx, const adacom_scan_term *
 			narrow = prod < ldexpl(1.0L, 62);
 		}
 		q.narrow_products = narrow ? 1u : 0u;
+		// 32-bit mode of the dense kernel: every value and every factor fits int32
+		bool narrow32 = true;
+		for (uint32_t c = 0; c < n_terms; c++) {
+			narrow32 = narrow32 && bound[c] < ldexpl(1.0L, 31);
+		}
+		for (uint32_t g = 0; g < n_sums; g++) {
+			for (uint32_t k = 0; k < sums[g].n_factors; k++) {
+				narrow32 = narrow32 && fabsl((long double)sums[g].add[k]) +
+				                               fabsl((long double)sums[g].mul[k]) * bound[sums[g].term[k]] <
+				                           ldexpl(1.0L, 31);
+			}
+		}
+		q.narrow_values = narrow32 ? 1u : 0u;
 		max_prod = 0;
 		for (uint32_t g = 0; g < n_sums; g++) {
 			long double prod = 1;

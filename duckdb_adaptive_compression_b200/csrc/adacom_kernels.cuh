@@ -106,6 +106,7 @@ struct QueryArgs {
 	uint32_t stages = 2;
 	uint32_t stage_bytes = 0;             // multiple of 128: worst-case staged bytes of one row block
 	int literal = 0;
+	uint32_t narrow_values = 0;           // every value and every factor (add + mul * value) fits int32 (dense kernel)
 	uint32_t narrow_products = 0;         // every prod_k (add + mul * value) provably fits int64: 64-bit products
 	uint32_t group_col = 0;               // GROUP BY: column whose decoded value (0 .. n_groups-1) is the group key
 	uint32_t n_groups = 0;                // 0: no grouping; rows whose key is outside the range are dropped

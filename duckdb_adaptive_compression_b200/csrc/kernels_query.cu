@@ -1296,7 +1296,7 @@ constexpr int kDWarps = 4;
 constexpr int kDThreads = kDWarps * 32;
 constexpr uint32_t kDRows = 1024;
 
-template <int NA>
+template <int NA, bool N32>
 __global__ void __launch_bounds__(kDThreads, 4) scan_columns_dense_kernel(const QueryArgs a, const DenseRange *ranges,
                                                                           uint32_t n_ranges, uint32_t n_blocks,
                                                                           uint32_t window_bytes) {
@@ -1306,6 +1306,7 @@ __global__ void __launch_bounds__(kDThreads, 4) scan_columns_dense_kernel(const 
 	// dynamic shared memory: windows | per-thread values [col][thread] | accumulators [group][agg][thread] | counts
 	uint8_t *window = d_mem + (size_t)warp * window_bytes;
 	long long *vals = (long long *)(d_mem + (size_t)kDWarps * window_bytes);
+	int *vals32 = (int *)vals;  // N32: the same slice holds 32-bit values
 	long long *dacc = vals + (size_t)kQueryMaxCols * kDThreads;
 	uint32_t *dcnt = (uint32_t *)(dacc + (size_t)a.n_groups * a.n_aggs * kDThreads);
 	for (uint32_t i = tid; i < a.n_groups * a.n_aggs * kDThreads; i += kDThreads) {
@@ -1418,7 +1419,17 @@ __global__ void __launch_bounds__(kDThreads, 4) scan_columns_dense_kernel(const 
 			if (!__any_sync(0xffffffffu, sel != 0)) {
 				continue;
 			}
-			// ---- rows: lane = row, group by group ----
+			// ---- rows: lane = row, group by group; the per-column parameters of the block stay in registers ----
+			uint32_t pw[kQueryMaxCols], pbb[kQueryMaxCols];
+			const uint32_t *pwin[kQueryMaxCols];
+			uint64_t pvb[kQueryMaxCols];
+#pragma unroll
+			for (int c = 0; c < kQueryMaxCols; c++) {
+				pw[c] = __shfl_sync(0xffffffffu, c_w, c);
+				pbb[c] = __shfl_sync(0xffffffffu, bit_base, c);
+				pwin[c] = (const uint32_t *)(window + __shfl_sync(0xffffffffu, smem_off, c));
+				pvb[c] = __shfl_sync(0xffffffffu, c_vbase, c);
+			}
 #pragma unroll 1
 			for (uint32_t gg = 0; gg < n_groups32; gg++) {
 				const uint32_t word = __shfl_sync(0xffffffffu, sel, gg);
@@ -1430,15 +1441,16 @@ __global__ void __launch_bounds__(kDThreads, 4) scan_columns_dense_kernel(const 
 #pragma unroll
 				for (int c = 0; c < kQueryMaxCols; c++) {
 					if ((need_mask >> c) & 1u) {  // uniform
-						const uint32_t w = __shfl_sync(0xffffffffu, c_w, c);
-						const uint32_t bb = __shfl_sync(0xffffffffu, bit_base, c);
-						const uint32_t so = __shfl_sync(0xffffffffu, smem_off, c);
-						const uint64_t vb = __shfl_sync(0xffffffffu, c_vbase, c);
-						const uint32_t f = read_bits32((const uint32_t *)(window + so), bb + i * w) & (0xffffffffu >> (32u - w));
-						vals[c * kDThreads + tid] = (long long)(vb + (uint64_t)f);
+						const uint32_t f = read_bits32(pwin[c], pbb[c] + i * pw[c]) & (0xffffffffu >> (32u - pw[c]));
+						if (N32) {
+							vals32[c * kDThreads + tid] = (int)((uint32_t)pvb[c] + f);
+						} else {
+							vals[c * kDThreads + tid] = (long long)(pvb[c] + (uint64_t)f);
+						}
 					}
 				}
-				const uint64_t kv = (uint64_t)vals[a.group_col * kDThreads + tid];
+				const uint64_t kv = N32 ? (uint64_t)(long long)vals32[a.group_col * kDThreads + tid]
+				                        : (uint64_t)vals[a.group_col * kDThreads + tid];
 				if (on && kv < (uint64_t)a.n_groups) {
 					long long *slot = dacc + (size_t)kv * a.n_aggs * kDThreads + tid;
 #pragma unroll
@@ -1449,7 +1461,14 @@ __global__ void __launch_bounds__(kDThreads, 4) scan_columns_dense_kernel(const 
 #pragma unroll
 							for (int f = 0; f < kQueryMaxFactors; f++) {
 								if (f < (int)qa.n_factors) {
-									term *= qa.add[f] + qa.mul[f] * vals[qa.col[f] * kDThreads + tid];
+									if (N32) {
+										// every value and every factor fits int32 (planner: narrow_values): a 32-bit multiply-add per
+										// factor and one widening multiply per extra factor
+										const int x = (int)qa.add[f] + (int)qa.mul[f] * vals32[qa.col[f] * kDThreads + tid];
+										term *= (long long)x;
+									} else {
+										term *= qa.add[f] + qa.mul[f] * vals[qa.col[f] * kDThreads + tid];
+									}
 								}
 							}
 							slot[(size_t)kk * kDThreads] += term;
@@ -1508,8 +1527,14 @@ cudaError_t launch_scan_columns(const QueryArgs &args, int sm_count, cudaStream_
 	if (args.n_groups && args.dense_ranges != nullptr && args.in_bitmap == nullptr && args.out_bitmap == nullptr) {
 		const size_t smem = (size_t)kDWarps * args.dense_window + (size_t)kQueryMaxCols * kDThreads * 8 +
 		                    (size_t)args.n_groups * args.n_aggs * kDThreads * 8 + (size_t)args.n_groups * kDThreads * 4;
-		void (*kernel)(const QueryArgs, const DenseRange *, uint32_t, uint32_t, uint32_t) =
-		    args.n_aggs <= 2 ? scan_columns_dense_kernel<2> : (args.n_aggs <= 4 ? scan_columns_dense_kernel<4> : scan_columns_dense_kernel<8>);
+		void (*kernel)(const QueryArgs, const DenseRange *, uint32_t, uint32_t, uint32_t);
+		if (args.narrow_values) {
+			kernel = args.n_aggs <= 2 ? scan_columns_dense_kernel<2, true>
+			                          : (args.n_aggs <= 4 ? scan_columns_dense_kernel<4, true> : scan_columns_dense_kernel<8, true>);
+		} else {
+			kernel = args.n_aggs <= 2 ? scan_columns_dense_kernel<2, false>
+			                          : (args.n_aggs <= 4 ? scan_columns_dense_kernel<4, false> : scan_columns_dense_kernel<8, false>);
+		}
 		cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 		if (e != cudaSuccess) {
 			return e;
