@@ -110,6 +110,7 @@ _PROTOTYPES = {
     "adacom_uncompact": (_i, [_vp, _u64, _u64, _i]),
     "adacom_scan_sum": (_i, [_vp, _u64, _u64, _i, C.POINTER(Agg)]),
     "adacom_scan_sum_async": (_i, [_vp, _u64, _u64, _i, _vp]),
+    "adacom_packed_sum_noalloc": (_i, [_vp, _u64, _u32, _u64, _i, _vp, _vp]),
     "adacom_scan_filter": (_i, [_vp, _u64, _u64, _i, _i, C.c_int64, C.POINTER(Agg), _vp]),
     "adacom_scan_select": (_i, [_vp, _u64, _u64, _i, _vp, _u32, _i, _vp, _i, _vp, _vp, C.POINTER(Agg)]),
     "adacom_scan_sum_valid": (_i, [_vp, _u64, _u64, _i, _vp, _i, C.POINTER(Agg)]),

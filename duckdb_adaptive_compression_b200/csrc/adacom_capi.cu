@@ -90,6 +90,12 @@ struct adacom_column {
 	uint64_t epoch = 0;
 };
 
+namespace adacom {
+void set_process_error(const std::string &msg) {
+	g_process_error = msg;
+}
+}  // namespace adacom
+
 namespace {
 
 adacom_status fail(adacom_ctx *ctx, adacom_status st, const std::string &msg) {

@@ -4,6 +4,8 @@
 
 #include "adacom_device.cuh"
 
+#include <string>
+
 namespace adacom {
 
 enum DecodeMode : int { kModeFlat = 0, kModeSum = 1, kModeFilter = 2, kModePoint = 3 };
@@ -230,6 +232,8 @@ struct CodecArgs {
 	uint32_t *run_start = nullptr;  // RLE: exclusive prefix sums of the run lengths
 };
 // codec 0 = bitpacking, 1 = RLE; mode 0 = decode to flat values, 1 = fused SUM/COUNT
+// text behind adacom_last_error(NULL) (adacom_capi.cu), for entry points that live outside adacom_capi.cu
+void set_process_error(const std::string &msg);
 cudaError_t launch_codec_scan(TypeInfo t, int codec, int mode, const CodecArgs &args, int sm_count, cudaStream_t stream);
 cudaError_t launch_codec_fetch(TypeInfo t, int codec, const CodecArgs &args, const uint32_t *seg_idx,
                                const uint32_t *row_in_seg, uint64_t n, cudaStream_t stream);

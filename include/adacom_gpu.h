@@ -218,6 +218,26 @@ adacom_status adacom_scan_sum(adacom_column *col, uint64_t seg_begin, uint64_t s
 /* same, asynchronous: the aggregate is left in device memory (32 bytes, adacom_agg layout) */
 adacom_status adacom_scan_sum_async(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags,
                                     adacom_agg *device_out);
+/* Allocation-free fused decode + SUM/COUNT of ONE packed payload.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  The call takes no context and allocates nothing, on the device or the host side:
+ * no cudaMalloc / cudaFree / stream-ordered allocation, no allocating library routine.  Its only working memory is a
+ * file-scope `static __device__` array of the library (kernels_noalloc.cu: 524,544 bytes, resident on every GPU that
+ * loads the library until the process exits): one 32-byte partial per 4096 values plus a ticket word, which is why
+ * count is limited to ADACOM_NOALLOC_MAX_VALUES -- a larger count is rejected with ADACOM_ERR_INVALID (split the call).
+ *   device_words  the payload on the device: count fields of `width` bits, LSB first in 64-bit words (the packed arena
+ *                 layout: adacom_column_packed_device_ptr() + 8 * meta.word_offset), ceil(count * width / 64) words
+ *   min_factor    the frame of reference added to every field (adacom_segment_meta.min_factor; 0 for none)
+ *   stream        a cudaStream_t of the CURRENT device (NULL = the default stream); the caller keeps that device current
+ *   device_out    one adacom_agg in device-accessible memory (device or pinned host), overwritten on the stream:
+ *                 sum over i of T(min_factor + field_i) sign-/zero-extended to 128 bits, count, reserved = 0
+ * Same answer as adacom_scan_sum over the segment the payload belongs to.  Every call on a device shares the array
+ * and starts by clearing its ticket on `stream`; calls that overlap on the GPU (different streams or threads) race on
+ * it -- keep them on one stream or otherwise ordered.  The first call on a device looks the array's device address
+ * up (cudaGetSymbolAddress); make that call outside a graph capture.  Errors: text in adacom_last_error(NULL). */
+#define ADACOM_NOALLOC_MAX_VALUES (1ull << 26)
+adacom_status adacom_packed_sum_noalloc(const uint64_t *device_words, uint64_t count, uint32_t width, uint64_t min_factor,
+                                        adacom_ptype type, void *stream, adacom_agg *device_out);
 /* fused decode + (value <op> constant) + COUNT/SUM of the matching rows; optional selection bitmap
  * (1 bit per row of the range, bit r - row_start(seg_begin); device pointer, zeroed by the call). */
 adacom_status adacom_scan_filter(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags, adacom_cmp op,
