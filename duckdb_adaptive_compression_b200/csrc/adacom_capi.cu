@@ -40,7 +40,7 @@ struct adacom_ctx {
 	Agg *d_agg = nullptr;
 	unsigned long long *d_totals = nullptr;  // device alias of h_totals (host-mapped)
 	unsigned long long ticket = 0;           // sequence number of the last layout launch
-	unsigned long long *d_layout_scratch = nullptr;  // chained scan of layout_kernel (128 words)
+	unsigned long long *d_layout_scratch = nullptr;  // chained scan of layout_kernel (2 words per CTA, <= 128 CTAs)
 	Agg *d_aggs = nullptr;                // adacom_scan_columns: kQueryMaxAggs aggregates (lazily allocated)
 	Agg *h_aggs = nullptr;                // pinned
 	Agg *h_agg = nullptr;                 // pinned
@@ -73,7 +73,8 @@ struct adacom_column {
 	SegDesc *d_desc = nullptr;
 	std::vector<SegDesc> h_desc;
 	bool mirror_dirty = false;
-	std::vector<Extent> extents;
+	std::vector<Extent> extents;  // indexed by SegDesc::extent; a dead slot (base == nullptr) is reused by the next encode
+	size_t latest = 0;            // slot of the most recent encode: "the packed arena" of the accessors
 	std::vector<Extent> spares;  // dead extents kept for the next encode (no allocator call on the hot path)
 	// 2048-value tiles of every segment, (segment, k) pairs in segment order: depends on the segment counts only,
 	// so it is built once; the tiles of the segments [b, e) are d_tiles[tile_first[b] .. tile_first[e])
@@ -158,6 +159,7 @@ adacom_status retire_extent(adacom_column *col, Extent &x) {
 	x.base = nullptr;
 	x.words = 0;
 	x.capacity = 0;
+	x.live = 0;
 	return ADACOM_OK;
 }
 
@@ -372,8 +374,8 @@ extern "C" adacom_status adacom_ctx_create(int device, adacom_ctx **out) {
 	CK(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
 	CK(nullptr, cudaMalloc((void **)&ctx->d_agg, sizeof(Agg)));
 	CK(nullptr, cudaHostAlloc((void **)&ctx->h_agg, sizeof(Agg), cudaHostAllocDefault));
-	CK(nullptr, cudaMalloc((void **)&ctx->d_layout_scratch, 128 * sizeof(unsigned long long)));
-	CK(nullptr, cudaMemset(ctx->d_layout_scratch, 0, 128 * sizeof(unsigned long long)));
+	CK(nullptr, cudaMalloc((void **)&ctx->d_layout_scratch, 256 * sizeof(unsigned long long)));
+	CK(nullptr, cudaMemset(ctx->d_layout_scratch, 0, 256 * sizeof(unsigned long long)));
 	// {payload words, ticket} written by layout_kernel straight into host memory; the encode path spins on the
 	// ticket (a few microseconds) instead of a copy + stream synchronisation
 	CK(nullptr, cudaHostAlloc((void **)&ctx->h_totals, 4 * sizeof(unsigned long long), cudaHostAllocMapped));
@@ -632,7 +634,7 @@ extern "C" void *adacom_column_packed_device_ptr(adacom_column *col) {
 	if (!col || col->extents.empty()) {
 		return nullptr;
 	}
-	return (void *)col->extents.back().base;
+	return (void *)col->extents[col->latest].base;
 }
 
 extern "C" adacom_status adacom_column_upload_raw(adacom_column *col, const void *host_values, uint64_t first_value,
@@ -698,30 +700,45 @@ extern "C" adacom_status adacom_column_from_packed(adacom_ctx *ctx, adacom_ptype
 		delete col;
 		return fail(ctx, ADACOM_ERR_NOMEM, std::string("adacom_column_from_packed: ") + cudaGetErrorString(e));
 	}
+	// the caller's metas become descriptors the kernels trust: same checks as a checkpoint image gets (restore_locked)
+	auto bad = [&](uint64_t g, const char *what) -> adacom_status {
+		cudaFreeAsync(ext.base, ctx->stream);
+		cudaFreeAsync(col->d_desc, ctx->stream);
+		col->d_desc = nullptr;
+		delete col;
+		return fail(ctx, ADACOM_ERR_INVALID, "adacom_column_from_packed: segment " + std::to_string(g) + ": " + what);
+	};
+	const uint32_t slot_w = 8u * (uint32_t)col->t.size;
 	uint64_t row = 0;
 	for (uint64_t g = 0; g < n_segments; g++) {
 		const adacom_segment_meta &m = metas[g];
 		SegDesc &d = col->h_desc[g];
 		memset(&d, 0, sizeof(d));
 		bool repacked = m.state & ADACOM_SEG_REPACKED;
+		if (m.state & ~(ADACOM_SEG_COMPACTED | ADACOM_SEG_REPACKED | ADACOM_SEG_ANALYZED)) {
+			return bad(g, "unknown state bits");
+		}
 		if (m.count && !repacked) {
-			cudaFreeAsync(ext.base, ctx->stream);
-			cudaFreeAsync(col->d_desc, ctx->stream);
-			delete col;
-			return fail(ctx, ADACOM_ERR_INVALID, "adacom_column_from_packed: segment is not repacked (no packed image)");
+			return bad(g, "not repacked (no packed image)");
+		}
+		if (repacked && !(m.state & ADACOM_SEG_COMPACTED)) {
+			return bad(g, "repacked but not compacted");
+		}
+		if (repacked && (m.width == 0 || m.width >= slot_w)) {
+			return bad(g, "width of a repacked payload must be in [1, 8 * sizeof(T))");
+		}
+		if (!repacked && m.width != slot_w && m.width != 0) {
+			return bad(g, "width of an empty segment must be the slot width");
+		}
+		if (m.count > m.capacity) {
+			return bad(g, "count exceeds capacity");
 		}
 		if (repacked && (m.word_offset % kSegAlignWords != 0 ||
 		                 m.word_offset + (((uint64_t)m.count * m.width + 63) >> 6) > total_words)) {
-			cudaFreeAsync(ext.base, ctx->stream);
-			cudaFreeAsync(col->d_desc, ctx->stream);
-			delete col;
-			return fail(ctx, ADACOM_ERR_INVALID, "adacom_column_from_packed: bad word_offset");
+			return bad(g, "bad word_offset");
 		}
 		if (m.count * (uint64_t)col->t.size > kBlockSize || (uint64_t)m.capacity * col->t.size > kBlockSize) {
-			cudaFreeAsync(ext.base, ctx->stream);
-			cudaFreeAsync(col->d_desc, ctx->stream);
-			delete col;
-			return fail(ctx, ADACOM_ERR_INVALID, "adacom_column_from_packed: segment exceeds one block");
+			return bad(g, "exceeds one block");
 		}
 		d.row_start = row;
 		d.word_offset = m.word_offset;
@@ -731,13 +748,14 @@ extern "C" adacom_status adacom_column_from_packed(adacom_ctx *ctx, adacom_ptype
 		d.count = (uint32_t)m.count;
 		d.capacity = m.capacity;
 		d.extent = 0;
-		d.width = m.width;
+		d.width = repacked ? m.width : (uint8_t)slot_w;
 		d.state = m.state;
 		ext.live += repacked ? 1 : 0;
 		row += m.count;
 	}
 	col->n_values = row;
 	col->extents.push_back(ext);
+	col->latest = col->extents.size() - 1;
 	if (total_words) {
 		CK(ctx, cudaMemcpyAsync(ext.base, host_words, total_words * 8, cudaMemcpyHostToDevice, ctx->stream));
 	}
@@ -809,12 +827,38 @@ static adacom_status encode_locked(adacom_column *col, uint64_t seg_begin, uint3
                                    const Job *d_jobs, uint32_t n_jobs) {
 	adacom_ctx *ctx = col->ctx;
 	const uint64_t seg_end = d_list ? seg_begin : seg_begin + n;  // a list owns no segment range (extent retirement)
-	const uint32_t extent_id = (uint32_t)col->extents.size();
+	// extent id = the first dead slot (retired, or created without any payload): no Repacked descriptor carries its id
+	// any more (retire follows the descriptor reset in stream order; gc_extents counted none), so the table stays as
+	// small as the number of live extents however many encodes a column sees
+	uint32_t extent_id = (uint32_t)col->extents.size();
+	for (size_t i = 0; i < col->extents.size(); i++) {
+		if (col->extents[i].base == nullptr) {
+			extent_id = (uint32_t)i;
+			break;
+		}
+	}
 	// 1. widths, repack decisions and payload offsets, all on the device
 	const unsigned long long ticket = ++ctx->ticket;
 	LAUNCH(ctx, launch_layout(col->t, col->d_desc, (uint32_t)seg_begin, n, flags, extent_id, ctx->d_totals, ticket,
 	                          col->d_parts, (!d_list && seg_begin == 0 && seg_end == col->n_segs) ? 1 : 0,
 	                          ctx->d_layout_scratch, ctx->stream, d_list));
+	// From here on the descriptors of the call are rewritten (Compacted | Repacked, packed_ptr = 0, extent = extent_id).
+	// If anything below fails -- the extent allocation running out of memory is an expected path -- they are put back
+	// (launch_revert_layout) before the error is returned: no segment is left "repacked" without a payload, and the next
+	// encode, which reuses extent_id, cannot bind such a segment into an unrelated extent.
+	auto rollback = [&](adacom_status st, uint64_t *allocated) -> adacom_status {
+		const std::string msg = ctx->err;
+		cudaGetLastError();  // clear the non-sticky error of the failed call
+		cudaError_t r = launch_revert_layout(col->d_desc, (uint32_t)seg_begin, n, extent_id, col->d_parts, col->raw_parts,
+		                                     ctx->stream, d_list);
+		ctx->launches++;
+		if (allocated) {
+			cudaFreeAsync(allocated, ctx->stream);
+		}
+		col->mirror_dirty = true;
+		ctx->err = msg + (r == cudaSuccess ? " (descriptors rolled back)" : std::string(" (rollback failed: ") + cudaGetErrorString(r) + ")");
+		return st;
+	};
 	// the only host round trip of an encode: 8 bytes that size the new extent, polled from mapped memory
 	{
 		volatile unsigned long long *t = ctx->h_totals;
@@ -823,10 +867,11 @@ static adacom_status encode_locked(adacom_column *col, uint64_t seg_begin, uint3
 			if ((++spins & 0x3ffu) == 0) {
 				cudaError_t q = cudaStreamQuery(ctx->stream);
 				if (q != cudaSuccess && q != cudaErrorNotReady) {
-					CK(ctx, q);
+					return rollback(fail(ctx, ADACOM_ERR_CUDA, std::string("adacom_encode: layout: ") + cudaGetErrorString(q)), nullptr);
 				}
 				if (q == cudaSuccess && t[1] != ticket) {
-					return fail(ctx, ADACOM_ERR_CUDA, "adacom_encode: layout kernel finished without publishing its total");
+					return rollback(fail(ctx, ADACOM_ERR_CUDA, "adacom_encode: layout kernel finished without publishing its total"),
+					                nullptr);
 				}
 			}
 		}
@@ -846,20 +891,45 @@ static adacom_status encode_locked(adacom_column *col, uint64_t seg_begin, uint3
 				pick = (int)i;
 			}
 		}
+		uint64_t *fresh = nullptr;
 		if (pick >= 0) {
 			ext.base = col->spares[(size_t)pick].base;
 			ext.capacity = col->spares[(size_t)pick].capacity;
-			col->spares.erase(col->spares.begin() + pick);
 		} else {
 			ext.capacity = ext.words + ext.words / 32 + 64;
-			CK(ctx, cudaMallocAsync((void **)&ext.base, ext.capacity * 8 + kArenaPad, ctx->stream));
+			// ADACOM_FAULT_ENCODE_ALLOC (test hook, tests/test_gpu_edges.py): behave as if the allocator had run dry
+			const char *fault = getenv("ADACOM_FAULT_ENCODE_ALLOC");
+			cudaError_t e = (fault && fault[0] == '1') ? cudaErrorMemoryAllocation
+			                                           : cudaMallocAsync((void **)&ext.base, ext.capacity * 8 + kArenaPad, ctx->stream);
+			if (e != cudaSuccess) {
+				return rollback(fail(ctx, e == cudaErrorMemoryAllocation ? ADACOM_ERR_NOMEM : ADACOM_ERR_CUDA,
+				                     std::string("adacom_encode: packed extent of ") + std::to_string(ext.capacity * 8) +
+				                         " bytes: " + cudaGetErrorString(e)),
+				                nullptr);
+			}
+			fresh = ext.base;
 		}
 		// 3. pack, then publish packed_ptr = base + word_offset (scans launched later on this stream see it)
-		LAUNCH(ctx, launch_encode(col->t, col->d_desc, d_jobs, n_jobs, col->raw, extent_id, ext.base, ctx->sm_count,
-		                          ctx->stream));
-		LAUNCH(ctx, launch_bind_extent(col->d_desc, (uint32_t)seg_begin, n, ext.base, extent_id, ctx->stream, d_list));
+		cudaError_t e = launch_encode(col->t, col->d_desc, d_jobs, n_jobs, col->raw, extent_id, ext.base, ctx->sm_count, ctx->stream);
+		ctx->launches++;
+		if (e == cudaSuccess) {
+			e = launch_bind_extent(col->d_desc, (uint32_t)seg_begin, n, ext.base, extent_id, ctx->stream, d_list);
+			ctx->launches++;
+		}
+		if (e != cudaSuccess) {
+			// a spare stays a spare; a fresh allocation goes back to the pool
+			return rollback(fail(ctx, ADACOM_ERR_CUDA, std::string("adacom_encode: pack / bind launch: ") + cudaGetErrorString(e)), fresh);
+		}
+		if (pick >= 0) {
+			col->spares.erase(col->spares.begin() + pick);
+		}
 	}
-	col->extents.push_back(ext);
+	if (extent_id == col->extents.size()) {
+		col->extents.push_back(ext);
+	} else {
+		col->extents[extent_id] = ext;
+	}
+	col->latest = extent_id;
 	col->mirror_dirty = true;
 	col->epoch++;
 	return ADACOM_OK;
@@ -1049,18 +1119,18 @@ extern "C" uint64_t adacom_column_packed_words(const adacom_column *col) {
 	if (!col || col->extents.empty()) {
 		return 0;
 	}
-	return col->extents.back().words;
+	return col->extents[col->latest].words;
 }
 
 extern "C" adacom_status adacom_column_download_packed(adacom_column *col, uint64_t first_word, uint64_t n_words,
                                                        uint64_t *host_out) {
-	if (!col || col->extents.empty() || (!host_out && n_words) || first_word + n_words > col->extents.back().words) {
+	if (!col || col->extents.empty() || (!host_out && n_words) || first_word + n_words > col->extents[col->latest].words) {
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_column_download_packed: bad range");
 	}
 	adacom_ctx *ctx = col->ctx;
 	std::lock_guard<std::mutex> lock(ctx->mu);
 	if (n_words) {
-		CK(ctx, cudaMemcpyAsync(host_out, col->extents.back().base + first_word, n_words * 8, cudaMemcpyDeviceToHost,
+		CK(ctx, cudaMemcpyAsync(host_out, col->extents[col->latest].base + first_word, n_words * 8, cudaMemcpyDeviceToHost,
 		                        ctx->stream));
 	}
 	CK(ctx, cudaStreamSynchronize(ctx->stream));
@@ -2338,6 +2408,7 @@ static adacom_status restore_locked(adacom_ctx *ctx, const void *image, uint64_t
 	ext.seg_end = h.n_segments;
 	CK(ctx, cudaMallocAsync((void **)&ext.base, words * 8 + kArenaPad, ctx->stream));
 	col->extents.push_back(ext);
+	col->latest = col->extents.size() - 1;
 	CK(ctx, cudaMallocAsync((void **)&col->d_desc, std::max<uint64_t>(h.n_segments, 1) * sizeof(SegDesc), ctx->stream));
 	if (any_raw) {
 		st = ensure_raw(col);

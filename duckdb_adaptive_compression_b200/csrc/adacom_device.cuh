@@ -28,7 +28,7 @@ struct __align__(16) SegDesc {
 	uint32_t count;
 	uint32_t capacity;     // slots (segment_size / sizeof(T))
 	uint32_t extent;       // id of the packed extent holding the payload
-	uint32_t reserved;
+	uint32_t prev_wst;     // width | state << 8 as they were before the last layout_kernel rewrote them (rollback)
 	uint8_t width;         // current payload width (8*S when not repacked)
 	uint8_t state;         // kSeg* bits
 	uint8_t pad[6];
@@ -46,7 +46,7 @@ struct DescQ {
 	uint4 q0;  // row_start, packed_ptr
 	uint4 q1;  // word_offset, min_factor
 	uint4 q2;  // max_factor, count, capacity
-	uint4 q3;  // extent, reserved, width | state << 8 | pad, pad
+	uint4 q3;  // extent, prev_wst, width | state << 8 | pad, pad
 #ifdef __CUDACC__
 	__device__ __forceinline__ uint64_t row_start() const { return ((uint64_t)q0.y << 32) | q0.x; }
 	__device__ __forceinline__ uint64_t packed_ptr() const { return ((uint64_t)q0.w << 32) | q0.z; }

@@ -167,6 +167,9 @@ cudaError_t launch_layout(TypeInfo t, SegDesc *desc, uint32_t seg_begin, uint32_
 cudaError_t launch_bind_extent(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, uint64_t *base, uint32_t extent,
                                cudaStream_t stream, const uint32_t *seg_list = nullptr);
 
+// rollback of launch_layout when the encode behind it cannot complete: unbound descriptors of `extent` get their old width / state
+cudaError_t launch_revert_layout(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, uint32_t extent, uint32_t *parts,
+                                 uint32_t raw_parts, cudaStream_t stream, const uint32_t *seg_list = nullptr);
 // after an uncompact decode: segments of the range that were compacted go back to slot width / UNCOMPRESSED
 cudaError_t launch_reset_uncompacted(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, int type_size,
                                      uint32_t *parts, uint32_t raw_parts, cudaStream_t stream,

@@ -174,7 +174,8 @@ __global__ void __launch_bounds__(kAnalyzeThreads) analyze_kernel(SegDesc *desc,
 
 constexpr int kLayoutThreads = 256;
 constexpr int kLayoutMaxCtas = 128;  // <= SM count: every CTA is resident, a CTA only ever waits for lower-indexed ones
-constexpr int kLayoutTagShift = 48;  // scratch word = ticket tag (16 bits) | scan chunks (5 bits, << 43) | words (43 bits)
+// scratch: two words per CTA, {scan chunks (<< 43) | words (43 bits), ticket of the call that wrote them}: a slot is
+// trusted only while its ticket word equals the call's full 64-bit ticket (tickets never repeat on a context)
 
 struct LayoutItem {
 	unsigned long long aligned;  // payload words rounded up to 128 bytes; ~0: descriptor left untouched
@@ -237,7 +238,6 @@ __global__ void __launch_bounds__(kLayoutThreads) layout_kernel(SegDesc *desc, u
 	const bool padded = flags & kFlagPadded;
 	const bool zero_ext = flags & kFlagZeroExt;
 	const uint32_t slot_w = 8u * (uint32_t)type_size;
-	const unsigned long long tag = (ticket & 0xffffull) << kLayoutTagShift;
 	if (tid == 0) {
 		base_s = 0;
 		parts_s = 1;
@@ -285,15 +285,17 @@ __global__ void __launch_bounds__(kLayoutThreads) layout_kernel(SegDesc *desc, u
 	__syncthreads();
 	// ---- chained scan over the CTAs ----
 	if (tid == 0) {
-		scratch[blockIdx.x] = tag | ((unsigned long long)parts_s << 43) | cta_total;
+		scratch[2u * blockIdx.x] = ((unsigned long long)parts_s << 43) | cta_total;
+		__threadfence();
+		scratch[2u * blockIdx.x + 1u] = ticket;
 	}
 	unsigned long long before = 0;
 	uint32_t parts_before = 1;
 	for (uint32_t j = tid; j < blockIdx.x; j += kLayoutThreads) {
-		unsigned long long v;
-		do {
-			v = scratch[j];
-		} while ((v >> kLayoutTagShift) != (tag >> kLayoutTagShift));
+		while (scratch[2u * j + 1u] != ticket) {
+		}
+		__threadfence();
+		const unsigned long long v = scratch[2u * j];
 		before += v & ((1ull << 43) - 1ull);
 		parts_before = max(parts_before, (uint32_t)((v >> 43) & 31u));
 	}
@@ -318,6 +320,7 @@ __global__ void __launch_bounds__(kLayoutThreads) layout_kernel(SegDesc *desc, u
 			d->packed_ptr = 0;
 			d->word_offset = off;
 			d->extent = extent;
+			d->prev_wst = ((const uint32_t *)d)[14] & 0xffffu;
 			((uint32_t *)d)[14] = it.wst;
 			off += it.aligned;
 		}
@@ -341,6 +344,27 @@ __global__ void bind_extent_kernel(SegDesc *desc, uint32_t seg_begin, uint32_t n
 		SegDesc *d = desc + (seg_list ? __ldg(seg_list + g) : seg_begin + g);
 		if ((d->state & kSegRepacked) && d->extent == extent && d->packed_ptr == 0) {
 			d->packed_ptr = (uint64_t)(base + d->word_offset);
+		}
+	}
+}
+
+// Rollback of a layout whose encode could not be completed (extent allocation failed, a later launch failed): every
+// descriptor the layout of extent id `extent` rewrote and that was never bound to a payload gets the width / state it
+// had before; its extent id is cleared so that the next encode -- which reuses the id -- cannot bind it by mistake.
+__global__ void revert_layout_kernel(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, uint32_t extent, uint32_t *parts,
+                                     uint32_t raw_parts, const uint32_t *seg_list) {
+	uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+	if (g == 0) {
+		atomicMax(parts, raw_parts);  // slot-width segments need the most scan chunks
+	}
+	if (g < n_segs) {
+		SegDesc *d = desc + (seg_list ? __ldg(seg_list + g) : seg_begin + g);
+		if ((d->state & kSegCompacted) && d->extent == extent && d->packed_ptr == 0) {
+			const uint32_t prev = d->prev_wst;
+			d->width = (uint8_t)(prev & 0xffu);
+			d->state = (uint8_t)((prev >> 8) & 0xffu);
+			d->word_offset = 0;
+			d->extent = ~0u;
 		}
 	}
 }
@@ -418,6 +442,15 @@ cudaError_t launch_bind_extent(SegDesc *desc, uint32_t seg_begin, uint32_t n_seg
 		return cudaSuccess;
 	}
 	bind_extent_kernel<<<(n_segs + 255) / 256, 256, 0, stream>>>(desc, seg_begin, n_segs, base, extent, seg_list);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_revert_layout(SegDesc *desc, uint32_t seg_begin, uint32_t n_segs, uint32_t extent, uint32_t *parts,
+                                 uint32_t raw_parts, cudaStream_t stream, const uint32_t *seg_list) {
+	if (n_segs == 0) {
+		return cudaSuccess;
+	}
+	revert_layout_kernel<<<(n_segs + 255) / 256, 256, 0, stream>>>(desc, seg_begin, n_segs, extent, parts, raw_parts, seg_list);
 	return cudaGetLastError();
 }
 

@@ -350,3 +350,102 @@ def test_point_lookups_hits_misses_duplicates(gpu_ctx, dtype):
         if len(hit):
             assert first[j] == hit[0], (g, k)
     col.close()
+
+
+def test_encode_rolls_back_when_the_extent_allocation_fails(gpu_ctx, port_oracle, monkeypatch):
+    """An encode whose packed extent cannot be allocated (ADACOM_FAULT_ENCODE_ALLOC: the allocator "runs dry" after
+    layout_kernel has already rewritten the descriptors) must leave every segment as it was -- not compacted, slot
+    width, readable from the raw arena -- and the next encode must produce exactly the payloads of a clean one."""
+    dtype = np.int32
+    vals = [width_values(dtype, w, n, base, seed=g) for g, (w, n, base) in
+            enumerate([(5, 40000, 7), (32, 3000, -5), (13, 65534, 1000), (1, 1, 0), (20, 2049, -(1 << 30))])]
+    flat = np.concatenate(vals)
+    counts = [len(v) for v in vals]
+    col = gpu_ctx.column_from_values(flat, counts)
+    col.analyze()
+    before = [(m.width, m.state, m.size_in_bytes) for m in col.meta()]
+    for attempt in ("range", "list"):
+        monkeypatch.setenv("ADACOM_FAULT_ENCODE_ALLOC", "1")
+        with pytest.raises(adacom.AdacomError) as err:
+            if attempt == "range":
+                col.encode()
+            else:
+                col.compact_list([0, 2, 4], analyze=False)
+        assert err.value.status == 3 and "rolled back" in str(err.value)  # ADACOM_ERR_NOMEM
+        monkeypatch.delenv("ADACOM_FAULT_ENCODE_ALLOC")
+        assert [(m.width, m.state, m.size_in_bytes) for m in col.meta()] == before, attempt
+        assert np.array_equal(col.decode(), flat)
+        got = col.scan_sum()
+        assert (got.sum, got.count) == (int(flat.astype(object).sum()), len(flat))
+        assert col.scan_filter(2, 100).count == int((flat < 100).sum())
+    col.encode()  # the same extent id is used again: nothing stale may be bound
+    segs = [port_oracle.encode(v, 0) for v in vals]
+    for g, (m, s) in enumerate(zip(col.meta(), segs)):
+        assert (m.width, m.size_in_bytes) == (s.meta().width, s.meta().data_size), g
+        if s.meta().repacked:
+            assert col.serialize(g) == s.serialize(), g
+    assert np.array_equal(col.decode(), flat)
+    # ... and a failure on an already partly compacted column only reverts the segments that call touched
+    col.uncompact(1, 4)
+    col.analyze(1, 4)
+    mid = [(m.width, m.state) for m in col.meta()]
+    monkeypatch.setenv("ADACOM_FAULT_ENCODE_ALLOC", "1")
+    with pytest.raises(adacom.AdacomError):
+        col.encode(0, 5)
+    monkeypatch.delenv("ADACOM_FAULT_ENCODE_ALLOC")
+    assert [(m.width, m.state) for m in col.meta()] == mid
+    assert np.array_equal(col.decode(), flat)
+    col.encode(0, 5)
+    assert np.array_equal(col.decode(), flat)
+    for g, (m, s) in enumerate(zip(col.meta(), segs)):
+        assert (m.width, m.size_in_bytes) == (s.meta().width, s.meta().data_size), g
+    col.close()
+
+
+def test_many_encode_cycles_reuse_extent_slots(gpu_ctx):
+    """hot/cold cycles of the policy on one column: the extent table must not grow with the number of encodes and
+    the payloads stay right (dead slots are reused; ids repeat)"""
+    dtype = np.uint16
+    rng = np.random.default_rng(3)
+    counts = [5000, 131068, 1, 70000]
+    flat = rng.integers(100, 100 + (1 << 9), size=sum(counts)).astype(dtype)
+    col = gpu_ctx.column_from_values(flat, counts)
+    col.compact()
+    want = int(flat.astype(object).sum())
+    for it in range(200):
+        segs = sorted(rng.choice(len(counts), size=int(rng.integers(1, len(counts) + 1)), replace=False).tolist())
+        col.uncompact_list(segs)
+        if it % 3 == 0:
+            col.meta()  # refresh the mirror: gc of dead extents
+        col.compact_list(segs)
+        if it % 10 == 0:
+            got = col.scan_sum()
+            assert (got.sum, got.count) == (want, len(flat)), it
+    assert np.array_equal(col.decode(), flat)
+    assert all(m.state & 2 for m in col.meta())
+    col.close()
+
+
+def test_from_packed_rejects_malformed_metas(gpu_ctx):
+    dtype = np.uint32
+    vals = width_values(dtype, 11, 5000, 3, seed=1)
+    col = gpu_ctx.column_from_values(vals, [3000, 2000])
+    col.compact()
+    metas, words = col.meta(), col.download_packed()
+    good = gpu_ctx.column_from_packed(dtype, metas, words)
+    assert np.array_equal(good.decode(), vals)
+    good.close()
+
+    def broken(**kw):
+        ms = col.meta()
+        for k, v in kw.items():
+            setattr(ms[1], k, v)
+        return ms
+
+    for ms in (broken(width=0), broken(width=32), broken(width=64), broken(state=0x13), broken(state=2),
+               broken(count=70000), broken(word_offset=metas[1].word_offset + 1), broken(word_offset=1 << 40)):
+        with pytest.raises(adacom.AdacomError) as err:
+            gpu_ctx.column_from_packed(dtype, ms, words)
+        assert err.value.status == 1
+    assert col.scan_sum().count == 5000
+    col.close()
