@@ -445,3 +445,52 @@ def neighbour_codecs(ctx, peak, threads, log2_values=26, steps=5, warmup=3):
     out["value"] = out["bitpacking"]["decode"]["logical_GBs"]
     out["unit"] = "GB/s decoded (bitpacking scan -> flat)"
     return out
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# the drop-in vtable path: SuccinctGpuFun's slots driven like ColumnData drives the reference's
+# ---------------------------------------------------------------------------------------------------------------------
+def vtable_dropin(threads, log2_values=27, bits=17, cpu_log2_values=22):
+    """host/build/vtable_bench (C++: ColumnData::AppendData -> batched compaction, ColumnData::ScanVector pulls of 2048
+    values through scan_vector / scan_partial, FetchRow / FetchRows) on config 2's column shape (INT64, 2^27 values,
+    one width), HOST buffers on both sides; beside it the reference's SuccinctScanPartial loop incl. its per-call deep
+    copy (succinct.cpp:127 -- what the reference really executes per pull) from oracle/_ref on the host cores."""
+    import json as _json
+    import subprocess as _sp
+    exe = os.path.join(ROOT, "duckdb_adaptive_compression_b200", "host", "build", "vtable_bench")
+    if not os.path.exists(exe):
+        raise RuntimeError("host/build/vtable_bench is not built (run __graft_entry__.build())")
+    scan_threads = max(1, min(8, threads // 2))
+    runs = {}
+    for t in sorted({1, scan_threads}):
+        r = _sp.run([exe, str(log2_values), str(bits), str(t)], capture_output=True, text=True, timeout=600)
+        if r.returncode != 0:
+            raise RuntimeError(f"vtable_bench failed (rc {r.returncode}): {r.stdout[-300:]} {r.stderr[-300:]}")
+        runs[t] = _json.loads(r.stdout.strip().splitlines()[-1])
+    best = runs[scan_threads]
+    out = {"workload": f"SuccinctGpuFun vtable driven like ColumnData (append / ScanVector / FetchRow): INT64, 2^{log2_values} "
+                       f"values, {bits}-bit payloads, host buffers on both sides",
+           "value": best["scan_GBs"], "unit": "GB/s decoded into host vectors (scan_vector pulls)",
+           "scan_threads": scan_threads, "scan_1thread_GBs": runs[1]["scan_GBs"],
+           "scan_verified_GBs": best["scan_verify_GBs"], "zero_copy_vectors": best["zero_copy_vectors"],
+           "vectors": best["vectors"], "segments": best["segments"], "device_columns": best["device_columns"],
+           "append_compact_GBs": best["load_GBs"], "fetch_row_per_s": best["fetch_row_per_s"],
+           "fetch_rows_batched_per_s": best["fetch_rows_batched_per_s"], "answers_checked": best["scan_ok"] and best["fetch_ok"],
+           "timed": "host clock around the pull loops (device work, D2H of the pinned windows and the pulls overlap); load = "
+                    "append of host vectors + H2D + analyze + encode, batched per 512 segments"}
+    o = _ref_oracle()
+    if o is not None:
+        from tests.cases import splitmix64
+        n = 1 << cpu_log2_values
+        vals = (splitmix64(np.arange(n, dtype=np.uint64)) & np.uint64((1 << bits) - 1)).view(np.int64) + 1000003
+        one = o.bench_column(vals, 32767, 1, copy_per_call=True)
+        allc = o.bench_column(vals, 32767, threads, copy_per_call=True)
+        per_thread = n * 8 / one["scan_s"] / 1e9
+        out["cpu_baseline"] = {"value": round(n * 8 / allc["scan_s"] / 1e9, 3), "unit": "GB/s decoded", "cores": threads,
+                               "kind": "reference", "per_thread_GBs": round(per_thread, 3),
+                               "append_compact_GBs": round(n * 8 / (allc["analyze_s"] + allc["encode_s"]) / 1e9, 3),
+                               "sample": f"2^{cpu_log2_values} values of the same distribution: SuccinctScanPartial per 2048-value "
+                                         f"vector incl. the per-call deep copy of the packed vector (succinct.cpp:127), one "
+                                         f"thread and {threads} threads"}
+        out["speedup_per_host_thread"] = round(runs[1]["scan_GBs"] / per_thread, 1)
+    return out
