@@ -53,9 +53,10 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-log2-values", type=int, default=21)
     ap.add_argument("--detail", default="", help="write the per-width table to this JSON file")
-    ap.add_argument("--configs", default="1,3,4,5,codecs", help="the other BASELINE.json workload shapes to run after the "
+    ap.add_argument("--configs", default="1,3,4,5,codecs,vtable", help="the other BASELINE.json workload shapes to run after the "
                     "headline sweep (1 Zipf point filters, 3 skew sweep + policy epochs, 4 TPC-H SF10 Q6/Q1, "
-                    "5 TPC-H SF100 sharded Q6 over NCCL); '' = none")
+                    "5 TPC-H SF100 sharded Q6 over NCCL, codecs = DuckDB bitpacking / RLE, vtable = the drop-in "
+                    "CompressionFunction slots driven like ColumnData from C++); '' = none")
     return ap.parse_args()
 
 
@@ -420,6 +421,8 @@ def run_ours(args):
             "parallelism": f"row groups sharded, {world} rank(s), NCCL all-gather of 64 aggregates/step",
             "segments_per_column": int(len(counts)),
             "ops": op_summary, "configs": configs, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+            # the drop-in path: SuccinctGpuFun's vtable slots driven like ColumnData::ScanVector / FetchRow (C++ host shim)
+            "e2e_vtable": (configs or {}).pop("e2e_vtable", None),
             "gpu_launches": int(launches), "clocks": clocks,
         }
         print(json.dumps(line), flush=True)
@@ -466,6 +469,8 @@ def run_configs(args, ctx, rank, world, peak):
         leg("4_tpch_sf10", lambda: workloads.config4_tpch(ctx, peak, threads), True)
     if "codecs" in wanted:
         leg("f4_neighbour_codecs", lambda: workloads.neighbour_codecs(ctx, peak, threads), True)
+    if "vtable" in wanted:
+        leg("e2e_vtable", lambda: workloads.vtable_dropin(threads), True)
     if "5" in wanted:
         leg("5_tpch_sf100_sharded", lambda: workloads.config5_tpch_sharded(ctx, peak, rank, world), False)
     return out if rank == 0 else None
@@ -474,7 +479,13 @@ def run_configs(args, ctx, rank, world, peak):
 def run_e2e(args, ctx, cols, widths, counts, n, S, rank, world, dev):
     import torch
     import torch.distributed as dist
+    from duckdb_adaptive_compression_b200 import numa
     raw_bytes = n * S
+    # threads + pinned staging of this rank onto the NUMA node of its GPU (restored at the end of the leg: the CPU
+    # baseline uses all host cores)
+    affinity_before = os.sched_getaffinity(0)
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    placement = numa.bind_to_gpu_node(local_rank, local_rank, int(os.environ.get("LOCAL_WORLD_SIZE", str(world))))
     # pinned budget: raw per width + a packed and a flat buffer per host thread; keep half of the host memory free
     avail = host_mem_available_bytes()
     local_world = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
@@ -485,6 +496,7 @@ def run_e2e(args, ctx, cols, widths, counts, n, S, rank, world, dev):
         dist.all_reduce(t, op=dist.ReduceOp.MIN)
         max_w = int(t.item())
     if max_w < 1:
+        os.sched_setaffinity(0, affinity_before)
         return {"value": None, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
                 "note": f"not enough host memory for pinned staging ({avail >> 30} GiB available)"}
     if max_w >= len(widths):
@@ -560,7 +572,11 @@ def run_e2e(args, ctx, cols, widths, counts, n, S, rank, world, dev):
         wk["ctx"].free_pinned(wk["flat"])
         if wk["ctx"] is not ctx:
             wk["ctx"].close()
-    return {"value": round(logical / dt / 1e9, 2), "unit": "GB/s", "h2d_bytes_per_step": int(h2d),
+    try:
+        os.sched_setaffinity(0, affinity_before)
+    except OSError:
+        pass
+    return {"value": round(logical / dt / 1e9, 2), "unit": "GB/s", "h2d_bytes_per_step": int(h2d), "placement": placement,
             "d2h_bytes_per_step": int(d2h), "steps": args.e2e_steps, "warmup": 1, "ms_per_step": round(dt * 1e3, 2),
             "widths": e_widths if len(e_widths) < len(widths) else args.widths,
             "host_threads": n_workers,

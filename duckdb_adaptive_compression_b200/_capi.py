@@ -107,6 +107,9 @@ _PROTOTYPES = {
     "adacom_segment_serialize": (_i, [_vp, _u64, _vp, _u64, C.POINTER(_u64)]),
     "adacom_decode": (_i, [_vp, _u64, _u64, _i, _vp, _i]),
     "adacom_scan_partial": (_i, [_vp, _u64, _u64, _u64, _i, _vp, _u64, _i]),
+    "adacom_scan_stream_open": (_i, [_vp, _u64, _u64, _u32, _u32, _i, C.POINTER(_vp)]),
+    "adacom_scan_stream_segment": (_i, [_vp, _u64, C.POINTER(_vp), C.POINTER(_u64)]),
+    "adacom_scan_stream_close": (None, [_vp]),
     "adacom_uncompact": (_i, [_vp, _u64, _u64, _i]),
     "adacom_scan_sum": (_i, [_vp, _u64, _u64, _i, C.POINTER(Agg)]),
     "adacom_scan_sum_async": (_i, [_vp, _u64, _u64, _i, _vp]),

@@ -263,6 +263,35 @@ class CodecColumn:
         return out
 
 
+class ScanStream:
+    """adacom_scan_stream: segment(seg) returns a numpy VIEW of the pinned window (valid until the stream has moved
+    depth-1 windows on or is closed) -- copy it if it has to live longer."""
+
+    def __init__(self, col: "Column", seg_begin: int, seg_end: int, window_segments: int, depth: int, flags: int):
+        self.col = col
+        self.h = C.c_void_p()
+        col.ctx.check(col.lib.adacom_scan_stream_open(col.h, seg_begin, seg_end, window_segments, depth, flags, C.byref(self.h)))
+
+    def segment(self, seg: int) -> np.ndarray:
+        ptr, cnt = C.c_void_p(), C.c_uint64()
+        self.col.ctx.check(self.col.lib.adacom_scan_stream_segment(self.h, seg, C.byref(ptr), C.byref(cnt)))
+        if cnt.value == 0:
+            return np.zeros(0, dtype=self.col.dtype)
+        buf = (C.c_uint8 * (cnt.value * self.col.dtype.itemsize)).from_address(ptr.value)
+        return np.frombuffer(buf, dtype=self.col.dtype)
+
+    def close(self):
+        if self.h:
+            self.col.lib.adacom_scan_stream_close(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def _wrap_i64(v: int) -> int:
     v = int(v)
     return v - (1 << 64) if v >= 1 << 63 else v
@@ -460,6 +489,11 @@ class Column:
 
     def scan_vector(self, seg: int, start: int, scan_count: int = VECTOR_SIZE, flags=0) -> np.ndarray:
         return self.scan_partial(seg, start, scan_count, flags)
+
+    def scan_stream(self, seg_begin=0, seg_end=None, window_segments=0, depth=0, flags=0) -> "ScanStream":
+        """Pull-model scan (adacom_scan_stream_*): windows of segments decoded ahead into a pinned host ring."""
+        b, e = self._range(seg_begin, seg_end)
+        return ScanStream(self, b, e, window_segments, depth, flags)
 
     def uncompact(self, seg_begin=0, seg_end=None, flags=0):
         b, e = self._range(seg_begin, seg_end)

@@ -53,6 +53,16 @@ struct adacom_ctx {
 	// staging pair of the batched look-ups (pinned host + device, grown on demand): one H2D, one kernel, one D2H
 	uint8_t *h_stage = nullptr, *d_stage = nullptr;
 	size_t stage_bytes = 0;
+	// window rings of closed scan streams (pinned host + device buffer + copy stream + events), reused by the next
+	// adacom_scan_stream_open: allocating 24 MiB of pinned memory costs milliseconds, a scan opens one stream per
+	// device column it crosses
+	struct ScanRing {
+		uint8_t *d_ring = nullptr, *h_ring = nullptr;
+		size_t bytes = 0;
+		cudaStream_t copy_stream = nullptr;
+		std::vector<cudaEvent_t> events;
+	};
+	std::vector<ScanRing> ring_cache;
 };
 
 struct Extent {
@@ -409,6 +419,15 @@ extern "C" void adacom_ctx_destroy(adacom_ctx *ctx) {
 	cudaFreeHost(ctx->h_totals);
 	cudaFreeHost(ctx->h_stage);
 	cudaFree(ctx->d_stage);
+	for (auto &r : ctx->ring_cache) {
+		cudaStreamSynchronize(r.copy_stream);
+		for (auto e : r.events) {
+			cudaEventDestroy(e);
+		}
+		cudaFreeHost(r.h_ring);
+		cudaFree(r.d_ring);
+		cudaStreamDestroy(r.copy_stream);
+	}
 	cudaStreamDestroy(ctx->stream);
 	delete ctx;
 }
@@ -2552,6 +2571,7 @@ struct adacom_codec_column {
 	std::vector<CodecSeg> h_segs;
 	Job *d_jobs = nullptr;        // (segment, 2048-value group) in segment order
 	std::vector<uint32_t> job_first;
+	CodecGroup *d_groups = nullptr;  // one record per entry of d_jobs, resolved at creation (codec_groups_kernel)
 	Job *d_sum_jobs = nullptr;    // RLE SUM: (segment, tile of 2048 runs)
 	std::vector<uint32_t> sum_job_first;
 	uint32_t *d_run_start = nullptr;
@@ -2661,6 +2681,16 @@ extern "C" adacom_status adacom_codec_column_create(adacom_ctx *ctx, adacom_code
 		a.run_start = col->d_run_start;
 		LAUNCH(ctx, launch_rle_run_starts(a, 0, (uint32_t)n_segments, ctx->sm_count, ctx->stream));
 	}
+	{
+		CK(ctx, cudaMallocAsync((void **)&col->d_groups, std::max<size_t>(jobs.size(), 1) * sizeof(CodecGroup), ctx->stream));
+		CodecArgs a;
+		a.images = col->d_images;
+		a.segs = col->d_segs;
+		a.run_start = col->d_run_start;
+		a.jobs = col->d_jobs;
+		a.n_jobs = (uint32_t)jobs.size();
+		LAUNCH(ctx, launch_codec_groups(col->t, col->codec, a, col->d_groups, ctx->stream));
+	}
 	CK(ctx, cudaStreamSynchronize(ctx->stream));  // the host vectors and the caller's images may go away now
 	*out = col.release();
 	return ADACOM_OK;
@@ -2674,7 +2704,7 @@ extern "C" void adacom_codec_column_destroy(adacom_codec_column *col) {
 	std::lock_guard<std::mutex> lock(ctx->mu);
 	cudaSetDevice(ctx->device);
 	for (void *p : {(void *)col->d_images, (void *)col->d_segs, (void *)col->d_jobs, (void *)col->d_sum_jobs,
-	                (void *)col->d_run_start}) {
+	                (void *)col->d_run_start, (void *)col->d_groups}) {
 		if (p) {
 			cudaFreeAsync(p, ctx->stream);
 		}
@@ -2705,6 +2735,7 @@ static CodecArgs codec_args(adacom_codec_column *col, uint64_t b, uint64_t e, bo
 		a.n_jobs = col->sum_job_first[e] - col->sum_job_first[b];
 	} else {
 		a.jobs = col->d_jobs + col->job_first[b];
+		a.groups = col->d_groups + col->job_first[b];
 		a.n_jobs = col->job_first[e] - col->job_first[b];
 	}
 	a.out_row0 = b < col->n_segs ? col->h_segs[b].row_start : 0;
@@ -2799,4 +2830,266 @@ extern "C" adacom_status adacom_codec_fetch_rows(adacom_codec_column *col, uint6
 	CK(ctx, cudaFreeAsync(d_out, ctx->stream));
 	CK(ctx, cudaStreamSynchronize(ctx->stream));
 	return ADACOM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Pull-model scan stream (include/adacom_gpu.h: adacom_scan_stream_*).  Decode kernels go onto the context's stream
+// (ordered with the encodes / uncompacts of the column, so a window never reads a descriptor in mid-update); the
+// device->host copies of the windows run on the scan's own stream behind an event, and the consumer waits on events
+// only -- never on the context mutex, never on a stream synchronisation.
+// ---------------------------------------------------------------------------------------------------------------
+struct adacom_scan_stream {
+	adacom_column *col = nullptr;
+	uint64_t seg_begin = 0, seg_end = 0;
+	uint32_t win_segs = 32, depth = 3;
+	int flags = 0;
+	cudaStream_t copy_stream = nullptr;
+	uint8_t *d_ring = nullptr, *h_ring = nullptr;
+	size_t win_bytes = 0, ring_bytes = 0;
+	struct Win {
+		uint64_t index = ~0ull;  // window number held (or in flight) in this slot
+		cudaEvent_t decoded = nullptr, arrived = nullptr;
+		bool waited = false;     // the consumer has already synchronised on `arrived`
+		bool used = false;       // `arrived` has been recorded at least once
+	};
+	std::vector<Win> wins;
+	uint64_t n_windows = 0;
+};
+
+namespace {
+
+uint64_t window_first(const adacom_scan_stream *s, uint64_t w) {
+	return s->seg_begin + w * s->win_segs;
+}
+uint64_t window_end(const adacom_scan_stream *s, uint64_t w) {
+	const uint64_t e = window_first(s, w) + s->win_segs;
+	return e < s->seg_end ? e : s->seg_end;
+}
+
+// enqueue window w into its slot: decode on the context stream, D2H on the copy stream
+adacom_status issue_window(adacom_scan_stream *s, uint64_t w) {
+	adacom_column *col = s->col;
+	adacom_ctx *ctx = col->ctx;
+	adacom_scan_stream::Win &win = s->wins[w % s->depth];
+	const uint64_t b = window_first(s, w), e = window_end(s, w);
+	const uint64_t rows = range_rows(col, b, e);
+	uint8_t *d_buf = s->d_ring + (w % s->depth) * s->win_bytes;
+	uint8_t *h_buf = s->h_ring + (w % s->depth) * s->win_bytes;
+	std::lock_guard<std::mutex> lock(ctx->mu);
+	CK(ctx, cudaSetDevice(ctx->device));
+	if (win.used) {
+		// the slot's previous copy must have left the device buffer before the kernel overwrites it
+		CK(ctx, cudaStreamWaitEvent(ctx->stream, win.arrived, 0));
+	}
+	if (rows) {
+		DecodeArgs a;
+		a.desc = col->d_desc;
+		a.jobs = col->d_tiles + col->tile_first[b];
+		a.n_jobs = col->tile_first[e] - col->tile_first[b];
+		a.raw = col->raw;
+		a.literal = (s->flags & ADACOM_LITERAL) ? 1 : 0;
+		a.out = d_buf;
+		a.out_row0 = col->h_desc[b].row_start;
+		LAUNCH(ctx, launch_decode(col->t, kModeFlat, a, ctx->sm_count, ctx->stream));
+	}
+	CK(ctx, cudaEventRecord(win.decoded, ctx->stream));
+	CK(ctx, cudaStreamWaitEvent(s->copy_stream, win.decoded, 0));
+	if (rows) {
+		CK(ctx, cudaMemcpyAsync(h_buf, d_buf, rows * col->t.size, cudaMemcpyDeviceToHost, s->copy_stream));
+	}
+	CK(ctx, cudaEventRecord(win.arrived, s->copy_stream));
+	win.index = w;
+	win.waited = false;
+	win.used = true;
+	return ADACOM_OK;
+}
+
+}  // namespace
+
+extern "C" adacom_status adacom_scan_stream_open(adacom_column *col, uint64_t seg_begin, uint64_t seg_end,
+                                                 uint32_t window_segments, uint32_t depth, int flags,
+                                                 adacom_scan_stream **out) {
+	if (!range_ok(col, seg_begin, seg_end) || !out || depth == 1) {
+		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_scan_stream_open: bad arguments");
+	}
+	*out = nullptr;
+	adacom_ctx *ctx = col->ctx;
+	adacom_scan_stream *s = new (std::nothrow) adacom_scan_stream();
+	if (!s) {
+		return fail(ctx, ADACOM_ERR_NOMEM, "out of host memory");
+	}
+	s->col = col;
+	s->seg_begin = seg_begin;
+	s->seg_end = seg_end;
+	s->win_segs = window_segments ? window_segments : 32;
+	s->depth = depth ? depth : 3;
+	s->flags = flags;
+	s->n_windows = (seg_end - seg_begin + s->win_segs - 1) / s->win_segs;
+	if (s->n_windows < s->depth) {
+		s->depth = s->n_windows < 2 ? 2 : (uint32_t)s->n_windows;
+	}
+	uint64_t max_rows = 0;
+	for (uint64_t w = 0; w < s->n_windows; w++) {
+		const uint64_t r = range_rows(col, window_first(s, w), window_end(s, w));
+		max_rows = r > max_rows ? r : max_rows;
+	}
+	s->win_bytes = ((size_t)max_rows * col->t.size + kArenaPad + 255) & ~(size_t)255;
+	s->wins.resize(s->depth);
+	auto bail = [&](cudaError_t e, const char *what) {
+		std::string msg = std::string(what) + ": " + cudaGetErrorString(e);
+		adacom_scan_stream_close(s);
+		return fail(ctx, e == cudaErrorMemoryAllocation ? ADACOM_ERR_NOMEM : ADACOM_ERR_CUDA, msg);
+	};
+	cudaError_t e;
+	const size_t need = s->win_bytes * s->depth;
+	std::vector<cudaEvent_t> events;
+	{
+		std::lock_guard<std::mutex> lock(ctx->mu);
+		if ((e = cudaSetDevice(ctx->device)) != cudaSuccess) {
+			return bail(e, "cudaSetDevice");
+		}
+		// a ring of a closed stream that is large enough (smallest such)
+		int best = -1;
+		for (size_t i = 0; i < ctx->ring_cache.size(); i++) {
+			if (ctx->ring_cache[i].bytes >= need && (best < 0 || ctx->ring_cache[i].bytes < ctx->ring_cache[best].bytes)) {
+				best = (int)i;
+			}
+		}
+		if (best >= 0) {
+			adacom_ctx::ScanRing r = std::move(ctx->ring_cache[best]);
+			ctx->ring_cache.erase(ctx->ring_cache.begin() + best);
+			s->d_ring = r.d_ring;
+			s->h_ring = r.h_ring;
+			s->ring_bytes = r.bytes;
+			s->copy_stream = r.copy_stream;
+			events = std::move(r.events);
+		}
+	}
+	if (!s->copy_stream) {
+		if ((e = cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) {
+			return bail(e, "cudaStreamCreateWithFlags");
+		}
+		if ((e = cudaMalloc((void **)&s->d_ring, need)) != cudaSuccess) {
+			return bail(e, "cudaMalloc(scan ring)");
+		}
+		if ((e = cudaHostAlloc((void **)&s->h_ring, need, cudaHostAllocDefault)) != cudaSuccess) {
+			return bail(e, "cudaHostAlloc(scan ring)");
+		}
+		s->ring_bytes = need;
+	}
+	for (auto &w : s->wins) {
+		for (cudaEvent_t *ev : {&w.decoded, &w.arrived}) {
+			if (!events.empty()) {
+				*ev = events.back();
+				events.pop_back();
+			} else if ((e = cudaEventCreateWithFlags(ev, cudaEventDisableTiming)) != cudaSuccess) {
+				return bail(e, "cudaEventCreateWithFlags");
+			}
+		}
+	}
+	for (auto ev : events) {
+		cudaEventDestroy(ev);
+	}
+	// run ahead right away: the first depth-1 windows are in flight before the first pull
+	for (uint64_t w = 0; w + 1 < s->depth && w < s->n_windows; w++) {
+		adacom_status st = issue_window(s, w);
+		if (st != ADACOM_OK) {
+			adacom_scan_stream_close(s);
+			return st;
+		}
+	}
+	*out = s;
+	return ADACOM_OK;
+}
+
+extern "C" adacom_status adacom_scan_stream_segment(adacom_scan_stream *s, uint64_t seg, const void **values,
+                                                    uint64_t *count) {
+	if (!s || !values || seg < s->seg_begin || seg >= s->seg_end) {
+		return fail(s ? s->col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_scan_stream_segment: segment outside the stream");
+	}
+	adacom_column *col = s->col;
+	adacom_ctx *ctx = col->ctx;
+	const uint64_t w = (seg - s->seg_begin) / s->win_segs;
+	adacom_scan_stream::Win *win = &s->wins[w % s->depth];
+	if (win->index != w) {
+		// not resident and not in flight: (re)start the pipeline here
+		adacom_status st = issue_window(s, w);
+		if (st != ADACOM_OK) {
+			return st;
+		}
+	}
+	if (!win->waited) {
+		// first touch of this window: keep the ring full -- windows w+1 .. w+depth-2 (the slot of w-1 may still be
+		// referenced by the consumer's last vector and is left alone)
+		for (uint64_t k = w + 1; k + 1 < w + s->depth && k < s->n_windows; k++) {
+			if (s->wins[k % s->depth].index != k) {
+				adacom_status st = issue_window(s, k);
+				if (st != ADACOM_OK) {
+					return st;
+				}
+			}
+		}
+		CK(ctx, cudaEventSynchronize(win->arrived));
+		win->waited = true;
+	}
+	const uint64_t row0 = col->h_desc[window_first(s, w)].row_start;
+	*values = s->h_ring + (w % s->depth) * s->win_bytes + (col->h_desc[seg].row_start - row0) * col->t.size;
+	if (count) {
+		*count = col->h_desc[seg].count;
+	}
+	return ADACOM_OK;
+}
+
+extern "C" void adacom_scan_stream_close(adacom_scan_stream *s) {
+	if (!s) {
+		return;
+	}
+	adacom_ctx *ctx = s->col->ctx;
+	{
+		std::lock_guard<std::mutex> lock(ctx->mu);
+		cudaSetDevice(ctx->device);
+	}
+	if (s->copy_stream) {
+		cudaStreamSynchronize(s->copy_stream);
+	}
+	if (s->copy_stream && s->d_ring && s->h_ring) {
+		// the decode kernels of this stream's windows sit on the context stream: by the time a later stream reuses
+		// the ring its first kernel is ordered behind them there, and the copies have drained above
+		adacom_ctx::ScanRing r;
+		r.d_ring = s->d_ring;
+		r.h_ring = s->h_ring;
+		r.bytes = s->ring_bytes;
+		r.copy_stream = s->copy_stream;
+		for (auto &w : s->wins) {
+			for (cudaEvent_t ev : {w.decoded, w.arrived}) {
+				if (ev) {
+					r.events.push_back(ev);
+				}
+			}
+		}
+		std::lock_guard<std::mutex> lock(ctx->mu);
+		if (ctx->ring_cache.size() < 16) {
+			ctx->ring_cache.push_back(std::move(r));
+			delete s;
+			return;
+		}
+	}
+	for (auto &w : s->wins) {
+		if (w.arrived) {
+			cudaEventDestroy(w.arrived);
+		}
+		if (w.decoded) {
+			cudaEventDestroy(w.decoded);
+		}
+	}
+	if (s->h_ring) {
+		cudaFreeHost(s->h_ring);
+	}
+	if (s->d_ring) {
+		cudaFree(s->d_ring);
+	}
+	if (s->copy_stream) {
+		cudaStreamDestroy(s->copy_stream);
+	}
+	delete s;
 }

@@ -224,10 +224,24 @@ struct CodecSeg {
 	uint32_t first_run;     // RLE: index of the segment's first run in the run_start array
 	uint32_t reserved;
 };
+// One record per (segment, 2048-value group), resolved ONCE when the column is created (like the tile table of the
+// succinct codec): the scan kernels start from it instead of walking job -> segment -> metadata entry -> group header,
+// four dependent global loads per 2048 values.
+struct CodecGroup {
+	uint64_t payload;       // bitpacking: byte offset of the group's packed payload in the image arena; RLE: of the run values
+	uint64_t out_row;       // column row of the group's first value
+	uint64_t frame, constant, delta_offset;  // bitpacking group header (bitpacking.cpp:576-632)
+	uint32_t mode, width;   // bitpacking
+	uint32_t count;         // values in the group
+	uint32_t run_lo, run_hi;  // RLE: run_start indices of the run holding the group's first row / the next group's first row
+	uint32_t first;         // RLE: row of the group's first value inside its segment
+};
+static_assert(sizeof(CodecGroup) == 64, "CodecGroup is one 64-byte record");
 struct CodecArgs {
 	const uint8_t *images = nullptr;
 	const CodecSeg *segs = nullptr;
 	const Job *jobs = nullptr;      // (segment, 2048-value group) -- or (segment, tile of 2048 runs) for the RLE SUM
+	const CodecGroup *groups = nullptr;  // records of the same groups (same slice as jobs; not for the RLE SUM tiles)
 	uint32_t n_jobs = 0;
 	void *out = nullptr;            // decode: flat T values, out[row - out_row0]; fetch: one value per query
 	uint64_t out_row0 = 0;
@@ -241,6 +255,8 @@ cudaError_t launch_codec_scan(TypeInfo t, int codec, int mode, const CodecArgs &
 cudaError_t launch_codec_fetch(TypeInfo t, int codec, const CodecArgs &args, const uint32_t *seg_idx,
                                const uint32_t *row_in_seg, uint64_t n, cudaStream_t stream);
 cudaError_t launch_rle_run_starts(const CodecArgs &args, uint32_t seg_b, uint32_t n_segs, int sm_count, cudaStream_t stream);
+// fills groups_out[j] for the jobs of args (after launch_rle_run_starts for RLE)
+cudaError_t launch_codec_groups(TypeInfo t, int codec, const CodecArgs &args, CodecGroup *groups_out, cudaStream_t stream);
 
 // the same operator, warp per 2048-value tile (static tile table), lane per 32-row group (pred32); handles every kind of
 // segment (field-comparable ones in the field domain, the others per value); wmax: widest live payload of the column

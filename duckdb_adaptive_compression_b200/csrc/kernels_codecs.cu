@@ -15,9 +15,13 @@
 //   RLE         src/storage/compression/rle.cpp: [u64 offset of the counts | T values[runs] | u16 counts[runs]] (:170-215);
 //               RLEScanPartial / RLEFetchRow :298-331.
 //
-// One CTA works on one metadata group (bitpacking) or one 2048-row tile (RLE) at a time: the group's payload is staged in
-// shared memory with aligned 4-byte loads (the misalignment becomes a bit offset), lanes take consecutive values, so the
-// stores are coalesced; DELTA_FOR runs a block-wide prefix sum.  Fused SUM never materialises the values.
+// One CTA works on one metadata group (bitpacking) or one 2048-row tile (RLE) at a time, starting from the group's
+// 64-byte CodecGroup record (resolved once per column by codec_groups_kernel, so a scan has no dependent metadata
+// loads).  Bitpacking: the payload is staged in double-buffered shared memory with aligned 4-byte loads (the
+// misalignment becomes a bit offset; one barrier per group), lanes take consecutive values, so the stores are
+// coalesced; DELTA_FOR runs a block-wide prefix sum.  RLE: the heads of the runs that start inside the tile are
+// scattered into a 2048-entry shared array and a block-wide max-scan turns them into the run of every row -- no
+// per-row binary search.  Fused SUM never materialises the values.
 #include "adacom_kernels.cuh"
 
 namespace adacom {
@@ -87,33 +91,78 @@ __device__ __forceinline__ uint64_t trunc_T(uint64_t v) {
 	return S == 8 ? v : (v & ((1ull << (8 * (S & 7))) - 1ull));
 }
 
+// records of the jobs (one thread per group): bitpacking header fields / RLE run range of the tile
+template <int S>
+__global__ void __launch_bounds__(kCodecThreads) codec_groups_kernel(CodecArgs a, CodecGroup *groups, int codec) {
+	const uint32_t j = blockIdx.x * kCodecThreads + threadIdx.x;
+	if (j >= a.n_jobs) {
+		return;
+	}
+	const Job job = a.jobs[j];
+	const CodecSeg seg = a.segs[job.seg];
+	const uint8_t *img = a.images + seg.image_offset;
+	CodecGroup g;
+	g.frame = g.constant = g.delta_offset = 0;
+	g.mode = g.width = g.run_lo = g.run_hi = 0;
+	g.first = job.k * kGroupValues;
+	g.out_row = seg.row_start + (uint64_t)job.k * kGroupValues;
+	g.count = g.first < seg.count ? min(kGroupValues, seg.count - g.first) : 0u;
+	if (codec == 0) {
+		const GroupHeader h = read_group_header<S>(img, seg.count, job.k);
+		g.payload = seg.image_offset + h.data_off;
+		g.frame = h.frame;
+		g.constant = h.constant;
+		g.delta_offset = h.delta_offset;
+		g.mode = h.mode;
+		g.width = h.width;
+	} else {
+		const uint64_t counts_off = *(const uint64_t *)img;
+		const uint32_t n_runs = (seg.bytes - (uint32_t)counts_off) / 2u;
+		const uint32_t *starts = a.run_start + seg.first_run;
+		g.payload = seg.image_offset + 8u;
+		auto find = [&](uint32_t row) {
+			uint32_t lo = 0, hi = n_runs;  // last run whose start <= row
+			while (hi - lo > 1) {
+				const uint32_t mid = (lo + hi) >> 1;
+				if (starts[mid] <= row) {
+					lo = mid;
+				} else {
+					hi = mid;
+				}
+			}
+			return lo;
+		};
+		if (g.count) {
+			g.run_lo = seg.first_run + find(g.first);
+			g.run_hi = seg.first_run + find(g.first + g.count - 1u);
+		}
+	}
+	groups[j] = g;
+}
+
 // MODE 0: decode into out[(row_start + i) - out_row0]; MODE 1: fused SUM/COUNT
 template <int S, bool SIGNED, int MODE>
 __global__ void __launch_bounds__(kCodecThreads) bitpacking_groups_kernel(CodecArgs a) {
 	using T = typename UIntOf<S>::type;
-	__shared__ __align__(16) uint32_t stage[kGroupValues * 64 / 32 + 8];
-	__shared__ GroupHeader hdr;
+	constexpr uint32_t kStageWords = kGroupValues * 8 * S / 32 + 8;  // widest payload of the type + the funnel's look-ahead
+	__shared__ __align__(16) uint32_t stage2[2][kStageWords];
 	__shared__ uint64_t warp_tot[kCodecThreads / 32];
 	__shared__ uint64_t red[96];
 	const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
 	Acc96 acc;
 	uint32_t n_rows = 0;
-	for (uint32_t j = blockIdx.x; j < a.n_jobs; j += gridDim.x) {
-		const Job job = a.jobs[j];
-		const CodecSeg seg = a.segs[job.seg];
-		const uint8_t *img = a.images + seg.image_offset;
-		__syncthreads();  // the previous group has been consumed
-		if (tid == 0) {
-			hdr = read_group_header<S>(img, seg.count, job.k);
-		}
-		__syncthreads();
-		const GroupHeader h = hdr;
-		const uint32_t cnt = h.count, w = h.width;
-		T *out = MODE == 0 ? (T *)a.out + (seg.row_start + (uint64_t)job.k * kGroupValues - a.out_row0) : nullptr;
+	uint32_t parity = 0;
+	for (uint32_t j = blockIdx.x; j < a.n_jobs; j += gridDim.x, parity ^= 1u) {
+		const CodecGroup *gp = a.groups + j;
+		const uint32_t mode = __ldg(&gp->mode), w = __ldg(&gp->width), cnt = __ldg(&gp->count);
+		const uint64_t frame = __ldg(&gp->frame);
+		T *out = MODE == 0 ? (T *)a.out + (__ldg(&gp->out_row) - a.out_row0) : nullptr;
+		uint32_t *stage = stage2[parity];
 		uint32_t mis_bits = 0;
-		if (h.mode == kBpFor || h.mode == kBpDeltaFor) {
-			// stage ceil(cnt / 32) * 4 * w payload bytes; the source is only sizeof(T)-aligned
-			const uint8_t *src = img + h.data_off;
+		if (mode == kBpFor || mode == kBpDeltaFor) {
+			// stage ceil(cnt / 32) * 4 * w payload bytes; the source is only sizeof(T)-aligned.  The other buffer may
+			// still be read by slower threads (they are at most one group behind: one barrier per group)
+			const uint8_t *src = a.images + __ldg(&gp->payload);
 			const uint32_t mis = (uint32_t)((uintptr_t)src & 3u);
 			const uint32_t *src4 = (const uint32_t *)(src - mis);
 			const uint32_t n_words = (mis + ((cnt + 31u) / 32u) * 4u * w + 3u) / 4u;
@@ -124,16 +173,16 @@ __global__ void __launch_bounds__(kCodecThreads) bitpacking_groups_kernel(CodecA
 				stage[n_words + tid] = 0u;  // the funnel's look-ahead words
 			}
 			mis_bits = mis * 8u;
-			__syncthreads();
 		}
-		if (h.mode == kBpDeltaFor) {
+		__syncthreads();
+		if (mode == kBpDeltaFor) {
 			// blocked: thread t owns values [8t, 8t + 8); running sum of (field + for) in T arithmetic
 			uint64_t d[8];
 			uint64_t run = 0;
 #pragma unroll
 			for (int k = 0; k < 8; k++) {
 				const uint32_t i = tid * 8u + k;
-				const uint64_t f = i < cnt ? field_at(stage, mis_bits + i * w, w) + h.frame : 0ull;
+				const uint64_t f = i < cnt ? field_at(stage, mis_bits + i * w, w) + frame : 0ull;
 				run += f;
 				d[k] = run;
 			}
@@ -149,7 +198,7 @@ __global__ void __launch_bounds__(kCodecThreads) bitpacking_groups_kernel(CodecA
 				warp_tot[warp] = incl;
 			}
 			__syncthreads();
-			uint64_t base = h.delta_offset + incl - run;
+			uint64_t base = __ldg(&gp->delta_offset) + incl - run;
 			for (uint32_t wi = 0; wi < warp; wi++) {
 				base += warp_tot[wi];
 			}
@@ -166,18 +215,24 @@ __global__ void __launch_bounds__(kCodecThreads) bitpacking_groups_kernel(CodecA
 					}
 				}
 			}
-		} else {
+		} else if (mode == kBpFor) {
+#pragma unroll 4
 			for (uint32_t i = tid; i < cnt; i += kCodecThreads) {
-				uint64_t v;
-				if (h.mode == kBpFor) {
-					v = field_at(stage, mis_bits + i * w, w) + h.frame;
-				} else if (h.mode == kBpConstant) {
-					v = h.constant;
+				const uint64_t v = trunc_T<S>(field_at(stage, mis_bits + i * w, w) + frame);
+				if (MODE == 0) {
+					out[i] = (T)v;
 				} else {
-					// (group_offset + i) * constant + frame in idx_t arithmetic, truncated to T (bitpacking.cpp:757-760)
-					v = (uint64_t)i * extend_low<S, SIGNED>(h.constant) + extend_low<S, SIGNED>(h.frame);
+					acc.add<SIGNED>(extend_low<S, SIGNED>(v));
+					n_rows++;
 				}
-				v = trunc_T<S>(v);
+			}
+		} else {
+			const uint64_t constant = __ldg(&gp->constant);
+			for (uint32_t i = tid; i < cnt; i += kCodecThreads) {
+				// CONSTANT, or (group_offset + i) * constant + frame in idx_t arithmetic, truncated to T (bitpacking.cpp:757-760)
+				const uint64_t v = trunc_T<S>(mode == kBpConstant ? constant
+				                                                  : (uint64_t)i * extend_low<S, SIGNED>(constant) +
+				                                                        extend_low<S, SIGNED>(frame));
 				if (MODE == 0) {
 					out[i] = (T)v;
 				} else {
@@ -312,7 +367,82 @@ __device__ __forceinline__ uint32_t rle_find_run(const uint32_t *starts, uint32_
 	return lo;
 }
 
-// MODE 0: decode 2048-row tiles; MODE 1: SUM = sum_runs value * length (job = 2048 runs of a segment)
+// decode 2048-row tiles: the heads of the runs that start inside the tile are scattered to their row, an inclusive
+// max-scan over the 2048 rows gives every row its run (RLEScanPartial, rle.cpp:298-318, without the per-row walk)
+template <int S>
+__global__ void __launch_bounds__(kCodecThreads) rle_decode_kernel(CodecArgs a) {
+	using T = typename UIntOf<S>::type;
+	__shared__ uint32_t head[kGroupValues];  // run (relative to the tile's first run) that starts at this row, else 0
+	__shared__ uint32_t warp_max[kCodecThreads / 32];
+	const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+	for (uint32_t j = blockIdx.x; j < a.n_jobs; j += gridDim.x) {
+		const CodecGroup *gp = a.groups + j;
+		const uint32_t cnt = __ldg(&gp->count);
+		if (cnt == 0) {
+			continue;
+		}
+		const uint32_t run_lo = __ldg(&gp->run_lo), run_hi = __ldg(&gp->run_hi), first = __ldg(&gp->first);
+		const T *values = (const T *)(a.images + __ldg(&gp->payload));
+		// run_start is indexed column-wide, the values segment-wide: the segment's first run index is run_lo - (its
+		// position inside the segment); both advance together, so work with the difference
+		const Job job = a.jobs[j];
+		const uint32_t seg_first_run = __ldg(&a.segs[job.seg].first_run);
+		T *out = (T *)a.out + (__ldg(&gp->out_row) - a.out_row0);
+		__syncthreads();  // the previous tile's head[] has been consumed
+#pragma unroll
+		for (uint32_t i = tid; i < kGroupValues; i += kCodecThreads) {
+			head[i] = 0u;
+		}
+		__syncthreads();
+		for (uint32_t r = run_lo + 1u + tid; r <= run_hi; r += kCodecThreads) {
+			const uint32_t pos = __ldg(a.run_start + r) - first;  // > 0: run_lo is the last run that starts at or before `first`
+			if (pos < cnt) {
+				atomicMax(&head[pos], r - run_lo);  // zero-length runs share a row: the last one holds it
+			}
+		}
+		__syncthreads();
+		// thread t owns rows [8t, 8t + 8)
+		uint32_t m[8];
+		uint32_t run = 0;
+#pragma unroll
+		for (int k = 0; k < 8; k++) {
+			run = max(run, head[tid * 8u + k]);
+			m[k] = run;
+		}
+		uint32_t incl = run;
+#pragma unroll
+		for (int s = 1; s < 32; s <<= 1) {
+			const uint32_t o = __shfl_up_sync(0xffffffffu, incl, s);
+			if (lane >= (uint32_t)s) {
+				incl = max(incl, o);
+			}
+		}
+		if (lane == 31) {
+			warp_max[warp] = incl;
+		}
+		uint32_t before = __shfl_up_sync(0xffffffffu, incl, 1);
+		if (lane == 0) {
+			before = 0u;
+		}
+		__syncthreads();
+		for (uint32_t wi = 0; wi < warp; wi++) {
+			before = max(before, warp_max[wi]);
+		}
+		// the run index of every row goes back to shared memory so that the stores are row-strided (coalesced)
+#pragma unroll
+		for (int k = 0; k < 8; k++) {
+			head[tid * 8u + k] = max(before, m[k]);
+		}
+		__syncthreads();
+		const T *tile_values = values + (run_lo - seg_first_run);
+#pragma unroll 4
+		for (uint32_t i = tid; i < cnt; i += kCodecThreads) {
+			out[i] = __ldg(tile_values + head[i]);
+		}
+	}
+}
+
+// SUM = sum_runs value * length (job = 2048 runs of a segment)
 template <int S, bool SIGNED, int MODE>
 __global__ void __launch_bounds__(kCodecThreads) rle_kernel(CodecArgs a) {
 	using T = typename UIntOf<S>::type;
@@ -326,18 +456,7 @@ __global__ void __launch_bounds__(kCodecThreads) rle_kernel(CodecArgs a) {
 		const uint64_t counts_off = *(const uint64_t *)img;
 		const uint32_t n_runs = (seg.bytes - (uint32_t)counts_off) / 2u;
 		const T *values = (const T *)(img + 8);
-		const uint32_t *starts = a.run_start + seg.first_run;
-		if (MODE == 0) {
-			const uint32_t first = job.k * kGroupValues;
-			if (first >= seg.count) {
-				continue;
-			}
-			const uint32_t cnt = min(kGroupValues, seg.count - first);
-			T *out = (T *)a.out + (seg.row_start + first - a.out_row0);
-			for (uint32_t i = tid; i < cnt; i += kCodecThreads) {
-				out[i] = __ldg(values + rle_find_run(starts, n_runs, first + i));
-			}
-		} else {
+		{
 			const uint16_t *counts = (const uint16_t *)(img + counts_off);
 			const uint32_t first = job.k * kGroupValues;
 			for (uint32_t k = first + tid; k < min(n_runs, first + kGroupValues); k += kCodecThreads) {
@@ -354,9 +473,7 @@ __global__ void __launch_bounds__(kCodecThreads) rle_kernel(CodecArgs a) {
 			}
 		}
 	}
-	if (MODE == 1) {
-		block_reduce_agg(lo, hi, rows, red, a.agg);
-	}
+	block_reduce_agg(lo, hi, rows, red, a.agg);
 }
 
 template <int S, bool SIGNED>
@@ -384,11 +501,17 @@ cudaError_t launch_typed(int codec, int mode, const CodecArgs &a, uint32_t grid,
 		}
 	} else {
 		if (mode == 0) {
-			rle_kernel<S, SIGNED, 0><<<grid, kCodecThreads, 0, stream>>>(a);
+			rle_decode_kernel<S><<<grid, kCodecThreads, 0, stream>>>(a);
 		} else {
 			rle_kernel<S, SIGNED, 1><<<grid, kCodecThreads, 0, stream>>>(a);
 		}
 	}
+	return cudaGetLastError();
+}
+
+template <int S, bool SIGNED>
+cudaError_t groups_typed(int codec, const CodecArgs &a, CodecGroup *groups, cudaStream_t stream) {
+	codec_groups_kernel<S><<<(a.n_jobs + kCodecThreads - 1) / kCodecThreads, kCodecThreads, 0, stream>>>(a, groups, codec);
 	return cudaGetLastError();
 }
 
@@ -424,9 +547,19 @@ cudaError_t launch_codec_scan(TypeInfo t, int codec, int mode, const CodecArgs &
 	if (a.n_jobs == 0) {
 		return cudaSuccess;
 	}
-	const uint32_t resident = (uint32_t)sm_count * 4u;
+	// 2048 values per CTA iteration: the tiles are latency-bound, so as many CTAs as fit (8 x 256 threads per SM; the
+	// 8-byte bitpacking stage is 2 x 16 KiB, six of those fit)
+	const uint32_t per_sm = (codec == 0 && t.size == 8) ? 6u : 8u;
+	const uint32_t resident = (uint32_t)sm_count * per_sm;
 	const uint32_t grid = a.n_jobs < resident ? a.n_jobs : resident;
 	CODEC_DISPATCH(launch_typed, codec, mode, a, grid, stream)
+}
+
+cudaError_t launch_codec_groups(TypeInfo t, int codec, const CodecArgs &a, CodecGroup *groups, cudaStream_t stream) {
+	if (a.n_jobs == 0) {
+		return cudaSuccess;
+	}
+	CODEC_DISPATCH(groups_typed, codec, a, groups, stream)
 }
 
 cudaError_t launch_codec_fetch(TypeInfo t, int codec, const CodecArgs &a, const uint32_t *seg_idx, const uint32_t *row_in_seg,

@@ -73,10 +73,15 @@ struct Vector {
 	PhysicalType type;
 	VectorType vector_type = VectorType::FLAT_VECTOR;
 	std::vector<uint8_t> buffer;
+	data_ptr_t external = nullptr;  // zero-copy view set by FlatVector::SetData (cleared by the next pull)
 };
 struct FlatVector {
 	static data_ptr_t GetData(Vector &v) {
-		return v.buffer.data();
+		return v.external ? v.external : v.buffer.data();
+	}
+	//! src/include/duckdb/common/types/vector.hpp: FlatVector::SetData -- the vector points at caller-owned memory
+	static void SetData(Vector &v, data_ptr_t data) {
+		v.external = data;
 	}
 };
 struct SelectionVector {
@@ -120,6 +125,10 @@ struct ColumnScanState {  // src/include/duckdb/storage/table/scan_state.hpp:43-
 	idx_t row_index = 0;
 	idx_t internal_index = 0;
 	unique_ptr<SegmentScanState> scan_state;
+	bool initialized = false;
+	idx_t version = 0;
+	//! scan states of the segments a vector has just left: kept alive until the next ScanVector (zero-copy vectors)
+	std::vector<unique_ptr<SegmentScanState>> previous_states;
 };
 struct ColumnFetchState {};
 struct ColumnAppendState {
@@ -183,7 +192,8 @@ struct DBConfig {  // src/include/duckdb/main/config.hpp:189-197 (same names, sa
 	bool succinct_extract_prefix_enabled = true;
 	bool succinct_padded_to_next_byte_enabled = false;
 	bool adaptive_succinct_compression_enabled = false;
-	int gpu_device = 0;                      // B200 ordinal this database instance is pinned to
+	int gpu_device = 0;                      // B200 ordinal this database instance is pinned to (first device)
+	int gpu_devices = 1;                     // number of GPUs the row groups are dealt over (gpu_device .. +n-1)
 	double compression_rate = 0.90;          // column_segment_catalog.cpp:65
 	double background_interval_s = 10.0;     // column_segment_catalog.cpp:70
 	CompressionFunction *GetCompressionFunction(CompressionType type, PhysicalType data_type);  // registry, locked
@@ -206,6 +216,16 @@ private:
 	std::atomic<int64_t> data_size {0};
 };
 
+class CompactableSegment;
+// The segments of one column live in one device column, so the policy's per-epoch subsets become ONE launch set each
+// (adacom_encode_list / adacom_uncompact_list) instead of one launch set per segment.  ColumnData implements it.
+class SegmentBatchOwner {
+public:
+	virtual ~SegmentBatchOwner() = default;
+	virtual void CompactMany(const std::vector<CompactableSegment *> &segments) = 0;
+	virtual void UncompactMany(const std::vector<CompactableSegment *> &segments) = 0;
+};
+
 // Anything the access-frequency policy can compact: ColumnSegment implements it, CPU tests use a fake.
 class CompactableSegment {
 public:
@@ -214,6 +234,18 @@ public:
 	virtual void Uncompact() = 0;
 	virtual idx_t GetDataSize() const = 0;
 	virtual bool IsDataSegment() const = 0;
+	//! non-null: Compact()/Uncompact() decisions of an epoch for this segment are handed to the owner in one batch
+	virtual SegmentBatchOwner *BatchOwner() const {
+		return nullptr;
+	}
+	//! GPU this segment's payload lives on (device-sharded catalog: per-device accounting); -1 = host only
+	virtual int Device() const {
+		return -1;
+	}
+	//! reads since the last epoch.  The counter lives in the segment so that AddReadAccess on the scan path (one call
+	//! per 2048-value pull, from every scan thread) is one relaxed atomic increment instead of a catalog-wide lock
+	std::atomic<idx_t> catalog_reads {0};
+	std::atomic<bool> catalog_registered {false};
 };
 
 struct AccessStatistics {
@@ -235,6 +267,8 @@ public:
 	}
 	void CompactAllSegments();
 	size_t GetTotalDataSize();
+	//! the same sum split by the GPU the segments live on (key -1: segments without a device payload)
+	std::unordered_map<int, size_t> GetDataSizePerDevice();
 	//! One iteration of CompressLowestKSegments' loop body (column_segment_catalog.cpp:71-112): sort by
 	//! reads, Compact() the coldest `compression_rate` share, Uncompact() the rest, zero the counters.
 	//! Returns {compacted, uncompacted}.
@@ -246,7 +280,7 @@ private:
 	void CompressLowestKSegments();
 	std::mutex lock;
 	std::unordered_map<CompactableSegment *, AccessStatistics> statistics;
-	idx_t event_counter = 0;
+	std::atomic<idx_t> event_counter {0};
 	bool background_compaction_enabled = false;
 	double compression_rate;
 	double interval_s;
@@ -264,7 +298,18 @@ public:
 	ColumnSegmentCatalog column_segment_catalog;
 	adacom_ctx *gpu = nullptr;  // created lazily by Gpu(); throws InternalException when no B200 is usable
 	adacom_ctx *Gpu();
+	//! context of GPU `device` (config.gpu_device when < 0); one per device, created on first use.  Columns are dealt
+	//! over config.gpu_devices GPUs by ColumnData (row group g -> device g mod G)
+	adacom_ctx *Gpu(int device);
+	//! owner of row group g: gpu_device + g mod gpu_devices (segments never span row groups, so nothing else moves)
+	int DeviceForRowGroup(idx_t row_group) const {
+		return config.gpu_device + (int)(row_group % (idx_t)(config.gpu_devices > 0 ? config.gpu_devices : 1));
+	}
 	[[noreturn]] void Throw(const char *what);
+
+private:
+	std::mutex gpu_lock;
+	std::unordered_map<int, adacom_ctx *> gpus;
 };
 
 // ---- ColumnSegment ----------------------------------------------------------------------------------------
@@ -305,6 +350,8 @@ public:
 	bool IsBitCompressed() const {
 		return compacted;
 	}
+	SegmentBatchOwner *BatchOwner() const override;
+	int Device() const override;
 
 	DatabaseInstance &db;
 	PhysicalType type;
@@ -323,13 +370,20 @@ public:
 	bool force_reinitializing_scan_state = false;
 	std::mutex bit_compression_lock;
 
-	// device side: one single-segment column of the C ABI; values are staged here until the first Compact()
+	// device side: segment `gpu_index` of `gpu_column`.  A lone segment owns a one-segment column of the C ABI; a
+	// segment of a ColumnData is a member of the column's shared device column (one launch set per batch, one scan
+	// stream per scan).  Values are staged on the host until the first Compact().
 	adacom_column *gpu_column = nullptr;
+	uint64_t gpu_index = 0;
+	bool owns_gpu_column = true;
+	ColumnData *column_data = nullptr;
+	int device = -1;                      // GPU ordinal of gpu_column (-1: default device of the database)
 	std::vector<uint8_t> staging;         // slot-width host image of the appended values (== the raw arena)
 	std::vector<uint64_t> staging_validity;
 	bool staging_has_nulls = false;
 	idx_t uploaded = 0;                   // values already copied to the device
 	uint64_t epoch = 0;                   // bumped by Compact/Uncompact: scan states re-initialise
+	idx_t compacted_size = 0;             // size_in_bytes of the compacted image (GetDataSize without a device call)
 
 private:
 	ColumnSegment(DatabaseInstance &db, PhysicalType type, idx_t start, idx_t segment_size, CompressionFunction *function,
@@ -337,9 +391,68 @@ private:
 	void Scan(ColumnScanState &state, idx_t scan_count, Vector &result);
 	void ScanPartial(ColumnScanState &state, idx_t scan_count, Vector &result, idx_t result_offset);
 	void EnsureDeviceColumn();
+	void EnsureStaging();
+	void DetachFromBatch();
 	void Upload();
+	int CompactFlags() const;
+	void FinishCompact(idx_t size_before, const adacom_segment_meta &m);
+	void FinishUncompact(idx_t compressed_size);
 	adacom_segment_meta Meta() const;
 	friend struct SuccinctGpuFun;
+	friend class ColumnData;
+};
+
+// ---- ColumnData: the owner of a column's segments (src/storage/table/column_data.cpp) ---------------------
+// Same entry points as the reference for the succinct path: AppendData (:249-270), InitializeScan[WithOffset]
+// (:73-89), ScanVector (:92-139), FetchRow (:304-315).  What is new is below the segments: all sealed segments of the
+// column share ONE device column, so
+//   * compaction of many segments is one analyze + one encode launch set (CompactPending / CompactMany),
+//   * a scan is served by one adacom_scan_stream that runs ahead of the 2048-value pulls across segment borders,
+//   * the column sits on one GPU (`device`), chosen by the caller: row group g -> device g mod G.
+class ColumnData : public SegmentBatchOwner {
+public:
+	ColumnData(DatabaseInstance &db, PhysicalType type, idx_t start_row = 0, int device = -1);
+	~ColumnData() override;
+
+	void InitializeAppend(ColumnAppendState &state);
+	void AppendData(ColumnAppendState &state, UnifiedVectorFormat &vdata, idx_t count);
+	void InitializeScan(ColumnScanState &state);
+	void InitializeScanWithOffset(ColumnScanState &state, idx_t row_idx);
+	idx_t ScanVector(ColumnScanState &state, Vector &result, idx_t remaining);
+	void FetchRow(ColumnFetchState &state, row_t row_id, Vector &result, idx_t result_idx);
+	//! batched form of FetchRow for index joins: one adacom_fetch_rows launch for all row ids
+	void FetchRows(const row_t *row_ids, idx_t count, Vector &result);
+	idx_t GetMaxEntry() const;
+	ColumnSegment *GetSegment(idx_t row_idx) const;
+
+	//! move every sealed (full or finalized) segment that is still host-staged into the shared device column and
+	//! compact them with one analyze + one encode; called by the append path every `pending_limit` segments, by
+	//! the first scan that meets a pending segment, and by ColumnSegmentCatalog::CompactAllSegments
+	void CompactPending(bool include_last = true);
+	//! Append filled a segment: the batch is flushed once `pending_limit` sealed segments wait on the host
+	void SegmentSealed();
+	void CompactMany(const std::vector<CompactableSegment *> &segments) override;
+	void UncompactMany(const std::vector<CompactableSegment *> &segments) override;
+
+	DatabaseInstance &db;
+	PhysicalType type;
+	idx_t start;
+	int device;
+	idx_t version = 0;
+	idx_t pending_limit = 64;  // sealed segments staged on the host before a batch is uploaded (16 MiB)
+	std::vector<unique_ptr<ColumnSegment>> segments;
+
+	//! shared device columns of this ColumnData: the members of batch k are segments whose gpu_column == col
+	struct Batch {
+		adacom_column *col = nullptr;
+		idx_t n = 0;
+		uint64_t *validity = nullptr;  // pinned: validity bits of the batch's rows when a member has NULLs
+	};
+	std::vector<Batch> batches;
+	std::mutex lock;
+
+private:
+	void AppendTransientSegment(idx_t start_row);
 };
 
 adacom_ptype ToAdacomType(PhysicalType type);

@@ -1,0 +1,433 @@
+// column_data.cpp -- ColumnData re-hosted on the GPU codec: the owner of a column's segments.
+//
+// Entry points and control flow follow the reference (paths relative to its repository root):
+//   ColumnData::InitializeScan / InitializeScanWithOffset .. src/storage/table/column_data.cpp:73-89
+//   ColumnData::ScanVector .................................. column_data.cpp:92-139
+//   ColumnData::InitializeAppend / AppendData ............... column_data.cpp:222-270
+//   ColumnData::FetchRow ..................................... column_data.cpp:304-315
+// What the reference does per segment on the CPU (Compact() of each full segment, a deep copy + decode per 2048-value
+// pull, one FetchRow per row id) is batched here below the same interface: the sealed segments of the column share one
+// device column, so compaction is one analyze + one encode launch set per batch, a scan is one decode launch per
+// 32 segments running ahead of the pulls in a pinned ring, and the policy's per-epoch subsets are one launch set each.
+#include "adacom_host.hpp"
+
+#include <algorithm>
+#include <map>
+#include <vector>
+
+namespace adacom_host {
+
+#define GPU_CHECK(db, call)              \
+	do {                                 \
+		adacom_status st__ = (call);     \
+		if (st__ == ADACOM_ERR_NOMEM) {  \
+			throw std::bad_alloc();      \
+		}                                \
+		if (st__ != ADACOM_OK) {         \
+			(db).Throw(#call);           \
+		}                                \
+	} while (0)
+
+ColumnData::ColumnData(DatabaseInstance &db_p, PhysicalType type_p, idx_t start_row, int device_p)
+    : db(db_p), type(type_p), start(start_row), device(device_p < 0 ? db_p.config.gpu_device : device_p) {
+}
+
+ColumnData::~ColumnData() {
+	segments.clear();  // members only drop their reference; the shared device columns go last
+	for (auto &b : batches) {
+		if (b.col) {
+			adacom_column_destroy(b.col);
+		}
+		if (b.validity) {
+			adacom_host_free(db.Gpu(device), b.validity);
+		}
+	}
+}
+
+void ColumnData::AppendTransientSegment(idx_t start_row) {
+	auto segment = ColumnSegment::CreateTransientSegment(db, type, start_row);
+	segment->column_data = this;
+	segment->device = device;
+	segments.push_back(std::move(segment));
+	version++;
+}
+
+void ColumnData::InitializeAppend(ColumnAppendState &state) {
+	std::lock_guard<std::mutex> guard(lock);
+	if (segments.empty()) {
+		AppendTransientSegment(start);
+	}
+	segments.back()->InitializeAppend(state);
+}
+
+void ColumnData::AppendData(ColumnAppendState &state, UnifiedVectorFormat &vdata, idx_t count) {
+	idx_t offset = 0;
+	while (true) {
+		ColumnSegment *current = segments.back().get();
+		idx_t copied_elements = current->Append(state, vdata, offset, count);
+		if (copied_elements == count) {
+			break;
+		}
+		{
+			std::lock_guard<std::mutex> guard(lock);
+			AppendTransientSegment(current->start + current->count);
+			segments.back()->InitializeAppend(state);
+		}
+		offset += copied_elements;
+		count -= copied_elements;
+	}
+}
+
+idx_t ColumnData::GetMaxEntry() const {
+	return segments.empty() ? 0 : segments.back()->start + segments.back()->count - segments.front()->start;
+}
+
+ColumnSegment *ColumnData::GetSegment(idx_t row_idx) const {
+	// SegmentTree::GetSegment: binary search over the segment starts
+	auto it = std::upper_bound(segments.begin(), segments.end(), row_idx,
+	                           [](idx_t row, const unique_ptr<ColumnSegment> &s) { return row < s->start; });
+	if (it == segments.begin()) {
+		throw InternalException("ColumnData::GetSegment: row before the first segment");
+	}
+	--it;
+	if (row_idx >= (*it)->start + (*it)->count && it + 1 != segments.end()) {
+		throw InternalException("ColumnData::GetSegment: row not covered by a segment");
+	}
+	return it->get();
+}
+
+static ColumnSegment *NextSegment(const ColumnData &col, ColumnSegment *current) {
+	auto it = std::lower_bound(col.segments.begin(), col.segments.end(), current->start,
+	                           [](const unique_ptr<ColumnSegment> &s, idx_t row) { return s->start < row; });
+	while (it != col.segments.end() && it->get() != current) {
+		++it;
+	}
+	if (it == col.segments.end() || it + 1 == col.segments.end()) {
+		return nullptr;
+	}
+	return (it + 1)->get();
+}
+
+void ColumnData::InitializeScan(ColumnScanState &state) {
+	state.current = segments.empty() ? nullptr : segments.front().get();
+	state.row_index = state.current ? state.current->start : 0;
+	state.internal_index = state.row_index;
+	state.initialized = false;
+	state.version = version;
+	state.scan_state.reset();
+}
+
+void ColumnData::InitializeScanWithOffset(ColumnScanState &state, idx_t row_idx) {
+	state.current = GetSegment(row_idx);
+	state.row_index = row_idx;
+	state.internal_index = state.current->start;
+	state.initialized = false;
+	state.version = version;
+	state.scan_state.reset();
+}
+
+idx_t ColumnData::ScanVector(ColumnScanState &state, Vector &result, idx_t remaining) {
+	state.previous_states.clear();
+	result.external = nullptr;
+	if (state.version != version) {
+		InitializeScanWithOffset(state, state.row_index);
+		state.current->InitializeScan(state);
+		state.initialized = true;
+	} else if (!state.initialized) {
+		state.current->InitializeScan(state);
+		state.internal_index = state.current->start;
+		state.initialized = true;
+	}
+	if (state.internal_index < state.row_index) {
+		state.current->Skip(state);
+	}
+	idx_t initial_remaining = remaining;
+	while (remaining > 0) {
+		idx_t scan_count = std::min<idx_t>(remaining, state.current->start + state.current->count - state.row_index);
+		idx_t result_offset = initial_remaining - remaining;
+		if (scan_count > 0) {
+			state.current->Scan(state, scan_count, result, result_offset, scan_count == initial_remaining);
+			state.row_index += scan_count;
+			remaining -= scan_count;
+		}
+		if (remaining > 0) {
+			ColumnSegment *next = NextSegment(*this, state.current);
+			if (!next) {
+				break;
+			}
+			state.previous_states.emplace_back(std::move(state.scan_state));
+			state.current = next;
+			state.current->InitializeScan(state);
+		}
+	}
+	state.internal_index = state.row_index;
+	return initial_remaining - remaining;
+}
+
+void ColumnData::FetchRow(ColumnFetchState &state, row_t row_id, Vector &result, idx_t result_idx) {
+	auto segment = GetSegment((idx_t)row_id);
+	segment->FetchRow(state, row_id, result, result_idx);
+}
+
+void ColumnData::FetchRows(const row_t *row_ids, idx_t count, Vector &result) {
+	// the per-row slot is one launch + one PCIe round trip per row id; an index join hands over its whole batch:
+	// one adacom_fetch_rows launch per device column the row ids touch
+	const idx_t S = GetTypeIdSize(type);
+	result.external = nullptr;
+	if (result.buffer.size() < count * S) {
+		result.buffer.resize(count * S);
+	}
+	if (segments.empty()) {
+		throw InternalException("ColumnData::FetchRows: empty column");
+	}
+	struct Group {
+		adacom_column *column;
+		std::vector<uint32_t> seg_idx, row_in_seg;
+		std::vector<idx_t> pos;
+	};
+	std::vector<Group> groups;
+	ColumnFetchState fetch_state;
+	const idx_t cap = segments.front()->SegmentSize() / S;
+	idx_t last_group = 0;
+	for (idx_t i = 0; i < count; i++) {
+		const idx_t row = (idx_t)row_ids[i];
+		// segments are full except the open one: guess by division, fall back to the tree search
+		idx_t guess = std::min<idx_t>((row - start) / cap, segments.size() - 1);
+		ColumnSegment *seg = segments[guess].get();
+		if (row < seg->start || row >= seg->start + seg->count) {
+			seg = GetSegment(row);
+			if (row >= seg->start + seg->count) {
+				throw InternalException("ColumnData::FetchRows: row id outside the column");
+			}
+		}
+		if (!seg->gpu_column || seg->owns_gpu_column) {
+			seg->FetchRow(fetch_state, row_ids[i], result, i);
+			continue;
+		}
+		if (groups.empty() || groups[last_group].column != seg->gpu_column) {
+			for (last_group = 0; last_group < groups.size() && groups[last_group].column != seg->gpu_column; last_group++) {
+			}
+			if (last_group == groups.size()) {
+				groups.emplace_back();
+				groups.back().column = seg->gpu_column;
+			}
+		}
+		Group &g = groups[last_group];
+		g.seg_idx.push_back((uint32_t)seg->gpu_index);
+		g.row_in_seg.push_back((uint32_t)(row - seg->start));
+		g.pos.push_back(i);
+	}
+	std::vector<uint8_t> out;
+	for (auto &g : groups) {
+		const idx_t n = g.pos.size();
+		const bool in_place = groups.size() == 1 && n == count;  // every row from one device column: no scatter
+		uint8_t *dst = result.buffer.data();
+		if (!in_place) {
+			out.resize(n * S);
+			dst = out.data();
+		}
+		GPU_CHECK(db, adacom_fetch_rows(g.column, n, g.seg_idx.data(), g.row_in_seg.data(), 0, dst, 0));
+		if (!in_place) {
+			for (idx_t k = 0; k < n; k++) {
+				memcpy(result.buffer.data() + g.pos[k] * S, out.data() + k * S, S);
+			}
+		}
+	}
+}
+
+void ColumnData::SegmentSealed() {
+	idx_t pending = 0;
+	{
+		std::lock_guard<std::mutex> guard(lock);
+		for (idx_t i = segments.size(); i-- > 0;) {
+			auto &s = segments[i];
+			if (s->gpu_column || s->compacted) {
+				break;
+			}
+			pending++;
+		}
+	}
+	if (pending >= pending_limit) {
+		CompactPending(false);
+	}
+}
+
+static void AppendBits(std::vector<uint64_t> &dst, idx_t dst_bit, const uint64_t *src, idx_t n_bits) {
+	for (idx_t i = 0; i < n_bits; i += 64) {
+		uint64_t w = src[i >> 6];
+		idx_t m = std::min<idx_t>(64, n_bits - i);
+		if (m < 64) {
+			w |= ~0ull << m;  // bits past the segment stay "valid"
+		}
+		idx_t pos = dst_bit + i;
+		idx_t sh = pos & 63;
+		// dst is initialised to all ones: clear where w is zero
+		dst[pos >> 6] &= (w << sh) | ((1ull << sh) - 1);
+		if (sh && (pos >> 6) + 1 < dst.size()) {
+			dst[(pos >> 6) + 1] &= (w >> (64 - sh)) | (~0ull << sh);
+		}
+	}
+}
+
+void ColumnData::CompactPending(bool include_last) {
+	std::lock_guard<std::mutex> guard(lock);
+	std::vector<ColumnSegment *> pending;
+	for (idx_t i = 0; i < segments.size(); i++) {
+		ColumnSegment *s = segments[i].get();
+		if (s->gpu_column || s->compacted || s->count == 0 || !s->succinct_possible) {
+			continue;
+		}
+		if (!include_last && i + 1 == segments.size()) {
+			continue;  // still open for appends
+		}
+		pending.push_back(s);
+	}
+	if (pending.empty()) {
+		return;
+	}
+	const idx_t S = GetTypeIdSize(type);
+	const int flags = pending.front()->CompactFlags();
+	std::vector<uint64_t> counts(pending.size());
+	idx_t rows = 0;
+	bool nulls = false;
+	for (idx_t i = 0; i < pending.size(); i++) {
+		counts[i] = pending[i]->count;
+		rows += pending[i]->count;
+		nulls |= pending[i]->staging_has_nulls;
+	}
+	Batch batch;
+	batch.n = pending.size();
+	adacom_ctx *ctx = db.Gpu(device);
+	GPU_CHECK(db, adacom_column_create(ctx, ToAdacomType(type), pending.size(), counts.data(),
+	                                   (uint32_t)(pending.front()->SegmentSize() / S), &batch.col));
+	batches.push_back(batch);  // owned from here on (freed by the destructor even if a later step throws)
+	Batch &b = batches.back();
+	idx_t row = 0;
+	for (auto *s : pending) {
+		GPU_CHECK(db, adacom_column_upload_raw(b.col, s->staging.data(), row, s->count));
+		row += s->count;
+	}
+	if (nulls) {
+		// validity of the whole batch (bit i = row i of the device column), kept in pinned host memory so that later
+		// re-compactions of members (the policy) can hand it to the analyze kernel again
+		std::vector<uint64_t> bits((rows + 63) / 64 + 1, ~0ull);
+		row = 0;
+		for (auto *s : pending) {
+			AppendBits(bits, row, s->staging_validity.data(), s->count);
+			row += s->count;
+		}
+		void *pinned = nullptr;
+		GPU_CHECK(db, adacom_host_alloc(ctx, bits.size() * 8, &pinned));
+		memcpy(pinned, bits.data(), bits.size() * 8);
+		b.validity = (uint64_t *)pinned;
+	}
+	GPU_CHECK(db, adacom_analyze(b.col, 0, b.n, flags, b.validity, 0));
+	GPU_CHECK(db, adacom_encode(b.col, 0, b.n, flags));
+	std::vector<adacom_segment_meta> metas(b.n);
+	GPU_CHECK(db, adacom_column_get_meta(b.col, 0, b.n, metas.data()));
+	for (idx_t i = 0; i < pending.size(); i++) {
+		ColumnSegment *s = pending[i];
+		const idx_t size_before = s->GetDataSize();
+		s->gpu_column = b.col;
+		s->gpu_index = i;
+		s->owns_gpu_column = false;
+		s->uploaded = s->count;
+		s->FinishCompact(size_before, metas[i]);
+		std::vector<uint8_t>().swap(s->staging);  // the values live on the device now (EnsureStaging brings them back)
+	}
+}
+
+// the policy's subsets: group the members by device column, ids ascending, one launch set per column
+static std::map<adacom_column *, std::vector<ColumnSegment *>> GroupByColumn(const std::vector<CompactableSegment *> &in) {
+	std::map<adacom_column *, std::vector<ColumnSegment *>> groups;
+	for (auto *c : in) {
+		auto *s = static_cast<ColumnSegment *>(c);
+		if (s->gpu_column && !s->owns_gpu_column) {
+			groups[s->gpu_column].push_back(s);
+		}
+	}
+	for (auto &kv : groups) {
+		std::sort(kv.second.begin(), kv.second.end(),
+		          [](ColumnSegment *l, ColumnSegment *r) { return l->gpu_index < r->gpu_index; });
+	}
+	return groups;
+}
+
+void ColumnData::CompactMany(const std::vector<CompactableSegment *> &list) {
+	bool any_pending = false;
+	std::vector<CompactableSegment *> members;
+	for (auto *c : list) {
+		auto *s = static_cast<ColumnSegment *>(c);
+		if (s->compacted || s->num_elements == 0 || !s->succinct_possible) {
+			continue;  // column_segment.cpp:278
+		}
+		if (!s->gpu_column) {
+			any_pending = true;
+		} else if (!s->owns_gpu_column) {
+			members.push_back(s);
+		} else {
+			s->column_data = nullptr;  // detached earlier: compacts on its own
+			s->Compact();
+			s->column_data = this;
+		}
+	}
+	if (any_pending) {
+		CompactPending(true);
+	}
+	std::lock_guard<std::mutex> guard(lock);
+	for (auto &kv : GroupByColumn(members)) {
+		std::vector<uint32_t> ids;
+		for (auto *s : kv.second) {
+			ids.push_back((uint32_t)s->gpu_index);
+		}
+		const uint64_t *validity = nullptr;
+		for (auto &b : batches) {
+			if (b.col == kv.first) {
+				validity = b.validity;
+			}
+		}
+		const int flags = kv.second.front()->CompactFlags();
+		GPU_CHECK(db, adacom_analyze_list(kv.first, ids.size(), ids.data(), flags, validity));
+		GPU_CHECK(db, adacom_encode_list(kv.first, ids.size(), ids.data(), flags));
+		const uint32_t lo = ids.front(), hi = ids.back() + 1;
+		std::vector<adacom_segment_meta> metas(hi - lo);
+		GPU_CHECK(db, adacom_column_get_meta(kv.first, lo, hi, metas.data()));
+		for (auto *s : kv.second) {
+			s->FinishCompact(s->GetDataSize(), metas[s->gpu_index - lo]);
+		}
+	}
+}
+
+void ColumnData::UncompactMany(const std::vector<CompactableSegment *> &list) {
+	std::vector<CompactableSegment *> members;
+	for (auto *c : list) {
+		auto *s = static_cast<ColumnSegment *>(c);
+		if (!s->compacted || !s->function || s->function->type != CompressionType::COMPRESSION_SUCCINCT) {
+			continue;  // column_segment.cpp:327-330
+		}
+		if (s->gpu_column && !s->owns_gpu_column) {
+			members.push_back(s);
+		} else {
+			s->column_data = nullptr;
+			s->Uncompact();
+			s->column_data = this;
+		}
+	}
+	std::lock_guard<std::mutex> guard(lock);
+	for (auto &kv : GroupByColumn(members)) {
+		std::vector<uint32_t> ids;
+		std::vector<idx_t> sizes;
+		for (auto *s : kv.second) {
+			ids.push_back((uint32_t)s->gpu_index);
+			sizes.push_back(s->GetDataSize());
+		}
+		GPU_CHECK(db, adacom_uncompact_list(kv.first, ids.size(), ids.data(), 0));
+		// the flat image stays on the device (scans of a member go through the scan stream either way); the host
+		// block is only brought back when an append needs it (ColumnSegment::EnsureStaging)
+		for (idx_t i = 0; i < kv.second.size(); i++) {
+			kv.second[i]->FinishUncompact(sizes[i]);
+		}
+	}
+}
+
+}  // namespace adacom_host

@@ -45,32 +45,41 @@ void ColumnSegmentCatalog::AddColumnSegment(CompactableSegment *segment) {
 	if (segment && segment->IsDataSegment()) {
 		std::lock_guard<std::mutex> guard(lock);
 		statistics[segment] = AccessStatistics {/* num_reads= */ 0};
+		segment->catalog_reads.store(0, std::memory_order_relaxed);
+		segment->catalog_registered.store(true, std::memory_order_release);
 	}
 }
 
 void ColumnSegmentCatalog::RemoveColumnSegment(CompactableSegment *segment) {
 	std::lock_guard<std::mutex> guard(lock);
 	statistics.erase(segment);
+	segment->catalog_registered.store(false, std::memory_order_release);
 }
 
 void ColumnSegmentCatalog::AddReadAccess(CompactableSegment *segment) {
 	if (segment == nullptr || !segment->IsDataSegment()) {
 		return;
 	}
+	if (segment->catalog_registered.load(std::memory_order_acquire)) {
+		segment->catalog_reads.fetch_add(1, std::memory_order_relaxed);
+		event_counter.fetch_add(1, std::memory_order_relaxed);
+		return;
+	}
 	std::lock_guard<std::mutex> guard(lock);
-	auto it = statistics.find(segment);
-	if (it == statistics.end()) {
-		statistics[segment] = AccessStatistics {/* num_reads= */ 1};
+	if (statistics.find(segment) == statistics.end()) {
+		statistics[segment] = AccessStatistics {/* num_reads= */ 0};
+		segment->catalog_reads.store(1, std::memory_order_relaxed);  // column_segment_catalog.cpp:44-46: first access
+		segment->catalog_registered.store(true, std::memory_order_release);
 	} else {
-		it->second.num_reads++;
-		event_counter++;
+		segment->catalog_reads.fetch_add(1, std::memory_order_relaxed);
+		event_counter.fetch_add(1, std::memory_order_relaxed);
 	}
 }
 
 idx_t ColumnSegmentCatalog::NumReads(CompactableSegment *segment) {
 	std::lock_guard<std::mutex> guard(lock);
 	auto it = statistics.find(segment);
-	return it == statistics.end() ? 0 : it->second.num_reads;
+	return it == statistics.end() ? 0 : segment->catalog_reads.load(std::memory_order_relaxed);
 }
 
 void ColumnSegmentCatalog::CompactAllSegments() {
@@ -81,8 +90,17 @@ void ColumnSegmentCatalog::CompactAllSegments() {
 			all.push_back(kv.first);
 		}
 	}
+	// segments of a ColumnData are compacted by their owner in one launch set; the others one by one
+	std::unordered_map<SegmentBatchOwner *, std::vector<CompactableSegment *>> batches;
 	for (auto *seg : all) {
-		seg->Compact();
+		if (auto *owner = seg->BatchOwner()) {
+			batches[owner].push_back(seg);
+		} else {
+			seg->Compact();
+		}
+	}
+	for (auto &kv : batches) {
+		kv.first->CompactMany(kv.second);
 	}
 }
 
@@ -90,7 +108,10 @@ std::pair<size_t, size_t> ColumnSegmentCatalog::RunCompactionEpoch() {
 	std::vector<std::pair<CompactableSegment *, AccessStatistics>> v;
 	{
 		std::lock_guard<std::mutex> guard(lock);
-		v.assign(statistics.begin(), statistics.end());
+		v.reserve(statistics.size());
+		for (auto &kv : statistics) {
+			v.emplace_back(kv.first, AccessStatistics {kv.first->catalog_reads.load(std::memory_order_relaxed)});
+		}
 	}
 	// stable order for equal read counts (the reference's unordered_map order is unspecified)
 	std::stable_sort(v.begin(), v.end(),
@@ -101,14 +122,35 @@ std::pair<size_t, size_t> ColumnSegmentCatalog::RunCompactionEpoch() {
 	size_t compacted = 0, uncompacted = 0;
 	float cum_sum = 0;
 	const size_t curr_counter = v.size();
+	// same decisions as the reference's loop; segments that share a device column (BatchOwner) are handed over as
+	// two lists per owner -- one launch set each -- instead of one Compact()/Uncompact() call per segment
+	std::unordered_map<SegmentBatchOwner *, std::pair<std::vector<CompactableSegment *>, std::vector<CompactableSegment *>>>
+	    batches;
 	for (auto &entry : v) {
 		cum_sum += 1;
+		SegmentBatchOwner *owner = entry.first->BatchOwner();
 		if (cum_sum / curr_counter < compression_rate) {
-			entry.first->Compact();  // least accessed share
+			if (owner) {
+				batches[owner].first.push_back(entry.first);
+			} else {
+				entry.first->Compact();  // least accessed share
+			}
 			compacted++;
 		} else {
-			entry.first->Uncompact();  // frequently accessed: leave / make flat
+			if (owner) {
+				batches[owner].second.push_back(entry.first);
+			} else {
+				entry.first->Uncompact();  // frequently accessed: leave / make flat
+			}
 			uncompacted++;
+		}
+	}
+	for (auto &kv : batches) {
+		if (!kv.second.first.empty()) {
+			kv.first->CompactMany(kv.second.first);
+		}
+		if (!kv.second.second.empty()) {
+			kv.first->UncompactMany(kv.second.second);
 		}
 	}
 	{
@@ -116,7 +158,7 @@ std::pair<size_t, size_t> ColumnSegmentCatalog::RunCompactionEpoch() {
 		for (auto &entry : v) {
 			auto it = statistics.find(entry.first);
 			if (it != statistics.end()) {
-				it->second.num_reads = 0;
+				entry.first->catalog_reads.store(0, std::memory_order_relaxed);
 			}
 		}
 		event_counter = 0;
@@ -144,6 +186,15 @@ size_t ColumnSegmentCatalog::GetTotalDataSize() {
 		data_size += kv.first->GetDataSize();
 	}
 	return data_size;
+}
+
+std::unordered_map<int, size_t> ColumnSegmentCatalog::GetDataSizePerDevice() {
+	std::lock_guard<std::mutex> guard(lock);
+	std::unordered_map<int, size_t> sizes;
+	for (auto &kv : statistics) {
+		sizes[kv.first->Device()] += kv.first->GetDataSize();
+	}
+	return sizes;
 }
 
 }  // namespace adacom_host

@@ -67,6 +67,7 @@ DatabaseInstance::DatabaseInstance(const DBConfig *cfg)
 		config.succinct_padded_to_next_byte_enabled = cfg->succinct_padded_to_next_byte_enabled;
 		config.adaptive_succinct_compression_enabled = cfg->adaptive_succinct_compression_enabled;
 		config.gpu_device = cfg->gpu_device;
+		config.gpu_devices = cfg->gpu_devices;
 		config.compression_rate = cfg->compression_rate;
 		config.background_interval_s = cfg->background_interval_s;
 	}
@@ -74,19 +75,34 @@ DatabaseInstance::DatabaseInstance(const DBConfig *cfg)
 
 DatabaseInstance::~DatabaseInstance() {
 	column_segment_catalog.StopBackgroundThread();
-	if (gpu) {
-		adacom_ctx_destroy(gpu);
+	for (auto &kv : gpus) {
+		adacom_ctx_destroy(kv.second);
 	}
 }
 
 adacom_ctx *DatabaseInstance::Gpu() {
-	if (!gpu) {
-		adacom_status st = adacom_ctx_create(config.gpu_device, &gpu);
-		if (st != ADACOM_OK) {
-			throw InternalException(std::string("succinct GPU codec unavailable: ") + adacom_last_error(nullptr));
-		}
+	return Gpu(config.gpu_device);
+}
+
+adacom_ctx *DatabaseInstance::Gpu(int device) {
+	if (device < 0) {
+		device = config.gpu_device;
 	}
-	return gpu;
+	std::lock_guard<std::mutex> guard(gpu_lock);
+	auto it = gpus.find(device);
+	if (it != gpus.end()) {
+		return it->second;
+	}
+	adacom_ctx *ctx = nullptr;
+	adacom_status st = adacom_ctx_create(device, &ctx);
+	if (st != ADACOM_OK) {
+		throw InternalException(std::string("succinct GPU codec unavailable: ") + adacom_last_error(nullptr));
+	}
+	gpus[device] = ctx;
+	if (device == config.gpu_device) {
+		gpu = ctx;
+	}
+	return ctx;
 }
 
 void DatabaseInstance::Throw(const char *what) {
@@ -168,23 +184,57 @@ ColumnSegment::ColumnSegment(DatabaseInstance &db_p, PhysicalType type_p, idx_t 
 
 ColumnSegment::~ColumnSegment() {
 	db.column_segment_catalog.RemoveColumnSegment(this);
-	if (gpu_column) {
+	if (gpu_column && owns_gpu_column) {
 		adacom_column_destroy(gpu_column);
 	}
+}
+
+SegmentBatchOwner *ColumnSegment::BatchOwner() const {
+	return column_data;
+}
+
+int ColumnSegment::Device() const {
+	return device < 0 ? db.config.gpu_device : device;
 }
 
 void ColumnSegment::EnsureDeviceColumn() {
 	if (!gpu_column) {
 		uint64_t cnt = count;
-		GPU_CHECK(db, adacom_column_create(db.Gpu(), ToAdacomType(type), 1, &cnt, (uint32_t)(segment_size / type_size),
-		                                   &gpu_column));
+		GPU_CHECK(db, adacom_column_create(db.Gpu(device), ToAdacomType(type), 1, &cnt,
+		                                   (uint32_t)(segment_size / type_size), &gpu_column));
+		gpu_index = 0;
+		owns_gpu_column = true;
+		uploaded = 0;
+	}
+}
+
+void ColumnSegment::EnsureStaging() {
+	// a member of a shared device column gives its host block back after the upload; appends (and host-side
+	// reads of an uncompacted segment) bring it back from the device
+	if (staging.size() == segment_size) {
+		return;
+	}
+	staging.resize(segment_size);
+	if (gpu_column && count) {
+		GPU_CHECK(db, adacom_decode(gpu_column, gpu_index, gpu_index + 1, 0, staging.data(), 0));
+	}
+}
+
+void ColumnSegment::DetachFromBatch() {
+	// the segment is about to change (append after Uncompact): its slot in the shared column goes stale, the
+	// segment continues on its own
+	if (gpu_column && !owns_gpu_column) {
+		EnsureStaging();
+		gpu_column = nullptr;
+		gpu_index = 0;
+		owns_gpu_column = true;
 		uploaded = 0;
 	}
 }
 
 void ColumnSegment::Upload() {
 	// the device column is created at Compact() time with the final count (segments are append-only until then)
-	if (gpu_column && adacom_column_num_values(gpu_column) != count) {
+	if (gpu_column && owns_gpu_column && adacom_column_num_values(gpu_column) != count) {
 		adacom_column_destroy(gpu_column);
 		gpu_column = nullptr;
 	}
@@ -200,7 +250,7 @@ adacom_segment_meta ColumnSegment::Meta() const {
 	adacom_segment_meta m;
 	memset(&m, 0, sizeof(m));
 	if (gpu_column) {
-		adacom_status st = adacom_column_get_meta(gpu_column, 0, 1, &m);
+		adacom_status st = adacom_column_get_meta(gpu_column, gpu_index, gpu_index + 1, &m);
 		if (st != ADACOM_OK) {
 			const_cast<DatabaseInstance &>(db).Throw("adacom_column_get_meta");
 		}
@@ -239,7 +289,7 @@ void ColumnSegment::Skip(ColumnScanState &state) {
 void ColumnSegment::Scan(ColumnScanState &state, idx_t scan_count, Vector &result) {
 	db.column_segment_catalog.AddReadAccess(this);
 	if (!compacted && !background_compaction_enabled) {
-		Compact();  // lazy encode on first read (column_segment.cpp:157-160)
+		Compact();  // lazy encode on first read (column_segment.cpp:157-160); a ColumnData flushes its whole batch
 	}
 	{
 		std::lock_guard<std::mutex> guard(bit_compression_lock);
@@ -287,10 +337,18 @@ idx_t ColumnSegment::Append(ColumnAppendState &state, UnifiedVectorFormat &appen
 		InitializeAppend(state);
 		uncompacted = true;
 	}
+	if (count < segment_size / type_size) {
+		DetachFromBatch();  // the slot in the shared device column is fixed-size and about to go stale
+		EnsureStaging();
+	}
 	idx_t copy_count = function->append(*state.append_state, *this, stats, append_data, offset, count_p);
 	num_elements += count_p;  // requested, not copied: quirk Q6 kept for the trigger below
 	if (!compacted && !background_compaction_enabled && (num_elements >= segment_size / type_size || uncompacted)) {
-		Compact();
+		if (column_data && !gpu_column && !uncompacted) {
+			column_data->SegmentSealed();  // deferred: the column compacts its sealed segments a batch at a time
+		} else {
+			Compact();
+		}
 	}
 	return copy_count;
 }
@@ -306,26 +364,44 @@ void ColumnSegment::Compact() {
 	if (compacted || !function || num_elements == 0 || !succinct_possible) {
 		return;  // column_segment.cpp:278
 	}
-	int flags = db.config.succinct_padded_to_next_byte_enabled ? ADACOM_PADDED : 0;
-	const bool from_uncompressed = function->type != CompressionType::COMPRESSION_SUCCINCT;
-	if (from_uncompressed) {
-		flags |= ADACOM_ZERO_EXT_MINMAX;  // BitCompressFromUncompressed scans zero-extended raw bytes (Q2b)
+	if (column_data) {
+		// member of a ColumnData: compaction is a batch operation of the column (one launch set for all pending
+		// segments, or a one-element list for a member that the policy uncompacted earlier)
+		if (!gpu_column) {
+			column_data->CompactPending(true);
+		} else {
+			column_data->CompactMany({this});
+		}
+		return;
 	}
+	const int flags = CompactFlags();
 	const idx_t size_before = GetDataSize();
 	Upload();
 	// analyze: the min/max SuccinctAppendLoop tracks while appending, taken by the reduction kernel
 	GPU_CHECK(db, adacom_analyze(gpu_column, 0, 1, flags, staging_has_nulls ? staging_validity.data() : nullptr, 0));
 	// encode: BitCompressFromSuccinct / BitCompressFromUncompressed
 	GPU_CHECK(db, adacom_encode(gpu_column, 0, 1, flags));
+	FinishCompact(size_before, Meta());
+}
+
+int ColumnSegment::CompactFlags() const {
+	int flags = db.config.succinct_padded_to_next_byte_enabled ? ADACOM_PADDED : 0;
+	if (function->type != CompressionType::COMPRESSION_SUCCINCT) {
+		flags |= ADACOM_ZERO_EXT_MINMAX;  // BitCompressFromUncompressed scans zero-extended raw bytes (Q2b)
+	}
+	return flags;
+}
+
+void ColumnSegment::FinishCompact(idx_t size_before, const adacom_segment_meta &m) {
 	{
 		std::lock_guard<std::mutex> guard(bit_compression_lock);
-		if (from_uncompressed) {
+		if (function->type != CompressionType::COMPRESSION_SUCCINCT) {
 			function = db.config.GetCompressionFunction(CompressionType::COMPRESSION_SUCCINCT, type);
 		}
 		compacted = true;
 		epoch++;
 	}
-	adacom_segment_meta m = Meta();
+	compacted_size = m.size_in_bytes;
 	if (m.min_factor != UINT64_MAX) {
 		stats.has_value = true;
 		stats.umin = m.min_factor;
@@ -333,17 +409,26 @@ void ColumnSegment::Compact() {
 		stats.min = (int64_t)m.min_factor;
 		stats.max = (int64_t)m.max_factor;
 	}
-	db.buffer_manager.AddToDataSize((int64_t)GetDataSize() - (int64_t)size_before);
+	db.buffer_manager.AddToDataSize((int64_t)m.size_in_bytes - (int64_t)size_before);
 }
 
 void ColumnSegment::Uncompact() {
 	if (!compacted || !function || function->type != CompressionType::COMPRESSION_SUCCINCT) {
 		return;  // column_segment.cpp:327-330
 	}
+	if (column_data && gpu_column && !owns_gpu_column) {
+		column_data->UncompactMany({this});
+		return;
+	}
 	const idx_t compressed_size = GetDataSize();
-	GPU_CHECK(db, adacom_uncompact(gpu_column, 0, 1, 0));
+	GPU_CHECK(db, adacom_uncompact(gpu_column, gpu_index, gpu_index + 1, 0));
 	// the flat block lives on the host again (appends continue there)
-	GPU_CHECK(db, adacom_decode(gpu_column, 0, 1, 0, staging.data(), 0));
+	staging.resize(segment_size);
+	GPU_CHECK(db, adacom_decode(gpu_column, gpu_index, gpu_index + 1, 0, staging.data(), 0));
+	FinishUncompact(compressed_size);
+}
+
+void ColumnSegment::FinishUncompact(idx_t compressed_size) {
 	{
 		std::lock_guard<std::mutex> guard(bit_compression_lock);
 		function = db.config.GetCompressionFunction(CompressionType::COMPRESSION_UNCOMPRESSED, type);
@@ -360,7 +445,7 @@ idx_t ColumnSegment::GetDataSize() const {
 	}
 	if (function->type == CompressionType::COMPRESSION_SUCCINCT) {
 		if (compacted && gpu_column) {
-			return Meta().size_in_bytes;
+			return compacted_size;
 		}
 		return SlotVectorBytes(segment_size);
 	}
@@ -496,16 +581,56 @@ void SuccinctFinalizeCompress(CompressionState &state_p) {
 }
 
 // ---- scan ---------------------------------------------------------------------------------------------
-// init_scan decodes the whole segment ONCE (one kernel launch + one D2H of <= 256 KiB) so that the
-// 2048-value pull calls that follow are slices of that image -- the reference re-copies the packed vector
-// on every call instead (quirk Q4).
+// A segment of a ColumnData is served by the column's scan stream (adacom_scan_stream): windows of 32 segments are
+// decoded by ONE launch each and copied into a pinned ring that runs ahead of the pulls, across segment borders --
+// the state of the next segment adopts the stream of the one the scan has just left (DuckDB keeps that state alive in
+// ColumnScanState::previous_states until the next ScanVector).  A whole vector is handed out zero-copy
+// (FlatVector::SetData, like FixedSizeScan); a partial one is a memcpy slice.  A lone segment decodes itself once
+// (one launch + one D2H of <= 256 KiB) -- the reference re-copies the packed vector on every call (quirk Q4).
+struct GpuScanStream {
+	adacom_scan_stream *handle = nullptr;
+	adacom_column *column = nullptr;
+	uint64_t seg_begin = 0, seg_end = 0;
+	~GpuScanStream() {
+		adacom_scan_stream_close(handle);
+	}
+};
+
 struct SuccinctGpuScanState : public SegmentScanState {
-	std::vector<uint8_t> decoded;
+	std::shared_ptr<GpuScanStream> stream;
+	const uint8_t *values = nullptr;  // this segment inside the stream's current window
+	std::vector<uint8_t> decoded;     // lone segments
 	uint64_t epoch = ~0ull;
 };
 
 unique_ptr<SegmentScanState> SuccinctInitScan(ColumnSegment &) {
 	return unique_ptr<SegmentScanState>(new SuccinctGpuScanState());
+}
+
+const uint8_t *StreamValues(ColumnSegment &segment, ColumnScanState &state, SuccinctGpuScanState &scan_state) {
+	if (scan_state.values) {
+		return scan_state.values;
+	}
+	if (!scan_state.stream && !state.previous_states.empty() && state.previous_states.back()) {
+		auto *prev = dynamic_cast<SuccinctGpuScanState *>(state.previous_states.back().get());
+		if (prev && prev->stream && prev->stream->column == segment.gpu_column &&
+		    segment.gpu_index >= prev->stream->seg_begin && segment.gpu_index < prev->stream->seg_end) {
+			scan_state.stream = prev->stream;
+		}
+	}
+	if (!scan_state.stream) {
+		auto stream = std::make_shared<GpuScanStream>();
+		stream->column = segment.gpu_column;
+		stream->seg_begin = segment.gpu_index;
+		stream->seg_end = adacom_column_num_segments(segment.gpu_column);
+		GPU_CHECK(segment.db, adacom_scan_stream_open(segment.gpu_column, stream->seg_begin, stream->seg_end, 0, 0, 0,
+		                                              &stream->handle));
+		scan_state.stream = std::move(stream);
+	}
+	const void *values = nullptr;
+	GPU_CHECK(segment.db, adacom_scan_stream_segment(scan_state.stream->handle, segment.gpu_index, &values, nullptr));
+	scan_state.values = (const uint8_t *)values;
+	return scan_state.values;
 }
 
 void SuccinctScanPartial(ColumnSegment &segment, ColumnScanState &state, idx_t scan_count, Vector &result,
@@ -515,23 +640,46 @@ void SuccinctScanPartial(ColumnSegment &segment, ColumnScanState &state, idx_t s
 		throw InternalException("SuccinctScanPartial: scan runs past the end of the segment");
 	}
 	result.SetVectorType(VectorType::FLAT_VECTOR);
+	if (result_offset == 0) {
+		result.external = nullptr;  // a zero-copy view of the previous pull ends here
+	}
 	idx_t S = segment.type_size;
 	data_ptr_t target_ptr = FlatVector::GetData(result) + result_offset * S;
-	if (!segment.compacted || !segment.gpu_column) {
+	if (!segment.gpu_column) {
 		// not compacted yet (adaptive mode): the slot-width image is the flat block (FixedSizeScanPartial)
 		memcpy(target_ptr, segment.staging.data() + start * S, scan_count * S);
 		return;
 	}
 	auto &scan_state = (SuccinctGpuScanState &)*state.scan_state;
+	if (segment.column_data && !segment.owns_gpu_column) {
+		memcpy(target_ptr, StreamValues(segment, state, scan_state) + start * S, scan_count * S);
+		return;
+	}
+	if (!segment.compacted) {
+		memcpy(target_ptr, segment.staging.data() + start * S, scan_count * S);
+		return;
+	}
 	if (scan_state.epoch != segment.epoch) {
 		scan_state.decoded.resize(segment.count * S);
-		GPU_CHECK(segment.db, adacom_decode(segment.gpu_column, 0, 1, 0, scan_state.decoded.data(), 0));
+		GPU_CHECK(segment.db, adacom_decode(segment.gpu_column, segment.gpu_index, segment.gpu_index + 1, 0,
+		                                    scan_state.decoded.data(), 0));
 		scan_state.epoch = segment.epoch;
 	}
 	memcpy(target_ptr, scan_state.decoded.data() + start * S, scan_count * S);
 }
 
 void SuccinctScan(ColumnSegment &segment, ColumnScanState &state, idx_t scan_count, Vector &result) {
+	if (segment.gpu_column && segment.column_data && !segment.owns_gpu_column) {
+		// entire vector out of one segment: zero-copy view into the pinned window
+		auto start = segment.GetRelativeIndex(state.row_index);
+		if (start + scan_count > segment.count) {
+			throw InternalException("SuccinctScan: scan runs past the end of the segment");
+		}
+		auto &scan_state = (SuccinctGpuScanState &)*state.scan_state;
+		result.SetVectorType(VectorType::FLAT_VECTOR);
+		FlatVector::SetData(result, (data_ptr_t)StreamValues(segment, state, scan_state) + start * segment.type_size);
+		return;
+	}
 	SuccinctScanPartial(segment, state, scan_count, result, 0);
 }
 
@@ -541,11 +689,11 @@ void SuccinctFetchRow(ColumnSegment &segment, ColumnFetchState &, row_t row_id, 
 	}
 	idx_t S = segment.type_size;
 	data_ptr_t target_ptr = FlatVector::GetData(result) + result_idx * S;
-	if (!segment.compacted || !segment.gpu_column) {
+	if (!segment.gpu_column || (!segment.compacted && segment.owns_gpu_column)) {
 		memcpy(target_ptr, segment.staging.data() + (idx_t)row_id * S, S);
 		return;
 	}
-	uint32_t seg = 0, row = (uint32_t)row_id;
+	uint32_t seg = (uint32_t)segment.gpu_index, row = (uint32_t)row_id;
 	GPU_CHECK(segment.db, adacom_fetch_rows(segment.gpu_column, 1, &seg, &row, 0, target_ptr, 0));
 }
 
@@ -564,6 +712,12 @@ idx_t SuccinctAppend(CompressionAppendState &, ColumnSegment &segment, SegmentSt
 	idx_t copy_count = std::min<idx_t>(count, max_tuple_count - segment.count);
 	auto sdata = (const T *)data.data;
 	auto target = (T *)segment.staging.data();
+	if ((!data.sel || !data.sel->sel) && data.validity.AllValid()) {
+		// flat, all-valid vector (the common case of a bulk load): one block copy
+		memcpy(target + segment.count, sdata + offset, copy_count * sizeof(T));
+		segment.count += copy_count;
+		return copy_count;
+	}
 	SelectionVector identity;
 	const SelectionVector *sel = data.sel ? data.sel : &identity;
 	for (idx_t i = 0; i < copy_count; i++) {

@@ -162,7 +162,183 @@ void RunColumn(DatabaseInstance &db, PhysicalType type, idx_t n, uint64_t span, 
 	CHECK(col.segments[0]->IsBitCompressed());  // lazily compacted again by the scan (non-adaptive mode)
 }
 
+// ColumnData: the segments of a column share one device column -- batched compaction, one scan stream across segment
+// borders (zero-copy whole vectors), batched policy epochs, batched fetches, NULLs, appends after Uncompact.
+template <class T>
+void RunColumnData(PhysicalType type, idx_t n, uint64_t span, int64_t base, bool nulls, bool adaptive, idx_t pending_limit) {
+	DBConfig cfg;
+	cfg.adaptive_succinct_compression_enabled = adaptive;
+	DatabaseInstance db(&cfg);
+	std::mt19937_64 rng(7 + n + span);
+	std::vector<T> values(n);
+	for (auto &v : values) {
+		v = (T)(base + (int64_t)(rng() % span));
+	}
+	auto valid = [&](idx_t row) { return !nulls || row % 7 != 3; };
+	ColumnData col(db, type);
+	col.pending_limit = pending_limit;
+	ColumnAppendState astate;
+	col.InitializeAppend(astate);
+	for (idx_t off = 0; off < n; off += STANDARD_VECTOR_SIZE) {
+		idx_t m = std::min<idx_t>(STANDARD_VECTOR_SIZE, n - off);
+		std::vector<uint64_t> local((m + 63) / 64, ~0ull);
+		for (idx_t i = 0; i < m; i++) {
+			if (!valid(off + i)) {
+				local[i >> 6] &= ~(1ull << (i & 63));
+			}
+		}
+		UnifiedVectorFormat vdata;
+		vdata.data = (data_ptr_t)(values.data() + off);
+		vdata.validity.mask = nulls ? local.data() : nullptr;
+		col.AppendData(astate, vdata, m);
+	}
+	CHECK(col.GetMaxEntry() == n);
+	idx_t cap = BLOCK_SIZE / sizeof(T);
+	CHECK(col.segments.size() == (n + cap - 1) / cap);
+	if (adaptive) {
+		for (auto &s : col.segments) {
+			CHECK(!s->IsBitCompressed());
+		}
+		CHECK(db.column_segment_catalog.GetTotalDataSize() == col.segments.size() * BLOCK_SIZE);
+		db.column_segment_catalog.CompactAllSegments();  // one launch set for the whole column
+		CHECK(col.batches.size() == 1);
+	}
+	// full scan, row-aligned vectors; whole vectors inside a segment must arrive zero-copy
+	auto full_scan = [&]() {
+		ColumnScanState state;
+		col.InitializeScan(state);
+		Vector result(type);
+		idx_t zero_copy = 0;
+		for (idx_t row = 0; row < n;) {
+			idx_t got = col.ScanVector(state, result, std::min<idx_t>(STANDARD_VECTOR_SIZE, n - row));
+			CHECK(got == std::min<idx_t>(STANDARD_VECTOR_SIZE, n - row));
+			zero_copy += result.external != nullptr;
+			auto out = (T *)FlatVector::GetData(result);
+			for (idx_t i = 0; i < got; i++) {
+				if (valid(row + i)) {
+					CHECK(out[i] == values[row + i]);
+				}
+			}
+			row += got;
+		}
+		return zero_copy;
+	};
+	idx_t zero_copy = full_scan();
+	idx_t vectors = (n + STANDARD_VECTOR_SIZE - 1) / STANDARD_VECTOR_SIZE;
+	CHECK(zero_copy + 2 * col.segments.size() >= vectors);  // all but the vectors that straddle a segment border
+	for (auto &s : col.segments) {
+		CHECK(s->IsBitCompressed() && s->gpu_column && !s->owns_gpu_column && s->staging.empty());
+	}
+	// sizes: 9 + 8*ceil(n*w/64) per segment; catalog and buffer manager agree
+	idx_t total = 0;
+	for (auto &s : col.segments) {
+		idx_t w = s->Width();
+		idx_t expect = w < 8 * sizeof(T) ? 9 + 8 * ((s->count * w + 63) / 64) : 9 + 8 * ((s->SegmentSize() * 8 + 63) / 64);
+		CHECK(s->GetDataSize() == expect);
+		total += expect;
+	}
+	CHECK(db.column_segment_catalog.GetTotalDataSize() == total);
+	CHECK(db.buffer_manager.GetDataSize() == total);
+	auto per_device = db.column_segment_catalog.GetDataSizePerDevice();
+	CHECK(per_device.size() == 1 && per_device[0] == total);
+	// a scan from the middle (InitializeScanWithOffset), crossing batches when pending_limit split the column
+	{
+		ColumnScanState state;
+		idx_t row = (n / 2) / STANDARD_VECTOR_SIZE * STANDARD_VECTOR_SIZE;
+		col.InitializeScanWithOffset(state, row);
+		Vector result(type);
+		for (int k = 0; k < 40 && row < n; k++) {
+			idx_t got = col.ScanVector(state, result, std::min<idx_t>(STANDARD_VECTOR_SIZE, n - row));
+			auto out = (T *)FlatVector::GetData(result);
+			for (idx_t i = 0; i < got; i++) {
+				if (valid(row + i)) {
+					CHECK(out[i] == values[row + i]);
+				}
+			}
+			row += got;
+		}
+	}
+	// fetch_row per row and batched
+	ColumnFetchState fstate;
+	Vector one(type);
+	std::vector<row_t> ids;
+	for (int q = 0; q < 300; q++) {
+		idx_t row = rng() % n;
+		if (!valid(row)) {
+			continue;
+		}
+		ids.push_back((row_t)row);
+		if (q < 40) {
+			col.FetchRow(fstate, (row_t)row, one, 5);
+			CHECK(((T *)FlatVector::GetData(one))[5] == values[row]);
+		}
+	}
+	Vector many(type);
+	col.FetchRows(ids.data(), ids.size(), many);
+	for (idx_t k = 0; k < ids.size(); k++) {
+		CHECK(((T *)FlatVector::GetData(many))[k] == values[ids[k]]);
+	}
+	// policy epoch: hot segments (read above by the fetches / scans) are uncompacted in ONE call, cold re-compacted
+	if (col.segments.size() >= 10) {
+		for (int rep = 0; rep < 50; rep++) {
+			db.column_segment_catalog.AddReadAccess(col.segments[1].get());
+		}
+		auto res = db.column_segment_catalog.RunCompactionEpoch();
+		CHECK(res.first + res.second == col.segments.size());
+		CHECK(!col.segments[1]->IsBitCompressed());
+		CHECK(col.segments[1]->GetDataSize() == col.segments[1]->SegmentSize());
+		idx_t after = db.column_segment_catalog.GetTotalDataSize();
+		CHECK(after > total);
+		CHECK(db.buffer_manager.GetDataSize() == after);
+		full_scan();  // values unchanged; non-adaptive mode re-compacts lazily, adaptive serves the flat image
+		if (adaptive) {
+			CHECK(!col.segments[1]->IsBitCompressed());
+			db.column_segment_catalog.CompactAllSegments();
+		}
+		CHECK(col.segments[1]->IsBitCompressed());
+		CHECK(db.column_segment_catalog.GetTotalDataSize() == total);
+		CHECK(db.buffer_manager.GetDataSize() == total);
+	}
+	// append after the column was compacted: the open last segment leaves the shared column, continues on the host
+	{
+		idx_t extra = 3000;
+		std::vector<T> more(extra);
+		for (auto &v : more) {
+			v = (T)(base + (int64_t)(rng() % span));
+		}
+		UnifiedVectorFormat vdata;
+		vdata.data = (data_ptr_t)more.data();
+		for (idx_t off = 0; off < extra; off += STANDARD_VECTOR_SIZE) {
+			UnifiedVectorFormat part = vdata;
+			part.data = (data_ptr_t)(more.data() + off);
+			col.AppendData(astate, part, std::min<idx_t>(STANDARD_VECTOR_SIZE, extra - off));
+		}
+		values.insert(values.end(), more.begin(), more.end());
+		idx_t n_old = n;
+		n += extra;
+		CHECK(col.GetMaxEntry() == n);
+		ColumnScanState state;
+		col.InitializeScanWithOffset(state, n_old / STANDARD_VECTOR_SIZE * STANDARD_VECTOR_SIZE);
+		Vector result(type);
+		for (idx_t row = n_old / STANDARD_VECTOR_SIZE * STANDARD_VECTOR_SIZE; row < n;) {
+			idx_t got = col.ScanVector(state, result, std::min<idx_t>(STANDARD_VECTOR_SIZE, n - row));
+			auto out = (T *)FlatVector::GetData(result);
+			for (idx_t i = 0; i < got; i++) {
+				if (row + i >= n_old || (row + i) % 7 != 3) {
+					CHECK(out[i] == values[row + i]);
+				}
+			}
+			row += got;
+		}
+	}
+}
+
 int main() {
+	RunColumnData<int64_t>(PhysicalType::INT64, 32767 * 12 + 500, 1ull << 33, -40000000000ll, false, false, 64);
+	RunColumnData<int64_t>(PhysicalType::INT64, 32767 * 12 + 500, 1ull << 33, -40000000000ll, false, false, 5);
+	RunColumnData<uint32_t>(PhysicalType::UINT32, 65534 * 11 + 77, 1ull << 13, 1000, true, false, 4);
+	RunColumnData<int16_t>(PhysicalType::INT16, 131068 * 10, 1ull << 7, -50, false, true, 64);
+	RunColumnData<uint8_t>(PhysicalType::UINT8, 262136 * 3 + 9, 1ull << 3, 2, true, true, 64);
 	DatabaseInstance db;
 	idx_t base_size = db.buffer_manager.GetDataSize();
 	CHECK(base_size == 0);

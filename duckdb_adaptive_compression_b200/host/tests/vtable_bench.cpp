@@ -1,0 +1,171 @@
+// vtable_bench.cpp -- the drop-in path timed the way DuckDB drives it (needs a B200):
+//   load   ColumnData::AppendData in 2048-value vectors (host buffers) + the batched compaction it triggers
+//   scan   ColumnData::ScanVector pulls of 2048 values through SuccinctGpuFun's scan_vector / scan_partial slots,
+//          T scan threads over disjoint row ranges (DuckDB's parallel table scan hands out row groups the same way);
+//          the timed loop only pulls (the operator above the scan is not part of the codec); a second, untimed pass
+//          checks every value
+//   fetch  ColumnData::FetchRow per row id (the fetch_row slot) and ColumnData::FetchRows (batched)
+// usage: vtable_bench <log2 values> <bits> <scan threads> [pending_limit]      -> one JSON line on stdout
+#include "../adacom_host.hpp"
+
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <thread>
+
+using namespace adacom_host;
+using Clock = std::chrono::steady_clock;
+
+static inline uint64_t splitmix(uint64_t x) {
+	x += 0x9E3779B97F4A7C15ull;
+	x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+	x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+	return x ^ (x >> 31);
+}
+
+static double seconds(Clock::time_point a, Clock::time_point b) {
+	return std::chrono::duration<double>(b - a).count();
+}
+
+int main(int argc, char **argv) {
+	const int logn = argc > 1 ? atoi(argv[1]) : 27;
+	const int bits = argc > 2 ? atoi(argv[2]) : 17;
+	const int threads = argc > 3 ? atoi(argv[3]) : 1;
+	const idx_t pending_limit = argc > 4 ? (idx_t)atoll(argv[4]) : 512;
+	const idx_t n = 1ull << logn;
+	const uint64_t mask = bits >= 64 ? ~0ull : (1ull << bits) - 1;
+	const int64_t base = 1000003;
+
+	DatabaseInstance db;
+	ColumnData col(db, PhysicalType::INT64);
+	col.pending_limit = pending_limit;
+	db.Gpu();  // context creation is not part of the load
+
+	// ---- load ------------------------------------------------------------------------------------------
+	// the source vectors are minted before the clock starts: a pool of 1021 distinct vectors used round-robin
+	// (value of row r = pool[(r / 2048) % 1021][r % 2048]; 1021 is prime, so segments do not repeat)
+	const idx_t kPool = 1021;
+	std::vector<int64_t> pool(kPool * STANDARD_VECTOR_SIZE);
+	std::vector<unsigned __int128> pool_sum(kPool, 0);
+	for (idx_t v = 0; v < kPool; v++) {
+		for (idx_t i = 0; i < STANDARD_VECTOR_SIZE; i++) {
+			pool[v * STANDARD_VECTOR_SIZE + i] = base + (int64_t)(splitmix(v * STANDARD_VECTOR_SIZE + i) & mask);
+			pool_sum[v] += (unsigned __int128)(uint64_t)pool[v * STANDARD_VECTOR_SIZE + i];
+		}
+	}
+	auto value_of = [&](idx_t row) {
+		return pool[((row / STANDARD_VECTOR_SIZE) % kPool) * STANDARD_VECTOR_SIZE + row % STANDARD_VECTOR_SIZE];
+	};
+	unsigned __int128 expect_sum = 0;
+	for (idx_t off = 0; off < n; off += STANDARD_VECTOR_SIZE) {
+		expect_sum += pool_sum[(off / STANDARD_VECTOR_SIZE) % kPool];
+	}
+	auto t0 = Clock::now();
+	{
+		ColumnAppendState astate;
+		col.InitializeAppend(astate);
+		for (idx_t off = 0; off < n; off += STANDARD_VECTOR_SIZE) {
+			UnifiedVectorFormat vdata;
+			vdata.data = (data_ptr_t)(pool.data() + ((off / STANDARD_VECTOR_SIZE) % kPool) * STANDARD_VECTOR_SIZE);
+			col.AppendData(astate, vdata, STANDARD_VECTOR_SIZE);
+		}
+		col.CompactPending(true);
+		adacom_ctx_synchronize(db.Gpu());
+	}
+	auto t1 = Clock::now();
+	const double load_s = seconds(t0, t1);
+	const idx_t data_size = db.column_segment_catalog.GetTotalDataSize();
+
+	// ---- scan (timed: pulls only) --------------------------------------------------------------------
+	auto scan_range = [&](idx_t row_begin, idx_t row_end, bool verify, unsigned __int128 *sum_out, idx_t *zero_copy_out) {
+		ColumnScanState state;
+		col.InitializeScanWithOffset(state, row_begin);
+		Vector result(PhysicalType::INT64);
+		unsigned __int128 sum = 0;
+		idx_t zero_copy = 0;
+		for (idx_t row = row_begin; row < row_end;) {
+			idx_t got = col.ScanVector(state, result, std::min<idx_t>(STANDARD_VECTOR_SIZE, row_end - row));
+			auto out = (const int64_t *)FlatVector::GetData(result);
+			zero_copy += result.external != nullptr;
+			if (verify) {
+				for (idx_t i = 0; i < got; i++) {
+					sum += (unsigned __int128)(uint64_t)out[i];
+				}
+			} else {
+				sum += (uint64_t)out[0];  // touch the vector
+			}
+			row += got;
+		}
+		*sum_out = sum;
+		*zero_copy_out = zero_copy;
+	};
+	auto run_scan = [&](int T, bool verify, unsigned __int128 *total, idx_t *zero_copy) {
+		std::vector<std::thread> pool;
+		std::vector<unsigned __int128> sums(T, 0);
+		std::vector<idx_t> zc(T, 0);
+		const idx_t vectors = n / STANDARD_VECTOR_SIZE;
+		auto a = Clock::now();
+		for (int t = 0; t < T; t++) {
+			idx_t b = vectors * t / T * STANDARD_VECTOR_SIZE, e = vectors * (t + 1) / T * STANDARD_VECTOR_SIZE;
+			pool.emplace_back(scan_range, b, e, verify, &sums[t], &zc[t]);
+		}
+		for (auto &th : pool) {
+			th.join();
+		}
+		auto b = Clock::now();
+		*total = 0;
+		*zero_copy = 0;
+		for (int t = 0; t < T; t++) {
+			*total += sums[t];
+			*zero_copy += zc[t];
+		}
+		return seconds(a, b);
+	};
+	unsigned __int128 sum = 0;
+	idx_t zero_copy = 0;
+	run_scan(threads, false, &sum, &zero_copy);  // warm-up (pinned rings, first launches)
+	double scan_s = 1e30, scan1_s = 1e30;
+	for (int rep = 0; rep < 3; rep++) {
+		scan_s = std::min(scan_s, run_scan(threads, false, &sum, &zero_copy));
+	}
+	for (int rep = 0; rep < 2; rep++) {
+		scan1_s = std::min(scan1_s, threads == 1 ? scan_s : run_scan(1, false, &sum, &zero_copy));
+	}
+	const double verify_s = run_scan(threads, true, &sum, &zero_copy);
+	const bool ok = sum == expect_sum;
+
+	// ---- fetch_row ---------------------------------------------------------------------------------------
+	const idx_t n_single = 20000, n_batch = 1000000;
+	std::vector<row_t> ids(n_batch);
+	for (idx_t i = 0; i < n_batch; i++) {
+		ids[i] = (row_t)(splitmix(0xFE7C000 + i) % n);
+	}
+	ColumnFetchState fstate;
+	Vector one(PhysicalType::INT64);
+	bool fetch_ok = true;
+	auto f0 = Clock::now();
+	for (idx_t i = 0; i < n_single; i++) {
+		col.FetchRow(fstate, ids[i], one, 0);
+		fetch_ok &= ((int64_t *)FlatVector::GetData(one))[0] == value_of((idx_t)ids[i]);
+	}
+	auto f1 = Clock::now();
+	Vector many(PhysicalType::INT64, n_batch);
+	col.FetchRows(ids.data(), n_batch, many);  // warm-up
+	auto f2 = Clock::now();
+	col.FetchRows(ids.data(), n_batch, many);
+	auto f3 = Clock::now();
+	for (idx_t i = 0; i < n_batch; i += 997) {
+		fetch_ok &= ((int64_t *)FlatVector::GetData(many))[i] == value_of((idx_t)ids[i]);
+	}
+
+	const double gb = (double)n * 8 / 1e9;
+	printf("{\"values\": %llu, \"bits\": %d, \"segments\": %zu, \"device_columns\": %zu, \"data_size\": %llu, "
+	       "\"load_s\": %.4f, \"load_GBs\": %.2f, \"scan_threads\": %d, \"scan_s\": %.5f, \"scan_GBs\": %.2f, "
+	       "\"scan_1thread_GBs\": %.2f, \"scan_verify_GBs\": %.2f, \"zero_copy_vectors\": %llu, \"vectors\": %llu, "
+	       "\"scan_ok\": %s, \"fetch_row_per_s\": %.0f, \"fetch_rows_batched_per_s\": %.0f, \"fetch_ok\": %s}\n",
+	       (unsigned long long)n, bits, col.segments.size(), col.batches.size(), (unsigned long long)data_size, load_s,
+	       gb / load_s, threads, scan_s, gb / scan_s, gb / scan1_s, gb / verify_s, (unsigned long long)zero_copy,
+	       (unsigned long long)(n / STANDARD_VECTOR_SIZE), ok ? "true" : "false", n_single / seconds(f0, f1),
+	       n_batch / seconds(f2, f3), fetch_ok ? "true" : "false");
+	return ok && fetch_ok ? 0 : 1;
+}

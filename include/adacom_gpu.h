@@ -210,6 +210,25 @@ adacom_status adacom_decode(adacom_column *col, uint64_t seg_begin, uint64_t seg
  * (SuccinctScanPartial, succinct.cpp:123-144).  scan_count may exceed 2048. */
 adacom_status adacom_scan_partial(adacom_column *col, uint64_t seg, uint64_t start, uint64_t scan_count,
                                   int flags, void *result, uint64_t result_offset, int result_on_device);
+/* ---- pull-model scan (the vtable path) ------------------------------------------------------------------
+ * ColumnData::ScanVector (src/storage/table/column_data.cpp:92-139) pulls <= 2048 values per call and walks the
+ * segments of a column in order; SuccinctScanPartial (succinct.cpp:123-144) re-copies and decodes per call.  A scan
+ * stream serves that loop from the device: segments [seg_begin, seg_end) are decoded `window_segments` at a time
+ * (one launch per window) on a stream of the scan's own and copied into a ring of `depth` pinned host windows that
+ * run ahead of the consumer, so scan_vector / scan_partial become pointer arithmetic into pinned memory (zero-copy
+ * FlatVector::SetData, like FixedSizeScan, fixed_size_uncompressed.cpp).  No call of the scan holds the context
+ * mutex while it waits; any number of streams (one per DuckDB scan thread) run concurrently.
+ * window_segments = 0 / depth = 0 pick the defaults (32 segments = 8 MiB, 3 windows; depth >= 2). */
+typedef struct adacom_scan_stream adacom_scan_stream;
+adacom_status adacom_scan_stream_open(adacom_column *col, uint64_t seg_begin, uint64_t seg_end,
+                                      uint32_t window_segments, uint32_t depth, int flags, adacom_scan_stream **out);
+/* Decoded values of segment `seg` (flat T array, `*count` values) in pinned host memory.  Blocks until the window
+ * holding it has arrived; touching a window issues the ones after it.  The pointer stays valid until the stream has
+ * moved depth-1 windows past the segment's window or is closed.  Segments may be revisited inside the current and
+ * the previous window for free; anything else restarts the pipeline at that window. */
+adacom_status adacom_scan_stream_segment(adacom_scan_stream *s, uint64_t seg, const void **values, uint64_t *count);
+void adacom_scan_stream_close(adacom_scan_stream *s);
+
 /* UncompressSuccinct over a range: decode back into the raw arena, segments become not compacted */
 adacom_status adacom_uncompact(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags);
 
