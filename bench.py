@@ -266,6 +266,10 @@ def run_ours(args):
     ctx.synchronize()
 
     n_ev = len(OPS) + 1
+    # NCCL work is enqueued on the codec's own stream (an ExternalStream view of it): the all-gather runs right behind
+    # the last kernel of the sweep, without a host synchronisation in between
+    codec_stream = torch.cuda.ExternalStream(ctx.stream_ptr, device=dev)
+
     def step(events=None):
         for wi, b in enumerate(widths):
             col = cols[b]
@@ -283,8 +287,8 @@ def run_ours(args):
             if ev: ctx.record(ev[5])
         if world > 1:
             # the only cross-GPU exchange of the path: 64 x {sum_lo, sum_hi, count} per rank over NCCL
-            ctx.synchronize()
-            return sharding.all_gather_aggregates(aggs)
+            with torch.cuda.stream(codec_stream):
+                return sharding.all_gather_aggregates(aggs)
         return None
 
     def barrier():

@@ -26,6 +26,7 @@ static_assert(sizeof(adacom_agg) == sizeof(Agg), "adacom_agg layout");
 namespace {
 std::string g_process_error;
 constexpr size_t kArenaPad = 256;          // slack behind every arena for the 16-byte rounded bulk copies
+constexpr size_t kSmallFetch = 64;         // fetch batches up to this size go through the host-mapped page
 }  // namespace
 
 struct adacom_ctx {
@@ -53,6 +54,9 @@ struct adacom_ctx {
 	// staging pair of the batched look-ups (pinned host + device, grown on demand): one H2D, one kernel, one D2H
 	uint8_t *h_stage = nullptr, *d_stage = nullptr;
 	size_t stage_bytes = 0;
+	// host-mapped page for the smallest fetch batches (fetch_row of one row id): the kernel reads the ids and writes
+	// the answers through the mapping, so the call is one launch + one synchronisation instead of copy, launch, copy
+	uint8_t *h_small = nullptr, *d_small = nullptr;
 	// window rings of closed scan streams (pinned host + device buffer + copy stream + events), reused by the next
 	// adacom_scan_stream_open: allocating 24 MiB of pinned memory costs milliseconds, a scan opens one stream per
 	// device column it crosses
@@ -391,6 +395,8 @@ extern "C" adacom_status adacom_ctx_create(int device, adacom_ctx **out) {
 	CK(nullptr, cudaHostAlloc((void **)&ctx->h_totals, 4 * sizeof(unsigned long long), cudaHostAllocMapped));
 	memset(ctx->h_totals, 0, 4 * sizeof(unsigned long long));
 	CK(nullptr, cudaHostGetDevicePointer((void **)&ctx->d_totals, ctx->h_totals, 0));
+	CK(nullptr, cudaHostAlloc((void **)&ctx->h_small, kSmallFetch * 16, cudaHostAllocMapped));
+	CK(nullptr, cudaHostGetDevicePointer((void **)&ctx->d_small, ctx->h_small, 0));
 	// keep freed extents cached in the stream-ordered pool instead of returning them to the driver
 	cudaMemPool_t pool;
 	if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
@@ -417,6 +423,7 @@ extern "C" void adacom_ctx_destroy(adacom_ctx *ctx) {
 	cudaFreeHost(ctx->h_aggs);
 	cudaFreeHost(ctx->h_agg);
 	cudaFreeHost(ctx->h_totals);
+	cudaFreeHost(ctx->h_small);
 	cudaFreeHost(ctx->h_stage);
 	cudaFree(ctx->d_stage);
 	for (auto &r : ctx->ring_cache) {
@@ -2044,6 +2051,23 @@ extern "C" adacom_status adacom_fetch_rows(adacom_column *col, uint64_t n, const
 	const int literal = (flags & ADACOM_LITERAL) ? 1 : 0;
 	if (on_device) {
 		LAUNCH(ctx, launch_fetch_rows(col->t, col->d_desc, col->raw, n, seg_idx, row_in_seg, literal, out, ctx->stream));
+		return ADACOM_OK;
+	}
+	if (n <= kSmallFetch) {
+		// [segments | rows | answers] in the host-mapped page: one launch, one synchronisation
+		uint32_t *h_seg = (uint32_t *)ctx->h_small, *h_row = h_seg + kSmallFetch;
+		for (uint64_t q = 0; q < n; q++) {
+			if (seg_idx[q] >= col->n_segs || row_in_seg[q] >= col->h_desc[seg_idx[q]].count) {
+				return fail(ctx, ADACOM_ERR_INVALID, "adacom_fetch_rows: (segment, row) out of range");
+			}
+			h_seg[q] = seg_idx[q];
+			h_row[q] = row_in_seg[q];
+		}
+		const uint32_t *d_seg = (const uint32_t *)ctx->d_small;
+		LAUNCH(ctx, launch_fetch_rows(col->t, col->d_desc, col->raw, n, d_seg, d_seg + kSmallFetch, literal,
+		                              ctx->d_small + kSmallFetch * 8, ctx->stream));
+		CK(ctx, cudaStreamSynchronize(ctx->stream));
+		memcpy(out, ctx->h_small + kSmallFetch * 8, n * col->t.size);
 		return ADACOM_OK;
 	}
 	// validated and copied into the pinned staging buffer in one pass: [segments | rows | answers]

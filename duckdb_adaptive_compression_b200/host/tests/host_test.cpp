@@ -283,12 +283,23 @@ void RunColumnData(PhysicalType type, idx_t n, uint64_t span, int64_t base, bool
 		for (int rep = 0; rep < 50; rep++) {
 			db.column_segment_catalog.AddReadAccess(col.segments[1].get());
 		}
+		std::vector<idx_t> sizes_before;
+		for (auto &s : col.segments) {
+			sizes_before.push_back(s->GetDataSize());
+		}
 		auto res = db.column_segment_catalog.RunCompactionEpoch();
 		CHECK(res.first + res.second == col.segments.size());
 		CHECK(!col.segments[1]->IsBitCompressed());
 		CHECK(col.segments[1]->GetDataSize() == col.segments[1]->SegmentSize());
 		idx_t after = db.column_segment_catalog.GetTotalDataSize();
-		CHECK(after > total);
+		// every uncompacted segment is back at the flat block size (262136 B; its succinct image may have been
+		// LARGER: a slot-width int_vector carries a 9-byte header -- INT16 with a negative base under the adaptive
+		// encoder's zero-extended min/max does not shrink, quirk Q2b)
+		idx_t expect_after = 0;
+		for (size_t g = 0; g < col.segments.size(); g++) {
+			expect_after += col.segments[g]->IsBitCompressed() ? sizes_before[g] : col.segments[g]->SegmentSize();
+		}
+		CHECK(after == expect_after && after != total);
 		CHECK(db.buffer_manager.GetDataSize() == after);
 		full_scan();  // values unchanged; non-adaptive mode re-compacts lazily, adaptive serves the flat image
 		if (adaptive) {

@@ -20,6 +20,11 @@ def _dev_words(n_words):
     return torch.zeros(max(n_words, 1) + 2, dtype=torch.int64, device="cuda:0")
 
 
+def _sync():
+    import torch
+    torch.cuda.synchronize()
+
+
 def _to_np(t, n_words):
     return t.cpu().numpy().view(np.uint64)[:n_words].copy()
 
@@ -77,6 +82,7 @@ def _check_filter_bitmaps(gpu_ctx, port_oracle, dtype, cases, ranges):
         for op in range(6):
             for const in _constants(dtype, segs[b:e], rng):
                 bm.fill_(-1)  # the call must zero it
+                _sync()       # fill_ runs on torch's stream, the codec on its own: order them
                 got = col.scan_filter(op, const, b, e, device_bitmap=bm.data_ptr())
                 want_bm = np.zeros(nw, dtype=np.uint64)
                 wsum = wcnt = 0
@@ -152,6 +158,7 @@ def test_scan_select_nulls_conjunctions(gpu_ctx, port_oracle, dtype):
             preds = [(p[0], p[1], lo if p[2] is None else hi) if p[0] == "cmp" else p for p in tmpl]
             use_in = k % 2 == 1
             bm_out.fill_(-1)
+            _sync()
             got, got_valid = col.scan_select(preds, conj, validity=words, seg_begin=b, seg_end=e,
                                              bitmap_in=bm_in.data_ptr() if use_in else None,
                                              bitmap_out=bm_out.data_ptr())
