@@ -500,8 +500,8 @@ class Column:
         self.ctx.check(self.lib.adacom_uncompact(self.h, b, e, flags))
 
     def download_raw(self) -> np.ndarray:
-        """Test helper: read the raw arena back through a decode of never-compacted state is not possible,
-        so this copies via scan of each segment (raw segments scan as identity)."""
+        """Test helper: the current values of every segment as one flat array (one batched decode: segments that are not
+        re-packed decode as their slot-width image)."""
         return self.decode()
 
     def scan_sum(self, seg_begin=0, seg_end=None, flags=0) -> AggResult:

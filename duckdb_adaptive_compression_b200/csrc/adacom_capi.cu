@@ -16,6 +16,7 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <tuple>
 #include <vector>
 
 using namespace adacom;
@@ -1709,6 +1710,60 @@ static adacom_status plan_scan_columns(adacom_ctx *ctx, const adacom_scan_term *
 			qa.mul[k] = sums[g].mul[k];
 		}
 	}
+	// the factor program of the dense kernel: aggregates sorted by their factor lists, so that a list which extends the
+	// previous one continues its term (the products are the same numbers, only evaluated once)
+	{
+		std::vector<uint32_t> order(n_sums);
+		for (uint32_t g = 0; g < n_sums; g++) {
+			order[g] = g;
+		}
+		auto key = [&](uint32_t g, uint32_t k) {
+			return std::make_tuple(q.aggs[g].col[k], q.aggs[g].add[k], q.aggs[g].mul[k]);
+		};
+		std::stable_sort(order.begin(), order.end(), [&](uint32_t l, uint32_t r) {
+			const uint32_t nl = q.aggs[l].n_factors, nr = q.aggs[r].n_factors;
+			for (uint32_t k = 0; k < std::min(nl, nr); k++) {
+				if (key(l, k) != key(r, k)) {
+					return key(l, k) < key(r, k);
+				}
+			}
+			return nl < nr;
+		});
+		q.n_steps = 0;
+		int prev = -1;  // aggregate whose full product the running term holds
+		for (uint32_t g : order) {
+			const QueryAgg &qa = q.aggs[g];
+			uint32_t shared = 0;
+			if (prev >= 0 && q.aggs[prev].n_factors > 0 && q.aggs[prev].n_factors <= qa.n_factors) {
+				shared = q.aggs[prev].n_factors;
+				for (uint32_t k = 0; k < shared; k++) {
+					if (key((uint32_t)prev, k) != key(g, k)) {
+						shared = 0;
+						break;
+					}
+				}
+			}
+			if (qa.n_factors == shared || qa.n_factors == 0) {
+				// COUNT(*) (term = 1), or the same product again: one step with x = 1
+				QueryStep &st = q.steps[q.n_steps++];
+				st.add = 1;
+				st.mul = 0;
+				st.col = 0;
+				st.fresh = qa.n_factors == 0 ? 1 : 0;
+				st.emit = (uint8_t)(g + 1);
+			} else {
+				for (uint32_t k = shared; k < qa.n_factors; k++) {
+					QueryStep &st = q.steps[q.n_steps++];
+					st.add = qa.add[k];
+					st.mul = qa.mul[k];
+					st.col = (uint16_t)qa.col[k];
+					st.fresh = k == 0 ? 1 : 0;
+					st.emit = k + 1 == qa.n_factors ? (uint8_t)(g + 1) : 0;
+				}
+			}
+			prev = qa.n_factors ? (int)g : -1;
+		}
+	}
 	// 64-bit products: bound |value| per term from the analyzed min / max of the scanned segments (type range when a
 	// segment was never analyzed or mixes signs), then every prod_k (|add| + |mul| * bound) against 2^62
 	long double max_prod = ldexpl(1.0L, 70);
@@ -1876,7 +1931,7 @@ static adacom_status plan_scan_columns(adacom_ctx *ctx, const adacom_scan_term *
 			win += (uint64_t)kDenseBlockRows * wmax / 8 + 48;
 		}
 		win = (win + 127) & ~127ull;
-		const uint64_t smem = 4 * win + (uint64_t)kQueryMaxCols * kDenseThreads * 8 + (uint64_t)n_groups * n_sums * kDenseThreads * 8 +
+		const uint64_t smem = 4 * win + 4ull * kQueryMaxSteps * 32 + (uint64_t)n_groups * n_sums * kDenseThreads * 8 +
 		                      (uint64_t)n_groups * kDenseThreads * 4;
 		if (ok && smem <= 100u * 1024u) {
 			std::vector<uint64_t> key = {row_begin, row_end, n_terms};

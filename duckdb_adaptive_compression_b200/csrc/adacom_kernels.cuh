@@ -88,6 +88,20 @@ struct QueryAgg {  // sum over the selected rows of prod_k (add[k] + mul[k] * va
 	int64_t mul[kQueryMaxFactors] = {0, 0, 0};
 };
 
+// The sum expressions of a query flattened into one factor program (scan_columns_dense_kernel): per step
+// x = add + mul * value(col); term = fresh ? x : term * x; if (emit) accumulator[emit - 1] += term.  The planner orders
+// the aggregates so that one whose factor list extends another's continues that term (TPC-H Q1: price, price*(100-d),
+// price*(100-d)*(100+t) are three steps, not six), and the kernel walks the program in a real loop: the unrolled
+// kQueryMaxAggs x kQueryMaxFactors form issued every predicated-off slot for every row.
+struct QueryStep {
+	int64_t add = 0, mul = 0;
+	uint16_t col = 0;
+	uint8_t fresh = 1;
+	uint8_t emit = 0;   // 0: keep going; else index of the aggregate + 1
+	uint32_t reserved = 0;
+};
+constexpr int kQueryMaxSteps = kQueryMaxAggs * kQueryMaxFactors;
+
 // a run of table rows inside which every referenced column is ONE segment (scan_columns_dense_kernel)
 struct DenseRange {
 	uint64_t row_begin;
@@ -101,6 +115,8 @@ constexpr uint32_t kDenseThreads = 128;
 struct QueryArgs {
 	QueryCol cols[kQueryMaxCols];
 	QueryAgg aggs[kQueryMaxAggs];
+	QueryStep steps[kQueryMaxSteps];
+	uint32_t n_steps = 0;
 	uint32_t n_cols = 0, n_aggs = 0;
 	uint32_t factor_mask = 0;             // columns some sum expression reads
 	uint64_t row_begin = 0, row_end = 0;  // table rows; row_begin is a multiple of 2048
@@ -125,6 +141,7 @@ struct QueryArgs {
 	                                      // count = selected rows (of the group)
 };
 
+static_assert(sizeof(QueryArgs) <= 4000, "QueryArgs travels as a kernel parameter");
 cudaError_t launch_scan_columns(const QueryArgs &args, int sm_count, cudaStream_t stream);
 // extra dynamic shared memory of a grouped launch (bytes); dense: + the per-thread accumulators
 uint32_t scan_columns_group_smem(uint32_t n_groups, uint32_t n_aggs, uint32_t dense);

@@ -1294,6 +1294,17 @@ __global__ void __launch_bounds__(kSWarps * 32, 4) scan_columns_sparse_kernel(co
 // =====================================================================================================================
 constexpr int kDWarps = 4;
 constexpr int kDThreads = kDWarps * 32;
+
+// one step of the factor program resolved against the current block (per warp, in shared memory)
+struct __align__(16) DenseStep {
+	uint32_t win_off;    // byte offset of the column's staged piece inside the warp's window
+	uint32_t bit_base;   // bit position of the block's first row inside it
+	uint32_t w_flags;    // width | fresh << 8 | emit << 16
+	uint32_t mask;
+	long long base;      // add + mul * extend(min)
+	long long mul;
+};
+static_assert(sizeof(DenseStep) == 32, "two 16-byte broadcast loads per step");
 constexpr uint32_t kDRows = 1024;
 
 template <int NA, bool N32>
@@ -1303,11 +1314,10 @@ __global__ void __launch_bounds__(kDThreads, 4) scan_columns_dense_kernel(const 
 	extern __shared__ __align__(128) uint8_t d_mem[];
 	__shared__ uint64_t red[96];
 	const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-	// dynamic shared memory: windows | per-thread values [col][thread] | accumulators [group][agg][thread] | counts
+	// dynamic shared memory: windows | per-warp step tables | accumulators [group][agg][thread] | counts
 	uint8_t *window = d_mem + (size_t)warp * window_bytes;
-	long long *vals = (long long *)(d_mem + (size_t)kDWarps * window_bytes);
-	int *vals32 = (int *)vals;  // N32: the same slice holds 32-bit values
-	long long *dacc = vals + (size_t)kQueryMaxCols * kDThreads;
+	DenseStep *tab = (DenseStep *)(d_mem + (size_t)kDWarps * window_bytes) + (size_t)warp * kQueryMaxSteps;
+	long long *dacc = (long long *)(d_mem + (size_t)kDWarps * window_bytes + (size_t)kDWarps * kQueryMaxSteps * sizeof(DenseStep));
 	uint32_t *dcnt = (uint32_t *)(dacc + (size_t)a.n_groups * a.n_aggs * kDThreads);
 	for (uint32_t i = tid; i < a.n_groups * a.n_aggs * kDThreads; i += kDThreads) {
 		dacc[i] = 0ll;
@@ -1318,7 +1328,9 @@ __global__ void __launch_bounds__(kDThreads, 4) scan_columns_dense_kernel(const 
 	__syncthreads();
 	const bool active = lane < a.n_cols;
 	const QueryCol &mycol = a.cols[active ? lane : 0];
-	const uint32_t need_mask = a.factor_mask | (1u << a.group_col);
+	// my step of the factor program (lane = step) and the column it reads
+	const QueryStep &mystep = a.steps[lane < a.n_steps ? lane : 0];
+	const uint32_t step_col = mystep.col;
 	// per-lane segment cache (lane = column)
 	uint32_t c_seg = ~0u, c_w = 0;
 	uint64_t c_rs = 0, c_words = 0, c_vbase = 0, c_flo = ~0ull, c_span = 0;
@@ -1419,62 +1431,85 @@ __global__ void __launch_bounds__(kDThreads, 4) scan_columns_dense_kernel(const 
 			if (!__any_sync(0xffffffffu, sel != 0)) {
 				continue;
 			}
-			// ---- rows: lane = row, group by group; the per-column parameters of the block stay in registers ----
-			uint32_t pw[kQueryMaxCols], pbb[kQueryMaxCols];
-			const uint32_t *pwin[kQueryMaxCols];
-			uint64_t pvb[kQueryMaxCols];
-#pragma unroll
-			for (int c = 0; c < kQueryMaxCols; c++) {
-				pw[c] = __shfl_sync(0xffffffffu, c_w, c);
-				pbb[c] = __shfl_sync(0xffffffffu, bit_base, c);
-				pwin[c] = (const uint32_t *)(window + __shfl_sync(0xffffffffu, smem_off, c));
-				pvb[c] = __shfl_sync(0xffffffffu, c_vbase, c);
+			// ---- the block's step table: lane s resolves step s against the piece of the column it reads.  A value is
+			// extend(min) + field, so x = add + mul * value = (add + mul * extend(min)) + mul * field: the row loop never
+			// materialises the value (each column of TPC-H Q1 is read by exactly one step) ----
+			{
+				const uint32_t sw = __shfl_sync(0xffffffffu, c_w, step_col);
+				const uint32_t sbb = __shfl_sync(0xffffffffu, bit_base, step_col);
+				const uint32_t soff = __shfl_sync(0xffffffffu, smem_off, step_col);
+				const uint64_t svb = __shfl_sync(0xffffffffu, c_vbase, step_col);
+				__syncwarp();  // the previous block's rows are done with the table
+				if (lane < a.n_steps) {
+					DenseStep e;
+					e.win_off = soff;
+					e.bit_base = sbb;
+					e.w_flags = sw | ((uint32_t)mystep.fresh << 8) | ((uint32_t)mystep.emit << 16);
+					e.mask = 0xffffffffu >> (32u - sw);
+					e.base = (long long)((unsigned long long)mystep.add + (unsigned long long)mystep.mul * svb);
+					e.mul = mystep.mul;
+					tab[lane] = e;
+				}
+				__syncwarp();
 			}
+			const uint32_t gw = __shfl_sync(0xffffffffu, c_w, a.group_col);
+			const uint32_t gbb = __shfl_sync(0xffffffffu, bit_base, a.group_col);
+			const uint32_t *gwin = (const uint32_t *)(window + __shfl_sync(0xffffffffu, smem_off, a.group_col));
+			const uint64_t gvb = __shfl_sync(0xffffffffu, c_vbase, a.group_col);
+			const uint32_t gmask = 0xffffffffu >> (32u - gw);
+			// ---- rows: lane = row, TWO 32-row groups per iteration (two independent dependency chains per lane: the
+			// kernel is latency-bound at 12 warps per SM) ----
 #pragma unroll 1
-			for (uint32_t gg = 0; gg < n_groups32; gg++) {
-				const uint32_t word = __shfl_sync(0xffffffffu, sel, gg);
-				if (word == 0) {
+			for (uint32_t gg = 0; gg < n_groups32; gg += 2u) {
+				const uint32_t word0 = __shfl_sync(0xffffffffu, sel, gg);
+				const uint32_t word1 = gg + 1u < n_groups32 ? __shfl_sync(0xffffffffu, sel, (gg + 1u) & 31u) : 0u;
+				if ((word0 | word1) == 0) {
 					continue;
 				}
-				const bool on = (word >> lane) & 1u;
-				const uint32_t i = gg * 32u + lane;
-#pragma unroll
-				for (int c = 0; c < kQueryMaxCols; c++) {
-					if ((need_mask >> c) & 1u) {  // uniform
-						const uint32_t f = read_bits32(pwin[c], pbb[c] + i * pw[c]) & (0xffffffffu >> (32u - pw[c]));
-						if (N32) {
-							vals32[c * kDThreads + tid] = (int)((uint32_t)pvb[c] + f);
-						} else {
-							vals[c * kDThreads + tid] = (long long)(pvb[c] + (uint64_t)f);
+				const uint32_t i0 = gg * 32u + lane;
+				const uint32_t i1 = gg + 1u < n_groups32 ? i0 + 32u : i0;
+				const uint32_t f0 = read_bits32(gwin, gbb + i0 * gw) & gmask, f1 = read_bits32(gwin, gbb + i1 * gw) & gmask;
+				const uint64_t kv0 = N32 ? (uint64_t)(long long)(int)((uint32_t)gvb + f0) : gvb + (uint64_t)f0;
+				const uint64_t kv1 = N32 ? (uint64_t)(long long)(int)((uint32_t)gvb + f1) : gvb + (uint64_t)f1;
+				const bool ok0 = ((word0 >> lane) & 1u) && kv0 < (uint64_t)a.n_groups;
+				const bool ok1 = ((word1 >> lane) & 1u) && kv1 < (uint64_t)a.n_groups;
+				long long *slot0 = dacc + (size_t)(ok0 ? kv0 : 0) * a.n_aggs * kDThreads + tid;
+				long long *slot1 = dacc + (size_t)(ok1 ? kv1 : 0) * a.n_aggs * kDThreads + tid;
+				long long term0 = 0, term1 = 0;
+#pragma unroll 1
+				for (uint32_t st = 0; st < a.n_steps; st++) {
+					const DenseStep e = tab[st];  // broadcast
+					const uint32_t *win32 = (const uint32_t *)(window + e.win_off);
+					const uint32_t w = e.w_flags & 0xffu;
+					const uint32_t g0 = read_bits32(win32, e.bit_base + i0 * w) & e.mask;
+					const uint32_t g1 = read_bits32(win32, e.bit_base + i1 * w) & e.mask;
+					long long x0, x1;
+					if (N32) {
+						// every value and every factor fits int32 (planner: narrow_values); wrap-around arithmetic
+						x0 = (long long)(int)((uint32_t)e.base + (uint32_t)e.mul * g0);
+						x1 = (long long)(int)((uint32_t)e.base + (uint32_t)e.mul * g1);
+					} else {
+						x0 = e.base + e.mul * (long long)g0;
+						x1 = e.base + e.mul * (long long)g1;
+					}
+					const bool fresh = (e.w_flags >> 8) & 1u;
+					term0 = fresh ? x0 : term0 * x0;
+					term1 = fresh ? x1 : term1 * x1;
+					const uint32_t emit = e.w_flags >> 16;
+					if (emit) {  // uniform
+						if (ok0) {
+							slot0[(size_t)(emit - 1u) * kDThreads] += term0;
+						}
+						if (ok1) {
+							slot1[(size_t)(emit - 1u) * kDThreads] += term1;
 						}
 					}
 				}
-				const uint64_t kv = N32 ? (uint64_t)(long long)vals32[a.group_col * kDThreads + tid]
-				                        : (uint64_t)vals[a.group_col * kDThreads + tid];
-				if (on && kv < (uint64_t)a.n_groups) {
-					long long *slot = dacc + (size_t)kv * a.n_aggs * kDThreads + tid;
-#pragma unroll
-					for (int kk = 0; kk < NA; kk++) {
-						if (kk < (int)a.n_aggs) {  // uniform
-							const QueryAgg &qa = a.aggs[kk];
-							long long term = 1;
-#pragma unroll
-							for (int f = 0; f < kQueryMaxFactors; f++) {
-								if (f < (int)qa.n_factors) {
-									if (N32) {
-										// every value and every factor fits int32 (planner: narrow_values): a 32-bit multiply-add per
-										// factor and one widening multiply per extra factor
-										const int x = (int)qa.add[f] + (int)qa.mul[f] * vals32[qa.col[f] * kDThreads + tid];
-										term *= (long long)x;
-									} else {
-										term *= qa.add[f] + qa.mul[f] * vals[qa.col[f] * kDThreads + tid];
-									}
-								}
-							}
-							slot[(size_t)kk * kDThreads] += term;
-						}
-					}
-					dcnt[(uint32_t)kv * kDThreads + tid] += 1u;
+				if (ok0) {
+					dcnt[(uint32_t)kv0 * kDThreads + tid] += 1u;
+				}
+				if (ok1) {
+					dcnt[(uint32_t)kv1 * kDThreads + tid] += 1u;
 				}
 			}
 		}
@@ -1525,7 +1560,7 @@ cudaError_t launch_scan_columns(const QueryArgs &args, int sm_count, cudaStream_
 	int dev = 0;
 	cudaGetDevice(&dev);
 	if (args.n_groups && args.dense_ranges != nullptr && args.in_bitmap == nullptr && args.out_bitmap == nullptr) {
-		const size_t smem = (size_t)kDWarps * args.dense_window + (size_t)kQueryMaxCols * kDThreads * 8 +
+		const size_t smem = (size_t)kDWarps * args.dense_window + (size_t)kDWarps * kQueryMaxSteps * sizeof(DenseStep) +
 		                    (size_t)args.n_groups * args.n_aggs * kDThreads * 8 + (size_t)args.n_groups * kDThreads * 4;
 		void (*kernel)(const QueryArgs, const DenseRange *, uint32_t, uint32_t, uint32_t);
 		if (args.narrow_values) {

@@ -80,6 +80,40 @@ def test_grouped_scan_matches_per_group_passes_on_ragged_data(gpu_ctx):
         col.close()
 
 
+def test_grouped_factor_program_chains_and_duplicates(gpu_ctx):
+    """The dense grouped kernel evaluates the sums as one factor program in which an aggregate that extends another's
+    factor list continues its term: shared prefixes in any order, the same product twice, COUNT(*) between them, a
+    product over the same column twice, unrelated sums.  Narrow columns so that the dense kernel (32-bit values) runs."""
+    rng = np.random.default_rng(11)
+    n = 5 * 122880 + 4321
+    key = rng.integers(0, 4, size=n).astype(np.uint8)
+    p = rng.integers(900, 100000, size=n).astype(np.int32)
+    d = rng.integers(0, 11, size=n).astype(np.uint8)
+    t = rng.integers(0, 9, size=n).astype(np.uint8)
+    s = rng.integers(0, 3000, size=n).astype(np.int16)
+    cols = {}
+    for name, v in (("key", key), ("p", p), ("d", d), ("t", t), ("s", s)):
+        cols[name] = gpu_ctx.column_from_values(v, adacom.row_group_segment_counts(n, v.dtype))
+        cols[name].compact()
+    terms = [(cols["s"], (0, 2700)), (cols["key"], None), (cols["p"], None), (cols["d"], None), (cols["t"], None)]
+    P, D, T = (2, 0, 1), (3, 100, -1), (4, 100, 1)
+    sums = [[P, D, T], [], [P], [P, D], [(3, 0, 1)], [P, D], [(3, 0, 1), (3, 0, 1)], [T, P]]
+    sel = s <= 2700
+    po, do, to = p.astype(object), d.astype(object), t.astype(object)
+    exprs = [po * (100 - do) * (100 + to), None, po, po * (100 - do), do, po * (100 - do), do * do, (100 + to) * po]
+    for rows in ((0, n), (2048 * 7, n - 3)):
+        got = adacom.scan_columns(gpu_ctx, terms, sums, rows[0], rows[1], group_by=(1, 4))
+        for g in range(4):
+            m = sel & (key == g)
+            m[:rows[0]] = False
+            m[rows[1]:] = False
+            want = [int(m.sum()) if e is None else int(e[m].sum()) for e in exprs]
+            assert [r.sum for r in got[g]] == want, (rows, g)
+            assert all(r.count == int(m.sum()) for r in got[g])
+    for col in cols.values():
+        col.close()
+
+
 def test_q1_matches_numpy(table):
     cols, t = table
     assert t.q1() == tpch.q1_expected(cols)
