@@ -1294,6 +1294,7 @@ __global__ void __launch_bounds__(kSWarps * 32, 4) scan_columns_sparse_kernel(co
 // =====================================================================================================================
 constexpr int kDWarps = 4;
 constexpr int kDThreads = kDWarps * 32;
+constexpr int kDIlp = 4;  // 32-row groups a lane works on at a time
 
 // one step of the factor program resolved against the current block (per warp, in shared memory)
 struct __align__(16) DenseStep {
@@ -1305,7 +1306,7 @@ struct __align__(16) DenseStep {
 	long long mul;
 };
 static_assert(sizeof(DenseStep) == 32, "two 16-byte broadcast loads per step");
-constexpr uint32_t kDRows = 1024;
+constexpr uint32_t kDRows = kDenseBlockRows;
 
 template <int NA, bool N32>
 __global__ void __launch_bounds__(kDThreads, 4) scan_columns_dense_kernel(const QueryArgs a, const DenseRange *ranges,
@@ -1457,59 +1458,68 @@ __global__ void __launch_bounds__(kDThreads, 4) scan_columns_dense_kernel(const 
 			const uint32_t *gwin = (const uint32_t *)(window + __shfl_sync(0xffffffffu, smem_off, a.group_col));
 			const uint64_t gvb = __shfl_sync(0xffffffffu, c_vbase, a.group_col);
 			const uint32_t gmask = 0xffffffffu >> (32u - gw);
-			// ---- rows: lane = row, TWO 32-row groups per iteration (two independent dependency chains per lane: the
+			// ---- rows: lane = row, kDIlp 32-row groups per iteration (independent dependency chains per lane: the
 			// kernel is latency-bound at 12 warps per SM) ----
 #pragma unroll 1
-			for (uint32_t gg = 0; gg < n_groups32; gg += 2u) {
-				const uint32_t word0 = __shfl_sync(0xffffffffu, sel, gg);
-				const uint32_t word1 = gg + 1u < n_groups32 ? __shfl_sync(0xffffffffu, sel, (gg + 1u) & 31u) : 0u;
-				if ((word0 | word1) == 0) {
+			for (uint32_t gg = 0; gg < n_groups32; gg += kDIlp) {
+				uint32_t word[kDIlp], idx[kDIlp];
+				uint32_t any = 0;
+#pragma unroll
+				for (int r = 0; r < kDIlp; r++) {
+					const bool in = gg + r < n_groups32;
+					word[r] = in ? __shfl_sync(0xffffffffu, sel, (gg + r) & 31u) : 0u;
+					idx[r] = (in ? gg + r : gg) * 32u + lane;
+					any |= word[r];
+				}
+				if (any == 0) {
 					continue;
 				}
-				const uint32_t i0 = gg * 32u + lane;
-				const uint32_t i1 = gg + 1u < n_groups32 ? i0 + 32u : i0;
-				const uint32_t f0 = read_bits32(gwin, gbb + i0 * gw) & gmask, f1 = read_bits32(gwin, gbb + i1 * gw) & gmask;
-				const uint64_t kv0 = N32 ? (uint64_t)(long long)(int)((uint32_t)gvb + f0) : gvb + (uint64_t)f0;
-				const uint64_t kv1 = N32 ? (uint64_t)(long long)(int)((uint32_t)gvb + f1) : gvb + (uint64_t)f1;
-				const bool ok0 = ((word0 >> lane) & 1u) && kv0 < (uint64_t)a.n_groups;
-				const bool ok1 = ((word1 >> lane) & 1u) && kv1 < (uint64_t)a.n_groups;
-				long long *slot0 = dacc + (size_t)(ok0 ? kv0 : 0) * a.n_aggs * kDThreads + tid;
-				long long *slot1 = dacc + (size_t)(ok1 ? kv1 : 0) * a.n_aggs * kDThreads + tid;
-				long long term0 = 0, term1 = 0;
+				bool ok[kDIlp];
+				uint32_t kvi[kDIlp];
+				long long *slot[kDIlp];
+				long long term[kDIlp];
+#pragma unroll
+				for (int r = 0; r < kDIlp; r++) {
+					const uint32_t f = read_bits32(gwin, gbb + idx[r] * gw) & gmask;
+					const uint64_t kv = N32 ? (uint64_t)(long long)(int)((uint32_t)gvb + f) : gvb + (uint64_t)f;
+					ok[r] = ((word[r] >> lane) & 1u) && kv < (uint64_t)a.n_groups;
+					kvi[r] = ok[r] ? (uint32_t)kv : 0u;
+					slot[r] = dacc + (size_t)kvi[r] * a.n_aggs * kDThreads + tid;
+					term[r] = 0;
+				}
 #pragma unroll 1
 				for (uint32_t st = 0; st < a.n_steps; st++) {
 					const DenseStep e = tab[st];  // broadcast
 					const uint32_t *win32 = (const uint32_t *)(window + e.win_off);
 					const uint32_t w = e.w_flags & 0xffu;
-					const uint32_t g0 = read_bits32(win32, e.bit_base + i0 * w) & e.mask;
-					const uint32_t g1 = read_bits32(win32, e.bit_base + i1 * w) & e.mask;
-					long long x0, x1;
-					if (N32) {
-						// every value and every factor fits int32 (planner: narrow_values); wrap-around arithmetic
-						x0 = (long long)(int)((uint32_t)e.base + (uint32_t)e.mul * g0);
-						x1 = (long long)(int)((uint32_t)e.base + (uint32_t)e.mul * g1);
-					} else {
-						x0 = e.base + e.mul * (long long)g0;
-						x1 = e.base + e.mul * (long long)g1;
-					}
 					const bool fresh = (e.w_flags >> 8) & 1u;
-					term0 = fresh ? x0 : term0 * x0;
-					term1 = fresh ? x1 : term1 * x1;
+#pragma unroll
+					for (int r = 0; r < kDIlp; r++) {
+						const uint32_t g = read_bits32(win32, e.bit_base + idx[r] * w) & e.mask;
+						long long x;
+						if (N32) {
+							// every value and every factor fits int32 (planner: narrow_values); wrap-around arithmetic
+							x = (long long)(int)((uint32_t)e.base + (uint32_t)e.mul * g);
+						} else {
+							x = e.base + e.mul * (long long)g;
+						}
+						term[r] = fresh ? x : term[r] * x;
+					}
 					const uint32_t emit = e.w_flags >> 16;
 					if (emit) {  // uniform
-						if (ok0) {
-							slot0[(size_t)(emit - 1u) * kDThreads] += term0;
-						}
-						if (ok1) {
-							slot1[(size_t)(emit - 1u) * kDThreads] += term1;
+#pragma unroll
+						for (int r = 0; r < kDIlp; r++) {
+							if (ok[r]) {
+								slot[r][(size_t)(emit - 1u) * kDThreads] += term[r];
+							}
 						}
 					}
 				}
-				if (ok0) {
-					dcnt[(uint32_t)kv0 * kDThreads + tid] += 1u;
-				}
-				if (ok1) {
-					dcnt[(uint32_t)kv1 * kDThreads + tid] += 1u;
+#pragma unroll
+				for (int r = 0; r < kDIlp; r++) {
+					if (ok[r]) {
+						dcnt[kvi[r] * kDThreads + tid] += 1u;
+					}
 				}
 			}
 		}
