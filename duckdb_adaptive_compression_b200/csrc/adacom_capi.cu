@@ -70,6 +70,16 @@ struct adacom_ctx {
 	std::vector<ScanRing> ring_cache;
 };
 
+// Every entry point that touches the device holds the context mutex AND makes the context's device current: one
+// process may drive several GPUs (one context each, row group g -> device g mod G), and a host thread's current device
+// is whatever its last call left behind.
+struct CtxLock {
+	explicit CtxLock(adacom_ctx *ctx) : guard(ctx->mu) {
+		cudaSetDevice(ctx->device);
+	}
+	std::lock_guard<std::mutex> guard;
+};
+
 struct Extent {
 	uint64_t *base = nullptr;
 	uint64_t words = 0;      // payload words in use (incl. alignment gaps)
@@ -461,6 +471,7 @@ extern "C" adacom_status adacom_event_create(adacom_ctx *ctx, void **event_out) 
 		return ADACOM_ERR_INVALID;
 	}
 	cudaEvent_t ev;
+	CK(ctx, cudaSetDevice(ctx->device));  // an event belongs to the device that was current when it was created
 	CK(ctx, cudaEventCreate(&ev));
 	*event_out = (void *)ev;
 	return ADACOM_OK;
@@ -513,7 +524,7 @@ extern "C" adacom_status adacom_flush_l2(adacom_ctx *ctx) {
 	if (!ctx) {
 		return ADACOM_ERR_INVALID;
 	}
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	if (!ctx->flush_buf) {
 		ctx->flush_bytes = (size_t)256 << 20;  // 2x the 126 MB L2
 		CK(ctx, cudaMalloc(&ctx->flush_buf, ctx->flush_bytes));
@@ -553,7 +564,7 @@ extern "C" adacom_status adacom_column_create(adacom_ctx *ctx, adacom_ptype type
 		return fail(ctx, ADACOM_ERR_INVALID, "adacom_column_create: NULL argument");
 	}
 	*out = nullptr;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	CK(ctx, cudaSetDevice(ctx->device));
 	adacom_column *col = nullptr;
 	adacom_status st = column_alloc(ctx, type, n_segments, &col);
@@ -621,7 +632,7 @@ extern "C" void adacom_column_destroy(adacom_column *col) {
 		return;
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	cudaSetDevice(ctx->device);
 	cudaStreamSynchronize(ctx->stream);
 	for (auto &x : col->extents) {
@@ -670,7 +681,7 @@ extern "C" adacom_status adacom_column_upload_raw(adacom_column *col, const void
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_column_upload_raw: bad range");
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	adacom_status st = ensure_raw(col);
 	if (st != ADACOM_OK) {
 		return st;
@@ -685,7 +696,7 @@ extern "C" adacom_status adacom_column_release_raw(adacom_column *col) {
 		return ADACOM_ERR_INVALID;
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	adacom_status st = sync_mirror(col);
 	if (st != ADACOM_OK) {
 		return st;
@@ -708,7 +719,7 @@ extern "C" adacom_status adacom_column_from_packed(adacom_ctx *ctx, adacom_ptype
 		return fail(ctx, ADACOM_ERR_INVALID, "adacom_column_from_packed: NULL argument");
 	}
 	*out = nullptr;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	CK(ctx, cudaSetDevice(ctx->device));
 	adacom_column *col = nullptr;
 	adacom_status st = column_alloc(ctx, type, n_segments, &col);
@@ -804,7 +815,7 @@ extern "C" adacom_status adacom_column_fill_splitmix(adacom_column *col, uint64_
 		return ADACOM_ERR_INVALID;
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	adacom_status st = ensure_raw(col);
 	if (st != ADACOM_OK) {
 		return st;
@@ -823,7 +834,7 @@ extern "C" adacom_status adacom_analyze(adacom_column *col, uint64_t seg_begin, 
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_analyze: bad segment range");
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	if (!col->raw) {
 		return fail(ctx, ADACOM_ERR_STATE, "adacom_analyze: the raw arena was released");
 	}
@@ -967,7 +978,7 @@ extern "C" adacom_status adacom_encode(adacom_column *col, uint64_t seg_begin, u
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_encode: bad segment range");
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	if (!col->raw) {
 		return fail(ctx, ADACOM_ERR_STATE, "adacom_encode: the raw arena was released");
 	}
@@ -1024,7 +1035,7 @@ extern "C" adacom_status adacom_analyze_list(adacom_column *col, uint64_t n, con
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_analyze_list: bad arguments");
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	if (!col->raw) {
 		return fail(ctx, ADACOM_ERR_STATE, "adacom_analyze_list: the raw arena was released");
 	}
@@ -1048,7 +1059,7 @@ extern "C" adacom_status adacom_encode_list(adacom_column *col, uint64_t n, cons
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_encode_list: bad arguments");
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	if (!col->raw) {
 		return fail(ctx, ADACOM_ERR_STATE, "adacom_encode_list: the raw arena was released");
 	}
@@ -1070,7 +1081,7 @@ extern "C" adacom_status adacom_uncompact_list(adacom_column *col, uint64_t n, c
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_uncompact_list: bad arguments");
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	if (n == 0) {
 		return ADACOM_OK;
 	}
@@ -1111,7 +1122,7 @@ extern "C" adacom_status adacom_column_get_meta(adacom_column *col, uint64_t seg
 	if (!range_ok(col, seg_begin, seg_end) || (!out && seg_end > seg_begin)) {
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_column_get_meta: bad arguments");
 	}
-	std::lock_guard<std::mutex> lock(col->ctx->mu);
+	CtxLock lock(col->ctx);
 	adacom_status st = sync_mirror(col);
 	if (st != ADACOM_OK) {
 		return st;
@@ -1127,7 +1138,7 @@ extern "C" adacom_status adacom_column_data_size(adacom_column *col, uint64_t se
 	if (!range_ok(col, seg_begin, seg_end) || !out) {
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_column_data_size: bad arguments");
 	}
-	std::lock_guard<std::mutex> lock(col->ctx->mu);
+	CtxLock lock(col->ctx);
 	adacom_status st = sync_mirror(col);
 	if (st != ADACOM_OK) {
 		return st;
@@ -1155,7 +1166,7 @@ extern "C" adacom_status adacom_column_download_packed(adacom_column *col, uint6
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_column_download_packed: bad range");
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	if (n_words) {
 		CK(ctx, cudaMemcpyAsync(host_out, col->extents[col->latest].base + first_word, n_words * 8, cudaMemcpyDeviceToHost,
 		                        ctx->stream));
@@ -1170,7 +1181,7 @@ extern "C" adacom_status adacom_segment_serialize(adacom_column *col, uint64_t s
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_segment_serialize: bad arguments");
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	adacom_status st = sync_mirror(col);
 	if (st != ADACOM_OK) {
 		return st;
@@ -1214,7 +1225,7 @@ extern "C" adacom_status adacom_decode(adacom_column *col, uint64_t seg_begin, u
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_decode: bad arguments");
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	const uint64_t rows = range_rows(col, seg_begin, seg_end);
 	if (rows == 0) {
 		return ADACOM_OK;
@@ -1249,7 +1260,7 @@ extern "C" adacom_status adacom_scan_partial(adacom_column *col, uint64_t seg, u
 	if (start + scan_count > col->h_desc[seg].count) {
 		return fail(ctx, ADACOM_ERR_INVALID, "adacom_scan_partial: scan runs past the end of the segment");
 	}
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	if (scan_count == 0) {
 		return ADACOM_OK;
 	}
@@ -1275,7 +1286,7 @@ extern "C" adacom_status adacom_uncompact(adacom_column *col, uint64_t seg_begin
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_uncompact: bad segment range");
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	if (seg_begin == seg_end) {
 		return ADACOM_OK;
 	}
@@ -1401,7 +1412,7 @@ extern "C" adacom_status adacom_scan_sum_async(adacom_column *col, uint64_t seg_
 	if (!range_ok(col, seg_begin, seg_end) || !device_out) {
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_scan_sum_async: bad arguments");
 	}
-	std::lock_guard<std::mutex> lock(col->ctx->mu);
+	CtxLock lock(col->ctx);
 	return run_agg(col, seg_begin, seg_end, flags, kModeSum, 0, 0, nullptr, (Agg *)device_out);
 }
 
@@ -1411,7 +1422,7 @@ extern "C" adacom_status adacom_scan_sum(adacom_column *col, uint64_t seg_begin,
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_scan_sum: bad arguments");
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	adacom_status st = run_agg(col, seg_begin, seg_end, flags, kModeSum, 0, 0, nullptr, ctx->d_agg);
 	if (st != ADACOM_OK) {
 		return st;
@@ -1428,7 +1439,7 @@ extern "C" adacom_status adacom_scan_filter(adacom_column *col, uint64_t seg_beg
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_scan_filter: bad arguments");
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	if (device_bitmap) {
 		uint64_t rows = range_rows(col, seg_begin, seg_end);
 		CK(ctx, cudaMemsetAsync(device_bitmap, 0, ((rows + 63) / 64) * 8, ctx->stream));
@@ -1465,7 +1476,7 @@ extern "C" adacom_status adacom_scan_select(adacom_column *col, uint64_t seg_beg
 		a.preds[p].op_mask = pr.kind == ADACOM_PRED_COMPARE ? cmp_mask_for_op(pr.op) : 0u;
 		a.preds[p].constant = (uint64_t)pr.constant;
 	}
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	const uint64_t rows = range_rows(col, seg_begin, seg_end);
 	if (device_bitmap_out && rows) {
 		CK(ctx, cudaMemsetAsync(device_bitmap_out, 0, ((rows + 63) / 64) * 8, ctx->stream));
@@ -1530,7 +1541,7 @@ extern "C" adacom_status adacom_point_filter_batch(adacom_column *col, uint64_t 
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_point_filter_batch: bad arguments");
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	if (n_queries == 0) {
 		return ADACOM_OK;
 	}
@@ -2019,7 +2030,7 @@ extern "C" adacom_status adacom_scan_columns_async(adacom_ctx *ctx, const adacom
 	if (!ctx || !device_out) {
 		return fail(ctx, ADACOM_ERR_INVALID, "adacom_scan_columns_async: NULL argument");
 	}
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	QueryArgs q;
 	adacom_status st = plan_scan_columns(ctx, terms, n_terms, sums, n_sums, row_begin, row_end, flags, q);
 	if (st != ADACOM_OK) {
@@ -2041,7 +2052,7 @@ extern "C" adacom_status adacom_scan_columns(adacom_ctx *ctx, const adacom_scan_
 		return fail(ctx, ADACOM_ERR_INVALID, "adacom_scan_columns: NULL argument");
 	}
 	if (!ctx->d_aggs) {
-		std::lock_guard<std::mutex> lock(ctx->mu);
+		CtxLock lock(ctx);
 		CK(ctx, cudaMalloc((void **)&ctx->d_aggs, kQueryMaxAggs * kQueryMaxGroups * sizeof(Agg)));
 		CK(ctx, cudaHostAlloc((void **)&ctx->h_aggs, kQueryMaxAggs * kQueryMaxGroups * sizeof(Agg), cudaHostAllocDefault));
 	}
@@ -2050,7 +2061,7 @@ extern "C" adacom_status adacom_scan_columns(adacom_ctx *ctx, const adacom_scan_
 	if (st != ADACOM_OK) {
 		return st;
 	}
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	CK(ctx, cudaMemcpyAsync(ctx->h_aggs, ctx->d_aggs, n_sums * sizeof(Agg), cudaMemcpyDeviceToHost, ctx->stream));
 	CK(ctx, cudaStreamSynchronize(ctx->stream));
 	memcpy(out, ctx->h_aggs, n_sums * sizeof(Agg));
@@ -2065,7 +2076,7 @@ extern "C" adacom_status adacom_scan_columns_grouped(adacom_ctx *ctx, const adac
 	if (!ctx || !out || n_groups == 0 || n_sums > (uint32_t)kQueryMaxAggs) {
 		return fail(ctx, ADACOM_ERR_INVALID, "adacom_scan_columns_grouped: NULL argument, no groups or more than 8 sums");
 	}
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	if (!ctx->d_aggs) {
 		CK(ctx, cudaMalloc((void **)&ctx->d_aggs, kQueryMaxAggs * kQueryMaxGroups * sizeof(Agg)));
 		CK(ctx, cudaHostAlloc((void **)&ctx->h_aggs, kQueryMaxAggs * kQueryMaxGroups * sizeof(Agg), cudaHostAllocDefault));
@@ -2099,7 +2110,7 @@ extern "C" adacom_status adacom_fetch_rows(adacom_column *col, uint64_t n, const
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_fetch_rows: bad arguments");
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	if (n == 0) {
 		return ADACOM_OK;
 	}
@@ -2352,7 +2363,7 @@ extern "C" adacom_status adacom_column_checkpoint_size(adacom_column *col, uint6
 	if (!col || !bytes_out) {
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_column_checkpoint_size: NULL argument");
 	}
-	std::lock_guard<std::mutex> lock(col->ctx->mu);
+	CtxLock lock(col->ctx);
 	ImagePlan plan;
 	adacom_status st = plan_image(col, plan);
 	if (st != ADACOM_OK) {
@@ -2368,7 +2379,7 @@ extern "C" adacom_status adacom_column_checkpoint(adacom_column *col, void *out,
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_column_checkpoint: NULL argument");
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	CK(ctx, cudaSetDevice(ctx->device));
 	ImagePlan plan;
 	adacom_status st = plan_image(col, plan);
@@ -2621,7 +2632,7 @@ extern "C" adacom_status adacom_column_restore(adacom_ctx *ctx, const void *imag
 	adacom_status st;
 	std::string err;
 	{
-		std::lock_guard<std::mutex> lock(ctx->mu);
+		CtxLock lock(ctx);
 		st = restore_locked(ctx, image, bytes, image_on_device, &col);
 		err = ctx->err;
 	}
@@ -2668,7 +2679,7 @@ extern "C" adacom_status adacom_codec_column_create(adacom_ctx *ctx, adacom_code
 	if (!type_info(type, t)) {
 		return fail(ctx, ADACOM_ERR_UNSUPPORTED, "adacom_codec_column_create: unsupported physical type");
 	}
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	CK(ctx, cudaSetDevice(ctx->device));
 	std::unique_ptr<adacom_codec_column> col(new adacom_codec_column());
 	col->ctx = ctx;
@@ -2780,7 +2791,7 @@ extern "C" void adacom_codec_column_destroy(adacom_codec_column *col) {
 		return;
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	cudaSetDevice(ctx->device);
 	for (void *p : {(void *)col->d_images, (void *)col->d_segs, (void *)col->d_jobs, (void *)col->d_sum_jobs,
 	                (void *)col->d_run_start, (void *)col->d_groups}) {
@@ -2827,7 +2838,7 @@ extern "C" adacom_status adacom_codec_decode(adacom_codec_column *col, uint64_t 
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_codec_decode: bad arguments");
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	if (seg_begin == seg_end) {
 		return ADACOM_OK;
 	}
@@ -2857,7 +2868,7 @@ extern "C" adacom_status adacom_codec_scan_sum(adacom_codec_column *col, uint64_
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_codec_scan_sum: bad arguments");
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	CK(ctx, cudaMemsetAsync(ctx->d_agg, 0, sizeof(Agg), ctx->stream));
 	if (seg_begin != seg_end) {
 		CodecArgs a = codec_args(col, seg_begin, seg_end, col->codec == ADACOM_CODEC_RLE);
@@ -2881,7 +2892,7 @@ extern "C" adacom_status adacom_codec_fetch_rows(adacom_codec_column *col, uint6
 		return fail(col ? col->ctx : nullptr, ADACOM_ERR_INVALID, "adacom_codec_fetch_rows: bad arguments");
 	}
 	adacom_ctx *ctx = col->ctx;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	if (n == 0) {
 		return ADACOM_OK;
 	}
@@ -2954,7 +2965,7 @@ adacom_status issue_window(adacom_scan_stream *s, uint64_t w) {
 	const uint64_t rows = range_rows(col, b, e);
 	uint8_t *d_buf = s->d_ring + (w % s->depth) * s->win_bytes;
 	uint8_t *h_buf = s->h_ring + (w % s->depth) * s->win_bytes;
-	std::lock_guard<std::mutex> lock(ctx->mu);
+	CtxLock lock(ctx);
 	CK(ctx, cudaSetDevice(ctx->device));
 	if (win.used) {
 		// the slot's previous copy must have left the device buffer before the kernel overwrites it
@@ -3023,7 +3034,7 @@ extern "C" adacom_status adacom_scan_stream_open(adacom_column *col, uint64_t se
 	const size_t need = s->win_bytes * s->depth;
 	std::vector<cudaEvent_t> events;
 	{
-		std::lock_guard<std::mutex> lock(ctx->mu);
+		CtxLock lock(ctx);
 		if ((e = cudaSetDevice(ctx->device)) != cudaSuccess) {
 			return bail(e, "cudaSetDevice");
 		}
@@ -3125,7 +3136,7 @@ extern "C" void adacom_scan_stream_close(adacom_scan_stream *s) {
 	}
 	adacom_ctx *ctx = s->col->ctx;
 	{
-		std::lock_guard<std::mutex> lock(ctx->mu);
+		CtxLock lock(ctx);
 		cudaSetDevice(ctx->device);
 	}
 	if (s->copy_stream) {
@@ -3146,7 +3157,7 @@ extern "C" void adacom_scan_stream_close(adacom_scan_stream *s) {
 				}
 			}
 		}
-		std::lock_guard<std::mutex> lock(ctx->mu);
+		CtxLock lock(ctx);
 		if (ctx->ring_cache.size() < 16) {
 			ctx->ring_cache.push_back(std::move(r));
 			delete s;
