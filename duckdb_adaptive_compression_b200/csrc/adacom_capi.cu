@@ -1347,15 +1347,29 @@ static adacom_status run_agg(adacom_column *col, uint64_t b, uint64_t e, int fla
 	}
 	bool words_kernel = mode == kModeFilter && !getenv("ADACOM_FILTER_LEGACY");
 	if (words_kernel && col->t.size == 8) {
-		// 8-byte types: payloads wider than 32 bits and slot-width segments are not field-comparable in 32 bits; a range
-		// that holds any of them stays on the TMA-staged per-value kernel (decode_kernel<filter>)
+		// 8-byte types: slot-width segments are not field-comparable; a range that holds any of them stays on the
+		// TMA-staged per-value kernel (decode_kernel<filter>).  Re-packed payloads of any width run in the field domain
+		// (<= 32 bits: pred32 on the staged tile; wider: 64-bit fields, lane = row)
 		adacom_status st = sync_mirror(col);
 		if (st != ADACOM_OK) {
 			return st;
 		}
+		static const bool wide_legacy = getenv("ADACOM_FILTER_WIDE_LEGACY") != nullptr;  // A/B: wide payloads on decode_kernel
+		const bool sg = col->t.is_signed;
 		for (uint64_t g = b; g < e && words_kernel; g++) {
 			const SegDesc &d = col->h_desc[g];
-			words_kernel = d.count == 0 || ((d.state & kSegRepacked) && d.width <= 32);
+			if (d.count == 0) {
+				continue;
+			}
+			words_kernel = (d.state & kSegRepacked) != 0;
+			if (words_kernel && d.width > 32) {
+				// a wide payload is only field-comparable when its frame of reference cannot wrap inside T (the kernel's
+				// per-value path for the others reads global memory lane by lane: slower than decode_kernel<filter>)
+				const uint64_t mn = (d.min_factor != ~0ull) ? d.min_factor : 0ull;
+				const uint64_t range = d.width < 64 ? (1ull << d.width) - 1 : ~0ull, top = mn + range;
+				const bool linear = top >= mn && (sg ? (int64_t)mn <= (int64_t)top : true);
+				words_kernel = !wide_legacy && linear;
+			}
 		}
 	}
 	if (words_kernel) {
@@ -1364,8 +1378,7 @@ static adacom_status run_agg(adacom_column *col, uint64_t b, uint64_t e, int fla
 		LAUNCH(ctx, launch_filter_words(col->t, col->d_desc, col->d_tiles + col->tile_first[b],
 		                                col->tile_first[e] - col->tile_first[b], col->raw, (flags & ADACOM_LITERAL) ? 1 : 0,
 		                                op_mask, constant, bitmap32, col->h_desc[b].row_start, device_out,
-		                                (col->mirror_dirty || !col->wmax) ? std::min<uint32_t>(8u * (uint32_t)col->t.size, 32u)
-		                                                                  : std::min<uint32_t>(col->wmax, 32u),
+		                                (col->mirror_dirty || !col->wmax) ? 8u * (uint32_t)col->t.size : col->wmax,
 		                                ctx->sm_count, ctx->stream));
 		return ADACOM_OK;
 	}
