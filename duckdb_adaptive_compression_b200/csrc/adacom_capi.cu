@@ -2957,16 +2957,18 @@ struct adacom_scan_stream {
 	};
 	std::vector<Win> wins;
 	uint64_t n_windows = 0;
+	// first segment of every window (+ seg_end).  Default: a read-ahead ramp of 1, 2, 4, ... win_segs segments, so the
+	// first vector of a short scan (a point filter that touches one segment) waits for 256 KiB, not for 8 MiB
+	std::vector<uint64_t> win_start;
 };
 
 namespace {
 
 uint64_t window_first(const adacom_scan_stream *s, uint64_t w) {
-	return s->seg_begin + w * s->win_segs;
+	return s->win_start[w];
 }
 uint64_t window_end(const adacom_scan_stream *s, uint64_t w) {
-	const uint64_t e = window_first(s, w) + s->win_segs;
-	return e < s->seg_end ? e : s->seg_end;
+	return s->win_start[w + 1];
 }
 
 // enqueue window w into its slot: decode on the context stream, D2H on the copy stream
@@ -3027,7 +3029,19 @@ extern "C" adacom_status adacom_scan_stream_open(adacom_column *col, uint64_t se
 	s->win_segs = window_segments ? window_segments : 32;
 	s->depth = depth ? depth : 3;
 	s->flags = flags;
-	s->n_windows = (seg_end - seg_begin + s->win_segs - 1) / s->win_segs;
+	{
+		uint64_t at = seg_begin, step = window_segments ? s->win_segs : 1;
+		while (at < seg_end) {
+			s->win_start.push_back(at);
+			at += step;
+			step = step * 2 < s->win_segs ? step * 2 : s->win_segs;
+		}
+		if (s->win_start.empty()) {
+			s->win_start.push_back(seg_begin);
+		}
+		s->n_windows = seg_end > seg_begin ? s->win_start.size() : 0;
+		s->win_start.push_back(seg_end);
+	}
 	if (s->n_windows < s->depth) {
 		s->depth = s->n_windows < 2 ? 2 : (uint32_t)s->n_windows;
 	}
@@ -3112,7 +3126,7 @@ extern "C" adacom_status adacom_scan_stream_segment(adacom_scan_stream *s, uint6
 	}
 	adacom_column *col = s->col;
 	adacom_ctx *ctx = col->ctx;
-	const uint64_t w = (seg - s->seg_begin) / s->win_segs;
+	const uint64_t w = (uint64_t)(std::upper_bound(s->win_start.begin(), s->win_start.end(), seg) - s->win_start.begin()) - 1;
 	adacom_scan_stream::Win *win = &s->wins[w % s->depth];
 	if (win->index != w) {
 		// not resident and not in flight: (re)start the pipeline here

@@ -440,6 +440,7 @@ public:
 	int device;
 	idx_t version = 0;
 	idx_t pending_limit = 64;  // sealed segments staged on the host before a batch is uploaded (16 MiB)
+	bool hot_segments_on_host = true;  // Uncompact() brings the flat block of a (hot) segment back to host memory
 	std::vector<unique_ptr<ColumnSegment>> segments;
 
 	//! shared device columns of this ColumnData: the members of batch k are segments whose gpu_column == col
@@ -453,6 +454,8 @@ public:
 
 private:
 	void AppendTransientSegment(idx_t start_row);
+	//! one shared device column for the given host-staged segments: upload, one analyze, one encode
+	void CompactHostSegments(const std::vector<ColumnSegment *> &candidates);
 };
 
 adacom_ptype ToAdacomType(PhysicalType type);

@@ -270,15 +270,26 @@ static void AppendBits(std::vector<uint64_t> &dst, idx_t dst_bit, const uint64_t
 }
 
 void ColumnData::CompactPending(bool include_last) {
+	std::vector<ColumnSegment *> pending;
+	{
+		std::lock_guard<std::mutex> guard(lock);
+		for (idx_t i = 0; i < segments.size(); i++) {
+			ColumnSegment *s = segments[i].get();
+			if (!include_last && i + 1 == segments.size()) {
+				continue;  // still open for appends
+			}
+			pending.push_back(s);
+		}
+	}
+	CompactHostSegments(pending);
+}
+
+void ColumnData::CompactHostSegments(const std::vector<ColumnSegment *> &candidates) {
 	std::lock_guard<std::mutex> guard(lock);
 	std::vector<ColumnSegment *> pending;
-	for (idx_t i = 0; i < segments.size(); i++) {
-		ColumnSegment *s = segments[i].get();
+	for (auto *s : candidates) {
 		if (s->gpu_column || s->compacted || s->count == 0 || !s->succinct_possible) {
 			continue;
-		}
-		if (!include_last && i + 1 == segments.size()) {
-			continue;  // still open for appends
 		}
 		pending.push_back(s);
 	}
@@ -354,7 +365,7 @@ static std::map<adacom_column *, std::vector<ColumnSegment *>> GroupByColumn(con
 }
 
 void ColumnData::CompactMany(const std::vector<CompactableSegment *> &list) {
-	bool any_pending = false;
+	std::vector<ColumnSegment *> host_only;
 	std::vector<CompactableSegment *> members;
 	for (auto *c : list) {
 		auto *s = static_cast<ColumnSegment *>(c);
@@ -362,7 +373,7 @@ void ColumnData::CompactMany(const std::vector<CompactableSegment *> &list) {
 			continue;  // column_segment.cpp:278
 		}
 		if (!s->gpu_column) {
-			any_pending = true;
+			host_only.push_back(s);  // never uploaded (adaptive mode): only the listed ones move to the device
 		} else if (!s->owns_gpu_column) {
 			members.push_back(s);
 		} else {
@@ -371,8 +382,9 @@ void ColumnData::CompactMany(const std::vector<CompactableSegment *> &list) {
 			s->column_data = this;
 		}
 	}
-	if (any_pending) {
-		CompactPending(true);
+	if (!host_only.empty()) {
+		std::sort(host_only.begin(), host_only.end(), [](ColumnSegment *l, ColumnSegment *r) { return l->start < r->start; });
+		CompactHostSegments(host_only);
 	}
 	std::lock_guard<std::mutex> guard(lock);
 	for (auto &kv : GroupByColumn(members)) {
@@ -394,6 +406,7 @@ void ColumnData::CompactMany(const std::vector<CompactableSegment *> &list) {
 		GPU_CHECK(db, adacom_column_get_meta(kv.first, lo, hi, metas.data()));
 		for (auto *s : kv.second) {
 			s->FinishCompact(s->GetDataSize(), metas[s->gpu_index - lo]);
+			std::vector<uint8_t>().swap(s->staging);  // a re-compacted (cold again) segment gives its host block back
 		}
 	}
 }
@@ -422,9 +435,13 @@ void ColumnData::UncompactMany(const std::vector<CompactableSegment *> &list) {
 			sizes.push_back(s->GetDataSize());
 		}
 		GPU_CHECK(db, adacom_uncompact_list(kv.first, ids.size(), ids.data(), 0));
-		// the flat image stays on the device (scans of a member go through the scan stream either way); the host
-		// block is only brought back when an append needs it (ColumnSegment::EnsureStaging)
+		// Uncompact() is what the policy does to the HOT segments: their flat block comes back to the host (as in the
+		// reference, where a hot segment is an uncompressed block in RAM), so that scans and row fetches of hot
+		// segments are host memory reads while the cold ones stay packed in HBM
 		for (idx_t i = 0; i < kv.second.size(); i++) {
+			if (hot_segments_on_host) {
+				kv.second[i]->EnsureStaging();
+			}
 			kv.second[i]->FinishUncompact(sizes[i]);
 		}
 	}

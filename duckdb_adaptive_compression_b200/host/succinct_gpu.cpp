@@ -652,6 +652,11 @@ void SuccinctScanPartial(ColumnSegment &segment, ColumnScanState &state, idx_t s
 	}
 	auto &scan_state = (SuccinctGpuScanState &)*state.scan_state;
 	if (segment.column_data && !segment.owns_gpu_column) {
+		if (!segment.compacted && segment.staging.size() == segment.SegmentSize()) {
+			// a hot segment (uncompacted by the policy): its flat block is in host memory
+			memcpy(target_ptr, segment.staging.data() + start * S, scan_count * S);
+			return;
+		}
 		memcpy(target_ptr, StreamValues(segment, state, scan_state) + start * S, scan_count * S);
 		return;
 	}
@@ -677,6 +682,10 @@ void SuccinctScan(ColumnSegment &segment, ColumnScanState &state, idx_t scan_cou
 		}
 		auto &scan_state = (SuccinctGpuScanState &)*state.scan_state;
 		result.SetVectorType(VectorType::FLAT_VECTOR);
+		if (!segment.compacted && segment.staging.size() == segment.SegmentSize()) {
+			FlatVector::SetData(result, segment.staging.data() + start * segment.type_size);  // hot: host-resident flat block
+			return;
+		}
 		FlatVector::SetData(result, (data_ptr_t)StreamValues(segment, state, scan_state) + start * segment.type_size);
 		return;
 	}
@@ -689,8 +698,8 @@ void SuccinctFetchRow(ColumnSegment &segment, ColumnFetchState &, row_t row_id, 
 	}
 	idx_t S = segment.type_size;
 	data_ptr_t target_ptr = FlatVector::GetData(result) + result_idx * S;
-	if (!segment.gpu_column || (!segment.compacted && segment.owns_gpu_column)) {
-		memcpy(target_ptr, segment.staging.data() + (idx_t)row_id * S, S);
+	if (!segment.gpu_column || (!segment.compacted && segment.staging.size() == segment.SegmentSize())) {
+		memcpy(target_ptr, segment.staging.data() + (idx_t)row_id * S, S);  // host-resident flat block (open or hot segment)
 		return;
 	}
 	uint32_t seg = (uint32_t)segment.gpu_index, row = (uint32_t)row_id;

@@ -9,6 +9,7 @@
 #include "../adacom_host.hpp"
 
 #include <chrono>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <thread>
@@ -158,14 +159,78 @@ int main(int argc, char **argv) {
 		fetch_ok &= ((int64_t *)FlatVector::GetData(many))[i] == value_of((idx_t)ids[i]);
 	}
 
+	// ---- point reads under the access-frequency policy: the three arms of run_diff_zipfian.sh through the vtable ----
+	// A look-up = the scan of the 2048-row vector that holds the key (what a zone-map-pruned point filter pulls), keys
+	// Zipf-like with q = 1 (row = N^u - 1).  non-adaptive succinct: every segment packed in HBM (the column above);
+	// non-succinct: adaptive mode before the first epoch, every segment a flat host block; adaptive: after one epoch
+	// of ColumnSegmentCatalog (coldest 90 % packed in HBM by ONE launch set, hottest 10 % flat in host memory).
+	const idx_t n_point = 4000;
+	std::vector<idx_t> keys(n_point * 8);
+	for (idx_t i = 0; i < keys.size(); i++) {
+		const double u = (double)(splitmix(0x21BF000 + i) >> 11) / 9007199254740992.0;
+		keys[i] = std::min<idx_t>(n - 1, (idx_t)std::pow((double)n, u) - 0);
+		keys[i] = keys[i] ? keys[i] - 1 : 0;
+	}
+	auto point_reads = [&](ColumnData &c, idx_t first, idx_t count, bool *ok_out) {
+		Vector result(PhysicalType::INT64);
+		bool all_ok = true;
+		auto a = Clock::now();
+		for (idx_t i = first; i < first + count; i++) {
+			const idx_t row = keys[i], vec0 = row / STANDARD_VECTOR_SIZE * STANDARD_VECTOR_SIZE;
+			ColumnScanState state;
+			c.InitializeScanWithOffset(state, vec0);
+			c.ScanVector(state, result, std::min<idx_t>(STANDARD_VECTOR_SIZE, n - vec0));
+			all_ok &= ((const int64_t *)FlatVector::GetData(result))[row - vec0] == value_of(row);
+		}
+		auto b = Clock::now();
+		*ok_out = all_ok;
+		return count / seconds(a, b);
+	};
+	bool ok_succinct = true, ok_flat = true, ok_adaptive = true;
+	point_reads(col, 0, 200, &ok_succinct);  // warm-up
+	const double point_succinct = point_reads(col, 200, n_point, &ok_succinct);
+	double point_flat = 0, point_adaptive = 0, epoch_s = 0;
+	idx_t adaptive_bytes = 0, hot_segments = 0;
+	{
+		DBConfig acfg;
+		acfg.adaptive_succinct_compression_enabled = true;
+		DatabaseInstance adb(&acfg);
+		ColumnData acol(adb, PhysicalType::INT64);
+		acol.pending_limit = pending_limit;
+		adb.Gpu();
+		ColumnAppendState astate;
+		acol.InitializeAppend(astate);
+		for (idx_t off = 0; off < n; off += STANDARD_VECTOR_SIZE) {
+			UnifiedVectorFormat vdata;
+			vdata.data = (data_ptr_t)(pool.data() + ((off / STANDARD_VECTOR_SIZE) % kPool) * STANDARD_VECTOR_SIZE);
+			acol.AppendData(astate, vdata, STANDARD_VECTOR_SIZE);
+		}
+		point_reads(acol, 0, 200, &ok_flat);
+		point_flat = point_reads(acol, 200, 4 * n_point, &ok_flat);  // also the reads the policy learns from
+		auto e0 = Clock::now();
+		adb.column_segment_catalog.RunCompactionEpoch();
+		adacom_ctx_synchronize(adb.Gpu());
+		epoch_s = seconds(e0, Clock::now());
+		adaptive_bytes = adb.column_segment_catalog.GetTotalDataSize();
+		for (auto &sgm : acol.segments) {
+			hot_segments += !sgm->IsBitCompressed();
+		}
+		point_reads(acol, 0, 200, &ok_adaptive);
+		point_adaptive = point_reads(acol, 4 * n_point + 200, 3 * n_point, &ok_adaptive);
+	}
+	const bool point_ok = ok_succinct && ok_flat && ok_adaptive;
+
 	const double gb = (double)n * 8 / 1e9;
 	printf("{\"values\": %llu, \"bits\": %d, \"segments\": %zu, \"device_columns\": %zu, \"data_size\": %llu, "
 	       "\"load_s\": %.4f, \"load_GBs\": %.2f, \"scan_threads\": %d, \"scan_s\": %.5f, \"scan_GBs\": %.2f, "
 	       "\"scan_1thread_GBs\": %.2f, \"scan_verify_GBs\": %.2f, \"zero_copy_vectors\": %llu, \"vectors\": %llu, "
-	       "\"scan_ok\": %s, \"fetch_row_per_s\": %.0f, \"fetch_rows_batched_per_s\": %.0f, \"fetch_ok\": %s}\n",
+	       "\"scan_ok\": %s, \"fetch_row_per_s\": %.0f, \"fetch_rows_batched_per_s\": %.0f, \"fetch_ok\": %s, "
+	       "\"point_reads_per_s\": {\"non_adaptive_succinct\": %.0f, \"non_succinct\": %.0f, \"adaptive\": %.0f}, "
+	       "\"adaptive_epoch_s\": %.4f, \"adaptive_resident_bytes\": %llu, \"adaptive_hot_segments\": %llu, \"point_ok\": %s}\n",
 	       (unsigned long long)n, bits, col.segments.size(), col.batches.size(), (unsigned long long)data_size, load_s,
 	       gb / load_s, threads, scan_s, gb / scan_s, gb / scan1_s, gb / verify_s, (unsigned long long)zero_copy,
 	       (unsigned long long)(n / STANDARD_VECTOR_SIZE), ok ? "true" : "false", n_single / seconds(f0, f1),
-	       n_batch / seconds(f2, f3), fetch_ok ? "true" : "false");
-	return ok && fetch_ok ? 0 : 1;
+	       n_batch / seconds(f2, f3), fetch_ok ? "true" : "false", point_succinct, point_flat, point_adaptive, epoch_s,
+	       (unsigned long long)adaptive_bytes, (unsigned long long)hot_segments, point_ok ? "true" : "false");
+	return ok && fetch_ok && point_ok ? 0 : 1;
 }

@@ -218,7 +218,8 @@ adacom_status adacom_scan_partial(adacom_column *col, uint64_t seg, uint64_t sta
  * run ahead of the consumer, so scan_vector / scan_partial become pointer arithmetic into pinned memory (zero-copy
  * FlatVector::SetData, like FixedSizeScan, fixed_size_uncompressed.cpp).  No call of the scan holds the context
  * mutex while it waits; any number of streams (one per DuckDB scan thread) run concurrently.
- * window_segments = 0 / depth = 0 pick the defaults (32 segments = 8 MiB, 3 windows; depth >= 2). */
+ * window_segments = 0 picks a read-ahead ramp (windows of 1, 2, 4, ... 32 segments: the first vector of a short scan
+ * waits for one segment, a long scan settles at 8 MiB per launch); depth = 0 picks 3 windows (depth >= 2). */
 typedef struct adacom_scan_stream adacom_scan_stream;
 adacom_status adacom_scan_stream_open(adacom_column *col, uint64_t seg_begin, uint64_t seg_end,
                                       uint32_t window_segments, uint32_t depth, int flags, adacom_scan_stream **out);

@@ -476,7 +476,13 @@ def vtable_dropin(threads, log2_values=27, bits=17, cpu_log2_values=22):
            "scan_verified_GBs": best["scan_verify_GBs"], "zero_copy_vectors": best["zero_copy_vectors"],
            "vectors": best["vectors"], "segments": best["segments"], "device_columns": best["device_columns"],
            "append_compact_GBs": best["load_GBs"], "fetch_row_per_s": best["fetch_row_per_s"],
-           "fetch_rows_batched_per_s": best["fetch_rows_batched_per_s"], "answers_checked": best["scan_ok"] and best["fetch_ok"],
+           "fetch_rows_batched_per_s": best["fetch_rows_batched_per_s"],
+           # point reads (the scan of the key's 2048-row vector, Zipf-like keys, one host thread) under the three arms of
+           # run_diff_zipfian.sh:12-14: every segment packed in HBM / every segment a flat host block / after one policy
+           # epoch (coldest 90 % packed in HBM by one launch set, hottest 10 % flat in host memory)
+           "point_reads_per_s": best.get("point_reads_per_s"), "adaptive_epoch_s": best.get("adaptive_epoch_s"),
+           "adaptive_resident_bytes": best.get("adaptive_resident_bytes"), "resident_bytes_packed": best.get("data_size"),
+           "answers_checked": best["scan_ok"] and best["fetch_ok"] and best.get("point_ok", False),
            "timed": "host clock around the pull loops (device work, D2H of the pinned windows and the pulls overlap); load = "
                     "append of host vectors + H2D + analyze + encode, batched per 512 segments"}
     o = _ref_oracle()
