@@ -125,6 +125,10 @@ void set_process_error(const std::string &msg) {
 namespace {
 
 adacom_status fail(adacom_ctx *ctx, adacom_status st, const std::string &msg) {
+	static const bool verbose = getenv("ADACOM_VERBOSE_ERRORS") != nullptr;  // hosts that only forward the status code
+	if (verbose) {
+		fprintf(stderr, "[adacom] status %d: %s\n", (int)st, msg.c_str());
+	}
 	if (ctx) {
 		ctx->err = msg;
 	} else {

@@ -165,6 +165,10 @@ struct SuccinctGpuSegmentState : public CompressedSegmentState {
 	idx_t resident = 0;
 	//! ColumnSegment::GetDataSize() of the device state (0 = not known yet)
 	idx_t data_size = 0;
+	//! segment.count at which the device state was last compacted (Compact() is idempotent: the reference's lazy
+	//! `if (!compacted) Compact()` on the scan path is unlocked, column_segment.cpp:157-160, so two scan threads can
+	//! both decide to compact the same segment -- the second call must not find the raw slots gone)
+	idx_t compacted_for = (idx_t)-1;
 	//! serialises upload / re-encode against concurrent scans (the reference's bit_compression_lock)
 	std::mutex lock;
 };
@@ -202,6 +206,7 @@ void EnsureResident(ColumnSegment &segment, SuccinctGpuSegmentState &state) {
 	}
 	state.resident = count;
 	state.data_size = 0;
+	state.compacted_for = (idx_t)-1;
 }
 
 unique_ptr<CompressedSegmentState> SuccinctGpuInitSegment(ColumnSegment &segment, block_id_t block_id) {
@@ -552,6 +557,10 @@ unique_ptr<CompressedSegmentState> SuccinctGpuFun::InitSegmentFromBlock(ColumnSe
 idx_t SuccinctGpuFun::Compact(ColumnSegment &segment, bool zero_extended_minmax) {
 	auto &seg_state = StateOf(segment);
 	std::lock_guard<std::mutex> guard(seg_state.lock);
+	if (seg_state.column && seg_state.resident == segment.count && seg_state.compacted_for == segment.count &&
+	    seg_state.data_size) {
+		return seg_state.data_size; // already compacted at this size (a concurrent or repeated Compact())
+	}
 	StatTimer timer(Stats().compact_ns, Stats().compact_calls);
 	EnsureResident(segment, seg_state);
 	int flags = 0;
@@ -569,6 +578,7 @@ idx_t SuccinctGpuFun::Compact(ColumnSegment &segment, bool zero_extended_minmax)
 	uint64_t bytes = 0;
 	Check(adacom_column_data_size(seg_state.column, 0, 1, &bytes), "data_size");
 	seg_state.data_size = bytes;
+	seg_state.compacted_for = segment.count;
 	adacom_segment_meta meta;
 	Check(adacom_column_get_meta(seg_state.column, 0, 1, &meta), "get_meta");
 	if (meta.state & ADACOM_SEG_REPACKED) {
