@@ -152,29 +152,45 @@ __global__ void __launch_bounds__(kCodecThreads) bitpacking_groups_kernel(CodecA
 	Acc96 acc;
 	uint32_t n_rows = 0;
 	uint32_t parity = 0;
+	// Software pipeline over the CTA's groups: the payload of group j + grid is copied (cp.async, 4 bytes per request:
+	// the source is only sizeof(T)-aligned) into the other stage buffer while group j is decoded, so the barrier at the
+	// top of an iteration finds its data already in shared memory (the kernel was latency-bound: 35 % of the DRAM
+	// throughput at 39 % of the issue slots, profiles/r03q_codecs_ncu_summary.txt).
+	auto stage_group = [&](uint32_t j, uint32_t *stage) -> uint32_t {
+		const CodecGroup *gp = a.groups + j;
+		const uint32_t mode = __ldg(&gp->mode);
+		if (mode != kBpFor && mode != kBpDeltaFor) {
+			return 0u;
+		}
+		const uint32_t w = __ldg(&gp->width), cnt = __ldg(&gp->count);
+		const uint8_t *src = a.images + __ldg(&gp->payload);
+		const uint32_t mis = (uint32_t)((uintptr_t)src & 3u);
+		const uint32_t *src4 = (const uint32_t *)(src - mis);
+		const uint32_t n_words = (mis + ((cnt + 31u) / 32u) * 4u * w + 3u) / 4u;
+		for (uint32_t t = tid; t < n_words; t += kCodecThreads) {
+			asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_addr(stage + t)), "l"(src4 + t) : "memory");
+		}
+		if (tid < 4) {
+			stage[n_words + tid] = 0u;  // the funnel's look-ahead words
+		}
+		return mis * 8u;
+	};
+	uint32_t mis_next = 0;
+	if (blockIdx.x < a.n_jobs) {
+		mis_next = stage_group(blockIdx.x, stage2[0]);
+	}
 	for (uint32_t j = blockIdx.x; j < a.n_jobs; j += gridDim.x, parity ^= 1u) {
 		const CodecGroup *gp = a.groups + j;
 		const uint32_t mode = __ldg(&gp->mode), w = __ldg(&gp->width), cnt = __ldg(&gp->count);
 		const uint64_t frame = __ldg(&gp->frame);
 		T *out = MODE == 0 ? (T *)a.out + (__ldg(&gp->out_row) - a.out_row0) : nullptr;
 		uint32_t *stage = stage2[parity];
-		uint32_t mis_bits = 0;
-		if (mode == kBpFor || mode == kBpDeltaFor) {
-			// stage ceil(cnt / 32) * 4 * w payload bytes; the source is only sizeof(T)-aligned.  The other buffer may
-			// still be read by slower threads (they are at most one group behind: one barrier per group)
-			const uint8_t *src = a.images + __ldg(&gp->payload);
-			const uint32_t mis = (uint32_t)((uintptr_t)src & 3u);
-			const uint32_t *src4 = (const uint32_t *)(src - mis);
-			const uint32_t n_words = (mis + ((cnt + 31u) / 32u) * 4u * w + 3u) / 4u;
-			for (uint32_t t = tid; t < n_words; t += kCodecThreads) {
-				stage[t] = __ldg(src4 + t);
-			}
-			if (tid < 4) {
-				stage[n_words + tid] = 0u;  // the funnel's look-ahead words
-			}
-			mis_bits = mis * 8u;
+		const uint32_t mis_bits = mis_next;
+		asm volatile("cp.async.wait_all;" ::: "memory");
+		__syncthreads();  // group j is in stage[parity]; every thread is done with group j - 1 (stage[parity ^ 1])
+		if (j + gridDim.x < a.n_jobs) {
+			mis_next = stage_group(j + gridDim.x, stage2[parity ^ 1u]);
 		}
-		__syncthreads();
 		if (mode == kBpDeltaFor) {
 			// blocked: thread t owns values [8t, 8t + 8); running sum of (field + for) in T arithmetic
 			uint64_t d[8];
