@@ -385,47 +385,75 @@ __device__ __forceinline__ uint32_t rle_find_run(const uint32_t *starts, uint32_
 
 // decode 2048-row tiles: the heads of the runs that start inside the tile are scattered to their row, an inclusive
 // max-scan over the 2048 rows gives every row its run (RLEScanPartial, rle.cpp:298-318, without the per-row walk)
+struct RleTile {
+	uint32_t cnt, run_lo, run_hi, first;
+	uint64_t payload, out_row;
+};
+__device__ __forceinline__ RleTile load_rle_tile(const CodecGroup *gp) {
+	RleTile t;
+	t.cnt = __ldg(&gp->count);
+	t.run_lo = __ldg(&gp->run_lo);
+	t.run_hi = __ldg(&gp->run_hi);
+	t.first = __ldg(&gp->first);
+	t.payload = __ldg(&gp->payload);
+	t.out_row = __ldg(&gp->out_row);
+	return t;
+}
+
 template <int S>
 __global__ void __launch_bounds__(kCodecThreads) rle_decode_kernel(CodecArgs a) {
 	using T = typename UIntOf<S>::type;
-	__shared__ uint32_t head[kGroupValues];  // run (relative to the tile's first run) that starts at this row, else 0
+	__shared__ __align__(16) uint32_t head[kGroupValues];  // run (relative to the tile's first run) that starts at this row, else 0
 	__shared__ uint32_t warp_max[kCodecThreads / 32];
 	const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+	// the record of the NEXT tile is loaded while the current one is expanded (one global latency less per tile), and
+	// its run starts are pulled towards L2 (ncu: long-scoreboard 21.6 of 28 stall cycles per issue before)
+	RleTile next;
+	next.cnt = 0;
+	if (blockIdx.x < a.n_jobs) {
+		next = load_rle_tile(a.groups + blockIdx.x);
+	}
 	for (uint32_t j = blockIdx.x; j < a.n_jobs; j += gridDim.x) {
-		const CodecGroup *gp = a.groups + j;
-		const uint32_t cnt = __ldg(&gp->count);
-		if (cnt == 0) {
-			continue;
-		}
-		const uint32_t run_lo = __ldg(&gp->run_lo), run_hi = __ldg(&gp->run_hi), first = __ldg(&gp->first);
-		const T *values = (const T *)(a.images + __ldg(&gp->payload));
-		// run_start is indexed column-wide, the values segment-wide: the segment's first run index is run_lo - (its
-		// position inside the segment); both advance together, so work with the difference
+		const RleTile t = next;
 		const Job job = a.jobs[j];
 		const uint32_t seg_first_run = __ldg(&a.segs[job.seg].first_run);
-		T *out = (T *)a.out + (__ldg(&gp->out_row) - a.out_row0);
-		__syncthreads();  // the previous tile's head[] has been consumed
-#pragma unroll
-		for (uint32_t i = tid; i < kGroupValues; i += kCodecThreads) {
-			head[i] = 0u;
+		if (j + gridDim.x < a.n_jobs) {
+			next = load_rle_tile(a.groups + j + gridDim.x);
 		}
+		if (t.cnt == 0) {
+			continue;
+		}
+		const uint32_t cnt = t.cnt, run_lo = t.run_lo, run_hi = t.run_hi, first = t.first;
+		const T *values = (const T *)(a.images + t.payload);
+		T *out = (T *)a.out + (t.out_row - a.out_row0);
+		__syncthreads();  // the previous tile's head[] has been consumed
+		// 16-byte shared accesses: a thread's 8 consecutive words as two vectors (word-by-word they are 8-way conflicts)
+		*(uint4 *)&head[tid * 8u] = make_uint4(0u, 0u, 0u, 0u);
+		*(uint4 *)&head[tid * 8u + 4u] = make_uint4(0u, 0u, 0u, 0u);
 		__syncthreads();
 		for (uint32_t r = run_lo + 1u + tid; r <= run_hi; r += kCodecThreads) {
 			const uint32_t pos = __ldg(a.run_start + r) - first;  // > 0: run_lo is the last run that starts at or before `first`
 			if (pos < cnt) {
-				atomicMax(&head[pos], r - run_lo);  // zero-length runs share a row: the last one holds it
+				// a run of 65535 rows is followed by a ZERO-length run when the next value differs (RLEState::Update,
+				// rle.cpp:66-72 then :53-60): such runs share a row with their successor, the last one holds it
+				atomicMax(&head[pos], r - run_lo);
+			}
+		}
+		if (next.cnt) {
+			// the next tile's run starts: 4 bytes per run, one prefetch per 128-byte line
+			for (uint32_t r = next.run_lo + tid * 32u; r <= next.run_hi; r += kCodecThreads * 32u) {
+				asm volatile("prefetch.global.L2 [%0];" ::"l"(a.run_start + r));
 			}
 		}
 		__syncthreads();
 		// thread t owns rows [8t, 8t + 8)
-		uint32_t m[8];
-		uint32_t run = 0;
+		const uint4 h0 = *(const uint4 *)&head[tid * 8u], h1 = *(const uint4 *)&head[tid * 8u + 4u];
+		uint32_t m[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
 #pragma unroll
-		for (int k = 0; k < 8; k++) {
-			run = max(run, head[tid * 8u + k]);
-			m[k] = run;
+		for (int k = 1; k < 8; k++) {
+			m[k] = max(m[k], m[k - 1]);
 		}
-		uint32_t incl = run;
+		uint32_t incl = m[7];
 #pragma unroll
 		for (int s = 1; s < 32; s <<= 1) {
 			const uint32_t o = __shfl_up_sync(0xffffffffu, incl, s);
@@ -445,10 +473,8 @@ __global__ void __launch_bounds__(kCodecThreads) rle_decode_kernel(CodecArgs a) 
 			before = max(before, warp_max[wi]);
 		}
 		// the run index of every row goes back to shared memory so that the stores are row-strided (coalesced)
-#pragma unroll
-		for (int k = 0; k < 8; k++) {
-			head[tid * 8u + k] = max(before, m[k]);
-		}
+		*(uint4 *)&head[tid * 8u] = make_uint4(max(before, m[0]), max(before, m[1]), max(before, m[2]), max(before, m[3]));
+		*(uint4 *)&head[tid * 8u + 4u] = make_uint4(max(before, m[4]), max(before, m[5]), max(before, m[6]), max(before, m[7]));
 		__syncthreads();
 		const T *tile_values = values + (run_lo - seg_first_run);
 #pragma unroll 4
