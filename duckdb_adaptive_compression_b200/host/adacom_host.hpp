@@ -378,7 +378,20 @@ public:
 	bool owns_gpu_column = true;
 	ColumnData *column_data = nullptr;
 	int device = -1;                      // GPU ordinal of gpu_column (-1: default device of the database)
-	std::vector<uint8_t> staging;         // slot-width host image of the appended values (== the raw arena)
+	//! slot-width host image of the values (== the raw arena): the block of an open segment, of a segment that was never
+	//! uploaded (adaptive mode) and of a HOT segment the policy uncompacted; empty once the values only live on the device.
+	//! Shared ownership: a scan that handed out a zero-copy vector keeps the block alive while the policy drops it
+	//! (the pointer is swapped under bit_compression_lock; the reference's own version of this is a data race, Q5)
+	std::shared_ptr<std::vector<uint8_t>> host_block = std::make_shared<std::vector<uint8_t>>();
+	std::shared_ptr<std::vector<uint8_t>> HostBlock() {
+		std::lock_guard<std::mutex> guard(bit_compression_lock);
+		return host_block;
+	}
+	void DropHostBlock() {
+		auto empty = std::make_shared<std::vector<uint8_t>>();
+		std::lock_guard<std::mutex> guard(bit_compression_lock);
+		host_block.swap(empty);
+	}
 	std::vector<uint64_t> staging_validity;
 	bool staging_has_nulls = false;
 	idx_t uploaded = 0;                   // values already copied to the device

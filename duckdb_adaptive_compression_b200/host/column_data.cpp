@@ -315,7 +315,7 @@ void ColumnData::CompactHostSegments(const std::vector<ColumnSegment *> &candida
 	Batch &b = batches.back();
 	idx_t row = 0;
 	for (auto *s : pending) {
-		GPU_CHECK(db, adacom_column_upload_raw(b.col, s->staging.data(), row, s->count));
+		GPU_CHECK(db, adacom_column_upload_raw(b.col, s->host_block->data(), row, s->count));
 		row += s->count;
 	}
 	if (nulls) {
@@ -344,7 +344,7 @@ void ColumnData::CompactHostSegments(const std::vector<ColumnSegment *> &candida
 		s->owns_gpu_column = false;
 		s->uploaded = s->count;
 		s->FinishCompact(size_before, metas[i]);
-		std::vector<uint8_t>().swap(s->staging);  // the values live on the device now (EnsureStaging brings them back)
+		s->DropHostBlock();  // the values live on the device now (EnsureStaging brings them back)
 	}
 }
 
@@ -406,7 +406,7 @@ void ColumnData::CompactMany(const std::vector<CompactableSegment *> &list) {
 		GPU_CHECK(db, adacom_column_get_meta(kv.first, lo, hi, metas.data()));
 		for (auto *s : kv.second) {
 			s->FinishCompact(s->GetDataSize(), metas[s->gpu_index - lo]);
-			std::vector<uint8_t>().swap(s->staging);  // a re-compacted (cold again) segment gives its host block back
+			s->DropHostBlock();  // a re-compacted (cold again) segment gives its host block back
 		}
 	}
 }

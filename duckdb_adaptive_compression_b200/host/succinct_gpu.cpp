@@ -174,7 +174,7 @@ ColumnSegment::ColumnSegment(DatabaseInstance &db_p, PhysicalType type_p, idx_t 
     : db(db_p), type(type_p), type_size(GetTypeIdSize(type_p)), start(start_p), function(function_p),
       segment_size(segment_size_p), succinct_possible(succinct_possible_p), background_compaction_enabled(background),
       is_data_segment(is_data_segment_p) {
-	staging.resize(segment_size);
+	host_block->resize(segment_size);
 	staging_validity.assign((segment_size / type_size + 63) / 64, ~0ull);
 	if (function->type == CompressionType::COMPRESSION_SUCCINCT) {
 		db.buffer_manager.AddToDataSize((int64_t)SlotVectorBytes(segment_size));
@@ -211,13 +211,15 @@ void ColumnSegment::EnsureDeviceColumn() {
 void ColumnSegment::EnsureStaging() {
 	// a member of a shared device column gives its host block back after the upload; appends (and host-side
 	// reads of an uncompacted segment) bring it back from the device
-	if (staging.size() == segment_size) {
+	if (HostBlock()->size() == segment_size) {
 		return;
 	}
-	staging.resize(segment_size);
+	auto block = std::make_shared<std::vector<uint8_t>>(segment_size);
 	if (gpu_column && count) {
-		GPU_CHECK(db, adacom_decode(gpu_column, gpu_index, gpu_index + 1, 0, staging.data(), 0));
+		GPU_CHECK(db, adacom_decode(gpu_column, gpu_index, gpu_index + 1, 0, block->data(), 0));
 	}
+	std::lock_guard<std::mutex> guard(bit_compression_lock);
+	host_block.swap(block);
 }
 
 void ColumnSegment::DetachFromBatch() {
@@ -240,7 +242,7 @@ void ColumnSegment::Upload() {
 	}
 	EnsureDeviceColumn();
 	if (uploaded < count) {
-		GPU_CHECK(db, adacom_column_upload_raw(gpu_column, staging.data() + uploaded * type_size, uploaded,
+		GPU_CHECK(db, adacom_column_upload_raw(gpu_column, host_block->data() + uploaded * type_size, uploaded,
 		                                       count - uploaded));
 		uploaded = count;
 	}
@@ -423,8 +425,12 @@ void ColumnSegment::Uncompact() {
 	const idx_t compressed_size = GetDataSize();
 	GPU_CHECK(db, adacom_uncompact(gpu_column, gpu_index, gpu_index + 1, 0));
 	// the flat block lives on the host again (appends continue there)
-	staging.resize(segment_size);
-	GPU_CHECK(db, adacom_decode(gpu_column, gpu_index, gpu_index + 1, 0, staging.data(), 0));
+	{
+		auto block = std::make_shared<std::vector<uint8_t>>(segment_size);
+		GPU_CHECK(db, adacom_decode(gpu_column, gpu_index, gpu_index + 1, 0, block->data(), 0));
+		std::lock_guard<std::mutex> guard(bit_compression_lock);
+		host_block.swap(block);
+	}
 	FinishUncompact(compressed_size);
 }
 
@@ -598,6 +604,7 @@ struct GpuScanStream {
 
 struct SuccinctGpuScanState : public SegmentScanState {
 	std::shared_ptr<GpuScanStream> stream;
+	std::shared_ptr<std::vector<uint8_t>> hot;  // host block of a hot segment a zero-copy vector points into
 	const uint8_t *values = nullptr;  // this segment inside the stream's current window
 	std::vector<uint8_t> decoded;     // lone segments
 	uint64_t epoch = ~0ull;
@@ -645,23 +652,28 @@ void SuccinctScanPartial(ColumnSegment &segment, ColumnScanState &state, idx_t s
 	}
 	idx_t S = segment.type_size;
 	data_ptr_t target_ptr = FlatVector::GetData(result) + result_offset * S;
-	if (!segment.gpu_column) {
+	auto block = segment.HostBlock();  // keeps the block alive for the copy even if the policy drops it meanwhile
+	const bool host_resident = block->size() == segment.SegmentSize();
+	if (!segment.gpu_column && host_resident) {
 		// not compacted yet (adaptive mode): the slot-width image is the flat block (FixedSizeScanPartial)
-		memcpy(target_ptr, segment.staging.data() + start * S, scan_count * S);
+		memcpy(target_ptr, block->data() + start * S, scan_count * S);
 		return;
+	}
+	if (!segment.gpu_column) {
+		throw InternalException("SuccinctScanPartial: segment has neither a host block nor a device column");
 	}
 	auto &scan_state = (SuccinctGpuScanState &)*state.scan_state;
 	if (segment.column_data && !segment.owns_gpu_column) {
-		if (!segment.compacted && segment.staging.size() == segment.SegmentSize()) {
+		if (!segment.compacted && host_resident) {
 			// a hot segment (uncompacted by the policy): its flat block is in host memory
-			memcpy(target_ptr, segment.staging.data() + start * S, scan_count * S);
+			memcpy(target_ptr, block->data() + start * S, scan_count * S);
 			return;
 		}
 		memcpy(target_ptr, StreamValues(segment, state, scan_state) + start * S, scan_count * S);
 		return;
 	}
-	if (!segment.compacted) {
-		memcpy(target_ptr, segment.staging.data() + start * S, scan_count * S);
+	if (!segment.compacted && host_resident) {
+		memcpy(target_ptr, block->data() + start * S, scan_count * S);
 		return;
 	}
 	if (scan_state.epoch != segment.epoch) {
@@ -682,8 +694,10 @@ void SuccinctScan(ColumnSegment &segment, ColumnScanState &state, idx_t scan_cou
 		}
 		auto &scan_state = (SuccinctGpuScanState &)*state.scan_state;
 		result.SetVectorType(VectorType::FLAT_VECTOR);
-		if (!segment.compacted && segment.staging.size() == segment.SegmentSize()) {
-			FlatVector::SetData(result, segment.staging.data() + start * segment.type_size);  // hot: host-resident flat block
+		auto block = segment.HostBlock();
+		if (!segment.compacted && block->size() == segment.SegmentSize()) {
+			scan_state.hot = block;  // the zero-copy vector outlives this call: the scan state holds the block
+			FlatVector::SetData(result, block->data() + start * segment.type_size);  // hot: host-resident flat block
 			return;
 		}
 		FlatVector::SetData(result, (data_ptr_t)StreamValues(segment, state, scan_state) + start * segment.type_size);
@@ -698,8 +712,9 @@ void SuccinctFetchRow(ColumnSegment &segment, ColumnFetchState &, row_t row_id, 
 	}
 	idx_t S = segment.type_size;
 	data_ptr_t target_ptr = FlatVector::GetData(result) + result_idx * S;
-	if (!segment.gpu_column || (!segment.compacted && segment.staging.size() == segment.SegmentSize())) {
-		memcpy(target_ptr, segment.staging.data() + (idx_t)row_id * S, S);  // host-resident flat block (open or hot segment)
+	auto block = segment.HostBlock();
+	if (block->size() == segment.SegmentSize() && (!segment.gpu_column || !segment.compacted)) {
+		memcpy(target_ptr, block->data() + (idx_t)row_id * S, S);  // host-resident flat block (open or hot segment)
 		return;
 	}
 	uint32_t seg = (uint32_t)segment.gpu_index, row = (uint32_t)row_id;
@@ -720,7 +735,7 @@ idx_t SuccinctAppend(CompressionAppendState &, ColumnSegment &segment, SegmentSt
 	idx_t max_tuple_count = segment.SegmentSize() / sizeof(T);
 	idx_t copy_count = std::min<idx_t>(count, max_tuple_count - segment.count);
 	auto sdata = (const T *)data.data;
-	auto target = (T *)segment.staging.data();
+	auto target = (T *)segment.host_block->data();
 	if ((!data.sel || !data.sel->sel) && data.validity.AllValid()) {
 		// flat, all-valid vector (the common case of a bulk load): one block copy
 		memcpy(target + segment.count, sdata + offset, copy_count * sizeof(T));

@@ -9,7 +9,9 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <atomic>
 #include <random>
+#include <thread>
 
 using namespace adacom_host;
 
@@ -227,7 +229,7 @@ void RunColumnData(PhysicalType type, idx_t n, uint64_t span, int64_t base, bool
 	idx_t vectors = (n + STANDARD_VECTOR_SIZE - 1) / STANDARD_VECTOR_SIZE;
 	CHECK(zero_copy + 2 * col.segments.size() >= vectors);  // all but the vectors that straddle a segment border
 	for (auto &s : col.segments) {
-		CHECK(s->IsBitCompressed() && s->gpu_column && !s->owns_gpu_column && s->staging.empty());
+		CHECK(s->IsBitCompressed() && s->gpu_column && !s->owns_gpu_column && s->host_block->empty());
 	}
 	// sizes: 9 + 8*ceil(n*w/64) per segment; catalog and buffer manager agree
 	idx_t total = 0;
@@ -344,7 +346,71 @@ void RunColumnData(PhysicalType type, idx_t n, uint64_t span, int64_t base, bool
 	}
 }
 
+// Readers (full scans with zero-copy vectors, row fetches) against a policy thread that keeps moving segments between
+// "hot: flat block in host memory" and "cold: packed in HBM": the values never change, no reader may see a freed block.
+void RunConcurrentPolicy() {
+	DBConfig cfg;
+	cfg.adaptive_succinct_compression_enabled = true;
+	DatabaseInstance db(&cfg);
+	const idx_t n = 32767 * 14 + 123;
+	std::vector<int64_t> values(n);
+	std::mt19937_64 rng(99);
+	for (auto &v : values) {
+		v = 5000000000ll + (int64_t)(rng() % (1ull << 21));
+	}
+	ColumnData col(db, PhysicalType::INT64);
+	ColumnAppendState astate;
+	col.InitializeAppend(astate);
+	for (idx_t off = 0; off < n; off += STANDARD_VECTOR_SIZE) {
+		UnifiedVectorFormat vdata;
+		vdata.data = (data_ptr_t)(values.data() + off);
+		col.AppendData(astate, vdata, std::min<idx_t>(STANDARD_VECTOR_SIZE, n - off));
+	}
+	std::atomic<bool> stop {false};
+	std::atomic<int> errors {0};
+	std::atomic<idx_t> scans {0};
+	std::vector<std::thread> readers;
+	for (int t = 0; t < 3; t++) {
+		readers.emplace_back([&, t]() {
+			std::mt19937_64 r(t);
+			Vector result(PhysicalType::INT64), one(PhysicalType::INT64);
+			ColumnFetchState fstate;
+			while (!stop.load()) {
+				ColumnScanState state;
+				col.InitializeScan(state);
+				for (idx_t row = 0; row < n;) {
+					idx_t got = col.ScanVector(state, result, std::min<idx_t>(STANDARD_VECTOR_SIZE, n - row));
+					auto out = (const int64_t *)FlatVector::GetData(result);
+					for (idx_t i = 0; i < got; i += 97) {
+						errors += out[i] != values[row + i];
+					}
+					row += got;
+				}
+				for (int q = 0; q < 50; q++) {
+					idx_t row = r() % n;
+					col.FetchRow(fstate, (row_t)row, one, 0);
+					errors += ((int64_t *)FlatVector::GetData(one))[0] != values[row];
+				}
+				scans++;
+			}
+		});
+	}
+	for (int epoch = 0; epoch < 40; epoch++) {
+		for (int rep = 0; rep < 2000; rep++) {
+			db.column_segment_catalog.AddReadAccess(col.segments[(epoch * 3 + rep % 2) % col.segments.size()].get());
+		}
+		db.column_segment_catalog.RunCompactionEpoch();
+	}
+	stop = true;
+	for (auto &t : readers) {
+		t.join();
+	}
+	CHECK(errors.load() == 0);
+	CHECK(scans.load() > 0);
+}
+
 int main() {
+	RunConcurrentPolicy();
 	RunColumnData<int64_t>(PhysicalType::INT64, 32767 * 12 + 500, 1ull << 33, -40000000000ll, false, false, 64);
 	RunColumnData<int64_t>(PhysicalType::INT64, 32767 * 12 + 500, 1ull << 33, -40000000000ll, false, false, 5);
 	RunColumnData<uint32_t>(PhysicalType::UINT32, 65534 * 11 + 77, 1ull << 13, 1000, true, false, 4);
