@@ -1274,12 +1274,27 @@ extern "C" adacom_status adacom_scan_partial(adacom_column *col, uint64_t seg, u
 		                              result_offset, ctx->stream));
 		return ADACOM_OK;
 	}
+	const size_t bytes = scan_count * col->t.size;
+	if (bytes <= ((size_t)1 << 20)) {
+		// the per-vector pull of the drop-in path: no allocator call, the values come back through the context's pinned
+		// staging pair (a D2H copy into pageable memory is staged by the driver anyway, and slower)
+		adacom_status st = ensure_stage(ctx, bytes);
+		if (st != ADACOM_OK) {
+			return st;
+		}
+		LAUNCH(ctx, launch_scan_range(col->t, col->d_desc, (uint32_t)seg, col->raw, start, scan_count, literal, ctx->d_stage, 0,
+		                              ctx->stream));
+		CK(ctx, cudaMemcpyAsync(ctx->h_stage, ctx->d_stage, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(ctx, cudaStreamSynchronize(ctx->stream));
+		memcpy((uint8_t *)result + result_offset * col->t.size, ctx->h_stage, bytes);
+		return ADACOM_OK;
+	}
 	void *d_out = nullptr;
-	CK(ctx, cudaMallocAsync(&d_out, scan_count * col->t.size, ctx->stream));
+	CK(ctx, cudaMallocAsync(&d_out, bytes, ctx->stream));
 	LAUNCH(ctx, launch_scan_range(col->t, col->d_desc, (uint32_t)seg, col->raw, start, scan_count, literal, d_out, 0,
 	                              ctx->stream));
-	CK(ctx, cudaMemcpyAsync((uint8_t *)result + result_offset * col->t.size, d_out, scan_count * col->t.size,
-	                        cudaMemcpyDeviceToHost, ctx->stream));
+	CK(ctx, cudaMemcpyAsync((uint8_t *)result + result_offset * col->t.size, d_out, bytes, cudaMemcpyDeviceToHost,
+	                        ctx->stream));
 	CK(ctx, cudaFreeAsync(d_out, ctx->stream));
 	CK(ctx, cudaStreamSynchronize(ctx->stream));
 	return ADACOM_OK;
