@@ -2168,26 +2168,29 @@ extern "C" adacom_status adacom_fetch_rows(adacom_column *col, uint64_t n, const
 		memcpy(out, ctx->h_small + kSmallFetch * 8, n * col->t.size);
 		return ADACOM_OK;
 	}
-	// validated and copied into the pinned staging buffer in one pass: [segments | rows | answers]
+	// copied into the pinned staging buffer [segments | rows | answers] with two block copies; the (segment, row) pairs are
+	// validated by the kernel (the lowest offending query index comes back through a host-mapped word): walking the
+	// descriptors on the host cost more than the transfer and the kernel together
 	const size_t in_bytes = (size_t)n * 8;
 	adacom_status st = ensure_stage(ctx, in_bytes + (size_t)n * col->t.size);
 	if (st != ADACOM_OK) {
 		return st;
 	}
 	uint32_t *h_seg = (uint32_t *)ctx->h_stage, *h_row = h_seg + n;
-	for (uint64_t q = 0; q < n; q++) {
-		if (seg_idx[q] >= col->n_segs || row_in_seg[q] >= col->h_desc[seg_idx[q]].count) {
-			return fail(ctx, ADACOM_ERR_INVALID, "adacom_fetch_rows: (segment, row) out of range");
-		}
-		h_seg[q] = seg_idx[q];
-		h_row[q] = row_in_seg[q];
-	}
+	memcpy(h_seg, seg_idx, (size_t)n * 4);
+	memcpy(h_row, row_in_seg, (size_t)n * 4);
+	unsigned long long *h_bad = ctx->h_totals + 3, *d_bad = ctx->d_totals + 3;
+	*h_bad = ~0ull;
 	uint32_t *d_seg = (uint32_t *)ctx->d_stage;
 	void *d_out = ctx->d_stage + in_bytes;
 	CK(ctx, cudaMemcpyAsync(d_seg, h_seg, in_bytes, cudaMemcpyHostToDevice, ctx->stream));
-	LAUNCH(ctx, launch_fetch_rows(col->t, col->d_desc, col->raw, n, d_seg, d_seg + n, literal, d_out, ctx->stream));
+	LAUNCH(ctx, launch_fetch_rows(col->t, col->d_desc, col->raw, n, d_seg, d_seg + n, literal, d_out, ctx->stream,
+	                              (uint32_t)col->n_segs, d_bad));
 	CK(ctx, cudaMemcpyAsync(ctx->h_stage + in_bytes, d_out, n * col->t.size, cudaMemcpyDeviceToHost, ctx->stream));
 	CK(ctx, cudaStreamSynchronize(ctx->stream));
+	if (*h_bad != ~0ull) {
+		return fail(ctx, ADACOM_ERR_INVALID, "adacom_fetch_rows: (segment, row) out of range at query " + std::to_string(*h_bad));
+	}
 	memcpy(out, ctx->h_stage + in_bytes, n * col->t.size);
 	return ADACOM_OK;
 }

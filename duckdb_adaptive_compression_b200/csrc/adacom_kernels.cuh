@@ -153,7 +153,8 @@ cudaError_t launch_scan_range(TypeInfo t, const SegDesc *desc, uint32_t seg, con
 
 // batched fetch_row gather
 cudaError_t launch_fetch_rows(TypeInfo t, const SegDesc *desc, const uint8_t *raw, uint64_t n, const uint32_t *seg_idx,
-                              const uint32_t *row_in_seg, int literal, void *out, cudaStream_t stream);
+                              const uint32_t *row_in_seg, int literal, void *out, cudaStream_t stream, uint32_t n_segs = 0,
+                              unsigned long long *bad = nullptr);  // bad: lowest out-of-range query index (atomicMin), or NULL
 
 // batched equality look-ups whose queries share the chunks of their segment (byte-aligned widths 8 / 16 / 32 of
 // re-packed segments only; the host falls back to launch_decode(kModePoint) otherwise).  Queries are sorted by segment;

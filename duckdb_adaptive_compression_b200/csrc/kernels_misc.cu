@@ -51,13 +51,22 @@ __global__ void scan_range_kernel(const SegDesc *desc, uint32_t seg, const uint8
 	}
 }
 
+// `bad` (optional, host-mapped or device word): set to 1 + the index of a query whose (segment, row) lies outside the
+// column; such a query reads nothing and answers 0.  The host-buffer form of adacom_fetch_rows validates here instead of
+// walking the descriptors on the host (that loop cost more than the transfer and the kernel together).
 template <int S>
 __global__ void fetch_rows_kernel(const SegDesc *desc, const uint8_t *raw, uint64_t n, const uint32_t *seg_idx,
-                                  const uint32_t *row_in_seg, int literal, void *out) {
+                                  const uint32_t *row_in_seg, int literal, void *out, uint32_t n_segs,
+                                  unsigned long long *bad) {
 	using T = typename UIntOf<S>::type;
 	for (uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; q < n; q += (uint64_t)gridDim.x * blockDim.x) {
-		const SegDesc *d = desc + __ldg(seg_idx + q);
-		((T *)out)[q] = (T)fetch_value<S>(d, raw, (uint64_t)__ldg(row_in_seg + q), literal);
+		const uint32_t seg = __ldg(seg_idx + q), row = __ldg(row_in_seg + q);
+		if (bad != nullptr && (seg >= n_segs || row >= desc[seg].count)) {
+			atomicMin(bad, (unsigned long long)q);
+			((T *)out)[q] = (T)0;
+			continue;
+		}
+		((T *)out)[q] = (T)fetch_value<S>(desc + seg, raw, (uint64_t)row, literal);
 	}
 }
 
@@ -196,14 +205,15 @@ cudaError_t launch_scan_range(TypeInfo t, const SegDesc *desc, uint32_t seg, con
 }
 
 cudaError_t launch_fetch_rows(TypeInfo t, const SegDesc *desc, const uint8_t *raw, uint64_t n, const uint32_t *seg_idx,
-                              const uint32_t *row_in_seg, int literal, void *out, cudaStream_t stream) {
+                              const uint32_t *row_in_seg, int literal, void *out, cudaStream_t stream, uint32_t n_segs,
+                              unsigned long long *bad) {
 	if (n == 0) {
 		return cudaSuccess;
 	}
 	uint64_t blocks = (n + 255) / 256;
 	uint32_t grid = (uint32_t)(blocks > 148u * 16u ? 148u * 16u : blocks);
 	ADACOM_DISPATCH_SIZE(t.size,
-	                     (fetch_rows_kernel<S><<<grid, 256, 0, stream>>>(desc, raw, n, seg_idx, row_in_seg, literal, out)));
+	                     (fetch_rows_kernel<S><<<grid, 256, 0, stream>>>(desc, raw, n, seg_idx, row_in_seg, literal, out, n_segs, bad)));
 	return cudaGetLastError();
 }
 

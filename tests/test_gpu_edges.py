@@ -259,6 +259,16 @@ def test_argument_errors_are_reported(gpu_ctx):
     with pytest.raises(adacom.AdacomError):
         gpu_ctx.column_from_values(np.arange(10, dtype=np.int64), [10], seg_capacity=5)  # count > capacity
     assert col.scan_sum().count == 1000  # the context is still usable afterwards
+    # large batches are validated by the kernel (the lowest offending query is reported): a bad segment, a bad row
+    seg = np.zeros(5000, dtype=np.uint32)
+    row = (np.arange(5000) % 600).astype(np.uint32)
+    for bad_q, (bs, br) in ((4321, (2, 0)), (77, (1, 400)), (4999, (0, 600))):
+        s2, r2 = seg.copy(), row.copy()
+        s2[bad_q], r2[bad_q] = bs, br
+        with pytest.raises(adacom.AdacomError) as e:
+            col.fetch_rows(s2, r2)
+        assert f"query {bad_q}" in str(e.value)
+    assert np.array_equal(col.fetch_rows(seg, row), row.astype(np.int32))  # and the next valid batch is served
     col.close()
 
 
