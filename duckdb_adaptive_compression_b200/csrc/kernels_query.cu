@@ -1294,7 +1294,7 @@ __global__ void __launch_bounds__(kSWarps * 32, 4) scan_columns_sparse_kernel(co
 // =====================================================================================================================
 constexpr int kDWarps = 4;
 constexpr int kDThreads = kDWarps * 32;
-constexpr int kDIlp = 4;  // 32-row groups a lane works on at a time
+constexpr int kDIlp = 8;  // 32-row groups a lane works on at a time
 
 // one step of the factor program resolved against the current block (per warp, in shared memory)
 struct __align__(16) DenseStep {

@@ -80,14 +80,16 @@ def test_grouped_scan_matches_per_group_passes_on_ragged_data(gpu_ctx):
         col.close()
 
 
-def test_grouped_factor_program_chains_and_duplicates(gpu_ctx):
+@pytest.mark.parametrize("wide_values", [False, True], ids=["int32_values", "values_beyond_int32"])
+def test_grouped_factor_program_chains_and_duplicates(gpu_ctx, wide_values):
     """The dense grouped kernel evaluates the sums as one factor program in which an aggregate that extends another's
     factor list continues its term: shared prefixes in any order, the same product twice, COUNT(*) between them, a
     product over the same column twice, unrelated sums.  Narrow columns so that the dense kernel (32-bit values) runs."""
     rng = np.random.default_rng(11)
     n = 5 * 122880 + 4321
     key = rng.integers(0, 4, size=n).astype(np.uint8)
-    p = rng.integers(900, 100000, size=n).astype(np.int32)
+    # values_beyond_int32: the same kernel in its 64-bit arithmetic mode (values above 2^31, still <= 32-bit payloads)
+    p = (rng.integers(900, 100000, size=n) + (3_000_000_000 if wide_values else 0)).astype(np.uint32 if wide_values else np.int32)
     d = rng.integers(0, 11, size=n).astype(np.uint8)
     t = rng.integers(0, 9, size=n).astype(np.uint8)
     s = rng.integers(0, 3000, size=n).astype(np.int16)
