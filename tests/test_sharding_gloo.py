@@ -80,3 +80,16 @@ def test_combine_handles_carries_and_negative_sums():
     g = np.array([[neg & (2**64 - 1), neg >> 64, 1, 0]], dtype=np.uint64).astype(np.int64).reshape(-1)
     (total, count), = sharding.combine_aggregates(g, 1, signed=True)
     assert total == -12345
+
+
+def test_numa_placement_helper_is_best_effort():
+    """duckdb_adaptive_compression_b200/numa.py: cpulist parsing, and binding never raises (no GPU here: the dict says why)."""
+    import os
+    from duckdb_adaptive_compression_b200 import numa
+    assert numa._parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert numa._parse_cpulist("") == set()
+    before = os.sched_getaffinity(0)
+    info = numa.bind_to_gpu_node(0, 0, 1)
+    assert isinstance(info, dict) and "applied" in info
+    assert os.sched_getaffinity(0) == before or info.get("applied")
+    os.sched_setaffinity(0, before)
