@@ -276,11 +276,22 @@ cudaError_t launch_rle_run_starts(const CodecArgs &args, uint32_t seg_b, uint32_
 // fills groups_out[j] for the jobs of args (after launch_rle_run_starts for RLE)
 cudaError_t launch_codec_groups(TypeInfo t, int codec, const CodecArgs &args, CodecGroup *groups_out, cudaStream_t stream);
 
+// A single-column table filter in canonical form: the decoded value (sign- or zero-extended T) lies in [lo, hi] (compared
+// as T: signed or unsigned), or outside it (complement).  Every comparison of TemplatedFilterSelection, a BETWEEN (AND of
+// two) and an OR of two half-lines fit; `empty`: the range holds no value at all.
+struct FilterRange {
+	uint64_t lo = 0, hi = 0;
+	uint32_t empty = 0, complement = 0;
+};
+
 // the same operator, warp per 2048-value tile (static tile table), lane per 32-row group (pred32); handles every kind of
 // segment (field-comparable ones in the field domain, the others per value); wmax: widest live payload of the column
+// valid32 (bit = column row) / in32 (bit = row - out_row0): optional masks AND-ed into the selection -- NULL rows and
+// rows outside the incoming selection neither pass nor enter the SUM
 cudaError_t launch_filter_words(TypeInfo t, const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw,
-                                int literal, uint32_t op_mask, uint64_t constant, uint32_t *bitmap32, uint64_t out_row0,
-                                Agg *agg, uint32_t wmax, int sm_count, cudaStream_t stream);
+                                int literal, const FilterRange &range, const uint32_t *valid32, const uint32_t *in32,
+                                uint32_t *bitmap32, uint64_t out_row0, Agg *agg, uint32_t wmax, int sm_count,
+                                cudaStream_t stream);
 
 // ---- checkpoint image (kernels_checkpoint.cu) ----
 constexpr uint32_t kBlockAllocSize = 262144;  // Storage::BLOCK_ALLOC_SIZE: 8-byte checksum + Storage::BLOCK_SIZE payload

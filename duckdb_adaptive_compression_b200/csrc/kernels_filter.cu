@@ -242,6 +242,11 @@ __global__ void __launch_bounds__(kFiltThreads, 8) filter_fields_kernel(const Se
 // shares with its neighbours are atomics).  Segments that are not field-comparable (frames that wrap inside T, payloads
 // wider than 32 bits, slot-width segments) take a lane = row path in the same kernel, straight from global memory.
 // =====================================================================================================================
+template <bool SIGNED>
+__device__ __forceinline__ bool t_less(uint64_t a, uint64_t b) {
+	return SIGNED ? (int64_t)a < (int64_t)b : a < b;
+}
+
 constexpr int kFWarps = 8;
 constexpr uint32_t kFRows = 2048;
 constexpr uint32_t kFRun = 4;
@@ -250,10 +255,11 @@ __device__ __forceinline__ void f_cp_async16(void *smem_dst, const void *gmem_sr
 	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr(smem_dst)), "l"(gmem_src) : "memory");
 }
 
-template <int S, bool SIGNED>
+template <int S, bool SIGNED, bool ALLOW>
 __global__ void __launch_bounds__(kFWarps * 32, 3) filter_words_kernel(const SegDesc *desc, const Job *tiles, uint32_t n_tiles,
-                                                                       const uint8_t *raw, int literal, uint32_t op_mask,
-                                                                       uint64_t constant, uint32_t *bitmap32, uint64_t out_row0,
+                                                                       const uint8_t *raw, int literal, const FilterRange fr,
+                                                                       const uint32_t *valid32, const uint32_t *in32,
+                                                                       uint32_t *bitmap32, uint64_t out_row0,
                                                                        Agg *agg, uint32_t window_bytes) {
 	using T = typename UIntOf<S>::type;
 	extern __shared__ __align__(128) uint8_t f_mem[];
@@ -292,27 +298,26 @@ __global__ void __launch_bounds__(kFWarps * 32, 3) filter_words_kernel(const Seg
 				                    (SIGNED ? (int64_t)c_emin <= (int64_t)e_top : c_emin <= e_top);
 				c_kind = 3;
 				if (linear) {
-					const bool below = SIGNED ? (int64_t)constant < (int64_t)c_emin : constant < c_emin;
-					const bool above = SIGNED ? (int64_t)constant > (int64_t)e_top : constant > e_top;
-					const bool p_lt = op_mask & 1u, p_gt = (op_mask >> 2) & 1u;
-					const uint64_t fc = constant - c_emin;
-					c_kind = 1;
+					// the value range [lo, hi] (or its complement) clipped to the segment's interval, in the field domain
+					bool none = fr.empty != 0u;
+					uint64_t l = fr.lo, h = fr.hi;
+					if (!none) {
+						if (t_less<SIGNED>(h, c_emin) || t_less<SIGNED>(e_top, l)) {
+							none = true;  // the segment's interval and the range do not meet (zone map)
+						} else {
+							l = t_less<SIGNED>(l, c_emin) ? c_emin : l;
+							h = t_less<SIGNED>(e_top, h) ? e_top : h;
+						}
+					}
 					c_flo64 = 0;
 					c_span64 = mask64;
-					if (below || above) {
-						// a constant below the interval: every value is greater; above: every value is smaller
-						c_kind = (below ? p_gt : p_lt) ? 1 : 0;
+					if (none) {
+						c_kind = fr.complement ? 1 : 0;  // complement of nothing: every row of the segment
 					} else {
-						switch (op_mask & 7u) {
-						case 1u: c_kind = fc == 0u ? 0 : 1; c_span64 = fc - 1u; break;                                  // <
-						case 3u: c_span64 = fc; break;                                                               // <=
-						case 4u: c_kind = fc == mask64 ? 0 : 1; c_flo64 = fc + 1u; c_span64 = mask64 - c_flo64; break;   // >
-						case 6u: c_flo64 = fc; c_span64 = mask64 - fc; break;                                        // >=
-						case 2u: c_flo64 = fc; c_span64 = 0u; break;                                                 // =
-						case 5u: c_kind = 2; c_flo64 = fc; c_span64 = 0u; break;                                     // <>
-						case 0u: c_kind = 0; break;
-						default: break;                                                                              // everything passes
-						}
+						c_flo64 = l - c_emin;
+						c_span64 = h - l;
+						const bool whole = c_flo64 == 0 && c_span64 == mask64;
+						c_kind = !fr.complement ? 1 : (whole ? 0 : 2);
 					}
 					c_flo = (uint32_t)c_flo64;
 					c_span = (uint32_t)c_span64;
@@ -325,6 +330,24 @@ __global__ void __launch_bounds__(kFWarps * 32, 3) filter_words_kernel(const Seg
 			const uint32_t cnt = min(kFRows, c_count - first);
 			const uint64_t row0 = c_row_start + first;
 			uint32_t sel[2] = {0u, 0u};
+			// optional masks: validity (bit = column row) and the incoming selection (bit = row - out_row0).  allow_word:
+			// the 32 bits of rows [32 g, 32 g + nrows) of the tile (every lane may ask for a different group)
+			constexpr bool has_allow = ALLOW;  // (a kernel of its own: the plain filter keeps its registers)
+			auto mask_bits = [&](const uint32_t *m, uint64_t r, uint32_t nrows) -> uint32_t {
+				const uint32_t sh = (uint32_t)(r & 31u);
+				const uint32_t *p = m + (r >> 5);
+				return __funnelshift_r(__ldg(p), sh + nrows > 32u ? __ldg(p + 1) : 0u, sh);
+			};
+			auto allow_word = [&](uint32_t g, uint32_t nrows) -> uint32_t {
+				uint32_t aw = 0xffffffffu;
+				if (valid32 != nullptr) {
+					aw &= mask_bits(valid32, row0 + 32u * g, nrows);
+				}
+				if (in32 != nullptr) {
+					aw &= mask_bits(in32, row0 - out_row0 + 32u * g, nrows);
+				}
+				return aw;
+			};
 			if (S == 8 && c_kind != 3 && c_w > 32u) {
 				// wide payloads (33 .. 64 bits) in the field domain: the tile is staged in two halves of 1024 rows (128 w
 				// bytes each: 16-byte aligned, and the warp's window stays at 8 KiB so three CTAs fit an SM), lane = row,
@@ -357,7 +380,10 @@ __global__ void __launch_bounds__(kFWarps * 32, 3) filter_words_kernel(const Seg
 						const uint32_t i = gg * 32u + lane;
 						const bool inside = i < hcnt;
 						const uint64_t f = read_bits64(words, (inside ? i : 0u) * w) & mask64;
-						const bool pass = inside && (((f - c_flo64) <= c_span64) != (c_kind == 2));
+						bool pass = inside && (((f - c_flo64) <= c_span64) != (c_kind == 2));
+						if (has_allow) {
+							pass = pass && ((allow_word(half * 32u + gg, min(32u, hcnt - gg * 32u)) >> lane) & 1u);
+						}
 						const uint32_t word = __ballot_sync(0xffffffffu, pass);
 						const uint64_t add = pass ? f : 0ull;
 						fs_lo += add;
@@ -399,7 +425,10 @@ __global__ void __launch_bounds__(kFWarps * 32, 3) filter_words_kernel(const Seg
 					// group would have at this width
 					for (uint32_t gg = 0; gg < full_groups; gg++) {
 						const uint32_t f = window[gg * 32u + lane];
-						const bool pass = ((f - c_flo) <= c_span) != (c_kind == 2);
+						bool pass = ((f - c_flo) <= c_span) != (c_kind == 2);
+						if (has_allow) {
+							pass = pass && ((allow_word(gg, 32u) >> lane) & 1u);
+						}
 						const uint32_t word = __ballot_sync(0xffffffffu, pass);
 						fsum += pass ? (uint64_t)f : 0ull;
 						n += pass ? 1u : 0u;
@@ -417,12 +446,24 @@ __global__ void __launch_bounds__(kFWarps * 32, 3) filter_words_kernel(const Seg
 						if (c_kind == 1) {
 							word = pred32_sum_any(w, window + g * w, 0u, c_flo, c_span, fsum);
 						} else {
-							// value <> c: everything but the fields equal to fc; their sum is count_eq * fc
-							const uint32_t eq = pred32_any(w, window + g * w, 0u, c_flo, 0u);
-							uint64_t all = 0;
+							// outside the field range: everything but the fields inside it
+							uint64_t in_sum = 0, all = 0;
+							const uint32_t inr = pred32_sum_any(w, window + g * w, 0u, c_flo, c_span, in_sum);
 							pred32_sum_any(w, window + g * w, 0u, 0u, 0xffffffffu, all);
-							word = ~eq;
-							fsum += all - (uint64_t)__popc(eq) * c_flo;
+							word = ~inr;
+							fsum += all - in_sum;
+						}
+						if (has_allow) {
+							// rows the masks take out again: their fields leave the sum one by one (NULLs are few)
+							const uint32_t aw = allow_word(g, 32u);
+							uint32_t rem = word & ~aw;
+							word &= aw;
+							const uint32_t mask32 = w >= 32u ? 0xffffffffu : ((1u << w) - 1u);
+							while (rem) {
+								const uint32_t k = (uint32_t)__ffs((int)rem) - 1u;
+								rem &= rem - 1u;
+								fsum -= (uint64_t)(read_bits32(window, (g * 32u + k) * w) & mask32);
+							}
 						}
 						n += __popc(word);
 						sel[0] = j == 0 ? word : sel[0];
@@ -435,7 +476,10 @@ __global__ void __launch_bounds__(kFWarps * 32, 3) filter_words_kernel(const Seg
 					const bool inside = i < cnt;
 					const uint32_t mask32 = w >= 32u ? 0xffffffffu : ((1u << w) - 1u);
 					const uint32_t f = read_bits32(window, (inside ? i : 0u) * w) & mask32;
-					const bool pass = inside && (((f - c_flo) <= c_span) != (c_kind == 2));
+					bool pass = inside && (((f - c_flo) <= c_span) != (c_kind == 2));
+					if (has_allow) {
+						pass = pass && ((allow_word(full_groups, cnt & 31u) >> lane) & 1u);
+					}
 					const uint32_t word = __ballot_sync(0xffffffffu, pass);
 					fsum += pass ? (uint64_t)f : 0ull;
 					n += pass ? 1u : 0u;
@@ -477,7 +521,11 @@ __global__ void __launch_bounds__(kFWarps * 32, 3) filter_words_kernel(const Seg
 							f = (uint64_t)__ldg(slots + i);
 						}
 						v = extend_low<S, SIGNED>(f + c_min_add);
-						pass = cmp_passes<SIGNED>(v, constant, op_mask);
+						const bool inr = !fr.empty && !t_less<SIGNED>(v, fr.lo) && !t_less<SIGNED>(fr.hi, v);
+						pass = inr != (fr.complement != 0u);
+						if (has_allow) {
+							pass = pass && ((allow_word(gg, min(32u, cnt - gg * 32u)) >> lane) & 1u);
+						}
 					}
 					if (pass) {
 						acc.add<SIGNED>(v);
@@ -529,14 +577,21 @@ __global__ void __launch_bounds__(kFWarps * 32, 3) filter_words_kernel(const Seg
 
 template <int S>
 cudaError_t launch_w(bool is_signed, const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw, int literal,
-                     uint32_t op_mask, uint64_t constant, uint32_t *bitmap32, uint64_t out_row0, Agg *agg, uint32_t wmax,
+                     const FilterRange &range, const uint32_t *valid32, const uint32_t *in32, uint32_t *bitmap32, uint64_t out_row0,
+                     Agg *agg, uint32_t wmax,
                      int sm_count, cudaStream_t stream) {
 	// a whole 2048-row tile of a payload <= 32 bits (256 w bytes), or half a tile of a wider one (128 w bytes)
 	const uint32_t narrow = 256u * (wmax < 32u ? wmax : 32u), wide = wmax > 32u ? 128u * (wmax < 64u ? wmax : 64u) : 0u;
 	const uint32_t window = ((narrow > wide ? narrow : wide) + 16u + 127u) & ~127u;
 	const size_t smem = (size_t)kFWarps * window;
-	void (*kernel)(const SegDesc *, const Job *, uint32_t, const uint8_t *, int, uint32_t, uint64_t, uint32_t *, uint64_t, Agg *,
-	               uint32_t) = is_signed ? filter_words_kernel<S, true> : filter_words_kernel<S, false>;
+	void (*kernel)(const SegDesc *, const Job *, uint32_t, const uint8_t *, int, const FilterRange, const uint32_t *, const uint32_t *,
+	               uint32_t *, uint64_t, Agg *,
+	               uint32_t);
+	if (valid32 != nullptr || in32 != nullptr) {
+		kernel = is_signed ? filter_words_kernel<S, true, true> : filter_words_kernel<S, false, true>;
+	} else {
+		kernel = is_signed ? filter_words_kernel<S, true, false> : filter_words_kernel<S, false, false>;
+	}
 	cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 	if (e != cudaSuccess) {
 		return e;
@@ -551,7 +606,7 @@ cudaError_t launch_w(bool is_signed, const SegDesc *desc, const Job *tiles, uint
 	if (grid > need) {
 		grid = need;
 	}
-	kernel<<<(uint32_t)grid, kFWarps * 32, smem, stream>>>(desc, tiles, n_tiles, raw, literal, op_mask, constant, bitmap32, out_row0,
+	kernel<<<(uint32_t)grid, kFWarps * 32, smem, stream>>>(desc, tiles, n_tiles, raw, literal, range, valid32, in32, bitmap32, out_row0,
 	                                                       agg, window);
 	return cudaGetLastError();
 }
@@ -583,16 +638,17 @@ cudaError_t launch_s(bool is_signed, const SegDesc *desc, uint32_t seg_b, uint32
 }  // namespace
 
 cudaError_t launch_filter_words(TypeInfo t, const SegDesc *desc, const Job *tiles, uint32_t n_tiles, const uint8_t *raw,
-                                int literal, uint32_t op_mask, uint64_t constant, uint32_t *bitmap32, uint64_t out_row0,
-                                Agg *agg, uint32_t wmax, int sm_count, cudaStream_t stream) {
+                                int literal, const FilterRange &range, const uint32_t *valid32, const uint32_t *in32,
+                                uint32_t *bitmap32, uint64_t out_row0, Agg *agg, uint32_t wmax, int sm_count,
+                                cudaStream_t stream) {
 	if (n_tiles == 0) {
 		return cudaSuccess;
 	}
 	switch (t.size) {
-	case 1: return launch_w<1>(t.is_signed, desc, tiles, n_tiles, raw, literal, op_mask, constant, bitmap32, out_row0, agg, wmax, sm_count, stream);
-	case 2: return launch_w<2>(t.is_signed, desc, tiles, n_tiles, raw, literal, op_mask, constant, bitmap32, out_row0, agg, wmax, sm_count, stream);
-	case 4: return launch_w<4>(t.is_signed, desc, tiles, n_tiles, raw, literal, op_mask, constant, bitmap32, out_row0, agg, wmax, sm_count, stream);
-	case 8: return launch_w<8>(t.is_signed, desc, tiles, n_tiles, raw, literal, op_mask, constant, bitmap32, out_row0, agg, wmax, sm_count, stream);
+	case 1: return launch_w<1>(t.is_signed, desc, tiles, n_tiles, raw, literal, range, valid32, in32, bitmap32, out_row0, agg, wmax, sm_count, stream);
+	case 2: return launch_w<2>(t.is_signed, desc, tiles, n_tiles, raw, literal, range, valid32, in32, bitmap32, out_row0, agg, wmax, sm_count, stream);
+	case 4: return launch_w<4>(t.is_signed, desc, tiles, n_tiles, raw, literal, range, valid32, in32, bitmap32, out_row0, agg, wmax, sm_count, stream);
+	case 8: return launch_w<8>(t.is_signed, desc, tiles, n_tiles, raw, literal, range, valid32, in32, bitmap32, out_row0, agg, wmax, sm_count, stream);
 	default: return cudaErrorInvalidValue;
 	}
 }

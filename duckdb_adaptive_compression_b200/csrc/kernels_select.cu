@@ -5,9 +5,10 @@
 // CONJUNCTION_OR (:688-716), refining an incoming selection (the `sel` vector) and followed by the aggregate DuckDB
 // runs above the scan (SUM / COUNT skip NULL rows through the validity column).
 //
-// This is the catch-all path: any width 1..64, raw slots, validity mask, selection in / out.  The single-comparison,
-// all-valid case runs on the field-domain kernels (kernels_filter.cu, decode_kernel<filter>); this kernel decodes per
-// value.  Job = (segment, 2048-row tile) from the column's static tile table; lane = consecutive rows, so a ballot is
+// This is the catch-all path: any width 1..64, raw slots, validity mask, selection in / out.  Conjunctions that amount
+// to one value range over the valid rows (adacom_capi.cu: canonical_filter_range) run on the field-domain kernel
+// (kernels_filter.cu, filter_words_kernel<.., ALLOW>); this kernel decodes per value and serves the rest (IS NULL
+// children, two separate ranges, 8-byte columns with slot-width segments).  Job = (segment, 2048-row tile) from the column's static tile table; lane = consecutive rows, so a ballot is
 // 32 consecutive selection bits.  Algorithmic bytes: packed payload + 1 bit per row per bitmap / validity word read.
 #include "adacom_kernels.cuh"
 

@@ -291,7 +291,11 @@ typedef struct {
  *   out->count    = selected rows (approved_tuple_count), out->reserved = selected rows that are valid (COUNT(col)),
  *   out->sum      = SUM over the selected valid rows (DuckDB's aggregates skip NULLs),
  *   device_bitmap_out (optional, zeroed by the call): the new selection, bit (row - row_start(seg_begin)).
- * Nested filters (AND of ORs) chain calls through the bitmaps, like the recursion of FilterSelection. */
+ * Nested filters (AND of ORs) chain calls through the bitmaps, like the recursion of FilterSelection.
+ * A conjunction that amounts to ONE value range over the valid rows (or the complement of one: any single comparison,
+ * BETWEEN, an OR of two half-lines, with or without IS NOT NULL) runs on the field-domain filter kernel with the
+ * validity / selection words AND-ed in; IS NULL children and conjunctions that leave two separate ranges decode per
+ * value.  Same results either way. */
 adacom_status adacom_scan_select(adacom_column *col, uint64_t seg_begin, uint64_t seg_end, int flags,
                                  const adacom_pred *preds, uint32_t n_preds, adacom_conj conj, const uint64_t *validity,
                                  int validity_on_device, const uint64_t *device_bitmap_in, uint64_t *device_bitmap_out,

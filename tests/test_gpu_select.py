@@ -183,3 +183,55 @@ def test_scan_select_nulls_conjunctions(gpu_ctx, port_oracle, dtype):
     plain = col.scan_sum()
     assert plain.sum % MOD == int(allv.astype(object).sum()) % MOD
     col.close()
+
+
+@pytest.mark.parametrize("dtype", [np.int8, np.uint16, np.int32, np.int64, np.uint64], ids=lambda d: np.dtype(d).name)
+def test_scan_select_random_conjunctions(gpu_ctx, port_oracle, dtype):
+    """Random conjunctions of 1..4 children: the range canonicalisation in front of the filter-words kernel (AND =
+    intersection with <> holes, OR = merged ranges / complement of the gap, constants at the ends of the type's domain
+    and next to each other) and the per-value fallback must both give the oracle's selection."""
+    S = np.dtype(dtype).itemsize
+    info = np.iinfo(dtype)
+    rng = np.random.default_rng(77 + S)
+    counts = [33, 2048, 4100]
+    cases = [c for c in sweep_cases(dtype, counts=counts) if c[0] % 5 == 2 or c[0] == 8 * S][:12]
+    col, vals, segs, starts, words = _build(gpu_ctx, port_oracle, dtype, cases, validity_frac=0.1, seed=3)
+    allv = np.concatenate([s.decode_all() for s in segs])
+    b, e = 1, len(segs)
+    rows = int(starts[e] - starts[b])
+    nw = (rows + 63) // 64
+    bm_out = _dev_words(nw)
+    import torch
+    sel_in = rng.integers(0, 1 << 63, size=nw + 2, dtype=np.int64) | rng.integers(0, 1 << 63, size=nw + 2, dtype=np.int64)
+    bm_in = torch.from_numpy(sel_in).to("cuda:0")
+    pool = [info.min, info.max, info.min + 1, info.max - 1, int(np.median(allv))]
+    for trial in range(60):
+        anchor = int(allv[int(rng.integers(0, len(allv)))])
+        near = [min(max(anchor + d, info.min), info.max) for d in (-1, 0, 1, 2)]
+        preds = []
+        for _ in range(int(rng.integers(1, 5))):
+            if rng.random() < 0.12:
+                preds.append(("is_not_null",))
+            else:
+                c = (pool + near + [int(allv[int(rng.integers(0, len(allv)))])])[int(rng.integers(0, 10))]
+                preds.append(("cmp", int(rng.integers(0, 6)), c))
+        conj = int(rng.integers(0, 2))
+        use_in = trial % 3 == 0
+        use_valid = trial % 4 != 3
+        bm_out.fill_(-1)
+        _sync()
+        got, got_valid = col.scan_select(preds, conj, validity=words if use_valid else None, seg_begin=b, seg_end=e,
+                                         bitmap_in=bm_in.data_ptr() if use_in else None, bitmap_out=bm_out.data_ptr())
+        want_bm = np.zeros(nw, dtype=np.uint64)
+        wsum = wcnt = wvalid = 0
+        in_np = sel_in.view(np.uint64) if use_in else None
+        for g in range(b, e):
+            sm, c, nv = segs[g].select(preds, conj, validity=words if use_valid else None, validity_row0=int(starts[g]),
+                                       bitmap_in=in_np, bitmap_out=want_bm, bitmap_row0=int(starts[g] - starts[b]))
+            wsum += sm
+            wcnt += c
+            wvalid += nv
+        assert np.array_equal(_to_np(bm_out, nw), want_bm), (np.dtype(dtype).name, preds, conj)
+        assert (got.count, got_valid) == (wcnt, wvalid), (preds, conj)
+        assert got.sum % MOD == wsum % MOD, (preds, conj)
+    col.close()
