@@ -169,8 +169,10 @@ constexpr int kStagedThreads = kPackThreads + 32;
 
 struct PackStage {
 	PackTile t;
-	uint32_t mis;   // byte offset of the tile's first slot inside the staged (16-byte aligned) bytes
-	uint32_t done;  // sentinel
+	uint32_t mis;      // byte offset of the tile's first slot inside the staged (16-byte aligned) bytes
+	uint32_t done;     // sentinel
+	uint32_t n_words;  // output words of the tile
+	uint32_t magic;    // ceil(2^20 / w): m / w for m < 2048 as a multiply-shift (phase C's row of a word)
 };
 
 // staged phase A: slots (already in shared memory) -> swizzled fields
@@ -261,6 +263,9 @@ __global__ void __launch_bounds__(kStagedThreads, StagedSmem<S>::kMinCtas) pack_
 				st.mis = (uint32_t)((uint64_t)st.t.src - src16);
 				bytes = (st.mis + st.t.cnt * S + 15u) & ~15u;  // the raw arena is padded: the tail over-read stays inside
 				st.done = 0;
+				// once per tile here instead of once per consumer thread (the division was 7 % of the kernel's instructions)
+				st.n_words = (st.t.cnt * st.t.w + 63u) >> 6;
+				st.magic = st.t.w ? ((1u << 20) + st.t.w - 1u) / st.t.w : 0u;
 			}
 			uint32_t todo = __ballot_sync(0xffffffffu, st.t.cnt != 0);
 			while (todo) {
@@ -294,6 +299,52 @@ __global__ void __launch_bounds__(kStagedThreads, StagedSmem<S>::kMinCtas) pack_
 			break;
 		}
 		const PackTile t = infos[s].t;
+		const uint32_t n_words = infos[s].n_words, magic = infos[s].magic;
+		if constexpr (S == 1) {
+			// One-byte slots, w <= 7: 8 consecutive values are exactly w output bytes, so a thread packs its own 8
+			// slots with word-parallel arithmetic and the phases A / B (a shared-memory round trip per field and a
+			// barrier) fall away.  Four slots per register: (x | 0x80..) - (min & 0x7f..) cannot borrow across bytes
+			// and its low 7 bits per byte are the field's (w <= 7 masks the rest); two shift-and-merge steps squeeze the
+			// four w-bit fields together.  The w bytes go to a double-buffered byte image of the tile (the field area).
+			const uint32_t a = infos[s].mis + 8u * tid;
+			const uint32_t *w32 = (const uint32_t *)(ring + s * StagedSmem<S>::kRawBytes) + (a >> 2);
+			const uint32_t sh = (a & 3u) * 8u;
+			const uint32_t r0 = w32[0], r1 = w32[1], r2 = w32[2];
+			uint32_t x0 = __funnelshift_r(r0, r1, sh), x1 = __funnelshift_r(r1, r2, sh);
+			const uint32_t w = t.w;
+			const uint32_t sub7 = ((uint32_t)t.sub & 0x7fu) * 0x01010101u, fmask = ((1u << w) - 1u) * 0x01010101u;
+			x0 = ((x0 | 0x80808080u) - sub7) & fmask;
+			x1 = ((x1 | 0x80808080u) - sub7) & fmask;
+			if (t.cnt != kVectorSize) {  // slots behind the segment's last value: zero fields
+				const int v = (int)t.cnt - (int)(8u * tid);
+				x0 &= v >= 4 ? 0xffffffffu : (v <= 0 ? 0u : (1u << (8 * v)) - 1u);
+				x1 &= v >= 8 ? 0xffffffffu : (v <= 4 ? 0u : (1u << (8 * (v - 4))) - 1u);
+			}
+			const uint32_t p0 = (x0 & 0x00ff00ffu) | ((x0 & 0xff00ff00u) >> (8u - w));
+			const uint32_t p1 = (x1 & 0x00ff00ffu) | ((x1 & 0xff00ff00u) >> (8u - w));
+			const uint32_t q0 = (p0 & 0xffffu) | ((p0 >> 16) << (2u * w));
+			const uint32_t q1 = (p1 & 0xffffu) | ((p1 >> 16) << (2u * w));
+			const uint64_t c = (uint64_t)q0 | ((uint64_t)q1 << (4u * w));
+			uint8_t *image = (uint8_t *)fld + (it & 1u) * (kVectorSize * 7u / 8u);
+			uint8_t *o = image + tid * w;
+#pragma unroll
+			for (uint32_t k = 0; k < 7u; k++) {
+				if (k < w) {
+					o[k] = (uint8_t)(c >> (8u * k));
+				}
+			}
+			asm volatile("bar.sync 1, %0;" ::"n"(kPackThreads) : "memory");
+			if (tid == 0) {
+				mbar_arrive(&empty_bar[s]);
+			}
+			if (tid < n_words) {
+				t.out[tid] = ((const uint64_t *)image)[tid];
+			}
+			if (tid < t.gap) {
+				t.out[n_words + tid] = 0ull;
+			}
+			continue;
+		}
 		{
 			// phase A from shared memory: slot -> field, parked at its swizzled position.  Value i = j*256 + tid sits
 			// in row j*4 + tid/64, so its position i ^ (row & 31) is j*256 + ((tid ^ tid/64) ^ 4j): one XOR with a
@@ -322,10 +373,7 @@ __global__ void __launch_bounds__(kStagedThreads, StagedSmem<S>::kMinCtas) pack_
 			break;
 		}
 		asm volatile("bar.sync 1, %0;" ::"n"(kPackThreads) : "memory");
-		const uint32_t w = t.w;
-		const uint32_t n_words = (t.cnt * w + 63u) >> 6;
-		const uint32_t magic = ((1u << 20) + w - 1u) / w;
-		const uint32_t pad = (w & 1u) ^ 1u;
+		const uint32_t pad = (t.w & 1u) ^ 1u;
 		for (uint32_t m = tid; m < n_words; m += kPackThreads) {
 			const uint32_t row = (m * magic) >> 20;
 			t.out[m] = ostage[m + row * pad];
