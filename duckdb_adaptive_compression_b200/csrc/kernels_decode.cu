@@ -369,6 +369,36 @@ __global__ void __launch_bounds__(kThreads, StageCfg<S, MODE>::kMinCtas) decode_
 				constexpr int VS = 8 / S;                          // values per store
 				constexpr int GROUPS = kVectorSize / kGroupThreads / VS;  // stores per thread
 				uint64_t *dst = (uint64_t *)((T *)a.out + (in.row - a.out_row0)) + gtid;
+				if (S == 1) {
+					// one-byte slots: the 8 values of a store are exactly w payload bytes (w <= 7 re-packed, w = 8 for a
+					// slot-width segment).  They are spread word-parallel -- 4w bits -> two 2w-bit pairs at 16-bit positions
+					// -> four fields at byte positions -- and the frame of reference is added to four slots at once: the
+					// low 7 bits per byte cannot carry into the next byte, and the top bit is an XOR.  ~30 instructions per
+					// 8 values against ~80 for eight separate field reads.
+					const bool spread = w < 8u;
+					const uint32_t fm = ((1u << w) - 1u) * 0x01010101u, fm_even = fm & 0x00ff00ffu, fm_odd = fm & 0xff00ff00u;
+					const uint32_t m4 = spread ? (1u << (4u * w)) - 1u : 0u, m2 = (1u << (2u * w)) - 1u;
+					const uint32_t add7 = ((uint32_t)in.min_add & 0x7fu) * 0x01010101u;
+					const uint32_t add80 = ((uint32_t)in.min_add & 0x80u) * 0x01010101u;
+					const uint32_t byte0 = in.bit_base >> 3;
+#pragma unroll
+					for (int j = 0; j < GROUPS; j++) {
+						const uint32_t at = byte0 + (uint32_t)(j * kGroupThreads + gtid) * w;
+						const uint32_t *p32 = words32 + (at >> 2);
+						const uint32_t sh = (at & 3u) * 8u;
+						const uint32_t r0 = p32[0], r1 = p32[1], r2 = p32[2];
+						uint32_t x0 = __funnelshift_r(r0, r1, sh), x1 = __funnelshift_r(r1, r2, sh);
+						if (spread) {
+							const uint32_t q0 = x0 & m4, q1 = __funnelshift_r(x0, x1, 4u * w) & m4;
+							const uint32_t p0 = (q0 & m2) | ((q0 >> (2u * w)) << 16), p1 = (q1 & m2) | ((q1 >> (2u * w)) << 16);
+							x0 = (p0 & fm_even) | ((p0 << (8u - w)) & fm_odd);
+							x1 = (p1 & fm_even) | ((p1 << (8u - w)) & fm_odd);
+						}
+						const uint32_t y0 = ((x0 & 0x7f7f7f7fu) + add7) ^ ((x0 & 0x80808080u) ^ add80);
+						const uint32_t y1 = ((x1 & 0x7f7f7f7fu) + add7) ^ ((x1 & 0x80808080u) ^ add80);
+						dst[j * kGroupThreads] = (uint64_t)y0 | ((uint64_t)y1 << 32);
+					}
+				} else
 #pragma unroll
 				for (int j = 0; j < GROUPS; j++) {
 					const uint32_t i0 = (j * kGroupThreads + gtid) * VS;
