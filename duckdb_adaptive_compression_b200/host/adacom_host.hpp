@@ -415,6 +415,66 @@ private:
 	friend class ColumnData;
 };
 
+// ---- table filters pushed to one column (src/include/duckdb/planner/table_filter.hpp:21-27, planner/filter/*.hpp) --
+// Same class names, members and enum values as the reference; the constant of a comparison is an integer (the path
+// covers the integer physical types).
+enum class TableFilterType : uint8_t {
+	CONSTANT_COMPARISON = 0, IS_NULL = 1, IS_NOT_NULL = 2, CONJUNCTION_OR = 3, CONJUNCTION_AND = 4
+};
+enum class ExpressionType : uint8_t {  // src/include/duckdb/common/enums/expression_type.hpp:34-46
+	COMPARE_EQUAL = 25, COMPARE_NOTEQUAL = 26, COMPARE_LESSTHAN = 27, COMPARE_GREATERTHAN = 28,
+	COMPARE_LESSTHANOREQUALTO = 29, COMPARE_GREATERTHANOREQUALTO = 30
+};
+class TableFilter {
+public:
+	explicit TableFilter(TableFilterType filter_type_p) : filter_type(filter_type_p) {
+	}
+	virtual ~TableFilter() = default;
+	TableFilterType filter_type;
+};
+class ConstantFilter : public TableFilter {  // planner/filter/constant_filter.hpp:17-24
+public:
+	ConstantFilter(ExpressionType comparison_type_p, int64_t constant_p)
+	    : TableFilter(TableFilterType::CONSTANT_COMPARISON), comparison_type(comparison_type_p), constant(constant_p) {
+	}
+	ExpressionType comparison_type;
+	int64_t constant;
+};
+class IsNullFilter : public TableFilter {
+public:
+	IsNullFilter() : TableFilter(TableFilterType::IS_NULL) {
+	}
+};
+class IsNotNullFilter : public TableFilter {
+public:
+	IsNotNullFilter() : TableFilter(TableFilterType::IS_NOT_NULL) {
+	}
+};
+class ConjunctionFilter : public TableFilter {  // planner/filter/conjunction_filter.hpp:15-24
+public:
+	explicit ConjunctionFilter(TableFilterType filter_type_p) : TableFilter(filter_type_p) {
+	}
+	std::vector<unique_ptr<TableFilter>> child_filters;
+};
+class ConjunctionOrFilter : public ConjunctionFilter {
+public:
+	ConjunctionOrFilter() : ConjunctionFilter(TableFilterType::CONJUNCTION_OR) {
+	}
+};
+class ConjunctionAndFilter : public ConjunctionFilter {
+public:
+	ConjunctionAndFilter() : ConjunctionFilter(TableFilterType::CONJUNCTION_AND) {
+	}
+};
+//! What DuckDB computes above a filtered scan of one column: approved_tuple_count of FilterSelection
+//! (column_segment.cpp:685-844) and COUNT(col) / SUM(col) over the approved rows (NULL rows do not enter them)
+struct FilterAggregateResult {
+	idx_t approved_tuple_count = 0;
+	idx_t valid_count = 0;
+	uint64_t sum_lo = 0;  // 128-bit two's complement (HUGEINT)
+	uint64_t sum_hi = 0;
+};
+
 // ---- ColumnData: the owner of a column's segments (src/storage/table/column_data.cpp) ---------------------
 // Same entry points as the reference for the succinct path: AppendData (:249-270), InitializeScan[WithOffset]
 // (:73-89), ScanVector (:92-139), FetchRow (:304-315).  What is new is below the segments: all sealed segments of the
@@ -437,6 +497,12 @@ public:
 	void FetchRows(const row_t *row_ids, idx_t count, Vector &result);
 	idx_t GetMaxEntry() const;
 	ColumnSegment *GetSegment(idx_t row_idx) const;
+	//! The table filter of this column and the aggregate above it in one pass over the packed payload (the work of
+	//! ColumnData::Select -> ColumnSegment::FilterSelection on every vector, column_segment.cpp:685-844, plus the
+	//! SUM / COUNT DuckDB runs on the approved rows): one adacom_scan_select per run of segments that share a
+	//! device column.  Leaf filters and conjunctions of leaves (same-kind nesting is flattened); a conjunction
+	//! that mixes AND and OR levels throws -- such filters chain adacom_scan_select calls through selection bitmaps.
+	FilterAggregateResult FilterAggregate(const TableFilter &filter);
 
 	//! move every sealed (full or finalized) segment that is still host-staged into the shared device column and
 	//! compact them with one analyze + one encode; called by the append path every `pending_limit` segments, by

@@ -447,4 +447,104 @@ void ColumnData::UncompactMany(const std::vector<CompactableSegment *> &list) {
 	}
 }
 
+// ---- filter pushdown ---------------------------------------------------------------------------------------
+
+static adacom_cmp ToAdacomCmp(ExpressionType t) {
+	switch (t) {
+	case ExpressionType::COMPARE_EQUAL: return ADACOM_CMP_EQ;
+	case ExpressionType::COMPARE_NOTEQUAL: return ADACOM_CMP_NE;
+	case ExpressionType::COMPARE_LESSTHAN: return ADACOM_CMP_LT;
+	case ExpressionType::COMPARE_GREATERTHAN: return ADACOM_CMP_GT;
+	case ExpressionType::COMPARE_LESSTHANOREQUALTO: return ADACOM_CMP_LE;
+	case ExpressionType::COMPARE_GREATERTHANOREQUALTO: return ADACOM_CMP_GE;
+	default: throw InternalException("Unknown comparison type for filter pushed down to table!");  // column_segment.cpp:771
+	}
+}
+
+static void FlattenFilter(const TableFilter &filter, TableFilterType level, std::vector<adacom_pred> &preds) {
+	switch (filter.filter_type) {
+	case TableFilterType::CONSTANT_COMPARISON: {
+		auto &f = static_cast<const ConstantFilter &>(filter);
+		preds.push_back(adacom_pred {ADACOM_PRED_COMPARE, (int32_t)ToAdacomCmp(f.comparison_type), f.constant});
+		break;
+	}
+	case TableFilterType::IS_NULL:
+		preds.push_back(adacom_pred {ADACOM_PRED_IS_NULL, 0, 0});
+		break;
+	case TableFilterType::IS_NOT_NULL:
+		preds.push_back(adacom_pred {ADACOM_PRED_IS_NOT_NULL, 0, 0});
+		break;
+	case TableFilterType::CONJUNCTION_AND:
+	case TableFilterType::CONJUNCTION_OR: {
+		if (filter.filter_type != level) {
+			throw InternalException("ColumnData::FilterAggregate: AND and OR levels mixed in one filter (chain "
+			                        "adacom_scan_select through selection bitmaps)");
+		}
+		for (auto &child : static_cast<const ConjunctionFilter &>(filter).child_filters) {
+			FlattenFilter(*child, level, preds);
+		}
+		break;
+	}
+	default:
+		throw InternalException("FIXME: unsupported type for filter selection");  // column_segment.cpp:841
+	}
+}
+
+FilterAggregateResult ColumnData::FilterAggregate(const TableFilter &filter) {
+	std::vector<adacom_pred> preds;
+	const TableFilterType level =
+	    filter.filter_type == TableFilterType::CONJUNCTION_OR ? TableFilterType::CONJUNCTION_OR : TableFilterType::CONJUNCTION_AND;
+	FlattenFilter(filter, level, preds);
+	if (preds.size() > ADACOM_MAX_PREDS) {
+		throw InternalException("ColumnData::FilterAggregate: more than ADACOM_MAX_PREDS children");
+	}
+	const adacom_conj conj = level == TableFilterType::CONJUNCTION_OR ? ADACOM_CONJ_OR : ADACOM_CONJ_AND;
+	// sealed segments that still wait on the host join a shared device column first (what the first scan does)
+	CompactPending(true);
+	FilterAggregateResult result;
+	auto add = [&](const adacom_agg &a) {
+		result.approved_tuple_count += a.count;
+		result.valid_count += a.reserved;
+		const uint64_t lo = result.sum_lo + a.sum_lo;
+		result.sum_hi += a.sum_hi + (lo < a.sum_lo ? 1 : 0);
+		result.sum_lo = lo;
+	};
+	std::lock_guard<std::mutex> guard(lock);
+	// runs of consecutive members of one shared device column -> one call; a segment on its own (detached by an
+	// append after Uncompact, or never compacted) is scanned through its own single-segment column
+	idx_t i = 0;
+	while (i < segments.size()) {
+		ColumnSegment *s = segments[i].get();
+		if (s->count == 0) {
+			i++;
+			continue;
+		}
+		adacom_agg agg;
+		if (s->gpu_column && !s->owns_gpu_column) {
+			idx_t j = i + 1;
+			while (j < segments.size() && segments[j]->gpu_column == s->gpu_column && !segments[j]->owns_gpu_column &&
+			       segments[j]->gpu_index == s->gpu_index + (j - i)) {
+				j++;
+			}
+			const uint64_t *validity = nullptr;
+			for (auto &b : batches) {
+				if (b.col == s->gpu_column) {
+					validity = b.validity;
+				}
+			}
+			GPU_CHECK(db, adacom_scan_select(s->gpu_column, s->gpu_index, s->gpu_index + (j - i), 0, preds.data(),
+			                                 (uint32_t)preds.size(), conj, validity, 0, nullptr, nullptr, &agg));
+			i = j;
+		} else {
+			s->Upload();
+			GPU_CHECK(db, adacom_scan_select(s->gpu_column, 0, 1, 0, preds.data(), (uint32_t)preds.size(), conj,
+			                                 s->staging_has_nulls ? s->staging_validity.data() : nullptr, 0, nullptr,
+			                                 nullptr, &agg));
+			i++;
+		}
+		add(agg);
+	}
+	return result;
+}
+
 }  // namespace adacom_host

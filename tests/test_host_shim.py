@@ -35,7 +35,8 @@ def test_shim_exports_reference_surface():
                 "adacom_host::ColumnData::AppendData", "adacom_host::ColumnData::ScanVector",
                 "adacom_host::ColumnData::InitializeScanWithOffset", "adacom_host::ColumnData::FetchRow",
                 "adacom_host::ColumnData::FetchRows", "adacom_host::ColumnData::CompactPending",
-                "adacom_host::ColumnData::CompactMany", "adacom_host::ColumnData::UncompactMany"]:
+                "adacom_host::ColumnData::CompactMany", "adacom_host::ColumnData::UncompactMany",
+                "adacom_host::ColumnData::FilterAggregate"]:
         assert sym in out, sym
 
 
