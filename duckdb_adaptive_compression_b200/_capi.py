@@ -84,6 +84,8 @@ _PROTOTYPES = {
     "adacom_event_destroy": (None, [_vp, _vp]),
     "adacom_host_alloc": (_i, [_vp, C.c_size_t, C.POINTER(_vp)]),
     "adacom_host_free": (None, [_vp, _vp]),
+    "adacom_device_alloc": (_i, [_vp, C.c_size_t, C.POINTER(_vp)]),
+    "adacom_device_free": (None, [_vp, _vp]),
     "adacom_flush_l2": (_i, [_vp]),
     "adacom_column_create": (_i, [_vp, _i, _u64, _vp, _u32, C.POINTER(_vp)]),
     "adacom_column_destroy": (None, [_vp]),

@@ -524,6 +524,27 @@ extern "C" void adacom_host_free(adacom_ctx *ctx, void *ptr) {
 	}
 }
 
+extern "C" adacom_status adacom_device_alloc(adacom_ctx *ctx, size_t bytes, void **out) {
+	if (!ctx || !out) {
+		return ADACOM_ERR_INVALID;
+	}
+	CtxLock lock(ctx);
+	cudaError_t e = cudaMalloc(out, bytes ? bytes : 1);
+	if (e != cudaSuccess) {
+		*out = nullptr;
+		return fail(ctx, ADACOM_ERR_NOMEM, std::string("cudaMalloc: ") + cudaGetErrorString(e));
+	}
+	return ADACOM_OK;
+}
+
+extern "C" void adacom_device_free(adacom_ctx *ctx, void *ptr) {
+	if (ctx && ptr) {
+		CtxLock lock(ctx);
+		cudaStreamSynchronize(ctx->stream);  // kernels of this context may still read the buffer
+		cudaFree(ptr);
+	}
+}
+
 extern "C" adacom_status adacom_flush_l2(adacom_ctx *ctx) {
 	if (!ctx) {
 		return ADACOM_ERR_INVALID;

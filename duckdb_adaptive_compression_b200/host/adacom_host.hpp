@@ -500,8 +500,9 @@ public:
 	//! The table filter of this column and the aggregate above it in one pass over the packed payload (the work of
 	//! ColumnData::Select -> ColumnSegment::FilterSelection on every vector, column_segment.cpp:685-844, plus the
 	//! SUM / COUNT DuckDB runs on the approved rows): one adacom_scan_select per run of segments that share a
-	//! device column.  Leaf filters and conjunctions of leaves (same-kind nesting is flattened); a conjunction
-	//! that mixes AND and OR levels throws -- such filters chain adacom_scan_select calls through selection bitmaps.
+	//! device column.  Leaf filters, conjunctions of leaves (same-kind nesting is flattened) and an AND whose children
+	//! include OR groups of leaves (IN lists): one call per group, chained through device selection bitmaps like the
+	//! recursion of FilterSelection.  An AND group under an OR (a union of selections) throws.
 	FilterAggregateResult FilterAggregate(const TableFilter &filter);
 
 	//! move every sealed (full or finalized) segment that is still host-staged into the shared device column and

@@ -490,15 +490,52 @@ static void FlattenFilter(const TableFilter &filter, TableFilterType level, std:
 	}
 }
 
-FilterAggregateResult ColumnData::FilterAggregate(const TableFilter &filter) {
+namespace {
+// One adacom_scan_select: the children of one conjunction level
+struct FilterStage {
 	std::vector<adacom_pred> preds;
-	const TableFilterType level =
-	    filter.filter_type == TableFilterType::CONJUNCTION_OR ? TableFilterType::CONJUNCTION_OR : TableFilterType::CONJUNCTION_AND;
-	FlattenFilter(filter, level, preds);
-	if (preds.size() > ADACOM_MAX_PREDS) {
-		throw InternalException("ColumnData::FilterAggregate: more than ADACOM_MAX_PREDS children");
+	adacom_conj conj = ADACOM_CONJ_AND;
+};
+}  // namespace
+
+FilterAggregateResult ColumnData::FilterAggregate(const TableFilter &filter) {
+	// The filter becomes a chain of stages, each one call that refines the selection of the one before (the recursion
+	// of FilterSelection, column_segment.cpp:688-723): the leaves of the top level, then -- under an AND -- every OR
+	// group of leaves (what an IN list or a pushed OR looks like).  An AND group under an OR would need the union of two
+	// selections and is refused.
+	std::vector<FilterStage> stages;
+	const bool top_or = filter.filter_type == TableFilterType::CONJUNCTION_OR;
+	FilterStage top;
+	top.conj = top_or ? ADACOM_CONJ_OR : ADACOM_CONJ_AND;
+	if (filter.filter_type == TableFilterType::CONJUNCTION_AND) {
+		std::vector<const TableFilter *> todo {&filter};
+		while (!todo.empty()) {
+			const TableFilter *f = todo.back();
+			todo.pop_back();
+			if (f->filter_type == TableFilterType::CONJUNCTION_AND) {
+				for (auto &child : static_cast<const ConjunctionFilter *>(f)->child_filters) {
+					todo.push_back(child.get());
+				}
+			} else if (f->filter_type == TableFilterType::CONJUNCTION_OR) {
+				FilterStage group;
+				group.conj = ADACOM_CONJ_OR;
+				FlattenFilter(*f, TableFilterType::CONJUNCTION_OR, group.preds);
+				stages.push_back(std::move(group));
+			} else {
+				FlattenFilter(*f, TableFilterType::CONJUNCTION_AND, top.preds);
+			}
+		}
+	} else {
+		FlattenFilter(filter, top_or ? TableFilterType::CONJUNCTION_OR : TableFilterType::CONJUNCTION_AND, top.preds);
 	}
-	const adacom_conj conj = level == TableFilterType::CONJUNCTION_OR ? ADACOM_CONJ_OR : ADACOM_CONJ_AND;
+	if (!top.preds.empty() || stages.empty()) {
+		stages.insert(stages.begin(), std::move(top));
+	}
+	for (auto &st : stages) {
+		if (st.preds.size() > ADACOM_MAX_PREDS) {
+			throw InternalException("ColumnData::FilterAggregate: more than ADACOM_MAX_PREDS children in one conjunction");
+		}
+	}
 	// sealed segments that still wait on the host join a shared device column first (what the first scan does)
 	CompactPending(true);
 	FilterAggregateResult result;
@@ -510,8 +547,38 @@ FilterAggregateResult ColumnData::FilterAggregate(const TableFilter &filter) {
 		result.sum_lo = lo;
 	};
 	std::lock_guard<std::mutex> guard(lock);
-	// runs of consecutive members of one shared device column -> one call; a segment on its own (detached by an
-	// append after Uncompact, or never compacted) is scanned through its own single-segment column
+	// selection bitmaps between the stages (device memory, 1 bit per row of the largest run)
+	adacom_ctx *ctx = db.Gpu(device);
+	void *bitmaps[2] = {nullptr, nullptr};
+	struct Release {
+		adacom_ctx *ctx;
+		void **b;
+		~Release() {
+			adacom_device_free(ctx, b[0]);
+			adacom_device_free(ctx, b[1]);
+		}
+	} release {ctx, bitmaps};
+	idx_t bitmap_rows = 0;
+	auto run_stages = [&](adacom_column *column, idx_t seg_b, idx_t seg_e, idx_t rows, const uint64_t *validity) {
+		if (stages.size() > 1 && rows > bitmap_rows) {
+			for (auto &bm : bitmaps) {
+				adacom_device_free(ctx, bm);
+				bm = nullptr;
+				GPU_CHECK(db, adacom_device_alloc(ctx, ((rows + 63) / 64 + 2) * 8, &bm));
+			}
+			bitmap_rows = rows;
+		}
+		adacom_agg agg;
+		for (idx_t k = 0; k < stages.size(); k++) {
+			const bool last = k + 1 == stages.size();
+			GPU_CHECK(db, adacom_scan_select(column, seg_b, seg_e, 0, stages[k].preds.data(), (uint32_t)stages[k].preds.size(),
+			                                 stages[k].conj, validity, 0, k ? (const uint64_t *)bitmaps[(k - 1) & 1] : nullptr,
+			                                 last ? nullptr : (uint64_t *)bitmaps[k & 1], &agg));
+		}
+		add(agg);
+	};
+	// runs of consecutive members of one shared device column -> one chain of calls; a segment on its own (detached by
+	// an append after Uncompact, or never compacted) is scanned through its own single-segment column
 	idx_t i = 0;
 	while (i < segments.size()) {
 		ColumnSegment *s = segments[i].get();
@@ -519,11 +586,11 @@ FilterAggregateResult ColumnData::FilterAggregate(const TableFilter &filter) {
 			i++;
 			continue;
 		}
-		adacom_agg agg;
 		if (s->gpu_column && !s->owns_gpu_column) {
-			idx_t j = i + 1;
+			idx_t j = i + 1, rows = s->count;
 			while (j < segments.size() && segments[j]->gpu_column == s->gpu_column && !segments[j]->owns_gpu_column &&
 			       segments[j]->gpu_index == s->gpu_index + (j - i)) {
+				rows += segments[j]->count;
 				j++;
 			}
 			const uint64_t *validity = nullptr;
@@ -532,17 +599,13 @@ FilterAggregateResult ColumnData::FilterAggregate(const TableFilter &filter) {
 					validity = b.validity;
 				}
 			}
-			GPU_CHECK(db, adacom_scan_select(s->gpu_column, s->gpu_index, s->gpu_index + (j - i), 0, preds.data(),
-			                                 (uint32_t)preds.size(), conj, validity, 0, nullptr, nullptr, &agg));
+			run_stages(s->gpu_column, s->gpu_index, s->gpu_index + (j - i), rows, validity);
 			i = j;
 		} else {
 			s->Upload();
-			GPU_CHECK(db, adacom_scan_select(s->gpu_column, 0, 1, 0, preds.data(), (uint32_t)preds.size(), conj,
-			                                 s->staging_has_nulls ? s->staging_validity.data() : nullptr, 0, nullptr,
-			                                 nullptr, &agg));
+			run_stages(s->gpu_column, 0, 1, s->count, s->staging_has_nulls ? s->staging_validity.data() : nullptr);
 			i++;
 		}
-		add(agg);
 	}
 	return result;
 }

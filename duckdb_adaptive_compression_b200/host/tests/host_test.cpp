@@ -385,9 +385,32 @@ void RunColumnData(PhysicalType type, idx_t n, uint64_t span, int64_t base, bool
 		or_null.child_filters.push_back(unique_ptr<TableFilter>(new ConstantFilter(ExpressionType::COMPARE_EQUAL, lo)));
 		or_null.child_filters.push_back(unique_ptr<TableFilter>(new IsNullFilter()));
 		check(or_null, [&](bool v, int64_t x) { return !v || x == lo; });
-		// AND and OR levels in one filter are refused, not mis-evaluated
-		ConjunctionAndFilter mixed;
-		mixed.child_filters.push_back(unique_ptr<TableFilter>(new ConjunctionOrFilter()));
+		// x >= lo AND (x = a OR x = b OR x > hi) AND x IS NOT NULL: the OR group refines the selection of the leaves
+		{
+			const int64_t a = (int64_t)values[n / 3], b = (int64_t)values[n / 2];
+			ConjunctionAndFilter in_list;
+			in_list.child_filters.push_back(unique_ptr<TableFilter>(new ConstantFilter(ExpressionType::COMPARE_GREATERTHANOREQUALTO, lo)));
+			auto group = new ConjunctionOrFilter();
+			group->child_filters.push_back(unique_ptr<TableFilter>(new ConstantFilter(ExpressionType::COMPARE_EQUAL, a)));
+			group->child_filters.push_back(unique_ptr<TableFilter>(new ConstantFilter(ExpressionType::COMPARE_EQUAL, b)));
+			group->child_filters.push_back(unique_ptr<TableFilter>(new ConstantFilter(ExpressionType::COMPARE_GREATERTHAN, hi)));
+			in_list.child_filters.push_back(unique_ptr<TableFilter>(group));
+			in_list.child_filters.push_back(unique_ptr<TableFilter>(new IsNotNullFilter()));
+			check(in_list, [&](bool v, int64_t x) { return v && x >= lo && (x == a || x == b || x > hi); });
+			// only OR groups under the AND
+			ConjunctionAndFilter two_groups;
+			auto g1 = new ConjunctionOrFilter(), g2 = new ConjunctionOrFilter();
+			g1->child_filters.push_back(unique_ptr<TableFilter>(new ConstantFilter(ExpressionType::COMPARE_LESSTHAN, hi)));
+			g1->child_filters.push_back(unique_ptr<TableFilter>(new ConstantFilter(ExpressionType::COMPARE_EQUAL, b)));
+			g2->child_filters.push_back(unique_ptr<TableFilter>(new ConstantFilter(ExpressionType::COMPARE_GREATERTHAN, lo)));
+			g2->child_filters.push_back(unique_ptr<TableFilter>(new IsNullFilter()));
+			two_groups.child_filters.push_back(unique_ptr<TableFilter>(g1));
+			two_groups.child_filters.push_back(unique_ptr<TableFilter>(g2));
+			check(two_groups, [&](bool v, int64_t x) { return v && (x < hi || x == b) && x > lo; });
+		}
+		// an AND group under an OR (a union of selections) is refused, not mis-evaluated
+		ConjunctionOrFilter mixed;
+		mixed.child_filters.push_back(unique_ptr<TableFilter>(new ConjunctionAndFilter()));
 		bool threw = false;
 		try {
 			col.FilterAggregate(mixed);

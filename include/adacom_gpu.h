@@ -135,6 +135,10 @@ void adacom_event_destroy(adacom_ctx *ctx, void *event);
 /* pinned host memory for staging (cudaHostAlloc) */
 adacom_status adacom_host_alloc(adacom_ctx *ctx, size_t bytes, void **out);
 void adacom_host_free(adacom_ctx *ctx, void *ptr);
+/* device memory on the context's GPU for callers that do not link the CUDA runtime themselves: the selection bitmaps
+ * adacom_scan_filter / adacom_scan_select exchange (1 bit per row, 8-byte words), device-side fetch batches */
+adacom_status adacom_device_alloc(adacom_ctx *ctx, size_t bytes, void **out);
+void adacom_device_free(adacom_ctx *ctx, void *ptr);
 /* write `bytes` of zeros to a scratch buffer > L2 (benchmark hygiene: flush the 126 MB L2) */
 adacom_status adacom_flush_l2(adacom_ctx *ctx);
 

@@ -235,3 +235,26 @@ def test_scan_select_random_conjunctions(gpu_ctx, port_oracle, dtype):
         assert (got.count, got_valid) == (wcnt, wvalid), (preds, conj)
         assert got.sum % MOD == wsum % MOD, (preds, conj)
     col.close()
+
+
+def test_device_alloc_bitmap_chain(gpu_ctx, port_oracle):
+    """adacom_device_alloc / adacom_device_free: a caller without the CUDA runtime chains two selections through a
+    bitmap it got from the library (lo <= x AND (x = a OR x > hi)), same answer as one oracle pass per segment."""
+    import ctypes as C
+    dtype = np.int32
+    cases = [(13, 5000, 1000), (9, 2048, -300), (20, 4097, 7)]
+    col, vals, segs, starts, _ = _build(gpu_ctx, port_oracle, dtype, cases)
+    allv = np.concatenate(vals)
+    lo, hi, a = int(np.percentile(allv, 30)), int(np.percentile(allv, 80)), int(allv[17])
+    rows = len(allv)
+    bm = C.c_void_p()
+    gpu_ctx.check(gpu_ctx.lib.adacom_device_alloc(gpu_ctx.h, ((rows + 63) // 64 + 2) * 8, C.byref(bm)))
+    assert bm.value
+    first, _ = col.scan_select([("cmp", 5, lo)], 0, bitmap_out=bm.value)
+    got, got_valid = col.scan_select([("cmp", 0, a), ("cmp", 3, hi)], 1, bitmap_in=bm.value)
+    keep = (allv >= lo) & ((allv == a) | (allv > hi))
+    assert first.count == int((allv >= lo).sum())
+    assert got.count == got_valid == int(keep.sum())
+    assert got.sum % MOD == int(allv[keep].astype(object).sum()) % MOD
+    gpu_ctx.lib.adacom_device_free(gpu_ctx.h, bm)
+    col.close()
