@@ -126,6 +126,8 @@ struct ColumnScanState {  // src/include/duckdb/storage/table/scan_state.hpp:43-
 	idx_t internal_index = 0;
 	unique_ptr<SegmentScanState> scan_state;
 	bool initialized = false;
+	//! set by InitializeScanWithOffset: the first pull of such a scan is treated as a point read (hot-vector cache)
+	bool probe = false;
 	idx_t version = 0;
 	//! scan states of the segments a vector has just left: kept alive until the next ScanVector (zero-copy vectors)
 	std::vector<unique_ptr<SegmentScanState>> previous_states;
@@ -514,6 +516,18 @@ public:
 	void CompactMany(const std::vector<CompactableSegment *> &segments) override;
 	void UncompactMany(const std::vector<CompactableSegment *> &segments) override;
 
+	//! Hot vectors of point reads.  A scan that starts WithOffset and pulls one vector (how a point query reads a
+	//! column) or a FetchRow costs a launch and a PCIe round trip (13-37 us) where the reference reads RAM.  Skewed
+	//! point reads come back to the same vectors, so a 2048-row vector that is touched a SECOND time is decoded once
+	//! into host memory and served from there (direct-mapped, `vector_cache_bytes` per column; rows are append-only,
+	//! a partially filled tail vector is refreshed when a read goes past what it held).  Uniform random reads never
+	//! touch a vector twice and pay nothing but the look-up.  0 disables.
+	idx_t vector_cache_bytes = 32ull << 20;
+	struct VectorCacheStats {
+		idx_t hits = 0, fills = 0, misses = 0;
+	};
+	VectorCacheStats GetVectorCacheStats();
+
 	DatabaseInstance &db;
 	PhysicalType type;
 	idx_t start;
@@ -531,6 +545,23 @@ public:
 	};
 	std::vector<Batch> batches;
 	std::mutex lock;
+
+private:
+	struct CachedVector {
+		idx_t vec = ~(idx_t)0;  // absolute row / 2048
+		idx_t rows = 0;        // rows the entry holds (a tail vector may hold fewer than 2048)
+		std::vector<uint8_t> data;
+	};
+	std::vector<CachedVector> vector_cache;
+	std::vector<idx_t> vector_seen;  // vectors touched once (direct-mapped filter)
+	std::mutex vector_cache_lock;
+	VectorCacheStats vector_cache_stats;
+	//! copy `count` values from row `offset` of vector `vec` if the cache holds them; a second touch fills the entry
+	bool ReadHotVector(idx_t vec, idx_t offset, idx_t count, data_ptr_t dst);
+	//! rows [row, row + count) by ONE adacom_scan_partial when they lie inside one packed member of a shared column
+	bool ReadPackedRows(ColumnSegment *seg, idx_t row, idx_t count, data_ptr_t dst);
+
+public:
 
 private:
 	void AppendTransientSegment(idx_t start_row);

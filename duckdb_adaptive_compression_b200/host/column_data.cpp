@@ -113,6 +113,7 @@ void ColumnData::InitializeScan(ColumnScanState &state) {
 	state.row_index = state.current ? state.current->start : 0;
 	state.internal_index = state.row_index;
 	state.initialized = false;
+	state.probe = false;
 	state.version = version;
 	state.scan_state.reset();
 }
@@ -122,13 +123,113 @@ void ColumnData::InitializeScanWithOffset(ColumnScanState &state, idx_t row_idx)
 	state.row_index = row_idx;
 	state.internal_index = state.current->start;
 	state.initialized = false;
+	state.probe = true;
 	state.version = version;
 	state.scan_state.reset();
+}
+
+ColumnData::VectorCacheStats ColumnData::GetVectorCacheStats() {
+	std::lock_guard<std::mutex> guard(vector_cache_lock);
+	return vector_cache_stats;
+}
+
+bool ColumnData::ReadPackedRows(ColumnSegment *seg, idx_t row, idx_t count, data_ptr_t dst) {
+	if (!seg || !seg->gpu_column || seg->owns_gpu_column || !seg->compacted || row < seg->start ||
+	    row + count > seg->start + seg->count) {
+		return false;
+	}
+	GPU_CHECK(db, adacom_scan_partial(seg->gpu_column, seg->gpu_index, row - seg->start, count, 0, dst, 0, 0));
+	return true;
+}
+
+bool ColumnData::ReadHotVector(idx_t vec, idx_t offset, idx_t count, data_ptr_t dst) {
+	const idx_t S = GetTypeIdSize(type);
+	const idx_t n_slots = vector_cache_bytes / (STANDARD_VECTOR_SIZE * S);
+	if (n_slots == 0) {
+		return false;
+	}
+	{
+		std::lock_guard<std::mutex> guard(vector_cache_lock);
+		if (vector_cache.size() != n_slots) {
+			vector_cache.assign(n_slots, CachedVector());
+			vector_seen.assign(4 * n_slots, ~(idx_t)0);
+		}
+		CachedVector &slot = vector_cache[vec % n_slots];
+		if (slot.vec == vec && offset + count <= slot.rows) {
+			memcpy(dst, slot.data.data() + offset * S, count * S);
+			vector_cache_stats.hits++;
+			return true;
+		}
+		idx_t &seen = vector_seen[vec % vector_seen.size()];
+		if (seen != vec) {
+			seen = vec;  // first touch: the caller's ordinary path serves it
+			vector_cache_stats.misses++;
+			return false;
+		}
+	}
+	// second touch (or a tail vector that has grown): decode the whole vector once through the ordinary scan path
+	const idx_t first_row = vec * STANDARD_VECTOR_SIZE;
+	const idx_t end = start + GetMaxEntry();
+	if (first_row < start || first_row >= end) {
+		return false;
+	}
+	const idx_t rows = std::min<idx_t>(STANDARD_VECTOR_SIZE, end - first_row);
+	if (offset + count > rows) {
+		return false;
+	}
+	Vector decoded(type);
+	if (!ReadPackedRows(GetSegment(first_row), first_row, rows, decoded.buffer.data())) {
+		// the vector crosses a segment border or lives (partly) on the host: the ordinary scan path
+		ColumnScanState fill_state;
+		InitializeScanWithOffset(fill_state, first_row);
+		fill_state.probe = false;
+		if (ScanVector(fill_state, decoded, rows) != rows) {
+			return false;
+		}
+	}
+	const uint8_t *src = FlatVector::GetData(decoded);
+	memcpy(dst, src + offset * S, count * S);
+	std::lock_guard<std::mutex> guard(vector_cache_lock);
+	if (vector_cache.size() == n_slots) {
+		CachedVector &slot = vector_cache[vec % n_slots];
+		slot.vec = vec;
+		slot.rows = rows;
+		slot.data.assign(src, src + rows * S);
+		vector_cache_stats.fills++;
+	}
+	return true;
 }
 
 idx_t ColumnData::ScanVector(ColumnScanState &state, Vector &result, idx_t remaining) {
 	state.previous_states.clear();
 	result.external = nullptr;
+	if (state.probe) {
+		// the first pull of a scan WithOffset: a point read when it stays inside one aligned vector
+		state.probe = false;
+		const idx_t offset = state.row_index % STANDARD_VECTOR_SIZE;
+		const bool point_shaped = !state.initialized && state.version == version && vector_cache_bytes && remaining > 0 &&
+		                          offset + remaining <= STANDARD_VECTOR_SIZE &&
+		                          state.row_index + remaining <= start + GetMaxEntry() &&
+		                          result.buffer.size() >= remaining * GetTypeIdSize(type);
+		bool served = point_shaped &&
+		              ReadHotVector(state.row_index / STANDARD_VECTOR_SIZE, offset, remaining, result.buffer.data());
+		// first touch of a vector inside one packed segment: one decode of just these rows (one launch, one copy)
+		// instead of a scan stream that would decode the segment ahead of a reader who is not coming back
+		served = served || (point_shaped && ReadPackedRows(state.current, state.row_index, remaining, result.buffer.data()));
+		if (served) {
+			db.column_segment_catalog.AddReadAccess(state.current);  // the policy still sees the read
+			state.row_index += remaining;
+			while (state.row_index >= state.current->start + state.current->count) {
+				ColumnSegment *next = NextSegment(*this, state.current);
+				if (!next) {
+					break;
+				}
+				state.current = next;
+			}
+			state.internal_index = state.current->start;
+			return remaining;
+		}
+	}
 	if (state.version != version) {
 		InitializeScanWithOffset(state, state.row_index);
 		state.current->InitializeScan(state);
@@ -165,6 +266,11 @@ idx_t ColumnData::ScanVector(ColumnScanState &state, Vector &result, idx_t remai
 }
 
 void ColumnData::FetchRow(ColumnFetchState &state, row_t row_id, Vector &result, idx_t result_idx) {
+	if (vector_cache_bytes && row_id >= (row_t)start && (idx_t)row_id < start + GetMaxEntry() &&
+	    ReadHotVector((idx_t)row_id / STANDARD_VECTOR_SIZE, (idx_t)row_id % STANDARD_VECTOR_SIZE, 1,
+	                  FlatVector::GetData(result) + result_idx * GetTypeIdSize(type))) {
+		return;
+	}
 	auto segment = GetSegment((idx_t)row_id);
 	segment->FetchRow(state, row_id, result, result_idx);
 }

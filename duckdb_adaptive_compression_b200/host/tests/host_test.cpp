@@ -419,6 +419,63 @@ void RunColumnData(PhysicalType type, idx_t n, uint64_t span, int64_t base, bool
 		}
 		CHECK(threw);
 	}
+	// hot-vector cache: point reads (scan WithOffset + one pull, FetchRow) that come back to a vector are served from
+	// host memory after the second touch, with the same values; a tail vector that grows is refreshed
+	{
+		auto before = col.GetVectorCacheStats();
+		Vector result(type);
+		ColumnFetchState fstate2;
+		const idx_t probes[] = {0, 2048 * 3, n / 2 / 2048 * 2048, (n - 1) / 2048 * 2048};
+		for (int rep = 0; rep < 4; rep++) {
+			for (idx_t p : probes) {
+				const idx_t want = std::min<idx_t>(STANDARD_VECTOR_SIZE, n - p);
+				ColumnScanState state;
+				col.InitializeScanWithOffset(state, p);
+				CHECK(col.ScanVector(state, result, want) == want);
+				auto out = (T *)FlatVector::GetData(result);
+				for (idx_t i = 0; i < want; i++) {
+					if (p + i >= n - 3000 || valid(p + i)) {
+						CHECK(out[i] == values[p + i]);
+					}
+				}
+				// the scan continues correctly behind a vector that came from the cache
+				if (p + want < n) {
+					const idx_t more = std::min<idx_t>(STANDARD_VECTOR_SIZE, n - p - want);
+					CHECK(col.ScanVector(state, result, more) == more);
+					out = (T *)FlatVector::GetData(result);
+					for (idx_t i = 0; i < more; i++) {
+						if (p + want + i >= n - 3000 || valid(p + want + i)) {
+							CHECK(out[i] == values[p + want + i]);
+						}
+					}
+				}
+				const idx_t row = p + 17 < n ? p + 17 : p;
+				if (row >= n - 3000 || valid(row)) {
+					col.FetchRow(fstate2, (row_t)row, result, 3);
+					CHECK(((T *)FlatVector::GetData(result))[3] == values[row]);
+				}
+			}
+		}
+		auto after = col.GetVectorCacheStats();
+		CHECK(after.fills - before.fills >= 4 && after.hits - before.hits >= 8);
+		// the tail vector grows: rows behind what the entry held are read correctly
+		std::vector<T> more(700);
+		for (auto &v : more) {
+			v = (T)(base + (int64_t)(rng() % span));
+		}
+		UnifiedVectorFormat vdata;
+		vdata.data = (data_ptr_t)more.data();
+		col.AppendData(astate, vdata, more.size());
+		values.insert(values.end(), more.begin(), more.end());
+		const idx_t n_new = n + more.size();
+		for (int rep = 0; rep < 3; rep++) {
+			col.FetchRow(fstate2, (row_t)(n_new - 1), result, 0);
+			CHECK(((T *)FlatVector::GetData(result))[0] == values[n_new - 1]);
+			col.FetchRow(fstate2, (row_t)(n + 5), result, 1);
+			CHECK(((T *)FlatVector::GetData(result))[1] == values[n + 5]);
+		}
+		CHECK(col.GetMaxEntry() == n_new);
+	}
 }
 
 // Readers (full scans with zero-copy vectors, row fetches) against a policy thread that keeps moving segments between

@@ -187,8 +187,15 @@ int main(int argc, char **argv) {
 		return count / seconds(a, b);
 	};
 	bool ok_succinct = true, ok_flat = true, ok_adaptive = true;
+	// first without the hot-vector cache (every read is a launch + a PCIe round trip), then with it
+	const idx_t cache_bytes = col.vector_cache_bytes;
+	col.vector_cache_bytes = 0;
 	point_reads(col, 0, 200, &ok_succinct);  // warm-up
+	const double point_uncached = point_reads(col, 200, n_point, &ok_succinct);
+	col.vector_cache_bytes = cache_bytes;
+	point_reads(col, 0, 200, &ok_succinct);
 	const double point_succinct = point_reads(col, 200, n_point, &ok_succinct);
+	const auto cache_stats = col.GetVectorCacheStats();
 	double point_flat = 0, point_adaptive = 0, epoch_s = 0;
 	idx_t adaptive_bytes = 0, hot_segments = 0;
 	{
@@ -225,12 +232,15 @@ int main(int argc, char **argv) {
 	       "\"load_s\": %.4f, \"load_GBs\": %.2f, \"scan_threads\": %d, \"scan_s\": %.5f, \"scan_GBs\": %.2f, "
 	       "\"scan_1thread_GBs\": %.2f, \"scan_verify_GBs\": %.2f, \"zero_copy_vectors\": %llu, \"vectors\": %llu, "
 	       "\"scan_ok\": %s, \"fetch_row_per_s\": %.0f, \"fetch_rows_batched_per_s\": %.0f, \"fetch_ok\": %s, "
-	       "\"point_reads_per_s\": {\"non_adaptive_succinct\": %.0f, \"non_succinct\": %.0f, \"adaptive\": %.0f}, "
+	       "\"point_reads_per_s\": {\"non_adaptive_succinct\": %.0f, \"non_adaptive_succinct_no_cache\": %.0f, "
+	       "\"vector_cache\": {\"hits\": %llu, \"fills\": %llu, \"first_touches\": %llu}, \"non_succinct\": %.0f, \"adaptive\": %.0f}, "
 	       "\"adaptive_epoch_s\": %.4f, \"adaptive_resident_bytes\": %llu, \"adaptive_hot_segments\": %llu, \"point_ok\": %s}\n",
 	       (unsigned long long)n, bits, col.segments.size(), col.batches.size(), (unsigned long long)data_size, load_s,
 	       gb / load_s, threads, scan_s, gb / scan_s, gb / scan1_s, gb / verify_s, (unsigned long long)zero_copy,
 	       (unsigned long long)(n / STANDARD_VECTOR_SIZE), ok ? "true" : "false", n_single / seconds(f0, f1),
-	       n_batch / seconds(f2, f3), fetch_ok ? "true" : "false", point_succinct, point_flat, point_adaptive, epoch_s,
+	       n_batch / seconds(f2, f3), fetch_ok ? "true" : "false", point_succinct, point_uncached,
+	       (unsigned long long)cache_stats.hits, (unsigned long long)cache_stats.fills, (unsigned long long)cache_stats.misses,
+	       point_flat, point_adaptive, epoch_s,
 	       (unsigned long long)adaptive_bytes, (unsigned long long)hot_segments, point_ok ? "true" : "false");
 	return ok && fetch_ok && point_ok ? 0 : 1;
 }
