@@ -2420,8 +2420,14 @@ extern "C" adacom_status adacom_fetch_rows(adacom_column *col, uint64_t n, const
 			h_row[q] = row_in_seg[q];
 		}
 		const uint32_t *d_seg = (const uint32_t *)ctx->d_small;
-		LAUNCH(ctx, launch_fetch_rows(col->t, col->d_desc, col->raw, n, d_seg, d_seg + kSmallFetch, literal,
-		                              ctx->d_small + kSmallFetch * 8, ctx->stream));
+		if (n == 1) {
+			// the single-row slot: the pair travels with the launch, the device reads nothing back from the host
+			LAUNCH(ctx, launch_fetch_one(col->t, col->d_desc, col->raw, seg_idx[0], row_in_seg[0], literal,
+			                             ctx->d_small + kSmallFetch * 8, ctx->stream));
+		} else {
+			LAUNCH(ctx, launch_fetch_rows(col->t, col->d_desc, col->raw, n, d_seg, d_seg + kSmallFetch, literal,
+			                              ctx->d_small + kSmallFetch * 8, ctx->stream));
+		}
 		CK(ctx, cudaStreamSynchronize(ctx->stream));
 		memcpy(out, ctx->h_small + kSmallFetch * 8, n * col->t.size);
 		return ADACOM_OK;

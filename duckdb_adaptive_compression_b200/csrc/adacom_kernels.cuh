@@ -152,6 +152,8 @@ cudaError_t launch_scan_range(TypeInfo t, const SegDesc *desc, uint32_t seg, con
                               cudaStream_t stream);
 
 // batched fetch_row gather
+cudaError_t launch_fetch_one(TypeInfo t, const SegDesc *desc, const uint8_t *raw, uint32_t seg, uint32_t row, int literal,
+                             void *out, cudaStream_t stream);
 cudaError_t launch_fetch_rows(TypeInfo t, const SegDesc *desc, const uint8_t *raw, uint64_t n, const uint32_t *seg_idx,
                               const uint32_t *row_in_seg, int literal, void *out, cudaStream_t stream, uint32_t n_segs = 0,
                               unsigned long long *bad = nullptr);  // bad: lowest out-of-range query index (atomicMin), or NULL

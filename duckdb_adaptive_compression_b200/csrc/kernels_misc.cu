@@ -70,6 +70,15 @@ __global__ void fetch_rows_kernel(const SegDesc *desc, const uint8_t *raw, uint6
 	}
 }
 
+// ONE fetch with (segment, row) in the kernel parameters: the single-row slot of the vtable (SuccinctFetchRow) has no
+// id array for the device to read back over PCIe -- the launch carries the pair, the answer is one posted write into
+// the host-mapped page.
+template <int S>
+__global__ void fetch_one_kernel(const SegDesc *desc, const uint8_t *raw, uint32_t seg, uint32_t row, int literal, void *out) {
+	using T = typename UIntOf<S>::type;
+	*(T *)out = (T)fetch_value<S>(desc + seg, raw, (uint64_t)row, literal);
+}
+
 __device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
 	x += 0x9E3779B97F4A7C15ull;
 	x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
@@ -214,6 +223,12 @@ cudaError_t launch_fetch_rows(TypeInfo t, const SegDesc *desc, const uint8_t *ra
 	uint32_t grid = (uint32_t)(blocks > 148u * 16u ? 148u * 16u : blocks);
 	ADACOM_DISPATCH_SIZE(t.size,
 	                     (fetch_rows_kernel<S><<<grid, 256, 0, stream>>>(desc, raw, n, seg_idx, row_in_seg, literal, out, n_segs, bad)));
+	return cudaGetLastError();
+}
+
+cudaError_t launch_fetch_one(TypeInfo t, const SegDesc *desc, const uint8_t *raw, uint32_t seg, uint32_t row, int literal,
+                             void *out, cudaStream_t stream) {
+	ADACOM_DISPATCH_SIZE(t.size, (fetch_one_kernel<S><<<1, 1, 0, stream>>>(desc, raw, seg, row, literal, out)));
 	return cudaGetLastError();
 }
 
