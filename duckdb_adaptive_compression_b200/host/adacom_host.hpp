@@ -128,6 +128,8 @@ struct ColumnScanState {  // src/include/duckdb/storage/table/scan_state.hpp:43-
 	bool initialized = false;
 	//! set by InitializeScanWithOffset: the first pull of such a scan is treated as a point read (hot-vector cache)
 	bool probe = false;
+	//! the previous pull was served as a point read (a scan that pulls again tells the column it was not one)
+	bool was_point_read = false;
 	idx_t version = 0;
 	//! scan states of the segments a vector has just left: kept alive until the next ScanVector (zero-copy vectors)
 	std::vector<unique_ptr<SegmentScanState>> previous_states;
@@ -525,6 +527,7 @@ public:
 	idx_t vector_cache_bytes = 32ull << 20;
 	struct VectorCacheStats {
 		idx_t hits = 0, fills = 0, misses = 0;
+		idx_t lean_reads = 0;  // first touches served by one adacom_scan_partial
 	};
 	VectorCacheStats GetVectorCacheStats();
 
@@ -556,6 +559,10 @@ private:
 	std::vector<idx_t> vector_seen;  // vectors touched once (direct-mapped filter)
 	std::mutex vector_cache_lock;
 	VectorCacheStats vector_cache_stats;
+	//! scans that began WithOffset and were served as a point read / of those, the ones that pulled again: a parallel
+	//! table scan starts every row group WithOffset and always pulls again, so the one-launch first touch (which a
+	//! continuing scan pays on top of its stream) is only used while most such scans stop after one vector
+	std::atomic<uint32_t> point_reads_started {0}, point_reads_continued {0};
 	//! copy `count` values from row `offset` of vector `vec` if the cache holds them; a second touch fills the entry
 	bool ReadHotVector(idx_t vec, idx_t offset, idx_t count, data_ptr_t dst);
 	//! rows [row, row + count) by ONE adacom_scan_partial when they lie inside one packed member of a shared column

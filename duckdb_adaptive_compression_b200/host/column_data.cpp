@@ -114,6 +114,7 @@ void ColumnData::InitializeScan(ColumnScanState &state) {
 	state.internal_index = state.row_index;
 	state.initialized = false;
 	state.probe = false;
+	state.was_point_read = false;
 	state.version = version;
 	state.scan_state.reset();
 }
@@ -124,6 +125,7 @@ void ColumnData::InitializeScanWithOffset(ColumnScanState &state, idx_t row_idx)
 	state.internal_index = state.current->start;
 	state.initialized = false;
 	state.probe = true;
+	state.was_point_read = false;
 	state.version = version;
 	state.scan_state.reset();
 }
@@ -203,6 +205,10 @@ bool ColumnData::ReadHotVector(idx_t vec, idx_t offset, idx_t count, data_ptr_t 
 idx_t ColumnData::ScanVector(ColumnScanState &state, Vector &result, idx_t remaining) {
 	state.previous_states.clear();
 	result.external = nullptr;
+	if (state.was_point_read) {
+		state.was_point_read = false;
+		point_reads_continued.fetch_add(1, std::memory_order_relaxed);  // it was the start of a longer scan
+	}
 	if (state.probe) {
 		// the first pull of a scan WithOffset: a point read when it stays inside one aligned vector
 		state.probe = false;
@@ -215,7 +221,23 @@ idx_t ColumnData::ScanVector(ColumnScanState &state, Vector &result, idx_t remai
 		              ReadHotVector(state.row_index / STANDARD_VECTOR_SIZE, offset, remaining, result.buffer.data());
 		// first touch of a vector inside one packed segment: one decode of just these rows (one launch, one copy)
 		// instead of a scan stream that would decode the segment ahead of a reader who is not coming back
-		served = served || (point_shaped && ReadPackedRows(state.current, state.row_index, remaining, result.buffer.data()));
+		if (point_shaped && !served) {
+			const uint32_t started = point_reads_started.load(std::memory_order_relaxed);
+			const uint32_t continued = point_reads_continued.load(std::memory_order_relaxed);
+			if (2 * continued <= started && ReadPackedRows(state.current, state.row_index, remaining, result.buffer.data())) {
+				served = true;
+				std::lock_guard<std::mutex> guard(vector_cache_lock);
+				vector_cache_stats.lean_reads++;
+			}
+		}
+		if (point_shaped) {
+			// history of the scans that start WithOffset (halved now and then so that the column follows its workload)
+			if (point_reads_started.fetch_add(1, std::memory_order_relaxed) >= 256) {
+				point_reads_started.store(128, std::memory_order_relaxed);
+				point_reads_continued.store(point_reads_continued.load(std::memory_order_relaxed) / 2, std::memory_order_relaxed);
+			}
+			state.was_point_read = true;
+		}
 		if (served) {
 			db.column_segment_catalog.AddReadAccess(state.current);  // the policy still sees the read
 			state.row_index += remaining;

@@ -458,6 +458,27 @@ void RunColumnData(PhysicalType type, idx_t n, uint64_t span, int64_t base, bool
 		}
 		auto after = col.GetVectorCacheStats();
 		CHECK(after.fills - before.fills >= 4 && after.hits - before.hits >= 8);
+		// scans that start WithOffset and keep pulling (a parallel table scan starts every row group like that): the
+		// column learns that they are not point reads and stops paying the one-launch first touch for them
+		{
+			auto s0 = col.GetVectorCacheStats();
+			const idx_t n_vec = n / STANDARD_VECTOR_SIZE;
+			for (int k = 0; k < 60 && n_vec > 8; k++) {
+				const idx_t p = ((idx_t)(k * 37 + 5) % (n_vec - 4)) * STANDARD_VECTOR_SIZE;
+				ColumnScanState state;
+				col.InitializeScanWithOffset(state, p);
+				for (int pull = 0; pull < 3; pull++) {
+					CHECK(col.ScanVector(state, result, STANDARD_VECTOR_SIZE) == STANDARD_VECTOR_SIZE);
+					auto out = (T *)FlatVector::GetData(result);
+					const idx_t row = p + pull * STANDARD_VECTOR_SIZE + 11;
+					if (row >= n - 3000 || valid(row)) {
+						CHECK(out[11] == values[row]);
+					}
+				}
+			}
+			auto s1 = col.GetVectorCacheStats();
+			CHECK(n_vec <= 8 || s1.lean_reads - s0.lean_reads <= 16);
+		}
 		// the tail vector grows: rows behind what the entry held are read correctly
 		std::vector<T> more(700);
 		for (auto &v : more) {
