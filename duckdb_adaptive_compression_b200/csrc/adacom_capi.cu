@@ -1398,193 +1398,6 @@ static adacom_status filter_words_serves(adacom_column *col, uint64_t b, uint64_
 	return ADACOM_OK;
 }
 
-// Value ranges in KEY space: key(x) = x with the sign bit flipped for signed types, so unsigned order on keys is the
-// type's order on 64-bit extended values (the constants of a comparison are taken as 64-bit, like cmp_passes does).
-struct KeyRange {
-	uint64_t lo = 0, hi = ~0ull;
-	bool empty = false;
-	bool holds(uint64_t k) const {
-		return !empty && k >= lo && k <= hi;
-	}
-};
-
-static KeyRange key_range_for(uint32_t op_mask, uint64_t k) {
-	KeyRange r;
-	switch (op_mask & 7u) {
-	case 1: r.empty = k == 0; r.hi = k - 1; break;        // <
-	case 3: r.hi = k; break;                              // <=
-	case 4: r.empty = k == ~0ull; r.lo = k + 1; break;    // >
-	case 6: r.lo = k; break;                              // >=
-	case 2: r.lo = r.hi = k; break;                       // =
-	default: break;                                       // (<> is handled by the callers: complement of [k, k])
-	}
-	return r;
-}
-
-static FilterRange filter_range_from(const KeyRange &r, bool complement, bool is_signed) {
-	const uint64_t flip = is_signed ? (1ull << 63) : 0ull;
-	FilterRange f;
-	f.lo = r.lo ^ flip;
-	f.hi = r.hi ^ flip;
-	f.empty = r.empty ? 1u : 0u;
-	f.complement = complement ? 1u : 0u;
-	return f;
-}
-
-static FilterRange filter_range_for_cmp(uint32_t op_mask, uint64_t constant, bool is_signed) {
-	const uint64_t k = constant ^ (is_signed ? (1ull << 63) : 0ull);
-	if ((op_mask & 7u) == 5u) {
-		KeyRange r;
-		r.lo = r.hi = k;
-		return filter_range_from(r, true, is_signed);
-	}
-	return filter_range_from(key_range_for(op_mask, k), false, is_signed);
-}
-
-// The conjunction of a FilterSelection as ONE value range (or the complement of one) + "NULL rows never pass".
-// Returns false when the conjunction has no such form (IS NULL children, two separate ranges ...): select_kernel's job.
-static bool canonical_filter_range(const SelectArgs &a, bool is_signed, FilterRange *out) {
-	const uint64_t flip = is_signed ? (1ull << 63) : 0ull;
-	KeyRange acc;
-	uint64_t ne[ADACOM_MAX_PREDS];
-	uint32_t n_ne = 0;
-	if (!a.conj_or) {
-		for (uint32_t p = 0; p < a.n_preds; p++) {
-			const SelectPred &pr = a.preds[p];
-			if (pr.kind == 1) {
-				return false;  // IS NULL
-			}
-			if (pr.kind != 0) {
-				continue;  // IS NOT NULL: the validity mask already says so
-			}
-			const uint64_t k = pr.constant ^ flip;
-			if ((pr.op_mask & 7u) == 5u) {
-				ne[n_ne++] = k;
-				continue;
-			}
-			const KeyRange r = key_range_for(pr.op_mask, k);
-			acc.empty = acc.empty || r.empty;
-			acc.lo = r.lo > acc.lo ? r.lo : acc.lo;
-			acc.hi = r.hi < acc.hi ? r.hi : acc.hi;
-			acc.empty = acc.empty || acc.lo > acc.hi;
-		}
-		// <> children: outside the range they say nothing, at an end they shorten it, inside they split it
-		bool changed = true;
-		while (changed && !acc.empty) {
-			changed = false;
-			for (uint32_t i = 0; i < n_ne && !acc.empty; i++) {
-				if (!acc.holds(ne[i])) {
-					continue;
-				}
-				if (acc.lo == acc.hi) {
-					acc.empty = true;
-				} else if (ne[i] == acc.lo) {
-					acc.lo++;
-					changed = true;
-				} else if (ne[i] == acc.hi) {
-					acc.hi--;
-					changed = true;
-				}
-			}
-		}
-		uint32_t inside = 0;
-		uint64_t hole = 0;
-		for (uint32_t i = 0; i < n_ne; i++) {
-			if (acc.holds(ne[i]) && !(inside && ne[i] == hole)) {
-				inside++;
-				hole = ne[i];
-			}
-		}
-		if (inside == 0) {
-			*out = filter_range_from(acc, false, is_signed);
-			return true;
-		}
-		if (inside == 1 && acc.lo == 0 && acc.hi == ~0ull) {
-			KeyRange r;
-			r.lo = r.hi = hole;
-			*out = filter_range_from(r, true, is_signed);
-			return true;
-		}
-		return false;
-	}
-	// OR: zero children pass everything (like select_kernel); IS NOT NULL passes every valid row
-	if (a.n_preds == 0) {
-		*out = filter_range_from(acc, false, is_signed);
-		return true;
-	}
-	KeyRange rs[ADACOM_MAX_PREDS];
-	uint32_t n_r = 0;
-	for (uint32_t p = 0; p < a.n_preds; p++) {
-		const SelectPred &pr = a.preds[p];
-		if (pr.kind == 1) {
-			return false;
-		}
-		if (pr.kind != 0) {
-			*out = filter_range_from(KeyRange(), false, is_signed);
-			return true;
-		}
-		const uint64_t k = pr.constant ^ flip;
-		if ((pr.op_mask & 7u) == 5u) {
-			ne[n_ne++] = k;
-			continue;
-		}
-		const KeyRange r = key_range_for(pr.op_mask, k);
-		if (!r.empty) {
-			rs[n_r++] = r;
-		}
-	}
-	if (n_ne) {
-		// (x <> c) OR X: everything when X holds c (or another <> does), else x <> c
-		bool all = false;
-		for (uint32_t i = 1; i < n_ne; i++) {
-			all = all || ne[i] != ne[0];
-		}
-		for (uint32_t i = 0; i < n_r; i++) {
-			all = all || rs[i].holds(ne[0]);
-		}
-		KeyRange r;
-		if (!all) {
-			r.lo = r.hi = ne[0];
-		}
-		*out = filter_range_from(r, !all, is_signed);
-		return true;
-	}
-	if (n_r == 0) {
-		acc.empty = true;
-		*out = filter_range_from(acc, false, is_signed);
-		return true;
-	}
-	// merge the ranges in order of their lower ends
-	for (uint32_t i = 1; i < n_r; i++) {
-		for (uint32_t j = i; j > 0 && rs[j].lo < rs[j - 1].lo; j--) {
-			const KeyRange t = rs[j];
-			rs[j] = rs[j - 1];
-			rs[j - 1] = t;
-		}
-	}
-	KeyRange merged[ADACOM_MAX_PREDS];
-	uint32_t n_m = 0;
-	for (uint32_t i = 0; i < n_r; i++) {
-		if (n_m && (merged[n_m - 1].hi == ~0ull || rs[i].lo <= merged[n_m - 1].hi + 1)) {
-			merged[n_m - 1].hi = rs[i].hi > merged[n_m - 1].hi ? rs[i].hi : merged[n_m - 1].hi;
-		} else {
-			merged[n_m++] = rs[i];
-		}
-	}
-	if (n_m == 1) {
-		*out = filter_range_from(merged[0], false, is_signed);
-		return true;
-	}
-	if (n_m == 2 && merged[0].lo == 0 && merged[1].hi == ~0ull) {
-		KeyRange gap;
-		gap.lo = merged[0].hi + 1;
-		gap.hi = merged[1].lo - 1;
-		*out = filter_range_from(gap, true, is_signed);
-		return true;
-	}
-	return false;
-}
-
 static adacom_status run_agg(adacom_column *col, uint64_t b, uint64_t e, int flags, DecodeMode mode, uint32_t op_mask,
                              uint64_t constant, uint32_t *bitmap32, Agg *device_out) {
 	adacom_ctx *ctx = col->ctx;
@@ -1774,7 +1587,7 @@ extern "C" adacom_status adacom_scan_select(adacom_column *col, uint64_t seg_beg
 		// row, NULL or not: only the SUM skips NULLs, so that form takes the fast kernel when no selection is exchanged
 		// (count = rows of the range).  Everything else (IS NULL, two separate ranges) decodes per value.
 		FilterRange fr;
-		bool fast = !getenv("ADACOM_SELECT_LEGACY") && canonical_filter_range(a, col->t.is_signed, &fr) &&
+		bool fast = !getenv("ADACOM_SELECT_LEGACY") && canonical_filter_range(a.preds, a.n_preds, a.conj_or != 0, col->t.is_signed, &fr) &&
 		            (n_preds != 0 || (!device_bitmap_in && !device_bitmap_out));
 		if (fast) {
 			adacom_status st = filter_words_serves(col, seg_begin, seg_end, &fast);

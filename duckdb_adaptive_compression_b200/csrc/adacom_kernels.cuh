@@ -3,6 +3,7 @@
 #pragma once
 
 #include "adacom_device.cuh"
+#include "filter_range.hpp"
 
 #include <string>
 
@@ -212,12 +213,7 @@ cudaError_t launch_filter_fields(TypeInfo t, const SegDesc *desc, uint32_t seg_b
 
 // ---- general single-column table filter (kernels_select.cu): conjunction of comparisons / IS [NOT] NULL, validity
 // mask, selection bitmap in / out; per-value decode, any width
-constexpr uint32_t kSelectMaxPreds = 8;
-struct SelectPred {
-	uint32_t kind;       // 0 comparison, 1 IS NULL, 2 IS NOT NULL
-	uint32_t op_mask;    // cmp_mask_for_op
-	uint64_t constant;   // sign/zero-extended T value
-};
+// (FilterRange, SelectPred, kSelectMaxPreds: filter_range.hpp)
 struct SelectArgs {
 	const SegDesc *desc = nullptr;
 	const Job *jobs = nullptr;             // 2048-value tiles of the segment range (static tile table)
@@ -277,14 +273,6 @@ cudaError_t launch_codec_fetch(TypeInfo t, int codec, const CodecArgs &args, con
 cudaError_t launch_rle_run_starts(const CodecArgs &args, uint32_t seg_b, uint32_t n_segs, int sm_count, cudaStream_t stream);
 // fills groups_out[j] for the jobs of args (after launch_rle_run_starts for RLE)
 cudaError_t launch_codec_groups(TypeInfo t, int codec, const CodecArgs &args, CodecGroup *groups_out, cudaStream_t stream);
-
-// A single-column table filter in canonical form: the decoded value (sign- or zero-extended T) lies in [lo, hi] (compared
-// as T: signed or unsigned), or outside it (complement).  Every comparison of TemplatedFilterSelection, a BETWEEN (AND of
-// two) and an OR of two half-lines fit; `empty`: the range holds no value at all.
-struct FilterRange {
-	uint64_t lo = 0, hi = 0;
-	uint32_t empty = 0, complement = 0;
-};
 
 // the same operator, warp per 2048-value tile (static tile table), lane per 32-row group (pred32); handles every kind of
 // segment (field-comparable ones in the field domain, the others per value); wmax: widest live payload of the column
