@@ -26,6 +26,50 @@ struct SelectPred {
 	uint64_t constant;   // sign/zero-extended T value
 };
 
+#ifdef __CUDACC__
+#define ADACOM_FR_HD __host__ __device__ __forceinline__
+#else
+#define ADACOM_FR_HD inline
+#endif
+
+// The canonical range against ONE segment whose decoded values are extend(min) + field, field in [0, mask] without
+// wrap-around (a "linear" segment: [emin, etop] is an interval of T).  The range is clipped to the interval and moved to
+// the FIELD domain: a row passes iff kind == 1 and (field - flo) <= span, or kind == 2 and not (field - flo) <= span;
+// kind == 0: no row of the segment passes (zone map).  Used by filter_words_kernel per segment, and by the CPU test.
+struct FieldRange {
+	uint64_t flo, span;
+	int kind;
+};
+template <bool SIGNED>
+ADACOM_FR_HD bool filter_value_less(uint64_t a, uint64_t b) {
+	return SIGNED ? (int64_t)a < (int64_t)b : a < b;
+}
+template <bool SIGNED>
+ADACOM_FR_HD FieldRange clip_range_to_segment(const FilterRange &fr, uint64_t emin, uint64_t etop, uint64_t mask64) {
+	bool none = fr.empty != 0u;
+	uint64_t l = fr.lo, h = fr.hi;
+	if (!none) {
+		if (filter_value_less<SIGNED>(h, emin) || filter_value_less<SIGNED>(etop, l)) {
+			none = true;  // the segment's interval and the range do not meet (zone map)
+		} else {
+			l = filter_value_less<SIGNED>(l, emin) ? emin : l;
+			h = filter_value_less<SIGNED>(etop, h) ? etop : h;
+		}
+	}
+	FieldRange r;
+	r.flo = 0;
+	r.span = mask64;
+	if (none) {
+		r.kind = fr.complement ? 1 : 0;  // complement of nothing: every row of the segment
+	} else {
+		r.flo = l - emin;
+		r.span = h - l;
+		const bool whole = r.flo == 0 && r.span == mask64;
+		r.kind = !fr.complement ? 1 : (whole ? 0 : 2);
+	}
+	return r;
+}
+
 // Value ranges in KEY space: key(x) = x with the sign bit flipped for signed types, so unsigned order on keys is the
 // type's order on 64-bit extended values (the constants of a comparison are taken as 64-bit, like cmp_passes does).
 struct KeyRange {

@@ -299,26 +299,10 @@ __global__ void __launch_bounds__(kFWarps * 32, 3) filter_words_kernel(const Seg
 				c_kind = 3;
 				if (linear) {
 					// the value range [lo, hi] (or its complement) clipped to the segment's interval, in the field domain
-					bool none = fr.empty != 0u;
-					uint64_t l = fr.lo, h = fr.hi;
-					if (!none) {
-						if (t_less<SIGNED>(h, c_emin) || t_less<SIGNED>(e_top, l)) {
-							none = true;  // the segment's interval and the range do not meet (zone map)
-						} else {
-							l = t_less<SIGNED>(l, c_emin) ? c_emin : l;
-							h = t_less<SIGNED>(e_top, h) ? e_top : h;
-						}
-					}
-					c_flo64 = 0;
-					c_span64 = mask64;
-					if (none) {
-						c_kind = fr.complement ? 1 : 0;  // complement of nothing: every row of the segment
-					} else {
-						c_flo64 = l - c_emin;
-						c_span64 = h - l;
-						const bool whole = c_flo64 == 0 && c_span64 == mask64;
-						c_kind = !fr.complement ? 1 : (whole ? 0 : 2);
-					}
+					const FieldRange r = clip_range_to_segment<SIGNED>(fr, c_emin, e_top, mask64);
+					c_flo64 = r.flo;
+					c_span64 = r.span;
+					c_kind = r.kind;
 					c_flo = (uint32_t)c_flo64;
 					c_span = (uint32_t)c_span64;
 				}

@@ -3,7 +3,9 @@
 // range, IS NOT NULL) under AND and OR, for a signed and an unsigned 8-bit type: whenever the function says "one range",
 // that range (or its complement) must select exactly the values TemplatedFilterSelection would
 // (src/storage/table/column_segment.cpp:575-586: `mask.RowIsValid(idx) && OP(vec[idx], constant)`); IS NULL children
-// must be refused; the shapes the fast kernel is meant for must be accepted.  Plain C++: g++ -std=c++17, no GPU.
+// must be refused; the shapes the fast kernel is meant for must be accepted.  Every accepted range of up to two children
+// is then clipped to every linear 8-bit segment the way filter_words_kernel does it (clip_range_to_segment) and the
+// field-domain test is compared with the value test on every field.  Plain C++: g++ -std=c++17, no GPU.
 #include "../filter_range.hpp"
 
 #include <cstdio>
@@ -20,6 +22,39 @@ static bool cmp_passes(bool is_signed, uint64_t v, uint64_t c, uint32_t op_mask)
 	const bool lt = t_less(is_signed, v, c);
 	const uint32_t sel = lt ? 0u : (v == c ? 1u : 2u);
 	return (op_mask >> sel) & 1u;
+}
+
+// clip_range_to_segment (what filter_words_kernel runs per segment): every linear 8-bit segment -- extend(min) + field,
+// field < 2^w, the interval inside the type -- and every field of it: the field-domain test must agree with the value test
+static unsigned long long clipped = 0;
+static unsigned long long check_segments(bool is_signed, const FilterRange &fr) {
+	unsigned long long n_checked = 0;
+	const int lo = is_signed ? -128 : 0, hi = is_signed ? 127 : 255;
+	for (int mn = lo; mn <= hi; mn += 3) {
+		for (int w = 1; w <= 8; w++) {
+			const int mask = (1 << w) - 1;
+			if (mn + mask > hi) {
+				break;
+			}
+			const uint64_t emin = (uint64_t)(int64_t)mn, etop = (uint64_t)(int64_t)(mn + mask);
+			const FieldRange r = is_signed ? clip_range_to_segment<true>(fr, emin, etop, (uint64_t)mask)
+			                               : clip_range_to_segment<false>(fr, emin, etop, (uint64_t)mask);
+			for (int f = 0; f <= mask; f++) {
+				const uint64_t v = (uint64_t)(int64_t)(mn + f);
+				const bool inr = !fr.empty && !t_less(is_signed, v, fr.lo) && !t_less(is_signed, fr.hi, v);
+				const bool want = inr != (fr.complement != 0u);
+				const bool in_field = ((uint64_t)f - r.flo) <= r.span;
+				const bool got = r.kind == 0 ? false : (in_field != (r.kind == 2));
+				if (got != want || r.kind < 0 || r.kind > 2) {
+					printf("CLIP MISMATCH signed=%d min=%d w=%d f=%d want=%d got=%d kind=%d flo=%llu span=%llu\n", (int)is_signed, mn,
+					       w, f, want, got, r.kind, (unsigned long long)r.flo, (unsigned long long)r.span);
+					exit(1);
+				}
+				n_checked++;
+			}
+		}
+	}
+	return n_checked;
 }
 
 int main() {
@@ -59,6 +94,9 @@ int main() {
 						continue;
 					}
 					accepted++;
+					if (n <= 2) {
+						clipped += check_segments(is_signed != 0, fr);
+					}
 					for (int i = 0; i < 256; i++) {
 						const uint64_t v = domain[i];
 						bool any = false, all = true;
@@ -104,6 +142,6 @@ int main() {
 			}
 		}
 	}
-	printf("FILTER_RANGE_OK checked=%llu accepted=%llu refused=%llu\n", checked, accepted, refused);
+	printf("FILTER_RANGE_OK checked=%llu accepted=%llu refused=%llu clipped=%llu\n", checked, accepted, refused, clipped);
 	return accepted > refused / 4 ? 0 : 1;
 }

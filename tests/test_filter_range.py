@@ -1,7 +1,9 @@
 """CPU check of the host-side filter canonicalisation (csrc/filter_range.hpp): the conjunction of a FilterSelection as ONE
 value range or its complement.  csrc/tests/filter_range_test.cpp enumerates every conjunction of up to three children
 (6 comparisons x 12 constants, IS NOT NULL) under AND / OR for a signed and an unsigned 8-bit type -- 1.6 million
-conjunctions -- and compares the range with TemplatedFilterSelection's row-by-row answer on all 256 values."""
+conjunctions -- and compares the range with TemplatedFilterSelection's row-by-row answer on all 256 values; every accepted
+range of up to two children is then clipped to every linear 8-bit segment by clip_range_to_segment (the function
+filter_words_kernel runs per segment, same header) and the field-domain test is compared with the value test."""
 import os
 import subprocess
 
@@ -17,3 +19,4 @@ def test_canonical_filter_range_exhaustive(tmp_path):
     assert "FILTER_RANGE_OK" in out, out
     fields = dict(kv.split("=") for kv in out.split()[1:])
     assert int(fields["checked"]) > 1_500_000 and int(fields["accepted"]) > int(fields["refused"])
+    assert int(fields["clipped"]) > 200_000_000
