@@ -16,6 +16,7 @@
 //
 // Algorithmic HBM bytes per unit: flat = P_tile read + cnt*S written; SUM / filter = P_chunk read.
 #include "adacom_kernels.cuh"
+#include "swar8.hpp"
 
 namespace adacom {
 
@@ -390,12 +391,10 @@ __global__ void __launch_bounds__(kThreads, StageCfg<S, MODE>::kMinCtas) decode_
 						uint32_t x0 = __funnelshift_r(r0, r1, sh), x1 = __funnelshift_r(r1, r2, sh);
 						if (spread) {
 							const uint32_t q0 = x0 & m4, q1 = __funnelshift_r(x0, x1, 4u * w) & m4;
-							const uint32_t p0 = (q0 & m2) | ((q0 >> (2u * w)) << 16), p1 = (q1 & m2) | ((q1 >> (2u * w)) << 16);
-							x0 = (p0 & fm_even) | ((p0 << (8u - w)) & fm_odd);
-							x1 = (p1 & fm_even) | ((p1 << (8u - w)) & fm_odd);
+							x0 = swar8_spread(q0, w, m2, fm_even, fm_odd);
+							x1 = swar8_spread(q1, w, m2, fm_even, fm_odd);
 						}
-						const uint32_t y0 = ((x0 & 0x7f7f7f7fu) + add7) ^ ((x0 & 0x80808080u) ^ add80);
-						const uint32_t y1 = ((x1 & 0x7f7f7f7fu) + add7) ^ ((x1 & 0x80808080u) ^ add80);
+						const uint32_t y0 = swar8_add(x0, add7, add80), y1 = swar8_add(x1, add7, add80);
 						dst[j * kGroupThreads] = (uint64_t)y0 | ((uint64_t)y1 << 32);
 					}
 				} else

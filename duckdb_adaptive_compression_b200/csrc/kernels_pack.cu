@@ -24,6 +24,7 @@
 //
 // Algorithmic HBM bytes per tile: cnt*S read + 8*ceil(cnt*w/64) written; nothing is re-read.
 #include "adacom_kernels.cuh"
+#include "swar8.hpp"
 
 namespace adacom {
 
@@ -313,18 +314,14 @@ __global__ void __launch_bounds__(kStagedThreads, StagedSmem<S>::kMinCtas) pack_
 			uint32_t x0 = __funnelshift_r(r0, r1, sh), x1 = __funnelshift_r(r1, r2, sh);
 			const uint32_t w = t.w;
 			const uint32_t sub7 = ((uint32_t)t.sub & 0x7fu) * 0x01010101u, fmask = ((1u << w) - 1u) * 0x01010101u;
-			x0 = ((x0 | 0x80808080u) - sub7) & fmask;
-			x1 = ((x1 | 0x80808080u) - sub7) & fmask;
+			x0 = swar8_fields(x0, sub7, fmask);
+			x1 = swar8_fields(x1, sub7, fmask);
 			if (t.cnt != kVectorSize) {  // slots behind the segment's last value: zero fields
 				const int v = (int)t.cnt - (int)(8u * tid);
 				x0 &= v >= 4 ? 0xffffffffu : (v <= 0 ? 0u : (1u << (8 * v)) - 1u);
 				x1 &= v >= 8 ? 0xffffffffu : (v <= 4 ? 0u : (1u << (8 * (v - 4))) - 1u);
 			}
-			const uint32_t p0 = (x0 & 0x00ff00ffu) | ((x0 & 0xff00ff00u) >> (8u - w));
-			const uint32_t p1 = (x1 & 0x00ff00ffu) | ((x1 & 0xff00ff00u) >> (8u - w));
-			const uint32_t q0 = (p0 & 0xffffu) | ((p0 >> 16) << (2u * w));
-			const uint32_t q1 = (p1 & 0xffffu) | ((p1 >> 16) << (2u * w));
-			const uint64_t c = (uint64_t)q0 | ((uint64_t)q1 << (4u * w));
+			const uint64_t c = (uint64_t)swar8_squeeze(x0, w) | ((uint64_t)swar8_squeeze(x1, w) << (4u * w));
 			uint8_t *image = (uint8_t *)fld + (it & 1u) * (kVectorSize * 7u / 8u);
 			uint8_t *o = image + tid * w;
 #pragma unroll

@@ -20,3 +20,14 @@ def test_canonical_filter_range_exhaustive(tmp_path):
     fields = dict(kv.split("=") for kv in out.split()[1:])
     assert int(fields["checked"]) > 1_500_000 and int(fields["accepted"]) > int(fields["refused"])
     assert int(fields["clipped"]) > 200_000_000
+
+
+def test_swar8_byte_packing_exhaustive(tmp_path):
+    """csrc/swar8.hpp (the word-parallel pack / unpack of one-byte slots inside pack_staged_kernel<1> and
+    decode_kernel<1>) against the scalar definition of the codec: every width, every frame of reference, every slot value
+    in every byte lane."""
+    exe = str(tmp_path / "swar8_test")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-Wall", "-Werror", "-o", exe,
+                           os.path.join(CSRC, "tests", "swar8_test.cpp")])
+    out = subprocess.check_output([exe], text=True, timeout=120)
+    assert "SWAR8_OK" in out, out
