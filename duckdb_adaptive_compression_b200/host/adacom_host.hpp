@@ -470,6 +470,11 @@ public:
 	ConjunctionAndFilter() : ConjunctionFilter(TableFilterType::CONJUNCTION_AND) {
 	}
 };
+//! One adacom_scan_select of a pushed filter: the children of one conjunction level (ColumnData::BuildFilterStages)
+struct FilterStage {
+	std::vector<adacom_pred> preds;
+	adacom_conj conj = ADACOM_CONJ_AND;
+};
 //! What DuckDB computes above a filtered scan of one column: approved_tuple_count of FilterSelection
 //! (column_segment.cpp:685-844) and COUNT(col) / SUM(col) over the approved rows (NULL rows do not enter them)
 struct FilterAggregateResult {
@@ -508,6 +513,8 @@ public:
 	//! include OR groups of leaves (IN lists): one call per group, chained through device selection bitmaps like the
 	//! recursion of FilterSelection.  An AND group under an OR (a union of selections) throws.
 	FilterAggregateResult FilterAggregate(const TableFilter &filter);
+	//! the chain of calls FilterAggregate makes for `filter` (host logic only: no GPU is touched)
+	static std::vector<FilterStage> BuildFilterStages(const TableFilter &filter);
 
 	//! move every sealed (full or finalized) segment that is still host-staged into the shared device column and
 	//! compact them with one analyze + one encode; called by the append path every `pending_limit` segments, by

@@ -618,15 +618,7 @@ static void FlattenFilter(const TableFilter &filter, TableFilterType level, std:
 	}
 }
 
-namespace {
-// One adacom_scan_select: the children of one conjunction level
-struct FilterStage {
-	std::vector<adacom_pred> preds;
-	adacom_conj conj = ADACOM_CONJ_AND;
-};
-}  // namespace
-
-FilterAggregateResult ColumnData::FilterAggregate(const TableFilter &filter) {
+std::vector<FilterStage> ColumnData::BuildFilterStages(const TableFilter &filter) {
 	// The filter becomes a chain of stages, each one call that refines the selection of the one before (the recursion
 	// of FilterSelection, column_segment.cpp:688-723): the leaves of the top level, then -- under an AND -- every OR
 	// group of leaves (what an IN list or a pushed OR looks like).  An AND group under an OR would need the union of two
@@ -664,6 +656,11 @@ FilterAggregateResult ColumnData::FilterAggregate(const TableFilter &filter) {
 			throw InternalException("ColumnData::FilterAggregate: more than ADACOM_MAX_PREDS children in one conjunction");
 		}
 	}
+	return stages;
+}
+
+FilterAggregateResult ColumnData::FilterAggregate(const TableFilter &filter) {
+	const std::vector<FilterStage> stages = BuildFilterStages(filter);
 	// sealed segments that still wait on the host join a shared device column first (what the first scan does)
 	CompactPending(true);
 	FilterAggregateResult result;

@@ -20,6 +20,14 @@ def test_policy_decision_rule_cpu():
     assert "POLICY_TESTS_OK" in out
 
 
+def test_filter_pushdown_stages_cpu():
+    """host logic of ColumnData::FilterAggregate (how a pushed TableFilter becomes the chain of adacom_scan_select calls),
+    no GPU touched"""
+    _build()
+    out = subprocess.check_output([os.path.join(HOST, "build", "filter_stage_test")], text=True, timeout=60)
+    assert "FILTER_STAGE_TESTS_OK" in out
+
+
 def test_shim_exports_reference_surface():
     _build()
     out = subprocess.check_output(["nm", "-DC", "--defined-only", os.path.join(HOST, "libadacom_host.so")], text=True)
@@ -36,7 +44,7 @@ def test_shim_exports_reference_surface():
                 "adacom_host::ColumnData::InitializeScanWithOffset", "adacom_host::ColumnData::FetchRow",
                 "adacom_host::ColumnData::FetchRows", "adacom_host::ColumnData::CompactPending",
                 "adacom_host::ColumnData::CompactMany", "adacom_host::ColumnData::UncompactMany",
-                "adacom_host::ColumnData::FilterAggregate"]:
+                "adacom_host::ColumnData::FilterAggregate", "adacom_host::ColumnData::BuildFilterStages"]:
         assert sym in out, sym
 
 
