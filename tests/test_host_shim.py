@@ -28,6 +28,14 @@ def test_filter_pushdown_stages_cpu():
     assert "FILTER_STAGE_TESTS_OK" in out
 
 
+def test_hot_vector_cache_cpu():
+    """ColumnData's hot-vector cache on host-resident (adaptive, never uploaded) segments: second-touch fill, hits, scans
+    that continue behind a cached vector and across segment borders, the growing tail; no GPU touched"""
+    _build()
+    out = subprocess.check_output([os.path.join(HOST, "build", "cache_test")], text=True, timeout=60)
+    assert "CACHE_TESTS_OK" in out
+
+
 def test_shim_exports_reference_surface():
     _build()
     out = subprocess.check_output(["nm", "-DC", "--defined-only", os.path.join(HOST, "libadacom_host.so")], text=True)
