@@ -36,6 +36,15 @@ def test_hot_vector_cache_cpu():
     assert "CACHE_TESTS_OK" in out
 
 
+def test_column_data_over_host_resident_segments_cpu():
+    """ColumnData driven like DuckDB drives the reference over segments that live on the host (adaptive mode, nothing
+    uploaded): appends with NULLs and selection vectors, scans across segment borders, FetchRow / FetchRows, catalog
+    accounting; no GPU touched"""
+    _build()
+    out = subprocess.check_output([os.path.join(HOST, "build", "host_resident_test")], text=True, timeout=120)
+    assert "HOST_RESIDENT_TESTS_OK" in out
+
+
 def test_shim_exports_reference_surface():
     _build()
     out = subprocess.check_output(["nm", "-DC", "--defined-only", os.path.join(HOST, "libadacom_host.so")], text=True)
