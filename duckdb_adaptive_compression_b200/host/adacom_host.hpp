@@ -362,7 +362,9 @@ public:
 	idx_t type_size;
 	ColumnSegmentType segment_type = ColumnSegmentType::TRANSIENT;
 	idx_t start;
-	idx_t count = 0;
+	//! values in the segment; atomic like SegmentBase::count of the reference (src/include/duckdb/storage/table/
+	//! segment_base.hpp): a reader that sees the new count also sees the values an append wrote before it
+	std::atomic<idx_t> count {0};
 	idx_t num_elements = 0;
 	CompressionFunction *function;
 	SegmentStatistics stats;
@@ -542,7 +544,7 @@ public:
 	PhysicalType type;
 	idx_t start;
 	int device;
-	idx_t version = 0;
+	std::atomic<idx_t> version {0};
 	idx_t pending_limit = 64;  // sealed segments staged on the host before a batch is uploaded (16 MiB)
 	bool hot_segments_on_host = true;  // Uncompact() brings the flat block of a (hot) segment back to host memory
 	std::vector<unique_ptr<ColumnSegment>> segments;
@@ -555,6 +557,13 @@ public:
 	};
 	std::vector<Batch> batches;
 	std::mutex lock;
+	//! guards the STRUCTURE of `segments` (the reference's SegmentTree::node_lock): an append that opens a new segment
+	//! may move the vector's array under a reader.  Leaf lock, held only for the look-up or the push_back (never while
+	//! `lock` is waited for; `lock` may be held when it is taken).  Segments are never removed, so the pointers a
+	//! look-up returns stay valid.
+	mutable std::mutex tree_lock;
+	//! the segments as they are now (pointers stay valid; the vector itself may grow behind the snapshot)
+	std::vector<ColumnSegment *> SegmentSnapshot() const;
 
 private:
 	struct CachedVector {

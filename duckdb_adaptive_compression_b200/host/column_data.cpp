@@ -48,7 +48,10 @@ void ColumnData::AppendTransientSegment(idx_t start_row) {
 	auto segment = ColumnSegment::CreateTransientSegment(db, type, start_row);
 	segment->column_data = this;
 	segment->device = device;
-	segments.push_back(std::move(segment));
+	{
+		std::lock_guard<std::mutex> tree_guard(tree_lock);
+		segments.push_back(std::move(segment));
+	}
 	version++;
 }
 
@@ -78,12 +81,23 @@ void ColumnData::AppendData(ColumnAppendState &state, UnifiedVectorFormat &vdata
 	}
 }
 
+std::vector<ColumnSegment *> ColumnData::SegmentSnapshot() const {
+	std::lock_guard<std::mutex> tree_guard(tree_lock);
+	std::vector<ColumnSegment *> snapshot(segments.size());
+	for (idx_t i = 0; i < segments.size(); i++) {
+		snapshot[i] = segments[i].get();
+	}
+	return snapshot;
+}
+
 idx_t ColumnData::GetMaxEntry() const {
+	std::lock_guard<std::mutex> tree_guard(tree_lock);
 	return segments.empty() ? 0 : segments.back()->start + segments.back()->count - segments.front()->start;
 }
 
 ColumnSegment *ColumnData::GetSegment(idx_t row_idx) const {
 	// SegmentTree::GetSegment: binary search over the segment starts
+	std::lock_guard<std::mutex> tree_guard(tree_lock);
 	auto it = std::upper_bound(segments.begin(), segments.end(), row_idx,
 	                           [](idx_t row, const unique_ptr<ColumnSegment> &s) { return row < s->start; });
 	if (it == segments.begin()) {
@@ -97,6 +111,7 @@ ColumnSegment *ColumnData::GetSegment(idx_t row_idx) const {
 }
 
 static ColumnSegment *NextSegment(const ColumnData &col, ColumnSegment *current) {
+	std::lock_guard<std::mutex> tree_guard(col.tree_lock);
 	auto it = std::lower_bound(col.segments.begin(), col.segments.end(), current->start,
 	                           [](const unique_ptr<ColumnSegment> &s, idx_t row) { return s->start < row; });
 	while (it != col.segments.end() && it->get() != current) {
@@ -109,7 +124,10 @@ static ColumnSegment *NextSegment(const ColumnData &col, ColumnSegment *current)
 }
 
 void ColumnData::InitializeScan(ColumnScanState &state) {
-	state.current = segments.empty() ? nullptr : segments.front().get();
+	{
+		std::lock_guard<std::mutex> tree_guard(tree_lock);
+		state.current = segments.empty() ? nullptr : segments.front().get();
+	}
 	state.row_index = state.current ? state.current->start : 0;
 	state.internal_index = state.row_index;
 	state.initialized = false;
@@ -305,7 +323,8 @@ void ColumnData::FetchRows(const row_t *row_ids, idx_t count, Vector &result) {
 	if (result.buffer.size() < count * S) {
 		result.buffer.resize(count * S);
 	}
-	if (segments.empty()) {
+	const std::vector<ColumnSegment *> segs = SegmentSnapshot();
+	if (segs.empty()) {
 		throw InternalException("ColumnData::FetchRows: empty column");
 	}
 	struct Group {
@@ -315,13 +334,13 @@ void ColumnData::FetchRows(const row_t *row_ids, idx_t count, Vector &result) {
 	};
 	std::vector<Group> groups;
 	ColumnFetchState fetch_state;
-	const idx_t cap = segments.front()->SegmentSize() / S;
+	const idx_t cap = segs.front()->SegmentSize() / S;
 	idx_t last_group = 0;
 	for (idx_t i = 0; i < count; i++) {
 		const idx_t row = (idx_t)row_ids[i];
 		// segments are full except the open one: guess by division, fall back to the tree search
-		idx_t guess = std::min<idx_t>((row - start) / cap, segments.size() - 1);
-		ColumnSegment *seg = segments[guess].get();
+		idx_t guess = std::min<idx_t>((row - start) / cap, segs.size() - 1);
+		ColumnSegment *seg = segs[guess];
 		if (row < seg->start || row >= seg->start + seg->count) {
 			seg = GetSegment(row);
 			if (row >= seg->start + seg->count) {

@@ -45,6 +45,27 @@ def test_column_data_over_host_resident_segments_cpu():
     assert "HOST_RESIDENT_TESTS_OK" in out
 
 
+def test_host_shim_under_thread_sanitizer_cpu(tmp_path):
+    """readers (point reads through the hot-vector cache, FetchRow, full scans with zero-copy vectors, catalog read
+    counters) against a writer that appends to the same ColumnData and opens new segments, built with -fsanitize=thread
+    over the shim's own sources; any report fails.  (Found and fixed with it: the segment vector could move under a
+    reader while an append opened a segment; count and version are atomics like SegmentBase::count in the reference.)"""
+    exe = str(tmp_path / "race_tsan")
+    probe = subprocess.run(["g++", "-fsanitize=thread", "-x", "c++", "-", "-o", str(tmp_path / "probe")],
+                           input="int main(){return 0;}", text=True, capture_output=True)
+    if probe.returncode != 0:
+        pytest.skip("no ThreadSanitizer runtime in this toolchain")
+    csrc = os.path.join(os.path.dirname(HOST), "csrc")
+    subprocess.check_call(["g++", "-O1", "-g", "-std=c++14", "-pthread", "-fsanitize=thread", "-o", exe,
+                           os.path.join(HOST, "tests", "race_test.cpp"), os.path.join(HOST, "succinct_gpu.cpp"),
+                           os.path.join(HOST, "column_data.cpp"), os.path.join(HOST, "column_segment_catalog.cpp"),
+                           "-L" + csrc, "-ladacom_gpu", "-Wl,-rpath," + csrc])
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300,
+                       env=dict(os.environ, TSAN_OPTIONS="halt_on_error=0 exitcode=66"))
+    assert r.returncode == 0 and "RACE_TEST_OK" in r.stdout, (r.stdout[-500:], r.stderr[-2000:])
+    assert "ThreadSanitizer" not in r.stderr, r.stderr[-2000:]
+
+
 def test_shim_exports_reference_surface():
     _build()
     out = subprocess.check_output(["nm", "-DC", "--defined-only", os.path.join(HOST, "libadacom_host.so")], text=True)
