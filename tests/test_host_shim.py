@@ -66,6 +66,26 @@ def test_host_shim_under_thread_sanitizer_cpu(tmp_path):
     assert "ThreadSanitizer" not in r.stderr, r.stderr[-2000:]
 
 
+@pytest.mark.parametrize("name", ["cache_test", "host_resident_test"])
+def test_host_shim_under_address_sanitizer_cpu(tmp_path, name):
+    """the CPU drivers of the shim again, built with -fsanitize=address,undefined over the shim's own sources (leak
+    detection on): ColumnData over host-resident segments and the hot-vector cache"""
+    probe = subprocess.run(["g++", "-fsanitize=address,undefined", "-x", "c++", "-", "-o", str(tmp_path / "probe")],
+                           input="int main(){return 0;}", text=True, capture_output=True)
+    if probe.returncode != 0:
+        pytest.skip("no AddressSanitizer runtime in this toolchain")
+    exe = str(tmp_path / (name + "_asan"))
+    csrc = os.path.join(os.path.dirname(HOST), "csrc")
+    subprocess.check_call(["g++", "-O1", "-g", "-std=c++14", "-pthread", "-fsanitize=address,undefined",
+                           "-fno-sanitize-recover=undefined", "-o", exe, os.path.join(HOST, "tests", name + ".cpp"),
+                           os.path.join(HOST, "succinct_gpu.cpp"), os.path.join(HOST, "column_data.cpp"),
+                           os.path.join(HOST, "column_segment_catalog.cpp"), "-L" + csrc, "-ladacom_gpu",
+                           "-Wl,-rpath," + csrc])
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300,
+                       env=dict(os.environ, ASAN_OPTIONS="detect_leaks=1:protect_shadow_gap=0"))
+    assert r.returncode == 0 and "_OK" in r.stdout, (r.stdout[-500:], r.stderr[-2000:])
+
+
 def test_shim_exports_reference_surface():
     _build()
     out = subprocess.check_output(["nm", "-DC", "--defined-only", os.path.join(HOST, "libadacom_host.so")], text=True)
