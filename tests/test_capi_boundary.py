@@ -42,6 +42,19 @@ def test_no_cpu_fallback_without_a_device():
     assert "no CPU fallback" in str(e.value)
 
 
+def test_null_handles_are_refused_before_any_cuda_call():
+    """argument validation of the entry points added this round needs no device: a NULL context / column is
+    ADACOM_ERR_INVALID, never a crash and never a silent success"""
+    lib = _capi.load()
+    out = C.c_void_p()
+    assert lib.adacom_device_alloc(None, 64, C.byref(out)) == _capi.ERR_INVALID
+    lib.adacom_device_free(None, None)
+    agg = _capi.Agg()
+    assert lib.adacom_scan_select(None, 0, 0, 0, None, 0, 0, None, 0, None, None, C.byref(agg)) == _capi.ERR_INVALID
+    assert lib.adacom_scan_sum_valid(None, 0, 0, 0, None, 0, C.byref(agg)) == _capi.ERR_INVALID
+    assert lib.adacom_fetch_rows(None, 0, None, None, 0, None, 0) == _capi.ERR_INVALID
+
+
 def test_product_never_references_the_oracle():
     for dirpath, _, files in os.walk(PKG):
         if "build" in dirpath:
