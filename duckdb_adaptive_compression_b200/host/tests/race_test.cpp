@@ -68,6 +68,17 @@ int main() {
 				col.FetchRow(fstate, (row_t)row, result, 1);
 				errors += ((const int64_t *)FlatVector::GetData(result))[1] != values[row];
 				db.column_segment_catalog.AddReadAccess(col.GetSegment(row));
+				if ((rng() & 7) == 0) {  // a batch of row ids (snapshot of the segment vector while the writer grows it)
+					row_t ids[16];
+					for (auto &id : ids) {
+						id = (row_t)(rng() % n);
+					}
+					Vector many(PhysicalType::INT64);
+					col.FetchRows(ids, 16, many);
+					for (int k = 0; k < 16; k++) {
+						errors += ((const int64_t *)FlatVector::GetData(many))[k] != values[ids[k]];
+					}
+				}
 			}
 		});
 	}
